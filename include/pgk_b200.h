@@ -1,0 +1,230 @@
+/*
+ * pgk_b200.h -- C ABI of libpgk_b200.so: the B200 (sm_100a) decode hot path behind
+ * PyGPUkit's operator API.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; every pointer is a DEVICE pointer unless the
+ *     parameter name starts with `host_`.  Arguments are borrowed, never retained.
+ *   - every op is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default
+ *     stream) and returns 0 on success, non-zero on failure; pgk_last_error() then holds a
+ *     message of the form "<fn> failed: <cudaGetErrorString>" (the reference's
+ *     std::runtime_error text, native/ops/common/error.cuh:28-37).
+ *   - bf16 / f16 tensors are 16-bit storage, row-major contiguous; "u8" tensors carry
+ *     FP8-E4M3 codes or packed NVF4 (E2M1) nibbles.
+ *   - each entry point cites the reference interface it replaces (paths relative to the
+ *     PyGPUkit tree).
+ */
+#ifndef PGK_B200_H
+#define PGK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ runtime
+ * replaces native/core/{memory,stream,event,cuda_graph,device}.cpp as bound by
+ * native/bindings/core_bindings.cpp:29-509 */
+const char* pgk_last_error(void);
+int pgk_version(void);
+int pgk_device_count(int* count);
+int pgk_device_set(int device);
+int pgk_device_get(int* device);
+typedef struct {
+    char name[128];
+    int sm_count;
+    int cc_major, cc_minor;
+    size_t total_mem;
+    size_t l2_bytes;
+    int max_smem_per_block;
+} pgk_device_props_t;
+int pgk_device_props(int device, pgk_device_props_t* out);
+int pgk_device_sync(void);
+int pgk_mem_info(size_t* free_bytes, size_t* total_bytes);
+
+int pgk_malloc(void** ptr, size_t bytes);            /* memory.cpp:29 cuMemAlloc */
+int pgk_free(void* ptr);
+int pgk_host_alloc(void** host_ptr, size_t bytes);   /* pinned host memory */
+int pgk_host_free(void* host_ptr);
+int pgk_memset(void* ptr, int value, size_t bytes, void* stream);
+int pgk_memcpy_h2d(void* dst, const void* host_src, size_t bytes, void* stream);
+int pgk_memcpy_d2h(void* host_dst, const void* src, size_t bytes, void* stream);
+int pgk_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
+
+int pgk_stream_create(void** stream);                /* native/core/stream.cpp */
+int pgk_stream_destroy(void* stream);
+int pgk_stream_sync(void* stream);
+int pgk_event_create(void** event);                  /* native/core/event.cpp */
+int pgk_event_destroy(void* event);
+int pgk_event_record(void* event, void* stream);
+int pgk_event_sync(void* event);
+int pgk_event_elapsed_ms(void* start, void* stop, float* ms);
+
+/* CUDA-graph capture of a decode step: native/core/cuda_graph.cpp, used by
+ * llm/decode/m1_graph.py:248-457 */
+int pgk_graph_begin(void* stream);
+int pgk_graph_end(void* stream, void** graph_exec);
+int pgk_graph_launch(void* graph_exec, void* stream);
+int pgk_graph_destroy(void* graph_exec);
+
+/* programmatic dependent launch on/off for all subsequent launches (default off) */
+int pgk_set_pdl(int enabled);
+/* number of kernels this library has launched since load (or since reset) */
+int64_t pgk_launch_count(void);
+void pgk_launch_count_reset(void);
+/* write >L2-size scratch so the next kernel starts with a cold L2 (bench hygiene) */
+int pgk_flush_l2(void* stream);
+
+/* ------------------------------------------------------------------ W8A16 FP8 GEMV
+ * C[M,N] = A[M,K] . dequant(B[N,K])^T,  B = FP8-E4M3 codes, S = bf16 [ceil(N/128), ceil(K/128)].
+ * replaces gemv_fp8_bf16 / gemv_fp8_bf16_batched: ops/matmul/gemv.py:73-195,
+ * native/bindings/gemv/fp8xfp8_bf16.cpp:27-58, launch_gemv_fp8_opt(_batched)
+ * fp8_opt_kernels.cu:15-69.  Weights are read ONCE for all M rows. */
+int pgk_gemv_fp8_bf16(const void* A, const void* B_nk, const void* S, void* C, int M, int K,
+                      int N, void* stream);
+/* fused variants used by the llm layers (same math, reference rounding points kept):
+ *   residual != NULL : C = bf16( bf16(acc) + residual )        (add_inplace, elementwise_kernels.cuh:381-390)
+ *   bias     != NULL : C = bf16( bf16(acc) + bias[n] )         (bias_add,   elementwise_kernels.cuh:57-68) */
+int pgk_gemv_fp8_bf16_ex(const void* A, const void* B_nk, const void* S, void* C, int M, int K,
+                         int N, const void* bias, const void* residual, void* stream);
+/* C[M,I] = bf16( bf16(silu(bf16(A.Wg^T))) * bf16(A.Wu^T) ): gate/up GEMV + silu + mul
+ * (models/causal.py:489-514, activation_kernels.cuh:164-171, elementwise_kernels.cuh:429-438) */
+int pgk_gemv_fp8_swiglu_bf16(const void* A, const void* Wg_nk, const void* Sg, const void* Wu_nk,
+                             const void* Su, void* C, int M, int K, int N, void* stream);
+
+/* W8A16 GEMM with the reference's [K,N] weight layout: C[M,N] = A[M,K] . dequant(B[K,N]),
+ * S = bf16 [ceil(K/128), ceil(N/128)].  replaces pygpukit_w8a16_gemm_sm120
+ * (w8a16_gemm.cu:417-456, ops/matmul/w8a16.py:38-119). */
+int pgk_w8a16_gemm(const void* A, const void* B_kn, const void* S, void* C, int M, int K, int N,
+                   void* stream);
+
+/* ------------------------------------------------------------------ NVF4 (W4A16)
+ * C[M,N] = alpha * A[M,K] . dequant(B), B_data u8 [K/2, N] (low nibble = even k),
+ * B_scale u8 UE4M3 [ceil(K/32), N].  replaces pygpukit_gemv_nvf4_bf16 (nvf4.cu:161-178,
+ * ops/matmul/nvf4.py:132-194). */
+int pgk_gemv_nvf4_bf16(const void* A, const void* B_data, const void* B_scale, void* C, int M,
+                       int K, int N, float alpha, void* stream);
+int pgk_gemv_nvf4_bf16_ex(const void* A, const void* B_data, const void* B_scale, void* C, int M,
+                          int K, int N, float alpha, const void* bias, const void* residual,
+                          void* stream);
+/* gate/up GEMV + SiLU*up on ONE fused weight tensor: Wgu_data u8 [K/2, 2I], Wgu_scale
+ * [K/32, 2I] whose columns are gate/up interleaved in groups of 8
+ * ([g0..g7, u0..u7, g8..g15, u8..]); N2 = 2I, C = [M, I].  The layout is produced by
+ * pygpukit_b200.llm.layers.LinearNVF4.fuse_gate_up (net-new: the reference has no NVF4 MLP). */
+int pgk_gemv_nvf4_swiglu_bf16(const void* A, const void* Wgu_data, const void* Wgu_scale, void* C,
+                              int M, int K, int N2, void* stream);
+/* BF16 [K,N] row-major -> NVF4 data/scale, bit-exact with quantize_bf16_to_nvf4_kernel
+ * (nvf4_kernels.cu:239-324; ops/matmul/nvf4.py:32-77). */
+int pgk_quantize_bf16_to_nvf4(const void* in_kn, void* out_data, void* out_scale, int K, int N,
+                              void* stream);
+
+/* ------------------------------------------------------------------ BF16 GEMV
+ * C[M,N] = A[M,K] . B[N,K]^T (lm_head, router).  replaces pygpukit_gemv_bf16_opt
+ * (bf16_opt.cu:36-47, ops/matmul/gemv.py:15-70). */
+int pgk_gemv_bf16(const void* A, const void* B_nk, void* C, int M, int K, int N, void* stream);
+int pgk_gemv_bf16_ex(const void* A, const void* B_nk, void* C, int M, int K, int N,
+                     const void* bias, const void* residual, void* stream);
+/* lm_head + greedy sampling: logits (optional, may be NULL) and argmax token (int32,
+ * first maximum wins as np.argmax: llm/sampling.py:59-61). */
+int pgk_gemv_bf16_argmax(const void* A, const void* B_nk, void* logits, int32_t* token, int K,
+                         int N, void* stream);
+
+/* ------------------------------------------------------------------ norm / rope / glue
+ * dtype codes: 0 = f32, 1 = f16, 2 = bf16 */
+int pgk_rmsnorm(const void* x, const void* gamma, void* y, int rows, int features, float eps,
+                int dtype, void* stream);                    /* norm/rmsnorm.inl:9-57 */
+int pgk_layernorm(const void* x, const void* gamma, const void* beta, void* y, int rows,
+                  int features, float eps, int dtype, void* stream); /* norm/layernorm.inl */
+/* y = rmsnorm(x + residual) (sum NOT written back): fused_kernels.cuh:36-220 */
+int pgk_rmsnorm_residual(const void* x, const void* residual, const void* gamma, void* y, int rows,
+                         int features, float eps, int dtype, void* stream);
+/* NeoX half-split rotation in place; cos/sin [seq, head_dim] (table_dtype 0 = f32 table,
+ * otherwise same dtype as q/k): rope/rope_inplace.inl:8-149 */
+int pgk_rope_inplace(void* q, void* k, const void* cos, const void* sin, int seq, int n_heads_q,
+                     int n_heads_k, int head_dim, int dtype, int table_dtype, void* stream);
+int pgk_silu(const void* x, void* y, size_t n, int dtype, void* stream);
+int pgk_gelu(const void* x, void* y, size_t n, int dtype, void* stream);
+int pgk_swiglu(const void* gate, const void* up, void* y, size_t n, int dtype, void* stream);
+int pgk_add(const void* a, const void* b, void* c, size_t n, int dtype, void* stream);
+int pgk_mul(const void* a, const void* b, void* c, size_t n, int dtype, void* stream);
+int pgk_add_inplace(void* a, const void* b, size_t n, int dtype, void* stream);
+int pgk_mul_inplace(void* a, const void* b, size_t n, int dtype, void* stream);
+int pgk_bias_add_inplace(void* x, const void* bias, int rows, int features, int dtype,
+                         void* stream);
+int pgk_cast(const void* src, void* dst, size_t n, int src_dtype, int dst_dtype, void* stream);
+int pgk_embedding_lookup(const void* table, void* out, int hidden, int token, int elem_bytes,
+                         void* stream);                      /* embedding_kernels.cuh:27-60 */
+int pgk_embedding_lookup_ptr(const void* table, void* out, int hidden, const int32_t* token_buf,
+                             int n_tokens, int elem_bytes, void* stream);
+int pgk_argmax(const void* logits, int32_t* out, int n, int dtype, void* stream);
+/* transpose [d0,d1,d2] -> [d1,d0,d2] (transpose_3d_021) */
+int pgk_transpose_021(const void* in, void* out, int d0, int d1, int d2, int elem_bytes,
+                      void* stream);
+
+/* KV cache: new_kv [seq, n_kv, hd] -> cache [num_heads_out, max_seq, hd] at position pos..pos+seq-1.
+ * num_heads_out == n_kv writes the un-expanded cache; num_heads_out = G*n_kv replicates each KV
+ * head G times (the reference's GQA-expanded layout, kv_cache_kernels.cuh:176-421).  pos_buf != NULL
+ * reads the position from device memory (the `_ptr` variant). */
+int pgk_kv_cache_update(const void* new_kv, void* cache, int seq, int n_kv, int num_heads_out,
+                        int head_dim, int max_seq, int pos, const int32_t* pos_buf, int elem_bytes,
+                        void* stream);
+
+/* fused decode bracket (q_len == 1): per head QK-RMSNorm (optional, gamma NULL = off), RoPE from f32
+ * tables at position *pos_buf (or pos), K/V written into the un-expanded cache
+ * [n_kv, max_seq, hd].  Same rounding points as rmsnorm -> rope_inplace_f32table ->
+ * kv_cache_update_gqa (layers/attention.py:326-351). qkv = [.., (Hq + 2*Hkv) * hd] bf16, M rows
+ * are M consecutive positions of one sequence. */
+int pgk_qk_norm_rope_kv_write(void* qkv, const void* q_gamma, const void* k_gamma, float eps,
+                              const float* cos_table, const float* sin_table, void* k_cache,
+                              void* v_cache, int M, int n_heads_q, int n_kv, int head_dim,
+                              int max_seq, int pos, const int32_t* pos_buf, void* stream);
+
+/* ------------------------------------------------------------------ attention
+ * softmax(Q K^T * scale) V over the first context_len cache rows, causal offset
+ * kv_len - q_len for q_len > 1.  Q [Hq, q_len, hd] (q_stride_h/q_stride_t in elements allow
+ * reading straight out of a qkv row), K/V cache [n_kv, max_seq, hd] (n_kv == Hq is the
+ * reference's expanded layout), out [Hq, q_len, hd].  Split-KV flash-decoding with an
+ * in-kernel last-block combine.  replaces sdpa_causal_fixed_cache(_ptr)
+ * (sdpa_causal.inl:736-769, flash_decoding.cuh:75-377).  ctx_buf != NULL reads context_len
+ * from device memory. */
+int pgk_sdpa_decode(const void* Q, const void* K, const void* V, void* out, int n_heads_q,
+                    int n_kv, int q_len, int head_dim, int max_seq, int context_len,
+                    const int32_t* ctx_buf, float scale, long q_stride_h, long q_stride_t,
+                    long o_stride_h, long o_stride_t, int dtype, void* stream);
+size_t pgk_sdpa_workspace_bytes(int n_heads_q, int q_len, int head_dim, int max_context);
+
+/* ------------------------------------------------------------------ MoE (config 4)
+ * native/bindings/moe.cpp:43-223, native/ops/moe/{topk,permute,moe}_kernels.cuh; bf16 data */
+int pgk_moe_topk(const void* logits, void* values, int32_t* indices, int num_tokens,
+                 int num_experts, int k, int dtype, void* stream);      /* topk_kernels.cuh:69-186 */
+int pgk_moe_softmax_topk(void* values, int num_tokens, int k, int dtype, void* stream); /* :192-256 */
+/* counts [E], offsets [E+1], permute [T*k], reverse [T*k] (permute_kernels.cuh:21-88,245-256) */
+int pgk_moe_compute_permutation(const int32_t* expert_indices, int32_t* expert_counts,
+                                int32_t* expert_offsets, int32_t* permute_indices,
+                                int32_t* reverse_perm, int num_tokens, int num_experts, int k,
+                                void* stream);
+int pgk_moe_expand_expert_offsets(const int32_t* expert_offsets, int32_t* row_expert_ids,
+                                  int num_experts, int m_total, void* stream); /* moe_kernels.cuh:236-259 */
+int pgk_moe_gather(const void* hidden, const int32_t* permute_indices, void* gathered,
+                   int num_tokens, int hidden_size, int k, void* stream);      /* permute_kernels.cuh:95-182 */
+int pgk_moe_scatter(const void* expert_out, const void* router_weights, const int32_t* reverse_perm,
+                    void* output, int num_tokens, int hidden_size, int k, void* stream); /* :218-242 */
+/* row m of A[M,K] uses expert row_expert_ids[m] of B[E,N,K] (FP8) / S[E,N/128,K/128]:
+ * grouped_gemm_fp8_bf16 (ops/matmul/grouped.py:36-131, grouped_gemm.cu:77-201) */
+int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C,
+                             const int32_t* row_expert_ids, int M, int K, int N, void* stream);
+
+/* ------------------------------------------------------------------ tensor parallel (NCCL)
+ * net-new (the reference is single-GPU): one communicator per process. unique id is 128 bytes. */
+int pgk_nccl_unique_id(void* host_id128);
+int pgk_nccl_init(const void* host_id128, int rank, int world);
+int pgk_nccl_allreduce_bf16(void* buf, size_t count, void* stream);
+int pgk_nccl_allgather(const void* send, void* recv, size_t bytes_per_rank, void* stream);
+int pgk_nccl_destroy(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PGK_B200_H */

@@ -1,0 +1,314 @@
+// attention.cu -- split-KV flash-decoding over a fixed KV cache (q_len small), GQA-aware.
+//
+//   out[h, t, :] = softmax_j( Q[h,t,:] . K[kv(h), j, :] * scale ) V[kv(h), j, :],
+//   j < context_len - q_len + t + 1
+//
+// replaces sdpa_causal_fixed_cache(_ptr) -> sdpa_causal_dispatch (sdpa_causal.inl:452-769):
+// the naive sdpa_causal_*_kernel (attention_kernels.cuh:32-705, one thread per KV position,
+// scores in shared memory, fails past 12k context) and the FP16-only two-kernel
+// flash_decoding (flash_decoding.cuh:75-377).
+//
+// Design (HBM-bound; DESIGN.md "sdpa_decode"):
+//   * the cache is read in its UN-expanded [n_kv, max_seq, hd] form: one CTA serves all
+//     G = Hq/n_kv query heads of a KV head (in row tiles of RT), so K/V bytes are fetched
+//     once per group instead of G times (the reference stores and reads the expanded copy).
+//   * split-KV: `splits` CTAs per (kv head, row tile) each take a contiguous chunk computed
+//     from the DEVICE-side context length (graph-replay safe), keep an online-softmax state
+//     per query row in registers, and write (o, m, l) partials to an f32 workspace; the
+//     last-arriving CTA folds them in split order (deterministic) and writes the output.
+//   * K/V rows are loaded with 128-bit coalesced loads (16 lanes cover one 256-byte bf16
+//     row, two positions per warp iteration, two iterations in flight).
+#include "common.cuh"
+#include "../../include/pgk_b200.h"
+
+namespace pgk {
+
+template <int DT> struct KvVec;   // 16-byte vector of EPL elements -> f32
+template <> struct KvVec<0> {
+    static constexpr int EPL = 4;
+    static __device__ __forceinline__ void unpack(const uint4& v, float* f) {
+        f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y); f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+    }
+};
+template <> struct KvVec<1> {
+    static constexpr int EPL = 8;
+    static __device__ __forceinline__ void unpack(const uint4& v, float* f) {
+        const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { float2 t = __half22float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+    }
+};
+template <> struct KvVec<2> {
+    static constexpr int EPL = 8;
+    static __device__ __forceinline__ void unpack(const uint4& v, float* f) {
+        f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+        f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+    }
+};
+template <int DT> __device__ __forceinline__ float ld_elem(const void* p, size_t i);
+template <> __device__ __forceinline__ float ld_elem<0>(const void* p, size_t i) { return ((const float*)p)[i]; }
+template <> __device__ __forceinline__ float ld_elem<1>(const void* p, size_t i) { return __half2float(((const __half*)p)[i]); }
+template <> __device__ __forceinline__ float ld_elem<2>(const void* p, size_t i) { return __bfloat162float(((const __nv_bfloat16*)p)[i]); }
+template <int DT> __device__ __forceinline__ void st_elem(void* p, size_t i, float v);
+template <> __device__ __forceinline__ void st_elem<0>(void* p, size_t i, float v) { ((float*)p)[i] = v; }
+template <> __device__ __forceinline__ void st_elem<1>(void* p, size_t i, float v) { ((__half*)p)[i] = __float2half_rn(v); }
+template <> __device__ __forceinline__ void st_elem<2>(void* p, size_t i, float v) { ((__nv_bfloat16*)p)[i] = __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ uint4 ldg_kv(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
+struct SdpaParams {
+    const void* Q; const void* K; const void* V; void* out;
+    int hq, n_kv, q_len, max_seq, context_len;
+    const int32_t* ctx_buf;
+    float scale_log2;         // scale * log2(e)
+    long q_sh, q_st, o_sh, o_st;
+    int splits;
+    float* ws;                // [(kvh*row_tiles + rt)*splits + s][RT][HD+2]
+    unsigned* counters;       // [n_kv*row_tiles]
+};
+
+constexpr int kAttnWarps = 4;
+constexpr float kNegBig = -1e30f;
+
+template <int DT, int HD, int RT>
+__global__ void __launch_bounds__(kAttnWarps * 32)
+sdpa_decode_kernel(SdpaParams p) {
+    constexpr int EPL = KvVec<DT>::EPL;
+    constexpr int LPR = HD / EPL;          // lanes per KV row
+    constexpr int PPI = 32 / LPR;          // positions per warp iteration
+    constexpr int REC = HD + 2;            // partial record: o[HD], m, l
+    static_assert(LPR <= 32 && PPI >= 1, "head_dim too large for one warp row");
+    __shared__ float sm_part[kAttnWarps][RT][REC];
+    __shared__ unsigned s_ticket;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int li = lane % LPR, slot = lane / LPR;
+    const int G = p.hq / p.n_kv;
+    const int R = G * p.q_len;
+    const int row_tiles = (R + RT - 1) / RT;
+    const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z;
+
+    griddep_launch();
+    griddep_wait();
+    const int ctx = min(p.ctx_buf ? *p.ctx_buf : p.context_len, p.max_seq);
+    int chunk = (ctx + p.splits - 1) / p.splits;
+    chunk = (chunk + 31) & ~31;
+    const int c0 = split * chunk, c1 = min(ctx, c0 + chunk);
+
+    // query rows of this tile: this lane's EPL-slice, pre-scaled by scale*log2(e)
+    float q[RT][EPL];
+    int limit[RT];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        int row = rt * RT + r;
+        if (row < R) {
+            int g = row / p.q_len, t = row % p.q_len;
+            const size_t qo = (size_t)(kvh * G + g) * p.q_sh + (size_t)t * p.q_st + (size_t)li * EPL;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) q[r][e] = ld_elem<DT>(p.Q, qo + e) * p.scale_log2;
+            limit[r] = ctx - p.q_len + t + 1;
+        } else {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) q[r][e] = 0.f;
+            limit[r] = 0;
+        }
+    }
+    float m[RT], l[RT], o[RT][EPL];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        m[r] = kNegBig; l[r] = 0.f;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) o[r][e] = 0.f;
+    }
+
+    const size_t esz = (DT == 0) ? 4 : 2;
+    const uint8_t* Kb = (const uint8_t*)p.K + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
+    const uint8_t* Vb = (const uint8_t*)p.V + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
+    constexpr int STEP = kAttnWarps * PPI;
+    for (int j0 = c0 + warp * PPI + slot; j0 < c1 + STEP; j0 += 2 * STEP) {
+        // two positions in flight per lane
+        const int ja = j0, jb = j0 + STEP;
+        const bool va = ja < c1, vb = jb < c1;
+        if (!__any_sync(0xffffffffu, va)) break;
+        uint4 ka, kb, wa, wb;
+        if (va) { ka = ldg_kv(Kb + (size_t)ja * HD * esz); wa = ldg_kv(Vb + (size_t)ja * HD * esz); }
+        if (vb) { kb = ldg_kv(Kb + (size_t)jb * HD * esz); wb = ldg_kv(Vb + (size_t)jb * HD * esz); }
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+            const bool valid = it ? vb : va;
+            const int j = it ? jb : ja;
+            float kf[EPL], vf[EPL];
+            if (valid) { KvVec<DT>::unpack(it ? kb : ka, kf); KvVec<DT>::unpack(it ? wb : wa, vf); }
+            else {
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
+            }
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+                float s = 0.f;
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) s = fmaf(q[r][e], kf[e], s);
+#pragma unroll
+                for (int off = LPR / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+                if (valid && j < limit[r]) {
+                    float mn = fmaxf(m[r], s);
+                    float corr = exp2f(m[r] - mn), pj = exp2f(s - mn);
+                    l[r] = fmaf(l[r], corr, pj);
+#pragma unroll
+                    for (int e = 0; e < EPL; ++e) o[r][e] = fmaf(o[r][e], corr, pj * vf[e]);
+                    m[r] = mn;
+                }
+            }
+        }
+    }
+    // merge the PPI slots of the warp (lanes li, li+LPR, ...)
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+#pragma unroll
+        for (int off = LPR; off < 32; off <<= 1) {
+            float m2 = __shfl_xor_sync(0xffffffffu, m[r], off);
+            float l2 = __shfl_xor_sync(0xffffffffu, l[r], off);
+            float mn = fmaxf(m[r], m2);
+            float c1s = exp2f(m[r] - mn), c2s = exp2f(m2 - mn);
+            l[r] = l[r] * c1s + l2 * c2s;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) {
+                float o2 = __shfl_xor_sync(0xffffffffu, o[r][e], off);
+                o[r][e] = o[r][e] * c1s + o2 * c2s;
+            }
+            m[r] = mn;
+        }
+        if (slot == 0) {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) sm_part[warp][r][li * EPL + e] = o[r][e];
+            if (li == 0) { sm_part[warp][r][HD] = m[r]; sm_part[warp][r][HD + 1] = l[r]; }
+        }
+    }
+    __syncthreads();
+    // merge the warps of the CTA -> partial record
+    const size_t tile_id = (size_t)kvh * row_tiles + rt;
+    float* rec = p.ws + (tile_id * p.splits + split) * RT * REC;
+    for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
+        int r = idx / HD, d = idx % HD;
+        float mn = kNegBig;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) mn = fmaxf(mn, sm_part[w][r][HD]);
+        float ov = 0.f, lv = 0.f;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) {
+            float c = exp2f(sm_part[w][r][HD] - mn);
+            ov = fmaf(sm_part[w][r][d], c, ov);
+            lv = fmaf(sm_part[w][r][HD + 1], c, lv);
+        }
+        if (p.splits == 1) {
+            int row = rt * RT + r;
+            if (row < R) {
+                int g = row / p.q_len, t = row % p.q_len;
+                st_elem<DT>(p.out, (size_t)(kvh * G + g) * p.o_sh + (size_t)t * p.o_st + d, lv > 0.f ? ov / lv : 0.f);
+            }
+        } else {
+            __stcg(rec + r * REC + d, ov);
+            if (d == 0) { __stcg(rec + r * REC + HD, mn); __stcg(rec + r * REC + HD + 1, lv); }
+        }
+    }
+    if (p.splits == 1) return;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_ticket = atomicAdd(p.counters + tile_id, 1u);
+    __syncthreads();
+    if (s_ticket != (unsigned)(p.splits - 1)) return;
+    __threadfence();
+    const float* base = p.ws + tile_id * p.splits * RT * REC;
+    for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
+        int r = idx / HD, d = idx % HD;
+        int row = rt * RT + r;
+        if (row >= R) continue;
+        float mn = kNegBig;
+        for (int s = 0; s < p.splits; ++s) mn = fmaxf(mn, __ldcg(base + ((size_t)s * RT + r) * REC + HD));
+        float ov = 0.f, lv = 0.f;
+        for (int s = 0; s < p.splits; ++s) {
+            const float* rr = base + ((size_t)s * RT + r) * REC;
+            float c = exp2f(__ldcg(rr + HD) - mn);
+            ov = fmaf(__ldcg(rr + d), c, ov);
+            lv = fmaf(__ldcg(rr + HD + 1), c, lv);
+        }
+        int g = row / p.q_len, t = row % p.q_len;
+        st_elem<DT>(p.out, (size_t)(kvh * G + g) * p.o_sh + (size_t)t * p.o_st + d, lv > 0.f ? ov / lv : 0.f);
+    }
+    if (threadIdx.x == 0) p.counters[tile_id] = 0;
+}
+
+static float* g_attn_ws = nullptr;
+static unsigned* g_attn_cnt = nullptr;
+static const size_t kAttnWsBytes = 64ull << 20;
+static const int kAttnMaxTiles = 16384;
+
+template <int DT, int HD>
+static int launch_sdpa(SdpaParams p, cudaStream_t st) {
+    constexpr int RT = 4;
+    const int G = p.hq / p.n_kv, R = G * p.q_len;
+    const int row_tiles = (R + RT - 1) / RT;
+    const int base_ctas = p.n_kv * row_tiles;
+    // enough CTAs for ~2 per SM, at least 256 positions per split
+    int hint = p.context_len > 0 ? p.context_len : p.max_seq;
+    int splits = (2 * sm_count() + base_ctas - 1) / base_ctas;
+    int max_splits = (hint + 255) / 256;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    if (splits > 256) splits = 256;
+    PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * RT * (HD + 2) * 4 <= kAttnWsBytes,
+                "sdpa_causal_fixed_cache failed: workspace too small for %d heads x %d rows", p.hq, p.q_len);
+    if (!g_attn_ws) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(st, &cs);
+        PGK_REQUIRE(cs == cudaStreamCaptureStatusNone,
+                    "sdpa_causal_fixed_cache failed: first call must happen outside graph capture (workspace allocation)");
+        PGK_CUDA(cudaMalloc(&g_attn_ws, kAttnWsBytes));
+        PGK_CUDA(cudaMalloc(&g_attn_cnt, kAttnMaxTiles * sizeof(unsigned)));
+        PGK_CUDA(cudaMemset(g_attn_cnt, 0, kAttnMaxTiles * sizeof(unsigned)));
+    }
+    p.splits = splits;
+    p.ws = g_attn_ws;
+    p.counters = g_attn_cnt;
+    PGK_CUDA(launch(sdpa_decode_kernel<DT, HD, RT>, dim3(splits, row_tiles, p.n_kv), dim3(kAttnWarps * 32), 0, st, p));
+    return 0;
+}
+
+}  // namespace pgk
+
+using namespace pgk;
+
+extern "C" {
+
+int pgk_sdpa_decode(const void* Q, const void* K, const void* V, void* out, int n_heads_q, int n_kv, int q_len,
+                    int head_dim, int max_seq, int context_len, const int32_t* ctx_buf, float scale,
+                    long q_stride_h, long q_stride_t, long o_stride_h, long o_stride_t, int dtype, void* stream) {
+    PGK_REQUIRE(n_kv > 0 && n_heads_q % n_kv == 0, "sdpa_causal_fixed_cache failed: n_heads %d not a multiple of n_kv_heads %d", n_heads_q, n_kv);
+    PGK_REQUIRE(q_len >= 1, "sdpa_causal_fixed_cache failed: q_len must be >= 1");
+    PGK_REQUIRE(ctx_buf || (context_len >= 1 && context_len <= max_seq),
+                "sdpa_causal_fixed_cache failed: context_len %d out of range (max_seq_len %d)", context_len, max_seq);
+    PGK_REQUIRE(((uintptr_t)K % 16 == 0) && ((uintptr_t)V % 16 == 0), "sdpa_causal_fixed_cache failed: K/V must be 16-byte aligned");
+    if (scale <= 0.f) scale = 1.0f / sqrtf((float)head_dim);   // sdpa_causal.inl:464-467
+    SdpaParams p = {};
+    p.Q = Q; p.K = K; p.V = V; p.out = out;
+    p.hq = n_heads_q; p.n_kv = n_kv; p.q_len = q_len; p.max_seq = max_seq; p.context_len = context_len;
+    p.ctx_buf = ctx_buf;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    p.q_sh = q_stride_h; p.q_st = q_stride_t; p.o_sh = o_stride_h; p.o_st = o_stride_t;
+    cudaStream_t st = (cudaStream_t)stream;
+#define PGK_SDPA(DTV, HDV) if (dtype == DTV && head_dim == HDV) return launch_sdpa<DTV, HDV>(p, st);
+    PGK_SDPA(2, 128) PGK_SDPA(2, 64) PGK_SDPA(1, 128) PGK_SDPA(1, 64) PGK_SDPA(0, 128) PGK_SDPA(0, 64)
+    PGK_SDPA(2, 256) PGK_SDPA(1, 256) PGK_SDPA(2, 32) PGK_SDPA(1, 32) PGK_SDPA(0, 32)
+#undef PGK_SDPA
+    set_error("sdpa_causal_fixed_cache failed: unsupported dtype %d / head_dim %d", dtype, head_dim);
+    return 1;
+}
+
+size_t pgk_sdpa_workspace_bytes(int, int, int, int) { return kAttnWsBytes; }
+
+}  // extern "C"

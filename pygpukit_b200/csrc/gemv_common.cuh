@@ -1,0 +1,109 @@
+// gemv_common.cuh -- pieces shared by the weight-streaming GEMV kernels
+// (gemv_fp8.cu, gemv_nvf4.cu, gemv_bf16.cu).
+#pragma once
+#include "common.cuh"
+
+namespace pgk {
+
+struct GemvCfg {
+    int warps_per_cta;
+    int ctas;
+    int rho;  // rows per warp
+};
+
+// Pick (warps per CTA, CTAs) such that all CTAs are co-resident (one wave) and the rows
+// divide evenly over the warps.  max_ctas_per_sm[wpc] comes from the occupancy calculator.
+inline GemvCfg pick_gemv_cfg(int n_rows, const int* max_ctas_per_sm /* index = warps per CTA, 1..16 */) {
+    const int sms = sm_count();
+    GemvCfg best = {8, sms, (n_rows + sms * 8 - 1) / (sms * 8)};
+    double best_score = -1.0;
+    for (int wpc = 2; wpc <= 16; ++wpc) {
+        for (int c = 1; c <= max_ctas_per_sm[wpc]; ++c) {
+            int W = wpc * c;
+            long total = (long)sms * W;
+            int rho = (int)((n_rows + total - 1) / total);
+            double eff = (double)n_rows / ((double)rho * (double)total);
+            // prefer high efficiency; tie-break toward more resident warps (bytes in flight)
+            // and fewer, larger CTAs (less activation staging)
+            double score = eff + 0.0004 * (W > 40 ? 40 : W) - 0.0002 * c;
+            if (score > best_score) {
+                best_score = score;
+                best = {wpc, sms * c, rho};
+            }
+        }
+    }
+    return best;
+}
+
+// Stage A[M,K] (bf16) into shared memory as range-shifted f16.  Layout per row: four planes
+// [K/32 chunks][8 halves], plane p holding k%32 in [8p, 8p+8), so that the consumer's
+// per-lane 16-byte reads (lane = chunk) are bank-conflict free.
+// PLANES = false keeps the natural k order (used by the column-parallel NVF4 kernel).
+template <int M, bool PLANES = true>
+__device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict__ A, int K,
+                                                      __half* a_s, float* inv_s, uint32_t* red) {
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int nvec = K >> 3;  // 16-byte vectors per row
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    uint32_t mx[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) mx[m] = 0;
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
+        for (int j = tid; j < nvec; j += nthr) {
+            uint4 v = __ldg(src + j);
+            uint32_t t = __vmaxu2(__vmaxu2(v.x & 0x7fff7fffu, v.y & 0x7fff7fffu),
+                                  __vmaxu2(v.z & 0x7fff7fffu, v.w & 0x7fff7fffu));
+            mx[m] = max(mx[m], max(t & 0xffffu, t >> 16));
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx[m] = max(mx[m], __shfl_xor_sync(0xffffffffu, mx[m], o));
+        if (lane == 0) red[m * 16 + warp] = mx[m];
+    }
+    __syncthreads();
+    float mult[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        uint32_t v = 0;
+        for (int w = 0; w < nwarp; ++w) v = max(v, red[m * 16 + w]);
+        int e = (int)(v >> 7);           // biased bf16/f32 exponent of max|a|
+        e = min(max(e, 15), 254);        // keep both 2^(141-e) and 2^(e-141) normal
+        if ((v >> 7) == 255) e = 141;    // inf/nan present: no rescale, let it propagate
+        mult[m] = __uint_as_float((uint32_t)(268 - e) << 23);       // 2^(141-e)
+        if (tid == 0) inv_s[m] = __uint_as_float((uint32_t)(e - 14) << 23);  // 2^(e-141)
+    }
+    const int nchunk = K >> 5;
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
+        uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)m * K);
+        for (int j = tid; j < nvec; j += nthr) {
+            uint4 v = __ldg(src + j);
+            uint4 o;
+            __half2 h;
+            h = __floats2half2_rn(bf16lo(v.x) * mult[m], bf16hi(v.x) * mult[m]); o.x = *reinterpret_cast<uint32_t*>(&h);
+            h = __floats2half2_rn(bf16lo(v.y) * mult[m], bf16hi(v.y) * mult[m]); o.y = *reinterpret_cast<uint32_t*>(&h);
+            h = __floats2half2_rn(bf16lo(v.z) * mult[m], bf16hi(v.z) * mult[m]); o.z = *reinterpret_cast<uint32_t*>(&h);
+            h = __floats2half2_rn(bf16lo(v.w) * mult[m], bf16hi(v.w) * mult[m]); o.w = *reinterpret_cast<uint32_t*>(&h);
+            dst[PLANES ? ((j & 3) * nchunk + (j >> 2)) : j] = o;
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float silu_ref(float x) {
+    // silu_bf16_kernel: x / (1 + expf(-x)) in f32 (activation_kernels.cuh:40-42)
+    return x / (1.0f + __expf(-x));
+}
+
+struct GemvEpilogue {
+    const uint16_t* bias;      // [N] bf16 or null
+    const uint16_t* residual;  // [M,N] bf16 or null
+};
+
+
+}  // namespace pgk

@@ -1,0 +1,294 @@
+// gemv_fp8.cu -- W8A16 GEMV for decode batch 1..8 on B200 (sm_100a), CUDA cores only.
+//
+//   C[M,N] = A[M,K] . dequant(B[N,K])^T      B = FP8-E4M3 codes, S = bf16 [N/128, K/128]
+//
+// replaces gemv_fp8_warp_reduce_vec4_kernel / _batched_kernel
+// (native/ops/matmul/gemv/w8a16_bf16/sm120/fp8_opt.cuh:133-295).
+//
+// Design (HBM-bound; see DESIGN.md "gemv_fp8"):
+//   * one wave: every warp of the grid is resident at once and owns `rho` consecutive
+//     weight rows; the host picks (warps/CTA, CTAs/SM) so that N / (rho * warps) ~ 1.
+//   * weights stream with 256-bit ld.global.nc.L1::no_allocate.L2::evict_first loads (LDG.E.NA.EFL2.256), four
+//     256-bit loads in flight per lane; they are read ONCE for all M activation rows.
+//   * dequantisation in registers: F2FP.F16.E4M3.UNPACK_B turns two codes into an exact
+//     f16x2; the product with the activation is the mixed-precision FHFMA
+//     (fma.rn.f32.f16: exact product, f32 accumulate) -- 1.5 instructions per weight.
+//     Activations are staged once per CTA in shared memory as f16 after an exact
+//     power-of-two rescale (bf16 has 8 significant bits, f16 holds 11; the per-row shift
+//     puts max|a| at 2^14 so every element within 2^-28 of the maximum converts exactly).
+//   * the 128x128 block scale is applied per 32-weight chunk in f32:
+//     acc += scale * sum(chunk), so no rounding of LUT*scale is involved.
+//   * epilogues keep the reference's rounding points (bias, residual add, SiLU*up).
+//   * PDL: the first weight loads are issued before griddepcontrol.wait.
+#include "common.cuh"
+#include "gemv_common.cuh"
+#include "../../include/pgk_b200.h"
+
+#include <mutex>
+#include <unordered_map>
+
+namespace pgk {
+
+constexpr int kUnroll = 4;
+
+// 8 e4m3 weights (two 32-bit words) x 8 staged f16 activations (one uint4)
+__device__ __forceinline__ void dot8_e4m3(float& s0, float& s1, uint32_t w0, uint32_t w1, const uint4& a) {
+    uint32_t h;
+    h = e4m3x2_to_f16x2_lo(w0); fhfma_f16_lo(s0, h, a.x); fhfma_f16_hi(s1, h, a.x);
+    h = e4m3x2_to_f16x2_hi(w0); fhfma_f16_lo(s0, h, a.y); fhfma_f16_hi(s1, h, a.y);
+    h = e4m3x2_to_f16x2_lo(w1); fhfma_f16_lo(s0, h, a.z); fhfma_f16_hi(s1, h, a.z);
+    h = e4m3x2_to_f16x2_hi(w1); fhfma_f16_lo(s0, h, a.w); fhfma_f16_hi(s1, h, a.w);
+}
+// sum over 32 weights (one 256-bit load) x 32 staged activations (4 planes)
+__device__ __forceinline__ float dot32_e4m3(const u32x8& w, const uint4* ap, int nchunk, int c) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) dot8_e4m3(s0, s1, w.v[2 * p], w.v[2 * p + 1], ap[p * nchunk + c]);
+    return s0 + s1;
+}
+
+// NMAT = 1: plain GEMV; NMAT = 2: gate/up pair with SiLU*up epilogue.
+template <int M, int NMAT>
+__global__ void __launch_bounds__(512)
+gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
+                const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
+                const uint16_t* __restrict__ S1, uint16_t* __restrict__ C, int K, int N, int rho,
+                GemvEpilogue epi) {
+    constexpr int U = (NMAT == 2) ? 2 : kUnroll;   // 256-bit loads in flight per lane per matrix
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __half* a_s = reinterpret_cast<__half*>(smem_raw);
+    float* inv_s = reinterpret_cast<float*>(smem_raw + (size_t)M * K * 2);
+    uint32_t* red = reinterpret_cast<uint32_t*>(inv_s + 8);
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpc = blockDim.x >> 5;
+    const long gwarp = (long)blockIdx.x * wpc + warp;
+    const int row_begin = (int)min((long)N, gwarp * rho);
+    const int row_end = (int)min((long)N, gwarp * rho + rho);
+    const int nchunk = K >> 5;
+    const int SK = (K + 127) >> 7;
+
+    u32x8 w[NMAT][U];
+    auto load_group = [&](int n, int cb) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            int c = cb + lane + 32 * u;
+            if (c < nchunk) {
+                w[0][u] = ldg_stream256(B0 + (size_t)n * K + (size_t)c * 32);
+                if (NMAT == 2) w[NMAT - 1][u] = ldg_stream256(B1 + (size_t)n * K + (size_t)c * 32);
+            }
+        }
+    };
+    // weights never depend on the previous kernel: start pulling the first row now
+    if (row_begin < row_end) load_group(row_begin, 0);
+    griddep_launch();
+    griddep_wait();
+    stage_activations_f16<M>(A, K, a_s, inv_s, red);
+
+    const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
+    bool preloaded = true;
+    for (int n = row_begin; n < row_end; ++n) {
+        float acc[NMAT][M];
+#pragma unroll
+        for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+            for (int m = 0; m < M; ++m) acc[t][m] = 0.f;
+        const uint16_t* s0 = S0 + (size_t)(n >> 7) * SK;
+        const uint16_t* s1 = (NMAT == 2) ? S1 + (size_t)(n >> 7) * SK : nullptr;
+        for (int cb = 0; cb < nchunk; cb += 32 * U) {
+            if (!preloaded) load_group(n, cb);
+            preloaded = false;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                int c = cb + lane + 32 * u;
+                if (c < nchunk) {
+                    float sc0 = bf16_bits_to_f32(__ldg(s0 + (c >> 2)));
+                    float sc1 = (NMAT == 2) ? bf16_bits_to_f32(__ldg(s1 + (c >> 2))) : 0.f;
+#pragma unroll
+                    for (int m = 0; m < M; ++m) {
+                        const uint4* ap = a_lo + (size_t)m * (K >> 3);
+                        acc[0][m] = fmaf(dot32_e4m3(w[0][u], ap, nchunk, c), sc0, acc[0][m]);
+                        if (NMAT == 2)
+                            acc[NMAT - 1][m] = fmaf(dot32_e4m3(w[NMAT - 1][u], ap, nchunk, c), sc1, acc[NMAT - 1][m]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+            for (int m = 0; m < M; ++m) acc[t][m] = warp_sum(acc[t][m]);
+        if (lane == 0) {
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                float v = acc[0][m] * inv_s[m];
+                size_t o = (size_t)m * N + n;
+                if (NMAT == 2) {
+                    float g = round_bf16(v);
+                    float u = round_bf16(acc[NMAT - 1][m] * inv_s[m]);
+                    float s = round_bf16(silu_ref(g));
+                    C[o] = f32_to_bf16_bits(s * u);
+                } else {
+                    if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
+                    C[o] = epi.residual ? hadd_bf16_bits(v, epi.residual[o]) : f32_to_bf16_bits(v);
+                }
+            }
+        }
+    }
+}
+
+// Generic fallback (any K, any alignment): warp per row, byte loads, exact LUT semantics
+// including 0x7F/0xFF -> +-480 (fp8.cuh:89,121).
+template <int NMAT>
+__global__ void gemv_fp8_generic_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
+                                        const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
+                                        const uint16_t* __restrict__ S1, uint16_t* __restrict__ C,
+                                        int M, int K, int N, GemvEpilogue epi) {
+    griddep_launch();
+    griddep_wait();
+    const int lane = threadIdx.x & 31;
+    const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= (long)N * M) return;
+    const int n = (int)(gw % N), m = (int)(gw / N);
+    const int SK = (K + 127) >> 7;
+    float acc0 = 0.f, acc1 = 0.f;
+    for (int k = lane; k < K; k += 32) {
+        float a = bf16_bits_to_f32(A[(size_t)m * K + k]);
+        float s = bf16_bits_to_f32(S0[(size_t)(n >> 7) * SK + (k >> 7)]);
+        acc0 = fmaf(a, fp8_e4m3_to_f32(B0[(size_t)n * K + k]) * s, acc0);
+        if (NMAT == 2) {
+            float s2 = bf16_bits_to_f32(S1[(size_t)(n >> 7) * SK + (k >> 7)]);
+            acc1 = fmaf(a, fp8_e4m3_to_f32(B1[(size_t)n * K + k]) * s2, acc1);
+        }
+    }
+    acc0 = warp_sum(acc0);
+    if (NMAT == 2) acc1 = warp_sum(acc1);
+    if (lane == 0) {
+        size_t o = (size_t)m * N + n;
+        float v = acc0;
+        if (NMAT == 2) {
+            float g = round_bf16(v), u = round_bf16(acc1);
+            C[o] = f32_to_bf16_bits(round_bf16(silu_ref(g)) * u);
+        } else {
+            if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
+            C[o] = epi.residual ? hadd_bf16_bits(v, epi.residual[o]) : f32_to_bf16_bits(v);
+        }
+    }
+}
+
+template <int M, int NMAT>
+static int launch_fp8(const void* A, const void* B0, const void* S0, const void* B1, const void* S1,
+                      void* C, int K, int N, GemvEpilogue epi, cudaStream_t st) {
+    size_t smem = (size_t)M * K * 2 + 8 * sizeof(float) + 8 * 16 * sizeof(uint32_t);
+    auto kern = gemv_fp8_kernel<M, NMAT>;
+    static std::mutex mu;
+    static std::unordered_map<uint64_t, GemvCfg> cache;
+    static bool attr_set = false;
+    GemvCfg cfg;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!attr_set) {
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            attr_set = true;
+        }
+        uint64_t key = ((uint64_t)(uint32_t)K << 32) | (uint32_t)N;
+        auto it = cache.find(key);
+        if (it == cache.end()) {
+            int occ[17] = {0};
+            for (int wpc = 2; wpc <= 16; ++wpc) {
+                int nb = 0;
+                PGK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, wpc * 32, smem));
+                occ[wpc] = nb;
+            }
+            PGK_REQUIRE(occ[4] > 0, "gemv_fp8_bf16 failed: kernel does not fit (K=%d, M=%d)", K, M);
+            it = cache.emplace(key, pick_gemv_cfg(N, occ)).first;
+        }
+        cfg = it->second;
+    }
+    PGK_CUDA(launch(kern, dim3(cfg.ctas), dim3(cfg.warps_per_cta * 32), smem, st,
+                    (const uint16_t*)A, (const uint8_t*)B0, (const uint16_t*)S0, (const uint8_t*)B1,
+                    (const uint16_t*)S1, (uint16_t*)C, K, N, cfg.rho, epi));
+    return 0;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
+
+// Dispatch over M (activation rows).  M > 4 is processed in slabs of <= 4 rows (weights are
+// re-read once per slab; the tcgen05 skinny GEMM takes over for M >= 16, see gemm_w8a16_tc.cu).
+static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, const void* B1,
+                             const void* S1, void* C, int M, int K, int N, const void* bias,
+                             const void* residual, bool swiglu, cudaStream_t st) {
+    PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_fp8_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
+    const bool fast = (K % 32 == 0) && aligned16(A) && aligned32(B0) && (!swiglu || aligned32(B1)) &&
+                      ((size_t)K * 2 + 1024 <= 200 * 1024);
+    const uint16_t* a = (const uint16_t*)A;
+    uint16_t* c = (uint16_t*)C;
+    if (!fast) {
+        GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
+        long warps = (long)N * M;
+        int block = 256;
+        long grid = (warps * 32 + block - 1) / block;
+        if (swiglu)
+            PGK_CUDA(launch(gemv_fp8_generic_kernel<2>, dim3((unsigned)grid), dim3(block), 0, st, a,
+                            (const uint8_t*)B0, (const uint16_t*)S0, (const uint8_t*)B1,
+                            (const uint16_t*)S1, c, M, K, N, epi));
+        else
+            PGK_CUDA(launch(gemv_fp8_generic_kernel<1>, dim3((unsigned)grid), dim3(block), 0, st, a,
+                            (const uint8_t*)B0, (const uint16_t*)S0, (const uint8_t*)nullptr,
+                            (const uint16_t*)nullptr, c, M, K, N, epi));
+        return 0;
+    }
+    // rows per slab limited by shared memory (M*K*2 bytes) and registers
+    int max_m = 4;
+    while (max_m > 1 && (size_t)max_m * K * 2 + 1024 > 200 * 1024) max_m >>= 1;
+    if (swiglu && max_m > 2) max_m = 2;
+    for (int m0 = 0; m0 < M;) {
+        int mt = M - m0;
+        if (mt > max_m) mt = max_m;
+        GemvEpilogue epi = {(const uint16_t*)bias,
+                            residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr};
+        const uint16_t* am = a + (size_t)m0 * K;
+        uint16_t* cm = c + (size_t)m0 * N;
+        int rc = 0;
+        if (swiglu) {
+            if (mt == 1) rc = launch_fp8<1, 2>(am, B0, S0, B1, S1, cm, K, N, epi, st);
+            else         rc = launch_fp8<2, 2>(am, B0, S0, B1, S1, cm, K, N, epi, st);
+        } else {
+            if (mt == 1)      rc = launch_fp8<1, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
+            else if (mt == 2) rc = launch_fp8<2, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
+            else if (mt == 3) rc = launch_fp8<3, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
+            else              rc = launch_fp8<4, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
+        }
+        if (rc) return rc;
+        m0 += mt;
+    }
+    return 0;
+}
+
+}  // namespace pgk
+
+using namespace pgk;
+
+extern "C" {
+
+int pgk_gemv_fp8_bf16(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N,
+                      void* stream) {
+    return gemv_fp8_dispatch(A, B_nk, S, nullptr, nullptr, C, M, K, N, nullptr, nullptr, false,
+                             (cudaStream_t)stream);
+}
+
+int pgk_gemv_fp8_bf16_ex(const void* A, const void* B_nk, const void* S, void* C, int M, int K,
+                         int N, const void* bias, const void* residual, void* stream) {
+    return gemv_fp8_dispatch(A, B_nk, S, nullptr, nullptr, C, M, K, N, bias, residual, false,
+                             (cudaStream_t)stream);
+}
+
+int pgk_gemv_fp8_swiglu_bf16(const void* A, const void* Wg_nk, const void* Sg, const void* Wu_nk,
+                             const void* Su, void* C, int M, int K, int N, void* stream) {
+    return gemv_fp8_dispatch(A, Wg_nk, Sg, Wu_nk, Su, C, M, K, N, nullptr, nullptr, true,
+                             (cudaStream_t)stream);
+}
+
+}  // extern "C"

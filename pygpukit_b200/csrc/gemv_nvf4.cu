@@ -1,0 +1,385 @@
+// gemv_nvf4.cu -- W4A16 GEMV (PyGPUkit "NVF4": E2M1 nibbles, UE4M3 scale per 32-k block)
+// for decode batch 1..8 on B200 (sm_100a), CUDA cores only.
+//
+//   C[M,N] = alpha * A[M,K] . dequant(B)      B_data u8 [K/2, N] (low nibble = even k),
+//                                             B_scale u8 [ceil(K/32), N]
+//
+// replaces gemv_nvf4_bf16_kernel(_unrolled) (native/ops/matmul/gemv/w4a16_bf16/sm120/
+// nvf4_kernels.cu:19-233), which walks K serially with one thread per column.
+//
+// Design (see DESIGN.md "gemv_nvf4"):
+//   * the reference layout is N-contiguous, so lanes own COLS consecutive columns (one
+//     128-bit / 64-bit load = COLS bytes = COLS columns x 2 k) and K is split three ways:
+//     over the 16 byte-rows of a scale block (in flight together), over the warps of a CTA
+//     and over KS CTAs per 512-column group.  Partial sums meet in shared memory, then in
+//     an f32 workspace that the last-arriving CTA of the group folds in fixed order
+//     (deterministic, no float atomics).
+//   * dequantisation in registers: F2FP.F16.E2M1.UNPACK_B turns one byte into the exact f16
+//     pair (even k, odd k); FHFMA (fma.rn.f32.f16) multiplies by the staged f16 activation
+//     with an exact product and f32 accumulation: 1.5 instructions per weight.
+//   * the UE4M3 block scale is decoded with one shift-add and applied once per 32-k block
+//     (E2M1 x UE4M3 is exact in f32, so this equals the reference's pre-scaled LUT).
+#include "common.cuh"
+#include "gemv_common.cuh"
+#include "../../include/pgk_b200.h"
+
+#include <mutex>
+#include <unordered_map>
+
+namespace pgk {
+
+template <int COLS> struct ColVec;
+template <> struct ColVec<16> {
+    uint32_t w[4];
+    __device__ __forceinline__ void load(const uint8_t* p) {
+        uint4 v = ldg_stream(p);
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+    }
+};
+template <> struct ColVec<8> {
+    uint32_t w[2];
+    __device__ __forceinline__ void load(const uint8_t* p) {
+        asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p));
+    }
+};
+
+// accumulate one byte-row: COLS bytes (COLS columns x (even k, odd k)) against a2 = (a_even, a_odd)
+template <int M, int COLS>
+__device__ __forceinline__ void nvf4_row_fma(float (&part)[M][COLS], const uint32_t* w,
+                                             const uint32_t (&a2)[M]) {
+#pragma unroll
+    for (int q = 0; q < COLS / 4; ++q) {
+        uint32_t h0 = e2m1x2_to_f16x2<0>(w[q]);
+        uint32_t h1 = e2m1x2_to_f16x2<1>(w[q]);
+        uint32_t h2 = e2m1x2_to_f16x2<2>(w[q]);
+        uint32_t h3 = e2m1x2_to_f16x2<3>(w[q]);
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            fhfma_f16_lo(part[m][4 * q + 0], h0, a2[m]); fhfma_f16_hi(part[m][4 * q + 0], h0, a2[m]);
+            fhfma_f16_lo(part[m][4 * q + 1], h1, a2[m]); fhfma_f16_hi(part[m][4 * q + 1], h1, a2[m]);
+            fhfma_f16_lo(part[m][4 * q + 2], h2, a2[m]); fhfma_f16_hi(part[m][4 * q + 2], h2, a2[m]);
+            fhfma_f16_lo(part[m][4 * q + 3], h3, a2[m]); fhfma_f16_hi(part[m][4 * q + 3], h3, a2[m]);
+        }
+    }
+}
+
+struct Nvf4Params {
+    const uint16_t* A;
+    const uint8_t* Bd;
+    const uint8_t* Bs;
+    uint16_t* C;
+    int K, N;            // N = number of weight columns (2*I for the fused gate/up layout)
+    int KS;              // CTAs per column group
+    int bpc;             // scale blocks per CTA
+    float alpha;
+    float* ws;           // [G*KS][M][32*COLS] f32 partials
+    unsigned* counters;  // [G], zero between launches
+    GemvEpilogue epi;
+};
+
+constexpr int kNvf4Hdr = 1024;  // smem header: inv_s[8] floats, reduction scratch
+
+// SWIGLU: columns are gate/up interleaved in groups of 8 ([g0..g7,u0..u7,g8..]); the output
+// has N/2 columns: C = bf16( bf16(silu(bf16(g))) * bf16(u) ).
+template <int M, int COLS, bool SWIGLU>
+__global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
+    constexpr int CW = 32 * COLS;  // columns per warp / per CTA
+    constexpr int RH = 8;          // byte-rows in flight per lane
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* inv_s = reinterpret_cast<float*>(smem_raw);
+    uint32_t* red_u = reinterpret_cast<uint32_t*>(smem_raw + 64);
+    __half* a_s = reinterpret_cast<__half*>(smem_raw + kNvf4Hdr);
+    float* red_f = reinterpret_cast<float*>(smem_raw + kNvf4Hdr);  // aliases a_s after the main loop
+    __shared__ unsigned s_ticket;
+
+    const int K = p.K, N = p.N;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    const int g = blockIdx.x / p.KS, ks = blockIdx.x % p.KS;
+    const int KB = K >> 5;
+    const int kb0 = ks * p.bpc, kb1 = min(KB, kb0 + p.bpc);
+    const int n0 = g * CW + lane * COLS;
+    const bool col_ok = n0 < N;
+
+    // first half-block of weights does not depend on the previous kernel
+    ColVec<COLS> d[RH];
+    int b = kb0 + warp;
+    if (col_ok && b < kb1) {
+#pragma unroll
+        for (int r = 0; r < RH; ++r) d[r].load(p.Bd + (size_t)(b * 16 + r) * N + n0);
+    }
+    griddep_launch();
+    griddep_wait();
+    stage_activations_f16<M, false>(p.A, K, a_s, inv_s, red_u);
+
+    float acc[M][COLS];
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+#pragma unroll
+        for (int j = 0; j < COLS; ++j) acc[m][j] = 0.f;
+
+    const uint32_t* a32 = reinterpret_cast<const uint32_t*>(a_s);
+    bool preloaded = true;
+    for (; b < kb1; b += wpc) {
+        if (col_ok) {
+            float part[M][COLS];
+#pragma unroll
+            for (int m = 0; m < M; ++m)
+#pragma unroll
+                for (int j = 0; j < COLS; ++j) part[m][j] = 0.f;
+            ColVec<COLS> sc;
+            sc.load(p.Bs + (size_t)b * N + n0);
+#pragma unroll
+            for (int half = 0; half < 16 / RH; ++half) {
+                if (!preloaded) {
+#pragma unroll
+                    for (int r = 0; r < RH; ++r)
+                        d[r].load(p.Bd + (size_t)(b * 16 + half * RH + r) * N + n0);
+                }
+                preloaded = false;
+#pragma unroll
+                for (int r = 0; r < RH; ++r) {
+                    uint32_t a2[M];
+#pragma unroll
+                    for (int m = 0; m < M; ++m) a2[m] = a32[(size_t)m * (K >> 1) + b * 16 + half * RH + r];
+                    nvf4_row_fma<M, COLS>(part, d[r].w, a2);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < COLS; ++j) {
+                float s = ue4m3_to_f32((sc.w[j >> 2] >> (8 * (j & 3))) & 0xffu);
+#pragma unroll
+                for (int m = 0; m < M; ++m) acc[m][j] = fmaf(part[m][j], s, acc[m][j]);
+            }
+        }
+        preloaded = false;
+    }
+
+    // ---- CTA reduction over warps (a_s is dead from here on)
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+#pragma unroll
+        for (int j = 0; j < COLS; ++j)
+            red_f[((size_t)warp * M + m) * CW + lane * COLS + j] = acc[m][j];
+    __syncthreads();
+
+    const bool single = (p.KS == 1);
+    float* my_ws = p.ws + (size_t)blockIdx.x * M * CW;
+    if (!single) {
+        for (int t = threadIdx.x; t < M * CW; t += blockDim.x) {
+            float v = 0.f;
+            for (int w = 0; w < wpc; ++w) v += red_f[(size_t)w * M * CW + t];
+            __stcg(my_ws + t, v);
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_ticket = atomicAdd(p.counters + g, 1u);
+        __syncthreads();
+        if (s_ticket != (unsigned)(p.KS - 1)) return;
+        __threadfence();
+    }
+    // ---- final fold (this CTA is the only / the last one of its column group)
+    const float* grp_ws = p.ws + (size_t)g * p.KS * M * CW;
+    auto total = [&](int m, int col) -> float {
+        float v = 0.f;
+        if (single) {
+            for (int w = 0; w < wpc; ++w) v += red_f[((size_t)w * M + m) * CW + col];
+        } else {
+            for (int s = 0; s < p.KS; ++s) v += __ldcg(grp_ws + ((size_t)s * M + m) * CW + col);
+        }
+        return v * inv_s[m];
+    };
+    if (!SWIGLU) {
+        for (int t = threadIdx.x; t < M * CW; t += blockDim.x) {
+            int m = t / CW, col = t % CW, n = g * CW + col;
+            if (n >= N) continue;
+            float v = p.alpha * total(m, col);
+            size_t o = (size_t)m * N + n;
+            if (p.epi.bias) v = round_bf16(v) + bf16_bits_to_f32(p.epi.bias[n]);
+            p.C[o] = p.epi.residual ? hadd_bf16_bits(v, p.epi.residual[o]) : f32_to_bf16_bits(v);
+        }
+    } else {
+        const int I = N >> 1;
+        for (int t = threadIdx.x; t < M * (CW / 2); t += blockDim.x) {
+            int m = t / (CW / 2), j = t % (CW / 2);
+            int cg = 16 * (j >> 3) + (j & 7);
+            int i = g * (CW / 2) + j;
+            if (i >= I) continue;
+            float gate = round_bf16(p.alpha * total(m, cg));
+            float up = round_bf16(p.alpha * total(m, cg + 8));
+            float s = round_bf16(silu_ref(gate));
+            p.C[(size_t)m * I + i] = f32_to_bf16_bits(s * up);
+        }
+    }
+    if (!single && threadIdx.x == 0) p.counters[g] = 0;
+}
+
+// Generic fallback (any K / N / alignment): one thread per (m, column), serial over K in the
+// reference's own order (nvf4_kernels.cu:19-73).
+__global__ void gemv_nvf4_generic_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd,
+                                         const uint8_t* __restrict__ Bs, uint16_t* __restrict__ C, int M,
+                                         int K, int N, float alpha, GemvEpilogue epi) {
+    griddep_launch();
+    griddep_wait();
+    long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (long)M * N) return;
+    int n = (int)(t % N), m = (int)(t / N);
+    float acc = 0.f;
+    for (int k = 0; k < K; k += 2) {
+        float s = ue4m3_to_f32(Bs[(size_t)(k >> 5) * N + n]);
+        uint32_t byte = Bd[(size_t)(k >> 1) * N + n];
+        acc = fmaf(bf16_bits_to_f32(A[(size_t)m * K + k]), e2m1_to_f32(byte & 0xf) * s, acc);
+        if (k + 1 < K)
+            acc = fmaf(bf16_bits_to_f32(A[(size_t)m * K + k + 1]), e2m1_to_f32(byte >> 4) * s, acc);
+    }
+    float v = alpha * acc;
+    size_t o = (size_t)m * N + n;
+    if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
+    C[o] = epi.residual ? hadd_bf16_bits(v, epi.residual[o]) : f32_to_bf16_bits(v);
+}
+
+// ---------------------------------------------------------------- host side
+static float* g_ws = nullptr;
+static unsigned* g_counters = nullptr;
+static const size_t kWsBytes = 48ull << 20;
+static const int kMaxGroups = 4096;
+
+static int ensure_workspace(cudaStream_t st) {
+    if (g_ws) return 0;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cs);
+    PGK_REQUIRE(cs == cudaStreamCaptureStatusNone,
+                "gemv_nvf4_bf16 failed: first call must happen outside graph capture (workspace allocation)");
+    PGK_CUDA(cudaMalloc(&g_ws, kWsBytes));
+    PGK_CUDA(cudaMalloc(&g_counters, kMaxGroups * sizeof(unsigned)));
+    PGK_CUDA(cudaMemset(g_counters, 0, kMaxGroups * sizeof(unsigned)));
+    return 0;
+}
+
+struct Nvf4Cfg { int wpc, KS, bpc; size_t smem; };
+
+template <int M, int COLS, bool SWIGLU>
+static int launch_nvf4(Nvf4Params p, cudaStream_t st) {
+    constexpr int CW = 32 * COLS;
+    auto kern = gemv_nvf4_kernel<M, COLS, SWIGLU>;
+    static std::mutex mu;
+    static std::unordered_map<uint64_t, Nvf4Cfg> cache;
+    static bool attr_set = false;
+    const int G = (p.N + CW - 1) / CW, KB = p.K >> 5;
+    Nvf4Cfg cfg;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!attr_set) {
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            attr_set = true;
+        }
+        uint64_t key = ((uint64_t)(uint32_t)p.K << 32) | (uint32_t)p.N;
+        auto it = cache.find(key);
+        if (it == cache.end()) {
+            const int sms = sm_count();
+            Nvf4Cfg best = {8, 1, KB, 0};
+            double best_score = -1.0;
+            for (int wpc = 2; wpc <= 16; ++wpc) {
+                size_t body = (size_t)M * p.K * 2;
+                size_t redb = (size_t)wpc * M * CW * 4;
+                size_t smem = kNvf4Hdr + (body > redb ? body : redb);
+                if (smem > 227 * 1024) continue;
+                int occ = 0;
+                PGK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, wpc * 32, smem));
+                for (int c = 1; c <= occ; ++c) {
+                    long T = (long)sms * c;
+                    int KS = (int)(T / G);
+                    if (KS < 1) KS = 1;
+                    if (KS > KB) KS = KB;
+                    int bpc = (KB + KS - 1) / KS;
+                    KS = (KB + bpc - 1) / bpc;
+                    int bw = (bpc + wpc - 1) / wpc;
+                    long ctas = (long)G * KS;
+                    long per_sm = (ctas + sms - 1) / sms;
+                    double eff = (double)G * KB / ((double)sms * per_sm * wpc * bw);
+                    int W = (int)(per_sm * wpc);
+                    double score = eff + 0.0004 * (W > 32 ? 32 : W) - 0.0002 * c;
+                    if ((size_t)ctas * M * CW * 4 > kWsBytes || G > kMaxGroups) continue;
+                    if (score > best_score) { best_score = score; best = {wpc, KS, bpc, smem}; }
+                }
+            }
+            PGK_REQUIRE(best_score > 0, "gemv_nvf4_bf16 failed: no launch configuration (K=%d N=%d M=%d)", p.K, p.N, M);
+            it = cache.emplace(key, best).first;
+        }
+        cfg = it->second;
+    }
+    p.KS = cfg.KS;
+    p.bpc = cfg.bpc;
+    p.ws = g_ws;
+    p.counters = g_counters;
+    PGK_CUDA(launch(kern, dim3(G * cfg.KS), dim3(cfg.wpc * 32), cfg.smem, st, p));
+    return 0;
+}
+
+static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C, int M, int K, int N,
+                         float alpha, const void* bias, const void* residual, bool swiglu,
+                         cudaStream_t st) {
+    PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_nvf4_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
+    const bool fast = (K % 32 == 0) && (N % 16 == 0) && al16(A) && al16(Bd) && al16(Bs) &&
+                      ((size_t)K * 2 + kNvf4Hdr <= 200 * 1024);
+    PGK_REQUIRE(fast || !swiglu, "gemv_nvf4_swiglu_bf16 failed: needs K%%32==0, N%%16==0 and 16-byte aligned pointers");
+    const int Nout = swiglu ? N / 2 : N;
+    if (!fast) {
+        GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
+        long tot = (long)M * N;
+        PGK_CUDA(launch(gemv_nvf4_generic_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st,
+                        (const uint16_t*)A, (const uint8_t*)Bd, (const uint8_t*)Bs, (uint16_t*)C, M, K, N,
+                        alpha, epi));
+        return 0;
+    }
+    if (int rc = ensure_workspace(st)) return rc;
+    int max_m = 4;
+    while (max_m > 1 && (size_t)max_m * K * 2 + kNvf4Hdr > 200 * 1024) max_m >>= 1;
+    for (int m0 = 0; m0 < M;) {
+        int mt = M - m0 > max_m ? max_m : M - m0;
+        if (mt == 3) mt = 2;
+        Nvf4Params p = {};
+        p.A = (const uint16_t*)A + (size_t)m0 * K;
+        p.Bd = (const uint8_t*)Bd;
+        p.Bs = (const uint8_t*)Bs;
+        p.C = (uint16_t*)C + (size_t)m0 * Nout;
+        p.K = K; p.N = N; p.alpha = alpha;
+        p.epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr};
+        int rc;
+        if (swiglu) {
+            if (mt == 1)      rc = launch_nvf4<1, 16, true>(p, st);
+            else if (mt == 2) rc = launch_nvf4<2, 16, true>(p, st);
+            else              rc = launch_nvf4<4, 8, true>(p, st);
+        } else {
+            if (mt == 1)      rc = launch_nvf4<1, 16, false>(p, st);
+            else if (mt == 2) rc = launch_nvf4<2, 16, false>(p, st);
+            else              rc = launch_nvf4<4, 8, false>(p, st);
+        }
+        if (rc) return rc;
+        m0 += mt;
+    }
+    return 0;
+}
+
+}  // namespace pgk
+
+using namespace pgk;
+
+extern "C" {
+
+int pgk_gemv_nvf4_bf16(const void* A, const void* B_data, const void* B_scale, void* C, int M, int K,
+                       int N, float alpha, void* stream) {
+    return nvf4_dispatch(A, B_data, B_scale, C, M, K, N, alpha, nullptr, nullptr, false, (cudaStream_t)stream);
+}
+int pgk_gemv_nvf4_bf16_ex(const void* A, const void* B_data, const void* B_scale, void* C, int M, int K,
+                          int N, float alpha, const void* bias, const void* residual, void* stream) {
+    return nvf4_dispatch(A, B_data, B_scale, C, M, K, N, alpha, bias, residual, false, (cudaStream_t)stream);
+}
+int pgk_gemv_nvf4_swiglu_bf16(const void* A, const void* Wgu_data, const void* Wgu_scale, void* C, int M,
+                              int K, int N2, void* stream) {
+    return nvf4_dispatch(A, Wgu_data, Wgu_scale, C, M, K, N2, 1.0f, nullptr, nullptr, true, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,249 @@
+// moe.cu -- MoE routing and expert GEMV for decode (num_tokens <= 64).
+// replaces native/ops/moe/{topk,permute,moe}_kernels.cuh as bound by native/bindings/moe.cpp:43-223
+// and grouped_gemm_tiled_kernel (native/ops/matmul/gemm/w8a16_bf16/sm120/grouped_gemm.cu:77-201).
+// Index work is bit-exact; the permutation is built in ascending flat-index order (one of the
+// orders the reference's atomics can produce; everything downstream is invariant to it).
+#include "common.cuh"
+#include "gemv_common.cuh"
+#include "../../include/pgk_b200.h"
+
+namespace pgk {
+
+template <int DT> __device__ __forceinline__ float mld(const void* p, size_t i);
+template <> __device__ __forceinline__ float mld<0>(const void* p, size_t i) { return ((const float*)p)[i]; }
+template <> __device__ __forceinline__ float mld<1>(const void* p, size_t i) { return __half2float(((const __half*)p)[i]); }
+template <> __device__ __forceinline__ float mld<2>(const void* p, size_t i) { return bf16_bits_to_f32(((const uint16_t*)p)[i]); }
+template <int DT> __device__ __forceinline__ void mst(void* p, size_t i, float v);
+template <> __device__ __forceinline__ void mst<0>(void* p, size_t i, float v) { ((float*)p)[i] = v; }
+template <> __device__ __forceinline__ void mst<1>(void* p, size_t i, float v) { ((__half*)p)[i] = __float2half_rn(v); }
+template <> __device__ __forceinline__ void mst<2>(void* p, size_t i, float v) { ((uint16_t*)p)[i] = f32_to_bf16_bits(v); }
+
+// topk_with_indices_*_kernel topk_kernels.cuh:69-186: k passes of strict '>' argmax (lowest
+// index wins ties).  One warp per token: lane-strided scan + (value, index) shuffle reduce.
+template <int DT>
+__global__ void moe_topk_kernel(const void* __restrict__ logits, void* __restrict__ values,
+                                int32_t* __restrict__ indices, int T, int E, int k) {
+    griddep_launch();
+    griddep_wait();
+    const int lane = threadIdx.x & 31;
+    const int t = (int)(((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (t >= T) return;
+    constexpr int MAXPL = 16;   // up to 512 experts
+    float loc[MAXPL];
+#pragma unroll
+    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? mld<DT>(logits, (size_t)t * E + e) : -INFINITY; }
+    for (int j = 0; j < k; ++j) {
+        float bv = -1e30f;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (bi == 0x7fffffff) bi = 0;
+        if (lane == 0) { mst<DT>(values, (size_t)t * k + j, bv); indices[(size_t)t * k + j] = bi; }
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
+    }
+}
+
+// softmax_topk_*_kernel topk_kernels.cuh:192-256, in place, one thread per token
+template <int DT>
+__global__ void moe_softmax_topk_kernel(void* __restrict__ values, int T, int k) {
+    griddep_launch();
+    griddep_wait();
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    float mx = -INFINITY, sum = 0.f;
+    for (int i = 0; i < k; ++i) mx = fmaxf(mx, mld<DT>(values, (size_t)t * k + i));
+    for (int i = 0; i < k; ++i) sum += __expf(mld<DT>(values, (size_t)t * k + i) - mx);
+    float inv = 1.0f / sum;
+    for (int i = 0; i < k; ++i) {
+        float e = __expf(mld<DT>(values, (size_t)t * k + i) - mx);
+        mst<DT>(values, (size_t)t * k + i, e * inv);
+    }
+}
+
+// count/offsets/permute/reverse in one single-CTA kernel (T*k <= 512 at decode), ascending order.
+__global__ void moe_permutation_kernel(const int32_t* __restrict__ expert_indices, int32_t* __restrict__ counts,
+                                       int32_t* __restrict__ offsets, int32_t* __restrict__ permute,
+                                       int32_t* __restrict__ reverse, int total, int E) {
+    griddep_launch();
+    griddep_wait();
+    for (int e = threadIdx.x; e < E; e += blockDim.x) {
+        int c = 0;
+        for (int i = 0; i < total; ++i) c += (expert_indices[i] == e);
+        counts[e] = c;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int off = 0;
+        for (int e = 0; e < E; ++e) { offsets[e] = off; off += counts[e]; }
+        offsets[E] = off;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < E; e += blockDim.x) {
+        int p = offsets[e];
+        for (int i = 0; i < total; ++i)
+            if (expert_indices[i] == e) { permute[p] = i; reverse[i] = p; ++p; }
+    }
+}
+
+// expand_expert_offsets_kernel moe_kernels.cuh:236-259
+__global__ void moe_expand_offsets_kernel(const int32_t* __restrict__ offsets, int32_t* __restrict__ row_ids, int E,
+                                          int m_total) {
+    griddep_launch();
+    griddep_wait();
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= m_total) return;
+    int lo = 0, hi = E;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (offsets[mid + 1] <= r) lo = mid + 1; else hi = mid; }
+    row_ids[r] = lo;
+}
+
+// gather_hidden_states_* permute_kernels.cuh:95-182: gathered[p] = hidden[permute[p] / k]
+__global__ void moe_gather_kernel(const uint16_t* __restrict__ hidden, const int32_t* __restrict__ permute,
+                                  uint16_t* __restrict__ gathered, int rows, int H, int k) {
+    griddep_launch();
+    griddep_wait();
+    for (int p = blockIdx.x; p < rows; p += gridDim.x) {
+        const uint16_t* src = hidden + (size_t)(permute[p] / k) * H;
+        for (int i = threadIdx.x; i < H; i += blockDim.x) gathered[(size_t)p * H + i] = src[i];
+    }
+}
+
+// scatter_with_reverse_perm_kernel permute_kernels.cuh:218-242: f32 sum over slots 0..k-1
+__global__ void moe_scatter_kernel(const uint16_t* __restrict__ expert_out, const uint16_t* __restrict__ weights,
+                                   const int32_t* __restrict__ reverse, uint16_t* __restrict__ out, int T, int H, int k) {
+    griddep_launch();
+    griddep_wait();
+    for (int t = blockIdx.x; t < T; t += gridDim.x)
+        for (int h = threadIdx.x; h < H; h += blockDim.x) {
+            float sum = 0.f;
+            for (int s = 0; s < k; ++s) {
+                int f = t * k + s;
+                sum = fmaf(bf16_bits_to_f32(weights[f]), bf16_bits_to_f32(expert_out[(size_t)reverse[f] * H + h]), sum);
+            }
+            out[(size_t)t * H + h] = f32_to_bf16_bits(sum);
+        }
+}
+
+// Expert-grouped FP8 GEMV: row m uses expert row_expert_ids[m] of B[E,N,K], S[E,N/128,K/128].
+// One warp per (m, n): 128-bit weight loads, exact f32 products (bf16 activation x decoded
+// e4m3), scale per 128-k block.  K % 16 == 0 fast path, scalar tail otherwise.
+__global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B,
+                                            const uint16_t* __restrict__ S, uint16_t* __restrict__ C,
+                                            const int32_t* __restrict__ row_ids, int M, int K, int N) {
+    griddep_launch();
+    griddep_wait();
+    const int lane = threadIdx.x & 31;
+    const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= (long)M * N) return;
+    const int n = (int)(gw % N), m = (int)(gw / N);
+    const int e = row_ids[m];
+    const int SN = (N + 127) >> 7, SK = (K + 127) >> 7;
+    const uint8_t* brow = B + ((size_t)e * N + n) * K;
+    const uint16_t* srow = S + ((size_t)e * SN + (n >> 7)) * SK;
+    const uint16_t* arow = A + (size_t)m * K;
+    float acc = 0.f;
+    if ((K & 15) == 0) {
+        for (int c = lane; c < (K >> 4); c += 32) {
+            uint4 w = ldg_stream(brow + (size_t)c * 16);
+            uint4 a0 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16));
+            uint4 a1 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16 + 8));
+            float sc = bf16_bits_to_f32(srow[c >> 3]);
+            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+            const uint32_t aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float part = 0.f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t h0 = e4m3x2_to_f16x2_lo(ww[q]), h1 = e4m3x2_to_f16x2_hi(ww[q]);
+                float2 f0 = __half22float2(*reinterpret_cast<__half2*>(&h0));
+                float2 f1 = __half22float2(*reinterpret_cast<__half2*>(&h1));
+                part = fmaf(bf16lo(aa[2 * q]), f0.x, part);
+                part = fmaf(bf16hi(aa[2 * q]), f0.y, part);
+                part = fmaf(bf16lo(aa[2 * q + 1]), f1.x, part);
+                part = fmaf(bf16hi(aa[2 * q + 1]), f1.y, part);
+            }
+            acc = fmaf(part, sc, acc);
+        }
+    } else {
+        for (int k = lane; k < K; k += 32)
+            acc = fmaf(bf16_bits_to_f32(arow[k]), fp8_e4m3_to_f32(brow[k]) * bf16_bits_to_f32(srow[k >> 7]), acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
+}
+
+static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
+
+}  // namespace pgk
+
+using namespace pgk;
+#define ST(s) ((cudaStream_t)(s))
+
+extern "C" {
+
+int pgk_moe_topk(const void* logits, void* values, int32_t* indices, int num_tokens, int num_experts, int k,
+                 int dtype, void* stream) {
+    PGK_REQUIRE(num_experts >= 1 && num_experts <= 512 && k >= 1 && k <= num_experts,
+                "moe_topk_with_indices failed: unsupported num_experts=%d k=%d", num_experts, k);
+    if (num_tokens <= 0) return 0;
+    unsigned g = nblk((size_t)num_tokens * 32, 128);
+    if (dtype == 0) PGK_CUDA(launch(moe_topk_kernel<0>, dim3(g), dim3(128), 0, ST(stream), logits, values, indices, num_tokens, num_experts, k));
+    else if (dtype == 1) PGK_CUDA(launch(moe_topk_kernel<1>, dim3(g), dim3(128), 0, ST(stream), logits, values, indices, num_tokens, num_experts, k));
+    else if (dtype == 2) PGK_CUDA(launch(moe_topk_kernel<2>, dim3(g), dim3(128), 0, ST(stream), logits, values, indices, num_tokens, num_experts, k));
+    else { set_error("moe_topk_with_indices failed: unsupported dtype code %d", dtype); return 1; }
+    return 0;
+}
+int pgk_moe_softmax_topk(void* values, int num_tokens, int k, int dtype, void* stream) {
+    if (num_tokens <= 0) return 0;
+    unsigned g = nblk(num_tokens, 128);
+    if (dtype == 0) PGK_CUDA(launch(moe_softmax_topk_kernel<0>, dim3(g), dim3(128), 0, ST(stream), values, num_tokens, k));
+    else if (dtype == 1) PGK_CUDA(launch(moe_softmax_topk_kernel<1>, dim3(g), dim3(128), 0, ST(stream), values, num_tokens, k));
+    else if (dtype == 2) PGK_CUDA(launch(moe_softmax_topk_kernel<2>, dim3(g), dim3(128), 0, ST(stream), values, num_tokens, k));
+    else { set_error("moe_softmax_topk failed: unsupported dtype code %d", dtype); return 1; }
+    return 0;
+}
+int pgk_moe_compute_permutation(const int32_t* expert_indices, int32_t* expert_counts, int32_t* expert_offsets,
+                                int32_t* permute_indices, int32_t* reverse_perm, int num_tokens, int num_experts,
+                                int k, void* stream) {
+    PGK_CUDA(launch(moe_permutation_kernel, dim3(1), dim3(256), 0, ST(stream), expert_indices, expert_counts,
+                    expert_offsets, permute_indices, reverse_perm, num_tokens * k, num_experts));
+    return 0;
+}
+int pgk_moe_expand_expert_offsets(const int32_t* expert_offsets, int32_t* row_expert_ids, int num_experts,
+                                  int m_total, void* stream) {
+    if (m_total <= 0) return 0;
+    PGK_CUDA(launch(moe_expand_offsets_kernel, dim3(nblk(m_total, 128)), dim3(128), 0, ST(stream), expert_offsets,
+                    row_expert_ids, num_experts, m_total));
+    return 0;
+}
+int pgk_moe_gather(const void* hidden, const int32_t* permute_indices, void* gathered, int num_tokens,
+                   int hidden_size, int k, void* stream) {
+    int rows = num_tokens * k;
+    if (rows <= 0) return 0;
+    PGK_CUDA(launch(moe_gather_kernel, dim3(rows), dim3(256), 0, ST(stream), (const uint16_t*)hidden, permute_indices,
+                    (uint16_t*)gathered, rows, hidden_size, k));
+    return 0;
+}
+int pgk_moe_scatter(const void* expert_out, const void* router_weights, const int32_t* reverse_perm, void* output,
+                    int num_tokens, int hidden_size, int k, void* stream) {
+    if (num_tokens <= 0) return 0;
+    PGK_CUDA(launch(moe_scatter_kernel, dim3(num_tokens), dim3(256), 0, ST(stream), (const uint16_t*)expert_out,
+                    (const uint16_t*)router_weights, reverse_perm, (uint16_t*)output, num_tokens, hidden_size, k));
+    return 0;
+}
+int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C, const int32_t* row_expert_ids,
+                             int M, int K, int N, void* stream) {
+    if (M <= 0) return 0;
+    size_t warps = (size_t)M * N;
+    PGK_CUDA(launch(moe_grouped_gemv_fp8_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream),
+                    (const uint16_t*)A, (const uint8_t*)B_enk, (const uint16_t*)S, (uint16_t*)C, row_expert_ids, M, K, N));
+    return 0;
+}
+
+}  // extern "C"
