@@ -1,0 +1,262 @@
+"""GPU parity: weight-only-quantised GEMV family through the C ABI vs the CPU oracle and vs the
+reference's own CUDA kernels (oracle/_ref/libref_cuda.so) on identical seeded inputs.
+Tolerance (north_star): 2e-3 relative for f32-accumulate GEMV outputs (metric of the reference's
+own tests: max|d|/max|ref|); dequantisation / quantisation bit-exact."""
+import numpy as np
+import pytest
+
+import pygpukit_b200 as gk
+from oracle import oracle as orc
+from oracle import refcuda
+from pygpukit_b200 import ops
+from tests.util import bf16, f32, rand_bf16, rand_fp8_weights, rel_err, ulp_diff_bf16
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-3
+
+# (K, N): reference LLM_CONFIGS (src/pygpukit/benchmark/gemv.py:11-19) scaled to finish on the CPU
+# oracle in seconds + layer shapes of the configs + ragged cases
+FP8_SHAPES = [(4096, 4096), (4096, 1024), (2048, 8192), (14336, 512), (12288, 256), (768, 2048), (2048, 768),
+              (128, 128), (160, 96), (4100, 77), (64, 8)]
+
+
+@pytest.mark.parametrize("K,N", FP8_SHAPES)
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 8])
+def test_gemv_fp8_vs_oracle(K, N, M):
+    if M > 1 and K * N > 4096 * 4096:
+        pytest.skip("oracle time")
+    rng = np.random.default_rng(1234 + K + N + M)
+    codes, scale = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_fp8_bf16(A, codes, scale)
+    gB, gS = gk.from_numpy(codes), gk.from_numpy(scale)
+    if M == 1:
+        out = ops.gemv_fp8_bf16(gk.from_numpy(A[0]), gB, gS).to_numpy()[None]
+    else:
+        out = ops.gemv_fp8_bf16_batched(gk.from_numpy(A), gB, gS).to_numpy()
+    assert rel_err(out, ref) < TOL
+    assert ulp_diff_bf16(out, ref) <= 64          # near-zero outputs may differ by many ulps; most by <= 1
+    assert np.mean(out != ref) < 0.05             # f32 reordering flips few bf16 roundings
+
+
+@pytest.mark.parametrize("K,N", [(4096, 4096), (4096, 1024), (2048, 8192), (128, 128)])
+def test_oracle_vs_reference_cuda_gemv_fp8(K, N):
+    """Pins the oracle: the reference's own kernel on the same inputs must agree BIT FOR BIT with
+    the C restatement (same accumulation order)."""
+    if not refcuda.available():
+        pytest.skip("libref_cuda.so not built")
+    rng = np.random.default_rng(99 + K + N)
+    codes, scale = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (4, K))
+    gA, gB, gS = gk.from_numpy(A), gk.from_numpy(codes), gk.from_numpy(scale)
+    out1 = gk.empty((N,), gk.bfloat16)
+    refcuda.gemv_fp8(gA, gB, gS, out1, K, N)
+    outM = gk.empty((4, N), gk.bfloat16)
+    refcuda.gemv_fp8_batched(gA, gB, gS, outM, K, N, 4)
+    ref = orc.gemv_fp8_bf16(A, codes, scale)
+    assert np.array_equal(out1.to_numpy(), ref[0])
+    assert np.array_equal(outM.to_numpy(), ref)
+    ours = ops.gemv_fp8_bf16_batched(gA, gB, gS).to_numpy()
+    assert rel_err(ours, outM.to_numpy()) < TOL
+
+
+def test_gemv_fp8_large_k_reference_cannot_launch():
+    """K=28672 (Llama-3-70B down_proj): the reference kernel needs 56 KB of dynamic smem without
+    opting in (README.md:451,462); ours runs."""
+    K, N = 28672, 256
+    rng = np.random.default_rng(5)
+    codes, scale = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (1, K))
+    out = ops.gemv_fp8_bf16(gk.from_numpy(A[0]), gk.from_numpy(codes), gk.from_numpy(scale)).to_numpy()
+    assert rel_err(out, orc.gemv_fp8_bf16(A[0], codes, scale)) < TOL
+    if refcuda.available():
+        with pytest.raises(RuntimeError):
+            refcuda.gemv_fp8(gk.from_numpy(A[0]), gk.from_numpy(codes), gk.from_numpy(scale),
+                             gk.empty((N,), gk.bfloat16), K, N)
+
+
+def test_gemv_fp8_epilogues():
+    from pygpukit_b200._lib import api
+    rng = np.random.default_rng(11)
+    K, N, M = 1024, 512, 2
+    codes, scale = rand_fp8_weights(rng, N, K)
+    codes2, scale2 = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (M, K))
+    res = rand_bf16(rng, (M, N), 0.5)
+    bias = rand_bf16(rng, (N,), 0.1)
+    gA, gB, gS = gk.from_numpy(A), gk.from_numpy(codes), gk.from_numpy(scale)
+    gB2, gS2 = gk.from_numpy(codes2), gk.from_numpy(scale2)
+    out = gk.empty((M, N), gk.bfloat16)
+    y = orc.gemv_fp8_bf16(A, codes, scale)
+    # bias then residual, reference rounding points
+    api.gemv_fp8_bf16_ex(gA.device_ptr, gB.device_ptr, gS.device_ptr, out.device_ptr, M, K, N,
+                         gk.from_numpy(bias).device_ptr, gk.from_numpy(res).device_ptr, None)
+    exp = orc.add_inplace_bf16(orc.bias_add_bf16(y, bias), res)
+    assert rel_err(out.to_numpy(), exp) < TOL
+    # gate/up + silu*mul
+    api.gemv_fp8_swiglu_bf16(gA.device_ptr, gB.device_ptr, gS.device_ptr, gB2.device_ptr, gS2.device_ptr,
+                             out.device_ptr, M, K, N, None)
+    u = orc.gemv_fp8_bf16(A, codes2, scale2)
+    exp = orc.mul_inplace_bf16(orc.silu_bf16(y), u)
+    assert rel_err(out.to_numpy(), exp) < 4e-3
+
+
+def test_gemv_fp8_linearity_full_size():
+    """Full benchmark size (no oracle): GEMV(a1 + a2) ~ GEMV(a1) + GEMV(a2), and a unit vector
+    returns one dequantised column exactly."""
+    K, N = 4096, 14336
+    rng = np.random.default_rng(21)
+    codes = rng.integers(0, 0x7E, size=(N, K), dtype=np.uint8) | (rng.integers(0, 2, size=(N, K), dtype=np.uint8) << 7)
+    scale = bf16(rng.uniform(1e-3, 1e-2, (N // 128, K // 128)).astype(np.float32))
+    gB, gS = gk.from_numpy(codes), gk.from_numpy(scale)
+    e = np.zeros(K, np.float32)
+    e[1234] = 1.0
+    col = ops.gemv_fp8_bf16(gk.from_numpy(bf16(e)), gB, gS).to_numpy()
+    from pygpukit_b200.llm.quant import fp8_e4m3_table
+    exp = bf16(fp8_e4m3_table()[codes[:, 1234]] * f32(scale)[:, 1234 // 128].repeat(128))
+    assert np.array_equal(col, exp)
+    a1, a2 = rand_bf16(rng, (K,)), rand_bf16(rng, (K,))
+    s = bf16(f32(a1) + f32(a2))
+    y1 = f32(ops.gemv_fp8_bf16(gk.from_numpy(a1), gB, gS).to_numpy())
+    y2 = f32(ops.gemv_fp8_bf16(gk.from_numpy(a2), gB, gS).to_numpy())
+    ys = f32(ops.gemv_fp8_bf16(gk.from_numpy(s), gB, gS).to_numpy())
+    assert np.abs(ys - (y1 + y2)).max() / np.abs(ys).max() < 2e-2
+
+
+@pytest.mark.parametrize("K,N", [(4096, 1024), (1024, 4096), (2048, 50000), (4096, 151936 // 8), (100, 37)])
+@pytest.mark.parametrize("M", [1, 2, 4])
+def test_gemv_bf16_vs_oracle(K, N, M):
+    rng = np.random.default_rng(77 + K + N + M)
+    B = rand_bf16(rng, (N, K), 0.02)
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_bf16(A, B)
+    if M == 1:
+        out = ops.gemv_bf16(gk.from_numpy(A[0]), gk.from_numpy(B)).to_numpy()[None]
+    else:
+        out = ops.gemv_bf16_batched(gk.from_numpy(A), gk.from_numpy(B)).to_numpy()
+    assert rel_err(out, ref) < TOL
+    if refcuda.available() and M == 1 and K % 8 == 0:
+        o2 = gk.empty((N,), gk.bfloat16)
+        refcuda.gemv_bf16(gk.from_numpy(A[0]), gk.from_numpy(B), o2, K, N)
+        assert np.array_equal(o2.to_numpy(), ref[0])       # oracle pinned on the reference kernel
+
+
+def test_gemv_bf16_argmax_first_max_wins():
+    from pygpukit_b200._lib import api
+    rng = np.random.default_rng(5)
+    K, N = 1024, 40000
+    B = rand_bf16(rng, (N, K), 0.02)
+    B[31000] = B[12345]                       # exact tie between rows 12345 and 31000
+    A = f32(B[12345]) * 40.0                   # makes that row the maximum
+    A = bf16(A.astype(np.float32))
+    gA, gB = gk.from_numpy(A), gk.from_numpy(B)
+    logits = gk.empty((N,), gk.bfloat16)
+    tok = gk.zeros((1,), gk.int32)
+    for _ in range(3):                         # scratch must re-arm between launches
+        api.gemv_bf16_argmax(gA.device_ptr, gB.device_ptr, logits.device_ptr, tok.device_ptr, K, N, None)
+        lg = logits.to_numpy()
+        assert int(tok.to_numpy()[0]) == orc.argmax_bf16(lg) == 12345
+    assert rel_err(lg, orc.gemv_bf16(A, B)) < TOL
+    assert ops.sample_greedy(logits) == 12345
+
+
+NVF4_SHAPES = [(8192, 1024), (2048, 768), (768, 2048), (4096, 512), (1024, 28672 // 4), (64, 48), (96, 40), (34, 7)]
+
+
+def _nvf4_weights(rng, K, N):
+    W = rand_bf16(rng, (K, N), 0.02)
+    return orc.quantize_bf16_to_nvf4(W) if K % 2 == 0 else None, W
+
+
+@pytest.mark.parametrize("K,N", NVF4_SHAPES)
+@pytest.mark.parametrize("M", [1, 2, 4])
+def test_gemv_nvf4_vs_oracle(K, N, M):
+    rng = np.random.default_rng(4321 + K + N + M)
+    (data, scale), _ = _nvf4_weights(rng, K, N)
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_nvf4_bf16(A, data, scale, 0.75)
+    gD, gS = gk.from_numpy(data), gk.from_numpy(scale)
+    if M == 1:
+        out = ops.gemv_nvf4_bf16(gk.from_numpy(A[0]), gD, gS, alpha=0.75).to_numpy()[None]
+    else:
+        out = ops.gemv_nvf4_bf16_batched(gk.from_numpy(A), gD, gS, alpha=0.75).to_numpy()
+    assert rel_err(out, ref) < TOL
+    if refcuda.available() and M == 1:
+        o2 = gk.empty((N,), gk.bfloat16)
+        refcuda.gemv_nvf4(gk.from_numpy(A[0]), gD, gS, o2, K, N, 0.75)
+        assert np.array_equal(o2.to_numpy(), ref[0])       # oracle pinned on the reference kernel
+
+
+@pytest.mark.parametrize("K,N", [(8192, 1024), (4096, 4096), (64, 48), (96, 40), (2048, 768)])
+def test_quantize_nvf4_bit_exact(K, N):
+    rng = np.random.default_rng(8 + K + N)
+    W = rand_bf16(rng, (K, N), 0.02)
+    W[:32, 0] = 0                                            # an all-zero block (scale = 1.0 branch)
+    gW = gk.from_numpy(W)
+    d, s = gk.empty((K // 2, N), gk.uint8), gk.empty(((K + 31) // 32, N), gk.uint8)
+    ops.quantize_bf16_to_nvf4(gW, d, s)
+    od, os_ = orc.quantize_bf16_to_nvf4(W)
+    if refcuda.available():
+        rd, rs = gk.empty((K // 2, N), gk.uint8), gk.empty(((K + 31) // 32, N), gk.uint8)
+        refcuda.quantize_nvf4(gW, rd, rs, K, N)
+        assert np.array_equal(s.to_numpy(), rs.to_numpy())
+        assert np.array_equal(d.to_numpy(), rd.to_numpy())   # bit-exact vs the reference kernel
+        # the IEEE oracle may differ from the fast-math reference only on threshold ties
+        assert np.array_equal(os_, rs.to_numpy())
+        assert np.mean(od != rd.to_numpy()) < 1e-4
+    else:
+        assert np.array_equal(s.to_numpy(), os_)
+        assert np.mean(d.to_numpy() != od) < 1e-4
+
+
+def test_gemv_nvf4_swiglu():
+    from pygpukit_b200._lib import api
+    rng = np.random.default_rng(31)
+    K, I, M = 1024, 768, 2
+    Wg, Wu = rand_bf16(rng, (K, I), 0.03), rand_bf16(rng, (K, I), 0.03)
+    (dg, sg), (du, su) = orc.quantize_bf16_to_nvf4(Wg), orc.quantize_bf16_to_nvf4(Wu)
+
+    def interleave(g, u):                                   # groups of 8 columns: g0..7,u0..7,g8..15,...
+        r = g.shape[0]
+        return np.stack([g.reshape(r, I // 8, 8), u.reshape(r, I // 8, 8)], axis=2).reshape(r, 2 * I)
+    d, s = interleave(dg, du), interleave(sg, su)
+    A = rand_bf16(rng, (M, K))
+    out = gk.empty((M, I), gk.bfloat16)
+    api.gemv_nvf4_swiglu_bf16(gk.from_numpy(A).device_ptr, gk.from_numpy(d).device_ptr, gk.from_numpy(s).device_ptr,
+                              out.device_ptr, M, K, 2 * I, None)
+    g = orc.gemv_nvf4_bf16(A, dg, sg)
+    u = orc.gemv_nvf4_bf16(A, du, su)
+    exp = orc.mul_inplace_bf16(orc.silu_bf16(g), u)
+    assert rel_err(out.to_numpy(), exp) < 4e-3
+
+
+@pytest.mark.parametrize("M,K,N", [(1, 256, 384), (4, 512, 256), (16, 256, 256), (33, 384, 200)])
+def test_w8a16_gemm_kn_layout(M, K, N):
+    rng = np.random.default_rng(M + K + N)
+    codes_nk, scale_nk = rand_fp8_weights(rng, N, K)
+    B_kn = np.ascontiguousarray(codes_nk.T)
+    S_kn = np.ascontiguousarray(scale_nk.T)
+    A = rand_bf16(rng, (M, K))
+    out = ops.w8a16_gemm_sm120(gk.from_numpy(A), gk.from_numpy(B_kn), gk.from_numpy(S_kn)).to_numpy()
+    ref = orc.w8a16_gemm(A, B_kn, S_kn)
+    assert rel_err(out, ref) < (1e-2 if M >= 16 else TOL)   # M>=16: the reference rounds weights to bf16 first
+    if refcuda.available() and K % 128 == 0 and N % 128 == 0:
+        o2 = gk.empty((M, N), gk.bfloat16)
+        refcuda.w8a16_gemm(gk.from_numpy(A), gk.from_numpy(B_kn), gk.from_numpy(S_kn), o2, M, N, K)
+        assert rel_err(o2.to_numpy(), ref) < (1e-2 if M >= 16 else 1e-6)
+
+
+def test_validation_errors_match_reference():
+    a = gk.zeros((64,), gk.bfloat16)
+    b = gk.zeros((32, 64), gk.uint8)
+    s = gk.zeros((1, 1), gk.bfloat16)
+    with pytest.raises(ValueError, match="requires 1D input vector"):
+        ops.gemv_fp8_bf16(gk.zeros((1, 64), gk.bfloat16), b, s)
+    with pytest.raises(ValueError, match="requires uint8"):
+        ops.gemv_fp8_bf16(a, gk.zeros((32, 64), gk.bfloat16), s)
+    with pytest.raises(ValueError, match="dimension mismatch"):
+        ops.gemv_fp8_bf16(gk.zeros((32,), gk.bfloat16), b, s)
+    with pytest.raises(ValueError, match="out shape"):
+        ops.gemv_fp8_bf16(a, b, s, out=gk.zeros((31,), gk.bfloat16))
+    out = gk.zeros((32,), gk.bfloat16)
+    assert ops.gemv_fp8_bf16(a, b, s, out=out) is out

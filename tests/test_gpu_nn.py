@@ -1,0 +1,352 @@
+"""GPU parity: norm / RoPE / KV-cache / attention / glue / MoE routing through the C ABI vs the CPU
+oracle and the reference's own CUDA kernels.  Tolerances: bit-exact for copies and index work,
+<= 1 bf16 ulp for elementwise f32 math (fast-math exp/rsqrt in the reference build),
+1e-2 relative for attention (north_star, BF16)."""
+import numpy as np
+import pytest
+
+import pygpukit_b200 as gk
+from oracle import oracle as orc
+from oracle import refcuda
+from pygpukit_b200 import ops
+from pygpukit_b200._lib import api
+from tests.util import bf16, f32, rand_bf16, rel_err, ulp_diff_bf16
+
+pytestmark = pytest.mark.gpu
+
+
+def test_gpuarray_roundtrip_and_views():
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((4, 96)).astype(np.float32)
+    g = gk.from_numpy(x)
+    assert np.array_equal(g.to_numpy(), x)
+    assert g.shape == (4, 96) and g.dtype == gk.float32 and g.nbytes == x.nbytes and g.ndim == 2
+    v = g.view((2, 192))
+    assert np.array_equal(v.to_numpy(), x.reshape(2, 192))
+    r = gk.from_numpy(x[:1])
+    assert np.array_equal(r.narrow(32, 16).to_numpy(), x[:1, 32:48])
+    assert np.array_equal(g.slice_rows(2).to_numpy(), x[:2])
+    with pytest.raises(ValueError):
+        g.view((5, 5))
+    with pytest.raises(ValueError):
+        g.slice_rows(9)
+    assert np.array_equal(gk.zeros((3, 5), gk.bfloat16).to_numpy(), np.zeros((3, 5), np.uint16))
+    assert np.array_equal(gk.ones((2, 2), gk.bfloat16).to_numpy(), np.full((2, 2), 0x3F80, np.uint16))
+    assert gk.empty((0,), gk.float32).to_numpy().size == 0
+    assert np.array_equal(g.clone().to_numpy(), x)
+    assert np.array_equal(g.astype(gk.bfloat16).to_numpy(), bf16(x))
+
+
+@pytest.mark.parametrize("rows,features", [(1, 4096), (4, 4096), (32, 128), (3, 100), (1, 8192), (2, 2048)])
+def test_rmsnorm_bf16(rows, features):
+    rng = np.random.default_rng(rows + features)
+    x, g = rand_bf16(rng, (rows, features)), bf16(rng.uniform(0.5, 1.5, features).astype(np.float32))
+    out = ops.rmsnorm(gk.from_numpy(x), gk.from_numpy(g), 1e-6).to_numpy()
+    ref = orc.rmsnorm_bf16(x, g, 1e-6)
+    assert ulp_diff_bf16(out, ref) <= 1 and np.mean(out != ref) < 0.02
+    if refcuda.available():
+        y = gk.empty((rows, features), gk.bfloat16)
+        refcuda.rmsnorm_bf16(gk.from_numpy(x), gk.from_numpy(g), y, rows, features, 1e-6)
+        assert ulp_diff_bf16(y.to_numpy(), ref) <= 1 and np.mean(y.to_numpy() != ref) < 0.02
+        assert ulp_diff_bf16(out, y.to_numpy()) <= 1
+
+
+def test_rmsnorm_f32_and_layernorm_f32_golden(golden):
+    out = ops.rmsnorm(gk.from_numpy(golden["rms_x"]), gk.from_numpy(golden["rms_g"]), 1e-6).to_numpy()
+    np.testing.assert_allclose(out, golden["rms_y"], rtol=5e-6, atol=1e-6)
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((5, 768)).astype(np.float32)
+    g, b = rng.uniform(0.5, 1.5, 768).astype(np.float32), rng.standard_normal(768).astype(np.float32)
+    out = ops.layernorm(gk.from_numpy(x), gk.from_numpy(g), gk.from_numpy(b), 1e-5).to_numpy()
+    np.testing.assert_allclose(out, orc.layernorm_f32(x, g, b, 1e-5), rtol=2e-5, atol=2e-5)
+    with pytest.raises(ValueError, match="expects 2D input"):
+        ops.rmsnorm(gk.zeros((8,), gk.float32), gk.zeros((8,), gk.float32))
+    with pytest.raises(ValueError, match="gamma size"):
+        ops.rmsnorm(gk.zeros((2, 8), gk.float32), gk.zeros((4,), gk.float32))
+
+
+def test_rmsnorm_residual():
+    rng = np.random.default_rng(2)
+    x, r = rand_bf16(rng, (3, 512)), rand_bf16(rng, (3, 512))
+    g = bf16(rng.uniform(0.5, 1.5, 512).astype(np.float32))
+    out = f32(ops.rmsnorm_residual(gk.from_numpy(x), gk.from_numpy(r), gk.from_numpy(g), 1e-6).to_numpy())
+    s = f32(x) + f32(r)
+    ref = s / np.sqrt((s.astype(np.float64) ** 2).mean(axis=1, keepdims=True) + 1e-6) * f32(g)
+    assert np.abs(out - ref).max() / np.abs(ref).max() < 6e-3
+
+
+def test_rope_golden_and_bf16(golden):
+    q, k = gk.from_numpy(golden["rope_q"]), gk.from_numpy(golden["rope_k"])
+    ops.rope_inplace(q, k, gk.from_numpy(golden["rope_cos16"][:3]), gk.from_numpy(golden["rope_sin16"][:3]))
+    np.testing.assert_allclose(q.to_numpy(), golden["rope_q_out"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(k.to_numpy(), golden["rope_k_out"], rtol=1e-6, atol=1e-6)
+    from pygpukit_b200.llm.layers import precompute_freqs_cis
+    rng = np.random.default_rng(3)
+    cos, sin = precompute_freqs_cis(128, 64, 1e6)
+    cos, sin = cos[40:43].astype(np.float32), sin[40:43].astype(np.float32)
+    qb, kb = rand_bf16(rng, (3, 32, 128)), rand_bf16(rng, (3, 8, 128))
+    gq, gkk = gk.from_numpy(qb), gk.from_numpy(kb)
+    ops.rope_inplace_f32table(gq, gkk, gk.from_numpy(cos), gk.from_numpy(sin))
+    rq, rk = orc.rope_bf16_f32table(qb, kb, cos, sin)
+    assert ulp_diff_bf16(gq.to_numpy(), rq) <= 1 and np.mean(gq.to_numpy() != rq) < 0.01
+    assert ulp_diff_bf16(gkk.to_numpy(), rk) <= 1
+    if refcuda.available():
+        cq, ck = gk.from_numpy(qb), gk.from_numpy(kb)
+        refcuda.rope_bf16_f32table(cq, ck, gk.from_numpy(cos), gk.from_numpy(sin), 3, 32, 8, 128)
+        assert np.array_equal(cq.to_numpy(), rq) and np.array_equal(ck.to_numpy(), rk)   # oracle pinned
+
+
+def test_kv_cache_update_gqa_bit_exact():
+    rng = np.random.default_rng(4)
+    H, Hkv, hd, S = 32, 8, 128, 64
+    cache0 = rand_bf16(rng, (H, S, hd))
+    new = rand_bf16(rng, (1, Hkv, hd))
+    c = gk.from_numpy(cache0)
+    ops.kv_cache_update_gqa(gk.from_numpy(new), c, H, 17)
+    exp = cache0.copy()
+    orc.kv_cache_update_gqa(new, exp, H, 17)
+    assert np.array_equal(c.to_numpy(), exp)
+    if refcuda.available():
+        c2 = gk.from_numpy(cache0)
+        refcuda.kv_update_gqa_bf16(gk.from_numpy(new), c2, H, Hkv, hd, S, 17)
+        assert np.array_equal(c2.to_numpy(), exp)
+    pos = gk.from_numpy(np.array([33], np.int32))
+    ops.kv_cache_update_gqa_ptr(gk.from_numpy(new), c, H, pos)
+    orc.kv_cache_update_gqa(new, exp, H, 33)
+    assert np.array_equal(c.to_numpy(), exp)
+    seq = rand_bf16(rng, (5, Hkv, hd))
+    ops.kv_cache_prefill_gqa(gk.from_numpy(seq), c, H, 40)
+    orc.kv_cache_update_gqa(seq, exp, H, 40)
+    assert np.array_equal(c.to_numpy(), exp)
+    with pytest.raises(ValueError, match="exceeds max_seq_len"):
+        ops.kv_cache_update_gqa(gk.from_numpy(new), c, H, 64)
+
+
+def _sdpa_case(rng, H, Hkv, q_len, hd, ctx, max_seq, np_dtype):
+    def mk(shape, std):
+        x = (rng.standard_normal(shape) * std).astype(np.float32)
+        return bf16(x) if np_dtype == np.uint16 else x.astype(np_dtype)
+    return mk((H, q_len, hd), 1.0), mk((Hkv, max_seq, hd), 0.1 if hd > 32 else 0.5), mk((Hkv, max_seq, hd), 0.1)
+
+
+def _expand(K, G):
+    return np.ascontiguousarray(np.repeat(K, G, axis=0))
+
+
+@pytest.mark.parametrize("H,Hkv,q_len,hd,ctx,max_seq", [
+    (32, 8, 1, 128, 1, 64), (32, 8, 1, 128, 300, 512), (32, 8, 1, 128, 2048, 2048), (64, 8, 1, 128, 777, 1024),
+    (12, 12, 1, 64, 129, 256), (32, 32, 1, 128, 256, 512), (32, 8, 4, 128, 100, 128), (8, 2, 8, 128, 40, 64),
+    (32, 4, 1, 128, 1500, 2048)])
+@pytest.mark.parametrize("np_dtype", [np.uint16, np.float16, np.float32])
+def test_sdpa_decode_vs_oracle(H, Hkv, q_len, hd, ctx, max_seq, np_dtype):
+    if np_dtype != np.uint16 and ctx > 800:
+        pytest.skip("one dtype is enough for the long cases")
+    rng = np.random.default_rng(H + Hkv + q_len + hd + ctx)
+    Q, K, V = _sdpa_case(rng, H, Hkv, q_len, hd, ctx, max_seq, np_dtype)
+    out = gk.empty((H, q_len, hd), gk.DataType.from_numpy_dtype(np_dtype))
+    ops.sdpa_causal_fixed_cache(gk.from_numpy(Q), gk.from_numpy(K), gk.from_numpy(V), out, ctx)
+    ref = orc.sdpa_causal_fixed_cache(Q, _expand(K, H // Hkv), _expand(V, H // Hkv), ctx)
+    o = out.to_numpy()
+    if np_dtype == np.uint16:
+        assert rel_err(o, ref) < 1e-2
+    else:
+        tol = 2e-3 if np_dtype == np.float16 else 2e-5
+        assert np.abs(o.astype(np.float64) - ref.astype(np.float64)).max() / np.abs(ref.astype(np.float64)).max() < tol
+    # _ptr variant: context length from device memory
+    out2 = gk.empty((H, q_len, hd), out.dtype)
+    ops.sdpa_causal_fixed_cache_ptr(gk.from_numpy(Q), gk.from_numpy(K), gk.from_numpy(V), out2,
+                                    gk.from_numpy(np.array([ctx], np.int32)), max_seq)
+    assert np.array_equal(out2.to_numpy(), o)
+
+
+def test_oracle_vs_reference_cuda_attention():
+    """Pins the attention oracle: reference SDPA (bf16) and flash-decoding (f16) kernels on the
+    harness of benchmarks/test_flash_decoding.py:22-80 (H=32, hd=128, seed 42, FP16, max_diff<0.01)."""
+    if not refcuda.available():
+        pytest.skip("libref_cuda.so not built")
+    rng = np.random.default_rng(42)
+    H, hd, ctx, S = 32, 128, 1300, 2048
+    Qf = rng.standard_normal((H, 1, hd)).astype(np.float16)
+    Kf = (rng.standard_normal((H, S, hd)) * 0.1).astype(np.float16)
+    Vf = (rng.standard_normal((H, S, hd)) * 0.1).astype(np.float16)
+    gQ, gK, gV = gk.from_numpy(Qf), gk.from_numpy(Kf), gk.from_numpy(Vf)
+    o_sdpa, o_fd, o_ours = (gk.empty((H, 1, hd), gk.float16) for _ in range(3))
+    refcuda.sdpa(gQ, gK, gV, o_sdpa, H, 1, ctx, S, hd, f16=True)
+    ws = gk.empty((refcuda.flash_decoding_workspace(H, hd, ctx) // 4 + 1,), gk.float32)
+    refcuda.flash_decoding_f16(gQ, gK, gV, o_fd, ws, H, hd, ctx, S)
+    ops.sdpa_causal_fixed_cache(gQ, gK, gV, o_ours, ctx)
+    a, b, c = (x.to_numpy().astype(np.float32) for x in (o_sdpa, o_fd, o_ours))
+    assert np.abs(a - b).max() < 0.01                       # the reference's own acceptance test
+    assert np.abs(c - a).max() < 0.01 and np.abs(c - b).max() < 0.01
+    ra = orc.sdpa_causal_fixed_cache(Qf, Kf, Vf, ctx).astype(np.float32)
+    rb = orc.flash_decoding(Qf, Kf, Vf, ctx).astype(np.float32)
+    assert np.abs(ra - a).max() < 2e-3 and np.abs(rb - b).max() < 2e-3
+    Qb, Kb, Vb = bf16(Qf.astype(np.float32)), bf16(Kf.astype(np.float32)), bf16(Vf.astype(np.float32))
+    ob = gk.empty((H, 1, hd), gk.bfloat16)
+    refcuda.sdpa(gk.from_numpy(Qb), gk.from_numpy(Kb), gk.from_numpy(Vb), ob, H, 1, ctx, S, hd)
+    assert rel_err(ob.to_numpy(), orc.sdpa_causal_fixed_cache(Qb, Kb, Vb, ctx)) < 1e-2
+
+
+def test_sdpa_long_context_properties():
+    """32k context (no CPU oracle at this size): uniform keys -> output = mean of V; a single
+    dominant key -> output = that V row; the reference's SDPA cannot launch here (smem > 48 KB)."""
+    H, Hkv, hd, ctx = 32, 8, 128, 32768
+    rng = np.random.default_rng(6)
+    Q = rand_bf16(rng, (H, 1, hd))
+    K = np.zeros((Hkv, ctx, hd), np.uint16)
+    V = rand_bf16(rng, (Hkv, ctx, hd), 1.0)
+    out = gk.empty((H, 1, hd), gk.bfloat16)
+    gV = gk.from_numpy(V)
+    ops.sdpa_causal_fixed_cache(gk.from_numpy(Q), gk.from_numpy(K), gV, out, ctx)
+    mean = f32(V).astype(np.float64).mean(axis=1)
+    o = f32(out.to_numpy())[:, 0, :]
+    assert np.abs(o - np.repeat(mean, H // Hkv, axis=0)).max() < 2e-3
+    K[:, 31000, :] = bf16(np.full(hd, 8.0, np.float32))
+    Qp = bf16(np.full((H, 1, hd), 4.0, np.float32))
+    ops.sdpa_causal_fixed_cache(gk.from_numpy(Qp), gk.from_numpy(K), gV, out, ctx)
+    assert np.array_equal(out.to_numpy()[:, 0, :], np.repeat(V[:, 31000, :], H // Hkv, axis=0))
+    if refcuda.available():
+        with pytest.raises(RuntimeError):
+            refcuda.sdpa(gk.from_numpy(Qp), gk.from_numpy(_expand(K, 4)), gk.from_numpy(_expand(V, 4)),
+                         gk.empty((H, 1, hd), gk.bfloat16), H, 1, ctx, ctx, hd)
+
+
+def test_qk_norm_rope_kv_write_fused_equals_op_sequence():
+    """Fused bracket == rmsnorm -> rope_inplace_f32table -> kv_cache_update (layers/attention.py:326-351)."""
+    from pygpukit_b200.llm.layers import precompute_freqs_cis
+    rng = np.random.default_rng(9)
+    Hq, Hkv, hd, S, M, pos = 32, 8, 128, 64, 3, 20
+    qkv = rand_bf16(rng, (M, (Hq + 2 * Hkv) * hd))
+    qg, kg = (bf16(rng.uniform(0.5, 1.5, hd).astype(np.float32)) for _ in range(2))
+    cos, sin = precompute_freqs_cis(hd, S, 1e6)
+    cos, sin = cos.astype(np.float32), sin.astype(np.float32)
+    for use_norm in (True, False):
+        g = gk.from_numpy(qkv)
+        kc, vc = gk.zeros((Hkv, S, hd), gk.bfloat16), gk.zeros((Hkv, S, hd), gk.bfloat16)
+        api.qk_norm_rope_kv_write(g.device_ptr, gk.from_numpy(qg).device_ptr if use_norm else None,
+                                  gk.from_numpy(kg).device_ptr if use_norm else None, 1e-6,
+                                  gk.from_numpy(cos).device_ptr, gk.from_numpy(sin).device_ptr, kc.device_ptr,
+                                  vc.device_ptr, M, Hq, Hkv, hd, S, pos, None, None)
+        q = qkv[:, :Hq * hd].reshape(M, Hq, hd)
+        k = qkv[:, Hq * hd:(Hq + Hkv) * hd].reshape(M, Hkv, hd)
+        v = qkv[:, (Hq + Hkv) * hd:].reshape(M, Hkv, hd)
+        if use_norm:
+            q = orc.rmsnorm_bf16(q.reshape(-1, hd), qg, 1e-6).reshape(M, Hq, hd)
+            k = orc.rmsnorm_bf16(k.reshape(-1, hd), kg, 1e-6).reshape(M, Hkv, hd)
+        rq, rk = orc.rope_bf16_f32table(q, k, cos[pos:pos + M], sin[pos:pos + M])
+        got = g.to_numpy()
+        assert ulp_diff_bf16(got[:, :Hq * hd].reshape(M, Hq, hd), rq) <= 1
+        assert ulp_diff_bf16(got[:, Hq * hd:(Hq + Hkv) * hd].reshape(M, Hkv, hd), rk) <= 1
+        assert np.array_equal(kc.to_numpy()[:, pos:pos + M], got[:, Hq * hd:(Hq + Hkv) * hd].reshape(M, Hkv, hd).transpose(1, 0, 2))
+        assert np.array_equal(vc.to_numpy()[:, pos:pos + M], v.transpose(1, 0, 2))
+
+
+def test_elementwise_glue():
+    rng = np.random.default_rng(10)
+    a, b = rand_bf16(rng, (3, 1000), 2.0), rand_bf16(rng, (3, 1000), 2.0)
+    ga, gb = gk.from_numpy(a), gk.from_numpy(b)
+    s = ops.silu(ga).to_numpy()
+    assert ulp_diff_bf16(s, orc.silu_bf16(a)) <= 1 and np.mean(s != orc.silu_bf16(a)) < 0.02
+    assert np.array_equal(ops.add(ga, gb).to_numpy(), orc.add_bf16(a, b))
+    x = gk.from_numpy(a)
+    ops.add_inplace(x, gb)
+    assert np.array_equal(x.to_numpy(), orc.add_inplace_bf16(a, b))
+    y = gk.from_numpy(a)
+    ops.mul_inplace(y, gb)
+    assert np.array_equal(y.to_numpy(), orc.mul_inplace_bf16(a, b))
+    bias = rand_bf16(rng, (1000,))
+    z = gk.from_numpy(a)
+    ops.bias_add_inplace(z, gk.from_numpy(bias))
+    assert np.array_equal(z.to_numpy(), orc.bias_add_bf16(a, bias))
+    if refcuda.available():
+        r = gk.empty((3, 1000), gk.bfloat16)
+        refcuda.silu_bf16(ga, r, a.size)
+        assert ulp_diff_bf16(r.to_numpy(), orc.silu_bf16(a)) <= 1
+        x2, y2 = gk.from_numpy(a), gk.from_numpy(a)
+        refcuda.add_inplace_bf16(x2, gb, a.size)
+        refcuda.mul_inplace_bf16(y2, gb, a.size)
+        assert np.array_equal(x2.to_numpy(), x.to_numpy()) and np.array_equal(y2.to_numpy(), y.to_numpy())
+    xf = rng.standard_normal(777).astype(np.float32)
+    np.testing.assert_allclose(ops.gelu(gk.from_numpy(xf)).to_numpy(), orc.gelu_f32(xf), rtol=1e-5, atol=1e-6)
+    dst = gk.empty((3, 1000), gk.bfloat16)
+    ops.copy_to(ga, dst)
+    assert np.array_equal(dst.to_numpy(), a)
+    t = rand_bf16(rng, (5, 7, 16))
+    assert np.array_equal(ops.transpose_3d_021(gk.from_numpy(t)).to_numpy(), t.transpose(1, 0, 2))
+    with pytest.raises(ValueError, match="same shape"):
+        ops.add(ga, gk.zeros((3, 999), gk.bfloat16))
+
+
+def test_embedding_and_greedy():
+    rng = np.random.default_rng(12)
+    E = rand_bf16(rng, (1000, 768))
+    gE, out = gk.from_numpy(E), gk.empty((1, 768), gk.bfloat16)
+    ops.embedding_lookup(gE, out, 123)
+    assert np.array_equal(out.to_numpy()[0], E[123])
+    ops.embedding_lookup_ptr(gE, out, gk.from_numpy(np.array([999], np.int32)))
+    assert np.array_equal(out.to_numpy()[0], E[999])
+    ids = np.array([5, 0, 999, 17], np.int32)
+    outb = gk.empty((4, 768), gk.bfloat16)
+    ops.embedding_lookup_batch(gE, outb, gk.from_numpy(ids), 4)
+    assert np.array_equal(outb.to_numpy(), E[ids])
+    with pytest.raises(ValueError, match="out of range"):
+        ops.embedding_lookup(gE, out, 1000)
+    lg = rng.standard_normal(151936).astype(np.float32)
+    lg[[70000, 150000]] = 9.0
+    assert ops.sample_greedy(gk.from_numpy(lg)) == 70000 == orc.argmax_f32(lg)
+    assert ops.sample_greedy(gk.from_numpy(bf16(lg))) == orc.argmax_bf16(bf16(lg))
+
+
+def test_moe_routing_bit_exact():
+    rng = np.random.default_rng(13)
+    T, E, k, H = 7, 128, 8, 256
+    logits = rand_bf16(rng, (T, E))
+    logits[0, 5] = logits[0, 9]                         # tie -> lowest index first
+    gl = gk.from_numpy(logits)
+    vals, idx = gk.empty((T, k), gk.bfloat16), gk.empty((T, k), gk.int32)
+    ops.moe_topk_with_indices(gl, vals, idx, k)
+    rv, ri = orc.moe_topk_bf16(logits, k)
+    assert np.array_equal(idx.to_numpy(), ri) and np.array_equal(vals.to_numpy(), rv)
+    ops.moe_softmax_topk(vals, k)
+    rs = orc.moe_softmax_topk_bf16(rv)
+    assert ulp_diff_bf16(vals.to_numpy(), rs) <= 1
+    if refcuda.available():
+        v2, i2 = gk.empty((T, k), gk.bfloat16), gk.empty((T, k), gk.int32)
+        refcuda.moe_topk_bf16(gl, v2, i2, T, E, k)
+        assert np.array_equal(i2.to_numpy(), ri) and np.array_equal(v2.to_numpy(), rv)
+        refcuda.moe_softmax_topk_bf16(v2, T, k)
+        assert ulp_diff_bf16(v2.to_numpy(), rs) <= 1
+    counts, offs, perm, rev = (gk.empty((n,), gk.int32) for n in (E, E + 1, T * k, T * k))
+    ops.moe_compute_permutation(idx, counts, offs, perm, rev, E, k)
+    rc, ro, rp, rr = orc.moe_compute_permutation(ri, E)
+    for a, b in ((counts, rc), (offs, ro), (perm, rp), (rev, rr)):
+        assert np.array_equal(a.to_numpy(), b)
+    rows = gk.empty((T * k,), gk.int32)
+    ops.moe_expand_expert_offsets(offs, rows, E)
+    assert np.array_equal(rows.to_numpy(), orc.moe_expand_expert_offsets(ro, T * k))
+    hidden = rand_bf16(rng, (T, H))
+    gath = gk.empty((T * k, H), gk.bfloat16)
+    ops.moe_gather(gk.from_numpy(hidden), perm, gath, k)
+    assert np.array_equal(gath.to_numpy(), orc.moe_gather_bf16(hidden, rp, k))
+    eo = rand_bf16(rng, (T * k, H))
+    outp = gk.empty((T, H), gk.bfloat16)
+    ops.moe_scatter(gk.from_numpy(eo), vals, rev, outp, k)
+    assert np.array_equal(outp.to_numpy(), orc.moe_scatter_bf16(eo, vals.to_numpy(), rr, T, k))
+
+
+def test_grouped_gemm_fp8():
+    from tests.util import rand_fp8_weights
+    rng = np.random.default_rng(14)
+    E, N, K, M = 4, 256, 384, 9
+    cs = [rand_fp8_weights(rng, N, K) for _ in range(E)]
+    B = np.stack([c[0] for c in cs])
+    S = np.stack([c[1] for c in cs])
+    ids = np.sort(rng.integers(0, E, M)).astype(np.int32)
+    A = rand_bf16(rng, (M, K))
+    out = ops.grouped_gemm_fp8_bf16(gk.from_numpy(A), gk.from_numpy(B), gk.from_numpy(S), gk.from_numpy(ids)).to_numpy()
+    ref = orc.grouped_gemm_fp8_bf16(A, B, S, ids)
+    assert rel_err(out, ref) < 2e-3
+    if refcuda.available():
+        o2 = gk.empty((M, N), gk.bfloat16)
+        refcuda.grouped_gemm(gk.from_numpy(A), gk.from_numpy(B), gk.from_numpy(S), o2, gk.from_numpy(ids), M, N, K)
+        assert rel_err(o2.to_numpy(), ref) < 1e-5
