@@ -216,6 +216,23 @@ int pgk_moe_scatter(const void* expert_out, const void* router_weights, const in
 int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C,
                              const int32_t* row_expert_ids, int M, int K, int N, void* stream);
 
+/* NVF4 experts (net-new; the reference's MoE is FP8-only): B_data u8 [E_local, K/2, N], B_scale u8
+ * [E_local, K/32, N] (per-expert reference NVF4 layout); rows whose expert id falls outside
+ * [expert_offset, expert_offset + num_local_experts) are written as zeros. */
+int pgk_moe_grouped_gemv_nvf4(const void* A, const void* B_data, const void* B_scale, void* C,
+                              const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                              int num_local_experts, void* stream);
+
+/* ------------------------------------------------------------------ synthetic init (net-new)
+ * The benchmarks use random-init models (no checkpoint I/O): BF16 masters N(0, std^2) are drawn on
+ * the device and quantised there.  FP8 block quantiser = the definition of LinearFP8's storage
+ * (llm/layers/linear.py:101-179): codes [N,K] + bf16 scale_inv [ceil(N/128), ceil(K/128)]. */
+int pgk_fill_normal_bf16(void* out, size_t n, uint32_t seed, float std, void* stream);
+int pgk_quantize_bf16_to_fp8_block(const void* w_nk, void* codes, void* scale, int N, int K, void* stream);
+/* *pos_buf += delta; *ctx_buf += delta (either may be NULL): device-side counters of the
+ * graph-replayed decode step (position_buf of llm/decode/m1_graph.py:329-331,505-506). */
+int pgk_decode_advance(int32_t* pos_buf, int32_t* ctx_buf, int delta, void* stream);
+
 /* ------------------------------------------------------------------ tensor parallel (NCCL)
  * net-new (the reference is single-GPU): one communicator per process. unique id is 128 bytes. */
 int pgk_nccl_unique_id(void* host_id128);

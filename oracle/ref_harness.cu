@@ -20,6 +20,8 @@
 #include "nn/kv_cache_kernels.cuh"
 #include "nn/attention_kernels.cuh"
 #include "nn/flash_decoding.cuh"
+// the kernel bodies in activation_kernels.cuh sit behind this macro (activation_kernels.cuh:108)
+#define PYGPUKIT_IMPLEMENT_NN_KERNELS
 #include "nn/activation_kernels.cuh"
 #include "moe/topk_kernels.cuh"
 

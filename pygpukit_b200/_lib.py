@@ -74,6 +74,10 @@ _SIGS = {
     "pgk_moe_gather": [vp, vp, vp, i32, i32, i32, vp],
     "pgk_moe_scatter": [vp, vp, vp, vp, i32, i32, i32, vp],
     "pgk_moe_grouped_gemv_fp8": [vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "pgk_moe_grouped_gemv_nvf4": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
+    "pgk_quantize_bf16_to_fp8_block": [vp, vp, vp, i32, i32, vp],
+    "pgk_decode_advance": [vp, vp, i32, vp],
     "pgk_nccl_unique_id": [vp], "pgk_nccl_init": [vp, i32, i32],
     "pgk_nccl_allreduce_bf16": [vp, sz, vp], "pgk_nccl_allgather": [vp, vp, sz, vp],
     "pgk_nccl_destroy": [],

@@ -130,11 +130,12 @@ sdpa_decode_kernel(SdpaParams p) {
     const uint8_t* Kb = (const uint8_t*)p.K + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
     const uint8_t* Vb = (const uint8_t*)p.V + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
     constexpr int STEP = kAttnWarps * PPI;
-    for (int j0 = c0 + warp * PPI + slot; j0 < c1 + STEP; j0 += 2 * STEP) {
+    // the loop bound is warp-uniform (jw does not depend on the lane): every lane executes the
+    // same number of iterations, so the full-mask shuffles below are always convergent
+    for (int jw = c0 + warp * PPI; jw < c1; jw += 2 * STEP) {
         // two positions in flight per lane
-        const int ja = j0, jb = j0 + STEP;
+        const int ja = jw + slot, jb = jw + slot + STEP;
         const bool va = ja < c1, vb = jb < c1;
-        if (!__any_sync(0xffffffffu, va)) break;
         uint4 ka, kb, wa, wb;
         if (va) { ka = ldg_kv(Kb + (size_t)ja * HD * esz); wa = ldg_kv(Vb + (size_t)ja * HD * esz); }
         if (vb) { kb = ldg_kv(Kb + (size_t)jb * HD * esz); wb = ldg_kv(Vb + (size_t)jb * HD * esz); }

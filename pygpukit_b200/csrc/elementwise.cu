@@ -39,9 +39,9 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
     __syncthreads();
     if (lane == 0) red[warp] = v;
     __syncthreads();
-    float t = 0.f;
-    for (int w = 0; w < nw; ++w) t += red[w];
-    return t;
+    // the reference folds the per-warp totals with a second shfl_down tree in warp 0
+    // (norm_kernels.cuh:553-570); a butterfly over {red[lane] | 0} gives lane 0's pairing everywhere
+    return warp_sum(lane < nw ? red[lane] : 0.f);
 }
 
 // ---------------------------------------------------------------- RMSNorm / LayerNorm
@@ -311,9 +311,18 @@ __global__ void qk_norm_rope_kv_kernel(uint16_t* __restrict__ qkv, const uint16_
     const uint16_t* gamma = is_k ? kg : qg;
     float inv = 1.f;
     if (gamma) {
-        float ss = 0.f;
-        for (int d = lane; d < hd; d += 32) { float v = bf16_bits_to_f32(row[d]); ss = fmaf(v, v, ss); }
-        ss = warp_sum(ss);
+        // same summation tree as the reference's rmsnorm block of bs = min(256, hd^32) threads
+        // (virtual thread t = lane + 32 w owns elements t, t + bs, ...): per-warp trees, then a tree
+        // over the warp totals -- so the fused bracket rounds exactly like the separate QK-norm launch
+        const int bs = min(256, (hd + 31) & ~31), nw = bs >> 5;
+        float tot = 0.f;
+        for (int w = 0; w < nw; ++w) {
+            float part = 0.f;
+            for (int d = lane + 32 * w; d < hd; d += bs) { float v = bf16_bits_to_f32(row[d]); part = fmaf(v, v, part); }
+            part = warp_sum(part);
+            if (lane == w) tot = part;
+        }
+        float ss = warp_sum(tot);
         inv = rsqrtf(ss / (float)hd + eps);
     }
     uint16_t* dstk = (is_k && p < max_seq) ? kc + ((size_t)(h - hq) * max_seq + p) * hd : nullptr;
@@ -342,7 +351,8 @@ extern "C" {
 int pgk_rmsnorm(const void* x, const void* gamma, void* y, int rows, int features, float eps, int dtype, void* stream) {
     PGK_REQUIRE(rows >= 0 && features > 0, "rmsnorm failed: invalid shape");
     if (rows == 0) return 0;
-    int bs = features >= 1024 ? 256 : (features >= 256 ? 128 : 32 * ((features + 31) / 32 > 4 ? 4 : (features + 31) / 32));
+    int bs = (features + 31) / 32 * 32;          // the reference's block size (rmsnorm.inl:18-19): same partial sums
+    if (bs > 256) bs = 256;
     PGK_DISPATCH_DT(dtype, "rmsnorm",
         PGK_CUDA(launch(rmsnorm_kernel<DT, false>, dim3(rows), dim3(bs), 0, ST(stream), x, (const void*)nullptr, gamma, y, features, eps)));
     return 0;

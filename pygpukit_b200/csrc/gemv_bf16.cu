@@ -172,7 +172,7 @@ static int launch_bf16(const uint16_t* A, const uint16_t* B, uint16_t* C, int K,
     {
         std::lock_guard<std::mutex> lk(mu);
         if (!attr_set) {
-            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             attr_set = true;
         }
         uint64_t key = ((uint64_t)(uint32_t)K << 32) | (uint32_t)N;

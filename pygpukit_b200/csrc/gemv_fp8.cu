@@ -189,7 +189,7 @@ static int launch_fp8(const void* A, const void* B0, const void* S0, const void*
     {
         std::lock_guard<std::mutex> lk(mu);
         if (!attr_set) {
-            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             attr_set = true;
         }
         uint64_t key = ((uint64_t)(uint32_t)K << 32) | (uint32_t)N;

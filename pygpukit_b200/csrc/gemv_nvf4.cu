@@ -270,7 +270,7 @@ static int launch_nvf4(Nvf4Params p, cudaStream_t st) {
     {
         std::lock_guard<std::mutex> lk(mu);
         if (!attr_set) {
-            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             attr_set = true;
         }
         uint64_t key = ((uint64_t)(uint32_t)p.K << 32) | (uint32_t)p.N;

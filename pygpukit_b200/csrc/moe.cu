@@ -178,6 +178,90 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
     if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Expert-grouped NVF4 GEMV (net-new: the reference's MoE path is FP8-only, layers/moe.py:86-151).
+// Row r of A[R,K] uses expert e = row_expert_ids[r] - expert_offset of B_data[E,K/2,N] /
+// B_scale[E,K/32,N] (the reference NVF4 layout per expert, nvf4_kernels.cu:79-200); rows whose
+// expert is not held by this rank produce zeros (their value arrives through the all-reduce).
+// CTA = 32 warps over one row x 128 columns: lane owns 4 consecutive columns (32-bit loads, one
+// 128-byte line per warp per byte-row), warp w owns scale blocks w, w+32, ... of K; partial sums
+// meet in shared memory and are folded in warp order (deterministic).
+constexpr int kMoeNvf4Warps = 32;
+__global__ void __launch_bounds__(kMoeNvf4Warps * 32)
+moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd,
+                             const uint8_t* __restrict__ Bs, uint16_t* __restrict__ C,
+                             const int32_t* __restrict__ row_expert_ids, int K, int N, int expert_offset,
+                             int num_local) {
+    extern __shared__ __align__(16) unsigned char moe_smem[];
+    float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
+    float* red = a_s + K;                                             // [warps][128]
+    griddep_launch();
+    griddep_wait();
+    const int r = blockIdx.y, col0 = blockIdx.x * 128;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int e = row_expert_ids[r] - expert_offset;
+    const int c = col0 + lane * 4;
+    if (e < 0 || e >= num_local) {
+        if (warp == 0 && c < N) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) if (c + j < N) C[(size_t)r * N + c + j] = 0;
+        }
+        return;
+    }
+    for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * K + k]);
+    __syncthreads();
+    const uint8_t* bd = Bd + (size_t)e * (K >> 1) * N;
+    const uint8_t* bs = Bs + (size_t)e * ((K + 31) >> 5) * N;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int KB = K >> 5;
+    const bool full = (c + 3 < N) && ((N & 3) == 0);
+    for (int blk = warp; blk < KB; blk += kMoeNvf4Warps) {
+        float part[4] = {0.f, 0.f, 0.f, 0.f};
+        if (full) {
+            uint32_t w[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                w[i] = __ldg(reinterpret_cast<const uint32_t*>(bd + (size_t)(blk * 16 + i) * N + c));
+            const uint32_t sw = __ldg(reinterpret_cast<const uint32_t*>(bs + (size_t)blk * N + c));
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float2 a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 2 * i);
+                uint32_t h;
+                float2 f;
+                h = e2m1x2_to_f16x2<0>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                part[0] = fmaf(a.x, f.x, part[0]); part[0] = fmaf(a.y, f.y, part[0]);
+                h = e2m1x2_to_f16x2<1>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                part[1] = fmaf(a.x, f.x, part[1]); part[1] = fmaf(a.y, f.y, part[1]);
+                h = e2m1x2_to_f16x2<2>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                part[2] = fmaf(a.x, f.x, part[2]); part[2] = fmaf(a.y, f.y, part[2]);
+                h = e2m1x2_to_f16x2<3>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                part[3] = fmaf(a.x, f.x, part[3]); part[3] = fmaf(a.y, f.y, part[3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j] = fmaf(part[j], ue4m3_to_f32((sw >> (8 * j)) & 0xff), acc[j]);
+        } else {
+            for (int j = 0; j < 4; ++j) {
+                if (c + j >= N) break;
+                for (int i = 0; i < 16; ++i) {
+                    uint32_t b = bd[(size_t)(blk * 16 + i) * N + c + j];
+                    part[j] = fmaf(a_s[blk * 32 + 2 * i], e2m1_to_f32(b & 0xf), part[j]);
+                    part[j] = fmaf(a_s[blk * 32 + 2 * i + 1], e2m1_to_f32(b >> 4), part[j]);
+                }
+                acc[j] = fmaf(part[j], ue4m3_to_f32(bs[(size_t)blk * N + c + j]), acc[j]);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) red[warp * 128 + lane * 4 + j] = acc[j];
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        float s = 0.f;
+#pragma unroll 8
+        for (int w = 0; w < kMoeNvf4Warps; ++w) s += red[w * 128 + threadIdx.x];
+        if (col0 + threadIdx.x < N) C[(size_t)r * N + col0 + threadIdx.x] = f32_to_bf16_bits(s);
+    }
+}
+
 static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
 }  // namespace pgk
@@ -243,6 +327,24 @@ int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, vo
     size_t warps = (size_t)M * N;
     PGK_CUDA(launch(moe_grouped_gemv_fp8_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream),
                     (const uint16_t*)A, (const uint8_t*)B_enk, (const uint16_t*)S, (uint16_t*)C, row_expert_ids, M, K, N));
+    return 0;
+}
+
+int pgk_moe_grouped_gemv_nvf4(const void* A, const void* B_data, const void* B_scale, void* C,
+                              const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                              int num_local_experts, void* stream) {
+    if (M <= 0) return 0;
+    PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_grouped_gemv_nvf4 failed: K=%d must be a multiple of 32", K);
+    size_t smem = (size_t)K * 4 + (size_t)kMoeNvf4Warps * 128 * 4;
+    PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
+    static bool attr = false;
+    if (!attr) {
+        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr = true;
+    }
+    PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel, dim3((N + 127) / 128, M), dim3(kMoeNvf4Warps * 32), smem, ST(stream),
+                    (const uint16_t*)A, (const uint8_t*)B_data, (const uint8_t*)B_scale, (uint16_t*)C, row_expert_ids,
+                    K, N, expert_offset, num_local_experts));
     return 0;
 }
 

@@ -1,0 +1,16 @@
+"""pygpukit_b200.llm -- layers, model and decode strategies of the decode hot path (names of
+pygpukit/llm/__init__.py, pinned upstream by tests/test_llm_unified.py:198-239).  Checkpoint loading,
+tokenizer, chat templates, Jacobi / speculative strategies are out of scope."""
+from .buffers import DecodeBuffers, PrefillBuffers
+from .config import (GPT2_SPEC, LLAMA_SPEC, MIXTRAL_SPEC, MODEL_SPECS, QWEN2_SPEC, QWEN3_MOE_SPEC, QWEN3_SPEC,
+                     GPT2Config, LlamaConfig, ModelSpec, Qwen3Config, TransformerConfig, detect_model_spec,
+                     named_config)
+from .decode import DecodeBatch, DecodeM1, DecodeM1Graph, DecodeStrategy
+from .layers import (MLP, Attention, Linear, LinearBF16, LinearFP8, LinearNVF4, MoELayer, Norm, TransformerBlock,
+                     apply_rotary_pos_emb_numpy, precompute_freqs_cis)
+from .models import CausalTransformerModel, GPT2Model, LlamaModel, QwenModel
+from .random_init import build_random_model
+from .sampling import sample_token
+from .tp import TensorParallel, shard_plan, shard_range
+
+__all__ = [n for n in dir() if not n.startswith("_")]

@@ -1,0 +1,62 @@
+"""Transformer block (mirror of pygpukit/llm/layers/block.py:18-62): Norm -> Attention -> residual,
+Norm -> MLP/MoE -> residual.  Residual adds ride in the o_proj / down_proj GEMV epilogues with the
+fixed-cache path's rounding (bf16 + bf16 -> one rounding, elementwise_kernels.cuh:381-390).  Under
+tensor parallelism the row-parallel partial sums are all-reduced BEFORE the residual is added."""
+from __future__ import annotations
+
+from ...core.array import GPUArray
+from ...ops.elementwise import add_inplace
+from .attention import Attention
+from .mlp import MLP
+from .moe import MoELayer
+from .norm import Norm
+
+
+class TransformerBlock:
+    def __init__(self, attn_norm: Norm, attn: Attention, mlp_norm: Norm, mlp: "MLP | MoELayer", comm=None):
+        self.attn_norm = attn_norm
+        self.attn = attn
+        self.mlp_norm = mlp_norm
+        self.mlp = mlp
+        self.comm = comm   # TensorParallel communicator or None
+
+    def decode(self, hidden: GPUArray, position: int, context_len: int, bufs=None, pos_buf=None, ctx_buf=None) -> GPUArray:
+        """hidden [M, H] -> hidden [M, H], updated IN PLACE (M consecutive tokens of one sequence)."""
+        M = hidden.shape[0]
+
+        def buf(name):
+            b = getattr(bufs, name, None) if bufs is not None else None
+            return b if (b is None or b.shape[0] == M) else b.slice_rows(M)
+
+        tp = self.comm is not None and self.comm.world > 1
+        x = self.attn_norm(hidden, out=buf("norm_out"))
+        a = self.attn.attend(x, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
+                             pos_buf=pos_buf, ctx_buf=ctx_buf)
+        if tp:
+            part = self.attn.o_proj.forward(a, out=buf("partial"))
+            self.comm.allreduce(part)
+            add_inplace(hidden, part)
+        else:
+            self.attn.o_proj.forward(a, out=hidden, residual=hidden)
+        x = self.mlp_norm(hidden, out=buf("norm_out"))
+        if tp:
+            part = self.mlp.forward(x, out=buf("partial"), act_buf=buf("mlp_act"))
+            self.comm.allreduce(part)
+            add_inplace(hidden, part)
+        else:
+            self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"))
+        return hidden
+
+    def __call__(self, x: GPUArray, position_ids: list[int] | None = None, past_kv=None, use_cache: bool = False):
+        start = position_ids[0] if position_ids else (past_kv or 0)
+        h = x.clone()
+        self.decode(h, start, start + x.shape[0])
+        return h, (start + x.shape[0] if use_cache else None)
+
+    @property
+    def weight_bytes(self) -> int:
+        return (self.attn.weight_bytes + self.mlp.weight_bytes + self.attn_norm.weight.nbytes
+                + self.mlp_norm.weight.nbytes)
+
+
+__all__ = ["TransformerBlock"]

@@ -1,0 +1,275 @@
+"""CausalTransformerModel (mirror of pygpukit/llm/models/causal.py:78-1493, decode path only).
+
+Same constructor (config, embed_tokens, blocks, final_norm, lm_head, position_embed, spec) and the
+reference's entry points on this path: `__call__`, `get_logits`, `generate`,
+`_decode_step_fixed_cache`, `_decode_step_fixed_cache_batch`, `snapshot/restore` free.  Every
+forward runs on the fixed KV cache; the KV-concat path of the reference (`past_key_values` tuples
+growing by realloc, causal.py:245-256 of attention.py) is not reproduced -- `past_key_values` is
+the number of cached positions.
+
+Fast path (net-new orchestration, same math): `decode_step_device` runs one whole token on the
+device -- token id, position and context length live in int32 device buffers, greedy sampling is
+fused into the lm_head GEMV and feeds the next step's token buffer -- so the step captures into ONE
+CUDA graph (`init_decode_graph`) that replays for every position with no host round trip.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ..._lib import api
+from ...core.array import GPUArray
+from ...core.dtypes import bfloat16, int32
+from ...core.factory import from_numpy
+from ...core.stream import CudaGraph, Stream, current_stream_handle as _st, use_stream
+from ..buffers import DecodeBuffers
+from ..config import ModelSpec, TransformerConfig
+from ..layers.block import TransformerBlock
+from ..layers.norm import Norm
+from ..sampling import sample_token
+
+
+def _to_float32_logits(logits_np: np.ndarray) -> np.ndarray:
+    """bf16-as-uint16 -> f32 (causal.py:62-71)."""
+    if logits_np.dtype == np.uint16:
+        return (logits_np.astype(np.uint32) << 16).view(np.float32)
+    return logits_np.astype(np.float32)
+
+
+class CausalTransformerModel:
+    def __init__(self, config: TransformerConfig, embed_tokens: GPUArray, blocks: list[TransformerBlock],
+                 final_norm: Norm, lm_head: GPUArray | None = None, position_embed: GPUArray | None = None,
+                 spec: ModelSpec | None = None, comm=None):
+        self.config = config
+        self.embed_tokens = embed_tokens
+        self.blocks = blocks
+        self.final_norm = final_norm
+        self._lm_head = lm_head
+        self.position_embed = position_embed
+        self.spec = spec
+        self.comm = comm
+        self._buffers: DecodeBuffers | None = None
+        self._max_seq = 0
+        self._graph: CudaGraph | None = None
+        self._graph_stream: Stream | None = None
+        self._gathered_logits: GPUArray | None = None
+
+    # ------------------------------------------------------------------ setup
+    @property
+    def lm_head(self) -> GPUArray | None:
+        return self._lm_head
+
+    @property
+    def _head(self) -> GPUArray:
+        return self._lm_head if self._lm_head is not None else self.embed_tokens
+
+    @property
+    def tp(self) -> int:
+        return self.comm.world if self.comm is not None else 1
+
+    def init_decode(self, max_seq_len: int, max_batch_size: int = 1) -> DecodeBuffers:
+        """Allocate the fixed KV caches (all layers), the shared RoPE tables and the step buffers."""
+        tables = None
+        for blk in self.blocks:
+            blk.attn.init_fixed_cache(max_seq_len, "bfloat16", rope_tables=tables)
+            if tables is None and self.config.use_rope:
+                tables = (blk.attn._cos_dev, blk.attn._sin_dev)
+        v_local = self._head.shape[0]
+        self._buffers = DecodeBuffers.allocate(self.config, "bfloat16", vocab_size=v_local,
+                                               max_batch_size=max_batch_size)
+        self._max_seq = max_seq_len
+        if self.tp > 1:
+            self._gathered_logits = GPUArray((self.tp * v_local,), bfloat16)
+        self._graph = None
+        return self._buffers
+
+    @property
+    def buffers(self) -> DecodeBuffers:
+        assert self._buffers is not None, "Call init_decode first"
+        return self._buffers
+
+    # ------------------------------------------------------------------ pieces
+    def _embed(self, token_ids: list[int] | None, M: int, start_position: int, b: DecodeBuffers) -> GPUArray:
+        hidden = b.hidden if b.hidden.shape[0] == M else b.hidden.slice_rows(M)
+        if token_ids is not None:
+            ids = np.asarray(token_ids, np.int32)
+            api.memcpy_h2d(b.token_buf.device_ptr, ids.ctypes.data_as(C.c_void_p), ids.nbytes, _st())
+            api.stream_sync(_st()) if _st() is not None else api.device_sync()   # ids is pageable
+        api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, self.config.hidden_size,
+                                 b.token_buf.device_ptr, M, 2, _st())
+        if self.position_embed is not None:
+            raise NotImplementedError("learned position embeddings (GPT-2) are not on the fixed-cache B200 path")
+        return hidden
+
+    def _layers(self, hidden: GPUArray, position: int, context_len: int, b: DecodeBuffers,
+                pos_buf: GPUArray | None = None, ctx_buf: GPUArray | None = None) -> GPUArray:
+        for blk in self.blocks:
+            blk.decode(hidden, position, context_len, b, pos_buf, ctx_buf)
+        return hidden
+
+    def _final(self, hidden: GPUArray, b: DecodeBuffers) -> GPUArray:
+        M = hidden.shape[0]
+        out = b.norm_out if b.norm_out.shape[0] == M else b.norm_out.slice_rows(M)
+        return self.final_norm(hidden, out=out)
+
+    # ------------------------------------------------------------------ reference entry points
+    def _decode_step_fixed_cache(self, token_id: int, position: int, context_len: int) -> GPUArray:
+        """One token through all blocks + final norm -> hidden [1, H] (causal.py:799-840)."""
+        return self._decode_step_fixed_cache_batch([token_id], position, context_len)
+
+    def _decode_step_fixed_cache_batch(self, token_ids: list[int], start_position: int, context_len: int) -> GPUArray:
+        """M consecutive tokens of one sequence -> hidden [M, H] (causal.py:842-891)."""
+        b = self.buffers
+        M = len(token_ids)
+        if M > b.max_batch_size:
+            raise ValueError(f"batch of {M} tokens exceeds max_batch_size {b.max_batch_size} (init_decode)")
+        if context_len > self._max_seq:
+            raise ValueError(f"context_len {context_len} exceeds the fixed cache ({self._max_seq})")
+        hidden = self._embed(token_ids, M, start_position, b)
+        self._layers(hidden, start_position, context_len, b)
+        return self._final(hidden, b)
+
+    def get_logits(self, hidden: GPUArray, *, out: GPUArray | None = None) -> GPUArray:
+        """hidden [M, H] @ lm_head[V, H]^T -> logits [M, V] (causal.py:167-177).  Under TP every rank
+        returns the logits of its vocabulary shard."""
+        M = hidden.shape[0]
+        V = self._head.shape[0]
+        if out is None:
+            out = GPUArray((M, V), bfloat16)
+        api.gemv_bf16(hidden.device_ptr, self._head.device_ptr, out.device_ptr, M, self.config.hidden_size, V, _st())
+        return out
+
+    def __call__(self, input_ids: list[int], position_ids: list[int] | None = None, past_key_values=None,
+                 use_cache: bool = False):
+        """hidden states of `input_ids` (causal.py:108-160); past_key_values = cached positions."""
+        start = position_ids[0] if position_ids else int(past_key_values or 0)
+        hidden = None
+        slab = self.buffers.max_batch_size
+        for i in range(0, len(input_ids), slab):
+            ids = input_ids[i:i + slab]
+            hidden = self._decode_step_fixed_cache_batch(ids, start + i, start + i + len(ids))
+        return hidden, (start + len(input_ids) if use_cache else None)
+
+    # ------------------------------------------------------------------ device-resident step
+    def decode_step_device(self) -> None:
+        """One greedy token entirely on the device: reads token_buf / position_buf / context_buf,
+        writes the sampled token to next_token AND token_buf, then advances position / context."""
+        b = self.buffers
+        hidden = b.hidden.slice_rows(1) if b.hidden.shape[0] != 1 else b.hidden
+        api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, self.config.hidden_size,
+                                 b.token_buf.device_ptr, 1, 2, _st())
+        self._layers(hidden, 0, self._max_seq, b, b.position_buf, b.context_buf)
+        x = self._final(hidden, b)
+        V = self._head.shape[0]
+        if self.tp == 1:
+            api.gemv_bf16_argmax(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
+                                 self.config.hidden_size, V, _st())
+        else:
+            api.gemv_bf16(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, 1, self.config.hidden_size, V, _st())
+            self.comm.allgather_bytes(b.logits, self._gathered_logits, V * 2)
+            api.argmax(self._gathered_logits.device_ptr, b.token_buf.device_ptr, self.tp * V, 2, _st())
+        api.memcpy_d2d(b.next_token.device_ptr, b.token_buf.device_ptr, 4, _st())
+        api.decode_advance(b.position_buf.device_ptr, b.context_buf.device_ptr, 1, _st())
+
+    def set_decode_state(self, token_id: int, position: int) -> None:
+        """token_buf = token_id, position_buf = position, context_buf = position + 1."""
+        b = self.buffers
+        st = np.array([token_id, position, position + 1], np.int32)
+        for i, buf in enumerate((b.token_buf, b.position_buf, b.context_buf)):
+            api.memcpy_h2d(buf.device_ptr, st[i:i + 1].ctypes.data_as(C.c_void_p), 4, _st())
+        api.stream_sync(_st()) if _st() is not None else api.device_sync()
+
+    def init_decode_graph(self) -> None:
+        """Capture decode_step_device into one CUDA graph (replaces the reference's per-layer
+        pre/post-SDPA graphs with syncs in between, decode/m1_graph.py:248-457)."""
+        self._graph_stream = Stream()
+        with use_stream(self._graph_stream):
+            self.set_decode_state(0, 0)
+            self.decode_step_device()            # warm-up outside capture (workspaces, attributes)
+            self._graph_stream.synchronize()
+            g = CudaGraph()
+            with g.capture(self._graph_stream):
+                self.decode_step_device()
+            self._graph = g
+
+    def decode_graph_replay(self) -> None:
+        assert self._graph is not None, "Call init_decode_graph first"
+        self._graph.replay(self._graph_stream)
+
+    # ------------------------------------------------------------------ generation
+    def prefill(self, input_ids: list[int]) -> GPUArray:
+        """Run the prompt through the fixed cache; returns the final-norm hidden of the last slab."""
+        hidden, _ = self(list(input_ids), use_cache=True)
+        return hidden
+
+    def generate(self, input_ids: list[int], max_new_tokens: int = 20, temperature: float = 1.0, top_k: int = 50,
+                 top_p: float = 0.9, eos_token_id: int | None = None, use_cache: bool = True,
+                 gpu_sampling: bool = False, use_graph: bool = True) -> list[int]:
+        """Autoregressive generation (causal.py:179-255).  temperature == 0 takes the device-resident
+        greedy path (one graph replay per token, tokens read back once at the end unless an EOS id
+        must be checked); otherwise logits come back to the host for `sample_token`."""
+        tokens = list(input_ids)
+        if self._buffers is None or self._max_seq < len(tokens) + max_new_tokens:
+            self.init_decode(max(self.config.max_position_embeddings, len(tokens) + max_new_tokens),
+                             max_batch_size=min(64, max(1, len(tokens))))
+        if max_new_tokens <= 0:
+            return tokens
+        b = self.buffers
+        greedy_dev = temperature == 0 and self.tp == 1
+        if greedy_dev and use_graph and self._graph is None:
+            self.init_decode_graph()             # before prefill: capture clobbers cache slot 0 / step state
+        hidden = self.prefill(tokens)
+        last = hidden.row(hidden.shape[0] - 1).view((1, hidden.shape[1]))
+        if greedy_dev:
+            V = self._head.shape[0]
+            api.gemv_bf16_argmax(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
+                                 self.config.hidden_size, V, _st())
+            first = int(b.token_buf.to_numpy()[0])
+            tokens.append(first)
+            if (eos_token_id is not None and first == eos_token_id) or max_new_tokens == 1:
+                return tokens
+            n = max_new_tokens - 1
+            self.set_decode_state(first, len(tokens) - 1)
+            history = GPUArray((n,), int32)
+            stream = self._graph_stream if (use_graph and self._graph is not None) else None
+            api.device_sync()
+            with use_stream(stream):
+                for i in range(n):
+                    if stream is not None:
+                        self.decode_graph_replay()
+                    else:
+                        self.decode_step_device()
+                    api.memcpy_d2d(history.device_ptr + 4 * i, b.next_token.device_ptr, 4, _st())
+                    if eos_token_id is not None and int(b.next_token.to_numpy()[0]) == eos_token_id:
+                        n = i + 1
+                        break
+                out = history.to_numpy()[:n]
+            tokens.extend(int(v) for v in out)
+            return tokens
+        # host sampling path
+        for step in range(max_new_tokens):
+            logits = _to_float32_logits(self.get_logits(last).to_numpy()[0])
+            nxt = sample_token(logits, temperature, top_k, top_p)
+            tokens.append(nxt)
+            if (eos_token_id is not None and nxt == eos_token_id) or step == max_new_tokens - 1:
+                break
+            last = self._decode_step_fixed_cache(nxt, len(tokens) - 1, len(tokens))
+        return tokens
+
+    # ------------------------------------------------------------------ accounting
+    def weight_bytes_per_token(self) -> int:
+        """Algorithmic weight bytes one decode token streams on this rank."""
+        return sum(blk.weight_bytes for blk in self.blocks) + self._head.nbytes + self.final_norm.weight.nbytes
+
+    def kv_bytes_per_token(self, context_len: int) -> int:
+        a = self.blocks[0].attn
+        return len(self.blocks) * 2 * a.num_kv_heads * context_len * a.head_dim * 2
+
+
+GPT2Model = CausalTransformerModel
+LlamaModel = CausalTransformerModel
+QwenModel = CausalTransformerModel   # named by BASELINE.json's north_star; absent upstream
+
+__all__ = ["CausalTransformerModel", "GPT2Model", "LlamaModel", "QwenModel"]
+_ = from_numpy

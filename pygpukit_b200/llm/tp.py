@@ -1,0 +1,136 @@
+"""Tensor parallelism for the decode path (net-new: the reference is single-GPU,
+docs/scheduler.md:358).
+
+One process per GPU.  Megatron-style sharding decided at weight-creation time:
+  column-parallel  q/k/v (heads split), gate/up (intermediate split)   -> no communication
+  row-parallel     o_proj (K = local heads * hd), down_proj (K = I/tp) -> partial [M, H] sums,
+                   ONE all-reduce (bf16, sum) each on the compute stream (graph-capturable)
+  attention        local heads, KV cache sharded by KV head             -> no communication
+  lm_head          column-parallel over the vocabulary; greedy = all-gather of the per-rank
+                   (max logit, argmax) pairs (8 bytes per rank), not of the logits
+  MoE              experts sharded E/tp per rank with a replicated router -> same all-reduce
+
+The collective itself is NCCL over NVLink/NVSwitch through the C ABI (pgk_nccl_*); the unique id
+travels over whatever host-side channel the launcher has (torch.distributed store under torchrun,
+or a file).  The shard arithmetic below is pure Python and is what the world_size-2 gloo tests
+exercise on CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import time
+
+import numpy as np
+
+
+def shard_range(n: int, world: int, rank: int, multiple: int = 1) -> tuple[int, int]:
+    """[lo, hi) of rank's contiguous shard of n items; n must divide into world * multiple."""
+    if n % (world * multiple):
+        raise ValueError(f"cannot shard {n} over {world} ranks in multiples of {multiple}")
+    per = n // world
+    return rank * per, (rank + 1) * per
+
+
+def shard_plan(config, world: int, rank: int) -> dict:
+    """Row/column ranges of every sharded tensor of one layer for `rank` (global index space)."""
+    hd = config.head_dim
+    q0, q1 = shard_range(config.num_heads, world, rank)
+    kv0, kv1 = shard_range(config.num_kv_heads, world, rank)
+    plan = {
+        "q_rows": (q0 * hd, q1 * hd), "k_rows": (kv0 * hd, kv1 * hd), "v_rows": (kv0 * hd, kv1 * hd),
+        "o_cols": (q0 * hd, q1 * hd),
+        "vocab_rows": shard_range(config.vocab_size, world, rank) if config.vocab_size % world == 0 else
+        (rank * (config.vocab_size // world), config.vocab_size if rank == world - 1 else (rank + 1) * (config.vocab_size // world)),
+    }
+    if config.is_moe:
+        plan["experts"] = shard_range(config.num_experts, world, rank)
+    else:
+        # FP8 128-blocks / NVF4 32-blocks must not straddle ranks
+        plan["inter"] = shard_range(config.intermediate_size, world, rank, multiple=128)
+    return plan
+
+
+def combine_greedy(pairs: np.ndarray, vocab_offsets: list[int]) -> int:
+    """pairs [world, 2] = (max logit as f32, local argmax as int32 bits): global greedy token with
+    np.argmax's tie rule (first maximum wins = lowest global index)."""
+    vals = pairs[:, 0].astype(np.float32)
+    idx = pairs[:, 1].view(np.int32) if pairs.dtype == np.float32 else pairs[:, 1].astype(np.int64)
+    best = int(np.argmax(vals))           # first max over ranks; ranks are in vocabulary order
+    return int(vocab_offsets[best] + int(idx[best]))
+
+
+class TensorParallel:
+    """NCCL communicator of this process (rank <-> GPU)."""
+
+    def __init__(self, rank: int, world: int):
+        self.rank, self.world = rank, world
+        self._ready = False
+
+    @classmethod
+    def from_env(cls) -> "TensorParallel":
+        return cls(int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
+
+    def init(self, exchange=None, id_file: str | None = None) -> "TensorParallel":
+        """exchange(bytes|None) -> bytes: broadcast of rank 0's 128-byte id (e.g. over
+        torch.distributed); or id_file: a path on a shared filesystem."""
+        from .._lib import api
+        if self.world == 1 or self._ready:
+            self._ready = True
+            return self
+        buf = (C.c_char * 128)()
+        if self.rank == 0:
+            api.nccl_unique_id(buf)
+        if exchange is not None:
+            raw = exchange(bytes(buf) if self.rank == 0 else None)
+        elif id_file is not None:
+            if self.rank == 0:
+                with open(id_file + ".tmp", "wb") as f:
+                    f.write(bytes(buf))
+                os.replace(id_file + ".tmp", id_file)
+            t0 = time.time()
+            while not os.path.exists(id_file):
+                if time.time() - t0 > 120:
+                    raise RuntimeError("TensorParallel.init: timed out waiting for the NCCL id file")
+                time.sleep(0.05)
+            with open(id_file, "rb") as f:
+                raw = f.read()
+        else:
+            raise ValueError("TensorParallel.init needs exchange= or id_file= when world > 1")
+        idbuf = (C.c_char * 128).from_buffer_copy(raw)
+        api.nccl_init(idbuf, self.rank, self.world)
+        self._ready = True
+        return self
+
+    def allreduce(self, x) -> None:
+        """In-place bf16 sum over ranks on the current stream."""
+        if self.world == 1:
+            return
+        from .._lib import api
+        from ..core.stream import current_stream_handle
+        api.nccl_allreduce_bf16(x.device_ptr, x.size, current_stream_handle())
+
+    def allgather_bytes(self, send, recv, nbytes: int) -> None:
+        from .._lib import api
+        from ..core.stream import current_stream_handle
+        api.nccl_allgather(send.device_ptr, recv.device_ptr, nbytes, current_stream_handle())
+
+    def destroy(self) -> None:
+        if self._ready and self.world > 1:
+            from .._lib import api
+            api.nccl_destroy()
+        self._ready = False
+
+
+def torch_exchange():
+    """exchange() over an initialised torch.distributed process group (harness plumbing)."""
+    import torch.distributed as dist
+
+    def ex(payload):
+        obj = [payload]
+        dist.broadcast_object_list(obj, src=0)
+        return obj[0]
+    return ex
+
+
+__all__ = ["shard_range", "shard_plan", "combine_greedy", "TensorParallel", "torch_exchange"]

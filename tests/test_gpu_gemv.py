@@ -89,8 +89,9 @@ def test_gemv_fp8_epilogues():
     out = gk.empty((M, N), gk.bfloat16)
     y = orc.gemv_fp8_bf16(A, codes, scale)
     # bias then residual, reference rounding points
+    gbias, gres = gk.from_numpy(bias), gk.from_numpy(res)      # keep the owners alive across the launch
     api.gemv_fp8_bf16_ex(gA.device_ptr, gB.device_ptr, gS.device_ptr, out.device_ptr, M, K, N,
-                         gk.from_numpy(bias).device_ptr, gk.from_numpy(res).device_ptr, None)
+                         gbias.device_ptr, gres.device_ptr, None)
     exp = orc.add_inplace_bf16(orc.bias_add_bf16(y, bias), res)
     assert rel_err(out.to_numpy(), exp) < TOL
     # gate/up + silu*mul
@@ -114,7 +115,7 @@ def test_gemv_fp8_linearity_full_size():
     col = ops.gemv_fp8_bf16(gk.from_numpy(bf16(e)), gB, gS).to_numpy()
     from pygpukit_b200.llm.quant import fp8_e4m3_table
     exp = bf16(fp8_e4m3_table()[codes[:, 1234]] * f32(scale)[:, 1234 // 128].repeat(128))
-    assert np.array_equal(col, exp)
+    assert np.array_equal(f32(col), f32(exp))        # value equality: a -0.0 weight gives +0.0 (0 + 1*-0)
     a1, a2 = rand_bf16(rng, (K,)), rand_bf16(rng, (K,))
     s = bf16(f32(a1) + f32(a2))
     y1 = f32(ops.gemv_fp8_bf16(gk.from_numpy(a1), gB, gS).to_numpy())
@@ -222,8 +223,8 @@ def test_gemv_nvf4_swiglu():
     d, s = interleave(dg, du), interleave(sg, su)
     A = rand_bf16(rng, (M, K))
     out = gk.empty((M, I), gk.bfloat16)
-    api.gemv_nvf4_swiglu_bf16(gk.from_numpy(A).device_ptr, gk.from_numpy(d).device_ptr, gk.from_numpy(s).device_ptr,
-                              out.device_ptr, M, K, 2 * I, None)
+    gA, gd, gs = gk.from_numpy(A), gk.from_numpy(d), gk.from_numpy(s)
+    api.gemv_nvf4_swiglu_bf16(gA.device_ptr, gd.device_ptr, gs.device_ptr, out.device_ptr, M, K, 2 * I, None)
     g = orc.gemv_nvf4_bf16(A, dg, sg)
     u = orc.gemv_nvf4_bf16(A, du, su)
     exp = orc.mul_inplace_bf16(orc.silu_bf16(g), u)

@@ -1,0 +1,119 @@
+"""End-to-end parity of the decode path against the CPU restatement of the reference's step
+(oracle/model.py): logits within 1e-2 relative (BF16 bar of BASELINE.json), greedy tokens identical,
+graph replay == eager, for FP8 / NVF4 / BF16 weights, QK-norm on/off, dense and MoE."""
+import numpy as np
+import pytest
+
+import pygpukit_b200 as gk
+from oracle.model import OracleModel
+from pygpukit_b200 import llm
+from tests.util import f32, rel_err
+
+pytestmark = pytest.mark.gpu
+
+MAX_SEQ = 96
+
+
+def _build(name, fmt, **kw):
+    m = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, seed=7, std=0.05, **kw)
+    m.init_decode(MAX_SEQ, max_batch_size=16)
+    return m
+
+
+def _check_tokens(got, exp, margins, n_prompt):
+    """identical greedy tokens; a divergence is tolerated only at a step whose oracle top-1/top-2
+    margin is below one bf16 ulp of the logit scale (a genuine tie), and ends the comparison."""
+    for i, (g, e) in enumerate(zip(got[n_prompt:], exp[n_prompt:])):
+        if g != e:
+            assert margins[i] <= 2.0 ** -6, f"token {i}: got {g}, oracle {e}, margin {margins[i]}"
+            return i
+    return len(exp) - n_prompt
+
+
+@pytest.mark.parametrize("name,fmt", [("tiny-llama", "fp8"), ("tiny-qwen3", "fp8"), ("tiny-llama", "nvf4"),
+                                      ("tiny-qwen3", "bf16"), ("tiny-moe", "fp8"), ("tiny-moe", "nvf4")])
+def test_greedy_tokens_match_oracle(name, fmt):
+    model = _build(name, fmt)
+    orc_model = OracleModel(model, MAX_SEQ)
+    rng = np.random.default_rng(3)
+    prompt = [int(t) for t in rng.integers(0, model.config.vocab_size, 12)]
+    n_new = 24
+    exp, margins = orc_model.generate(prompt, n_new)
+    got = model.generate(prompt, n_new, temperature=0.0, use_graph=True)
+    assert len(got) == len(prompt) + n_new
+    agreed = _check_tokens(got, exp, margins, len(prompt))
+    assert agreed >= n_new // 2, f"only {agreed} tokens before a tie"
+    # eager (no graph) path gives the same tokens
+    model2 = _build(name, fmt)
+    got2 = model2.generate(prompt, n_new, temperature=0.0, use_graph=False)
+    _check_tokens(got2, exp, margins, len(prompt))
+
+
+@pytest.mark.parametrize("name,fmt", [("tiny-llama", "fp8"), ("tiny-qwen3", "nvf4")])
+def test_decode_m1_logits_vs_oracle(name, fmt):
+    model = _build(name, fmt)
+    orc_model = OracleModel(model, MAX_SEQ)
+    strat = llm.DecodeM1()
+    strat.bind(model)
+    rng = np.random.default_rng(5)
+    toks = [int(t) for t in rng.integers(0, model.config.vocab_size, 6)]
+    for pos, t in enumerate(toks):
+        got = strat.step(t, pos, pos + 1, model.buffers).to_numpy()[0]
+        exp, _ = orc_model.step(t, pos, pos + 1)
+        assert rel_err(got, exp) < 1e-2, f"pos {pos}"
+    # the graph strategy returns the same logits for the next position
+    g = llm.DecodeM1Graph()
+    g.bind(model)
+    g.init_graph(MAX_SEQ)
+    # graph capture clobbers cache slot 0: replay the prefix through the graph itself
+    for pos, t in enumerate(toks):
+        lg = g.step_graph(t, pos, pos + 1).to_numpy()[0]
+    exp, tok = orc_model.step(toks[-1], len(toks) - 1, len(toks))
+    assert rel_err(lg, exp) < 1e-2
+    assert int(model.buffers.next_token.to_numpy()[0]) == int(np.argmax(f32(lg)))
+
+
+def test_batch_decode_equals_single_steps():
+    """DecodeBatch: M consecutive tokens in one call == M single-token steps (same cache contents)."""
+    model = _build("tiny-qwen3", "fp8")
+    rng = np.random.default_rng(6)
+    toks = [int(t) for t in rng.integers(0, model.config.vocab_size, 8)]
+    single = []
+    for pos, t in enumerate(toks):
+        single.append(model._decode_step_fixed_cache(t, pos, pos + 1).to_numpy()[0].copy())
+    model_b = _build("tiny-qwen3", "fp8")
+    b = llm.DecodeBatch(8)
+    b.bind(model_b)
+    h = b.step_batch(toks, 0, len(toks), None).to_numpy()
+    for i in range(len(toks)):
+        assert rel_err(h[i], single[i]) < 1e-2
+    k1 = model.blocks[0].attn._k_cache.to_numpy()
+    k2 = model_b.blocks[0].attn._k_cache.to_numpy()
+    assert np.array_equal(k1[:, :len(toks)], k2[:, :len(toks)])      # layer-0 cache: bit-exact copy path
+
+
+def test_fp8_device_quantiser_matches_host():
+    from pygpukit_b200.llm.quant import quantize_fp8_e4m3_block
+    from pygpukit_b200.llm.random_init import normal_bf16, quantize_fp8
+    w = normal_bf16((384, 512), 99, 0.02)
+    lin = quantize_fp8(w)
+    codes, scale = quantize_fp8_e4m3_block(f32(w.to_numpy()))
+    assert np.array_equal(lin.scale_inv.to_numpy(), scale)
+    assert np.array_equal(lin.weight_fp8.to_numpy(), codes)
+    z = f32(w.to_numpy())
+    assert abs(z.std() - 0.02) < 1e-3 and abs(z.mean()) < 1e-3      # the device RNG is N(0, std^2)
+
+
+def test_api_surface_and_errors():
+    for n in ("CausalTransformerModel", "GPT2Model", "LlamaModel", "QwenModel", "TransformerConfig", "Attention",
+              "MLP", "MoELayer", "Norm", "TransformerBlock", "Linear", "LinearBF16", "LinearFP8", "DecodeM1",
+              "DecodeM1Graph", "DecodeBatch", "DecodeBuffers", "precompute_freqs_cis", "sample_token"):
+        assert hasattr(llm, n), n
+    lin = llm.LinearFP8(gk.zeros((128, 256), gk.uint8), gk.zeros((1, 2), gk.bfloat16))
+    with pytest.raises(ValueError):
+        lin(gk.zeros((256,), gk.bfloat16))                # 1-D input
+    with pytest.raises(ValueError):
+        lin(gk.zeros((1, 128), gk.bfloat16))              # wrong in_features
+    s = llm.DecodeM1()
+    with pytest.raises(RuntimeError):
+        _ = s.model                                       # not bound
