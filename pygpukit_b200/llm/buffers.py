@@ -26,6 +26,7 @@ class DecodeBuffers:
     context_buf: GPUArray     # int32 [1]
     next_token: GPUArray      # int32 [M]  greedy result
     max_batch_size: int = 1
+    state_buf: GPUArray | None = None   # int32 [2 + M] = [position, context, tokens...]: ONE H2D copy per step
 
     # aliases with the reference's member names (buffers.py:26-188)
     @property
@@ -51,12 +52,14 @@ class DecodeBuffers:
         hq, hkv = config.num_heads // tp, config.num_kv_heads // tp
         inter = (config.moe_intermediate_size if config.is_moe else config.intermediate_size) // (1 if config.is_moe else tp)
         V = vocab_size if vocab_size is not None else config.vocab_size
+        state = zeros((2 + M,), int32)
         return cls(
+            state_buf=state,
             hidden=zeros((M, H), bfloat16), norm_out=zeros((M, H), bfloat16),
             qkv_proj_out=zeros((M, (hq + 2 * hkv) * hd), bfloat16), attn_flat=zeros((M, hq * hd), bfloat16),
             mlp_act=zeros((M, inter), bfloat16), partial=zeros((M, H), bfloat16),
             logits=zeros((M, V), bfloat16) if V else None,
-            token_buf=zeros((M,), int32), position_buf=zeros((1,), int32), context_buf=zeros((1,), int32),
+            token_buf=state.narrow(2, M), position_buf=state.narrow(0, 1), context_buf=state.narrow(1, 1),
             next_token=zeros((M,), int32), max_batch_size=M)
 
 

@@ -173,12 +173,35 @@ class CausalTransformerModel:
         api.decode_advance(b.position_buf.device_ptr, b.context_buf.device_ptr, 1, _st())
 
     def set_decode_state(self, token_id: int, position: int) -> None:
-        """token_buf = token_id, position_buf = position, context_buf = position + 1."""
+        """position_buf = position, context_buf = position + 1, token_buf = token_id (one 12-byte copy)."""
         b = self.buffers
-        st = np.array([token_id, position, position + 1], np.int32)
-        for i, buf in enumerate((b.token_buf, b.position_buf, b.context_buf)):
-            api.memcpy_h2d(buf.device_ptr, st[i:i + 1].ctypes.data_as(C.c_void_p), 4, _st())
+        st = np.array([position, position + 1, token_id], np.int32)
+        api.memcpy_h2d(b.state_buf.device_ptr, st.ctypes.data_as(C.c_void_p), 12, _st())
         api.stream_sync(_st()) if _st() is not None else api.device_sync()
+
+    def _pinned_state(self):
+        """Pinned host staging: int32[3] step inputs + int32[1] result (allocated once)."""
+        if getattr(self, "_pin", None) is None:
+            h = C.c_void_p()
+            api.host_alloc(C.byref(h), 16)
+            self._pin = h
+            self._pin_np = np.ctypeslib.as_array(C.cast(h, C.POINTER(C.c_int32)), shape=(4,))
+        return self._pin, self._pin_np
+
+    def decode_step_host(self, token_id: int, position: int) -> int:
+        """One greedy decode step with the HOST in the loop (what a serving loop does): token id and
+        position go host -> device from pinned memory (12 bytes), the step graph replays, the sampled
+        token comes back device -> host (4 bytes).  Returns the next token."""
+        assert self._graph is not None, "Call init_decode_graph first"
+        pin, arr = self._pinned_state()
+        arr[0], arr[1], arr[2] = position, position + 1, token_id
+        b = self.buffers
+        sh = self._graph_stream.handle
+        api.memcpy_h2d(b.state_buf.device_ptr, pin, 12, sh)
+        self._graph.replay(self._graph_stream)
+        api.memcpy_d2h(pin.value + 12, b.next_token.device_ptr, 4, sh)
+        api.stream_sync(sh)
+        return int(arr[3])
 
     def init_decode_graph(self) -> None:
         """Capture decode_step_device into one CUDA graph (replaces the reference's per-layer
