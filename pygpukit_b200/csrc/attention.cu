@@ -72,11 +72,12 @@ struct SdpaParams {
     unsigned* counters;       // [n_kv*row_tiles]
 };
 
-constexpr int kAttnWarps = 4;
+constexpr int kAttnWarps = 8;
+constexpr int kAttnU = 4;     // KV positions per lane group per batch
 constexpr float kNegBig = -1e30f;
 
 template <int DT, int HD, int RT>
-__global__ void __launch_bounds__(kAttnWarps * 32)
+__global__ void __launch_bounds__(kAttnWarps * 32, 2)
 sdpa_decode_kernel(SdpaParams p) {
     constexpr int EPL = KvVec<DT>::EPL;
     constexpr int LPR = HD / EPL;          // lanes per KV row
@@ -129,42 +130,68 @@ sdpa_decode_kernel(SdpaParams p) {
     const size_t esz = (DT == 0) ? 4 : 2;
     const uint8_t* Kb = (const uint8_t*)p.K + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
     const uint8_t* Vb = (const uint8_t*)p.V + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
-    constexpr int STEP = kAttnWarps * PPI;
-    // the loop bound is warp-uniform (jw does not depend on the lane): every lane executes the
-    // same number of iterations, so the full-mask shuffles below are always convergent
-    for (int jw = c0 + warp * PPI; jw < c1; jw += 2 * STEP) {
-        // two positions in flight per lane
-        const int ja = jw + slot, jb = jw + slot + STEP;
-        const bool va = ja < c1, vb = jb < c1;
-        uint4 ka, kb, wa, wb;
-        if (va) { ka = ldg_kv(Kb + (size_t)ja * HD * esz); wa = ldg_kv(Vb + (size_t)ja * HD * esz); }
-        if (vb) { kb = ldg_kv(Kb + (size_t)jb * HD * esz); wb = ldg_kv(Vb + (size_t)jb * HD * esz); }
+    // Each lane group (LPR lanes = one KV row) takes U positions per batch; all 2*U 16-byte loads of a
+    // batch are issued before any is used (8 x 16 B in flight per lane, ~8 MB over the grid: enough to
+    // cover the HBM latency-bandwidth product).  One online-softmax rescale per batch, not per position.
+    // The loop bound is warp-uniform, so the full-mask shuffles below are always convergent.
+    constexpr int U = kAttnU;
+    constexpr int STEP = kAttnWarps * PPI;          // positions per CTA per u-slot
+    for (int jw = c0 + warp * PPI; jw < c1; jw += U * STEP) {
+        uint4 kq[U], vq[U];
+        bool valid[U];
 #pragma unroll
-        for (int it = 0; it < 2; ++it) {
-            const bool valid = it ? vb : va;
-            const int j = it ? jb : ja;
-            float kf[EPL], vf[EPL];
-            if (valid) { KvVec<DT>::unpack(it ? kb : ka, kf); KvVec<DT>::unpack(it ? wb : wa, vf); }
-            else {
-#pragma unroll
-                for (int e = 0; e < EPL; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
+        for (int u = 0; u < U; ++u) {
+            const int j = jw + slot + u * STEP;
+            valid[u] = j < c1;
+            if (valid[u]) {
+                kq[u] = ldg_kv(Kb + (size_t)j * HD * esz);
+                vq[u] = ldg_kv(Vb + (size_t)j * HD * esz);
+            } else {
+                kq[u] = make_uint4(0, 0, 0, 0); vq[u] = make_uint4(0, 0, 0, 0);
             }
+        }
+        float sc[U][RT];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float kf[EPL];
+            KvVec<DT>::unpack(kq[u], kf);
+            const int j = jw + slot + u * STEP;
 #pragma unroll
             for (int r = 0; r < RT; ++r) {
-                float s = 0.f;
+                float t = 0.f;
 #pragma unroll
-                for (int e = 0; e < EPL; ++e) s = fmaf(q[r][e], kf[e], s);
+                for (int e = 0; e < EPL; ++e) t = fmaf(q[r][e], kf[e], t);
 #pragma unroll
-                for (int off = LPR / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
-                if (valid && j < limit[r]) {
-                    float mn = fmaxf(m[r], s);
-                    float corr = exp2f(m[r] - mn), pj = exp2f(s - mn);
-                    l[r] = fmaf(l[r], corr, pj);
-#pragma unroll
-                    for (int e = 0; e < EPL; ++e) o[r][e] = fmaf(o[r][e], corr, pj * vf[e]);
-                    m[r] = mn;
-                }
+                for (int off = LPR / 2; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+                sc[u][r] = (valid[u] && j < limit[r]) ? t : kNegBig;
             }
+        }
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            float mn = m[r];
+#pragma unroll
+            for (int u = 0; u < U; ++u) mn = fmaxf(mn, sc[u][r]);
+            const float corr = exp2f(m[r] - mn);
+            m[r] = mn;
+            l[r] *= corr;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) o[r][e] *= corr;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                // masked slots carry kNegBig: exp2(kNegBig - mn) == 0 unless mn is kNegBig too
+                const float pj = (sc[u][r] > 0.5f * kNegBig) ? exp2f(sc[u][r] - mn) : 0.f;
+                sc[u][r] = pj;
+                l[r] += pj;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float vf[EPL];
+            KvVec<DT>::unpack(vq[u], vf);
+#pragma unroll
+            for (int r = 0; r < RT; ++r)
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) o[r][e] = fmaf(sc[u][r], vf[e], o[r][e]);
         }
     }
     // merge the PPI slots of the warp (lanes li, li+LPR, ...)
@@ -255,10 +282,10 @@ static int launch_sdpa(SdpaParams p, cudaStream_t st) {
     const int G = p.hq / p.n_kv, R = G * p.q_len;
     const int row_tiles = (R + RT - 1) / RT;
     const int base_ctas = p.n_kv * row_tiles;
-    // enough CTAs for ~2 per SM, at least 256 positions per split
+    // enough CTAs for ~2 per SM, at least 128 positions (two batches of the 8 warps) per split
     int hint = p.context_len > 0 ? p.context_len : p.max_seq;
     int splits = (2 * sm_count() + base_ctas - 1) / base_ctas;
-    int max_splits = (hint + 255) / 256;
+    int max_splits = (hint + 127) / 128;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
     if (splits > 256) splits = 256;
