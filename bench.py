@@ -320,6 +320,8 @@ def run_ours(args) -> None:
     from pygpukit_b200.core.stream import CudaEvent, event_elapsed_ms, use_stream
     lib = load()
     api.device_set(local_rank)
+    pdl = os.environ.get("PGK_PDL", "1") == "1"
+    api.set_pdl(1 if pdl else 0)               # programmatic dependent launch between the step's kernels
     d = Dist(rank, local_rank, world)
     comm = llm.TensorParallel(rank, world).init(exchange=d.exchange()) if world > 1 else None
     K, W = args.steps, max(3, args.warmup)
@@ -415,7 +417,7 @@ def run_ours(args) -> None:
             "step_roofline": {"bytes_per_step_per_gpu": step_bytes, "achieved": step_bytes / (ms / K) / 1e6,
                               "unit": "GB/s", "frac": step_bytes / (ms / K) / 1e6 / peak,
                               "frac_of_8000": step_bytes / (ms / K) / 1e6 / 8000.0},
-            "clocks": clk, "token_streams_agree": bool(same_tokens), "build_s": t_build,
+            "pdl": pdl, "clocks": clk, "token_streams_agree": bool(same_tokens), "build_s": t_build,
         }
         if world == 1 and not args.no_cpu_baseline:
             s = cpu_decode_sample(args.model, args.format, ctx, budget_s=15.0)

@@ -53,18 +53,47 @@ __global__ void rmsnorm_kernel(const void* __restrict__ x, const void* __restric
     griddep_launch();
     griddep_wait();
     const size_t base = (size_t)blockIdx.x * features;
+    // thread t owns elements t, t + bs, ... (the reference's partial sums); up to 32 of them are loaded
+    // up front (all loads in flight at once) and kept in registers for the second pass
+    constexpr int MAXE = 32;
+    float xv[MAXE];
+    const int bs = blockDim.x;
+    const bool cached = features <= bs * MAXE;
     float ss = 0.f;
-    for (int i = threadIdx.x; i < features; i += blockDim.x) {
-        float v = Elem<DT>::ld(x, base + i);
-        if (RESIDUAL) v += Elem<DT>::ld(res, base + i);   // fused_kernels.cuh:36-220 keeps the sum in f32
-        ss = fmaf(v, v, ss);
+    if (cached) {
+#pragma unroll
+        for (int e = 0; e < MAXE; ++e) {
+            const int i = threadIdx.x + e * bs;
+            xv[e] = 0.f;
+            if (i < features) {
+                xv[e] = Elem<DT>::ld(x, base + i);
+                if (RESIDUAL) xv[e] += Elem<DT>::ld(res, base + i);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < MAXE; ++e)
+            if (threadIdx.x + e * bs < features) ss = fmaf(xv[e], xv[e], ss);
+    } else {
+        for (int i = threadIdx.x; i < features; i += bs) {
+            float v = Elem<DT>::ld(x, base + i);
+            if (RESIDUAL) v += Elem<DT>::ld(res, base + i);   // fused_kernels.cuh:36-220 keeps the sum in f32
+            ss = fmaf(v, v, ss);
+        }
     }
     float tot = block_sum(ss, red);
     float inv = rsqrtf(tot / (float)features + eps);
-    for (int i = threadIdx.x; i < features; i += blockDim.x) {
-        float v = Elem<DT>::ld(x, base + i);
-        if (RESIDUAL) v += Elem<DT>::ld(res, base + i);
-        Elem<DT>::st(y, base + i, v * inv * Elem<DT>::ld(gamma, i));
+    if (cached) {
+#pragma unroll
+        for (int e = 0; e < MAXE; ++e) {
+            const int i = threadIdx.x + e * bs;
+            if (i < features) Elem<DT>::st(y, base + i, xv[e] * inv * Elem<DT>::ld(gamma, i));
+        }
+    } else {
+        for (int i = threadIdx.x; i < features; i += bs) {
+            float v = Elem<DT>::ld(x, base + i);
+            if (RESIDUAL) v += Elem<DT>::ld(res, base + i);
+            Elem<DT>::st(y, base + i, v * inv * Elem<DT>::ld(gamma, i));
+        }
     }
 }
 
