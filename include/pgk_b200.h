@@ -131,6 +131,27 @@ int pgk_gemv_bf16_ex(const void* A, const void* B_nk, void* C, int M, int K, int
 int pgk_gemv_bf16_argmax(const void* A, const void* B_nk, void* logits, int32_t* token, int K,
                          int N, void* stream);
 
+/* ------------------------------------------------------------------ fused RMSNorm -> GEMV
+ * y = GEMV( bf16(rmsnorm(A, gamma, eps)) ): the pre-norm of a decoder block folded into the staging of
+ * the activation rows of the GEMV that consumes it (one launch instead of two).  Every CTA recomputes
+ * the row statistics in the summation order of pgk_rmsnorm (= rmsnorm_bf16_kernel,
+ * norm_kernels.cuh:535-585), so results are bit-identical to pgk_rmsnorm followed by the plain GEMV
+ * (decode/m1.py:74-82 + layers/linear.py:241-251).  Needs K >= 512 and the fast-path alignment. */
+int pgk_rmsnorm_gemv_fp8_bf16(const void* A, const void* gamma, float eps, const void* B_nk, const void* S,
+                              void* C, int M, int K, int N, const void* bias, const void* residual, void* stream);
+int pgk_rmsnorm_gemv_fp8_swiglu_bf16(const void* A, const void* gamma, float eps, const void* Wg_nk,
+                                     const void* Sg, const void* Wu_nk, const void* Su, void* C, int M, int K,
+                                     int N, void* stream);
+int pgk_rmsnorm_gemv_nvf4_bf16(const void* A, const void* gamma, float eps, const void* B_data,
+                               const void* B_scale, void* C, int M, int K, int N, float alpha, const void* bias,
+                               const void* residual, void* stream);
+int pgk_rmsnorm_gemv_nvf4_swiglu_bf16(const void* A, const void* gamma, float eps, const void* Wgu_data,
+                                      const void* Wgu_scale, void* C, int M, int K, int N2, void* stream);
+int pgk_rmsnorm_gemv_bf16(const void* A, const void* gamma, float eps, const void* B_nk, void* C, int M, int K,
+                          int N, const void* bias, const void* residual, void* stream);
+int pgk_rmsnorm_gemv_bf16_argmax(const void* A, const void* gamma, float eps, const void* B_nk, void* logits,
+                                 int32_t* token, int K, int N, void* stream);
+
 /* ------------------------------------------------------------------ norm / rope / glue
  * dtype codes: 0 = f32, 1 = f16, 2 = bf16 */
 int pgk_rmsnorm(const void* x, const void* gamma, void* y, int rows, int features, float eps,

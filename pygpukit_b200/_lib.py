@@ -50,6 +50,12 @@ _SIGS = {
     "pgk_gemv_bf16": [vp, vp, vp, i32, i32, i32, vp],
     "pgk_gemv_bf16_ex": [vp, vp, vp, i32, i32, i32, vp, vp, vp],
     "pgk_gemv_bf16_argmax": [vp, vp, vp, vp, i32, i32, vp],
+    "pgk_rmsnorm_gemv_fp8_bf16": [vp, vp, f32, vp, vp, vp, i32, i32, i32, vp, vp, vp],
+    "pgk_rmsnorm_gemv_fp8_swiglu_bf16": [vp, vp, f32, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "pgk_rmsnorm_gemv_nvf4_bf16": [vp, vp, f32, vp, vp, vp, i32, i32, i32, f32, vp, vp, vp],
+    "pgk_rmsnorm_gemv_nvf4_swiglu_bf16": [vp, vp, f32, vp, vp, vp, i32, i32, i32, vp],
+    "pgk_rmsnorm_gemv_bf16": [vp, vp, f32, vp, vp, i32, i32, i32, vp, vp, vp],
+    "pgk_rmsnorm_gemv_bf16_argmax": [vp, vp, f32, vp, vp, vp, i32, i32, vp],
     "pgk_rmsnorm": [vp, vp, vp, i32, i32, f32, i32, vp],
     "pgk_layernorm": [vp, vp, vp, vp, i32, i32, f32, i32, vp],
     "pgk_rmsnorm_residual": [vp, vp, vp, vp, i32, i32, f32, i32, vp],

@@ -22,13 +22,23 @@
 namespace pgk {
 
 template <int M>
-__device__ __forceinline__ void stage_activations_bf16(const uint16_t* __restrict__ A, int K, uint16_t* a_s) {
+__device__ __forceinline__ void stage_activations_bf16(const uint16_t* __restrict__ A, int K, uint16_t* a_s,
+                                                       const uint16_t* __restrict__ gamma = nullptr, float eps = 0.f) {
     const int nvec = K >> 3, nchunk = K >> 4;
+    float rinv[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+        rinv[m] = gamma ? row_inv_rms_ref_order(A + (size_t)m * K, K, eps, reinterpret_cast<float*>(a_s)) : 1.f;
+    const uint4* gv = reinterpret_cast<const uint4*>(gamma);
 #pragma unroll
     for (int m = 0; m < M; ++m) {
         const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
         uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)m * K);
-        for (int j = threadIdx.x; j < nvec; j += blockDim.x) dst[(j & 1) * nchunk + (j >> 1)] = __ldg(src + j);
+        for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
+            uint4 v = __ldg(src + j);
+            if (gamma) v = norm8_bf16(v, __ldg(gv + j), rinv[m]);
+            dst[(j & 1) * nchunk + (j >> 1)] = v;
+        }
     }
     __syncthreads();
 }
@@ -76,7 +86,7 @@ gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
     if (row_begin < row_end) load_group(row_begin, 0);
     griddep_launch();
     griddep_wait();
-    stage_activations_bf16<M>(A, K, a_s);
+    stage_activations_bf16<M>(A, K, a_s, epi.norm_gamma, epi.norm_eps);
 
     const uint4* ap0 = reinterpret_cast<const uint4*>(a_s);
     bool preloaded = true;
@@ -205,12 +215,14 @@ static int launch_bf16(const uint16_t* A, const uint16_t* B, uint16_t* C, int K,
 static bool al(const void* p, int a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
 static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, int N, const void* bias,
-                         const void* residual, cudaStream_t st) {
+                         const void* residual, cudaStream_t st, const void* gamma = nullptr, float eps = 0.f) {
     PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
     const uint16_t* a = (const uint16_t*)A;
     const uint16_t* b = (const uint16_t*)B;
     uint16_t* c = (uint16_t*)C;
     const bool fast = (K % 16 == 0) && al(A, 16) && al(B, 32) && ((size_t)K * 2 <= 200 * 1024);
+    PGK_REQUIRE(!gamma || (fast && K >= 512 && al(gamma, 16)),
+                "rmsnorm_gemv_bf16 failed: the fused norm needs K %% 16 == 0, K >= 512 and aligned pointers (K=%d)", K);
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
         long warps = (long)N * M;
@@ -223,7 +235,8 @@ static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, in
     for (int m0 = 0; m0 < M;) {
         int mt = M - m0 > max_m ? max_m : M - m0;
         if (mt == 3) mt = 2;
-        GemvEpilogue epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr};
+        GemvEpilogue epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
+                            (const uint16_t*)gamma, eps};
         int rc;
         if (mt == 1)      rc = launch_bf16<1, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
         else if (mt == 2) rc = launch_bf16<2, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
@@ -252,6 +265,20 @@ int pgk_gemv_bf16_argmax(const void* A, const void* B_nk, void* logits, int32_t*
     PGK_REQUIRE(K % 16 == 0 && al(A, 16) && al(B_nk, 32) && (size_t)K * 2 <= 200 * 1024,
                 "gemv_bf16_argmax failed: needs K%%16==0 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr};
+    return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
+                                token, (cudaStream_t)stream);
+}
+
+/* rmsnorm(x, gamma, eps) -> GEMV in one launch (norm rounded to bf16 exactly as the separate op). */
+int pgk_rmsnorm_gemv_bf16(const void* A, const void* gamma, float eps, const void* B_nk, void* C, int M, int K,
+                          int N, const void* bias, const void* residual, void* stream) {
+    return bf16_dispatch(A, B_nk, C, M, K, N, bias, residual, (cudaStream_t)stream, gamma, eps);
+}
+int pgk_rmsnorm_gemv_bf16_argmax(const void* A, const void* gamma, float eps, const void* B_nk, void* logits,
+                                 int32_t* token, int K, int N, void* stream) {
+    PGK_REQUIRE(K % 16 == 0 && K >= 512 && al(A, 16) && al(B_nk, 32) && al(gamma, 16) && (size_t)K * 2 <= 200 * 1024,
+                "rmsnorm_gemv_bf16_argmax failed: needs K%%16==0, K>=512 and aligned pointers (K=%d)", K);
+    GemvEpilogue epi = {nullptr, nullptr, (const uint16_t*)gamma, eps};
     return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
 }

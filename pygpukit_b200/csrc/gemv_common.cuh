@@ -35,16 +35,75 @@ inline GemvCfg pick_gemv_cfg(int n_rows, const int* max_ctas_per_sm /* index = w
     return best;
 }
 
+struct GemvEpilogue {
+    const uint16_t* bias;      // [N] bf16 or null
+    const uint16_t* residual;  // [M,N] bf16 or null
+    const uint16_t* norm_gamma = nullptr;  // [K] bf16: A <- bf16(rmsnorm(A) * gamma) while staging, or null
+    float norm_eps = 0.f;
+};
+
+// ---- fused RMSNorm prologue -------------------------------------------------------------------
+// inv_rms of one activation row in EXACTLY the summation order of the stand-alone rmsnorm kernel
+// (= the reference's rmsnorm_bf16_kernel, norm_kernels.cuh:535-585): bs = min(256, K^32) virtual
+// threads, thread t folds elements t, t+bs, ... with fma, a shuffle tree per warp, then a tree over
+// the warp totals.  `scratch` needs bs floats of shared memory; every thread returns the same value,
+// so fused and unfused paths give bit-identical normalised activations.
+__device__ __forceinline__ float row_inv_rms_ref_order(const uint16_t* __restrict__ row, int K, float eps,
+                                                       float* scratch) {
+    const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31;
+    const int bs = min(256, (K + 31) & ~31), nw = bs >> 5;
+    for (int v = tid; v < bs; v += nthr) {
+        // the first 16 elements of the virtual thread are loaded together (16 loads in flight), the
+        // fma chain then runs in index order; padding zeros leave the partial sum unchanged
+        float xv[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            const int i = v + e * bs;
+            xv[e] = (i < K) ? bf16_bits_to_f32(__ldg(row + i)) : 0.f;
+        }
+        float part = 0.f;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) part = fmaf(xv[e], xv[e], part);
+        for (int i = v + 16 * bs; i < K; i += bs) { float x = bf16_bits_to_f32(__ldg(row + i)); part = fmaf(x, x, part); }
+        scratch[v] = part;
+    }
+    __syncthreads();
+    float tv = 0.f;
+    for (int w = 0; w < nw; ++w) {
+        float t = warp_sum(scratch[w * 32 + lane]);
+        if (lane == w) tv = t;
+    }
+    const float ss = warp_sum(tv);
+    __syncthreads();                       // scratch is free again
+    return rsqrtf(ss / (float)K + eps);
+}
+// eight elements: bf16( x * inv * gamma ) (left to right, as rmsnorm_bf16_kernel), packed as bf16 bits
+__device__ __forceinline__ uint4 norm8_bf16(const uint4& x, const uint4& g, float inv) {
+    uint4 o;
+    o.x = pack_bf16x2(bf16lo(x.x) * inv * bf16lo(g.x), bf16hi(x.x) * inv * bf16hi(g.x));
+    o.y = pack_bf16x2(bf16lo(x.y) * inv * bf16lo(g.y), bf16hi(x.y) * inv * bf16hi(g.y));
+    o.z = pack_bf16x2(bf16lo(x.z) * inv * bf16lo(g.z), bf16hi(x.z) * inv * bf16hi(g.z));
+    o.w = pack_bf16x2(bf16lo(x.w) * inv * bf16lo(g.w), bf16hi(x.w) * inv * bf16hi(g.w));
+    return o;
+}
+
 // Stage A[M,K] (bf16) into shared memory as range-shifted f16.  Layout per row: four planes
 // [K/32 chunks][8 halves], plane p holding k%32 in [8p, 8p+8), so that the consumer's
 // per-lane 16-byte reads (lane = chunk) are bank-conflict free.
 // PLANES = false keeps the natural k order (used by the column-parallel NVF4 kernel).
 template <int M, bool PLANES = true>
 __device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict__ A, int K,
-                                                      __half* a_s, float* inv_s, uint32_t* red) {
+                                                      __half* a_s, float* inv_s, uint32_t* red,
+                                                      const uint16_t* __restrict__ gamma = nullptr,
+                                                      float eps = 0.f) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int nvec = K >> 3;  // 16-byte vectors per row
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    float rinv[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+        rinv[m] = gamma ? row_inv_rms_ref_order(A + (size_t)m * K, K, eps, reinterpret_cast<float*>(a_s)) : 1.f;
+    const uint4* gv = reinterpret_cast<const uint4*>(gamma);
     uint32_t mx[M];
 #pragma unroll
     for (int m = 0; m < M; ++m) mx[m] = 0;
@@ -53,6 +112,7 @@ __device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict
         const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
         for (int j = tid; j < nvec; j += nthr) {
             uint4 v = __ldg(src + j);
+            if (gamma) v = norm8_bf16(v, __ldg(gv + j), rinv[m]);
             uint32_t t = __vmaxu2(__vmaxu2(v.x & 0x7fff7fffu, v.y & 0x7fff7fffu),
                                   __vmaxu2(v.z & 0x7fff7fffu, v.w & 0x7fff7fffu));
             mx[m] = max(mx[m], max(t & 0xffffu, t >> 16));
@@ -83,6 +143,7 @@ __device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict
         uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)m * K);
         for (int j = tid; j < nvec; j += nthr) {
             uint4 v = __ldg(src + j);
+            if (gamma) v = norm8_bf16(v, __ldg(gv + j), rinv[m]);
             uint4 o;
             __half2 h;
             h = __floats2half2_rn(bf16lo(v.x) * mult[m], bf16hi(v.x) * mult[m]); o.x = *reinterpret_cast<uint32_t*>(&h);
@@ -100,10 +161,6 @@ __device__ __forceinline__ float silu_ref(float x) {
     return x / (1.0f + __expf(-x));
 }
 
-struct GemvEpilogue {
-    const uint16_t* bias;      // [N] bf16 or null
-    const uint16_t* residual;  // [M,N] bf16 or null
-};
 
 
 }  // namespace pgk

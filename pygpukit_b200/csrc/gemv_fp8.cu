@@ -84,7 +84,7 @@ gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
     if (row_begin < row_end) load_group(row_begin, 0);
     griddep_launch();
     griddep_wait();
-    stage_activations_f16<M>(A, K, a_s, inv_s, red);
+    stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
 
     const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
     bool preloaded = true;
@@ -219,12 +219,15 @@ static bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 // re-read once per slab; the tcgen05 skinny GEMM takes over for M >= 16, see gemm_w8a16_tc.cu).
 static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, const void* B1,
                              const void* S1, void* C, int M, int K, int N, const void* bias,
-                             const void* residual, bool swiglu, cudaStream_t st) {
+                             const void* residual, bool swiglu, cudaStream_t st, const void* gamma = nullptr,
+                             float eps = 0.f) {
     PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_fp8_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
     const bool fast = (K % 32 == 0) && aligned16(A) && aligned32(B0) && (!swiglu || aligned32(B1)) &&
                       ((size_t)K * 2 + 1024 <= 200 * 1024);
     const uint16_t* a = (const uint16_t*)A;
     uint16_t* c = (uint16_t*)C;
+    PGK_REQUIRE(!gamma || (fast && K >= 512 && aligned16(gamma)),
+                "rmsnorm_gemv_fp8_bf16 failed: the fused norm needs K %% 32 == 0, K >= 512 and aligned pointers (K=%d)", K);
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
         long warps = (long)N * M;
@@ -248,7 +251,8 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
         int mt = M - m0;
         if (mt > max_m) mt = max_m;
         GemvEpilogue epi = {(const uint16_t*)bias,
-                            residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr};
+                            residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
+                            (const uint16_t*)gamma, eps};
         const uint16_t* am = a + (size_t)m0 * K;
         uint16_t* cm = c + (size_t)m0 * N;
         int rc = 0;
@@ -289,6 +293,20 @@ int pgk_gemv_fp8_swiglu_bf16(const void* A, const void* Wg_nk, const void* Sg, c
                              const void* Su, void* C, int M, int K, int N, void* stream) {
     return gemv_fp8_dispatch(A, Wg_nk, Sg, Wu_nk, Su, C, M, K, N, nullptr, nullptr, true,
                              (cudaStream_t)stream);
+}
+
+/* rmsnorm(x, gamma, eps) -> W8A16 GEMV in ONE launch: every CTA normalises the activation rows while it
+ * stages them (same summation order and bf16 rounding as pgk_rmsnorm / norm_kernels.cuh:535-585). */
+int pgk_rmsnorm_gemv_fp8_bf16(const void* A, const void* gamma, float eps, const void* B_nk, const void* S,
+                              void* C, int M, int K, int N, const void* bias, const void* residual, void* stream) {
+    return gemv_fp8_dispatch(A, B_nk, S, nullptr, nullptr, C, M, K, N, bias, residual, false,
+                             (cudaStream_t)stream, gamma, eps);
+}
+int pgk_rmsnorm_gemv_fp8_swiglu_bf16(const void* A, const void* gamma, float eps, const void* Wg_nk,
+                                     const void* Sg, const void* Wu_nk, const void* Su, void* C, int M, int K,
+                                     int N, void* stream) {
+    return gemv_fp8_dispatch(A, Wg_nk, Sg, Wu_nk, Su, C, M, K, N, nullptr, nullptr, true,
+                             (cudaStream_t)stream, gamma, eps);
 }
 
 }  // extern "C"

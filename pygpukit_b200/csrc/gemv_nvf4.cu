@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
     }
     griddep_launch();
     griddep_wait();
-    stage_activations_f16<M, false>(p.A, K, a_s, inv_s, red_u);
+    stage_activations_f16<M, false>(p.A, K, a_s, inv_s, red_u, p.epi.norm_gamma, p.epi.norm_eps);
 
     float acc[M][COLS];
 #pragma unroll
@@ -320,11 +320,13 @@ static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) =
 
 static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C, int M, int K, int N,
                          float alpha, const void* bias, const void* residual, bool swiglu,
-                         cudaStream_t st) {
+                         cudaStream_t st, const void* gamma = nullptr, float eps = 0.f) {
     PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_nvf4_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
     const bool fast = (K % 32 == 0) && (N % 16 == 0) && al16(A) && al16(Bd) && al16(Bs) &&
                       ((size_t)K * 2 + kNvf4Hdr <= 200 * 1024);
     PGK_REQUIRE(fast || !swiglu, "gemv_nvf4_swiglu_bf16 failed: needs K%%32==0, N%%16==0 and 16-byte aligned pointers");
+    PGK_REQUIRE(!gamma || (fast && K >= 512 && al16(gamma)),
+                "rmsnorm_gemv_nvf4_bf16 failed: the fused norm needs the fast path and K >= 512 (K=%d)", K);
     const int Nout = swiglu ? N / 2 : N;
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
@@ -346,7 +348,8 @@ static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C,
         p.Bs = (const uint8_t*)Bs;
         p.C = (uint16_t*)C + (size_t)m0 * Nout;
         p.K = K; p.N = N; p.alpha = alpha;
-        p.epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr};
+        p.epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
+                 (const uint16_t*)gamma, eps};
         int rc;
         if (swiglu) {
             if (mt == 1)      rc = launch_nvf4<1, 16, true>(p, st);
@@ -380,6 +383,19 @@ int pgk_gemv_nvf4_bf16_ex(const void* A, const void* B_data, const void* B_scale
 int pgk_gemv_nvf4_swiglu_bf16(const void* A, const void* Wgu_data, const void* Wgu_scale, void* C, int M,
                               int K, int N2, void* stream) {
     return nvf4_dispatch(A, Wgu_data, Wgu_scale, C, M, K, N2, 1.0f, nullptr, nullptr, true, (cudaStream_t)stream);
+}
+
+/* rmsnorm(x, gamma, eps) -> NVF4 GEMV in one launch (see pgk_rmsnorm_gemv_fp8_bf16). */
+int pgk_rmsnorm_gemv_nvf4_bf16(const void* A, const void* gamma, float eps, const void* B_data,
+                               const void* B_scale, void* C, int M, int K, int N, float alpha, const void* bias,
+                               const void* residual, void* stream) {
+    return nvf4_dispatch(A, B_data, B_scale, C, M, K, N, alpha, bias, residual, false, (cudaStream_t)stream,
+                         gamma, eps);
+}
+int pgk_rmsnorm_gemv_nvf4_swiglu_bf16(const void* A, const void* gamma, float eps, const void* Wgu_data,
+                                      const void* Wgu_scale, void* C, int M, int K, int N2, void* stream) {
+    return nvf4_dispatch(A, Wgu_data, Wgu_scale, C, M, K, N2, 1.0f, nullptr, nullptr, true,
+                         (cudaStream_t)stream, gamma, eps);
 }
 
 }  // extern "C"

@@ -213,6 +213,12 @@ def named_config(name: str, max_seq: int = 4096, tp_size: int = 1, tp_rank: int 
     if n == "tiny-qwen3":
         return TransformerConfig(vocab_size=1024, hidden_size=256, num_layers=2, num_heads=4, num_kv_heads=2,
                                  intermediate_size=512, _head_dim=128, norm_eps=1e-6, rope_theta=1e6, **kw), QWEN3_SPEC
+    if n == "small-qwen3":      # hidden >= 512: exercises the fused RMSNorm->GEMV prologue
+        return TransformerConfig(vocab_size=2048, hidden_size=512, num_layers=2, num_heads=8, num_kv_heads=2,
+                                 intermediate_size=1024, _head_dim=128, norm_eps=1e-6, rope_theta=1e6, **kw), QWEN3_SPEC
+    if n == "small-llama":
+        return TransformerConfig(vocab_size=2048, hidden_size=512, num_layers=2, num_heads=8, num_kv_heads=4,
+                                 intermediate_size=1536, _head_dim=64, norm_eps=1e-5, rope_theta=5e5, **kw), LLAMA_SPEC
     if n == "tiny-moe":
         return TransformerConfig(vocab_size=1024, hidden_size=256, num_layers=2, num_heads=4, num_kv_heads=2,
                                  intermediate_size=512, _head_dim=64, num_experts=8, num_experts_per_tok=2,

@@ -141,7 +141,7 @@ class Attention:
     # ---- decode
     def attend(self, x: GPUArray, position: int, context_len: int, *, qkv_buf: GPUArray | None = None,
                attn_buf: GPUArray | None = None, pos_buf: GPUArray | None = None,
-               ctx_buf: GPUArray | None = None) -> GPUArray:
+               ctx_buf: GPUArray | None = None, norm=None) -> GPUArray:
         """qkv projection -> QK-norm/RoPE/KV-write -> split-KV attention; returns [M, q_dim]
         (the input of o_proj).  M rows = M consecutive positions of one sequence."""
         assert self._k_cache is not None, "Call init_fixed_cache first"
@@ -150,7 +150,7 @@ class Attention:
         width = (H + 2 * Hkv) * hd
         if qkv_buf is not None and qkv_buf.shape[0] != M:
             qkv_buf = qkv_buf.slice_rows(M)
-        qkv = self.qkv_proj.forward(x, out=qkv_buf)
+        qkv = self.qkv_proj.forward(x, out=qkv_buf, norm=norm)   # norm: pre-attention RMSNorm fused into the launch
         if self.config.use_rope:
             api.qk_norm_rope_kv_write(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
                                       None if self.k_norm is None else self.k_norm.weight.device_ptr,

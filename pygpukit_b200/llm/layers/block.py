@@ -7,6 +7,7 @@ from __future__ import annotations
 from ...core.array import GPUArray
 from ...ops.elementwise import add_inplace
 from .attention import Attention
+from .linear import can_fuse_norm
 from .mlp import MLP
 from .moe import MoELayer
 from .norm import Norm
@@ -29,22 +30,29 @@ class TransformerBlock:
             return b if (b is None or b.shape[0] == M) else b.slice_rows(M)
 
         tp = self.comm is not None and self.comm.world > 1
-        x = self.attn_norm(hidden, out=buf("norm_out"))
-        a = self.attn.attend(x, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
-                             pos_buf=pos_buf, ctx_buf=ctx_buf)
+        # pre-norms ride inside the qkv / gate-up GEMV launches when the formats allow it
+        if can_fuse_norm(self.attn_norm, hidden.shape[1]):
+            a = self.attn.attend(hidden, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
+                                 pos_buf=pos_buf, ctx_buf=ctx_buf, norm=self.attn_norm)
+        else:
+            x = self.attn_norm(hidden, out=buf("norm_out"))
+            a = self.attn.attend(x, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
+                                 pos_buf=pos_buf, ctx_buf=ctx_buf)
         if tp:
             part = self.attn.o_proj.forward(a, out=buf("partial"))
             self.comm.allreduce(part)
             add_inplace(hidden, part)
         else:
             self.attn.o_proj.forward(a, out=hidden, residual=hidden)
-        x = self.mlp_norm(hidden, out=buf("norm_out"))
+        fuse_mlp = isinstance(self.mlp, MLP) and self.mlp.fuses_norm(self.mlp_norm)
+        x, nrm = (hidden, self.mlp_norm) if fuse_mlp else (self.mlp_norm(hidden, out=buf("norm_out")), None)
+        kw = {"norm": nrm} if fuse_mlp else {}
         if tp:
-            part = self.mlp.forward(x, out=buf("partial"), act_buf=buf("mlp_act"))
+            part = self.mlp.forward(x, out=buf("partial"), act_buf=buf("mlp_act"), **kw)
             self.comm.allreduce(part)
             add_inplace(hidden, part)
         else:
-            self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"))
+            self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"), **kw)
         return hidden
 
     def __call__(self, x: GPUArray, position_ids: list[int] | None = None, past_kv=None, use_cache: bool = False):

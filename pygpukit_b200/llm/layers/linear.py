@@ -41,6 +41,12 @@ def _ptr(a: GPUArray | None):
     return None if a is None else a.device_ptr
 
 
+def can_fuse_norm(norm, in_features: int) -> bool:
+    """RMSNorm (no bias) can be folded into the GEMV's activation staging (pgk_rmsnorm_gemv_*)."""
+    return (norm is not None and getattr(norm, "norm_type", None) == "rmsnorm" and norm.bias is None
+            and in_features >= 512 and in_features % 32 == 0)
+
+
 class LinearBF16:
     """y = x W^T + b, W [out_features, in_features] bf16 (layers/linear.py:25-99)."""
 
@@ -54,10 +60,17 @@ class LinearBF16:
         self.out_features = weight.shape[0]
         self.in_features = weight.shape[1]
 
-    def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None) -> GPUArray:
+    def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
+                norm=None) -> GPUArray:
+        """norm: an RMSNorm layer applied to x inside the same launch (see can_fuse_norm)."""
         _check_x(x, self.in_features)
         M = x.shape[0]
         y = _out2d(out, M, self.out_features)
+        if norm is not None:
+            api.rmsnorm_gemv_bf16(x.device_ptr, norm.weight.device_ptr, float(norm.eps), self.weight.device_ptr,
+                                  y.device_ptr, M, self.in_features, self.out_features, _ptr(self.bias),
+                                  _ptr(residual), _st())
+            return y
         api.gemv_bf16_ex(x.device_ptr, self.weight.device_ptr, y.device_ptr, M, self.in_features, self.out_features,
                          _ptr(self.bias), _ptr(residual), _st())
         return y
@@ -109,10 +122,16 @@ class LinearFP8:
         from ..quant import dequantize_fp8_e4m3_block
         return dequantize_fp8_e4m3_block(self.weight_fp8.to_numpy(), self.scale_inv.to_numpy())
 
-    def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None) -> GPUArray:
+    def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
+                norm=None) -> GPUArray:
         _check_x(x, self.in_features)
         M = x.shape[0]
         y = _out2d(out, M, self.out_features)
+        if norm is not None:
+            api.rmsnorm_gemv_fp8_bf16(x.device_ptr, norm.weight.device_ptr, float(norm.eps),
+                                      self.weight_fp8.device_ptr, self.scale_inv.device_ptr, y.device_ptr, M,
+                                      self.in_features, self.out_features, _ptr(self.bias), _ptr(residual), _st())
+            return y
         api.gemv_fp8_bf16_ex(x.device_ptr, self.weight_fp8.device_ptr, self.scale_inv.device_ptr, y.device_ptr, M,
                              self.in_features, self.out_features, _ptr(self.bias), _ptr(residual), _st())
         return y
@@ -151,10 +170,16 @@ class LinearNVF4:
         quantize_bf16_to_nvf4(weight_kn, data, scale)
         return cls(data, scale, K, N, bias)
 
-    def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None) -> GPUArray:
+    def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
+                norm=None) -> GPUArray:
         _check_x(x, self.in_features)
         M = x.shape[0]
         y = _out2d(out, M, self.out_features)
+        if norm is not None:
+            api.rmsnorm_gemv_nvf4_bf16(x.device_ptr, norm.weight.device_ptr, float(norm.eps), self.data.device_ptr,
+                                       self.scale.device_ptr, y.device_ptr, M, self.in_features, self.out_features,
+                                       self.alpha, _ptr(self.bias), _ptr(residual), _st())
+            return y
         api.gemv_nvf4_bf16_ex(x.device_ptr, self.data.device_ptr, self.scale.device_ptr, y.device_ptr, M,
                               self.in_features, self.out_features, self.alpha, _ptr(self.bias), _ptr(residual), _st())
         return y
@@ -167,4 +192,4 @@ class LinearNVF4:
         return self.data.nbytes + self.scale.nbytes
 
 
-__all__ = ["LinearBF16", "LinearFP8", "LinearNVF4", "Linear"]
+__all__ = ["LinearBF16", "LinearFP8", "LinearNVF4", "Linear", "can_fuse_norm"]

@@ -18,7 +18,7 @@ from ...core.factory import from_numpy
 from ...core.stream import current_stream_handle as _st
 from ...ops.elementwise import mul
 from ...ops.nn import gelu, silu
-from .linear import LinearBF16, LinearFP8, LinearNVF4
+from .linear import LinearBF16, LinearFP8, LinearNVF4, can_fuse_norm
 
 if TYPE_CHECKING:
     from ..config import TransformerConfig
@@ -71,10 +71,30 @@ class MLP:
                                       else self.gate_proj.out_features)
 
     # ---- fused activation( gate/up ) -> act_out [M, I]
-    def gate_up_act(self, x: GPUArray, *, out: GPUArray | None = None) -> GPUArray:
+    def fuses_norm(self, norm) -> bool:
+        """True when `norm` can ride inside the gate/up launch (FP8 / NVF4 fused SwiGLU kernels)."""
+        if self.activation != "silu" or not can_fuse_norm(norm, self.config.hidden_size):
+            return False
+        return self.gate_up_proj is not None or (
+            isinstance(self.gate_proj, LinearFP8) and isinstance(self.up_proj, LinearFP8)
+            and self.gate_proj.bias is None and self.up_proj.bias is None)
+
+    def gate_up_act(self, x: GPUArray, *, out: GPUArray | None = None, norm=None) -> GPUArray:
         M, K, I = x.shape[0], x.shape[1], self.intermediate_size
         if out is None:
             out = GPUArray((M, I), bfloat16)
+        if norm is not None:
+            g, e = norm.weight.device_ptr, float(norm.eps)
+            if self.gate_up_proj is not None:
+                gu = self.gate_up_proj
+                api.rmsnorm_gemv_nvf4_swiglu_bf16(x.device_ptr, g, e, gu.data.device_ptr, gu.scale.device_ptr,
+                                                  out.device_ptr, M, K, 2 * I, _st())
+            else:
+                gp, up = self.gate_proj, self.up_proj
+                api.rmsnorm_gemv_fp8_swiglu_bf16(x.device_ptr, g, e, gp.weight_fp8.device_ptr, gp.scale_inv.device_ptr,
+                                                 up.weight_fp8.device_ptr, up.scale_inv.device_ptr, out.device_ptr,
+                                                 M, K, I, _st())
+            return out
         if self.gate_up_proj is not None:
             gu = self.gate_up_proj
             api.gemv_nvf4_swiglu_bf16(x.device_ptr, gu.data.device_ptr, gu.scale.device_ptr, out.device_ptr, M, K,
@@ -94,11 +114,11 @@ class MLP:
         return out
 
     def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
-                act_buf: GPUArray | None = None) -> GPUArray:
+                act_buf: GPUArray | None = None, norm=None) -> GPUArray:
         if self.activation == "gelu":
             h = gelu(self.fc1(x))
             return self.fc2.forward(h, out=out, residual=residual)
-        h = self.gate_up_act(x, out=act_buf)
+        h = self.gate_up_act(x, out=act_buf, norm=norm)
         return self.down_proj.forward(h, out=out, residual=residual)
 
     def __call__(self, x: GPUArray) -> GPUArray:

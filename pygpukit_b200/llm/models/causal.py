@@ -26,6 +26,7 @@ from ...core.stream import CudaGraph, Stream, current_stream_handle as _st, use_
 from ..buffers import DecodeBuffers
 from ..config import ModelSpec, TransformerConfig
 from ..layers.block import TransformerBlock
+from ..layers.linear import can_fuse_norm
 from ..layers.norm import Norm
 from ..sampling import sample_token
 
@@ -160,13 +161,24 @@ class CausalTransformerModel:
         api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, self.config.hidden_size,
                                  b.token_buf.device_ptr, 1, 2, _st())
         self._layers(hidden, 0, self._max_seq, b, b.position_buf, b.context_buf)
-        x = self._final(hidden, b)
-        V = self._head.shape[0]
-        if self.tp == 1:
-            api.gemv_bf16_argmax(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
-                                 self.config.hidden_size, V, _st())
+        V, H = self._head.shape[0], self.config.hidden_size
+        fn = self.final_norm
+        if can_fuse_norm(fn, H):        # final RMSNorm rides inside the lm_head launch
+            g, e = fn.weight.device_ptr, float(fn.eps)
+            if self.tp == 1:
+                api.rmsnorm_gemv_bf16_argmax(hidden.device_ptr, g, e, self._head.device_ptr, b.logits.device_ptr,
+                                             b.token_buf.device_ptr, H, V, _st())
+            else:
+                api.rmsnorm_gemv_bf16(hidden.device_ptr, g, e, self._head.device_ptr, b.logits.device_ptr, 1, H, V,
+                                      None, None, _st())
         else:
-            api.gemv_bf16(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, 1, self.config.hidden_size, V, _st())
+            x = self._final(hidden, b)
+            if self.tp == 1:
+                api.gemv_bf16_argmax(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
+                                     H, V, _st())
+            else:
+                api.gemv_bf16(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, 1, H, V, _st())
+        if self.tp > 1:
             self.comm.allgather_bytes(b.logits, self._gathered_logits, V * 2)
             api.argmax(self._gathered_logits.device_ptr, b.token_buf.device_ptr, self.tp * V, 2, _st())
         api.memcpy_d2d(b.next_token.device_ptr, b.token_buf.device_ptr, 4, _st())

@@ -31,7 +31,8 @@ def _check_tokens(got, exp, margins, n_prompt):
 
 
 @pytest.mark.parametrize("name,fmt", [("tiny-llama", "fp8"), ("tiny-qwen3", "fp8"), ("tiny-llama", "nvf4"),
-                                      ("tiny-qwen3", "bf16"), ("tiny-moe", "fp8"), ("tiny-moe", "nvf4")])
+                                      ("tiny-qwen3", "bf16"), ("tiny-moe", "fp8"), ("tiny-moe", "nvf4"),
+                                      ("small-qwen3", "fp8"), ("small-llama", "nvf4"), ("small-qwen3", "bf16")])
 def test_greedy_tokens_match_oracle(name, fmt):
     model = _build(name, fmt)
     orc_model = OracleModel(model, MAX_SEQ)
@@ -117,3 +118,24 @@ def test_api_surface_and_errors():
     s = llm.DecodeM1()
     with pytest.raises(RuntimeError):
         _ = s.model                                       # not bound
+
+
+@pytest.mark.parametrize("fmt", ["fp8", "nvf4", "bf16"])
+def test_fused_rmsnorm_gemv_is_bit_identical_to_two_launches(fmt):
+    """pgk_rmsnorm_gemv_* == pgk_rmsnorm followed by the plain GEMV, bit for bit (same summation order)."""
+    from pygpukit_b200.llm.random_init import normal_bf16, quantize_fp8, quantize_nvf4
+    from tests.util import rand_bf16
+    rng = np.random.default_rng(17)
+    K, N = 1024, 768
+    for M in (1, 2, 4, 5):
+        x = gk.from_numpy(rand_bf16(rng, (M, K)))
+        norm = llm.Norm(gk.from_numpy(rand_bf16(rng, (K,), 0.5)), None, "rmsnorm", 1e-6)
+        if fmt == "fp8":
+            lin = quantize_fp8(normal_bf16((N, K), 5, 0.05))
+        elif fmt == "nvf4":
+            lin = quantize_nvf4(normal_bf16((K, N), 5, 0.05))
+        else:
+            lin = llm.LinearBF16(normal_bf16((N, K), 5, 0.05))
+        two = lin.forward(norm(x)).to_numpy()
+        one = lin.forward(x, norm=norm).to_numpy()
+        assert np.array_equal(one, two), f"M={M}"
