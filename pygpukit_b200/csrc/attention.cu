@@ -73,6 +73,7 @@ struct SdpaParams {
 };
 
 constexpr int kAttnWarps = 8;
+constexpr int kAttnMaxSplits = 128;
 constexpr int kAttnU = 4;     // KV positions per lane group per batch
 constexpr float kNegBig = -1e30f;
 
@@ -252,18 +253,40 @@ sdpa_decode_kernel(SdpaParams p) {
     if (s_ticket != (unsigned)(p.splits - 1)) return;
     __threadfence();
     const float* base = p.ws + tile_id * p.splits * RT * REC;
+    // last CTA of the tile: fold the partials in split order.  (m, l) of every split are staged in
+    // shared memory first so that the fold issues its o-loads 8 at a time instead of one dependent
+    // chain of L2 round trips per split.
+    __shared__ float s_m[RT][kAttnMaxSplits], s_l[RT][kAttnMaxSplits];
+    for (int idx = threadIdx.x; idx < RT * p.splits; idx += blockDim.x) {
+        const int r = idx / p.splits, sp = idx % p.splits;
+        const float* rr = base + ((size_t)sp * RT + r) * REC;
+        s_m[r][sp] = __ldcg(rr + HD);
+        s_l[r][sp] = __ldcg(rr + HD + 1);
+    }
+    __syncthreads();
     for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
-        int r = idx / HD, d = idx % HD;
-        int row = rt * RT + r;
+        const int r = idx / HD, d = idx % HD;
+        const int row = rt * RT + r;
         if (row >= R) continue;
         float mn = kNegBig;
-        for (int s = 0; s < p.splits; ++s) mn = fmaxf(mn, __ldcg(base + ((size_t)s * RT + r) * REC + HD));
+        for (int sp = 0; sp < p.splits; ++sp) mn = fmaxf(mn, s_m[r][sp]);
         float ov = 0.f, lv = 0.f;
-        for (int s = 0; s < p.splits; ++s) {
-            const float* rr = base + ((size_t)s * RT + r) * REC;
-            float c = exp2f(__ldcg(rr + HD) - mn);
-            ov = fmaf(__ldcg(rr + d), c, ov);
-            lv = fmaf(__ldcg(rr + HD + 1), c, lv);
+        int sp = 0;
+        for (; sp + 8 <= p.splits; sp += 8) {
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldcg(base + ((size_t)(sp + u) * RT + r) * REC + d);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float c = exp2f(s_m[r][sp + u] - mn);
+                ov = fmaf(v[u], c, ov);
+                lv = fmaf(s_l[r][sp + u], c, lv);
+            }
+        }
+        for (; sp < p.splits; ++sp) {
+            const float c = exp2f(s_m[r][sp] - mn);
+            ov = fmaf(__ldcg(base + ((size_t)sp * RT + r) * REC + d), c, ov);
+            lv = fmaf(s_l[r][sp], c, lv);
         }
         int g = row / p.q_len, t = row % p.q_len;
         st_elem<DT>(p.out, (size_t)(kvh * G + g) * p.o_sh + (size_t)t * p.o_st + d, lv > 0.f ? ov / lv : 0.f);
@@ -288,7 +311,7 @@ static int launch_sdpa(SdpaParams p, cudaStream_t st) {
     int max_splits = (hint + 127) / 128;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
-    if (splits > 256) splits = 256;
+    if (splits > kAttnMaxSplits) splits = kAttnMaxSplits;
     PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * RT * (HD + 2) * 4 <= kAttnWsBytes,
                 "sdpa_causal_fixed_cache failed: workspace too small for %d heads x %d rows", p.hq, p.q_len);
     if (!g_attn_ws) {

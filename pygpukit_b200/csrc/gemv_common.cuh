@@ -92,10 +92,10 @@ __device__ __forceinline__ uint4 norm8_bf16(const uint4& x, const uint4& g, floa
 // per-lane 16-byte reads (lane = chunk) are bank-conflict free.
 // PLANES = false keeps the natural k order (used by the column-parallel NVF4 kernel).
 template <int M, bool PLANES = true>
-__device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict__ A, int K,
-                                                      __half* a_s, float* inv_s, uint32_t* red,
-                                                      const uint16_t* __restrict__ gamma = nullptr,
-                                                      float eps = 0.f) {
+__device__ __forceinline__ void stage_activations_f16_3pass(const uint16_t* __restrict__ A, int K,
+                                                            __half* a_s, float* inv_s, uint32_t* red,
+                                                            const uint16_t* __restrict__ gamma = nullptr,
+                                                            float eps = 0.f) {
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int nvec = K >> 3;  // 16-byte vectors per row
     const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
@@ -151,6 +151,103 @@ __device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict
             h = __floats2half2_rn(bf16lo(v.z) * mult[m], bf16hi(v.z) * mult[m]); o.z = *reinterpret_cast<uint32_t*>(&h);
             h = __floats2half2_rn(bf16lo(v.w) * mult[m], bf16hi(v.w) * mult[m]); o.w = *reinterpret_cast<uint32_t*>(&h);
             dst[PLANES ? ((j & 3) * nchunk + (j >> 2)) : j] = o;
+        }
+    }
+    __syncthreads();
+}
+
+
+__device__ __forceinline__ uint4 bf16x8_to_f16x8_scaled(const uint4& v, float mult) {
+    uint4 o;
+    __half2 h;
+    h = __floats2half2_rn(bf16lo(v.x) * mult, bf16hi(v.x) * mult); o.x = *reinterpret_cast<uint32_t*>(&h);
+    h = __floats2half2_rn(bf16lo(v.y) * mult, bf16hi(v.y) * mult); o.y = *reinterpret_cast<uint32_t*>(&h);
+    h = __floats2half2_rn(bf16lo(v.z) * mult, bf16hi(v.z) * mult); o.z = *reinterpret_cast<uint32_t*>(&h);
+    h = __floats2half2_rn(bf16lo(v.w) * mult, bf16hi(v.w) * mult); o.w = *reinterpret_cast<uint32_t*>(&h);
+    return o;
+}
+
+// Single-global-read staging: each thread keeps its (<= VY) 16-byte vectors of a row in registers, so the
+// only L2 round trip is the first load; the RMSNorm statistics are taken from a raw copy of the row in
+// shared memory (reference summation order, see row_inv_rms_ref_order), the block maximum goes through
+// `red`, and the f16 planes are written last.  Same arithmetic, hence the same bits, as the 3-pass version.
+//   red[0 .. 63]   : per-warp maxima (m * 16 + warp)      red[64 .. 71] : per-virtual-warp sums of squares
+template <int M, bool PLANES = true>
+__device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict__ A, int K,
+                                                      __half* a_s, float* inv_s, uint32_t* red,
+                                                      const uint16_t* __restrict__ gamma = nullptr,
+                                                      float eps = 0.f) {
+    constexpr int VY = 8;
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int nvec = K >> 3;
+    if (nvec > VY * nthr) {
+        stage_activations_f16_3pass<M, PLANES>(A, K, a_s, inv_s, red, gamma, eps);
+        return;
+    }
+    const int lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+    const int nchunk = K >> 5;
+    const uint4* gv = reinterpret_cast<const uint4*>(gamma);
+    float* red_f = reinterpret_cast<float*>(red) + 64;
+#pragma unroll 1
+    for (int m = 0; m < M; ++m) {
+        const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
+        uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)m * K);
+        uint4 v[VY], g[VY];
+#pragma unroll
+        for (int e = 0; e < VY; ++e) {
+            const int j = tid + e * nthr;
+            if (j < nvec) {
+                v[e] = __ldg(src + j);
+                if (gamma) g[e] = __ldg(gv + j);
+            }
+        }
+        if (gamma) {
+            // raw row -> shared memory (natural order) for the reference-order sum of squares
+#pragma unroll
+            for (int e = 0; e < VY; ++e) {
+                const int j = tid + e * nthr;
+                if (j < nvec) dst[j] = v[e];
+            }
+            __syncthreads();
+            const uint16_t* raw = reinterpret_cast<const uint16_t*>(dst);
+            const int bs = min(256, (K + 31) & ~31), nvw = bs >> 5;
+            for (int w = warp; w < nvw; w += nwarp) {           // virtual warp w = virtual threads 32w .. 32w+31
+                float part = 0.f;
+                for (int i = w * 32 + lane; i < K; i += bs) { float x = bf16_bits_to_f32(raw[i]); part = fmaf(x, x, part); }
+                part = warp_sum(part);
+                if (lane == 0) red_f[w] = part;
+            }
+            __syncthreads();
+            const float ss = warp_sum(lane < nvw ? red_f[lane] : 0.f);
+            const float rinv = rsqrtf(ss / (float)K + eps);
+#pragma unroll
+            for (int e = 0; e < VY; ++e)
+                if (tid + e * nthr < nvec) v[e] = norm8_bf16(v[e], g[e], rinv);
+        }
+        uint32_t mx = 0;
+#pragma unroll
+        for (int e = 0; e < VY; ++e) {
+            if (tid + e * nthr < nvec) {
+                uint32_t t = __vmaxu2(__vmaxu2(v[e].x & 0x7fff7fffu, v[e].y & 0x7fff7fffu),
+                                      __vmaxu2(v[e].z & 0x7fff7fffu, v[e].w & 0x7fff7fffu));
+                mx = max(mx, max(t & 0xffffu, t >> 16));
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (lane == 0) red[m * 16 + warp] = mx;
+        __syncthreads();                 // also: every thread is done reading the raw row
+        uint32_t bm = 0;
+        for (int w = 0; w < nwarp; ++w) bm = max(bm, red[m * 16 + w]);
+        int ex = (int)(bm >> 7);
+        ex = min(max(ex, 15), 254);
+        if ((bm >> 7) == 255) ex = 141;
+        const float mult = __uint_as_float((uint32_t)(268 - ex) << 23);
+        if (tid == 0) inv_s[m] = __uint_as_float((uint32_t)(ex - 14) << 23);
+#pragma unroll
+        for (int e = 0; e < VY; ++e) {
+            const int j = tid + e * nthr;
+            if (j < nvec) dst[PLANES ? ((j & 3) * nchunk + (j >> 2)) : j] = bf16x8_to_f16x8_scaled(v[e], mult);
         }
     }
     __syncthreads();
