@@ -74,7 +74,10 @@ struct SdpaParams {
 
 constexpr int kAttnWarps = 8;
 constexpr int kAttnMaxSplits = 128;
-constexpr int kAttnU = 4;     // KV positions per lane group per batch
+constexpr int kAttnU = 4;
+constexpr int kAttnStages = 2; // K/V tiles in flight per CTA
+// KV positions per staged tile: 32 KB (K + V) per stage for 16-bit caches of head_dim 128
+template <int DT, int HD> struct AttnTile { static constexpr int TP = (DT == 0 ? 16 : 32) * 256 / HD >= 16 ? (DT == 0 ? 16 : 32) * 256 / HD : 16; };     // KV positions per lane group per batch
 constexpr float kNegBig = -1e30f;
 
 template <int DT, int HD, int RT>
@@ -128,71 +131,106 @@ sdpa_decode_kernel(SdpaParams p) {
         for (int e = 0; e < EPL; ++e) o[r][e] = 0.f;
     }
 
-    const size_t esz = (DT == 0) ? 4 : 2;
-    const uint8_t* Kb = (const uint8_t*)p.K + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
-    const uint8_t* Vb = (const uint8_t*)p.V + (size_t)kvh * p.max_seq * HD * esz + (size_t)li * 16;
-    // Each lane group (LPR lanes = one KV row) takes U positions per batch; all 2*U 16-byte loads of a
-    // batch are issued before any is used (8 x 16 B in flight per lane, ~8 MB over the grid: enough to
-    // cover the HBM latency-bandwidth product).  One online-softmax rescale per batch, not per position.
-    // The loop bound is warp-uniform, so the full-mask shuffles below are always convergent.
+    constexpr size_t esz = (DT == 0) ? 4 : 2;
+    constexpr int TP = AttnTile<DT, HD>::TP;               // KV positions per staged tile
+    constexpr uint32_t ROWB = HD * esz;                      // bytes of one K (or V) row
+    constexpr uint32_t TILEB = TP * ROWB;                    // bytes of one K (or V) tile
+    // K/V tiles are contiguous in the [n_kv, max_seq, hd] cache, so one cp.async.bulk (TMA, UBLKCP) per
+    // tensor stages a whole tile in shared memory; kAttnStages tiles are in flight per CTA (>= 64 KB per
+    // SM with two resident CTAs), decoupling the HBM latency from the softmax arithmetic.
+    extern __shared__ __align__(128) unsigned char kv_smem[];
+    __shared__ __align__(8) uint64_t full_bar[kAttnStages];
+    const uint8_t* Kg = (const uint8_t*)p.K + (size_t)kvh * p.max_seq * ROWB;
+    const uint8_t* Vg = (const uint8_t*)p.V + (size_t)kvh * p.max_seq * ROWB;
+    const int ntiles = (c1 > c0) ? (c1 - c0 + TP - 1) / TP : 0;
+    auto issue_tile = [&](int t) {                            // one elected thread
+        const int st = t % kAttnStages;
+        const int t0 = c0 + t * TP;
+        const uint32_t bytes = (uint32_t)(min(TP, c1 - t0)) * ROWB;
+        unsigned char* ks = kv_smem + (size_t)st * 2 * TILEB;
+        mbar_arrive_expect_tx(&full_bar[st], 2 * bytes);
+        bulk_copy_g2s(ks, Kg + (size_t)t0 * ROWB, bytes, &full_bar[st]);
+        bulk_copy_g2s(ks + TILEB, Vg + (size_t)t0 * ROWB, bytes, &full_bar[st]);
+    };
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < kAttnStages; ++i) mbar_init(&full_bar[i], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int t = 0; t < min(ntiles, kAttnStages); ++t) issue_tile(t);
+
     constexpr int U = kAttnU;
     constexpr int STEP = kAttnWarps * PPI;          // positions per CTA per u-slot
-    for (int jw = c0 + warp * PPI; jw < c1; jw += U * STEP) {
-        uint4 kq[U], vq[U];
-        bool valid[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int j = jw + slot + u * STEP;
-            valid[u] = j < c1;
-            if (valid[u]) {
-                kq[u] = ldg_kv(Kb + (size_t)j * HD * esz);
-                vq[u] = ldg_kv(Vb + (size_t)j * HD * esz);
-            } else {
-                kq[u] = make_uint4(0, 0, 0, 0); vq[u] = make_uint4(0, 0, 0, 0);
-            }
-        }
-        float sc[U][RT];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            float kf[EPL];
-            KvVec<DT>::unpack(kq[u], kf);
-            const int j = jw + slot + u * STEP;
-#pragma unroll
-            for (int r = 0; r < RT; ++r) {
-                float t = 0.f;
-#pragma unroll
-                for (int e = 0; e < EPL; ++e) t = fmaf(q[r][e], kf[e], t);
-#pragma unroll
-                for (int off = LPR / 2; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
-                sc[u][r] = (valid[u] && j < limit[r]) ? t : kNegBig;
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < RT; ++r) {
-            float mn = m[r];
-#pragma unroll
-            for (int u = 0; u < U; ++u) mn = fmaxf(mn, sc[u][r]);
-            const float corr = exp2f(m[r] - mn);
-            m[r] = mn;
-            l[r] *= corr;
-#pragma unroll
-            for (int e = 0; e < EPL; ++e) o[r][e] *= corr;
+    for (int t = 0; t < ntiles; ++t) {
+        const int st = t % kAttnStages;
+        const int t0 = c0 + t * TP, t1 = min(c1, t0 + TP);
+        mbar_wait(&full_bar[st], (uint32_t)((t / kAttnStages) & 1));
+        const unsigned char* ks = kv_smem + (size_t)st * 2 * TILEB + (size_t)li * 16;
+        const unsigned char* vs = ks + TILEB;
+        // Each lane group (LPR lanes = one KV row) takes U positions per batch; one online-softmax rescale
+        // per batch.  The loop bounds are warp-uniform, so the full-mask shuffles are always convergent.
+        for (int jw = t0 + warp * PPI; jw < t1; jw += U * STEP) {
+            uint4 kq[U], vq[U];
+            bool valid[U];
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                // masked slots carry kNegBig: exp2(kNegBig - mn) == 0 unless mn is kNegBig too
-                const float pj = (sc[u][r] > 0.5f * kNegBig) ? exp2f(sc[u][r] - mn) : 0.f;
-                sc[u][r] = pj;
-                l[r] += pj;
+                const int j = jw + slot + u * STEP;
+                valid[u] = j < t1;
+                if (valid[u]) {
+                    kq[u] = *reinterpret_cast<const uint4*>(ks + (size_t)(j - t0) * ROWB);
+                    vq[u] = *reinterpret_cast<const uint4*>(vs + (size_t)(j - t0) * ROWB);
+                } else {
+                    kq[u] = make_uint4(0, 0, 0, 0); vq[u] = make_uint4(0, 0, 0, 0);
+                }
+            }
+            float sc[U][RT];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float kf[EPL];
+                KvVec<DT>::unpack(kq[u], kf);
+                const int j = jw + slot + u * STEP;
+#pragma unroll
+                for (int r = 0; r < RT; ++r) {
+                    float tt = 0.f;
+#pragma unroll
+                    for (int e = 0; e < EPL; ++e) tt = fmaf(q[r][e], kf[e], tt);
+#pragma unroll
+                    for (int off = LPR / 2; off > 0; off >>= 1) tt += __shfl_xor_sync(0xffffffffu, tt, off);
+                    sc[u][r] = (valid[u] && j < limit[r]) ? tt : kNegBig;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+                float mn = m[r];
+#pragma unroll
+                for (int u = 0; u < U; ++u) mn = fmaxf(mn, sc[u][r]);
+                const float corr = exp2f(m[r] - mn);
+                m[r] = mn;
+                l[r] *= corr;
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) o[r][e] *= corr;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const float pj = (sc[u][r] > 0.5f * kNegBig) ? exp2f(sc[u][r] - mn) : 0.f;
+                    sc[u][r] = pj;
+                    l[r] += pj;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float vf[EPL];
+                KvVec<DT>::unpack(vq[u], vf);
+#pragma unroll
+                for (int r = 0; r < RT; ++r)
+#pragma unroll
+                    for (int e = 0; e < EPL; ++e) o[r][e] = fmaf(sc[u][r], vf[e], o[r][e]);
             }
         }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            float vf[EPL];
-            KvVec<DT>::unpack(vq[u], vf);
-#pragma unroll
-            for (int r = 0; r < RT; ++r)
-#pragma unroll
-                for (int e = 0; e < EPL; ++e) o[r][e] = fmaf(sc[u][r], vf[e], o[r][e]);
+        if (t + kAttnStages < ntiles) {               // refill this stage (CTA-uniform condition)
+            __syncthreads();                          // every warp is done reading it
+            if (threadIdx.x == 0) { fence_proxy_async(); issue_tile(t + kAttnStages); }
         }
     }
     // merge the PPI slots of the warp (lanes li, li+LPR, ...)
@@ -326,7 +364,13 @@ static int launch_sdpa(SdpaParams p, cudaStream_t st) {
     p.splits = splits;
     p.ws = g_attn_ws;
     p.counters = g_attn_cnt;
-    PGK_CUDA(launch(sdpa_decode_kernel<DT, HD, RT>, dim3(splits, row_tiles, p.n_kv), dim3(kAttnWarps * 32), 0, st, p));
+    constexpr size_t kSmem = (size_t)kAttnStages * 2 * AttnTile<DT, HD>::TP * HD * (DT == 0 ? 4 : 2);
+    static bool attr_set = false;
+    if (!attr_set) {
+        PGK_CUDA(cudaFuncSetAttribute(sdpa_decode_kernel<DT, HD, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        attr_set = true;
+    }
+    PGK_CUDA(launch(sdpa_decode_kernel<DT, HD, RT>, dim3(splits, row_tiles, p.n_kv), dim3(kAttnWarps * 32), kSmem, st, p));
     return 0;
 }
 
