@@ -71,6 +71,12 @@ int pgk_graph_destroy(void* graph_exec);
 
 /* programmatic dependent launch on/off for all subsequent launches (default off) */
 int pgk_set_pdl(int enabled);
+/* Cross-kernel HBM pipelining (net-new): name the head of the weights that FOLLOWING launches will stream
+ * (n <= 4 regions of device memory; host arrays of pointers / byte counts).  The next GEMV / attention
+ * launch made by the calling thread prefetches those bytes into L2 (cp.async.bulk.prefetch.L2): the
+ * attention kernel is latency-bound and leaves the DRAM pipe idle, so the o_proj / gate / up weights ride in
+ * behind its K/V tiles and the GEMVs that follow are fed from L2.  One-shot: consumed by that launch. */
+int pgk_prefetch_hint(const void* const* host_regions, const size_t* host_bytes, int n);
 /* number of kernels this library has launched since load (or since reset) */
 int64_t pgk_launch_count(void);
 void pgk_launch_count_reset(void);
@@ -214,6 +220,18 @@ int pgk_sdpa_decode(const void* Q, const void* K, const void* V, void* out, int 
                     int n_kv, int q_len, int head_dim, int max_seq, int context_len,
                     const int32_t* ctx_buf, float scale, long q_stride_h, long q_stride_t,
                     long o_stride_h, long o_stride_t, int dtype, void* stream);
+/* The whole decode attention bracket of ONE new token in one launch (bf16, head_dim 128): per-head
+ * QK-RMSNorm (gamma NULL = off) -> RoPE at *pos_buf (or pos) from f32 tables -> K/V row written into the
+ * un-expanded cache -> split-KV attention over the first *ctx_buf (or context_len) positions, new row
+ * included.  qkv = [(Hq + 2 Hkv) * 128] bf16 (left untouched), out = [Hq * 128] bf16.  Same rounding points
+ * as rmsnorm -> rope_inplace_f32table -> kv_cache_update_gqa -> sdpa_causal_fixed_cache_ptr
+ * (layers/attention.py:326-368).  K/V tiles are requested before griddepcontrol.wait (they do not depend on
+ * the qkv projection), so under PDL the HBM round trip overlaps the previous kernel. */
+int pgk_rope_sdpa_decode(const void* qkv, const void* q_gamma, const void* k_gamma, float eps,
+                         const float* cos_table, const float* sin_table, void* k_cache, void* v_cache,
+                         void* out, int n_heads_q, int n_kv, int head_dim, int max_seq, int pos,
+                         const int32_t* pos_buf, int context_len, const int32_t* ctx_buf, float scale,
+                         void* stream);
 size_t pgk_sdpa_workspace_bytes(int n_heads_q, int q_len, int head_dim, int max_context);
 
 /* ------------------------------------------------------------------ MoE (config 4)

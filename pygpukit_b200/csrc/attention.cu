@@ -98,8 +98,8 @@ sdpa_decode_kernel(SdpaParams p) {
     const int row_tiles = (R + RT - 1) / RT;
     const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z;
 
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int ctx = min(p.ctx_buf ? *p.ctx_buf : p.context_len, p.max_seq);
     int chunk = (ctx + p.splits - 1) / p.splits;
     chunk = (chunk + 31) & ~31;
@@ -374,6 +374,366 @@ static int launch_sdpa(SdpaParams p, cudaStream_t st) {
     return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Fused decode bracket + attention for the q_len == 1, bf16, head_dim 128 case (every config of
+// BASELINE.json): [QK-RMSNorm] -> RoPE -> K/V cache write -> split-KV attention in ONE launch.
+// Replaces the chain rmsnorm(q), rmsnorm(k), rope_inplace_f32table, kv_cache_update_gqa x2,
+// sdpa_causal_fixed_cache_ptr of layers/attention.py:326-368 with the same rounding points (q/k rounded
+// to bf16 after the norm and after the rotation, probabilities and the output accumulator in f32).
+//   * K/V tiles of the OLD positions do not depend on the previous kernel (the qkv GEMV), so one thread
+//     reads the device-side context length and issues every cp.async.bulk of the CTA's chunk (up to
+//     kFStages x 32 KB) BEFORE griddepcontrol.wait: the HBM round trip overlaps the GEMV's tail.
+//   * after the wait, warps 0..RT-1 normalise + rotate the RT query heads of the tile into shared memory,
+//     warps RT / RT+1 prepare the new K / V row; the CTA whose chunk holds the new position patches the row
+//     into its staged tile (and the rt == 0 CTA writes it to the cache) -- no kernel boundary between the
+//     cache write and the attention that reads it.
+//   * scores use FHFMA.BF16 on the packed K words (exact products, f32 accumulate; q is exactly bf16
+//     after the rotation), so K is never unpacked; one 64-position batch per tile, one rescale per batch.
+struct RopeSdpaParams {
+    const uint16_t* qkv;                       // [(hq + 2 n_kv) * 128] raw projections of the new token
+    const uint16_t* q_gamma; const uint16_t* k_gamma; float eps;
+    const float* cos_t; const float* sin_t;    // [positions, 128] f32
+    uint16_t* kc; uint16_t* vc;                // [n_kv, max_seq, 128]
+    uint16_t* out;                             // [hq * 128]
+    int hq, n_kv, max_seq, pos, context_len;
+    const int32_t* pos_buf; const int32_t* ctx_buf;
+    float scale_log2;
+    int splits;
+    float* ws; unsigned* counters;
+    PrefetchHint next;                         // head of the o_proj weights
+};
+constexpr int kFTile = 64;       // KV positions per staged tile (16 KB K + 16 KB V)
+constexpr int kFStages = 2;
+constexpr int kFRT = 4;          // query heads per CTA
+
+// one warp: [RMSNorm] + NeoX rotation of one 128-wide head row, result as bf16 bits (d = lane, lane+32 | +64).
+// cos/sin (c, s) and gamma (g, as f32) were loaded by the caller BEFORE the dependency wait.
+__device__ __forceinline__ void norm_rope_head128(const uint16_t* __restrict__ row, bool use_gamma, const float (&g)[4],
+                                                  float eps, const float (&c)[2], const float (&s)[2],
+                                                  int lane, uint16_t* __restrict__ dst_s, uint16_t* __restrict__ dst_g) {
+    float x[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[i] = bf16_bits_to_f32(row[lane + 32 * i]);
+    if (use_gamma) {
+        // summation tree of the reference's 128-thread rmsnorm block (norm_kernels.cuh:535-585): one element
+        // per virtual thread, a shuffle tree per 32 elements, then a tree over the four totals
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            float part = warp_sum(fmaf(x[w], x[w], 0.f));
+            if (lane == w) tot = part;
+        }
+        const float inv = rsqrtf(warp_sum(tot) / 128.f + eps);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = round_bf16(x[i] * inv * g[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const float x0 = x[i], x1 = x[i + 2];
+        const uint16_t y0 = f32_to_bf16_bits(x0 * c[i] - x1 * s[i]), y1 = f32_to_bf16_bits(x1 * c[i] + x0 * s[i]);
+        dst_s[lane + 32 * i] = y0; dst_s[lane + 32 * i + 64] = y1;
+        if (dst_g) { dst_g[lane + 32 * i] = y0; dst_g[lane + 32 * i + 64] = y1; }
+    }
+}
+
+__global__ void __launch_bounds__(kAttnWarps * 32, 2)
+rope_sdpa_decode_kernel(RopeSdpaParams p) {
+    constexpr int HD = 128, RT = kFRT, REC = HD + 2, LPR = 16, U = 4;
+    constexpr uint32_t ROWB = HD * 2, TILEB = kFTile * ROWB;
+    extern __shared__ __align__(128) unsigned char kv_smem[];
+    __shared__ float sm_part[kAttnWarps][RT][REC];
+    __shared__ __align__(16) uint16_t q_s[RT][HD];
+    __shared__ __align__(16) uint16_t new_s[2][HD];           // new K row, new V row
+    __shared__ __align__(8) uint64_t full_bar[kFStages];
+    __shared__ unsigned s_ticket;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int li = lane & 15, slot = lane >> 4;
+    const int G = p.hq / p.n_kv;
+    const int row_tiles = (G + RT - 1) / RT;
+    const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z;
+
+    // ---- independent of the previous kernel: position, barriers, the first K/V tiles
+    const int pos = p.pos_buf ? *p.pos_buf : p.pos;
+    const int ctx = min(p.ctx_buf ? *p.ctx_buf : p.context_len, p.max_seq);
+    int chunk = (ctx + p.splits - 1) / p.splits;
+    chunk = (chunk + kFTile - 1) & ~(kFTile - 1);
+    const int c0 = split * chunk, c1 = min(ctx, c0 + chunk);
+    const int ntiles = (c1 > c0) ? (c1 - c0 + kFTile - 1) / kFTile : 0;
+    const bool has_new = pos >= c0 && pos < c1;
+    // the cache write: the row-tile-0 CTA of the owning chunk (or split 0 when the caller's context excludes pos)
+    const bool writer = rt == 0 && pos < p.max_seq && (has_new || (pos >= ctx && split == 0));
+    const uint8_t* Kg = (const uint8_t*)p.kc + (size_t)kvh * p.max_seq * ROWB;
+    const uint8_t* Vg = (const uint8_t*)p.vc + (size_t)kvh * p.max_seq * ROWB;
+    auto issue_tile = [&](int t) {
+        const int st = t % kFStages;
+        const int t0 = c0 + t * kFTile;
+        const uint32_t bytes = (uint32_t)(min(kFTile, c1 - t0)) * ROWB;
+        unsigned char* ks = kv_smem + (size_t)st * 2 * TILEB;
+        mbar_arrive_expect_tx(&full_bar[st], 2 * bytes);
+        bulk_copy_g2s(ks, Kg + (size_t)t0 * ROWB, bytes, &full_bar[st]);
+        bulk_copy_g2s(ks + TILEB, Vg + (size_t)t0 * ROWB, bytes, &full_bar[st]);
+    };
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < kFStages; ++i) mbar_init(&full_bar[i], 1);
+        mbar_fence_init();
+        for (int t = 0; t < min(ntiles, kFStages); ++t) issue_tile(t);
+    }
+    {   // this kernel is latency-bound (16 MB of K/V, a dependent chain of round trips): let the DRAM pipe
+        // carry the weights of the GEMVs that follow into L2 meanwhile (weights never depend on earlier kernels)
+        const long cta = ((long)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        l2_prefetch_share(p.next, cta * blockDim.x + threadIdx.x, (long)gridDim.x * gridDim.y * gridDim.z * blockDim.x);
+    }
+    // rotation tables and norm weights of this warp's head: constants, requested before the wait as well
+    float rc[2] = {1.f, 1.f}, rs[2] = {0.f, 0.f}, rg[4] = {1.f, 1.f, 1.f, 1.f};
+    const uint16_t* my_gamma = (warp < RT) ? p.q_gamma : (warp == RT ? p.k_gamma : nullptr);
+    if (warp <= RT) {
+        const float* cs = p.cos_t + (size_t)pos * HD;
+        const float* sn = p.sin_t + (size_t)pos * HD;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) { rc[i] = __ldg(cs + lane + 32 * i); rs[i] = __ldg(sn + lane + 32 * i); }
+        if (my_gamma) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) rg[i] = bf16_bits_to_f32(__ldg(my_gamma + lane + 32 * i));
+        }
+    }
+    griddep_wait();
+    griddep_launch();
+
+    // ---- the new token's q heads of this tile, and (if this chunk owns the new position) its K / V rows
+    if (warp < RT) {
+        const int g = rt * RT + warp;
+        if (g < G) norm_rope_head128(p.qkv + (size_t)(kvh * G + g) * HD, my_gamma != nullptr, rg, p.eps, rc, rs, lane, q_s[warp], nullptr);
+        else for (int d = lane; d < HD; d += 32) q_s[warp][d] = 0;
+    } else if ((has_new || writer) && warp == RT) {
+        uint16_t* dst = writer ? p.kc + ((size_t)kvh * p.max_seq + pos) * HD : nullptr;
+        norm_rope_head128(p.qkv + (size_t)(p.hq + kvh) * HD, my_gamma != nullptr, rg, p.eps, rc, rs, lane, new_s[0], dst);
+    } else if ((has_new || writer) && warp == RT + 1) {
+        const uint16_t* src = p.qkv + (size_t)(p.hq + p.n_kv + kvh) * HD;
+        uint16_t* dst = writer ? p.vc + ((size_t)kvh * p.max_seq + pos) * HD : nullptr;
+        for (int d = lane; d < HD; d += 32) { uint16_t v = src[d]; new_s[1][d] = v; if (dst) dst[d] = v; }
+    }
+    __syncthreads();   // q_s / new_s visible; also orders the mbarrier init before every wait
+    uint32_t q[RT][4];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        const uint4 v = *reinterpret_cast<const uint4*>(&q_s[r][li * 8]);
+        q[r][0] = v.x; q[r][1] = v.y; q[r][2] = v.z; q[r][3] = v.w;
+    }
+    float m[RT], l[RT], o[RT][8];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        m[r] = kNegBig; l[r] = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[r][e] = 0.f;
+    }
+
+    for (int t = 0; t < ntiles; ++t) {
+        const int st = t % kFStages;
+        const int t0 = c0 + t * kFTile, t1 = min(c1, t0 + kFTile);
+        mbar_wait(&full_bar[st], (uint32_t)((t / kFStages) & 1));
+        unsigned char* tile = kv_smem + (size_t)st * 2 * TILEB;
+        if (has_new && pos >= t0 && pos < t1) {               // CTA-uniform: patch the new row into the staged tile
+            if (threadIdx.x < 32) {
+                const int which = threadIdx.x >> 4, v = threadIdx.x & 15;
+                reinterpret_cast<uint4*>(tile + (size_t)which * TILEB + (size_t)(pos - t0) * ROWB)[v] =
+                    reinterpret_cast<const uint4*>(new_s[which])[v];
+            }
+            __syncthreads();
+        }
+        const unsigned char* ks = tile + (size_t)li * 16;
+        const unsigned char* vs = ks + TILEB;
+        uint4 kq[U], vq[U];
+        bool valid[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int j = t0 + warp * 2 + slot + u * (kAttnWarps * 2);
+            valid[u] = j < t1;
+            if (valid[u]) {
+                kq[u] = *reinterpret_cast<const uint4*>(ks + (size_t)(j - t0) * ROWB);
+                vq[u] = *reinterpret_cast<const uint4*>(vs + (size_t)(j - t0) * ROWB);
+            } else {
+                kq[u] = make_uint4(0, 0, 0, 0); vq[u] = make_uint4(0, 0, 0, 0);
+            }
+        }
+        float sc[U][RT];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+                float a0 = 0.f, a1 = 0.f;
+                fhfma_bf16_lo(a0, q[r][0], kq[u].x); fhfma_bf16_hi(a1, q[r][0], kq[u].x);
+                fhfma_bf16_lo(a0, q[r][1], kq[u].y); fhfma_bf16_hi(a1, q[r][1], kq[u].y);
+                fhfma_bf16_lo(a0, q[r][2], kq[u].z); fhfma_bf16_hi(a1, q[r][2], kq[u].z);
+                fhfma_bf16_lo(a0, q[r][3], kq[u].w); fhfma_bf16_hi(a1, q[r][3], kq[u].w);
+                float tt = a0 + a1;
+#pragma unroll
+                for (int off = LPR / 2; off > 0; off >>= 1) tt += __shfl_xor_sync(0xffffffffu, tt, off);
+                sc[u][r] = valid[u] ? tt * p.scale_log2 : kNegBig;
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            float mn = m[r];
+#pragma unroll
+            for (int u = 0; u < U; ++u) mn = fmaxf(mn, sc[u][r]);
+            const float corr = exp2f(m[r] - mn);
+            m[r] = mn;
+            l[r] *= corr;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[r][e] *= corr;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const float pj = (sc[u][r] > 0.5f * kNegBig) ? exp2f(sc[u][r] - mn) : 0.f;
+                sc[u][r] = pj;
+                l[r] += pj;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float vf[8];
+            KvVec<2>::unpack(vq[u], vf);
+#pragma unroll
+            for (int r = 0; r < RT; ++r)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[r][e] = fmaf(sc[u][r], vf[e], o[r][e]);
+        }
+        if (t + kFStages < ntiles) {                  // refill this stage (CTA-uniform condition)
+            __syncthreads();
+            if (threadIdx.x == 0) { fence_proxy_async(); issue_tile(t + kFStages); }
+        }
+    }
+    // merge the two position slots of the warp
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        const float m2 = __shfl_xor_sync(0xffffffffu, m[r], 16);
+        const float l2 = __shfl_xor_sync(0xffffffffu, l[r], 16);
+        const float mn = fmaxf(m[r], m2);
+        const float c1s = exp2f(m[r] - mn), c2s = exp2f(m2 - mn);
+        l[r] = l[r] * c1s + l2 * c2s;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const float o2 = __shfl_xor_sync(0xffffffffu, o[r][e], 16);
+            o[r][e] = o[r][e] * c1s + o2 * c2s;
+        }
+        m[r] = mn;
+        if (slot == 0) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) sm_part[warp][r][li * 8 + e] = o[r][e];
+            if (li == 0) { sm_part[warp][r][HD] = m[r]; sm_part[warp][r][HD + 1] = l[r]; }
+        }
+    }
+    __syncthreads();
+    const size_t tile_id = (size_t)kvh * row_tiles + rt;
+    float* rec = p.ws + (tile_id * p.splits + split) * RT * REC;
+    for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
+        const int r = idx / HD, d = idx % HD;
+        float mn = kNegBig;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) mn = fmaxf(mn, sm_part[w][r][HD]);
+        float ov = 0.f, lv = 0.f;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) {
+            const float c = exp2f(sm_part[w][r][HD] - mn);
+            ov = fmaf(sm_part[w][r][d], c, ov);
+            lv = fmaf(sm_part[w][r][HD + 1], c, lv);
+        }
+        if (p.splits == 1) {
+            const int g = rt * RT + r;
+            if (g < G) p.out[(size_t)(kvh * G + g) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
+        } else {
+            __stcg(rec + r * REC + d, ov);
+            if (d == 0) { __stcg(rec + r * REC + HD, mn); __stcg(rec + r * REC + HD + 1, lv); }
+        }
+    }
+    if (p.splits == 1) return;
+    // release: the CTA barrier orders every thread's partial stores before thread 0's gpu-scope fence (fences
+    // are cumulative), which orders them before the ticket; acquire on the other side is symmetric
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_ticket = atomicAdd(p.counters + tile_id, 1u);
+        __threadfence();
+    }
+    __syncthreads();
+    if (s_ticket != (unsigned)(p.splits - 1)) return;
+    // last CTA of the (kv head, row tile): fold the partials in split order (deterministic)
+    const float* base = p.ws + tile_id * p.splits * RT * REC;
+    float* s_m = &sm_part[0][0][0];                          // [RT][kAttnMaxSplits] (sm_part is free again)
+    float* s_l = s_m + RT * kAttnMaxSplits;
+    for (int idx = threadIdx.x; idx < RT * p.splits; idx += blockDim.x) {
+        const int r = idx / p.splits, sp = idx % p.splits;
+        const float* rr = base + ((size_t)sp * RT + r) * REC;
+        s_m[r * kAttnMaxSplits + sp] = __ldcg(rr + HD);
+        s_l[r * kAttnMaxSplits + sp] = __ldcg(rr + HD + 1);
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
+        const int r = idx / HD, d = idx % HD;
+        const int g = rt * RT + r;
+        if (g >= G) continue;
+        const float* sm_r = s_m + r * kAttnMaxSplits;
+        const float* sl_r = s_l + r * kAttnMaxSplits;
+        float mn = kNegBig;
+        for (int sp = 0; sp < p.splits; ++sp) mn = fmaxf(mn, sm_r[sp]);
+        float ov = 0.f, lv = 0.f;
+        int sp = 0;
+        for (; sp + 16 <= p.splits; sp += 16) {
+            float v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = __ldcg(base + ((size_t)(sp + u) * RT + r) * REC + d);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+                const float c = exp2f(sm_r[sp + u] - mn);
+                ov = fmaf(v[u], c, ov);
+                lv = fmaf(sl_r[sp + u], c, lv);
+            }
+        }
+        for (; sp < p.splits; ++sp) {
+            const float c = exp2f(sm_r[sp] - mn);
+            ov = fmaf(__ldcg(base + ((size_t)sp * RT + r) * REC + d), c, ov);
+            lv = fmaf(sl_r[sp], c, lv);
+        }
+        p.out[(size_t)(kvh * G + g) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
+    }
+    if (threadIdx.x == 0) p.counters[tile_id] = 0;
+}
+
+static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
+    const int G = p.hq / p.n_kv;
+    const int row_tiles = (G + kFRT - 1) / kFRT;
+    const int base_ctas = p.n_kv * row_tiles;
+    int splits = (2 * sm_count() + base_ctas - 1) / base_ctas;
+    const int hint = p.ctx_buf ? p.max_seq : p.context_len;
+    const int max_splits = (hint + 2 * kFTile - 1) / (2 * kFTile);
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    if (splits > kAttnMaxSplits) splits = kAttnMaxSplits;
+    if (!g_attn_ws) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing(st, &cs);
+        PGK_REQUIRE(cs == cudaStreamCaptureStatusNone,
+                    "rope_sdpa_decode failed: first call must happen outside graph capture (workspace allocation)");
+        PGK_CUDA(cudaMalloc(&g_attn_ws, kAttnWsBytes));
+        PGK_CUDA(cudaMalloc(&g_attn_cnt, kAttnMaxTiles * sizeof(unsigned)));
+        PGK_CUDA(cudaMemset(g_attn_cnt, 0, kAttnMaxTiles * sizeof(unsigned)));
+    }
+    PGK_REQUIRE(base_ctas <= kAttnMaxTiles, "rope_sdpa_decode failed: too many heads (%d)", p.hq);
+    p.splits = splits;
+    p.ws = g_attn_ws;
+    p.counters = g_attn_cnt;
+    constexpr size_t kSmem = (size_t)kFStages * 2 * kFTile * 128 * 2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PGK_CUDA(cudaFuncSetAttribute(rope_sdpa_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        attr_set = true;
+    }
+    PGK_CUDA(launch(rope_sdpa_decode_kernel, dim3(splits, row_tiles, p.n_kv), dim3(kAttnWarps * 32), kSmem, st, p));
+    return 0;
+}
+
 }  // namespace pgk
 
 using namespace pgk;
@@ -402,6 +762,28 @@ int pgk_sdpa_decode(const void* Q, const void* K, const void* V, void* out, int 
 #undef PGK_SDPA
     set_error("sdpa_causal_fixed_cache failed: unsupported dtype %d / head_dim %d", dtype, head_dim);
     return 1;
+}
+
+int pgk_rope_sdpa_decode(const void* qkv, const void* q_gamma, const void* k_gamma, float eps, const float* cos_table,
+                         const float* sin_table, void* k_cache, void* v_cache, void* out, int n_heads_q, int n_kv,
+                         int head_dim, int max_seq, int pos, const int32_t* pos_buf, int context_len,
+                         const int32_t* ctx_buf, float scale, void* stream) {
+    PGK_REQUIRE(head_dim == 128, "rope_sdpa_decode failed: head_dim %d (the fused bracket is built for 128)", head_dim);
+    PGK_REQUIRE(n_kv > 0 && n_heads_q % n_kv == 0, "rope_sdpa_decode failed: n_heads %d not a multiple of n_kv_heads %d", n_heads_q, n_kv);
+    PGK_REQUIRE(ctx_buf || (context_len >= 1 && context_len <= max_seq),
+                "rope_sdpa_decode failed: context_len %d out of range (max_seq_len %d)", context_len, max_seq);
+    PGK_REQUIRE(pos_buf || (pos >= 0 && pos < max_seq), "rope_sdpa_decode failed: position %d out of range", pos);
+    PGK_REQUIRE(((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) && ((uintptr_t)qkv % 16 == 0),
+                "rope_sdpa_decode failed: qkv / K / V must be 16-byte aligned");
+    if (scale <= 0.f) scale = 1.0f / sqrtf((float)head_dim);
+    RopeSdpaParams p = {};
+    p.qkv = (const uint16_t*)qkv; p.q_gamma = (const uint16_t*)q_gamma; p.k_gamma = (const uint16_t*)k_gamma; p.eps = eps;
+    p.cos_t = cos_table; p.sin_t = sin_table; p.kc = (uint16_t*)k_cache; p.vc = (uint16_t*)v_cache; p.out = (uint16_t*)out;
+    p.hq = n_heads_q; p.n_kv = n_kv; p.max_seq = max_seq; p.pos = pos; p.context_len = context_len;
+    p.pos_buf = pos_buf; p.ctx_buf = ctx_buf;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    p.next = take_prefetch_hint();
+    return launch_rope_sdpa(p, (cudaStream_t)stream);
 }
 
 size_t pgk_sdpa_workspace_bytes(int, int, int, int) { return kAttnWsBytes; }

@@ -16,6 +16,17 @@ void count_launch(int n = 1);
 bool pdl_enabled();
 int  sm_count();
 
+// "What streams next": the head of the weights that FOLLOWING kernels will stream (up to four regions),
+// prefetched into L2 by a kernel that leaves the DRAM pipe idle (the latency-bound attention kernel, or a
+// GEMV whose own weights already sit in L2), so HBM keeps streaming across kernel boundaries.  Set by
+// pgk_prefetch_hint(), consumed (and cleared) by the next GEMV / attention launch of the calling thread.
+constexpr unsigned kPrefetchPiece = 4096;
+struct PrefetchHint {
+    const unsigned char* p[4] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned pieces[4] = {0, 0, 0, 0};     // kPrefetchPiece-byte pieces per region
+};
+PrefetchHint take_prefetch_hint();
+
 
 #define PGK_CUDA(call)                                                        \
     do {                                                                      \
@@ -61,8 +72,21 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 // ---------------------------------------------------------------- device helpers
 #ifdef __CUDACC__
 
+// PDL discipline of this library: every kernel executes griddepcontrol.wait BEFORE launch_dependents.  A
+// dependent grid can therefore only start once its predecessor has passed its own wait, i.e. once every
+// kernel before the predecessor has completed and flushed: code placed before griddep_wait() may read
+// anything that was last written two or more kernels back (weights, the device-side position counters,
+// KV-cache rows of earlier steps), never the predecessor's outputs.
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// fire-and-forget L2 prefetch of this thread's share of the hinted regions (cp.async.bulk.prefetch.L2)
+__device__ __forceinline__ void l2_prefetch_share(const PrefetchHint& h, long gthread, long nthreads) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        for (long i = gthread; i < (long)h.pieces[r]; i += nthreads)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(h.p[r] + i * kPrefetchPiece), "n"(kPrefetchPiece) : "memory");
+}
 
 __device__ __forceinline__ float bf16_bits_to_f32(uint32_t h) { return __uint_as_float(h << 16); }
 __device__ __forceinline__ float bf16lo(uint32_t p) { return __uint_as_float(p << 16); }

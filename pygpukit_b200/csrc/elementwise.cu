@@ -50,8 +50,8 @@ template <int DT, bool RESIDUAL>
 __global__ void rmsnorm_kernel(const void* __restrict__ x, const void* __restrict__ res,
                                const void* __restrict__ gamma, void* __restrict__ y, int features, float eps) {
     __shared__ float red[32];
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const size_t base = (size_t)blockIdx.x * features;
     // thread t owns elements t, t + bs, ... (the reference's partial sums); up to 32 of them are loaded
     // up front (all loads in flight at once) and kept in registers for the second pass
@@ -102,8 +102,8 @@ template <int DT>
 __global__ void layernorm_kernel(const void* __restrict__ x, const void* __restrict__ gamma,
                                  const void* __restrict__ beta, void* __restrict__ y, int features, float eps) {
     __shared__ float red[32];
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const size_t base = (size_t)blockIdx.x * features;
     float s = 0.f;
     for (int i = threadIdx.x; i < features; i += blockDim.x) s += Elem<DT>::ld(x, base + i);
@@ -128,8 +128,8 @@ __global__ void layernorm_kernel(const void* __restrict__ x, const void* __restr
 template <int DT, int TDT>
 __global__ void rope_kernel(void* __restrict__ q, void* __restrict__ k, const void* __restrict__ cs,
                             const void* __restrict__ sn, int seq, int hq, int hk, int hd) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int half = hd >> 1;
     const long nq = (long)seq * hq * half, nk = (long)seq * hk * half;
     long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -158,8 +158,8 @@ __device__ __forceinline__ float gelu_f(float x) {                              
 
 template <int DT, int OP>
 __global__ void unary_kernel(const void* __restrict__ x, void* __restrict__ y, size_t n) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float v = Elem<DT>::ld(x, i);
@@ -170,8 +170,8 @@ __global__ void unary_kernel(const void* __restrict__ x, void* __restrict__ y, s
 // mul: exact f32 product then rounding; swiglu: silu_f32(g)*u one rounding (fused_kernels.cuh:233-247)
 template <int DT, int OP>
 __global__ void binary_kernel(const void* __restrict__ a, const void* __restrict__ b, void* __restrict__ c, size_t n) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float x = Elem<DT>::ld(a, i), y = Elem<DT>::ld(b, i);
@@ -182,8 +182,8 @@ __global__ void binary_kernel(const void* __restrict__ a, const void* __restrict
 // elementwise_kernels.cuh:370-470
 template <int DT, int OP>
 __global__ void binary_inplace_kernel(void* __restrict__ a, const void* __restrict__ b, size_t n) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     using T = typename Elem<DT>::T;
@@ -196,8 +196,8 @@ __global__ void binary_inplace_kernel(void* __restrict__ a, const void* __restri
 // bias_add_*_kernel elementwise_kernels.cuh:22-75: f32 add, one rounding
 template <int DT>
 __global__ void bias_add_kernel(void* __restrict__ x, const void* __restrict__ bias, size_t n, int features) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     Elem<DT>::st(x, i, Elem<DT>::ld(x, i) + Elem<DT>::ld(bias, i % features));
@@ -205,8 +205,8 @@ __global__ void bias_add_kernel(void* __restrict__ x, const void* __restrict__ b
 
 template <int SDT, int DDT>
 __global__ void cast_kernel(const void* __restrict__ s, void* __restrict__ d, size_t n) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) Elem<DDT>::st(d, i, Elem<SDT>::ld(s, i));
 }
@@ -215,8 +215,8 @@ __global__ void cast_kernel(const void* __restrict__ s, void* __restrict__ d, si
 // embedding_lookup(_ptr,_batch) embedding_kernels.cuh:27-165: row copy; token id from host or device
 __global__ void embedding_kernel(const uint8_t* __restrict__ table, uint8_t* __restrict__ out, size_t row_bytes,
                                  int token, const int32_t* __restrict__ token_buf, int n_tokens) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const size_t vec = row_bytes >> 4;
     for (int t = blockIdx.y; t < n_tokens; t += gridDim.y) {
         long tok = token_buf ? (long)token_buf[t] : (long)token;
@@ -235,8 +235,8 @@ template <int DT>
 __global__ void argmax_kernel(const void* __restrict__ x, int32_t* __restrict__ out, int n) {
     __shared__ float sv[32];
     __shared__ int si[32];
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     float bv = -INFINITY;
     int bi = 0x7fffffff;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -261,8 +261,8 @@ __global__ void argmax_kernel(const void* __restrict__ x, int32_t* __restrict__ 
 // transpose_3d_021: [d0,d1,d2] -> [d1,d0,d2]
 template <typename T>
 __global__ void transpose021_kernel(const T* __restrict__ in, T* __restrict__ out, int d0, int d1, int d2) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     size_t n = (size_t)d0 * d1 * d2;
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -277,8 +277,8 @@ __global__ void transpose021_kernel(const T* __restrict__ in, T* __restrict__ ou
 __global__ void kv_update_kernel(const uint8_t* __restrict__ new_kv, uint8_t* __restrict__ cache, int seq, int n_kv,
                                  int heads_out, size_t row_bytes, int max_seq, int pos,
                                  const int32_t* __restrict__ pos_buf) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int p0 = pos_buf ? *pos_buf : pos;
     const int G = heads_out / n_kv;
     const size_t vec = row_bytes >> 4;                       // head_dim * elem is a multiple of 16 in practice
@@ -296,8 +296,8 @@ __global__ void kv_update_kernel(const uint8_t* __restrict__ new_kv, uint8_t* __
 __global__ void kv_update_bytes_kernel(const uint8_t* __restrict__ new_kv, uint8_t* __restrict__ cache, int seq,
                                        int n_kv, int heads_out, size_t row_bytes, int max_seq, int pos,
                                        const int32_t* __restrict__ pos_buf) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int p0 = pos_buf ? *pos_buf : pos;
     const int G = heads_out / n_kv;
     const size_t total = (size_t)seq * heads_out * row_bytes;
@@ -319,8 +319,8 @@ __global__ void qk_norm_rope_kv_kernel(uint16_t* __restrict__ qkv, const uint16_
                                        const float* __restrict__ sn, uint16_t* __restrict__ kc,
                                        uint16_t* __restrict__ vc, int M, int hq, int hkv, int hd, int max_seq,
                                        int pos, const int32_t* __restrict__ pos_buf) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int lane = threadIdx.x & 31;
     const int gw = (int)(((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const int H = hq + 2 * hkv;

@@ -20,8 +20,8 @@ __global__ void __launch_bounds__(kGW * 32)
 w8a16_gemm_kn_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B, const uint16_t* __restrict__ S,
                      uint16_t* __restrict__ C, int M, int K, int N) {
     __shared__ float red[kGW][MT][128];
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n0 = blockIdx.x * 128 + lane * 4;
     const int m0 = blockIdx.y * MT;

@@ -70,9 +70,11 @@ gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint16_t* a_s = reinterpret_cast<uint16_t*>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+    // rows dealt round-robin over the warps of the grid (see gemv_fp8.cu)
     const long gwarp = (long)blockIdx.x * wpc + warp;
-    const int row_begin = (int)min((long)N, gwarp * rho);
-    const int row_end = (int)min((long)N, gwarp * rho + rho);
+    const long nwarps = (long)gridDim.x * wpc;
+    const int row_begin = (int)min((long)N, gwarp);
+    (void)rho;
     const int nchunk = K >> 4;
 
     u32x8 w[U];
@@ -83,16 +85,18 @@ gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
             if (c < nchunk) w[u] = ldg_stream256(B + (size_t)n * K + (size_t)c * 16);
         }
     };
-    if (row_begin < row_end) load_group(row_begin, 0);
-    griddep_launch();
+    if (row_begin < N) load_group(row_begin, 0);
+    l2_prefetch_share(epi.next, gwarp * 32 + lane, nwarps * 32);
     griddep_wait();
+    griddep_launch();
     stage_activations_bf16<M>(A, K, a_s, epi.norm_gamma, epi.norm_eps);
 
     const uint4* ap0 = reinterpret_cast<const uint4*>(a_s);
     bool preloaded = true;
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
-    for (int n = row_begin; n < row_end; ++n) {
+    for (long nl = row_begin; nl < N; nl += nwarps) {
+        const int n = (int)nl;
         float acc[M];
 #pragma unroll
         for (int m = 0; m < M; ++m) acc[m] = 0.f;
@@ -150,8 +154,8 @@ gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
 template <bool ARGMAX>
 __global__ void gemv_bf16_generic_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
                                          uint16_t* __restrict__ C, int M, int K, int N, GemvEpilogue epi) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int lane = threadIdx.x & 31;
     const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (gw >= (long)N * M) return;
@@ -223,6 +227,7 @@ static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, in
     const bool fast = (K % 16 == 0) && al(A, 16) && al(B, 32) && ((size_t)K * 2 <= 200 * 1024);
     PGK_REQUIRE(!gamma || (fast && K >= 512 && al(gamma, 16)),
                 "rmsnorm_gemv_bf16 failed: the fused norm needs K %% 16 == 0, K >= 512 and aligned pointers (K=%d)", K);
+    const PrefetchHint hint = take_prefetch_hint();   // one-shot, whichever path runs
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
         long warps = (long)N * M;
@@ -237,6 +242,7 @@ static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, in
         if (mt == 3) mt = 2;
         GemvEpilogue epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
                             (const uint16_t*)gamma, eps};
+        if (m0 + mt >= M) epi.next = hint;
         int rc;
         if (mt == 1)      rc = launch_bf16<1, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
         else if (mt == 2) rc = launch_bf16<2, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
@@ -265,6 +271,7 @@ int pgk_gemv_bf16_argmax(const void* A, const void* B_nk, void* logits, int32_t*
     PGK_REQUIRE(K % 16 == 0 && al(A, 16) && al(B_nk, 32) && (size_t)K * 2 <= 200 * 1024,
                 "gemv_bf16_argmax failed: needs K%%16==0 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr};
+    epi.next = take_prefetch_hint();
     return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
 }
@@ -279,6 +286,7 @@ int pgk_rmsnorm_gemv_bf16_argmax(const void* A, const void* gamma, float eps, co
     PGK_REQUIRE(K % 16 == 0 && K >= 512 && al(A, 16) && al(B_nk, 32) && al(gamma, 16) && (size_t)K * 2 <= 200 * 1024,
                 "rmsnorm_gemv_bf16_argmax failed: needs K%%16==0, K>=512 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr, (const uint16_t*)gamma, eps};
+    epi.next = take_prefetch_hint();
     return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
 }

@@ -40,6 +40,7 @@ struct GemvEpilogue {
     const uint16_t* residual;  // [M,N] bf16 or null
     const uint16_t* norm_gamma = nullptr;  // [K] bf16: A <- bf16(rmsnorm(A) * gamma) while staging, or null
     float norm_eps = 0.f;
+    PrefetchHint next;                     // head of the next kernel's weights (L2 prefetch as warps drain)
 };
 
 // ---- fused RMSNorm prologue -------------------------------------------------------------------

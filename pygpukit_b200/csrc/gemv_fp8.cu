@@ -24,6 +24,7 @@
 #include "gemv_common.cuh"
 #include "../../include/pgk_b200.h"
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -48,9 +49,133 @@ __device__ __forceinline__ float dot32_e4m3(const u32x8& w, const uint4* ap, int
 }
 
 // NMAT = 1: plain GEMV; NMAT = 2: gate/up pair with SiLU*up epilogue.
+//
+// Work = the sequence of "groups" (row n, chunk block cb) of this warp: rows n = gwarp, gwarp + nwarps, ...
+// (round-robin over the warps of the grid: at any moment the grid streams one contiguous band of the matrix),
+// inside a row blocks of 32*U chunks of 32 weights.  Two groups are in flight per warp (register double
+// buffer, 2 x U x 256-bit loads per lane = 8 KB per warp, ~96 KB per SM), and BOTH are requested before
+// griddepcontrol.wait -- weights never depend on the previous kernel -- so under PDL the first ~14 MB of
+// the matrix are already on their way while the predecessor drains and the activations are staged.
+template <int M, int NMAT, int UT, int MAXW>
+__global__ void __launch_bounds__(MAXW * 32)
+gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
+                const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
+                const uint16_t* __restrict__ S1, uint16_t* __restrict__ C, int K, int N, int rho,
+                GemvEpilogue epi) {
+    constexpr int U = UT / NMAT;   // 256-bit loads per lane per matrix per group
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __half* a_s = reinterpret_cast<__half*>(smem_raw);
+    float* inv_s = reinterpret_cast<float*>(smem_raw + (size_t)M * K * 2);
+    uint32_t* red = reinterpret_cast<uint32_t*>(inv_s + 8);
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpc = blockDim.x >> 5;
+    const long gwarp = (long)blockIdx.x * wpc + warp;
+    const long nwarps = (long)gridDim.x * wpc;
+    const int nchunk = K >> 5;
+    const int SK = (K + 127) >> 7;
+    (void)rho;
+
+    struct Buf { u32x8 w[NMAT][U]; };
+    Buf bufA, bufB;
+    auto load_group = [&](Buf& b, long n, int cb) {
+        if (n >= N) return;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            int c = cb + lane + 32 * u;
+            if (c < nchunk) {
+                b.w[0][u] = ldg_stream256(B0 + (size_t)n * K + (size_t)c * 32);
+                if (NMAT == 2) b.w[NMAT - 1][u] = ldg_stream256(B1 + (size_t)n * K + (size_t)c * 32);
+            }
+        }
+    };
+    auto advance = [&](long& n, int& cb) {
+        cb += 32 * U;
+        if (cb >= nchunk) { cb = 0; n += nwarps; }
+    };
+    long nA = gwarp; int cbA = 0;
+    long nB = nA; int cbB = cbA;
+    advance(nB, cbB);
+    load_group(bufA, nA, cbA);
+    load_group(bufB, nB, cbB);
+    l2_prefetch_share(epi.next, gwarp * 32 + lane, nwarps * 32);   // only hinted when this launch is L2-fed itself
+    griddep_wait();
+    griddep_launch();
+    stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
+
+    const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
+    float acc[NMAT][M];
+#pragma unroll
+    for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+        for (int m = 0; m < M; ++m) acc[t][m] = 0.f;
+
+    auto compute_group = [&](const Buf& b, int n, int cb) {
+        const uint16_t* s0 = S0 + (size_t)(n >> 7) * SK;
+        const uint16_t* s1 = (NMAT == 2) ? S1 + (size_t)(n >> 7) * SK : nullptr;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            int c = cb + lane + 32 * u;
+            if (c < nchunk) {
+                float sc0 = bf16_bits_to_f32(__ldg(s0 + (c >> 2)));
+                float sc1 = (NMAT == 2) ? bf16_bits_to_f32(__ldg(s1 + (c >> 2))) : 0.f;
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    const uint4* ap = a_lo + (size_t)m * (K >> 3);
+                    acc[0][m] = fmaf(dot32_e4m3(b.w[0][u], ap, nchunk, c), sc0, acc[0][m]);
+                    if (NMAT == 2)
+                        acc[NMAT - 1][m] = fmaf(dot32_e4m3(b.w[NMAT - 1][u], ap, nchunk, c), sc1, acc[NMAT - 1][m]);
+                }
+            }
+        }
+    };
+    auto finish_row = [&](int n) {
+#pragma unroll
+        for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+            for (int m = 0; m < M; ++m) acc[t][m] = warp_sum(acc[t][m]);
+        if (lane == 0) {
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                float v = acc[0][m] * inv_s[m];
+                size_t o = (size_t)m * N + n;
+                if (NMAT == 2) {
+                    float g = round_bf16(v);
+                    float u = round_bf16(acc[NMAT - 1][m] * inv_s[m]);
+                    float s = round_bf16(silu_ref(g));
+                    C[o] = f32_to_bf16_bits(s * u);
+                } else {
+                    if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
+                    C[o] = epi.residual ? hadd_bf16_bits(v, epi.residual[o]) : f32_to_bf16_bits(v);
+                }
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+            for (int m = 0; m < M; ++m) acc[t][m] = 0.f;
+    };
+
+    while (nA < N) {
+        compute_group(bufA, (int)nA, cbA);
+        const int doneA = (cbA + 32 * U >= nchunk) ? (int)nA : -1;
+        nA = nB; cbA = cbB; advance(nA, cbA);            // the group after B refills buffer A
+        load_group(bufA, nA, cbA);
+        if (doneA >= 0) finish_row(doneA);
+        if (nB >= N) break;
+        compute_group(bufB, (int)nB, cbB);
+        const int doneB = (cbB + 32 * U >= nchunk) ? (int)nB : -1;
+        nB = nA; cbB = cbA; advance(nB, cbB);
+        load_group(bufB, nB, cbB);
+        if (doneB >= 0) finish_row(doneB);
+    }
+}
+
+// Single-buffered variant: one group (U x 256-bit loads per lane) in flight per warp, up to 16 warps per CTA.
 template <int M, int NMAT>
 __global__ void __launch_bounds__(512)
-gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
+gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
                 const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
                 const uint16_t* __restrict__ S1, uint16_t* __restrict__ C, int K, int N, int rho,
                 GemvEpilogue epi) {
@@ -64,38 +189,50 @@ gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
     const int warp = threadIdx.x >> 5;
     const int wpc = blockDim.x >> 5;
     const long gwarp = (long)blockIdx.x * wpc + warp;
-    const int row_begin = (int)min((long)N, gwarp * rho);
-    const int row_end = (int)min((long)N, gwarp * rho + rho);
+    const long nwarps = (long)gridDim.x * wpc;
+    const int row_begin = (int)min((long)N, gwarp);
+    (void)rho;
     const int nchunk = K >> 5;
     const int SK = (K + 127) >> 7;
 
     u32x8 w[NMAT][U];
+    uint16_t wsc[NMAT][U];     // the 128x128 block scales ride with their weights (same latency window)
     auto load_group = [&](int n, int cb) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             int c = cb + lane + 32 * u;
             if (c < nchunk) {
                 w[0][u] = ldg_stream256(B0 + (size_t)n * K + (size_t)c * 32);
-                if (NMAT == 2) w[NMAT - 1][u] = ldg_stream256(B1 + (size_t)n * K + (size_t)c * 32);
+                wsc[0][u] = __ldg(S0 + (size_t)(n >> 7) * SK + (c >> 2));
+                if (NMAT == 2) {
+                    w[NMAT - 1][u] = ldg_stream256(B1 + (size_t)n * K + (size_t)c * 32);
+                    wsc[NMAT - 1][u] = __ldg(S1 + (size_t)(n >> 7) * SK + (c >> 2));
+                }
             }
         }
     };
     // weights never depend on the previous kernel: start pulling the first row now
-    if (row_begin < row_end) load_group(row_begin, 0);
-    griddep_launch();
+    if (row_begin < N) load_group(row_begin, 0);
+    l2_prefetch_share(epi.next, gwarp * 32 + lane, nwarps * 32);   // only hinted when this launch is L2-fed itself
     griddep_wait();
+    griddep_launch();
     stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
 
     const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
     bool preloaded = true;
-    for (int n = row_begin; n < row_end; ++n) {
+    for (long nl = row_begin; nl < N; nl += nwarps) {
+        const int n = (int)nl;
         float acc[NMAT][M];
 #pragma unroll
         for (int t = 0; t < NMAT; ++t)
 #pragma unroll
             for (int m = 0; m < M; ++m) acc[t][m] = 0.f;
-        const uint16_t* s0 = S0 + (size_t)(n >> 7) * SK;
-        const uint16_t* s1 = (NMAT == 2) ? S1 + (size_t)(n >> 7) * SK : nullptr;
+        // the residual of this row is requested now and consumed after the dot product
+        uint16_t res[M];
+        if (NMAT == 1 && epi.residual && lane == 0) {
+#pragma unroll
+            for (int m = 0; m < M; ++m) res[m] = epi.residual[(size_t)m * N + n];
+        }
         for (int cb = 0; cb < nchunk; cb += 32 * U) {
             if (!preloaded) load_group(n, cb);
             preloaded = false;
@@ -103,8 +240,8 @@ gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
             for (int u = 0; u < U; ++u) {
                 int c = cb + lane + 32 * u;
                 if (c < nchunk) {
-                    float sc0 = bf16_bits_to_f32(__ldg(s0 + (c >> 2)));
-                    float sc1 = (NMAT == 2) ? bf16_bits_to_f32(__ldg(s1 + (c >> 2))) : 0.f;
+                    float sc0 = bf16_bits_to_f32(wsc[0][u]);
+                    float sc1 = (NMAT == 2) ? bf16_bits_to_f32(wsc[NMAT - 1][u]) : 0.f;
 #pragma unroll
                     for (int m = 0; m < M; ++m) {
                         const uint4* ap = a_lo + (size_t)m * (K >> 3);
@@ -131,12 +268,13 @@ gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
                     C[o] = f32_to_bf16_bits(s * u);
                 } else {
                     if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
-                    C[o] = epi.residual ? hadd_bf16_bits(v, epi.residual[o]) : f32_to_bf16_bits(v);
+                    C[o] = epi.residual ? hadd_bf16_bits(v, res[m]) : f32_to_bf16_bits(v);
                 }
             }
         }
     }
 }
+
 
 // Generic fallback (any K, any alignment): warp per row, byte loads, exact LUT semantics
 // including 0x7F/0xFF -> +-480 (fp8.cuh:89,121).
@@ -145,8 +283,8 @@ __global__ void gemv_fp8_generic_kernel(const uint16_t* __restrict__ A, const ui
                                         const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
                                         const uint16_t* __restrict__ S1, uint16_t* __restrict__ C,
                                         int M, int K, int N, GemvEpilogue epi) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int lane = threadIdx.x & 31;
     const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (gw >= (long)N * M) return;
@@ -177,14 +315,19 @@ __global__ void gemv_fp8_generic_kernel(const uint16_t* __restrict__ A, const ui
     }
 }
 
-template <int M, int NMAT>
-static int launch_fp8(const void* A, const void* B0, const void* S0, const void* B1, const void* S1,
-                      void* C, int K, int N, GemvEpilogue epi, cudaStream_t st) {
+// PGK_GEMV_VARIANT: 0 = single buffer (default), 1 = double buffer U=4 / 12 warps, 2 = double buffer U=2 / 16 warps
+static int gemv_variant() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("PGK_GEMV_VARIANT"); v = e ? atoi(e) : 0; }
+    return v;
+}
+
+template <typename Kern>
+static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void* B0, const void* S0, const void* B1,
+                           const void* S1, void* C, int K, int N, GemvEpilogue epi, cudaStream_t st,
+                           std::unordered_map<uint64_t, GemvCfg>& cache, bool& attr_set) {
     size_t smem = (size_t)M * K * 2 + 8 * sizeof(float) + 8 * 16 * sizeof(uint32_t);
-    auto kern = gemv_fp8_kernel<M, NMAT>;
     static std::mutex mu;
-    static std::unordered_map<uint64_t, GemvCfg> cache;
-    static bool attr_set = false;
     GemvCfg cfg;
     {
         std::lock_guard<std::mutex> lk(mu);
@@ -196,7 +339,7 @@ static int launch_fp8(const void* A, const void* B0, const void* S0, const void*
         auto it = cache.find(key);
         if (it == cache.end()) {
             int occ[17] = {0};
-            for (int wpc = 2; wpc <= 16; ++wpc) {
+            for (int wpc = 2; wpc <= maxw; ++wpc) {
                 int nb = 0;
                 PGK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, wpc * 32, smem));
                 occ[wpc] = nb;
@@ -210,6 +353,17 @@ static int launch_fp8(const void* A, const void* B0, const void* S0, const void*
                     (const uint16_t*)A, (const uint8_t*)B0, (const uint16_t*)S0, (const uint8_t*)B1,
                     (const uint16_t*)S1, (uint16_t*)C, K, N, cfg.rho, epi));
     return 0;
+}
+
+template <int M, int NMAT>
+static int launch_fp8(const void* A, const void* B0, const void* S0, const void* B1, const void* S1,
+                      void* C, int K, int N, GemvEpilogue epi, cudaStream_t st) {
+    static std::unordered_map<uint64_t, GemvCfg> cache[3];
+    static bool attr[3] = {false, false, false};
+    const int v = gemv_variant();
+    if (v == 1) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 4, 12>, 12, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[1], attr[1]);
+    if (v == 2) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 2, 16>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[2], attr[2]);
+    return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[0], attr[0]);
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -228,6 +382,7 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
     uint16_t* c = (uint16_t*)C;
     PGK_REQUIRE(!gamma || (fast && K >= 512 && aligned16(gamma)),
                 "rmsnorm_gemv_fp8_bf16 failed: the fused norm needs K %% 32 == 0, K >= 512 and aligned pointers (K=%d)", K);
+    const PrefetchHint hint = take_prefetch_hint();   // one-shot, whichever path runs
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
         long warps = (long)N * M;
@@ -253,6 +408,7 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
         GemvEpilogue epi = {(const uint16_t*)bias,
                             residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
                             (const uint16_t*)gamma, eps};
+        if (m0 + mt >= M) epi.next = hint;
         const uint16_t* am = a + (size_t)m0 * K;
         uint16_t* cm = c + (size_t)m0 * N;
         int rc = 0;

@@ -107,8 +107,8 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
 #pragma unroll
         for (int r = 0; r < RH; ++r) d[r].load(p.Bd + (size_t)(b * 16 + r) * N + n0);
     }
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     stage_activations_f16<M, false>(p.A, K, a_s, inv_s, red_u, p.epi.norm_gamma, p.epi.norm_eps);
 
     float acc[M][COLS];
@@ -219,8 +219,8 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
 __global__ void gemv_nvf4_generic_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd,
                                          const uint8_t* __restrict__ Bs, uint16_t* __restrict__ C, int M,
                                          int K, int N, float alpha, GemvEpilogue epi) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (long)M * N) return;
     int n = (int)(t % N), m = (int)(t / N);
@@ -321,6 +321,7 @@ static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) =
 static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C, int M, int K, int N,
                          float alpha, const void* bias, const void* residual, bool swiglu,
                          cudaStream_t st, const void* gamma = nullptr, float eps = 0.f) {
+    (void)take_prefetch_hint();   // column-panel streaming: the prefix hint does not apply (one-shot, dropped)
     PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_nvf4_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
     const bool fast = (K % 32 == 0) && (N % 16 == 0) && al16(A) && al16(Bd) && al16(Bs) &&
                       ((size_t)K * 2 + kNvf4Hdr <= 200 * 1024);

@@ -75,8 +75,8 @@ quantize_fp8_block_kernel(const uint16_t* __restrict__ W, uint8_t* __restrict__ 
 }
 
 __global__ void decode_advance_kernel(int32_t* a, int32_t* b, int delta) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     if (threadIdx.x == 0) {
         if (a) *a += delta;
         if (b) *b += delta;

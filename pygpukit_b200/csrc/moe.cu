@@ -23,8 +23,8 @@ template <> __device__ __forceinline__ void mst<2>(void* p, size_t i, float v) {
 template <int DT>
 __global__ void moe_topk_kernel(const void* __restrict__ logits, void* __restrict__ values,
                                 int32_t* __restrict__ indices, int T, int E, int k) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int lane = threadIdx.x & 31;
     const int t = (int)(((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (t >= T) return;
@@ -53,8 +53,8 @@ __global__ void moe_topk_kernel(const void* __restrict__ logits, void* __restric
 // softmax_topk_*_kernel topk_kernels.cuh:192-256, in place, one thread per token
 template <int DT>
 __global__ void moe_softmax_topk_kernel(void* __restrict__ values, int T, int k) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= T) return;
     float mx = -INFINITY, sum = 0.f;
@@ -71,8 +71,8 @@ __global__ void moe_softmax_topk_kernel(void* __restrict__ values, int T, int k)
 __global__ void moe_permutation_kernel(const int32_t* __restrict__ expert_indices, int32_t* __restrict__ counts,
                                        int32_t* __restrict__ offsets, int32_t* __restrict__ permute,
                                        int32_t* __restrict__ reverse, int total, int E) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     for (int e = threadIdx.x; e < E; e += blockDim.x) {
         int c = 0;
         for (int i = 0; i < total; ++i) c += (expert_indices[i] == e);
@@ -95,8 +95,8 @@ __global__ void moe_permutation_kernel(const int32_t* __restrict__ expert_indice
 // expand_expert_offsets_kernel moe_kernels.cuh:236-259
 __global__ void moe_expand_offsets_kernel(const int32_t* __restrict__ offsets, int32_t* __restrict__ row_ids, int E,
                                           int m_total) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= m_total) return;
     int lo = 0, hi = E;
@@ -107,8 +107,8 @@ __global__ void moe_expand_offsets_kernel(const int32_t* __restrict__ offsets, i
 // gather_hidden_states_* permute_kernels.cuh:95-182: gathered[p] = hidden[permute[p] / k]
 __global__ void moe_gather_kernel(const uint16_t* __restrict__ hidden, const int32_t* __restrict__ permute,
                                   uint16_t* __restrict__ gathered, int rows, int H, int k) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     for (int p = blockIdx.x; p < rows; p += gridDim.x) {
         const uint16_t* src = hidden + (size_t)(permute[p] / k) * H;
         for (int i = threadIdx.x; i < H; i += blockDim.x) gathered[(size_t)p * H + i] = src[i];
@@ -118,8 +118,8 @@ __global__ void moe_gather_kernel(const uint16_t* __restrict__ hidden, const int
 // scatter_with_reverse_perm_kernel permute_kernels.cuh:218-242: f32 sum over slots 0..k-1
 __global__ void moe_scatter_kernel(const uint16_t* __restrict__ expert_out, const uint16_t* __restrict__ weights,
                                    const int32_t* __restrict__ reverse, uint16_t* __restrict__ out, int T, int H, int k) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     for (int t = blockIdx.x; t < T; t += gridDim.x)
         for (int h = threadIdx.x; h < H; h += blockDim.x) {
             float sum = 0.f;
@@ -137,8 +137,8 @@ __global__ void moe_scatter_kernel(const uint16_t* __restrict__ expert_out, cons
 __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B,
                                             const uint16_t* __restrict__ S, uint16_t* __restrict__ C,
                                             const int32_t* __restrict__ row_ids, int M, int K, int N) {
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int lane = threadIdx.x & 31;
     const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (gw >= (long)M * N) return;
@@ -195,8 +195,8 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     extern __shared__ __align__(16) unsigned char moe_smem[];
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
     float* red = a_s + K;                                             // [warps][128]
-    griddep_launch();
     griddep_wait();
+    griddep_launch();
     const int r = blockIdx.y, col0 = blockIdx.x * 128;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int e = row_expert_ids[r] - expert_offset;

@@ -6,7 +6,8 @@ Same constructor, attributes (`q_proj/k_proj/v_proj/o_proj`, `q_norm/k_norm`, `_
   * q/k/v weights are concatenated row-wise into ONE projection for every weight format (rows are
     independent, so results equal the three separate GEMVs the reference runs for FP8,
     attention.py:315-319);
-  * QK-norm + RoPE + KV-cache write are one kernel (`pgk_qk_norm_rope_kv_write`) reading the f32
+  * QK-norm + RoPE + KV-cache write + attention are ONE kernel for a single new token
+    (`pgk_rope_sdpa_decode`; `pgk_qk_norm_rope_kv_write` + `pgk_sdpa_decode` for M > 1), reading f32
     cos/sin tables that were uploaded ONCE (the reference slices them on the host and does an H2D
     copy per layer per step, attention.py:338-347);
   * the KV cache is stored UN-expanded [num_kv_heads, max_seq, head_dim]; `sdpa_decode` serves the
@@ -17,6 +18,7 @@ Same constructor, attributes (`q_proj/k_proj/v_proj/o_proj`, `q_norm/k_norm`, `_
 """
 from __future__ import annotations
 
+import os
 from typing import TYPE_CHECKING
 
 import numpy as np
@@ -26,7 +28,7 @@ from ...core.array import GPUArray
 from ...core.dtypes import bfloat16, float32, uint8
 from ...core.factory import from_numpy, zeros
 from ...core.stream import current_stream_handle as _st
-from .linear import LinearBF16, LinearFP8, LinearNVF4
+from .linear import LinearBF16, LinearFP8, LinearNVF4, hint_next
 from .norm import Norm
 from .rope import precompute_freqs_cis
 
@@ -34,6 +36,8 @@ if TYPE_CHECKING:
     from ..config import TransformerConfig
 
 _LINEARS = (LinearBF16, LinearFP8, LinearNVF4)
+# PGK_FUSED_BRACKET=0 keeps the two-launch bracket (qk_norm_rope_kv_write + sdpa_decode) for A/B timing
+_FUSED_BRACKET = os.environ.get("PGK_FUSED_BRACKET", "1") != "0"
 
 
 def _concat_rows(arrs: list[GPUArray]) -> GPUArray:
@@ -141,7 +145,7 @@ class Attention:
     # ---- decode
     def attend(self, x: GPUArray, position: int, context_len: int, *, qkv_buf: GPUArray | None = None,
                attn_buf: GPUArray | None = None, pos_buf: GPUArray | None = None,
-               ctx_buf: GPUArray | None = None, norm=None) -> GPUArray:
+               ctx_buf: GPUArray | None = None, norm=None, prefetch=None) -> GPUArray:
         """qkv projection -> QK-norm/RoPE/KV-write -> split-KV attention; returns [M, q_dim]
         (the input of o_proj).  M rows = M consecutive positions of one sequence."""
         assert self._k_cache is not None, "Call init_fixed_cache first"
@@ -151,6 +155,21 @@ class Attention:
         if qkv_buf is not None and qkv_buf.shape[0] != M:
             qkv_buf = qkv_buf.slice_rows(M)
         qkv = self.qkv_proj.forward(x, out=qkv_buf, norm=norm)   # norm: pre-attention RMSNorm fused into the launch
+        if attn_buf is None:
+            attn_buf = GPUArray((M, H * hd), bfloat16)
+        elif attn_buf.shape[0] != M:
+            attn_buf = attn_buf.slice_rows(M)
+        if M == 1 and hd == 128 and self.config.use_rope and _FUSED_BRACKET:
+            # one launch: QK-norm + RoPE + KV write + split-KV attention (pgk_rope_sdpa_decode)
+            hint_next(prefetch)
+            api.rope_sdpa_decode(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
+                                 None if self.k_norm is None else self.k_norm.weight.device_ptr,
+                                 float(self.q_norm.eps if self.q_norm is not None else 0.0),
+                                 self._cos_dev.device_ptr, self._sin_dev.device_ptr, self._k_cache.device_ptr,
+                                 self._v_cache.device_ptr, attn_buf.device_ptr, H, Hkv, hd, self._max_cache_len,
+                                 int(position), None if pos_buf is None else pos_buf.device_ptr, int(context_len),
+                                 None if ctx_buf is None else ctx_buf.device_ptr, 0.0, _st())
+            return attn_buf
         if self.config.use_rope:
             api.qk_norm_rope_kv_write(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
                                       None if self.k_norm is None else self.k_norm.weight.device_ptr,
@@ -161,10 +180,6 @@ class Attention:
         else:
             # no RoPE (GPT-2): plain K/V cache writes straight out of the qkv rows
             raise NotImplementedError("fixed-cache decode without RoPE is not on the B200 path")
-        if attn_buf is None:
-            attn_buf = GPUArray((M, H * hd), bfloat16)
-        elif attn_buf.shape[0] != M:
-            attn_buf = attn_buf.slice_rows(M)
         # Q read in place from the qkv rows (head stride hd, token stride `width`); out [M, H*hd]
         api.sdpa_decode(qkv.device_ptr, self._k_cache.device_ptr, self._v_cache.device_ptr, attn_buf.device_ptr, H, Hkv,
                         M, hd, self._max_cache_len, int(context_len), None if ctx_buf is None else ctx_buf.device_ptr,

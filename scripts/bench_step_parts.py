@@ -71,6 +71,15 @@ def sdpa(blk):
                     a.head_dim, width, a.head_dim, a.num_heads * a.head_dim, 2, st.handle)
 
 
+def fused_attn(blk):
+    a = blk.attn
+    api.rope_sdpa_decode(b.qkv_proj_out.device_ptr, None if a.q_norm is None else a.q_norm.weight.device_ptr,
+                         None if a.k_norm is None else a.k_norm.weight.device_ptr, 1e-6, a._cos_dev.device_ptr,
+                         a._sin_dev.device_ptr, a._k_cache.device_ptr, a._v_cache.device_ptr, b.attn_flat.device_ptr,
+                         a.num_heads, a.num_kv_heads, a.head_dim, a._max_cache_len, 0, b.position_buf.device_ptr, 0,
+                         b.context_buf.device_ptr, 0.0, st.handle)
+
+
 def oproj(blk):
     blk.attn.o_proj.forward(b.attn_flat, out=b.partial, residual=hidden)
 
@@ -90,7 +99,7 @@ def full_layer(blk):
 a0 = model.blocks[0].attn
 kvb = 2 * a0.num_kv_heads * ctx * a0.head_dim * 2
 parts = [("qkv (+norm)", qkv, model.blocks[0].attn.qkv_proj.weight_bytes), ("qkv (no norm)", qkv_nonorm, model.blocks[0].attn.qkv_proj.weight_bytes),
-         ("qknorm+rope+kv", rope, 0), ("sdpa_decode", sdpa, kvb), ("o_proj (+res)", oproj, model.blocks[0].attn.o_proj.weight_bytes)]
+         ("qknorm+rope+kv", rope, 0), ("sdpa_decode", sdpa, kvb), ("rope+sdpa fused;", fused_attn, kvb), ("o_proj (+res)", oproj, model.blocks[0].attn.o_proj.weight_bytes)]
 if not model.config.is_moe:
     m0 = model.blocks[0].mlp
     gub = m0.gate_up_proj.weight_bytes if m0.gate_up_proj is not None else m0.gate_proj.weight_bytes + m0.up_proj.weight_bytes
@@ -102,6 +111,6 @@ for label, fn, nbytes in parts:
     us = timeit(fn)
     gbs = nbytes / us / 1e3 if nbytes else 0.0
     print(f"  {label:26s} {us:8.2f} us   {nbytes / 1e6:8.2f} MB   {gbs:7.0f} GB/s  {gbs / PEAK:5.2f}")
-    if label not in ("full layer", "qkv (no norm)") and ";" not in label:
+    if label not in ("full layer", "qkv (no norm)", "qknorm+rope+kv", "sdpa_decode"):
         tot += us
 print(f"  sum of parts {tot:.1f} us")

@@ -1,5 +1,5 @@
 """Launch ONE op of the decode step a few times (for `ncu --set full -k regex:<kernel>`):
-    python scripts/prof_one.py sdpa|qkv|oproj|gateup|down|rope [model] [format] [context]"""
+    python scripts/prof_one.py sdpa|fattn|qkv|oproj|gateup|down|rope [model] [format] [context]"""
 import os
 import sys
 
@@ -26,6 +26,12 @@ for rep in range(2):
             api.sdpa_decode(b.qkv_proj_out.device_ptr, a._k_cache.device_ptr, a._v_cache.device_ptr,
                             b.attn_flat.device_ptr, a.num_heads, a.num_kv_heads, 1, a.head_dim, a._max_cache_len, ctx,
                             b.context_buf.device_ptr, 0.0, a.head_dim, width, a.head_dim, a.num_heads * a.head_dim, 2, None)
+        elif op == "fattn":
+            api.rope_sdpa_decode(b.qkv_proj_out.device_ptr, None if a.q_norm is None else a.q_norm.weight.device_ptr,
+                                 None if a.k_norm is None else a.k_norm.weight.device_ptr, 1e-6, a._cos_dev.device_ptr,
+                                 a._sin_dev.device_ptr, a._k_cache.device_ptr, a._v_cache.device_ptr,
+                                 b.attn_flat.device_ptr, a.num_heads, a.num_kv_heads, a.head_dim, a._max_cache_len, 0,
+                                 b.position_buf.device_ptr, 0, b.context_buf.device_ptr, 0.0, None)
         elif op == "qkv":
             a.qkv_proj.forward(hidden, out=b.qkv_proj_out, norm=blk.attn_norm)
         elif op == "oproj":

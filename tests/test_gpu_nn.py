@@ -251,6 +251,58 @@ def test_qk_norm_rope_kv_write_fused_equals_op_sequence():
         assert np.array_equal(vc.to_numpy()[:, pos:pos + M], v.transpose(1, 0, 2))
 
 
+@pytest.mark.parametrize("Hq,Hkv,S,pos,use_norm", [
+    (32, 8, 4096, 4095, True),      # Qwen3-8B heads, full cache, last row
+    (32, 8, 4096, 1000, False),     # Llama-3-8B style (no QK-norm), ragged chunk
+    (64, 8, 8192, 5003, False),     # 70B heads: G = 8 -> two row tiles per KV head
+    (32, 4, 512, 0, True),          # A3B heads, first token (context 1)
+    (8, 8, 256, 77, True),          # MHA (G = 1)
+])
+def test_rope_sdpa_decode_fused_equals_two_launches(Hq, Hkv, S, pos, use_norm):
+    """pgk_rope_sdpa_decode == pgk_qk_norm_rope_kv_write + pgk_sdpa_decode on the same inputs: the cache
+    rows must be bit-identical, the attention output within the f32-accumulate tolerance; and both agree
+    with the oracle's naive SDPA over the GQA-expanded cache (attention_kernels.cuh:259-370)."""
+    from pygpukit_b200.llm.layers import precompute_freqs_cis
+    rng = np.random.default_rng(100 + Hq + pos)
+    hd, ctx = 128, pos + 1
+    qkv = rand_bf16(rng, (1, (Hq + 2 * Hkv) * hd))
+    qg, kg = (bf16(rng.uniform(0.5, 1.5, hd).astype(np.float32)) for _ in range(2))
+    cos, sin = precompute_freqs_cis(hd, S, 1e6)
+    gcos, gsin = gk.from_numpy(cos.astype(np.float32)), gk.from_numpy(sin.astype(np.float32))
+    gqg, gkg = gk.from_numpy(qg), gk.from_numpy(kg)
+    k0, v0 = rand_bf16(rng, (Hkv, S, hd), 0.5), rand_bf16(rng, (Hkv, S, hd), 0.5)
+    width = (Hq + 2 * Hkv) * hd
+    pos_buf = gk.from_numpy(np.array([pos], np.int32))
+    ctx_buf = gk.from_numpy(np.array([ctx], np.int32))
+    # two launches
+    qa, ka, va = gk.from_numpy(qkv), gk.from_numpy(k0), gk.from_numpy(v0)
+    oa = gk.zeros((1, Hq * hd), gk.bfloat16)
+    api.qk_norm_rope_kv_write(qa.device_ptr, gqg.device_ptr if use_norm else None, gkg.device_ptr if use_norm else None,
+                              1e-6, gcos.device_ptr, gsin.device_ptr, ka.device_ptr, va.device_ptr, 1, Hq, Hkv, hd, S,
+                              pos, None, None)
+    api.sdpa_decode(qa.device_ptr, ka.device_ptr, va.device_ptr, oa.device_ptr, Hq, Hkv, 1, hd, S, ctx, None, 0.0,
+                    hd, width, hd, Hq * hd, 2, None)
+    # one launch, once with host scalars and once with the device-side counters (graph-replay form)
+    for pb, cb in ((None, None), (pos_buf, ctx_buf)):
+        qb, kb, vb = gk.from_numpy(qkv), gk.from_numpy(k0), gk.from_numpy(v0)
+        ob = gk.zeros((1, Hq * hd), gk.bfloat16)
+        api.rope_sdpa_decode(qb.device_ptr, gqg.device_ptr if use_norm else None, gkg.device_ptr if use_norm else None,
+                             1e-6, gcos.device_ptr, gsin.device_ptr, kb.device_ptr, vb.device_ptr, ob.device_ptr,
+                             Hq, Hkv, hd, S, pos if pb is None else 0, None if pb is None else pb.device_ptr,
+                             ctx if cb is None else 0, None if cb is None else cb.device_ptr, 0.0, None)
+        assert np.array_equal(kb.to_numpy(), ka.to_numpy()) and np.array_equal(vb.to_numpy(), va.to_numpy())
+        assert np.array_equal(qb.to_numpy(), qkv)                  # the qkv row is left untouched
+        assert rel_err(ob.to_numpy(), oa.to_numpy()) <= 2e-3
+    # oracle: naive SDPA over the expanded cache with the roped q of the two-launch path
+    G = Hq // Hkv
+    q_roped = qa.to_numpy()[:, :Hq * hd].reshape(1, Hq, hd).transpose(1, 0, 2)
+    kexp = np.repeat(ka.to_numpy()[:, :ctx], G, axis=0)
+    vexp = np.repeat(va.to_numpy()[:, :ctx], G, axis=0)
+    ref = orc.sdpa_causal_fixed_cache(np.ascontiguousarray(q_roped), np.ascontiguousarray(kexp),
+                                      np.ascontiguousarray(vexp), ctx)
+    assert rel_err(ob.to_numpy().reshape(Hq, 1, hd), ref) <= 1e-2
+
+
 def test_elementwise_glue():
     rng = np.random.default_rng(10)
     a, b = rand_bf16(rng, (3, 1000), 2.0), rand_bf16(rng, (3, 1000), 2.0)
