@@ -423,9 +423,21 @@ def run_ours(args) -> None:
             s = cpu_decode_sample(args.model, args.format, ctx, budget_s=15.0)
             line["cpu_baseline"] = {k: s[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
+    # teardown: the graph that captured NCCL kernels must go before the communicator does, and a rank must
+    # never hang in a collective destroy after its line is printed -- a watchdog ends the process regardless
+    sys.stdout.flush()
+    if world > 1:
+        wd = threading.Timer(20.0, lambda: os._exit(0))
+        wd.daemon = True
+        wd.start()
+    model._graph = None
+    api.device_sync()
+    d.barrier()
     if comm is not None:
         comm.destroy()
     d.close()
+    if world > 1:
+        os._exit(0)
 
 
 def main():

@@ -86,10 +86,11 @@ class Attention:
         # local (per tensor-parallel rank) head counts
         tp = max(1, config.tp_size)
         assert config.num_kv_heads is not None
-        if config.num_heads % tp or config.num_kv_heads % tp:
-            raise ValueError(f"num_heads {config.num_heads} / num_kv_heads {config.num_kv_heads} not divisible by tp_size {tp}")
+        # tp > num_kv_heads: tp / num_kv_heads ranks share (replicate) one KV head, query heads still split
+        if config.num_heads % tp or (config.num_kv_heads % tp and tp % config.num_kv_heads):
+            raise ValueError(f"num_heads {config.num_heads} / num_kv_heads {config.num_kv_heads} not shardable over tp_size {tp}")
         self.num_heads = config.num_heads // tp
-        self.num_kv_heads = config.num_kv_heads // tp
+        self.num_kv_heads = max(1, config.num_kv_heads // tp)
         self.num_kv_groups = self.num_heads // self.num_kv_heads
         self.q_dim = self.num_heads * self.head_dim
         self.k_dim = self.num_kv_heads * self.head_dim

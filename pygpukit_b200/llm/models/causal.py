@@ -141,6 +141,27 @@ class CausalTransformerModel:
         api.gemv_bf16(hidden.device_ptr, self._head.device_ptr, out.device_ptr, M, self.config.hidden_size, V, _st())
         return out
 
+    def _full_logits_host(self, hidden_row: GPUArray) -> np.ndarray:
+        """Logits [V_global] of one final-normed row on the host; under TP the per-rank vocabulary shards are
+        all-gathered first (ranks are in vocabulary order)."""
+        logits = self.get_logits(hidden_row)
+        if self.tp == 1:
+            return logits.to_numpy()[0]
+        V = self._head.shape[0]
+        self.comm.allgather_bytes(logits, self._gathered_logits, V * 2)
+        return self._gathered_logits.to_numpy()
+
+    def _greedy_first_token(self, last: GPUArray, b: DecodeBuffers) -> None:
+        """argmax(lm_head(last)) -> b.token_buf on the device (sharded lm_head: gather, then argmax)."""
+        V, H = self._head.shape[0], self.config.hidden_size
+        if self.tp == 1:
+            api.gemv_bf16_argmax(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
+                                 H, V, _st())
+            return
+        api.gemv_bf16(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, 1, H, V, _st())
+        self.comm.allgather_bytes(b.logits, self._gathered_logits, V * 2)
+        api.argmax(self._gathered_logits.device_ptr, b.token_buf.device_ptr, self.tp * V, 2, _st())
+
     def __call__(self, input_ids: list[int], position_ids: list[int] | None = None, past_key_values=None,
                  use_cache: bool = False):
         """hidden states of `input_ids` (causal.py:108-160); past_key_values = cached positions."""
@@ -251,15 +272,13 @@ class CausalTransformerModel:
         if max_new_tokens <= 0:
             return tokens
         b = self.buffers
-        greedy_dev = temperature == 0 and self.tp == 1
+        greedy_dev = temperature == 0
         if greedy_dev and use_graph and self._graph is None:
             self.init_decode_graph()             # before prefill: capture clobbers cache slot 0 / step state
         hidden = self.prefill(tokens)
         last = hidden.row(hidden.shape[0] - 1).view((1, hidden.shape[1]))
         if greedy_dev:
-            V = self._head.shape[0]
-            api.gemv_bf16_argmax(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
-                                 self.config.hidden_size, V, _st())
+            self._greedy_first_token(last, b)
             first = int(b.token_buf.to_numpy()[0])
             tokens.append(first)
             if (eos_token_id is not None and first == eos_token_id) or max_new_tokens == 1:
@@ -284,7 +303,7 @@ class CausalTransformerModel:
             return tokens
         # host sampling path
         for step in range(max_new_tokens):
-            logits = _to_float32_logits(self.get_logits(last).to_numpy()[0])
+            logits = _to_float32_logits(self._full_logits_host(last))
             nxt = sample_token(logits, temperature, top_k, top_p)
             tokens.append(nxt)
             if (eos_token_id is not None and nxt == eos_token_id) or step == max_new_tokens - 1:

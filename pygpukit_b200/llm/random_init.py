@@ -112,7 +112,7 @@ def build_random_model(name: str = "qwen3-8b", weight_format: str = "fp8", max_s
     for L in range(config.num_layers):
         # q/k/v as ONE fused column-parallel projection: piece p = [q_p | k_p | v_p] rows
         q_rows, kv_rows = config.num_heads * hd, config.num_kv_heads * hd
-        qkv = _fused_qkv(mk, L, q_rows, kv_rows, H)
+        qkv = _fused_qkv(mk, L, q_rows, kv_rows, H, config.num_kv_heads)
         o = mk.linear(L, "o", H, q_rows, "in")
         qn = Norm(gamma(hd), None, "rmsnorm", eps) if spec.use_qk_norm else None
         kn = Norm(gamma(hd), None, "rmsnorm", eps) if spec.use_qk_norm else None
@@ -150,12 +150,28 @@ def build_random_model(name: str = "qwen3-8b", weight_format: str = "fp8", max_s
     return model
 
 
-def _fused_qkv(mk: _Maker, L: int, q_rows: int, kv_rows: int, H: int):
+def _fused_qkv(mk: _Maker, L: int, q_rows: int, kv_rows: int, H: int, n_kv: int = 0):
     """[q | k | v] projection of this process: for each piece p, q/k/v pieces are generated separately
     and stacked so that piece p holds heads [p*Hq/div, ...) and KV heads [p*Hkv/div, ...)."""
     div = max(mk.world, mk.shards)
     n, ids = mk._which()
     qp, kp = q_rows // div, kv_rows // div
+    if n_kv and div > n_kv:
+        # more ranks than KV heads: div / n_kv ranks replicate one whole KV head (same seed -> same weights)
+        if n != 1 or div % n_kv:
+            raise ValueError(f"cannot place {n_kv} KV heads on {div} shards")
+        rep, kp, p = div // n_kv, kv_rows // n_kv, ids[0]
+        width = qp + 2 * kp
+        if mk.fmt == "nvf4":
+            m = np.concatenate([normal_bf16((H, r), _seed(mk.base, L, t, pp), mk.std).to_numpy()
+                                for t, r, pp in (("q", qp, p), ("k", kp, p // rep), ("v", kp, p // rep))], axis=1)
+            return quantize_nvf4(from_numpy(np.ascontiguousarray(m)))
+        m = GPUArray((width, H), bfloat16)
+        off = 0
+        for t, r, pp in (("q", qp, p), ("k", kp, p // rep), ("v", kp, p // rep)):
+            api.fill_normal_bf16(m.device_ptr + off, r * H, _seed(mk.base, L, t, pp), float(mk.std), _st())
+            off += r * H * 2
+        return quantize_fp8(m) if mk.fmt == "fp8" else LinearBF16(m)
     if mk.fmt == "nvf4":
         mats = []
         for p in ids:

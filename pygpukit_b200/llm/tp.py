@@ -5,7 +5,8 @@ One process per GPU.  Megatron-style sharding decided at weight-creation time:
   column-parallel  q/k/v (heads split), gate/up (intermediate split)   -> no communication
   row-parallel     o_proj (K = local heads * hd), down_proj (K = I/tp) -> partial [M, H] sums,
                    ONE all-reduce (bf16, sum) each on the compute stream (graph-capturable)
-  attention        local heads, KV cache sharded by KV head             -> no communication
+  attention        local heads, KV cache sharded by KV head (replicated over world / n_kv ranks
+                   when world > n_kv, e.g. Qwen3-30B-A3B at TP8)        -> no communication
   lm_head          column-parallel over the vocabulary; greedy = all-gather of the per-rank
                    (max logit, argmax) pairs (8 bytes per rank), not of the logits
   MoE              experts sharded E/tp per rank with a replicated router -> same all-reduce
@@ -36,7 +37,13 @@ def shard_plan(config, world: int, rank: int) -> dict:
     """Row/column ranges of every sharded tensor of one layer for `rank` (global index space)."""
     hd = config.head_dim
     q0, q1 = shard_range(config.num_heads, world, rank)
-    kv0, kv1 = shard_range(config.num_kv_heads, world, rank)
+    if world > config.num_kv_heads:      # world / num_kv_heads ranks replicate one KV head
+        if world % config.num_kv_heads:
+            raise ValueError(f"cannot replicate {config.num_kv_heads} KV heads over {world} ranks")
+        kv0 = rank // (world // config.num_kv_heads)
+        kv1 = kv0 + 1
+    else:
+        kv0, kv1 = shard_range(config.num_kv_heads, world, rank)
     plan = {
         "q_rows": (q0 * hd, q1 * hd), "k_rows": (kv0 * hd, kv1 * hd), "v_rows": (kv0 * hd, kv1 * hd),
         "o_cols": (q0 * hd, q1 * hd),
