@@ -152,6 +152,13 @@ class LinearFP8:
         self.block_size = block_size
         self.out_features = weight_fp8.shape[0]
         self.in_features = weight_fp8.shape[1]
+        self._norm_scratch: dict[int, GPUArray] = {}
+
+    def uses_tensor_cores(self, M: int) -> bool:
+        """True when a batch of M rows is served by the tcgen05 skinny GEMM (pgk_gemm_fp8_bf16_tc) instead of
+        the CUDA-core GEMV: 16 <= M <= 64 and 128-aligned shapes (every model shape of BASELINE.json)."""
+        return (16 <= M <= 64 and self.in_features % 128 == 0 and self.out_features % 128 == 0
+                and os.environ.get("PGK_TC", "1") != "0")
 
     def _dequantize_cpu(self) -> np.ndarray:
         """f32 dequantised weight on the host (testing aid; layers/linear.py:181-211)."""
@@ -163,6 +170,12 @@ class LinearFP8:
         _check_x(x, self.in_features)
         M = x.shape[0]
         y = _out2d(out, M, self.out_features)
+        if norm is not None and self.uses_tensor_cores(M):
+            # batch >= 16 goes to the tcgen05 GEMM, which takes plain activations: normalise first (cached scratch)
+            sc = self._norm_scratch.get(M)
+            if sc is None:
+                sc = self._norm_scratch[M] = GPUArray((M, self.in_features), bfloat16)
+            x, norm = norm(x, out=sc), None
         if norm is not None:
             api.rmsnorm_gemv_fp8_bf16(x.device_ptr, norm.weight.device_ptr, float(norm.eps),
                                       self.weight_fp8.device_ptr, self.scale_inv.device_ptr, y.device_ptr, M,

@@ -83,6 +83,19 @@ class MLP:
         M, K, I = x.shape[0], x.shape[1], self.intermediate_size
         if out is None:
             out = GPUArray((M, I), bfloat16)
+        if (self.gate_up_proj is None and isinstance(self.gate_proj, LinearFP8) and isinstance(self.up_proj, LinearFP8)
+                and self.gate_proj.uses_tensor_cores(M) and self.up_proj.uses_tensor_cores(M)):
+            # batch >= 16: gate and up on the tcgen05 GEMM, then silu -> mul with the layer path's two roundings
+            if norm is not None:
+                xs = self._scratch.get(("x", M))
+                if xs is None:
+                    xs = self._scratch[("x", M)] = GPUArray((M, K), bfloat16)
+                x = norm(x, out=xs)
+            sc = self._scratch.get(M)
+            if sc is None:
+                sc = self._scratch[M] = (GPUArray((M, I), bfloat16), GPUArray((M, I), bfloat16))
+            gate = silu(self.gate_proj.forward(x, out=sc[0]), out=sc[0])
+            return mul(gate, self.up_proj.forward(x, out=sc[1]), out=out)
         if norm is not None:
             g, e = norm.weight.device_ptr, float(norm.eps)
             if self.gate_up_proj is not None:

@@ -39,6 +39,61 @@ def test_gemv_fp8_vs_oracle(K, N, M):
     assert np.mean(out != ref) < 0.05             # f32 reordering flips few bf16 roundings
 
 
+@pytest.mark.parametrize("K,N", [(4096, 4096), (1024, 256), (12288, 1024), (128, 128), (2048, 768), (256, 6144)])
+@pytest.mark.parametrize("M", [16, 17, 32, 50, 64])
+def test_gemm_fp8_tc_vs_oracle(K, N, M):
+    """Decode batch 16..64 on tcgen05 (pgk_gemm_fp8_bf16_tc, reached through gemv_fp8_bf16_batched) vs the
+    oracle's FP8 GEMV (f32 weights x bf16 activations).  The block scale is folded into the activations and
+    rounded to BF16 (the reference's M >= 16 path rounds weight*scale to BF16 instead, w8a16_gemm.cu:104-339):
+    BF16-operand tolerance 1e-2 (north_star); and the slab GEMV (PGK_TC=0 semantics, M rows in slabs of 4)
+    must agree with it to the same bar."""
+    if K * N * M > 4096 * 4096 * 16 * 2:
+        pytest.skip("oracle time")
+    from pygpukit_b200._lib import api
+    rng = np.random.default_rng(77 + K + N + M)
+    codes, scale = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_fp8_bf16(A, codes, scale)
+    gA, gB, gS = gk.from_numpy(A), gk.from_numpy(codes), gk.from_numpy(scale)
+    out = gk.zeros((M, N), gk.bfloat16)
+    api.gemm_fp8_bf16_tc(gA.device_ptr, gB.device_ptr, gS.device_ptr, out.device_ptr, M, K, N, None, None, None)
+    got = out.to_numpy()
+    assert rel_err(got, ref) < 1e-2
+    # typical error is far below the bar: the mean relative deviation over the outputs stays under 2e-3
+    d = np.abs(f32(got).astype(np.float64) - f32(ref).astype(np.float64))
+    assert d.mean() / np.abs(f32(ref).astype(np.float64)).mean() < 4e-3
+    # the public batched entry dispatches to the same kernel
+    out2 = ops.gemv_fp8_bf16_batched(gA, gB, gS).to_numpy()
+    assert np.array_equal(out2, got)
+    # epilogues: bias + residual with the reference's rounding points
+    bias, res = rand_bf16(rng, (N,), 0.1), rand_bf16(rng, (M, N), 0.5)
+    gb, gr = gk.from_numpy(bias), gk.from_numpy(res)
+    out3 = gk.zeros((M, N), gk.bfloat16)
+    api.gemm_fp8_bf16_tc(gA.device_ptr, gB.device_ptr, gS.device_ptr, out3.device_ptr, M, K, N, gb.device_ptr,
+                         gr.device_ptr, None)
+    exp = bf16(f32(bf16(f32(got) + f32(bias)[None, :])) + f32(res))
+    assert ulp_diff_bf16(out3.to_numpy(), exp) <= 1
+
+
+def test_gemm_fp8_tc_deterministic_and_linear():
+    """Full-size property checks (no oracle): bit-identical across launches (split-K folds in split order), and
+    rows are independent: a batch equals its two halves computed separately, bit for bit."""
+    from pygpukit_b200._lib import api
+    rng = np.random.default_rng(5)
+    M, K, N = 64, 4096, 12288
+    codes, scale = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (M, K))
+    gA, gB, gS = gk.from_numpy(A), gk.from_numpy(codes), gk.from_numpy(scale)
+    o1, o2 = gk.zeros((M, N), gk.bfloat16), gk.zeros((M, N), gk.bfloat16)
+    for o in (o1, o2):
+        api.gemm_fp8_bf16_tc(gA.device_ptr, gB.device_ptr, gS.device_ptr, o.device_ptr, M, K, N, None, None, None)
+    assert np.array_equal(o1.to_numpy(), o2.to_numpy())
+    h = gk.zeros((32, N), gk.bfloat16)
+    gA2 = gk.from_numpy(np.ascontiguousarray(A[32:]))
+    api.gemm_fp8_bf16_tc(gA2.device_ptr, gB.device_ptr, gS.device_ptr, h.device_ptr, 32, K, N, None, None, None)
+    assert np.array_equal(h.to_numpy(), o1.to_numpy()[32:])
+
+
 @pytest.mark.parametrize("K,N", [(4096, 4096), (4096, 1024), (2048, 8192), (128, 128)])
 def test_oracle_vs_reference_cuda_gemv_fp8(K, N):
     """Pins the oracle: the reference's own kernel on the same inputs must agree BIT FOR BIT with
