@@ -103,8 +103,12 @@ __device__ __forceinline__ uint16_t hadd_bf16_bits(float a, uint16_t b_bits) {
     __nv_bfloat16 r = __hadd(__float2bfloat16_rn(a), __ushort_as_bfloat16(b_bits));
     return __bfloat16_as_ushort(r);
 }
+// two f32 -> packed bf16x2 with ONE full-rate instruction (cvt.rn.bf16x2.f32 = F2FP.BF16.F32.PACK_AB); the
+// scalar F2F.BF16.F32 runs on the quarter-rate conversion pipe
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-    return (uint32_t)f32_to_bf16_bits(lo) | ((uint32_t)f32_to_bf16_bits(hi) << 16);
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
 }
 
 // streaming loads: read-only path, do not allocate in L1, evict-first in L2 (weights are

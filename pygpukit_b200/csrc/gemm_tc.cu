@@ -30,9 +30,9 @@ namespace pgk {
 
 constexpr int kTcRows = 128;      // weight rows per CTA = MMA M
 constexpr int kTcBK = 128;        // k block = FP8 scale block
-constexpr int kTcThreads = 256;
+constexpr int kTcThreads = 512;    // 16 warps: the FP8 -> BF16 conversion is CUDA-core work and needs the warps to hide its latencies
 constexpr int kTcStages = 2;      // BF16 operand stages (tensor-core side)
-constexpr int kTcRaw = 4;         // raw FP8 blocks in flight (cp.async ring)
+constexpr int kTcRaw = 3;         // raw FP8 weight blocks / activation slabs in flight (cp.async rings)
 
 struct TcParams {
     const uint16_t* A; const uint8_t* B; const uint16_t* S; uint16_t* C;
@@ -94,8 +94,9 @@ __device__ __forceinline__ void e4m3x4_to_bf16x4(uint32_t w, uint32_t& lo, uint3
 template <int NB>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_fp8_tc_kernel(TcParams p) {
-    constexpr int WI = 4;                         // weight items per thread per k block (8 rows x 64 B each per warp)
-    constexpr int AI = (NB / 2 + 7) / 8;          // activation items per thread per k block
+    constexpr int NW = kTcThreads / 32;
+    constexpr int WI = 32 / NW;                   // weight items per thread per k block (8 rows x 64 B each per warp)
+    constexpr int AI = (NB / 2 + NW - 1) / NW;    // activation items per thread per k block (copy: 2 rows per warp)
     constexpr uint32_t A_STAGE = kTcRows * kTcBK * 2;      // 32 KB of BF16 weights
     constexpr uint32_t B_STAGE = NB * kTcBK * 2;           // <= 16 KB of BF16 activations
     constexpr uint32_t TMEM_COLS = NB < 32 ? 32 : NB;
@@ -121,29 +122,34 @@ gemm_fp8_tc_kernel(TcParams p) {
         mbar_fence_init();
     }
 
-    // ---- raw FP8 ring: every thread copies (cp.async, 16 B each) and later reads back its OWN four slots of a
-    // block, so the ring needs no CTA barrier -- only cp.async.wait_group.  Weights never depend on the
-    // previous kernel: the first kTcRaw blocks are requested before the dependency wait.
-    unsigned char* raw = smem + (size_t)kTcStages * (A_STAGE + B_STAGE);
+    // ---- raw rings (cp.async / LDGSTS): global -> shared in FULL 128-byte lines (8 lanes per weight row, 16 lanes
+    // per activation row), stored row-major with the 16-byte pieces of a row XOR-swizzled by (row & 7) so that
+    // both the line-wise copy and the core-matrix-wise read-back (8 rows x one piece per quarter warp) are
+    // bank-conflict free.  Weights never depend on the previous kernel: their first kTcRaw blocks are requested
+    // before the dependency wait, the activation slabs after it.  Group order: W0..W(D-1) | A0..A(D-1) |
+    // (W_D, A_D) | ...: block `b` is complete for a thread once at most D-1 of its groups are pending, and
+    // visible to the CTA after the next barrier -- iteration `it` therefore waits for block it+1 before its barrier.
+    unsigned char* raw_w = smem + (size_t)kTcStages * (A_STAGE + B_STAGE);
+    unsigned char* raw_a = raw_w + (size_t)kTcRaw * kTcRows * kTcBK;
     auto issue_weights = [&](int kb, int rs) {
 #pragma unroll
         for (int i = 0; i < WI; ++i) {
-            const int q = i * 8 + warp;                       // 32 items: row group q>>1, 64-byte half q&1
-            const int r = 8 * (q >> 1) + rr;
-            const uint8_t* src = p.B + (size_t)(n0 + r) * p.K + (size_t)kb * kTcBK + (q & 1) * 64 + piece * 16;
-            const uint32_t dst = smem_u32(raw + ((size_t)(rs * WI + i) * kTcThreads + tid) * 16);
+            const int r = (i * NW + warp) * 4 + (lane >> 3), pc = lane & 7;     // 4 rows x 128 B per warp request
+            const uint8_t* src = p.B + (size_t)(n0 + r) * p.K + (size_t)kb * kTcBK + pc * 16;
+            const uint32_t dst = smem_u32(raw_w + (size_t)rs * (kTcRows * kTcBK) + r * 128 + ((pc ^ (r & 7)) * 16));
             asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
         }
     };
-    uint4 aq[AI];
-    auto load_acts = [&](int kb) {
+    auto issue_acts = [&](int kb, int rs) {
 #pragma unroll
         for (int i = 0; i < AI; ++i) {
-            const int q = i * 8 + warp;                       // NB/2 items: row group q>>2, 64-byte quarter q&3
-            const int m = 8 * (q >> 2) + rr;
-            aq[i] = make_uint4(0, 0, 0, 0);
-            if (q < NB / 2 && m < p.M)
-                aq[i] = *reinterpret_cast<const uint4*>(p.A + (size_t)m * p.K + (size_t)kb * kTcBK + (q & 3) * 32 + piece * 8);
+            const int m = (i * NW + warp) * 2 + (lane >> 4), pc = lane & 15;    // 2 rows x 256 B per warp request
+            if (m < NB) {
+                const bool ok = m < p.M;                       // rows past the batch are zero-filled (src-size 0)
+                const uint16_t* src = p.A + (ok ? (size_t)m * p.K + (size_t)kb * kTcBK + pc * 8 : 0);
+                const uint32_t dst = smem_u32(raw_a + (size_t)rs * (NB * kTcBK * 2) + m * 256 + ((pc ^ (m & 7)) * 16));
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
+            }
         }
     };
 #pragma unroll
@@ -153,7 +159,12 @@ gemm_fp8_tc_kernel(TcParams p) {
     }
     griddep_wait();
     griddep_launch();
-    if (nkb > 0) load_acts(kb0);
+#pragma unroll
+    for (int d = 0; d < kTcRaw; ++d) {
+        if (d < nkb) issue_acts(kb0 + d, d);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    asm volatile("cp.async.wait_group %0;" :: "n"(kTcRaw - 1) : "memory");       // block 0 (weights + slab) landed
 
     tc_fence_before();
     __syncthreads();
@@ -165,18 +176,30 @@ gemm_fp8_tc_kernel(TcParams p) {
         const int st = it & 1, kb = kb0 + it, rs = it % kTcRaw;
         unsigned char* a_s = smem + (size_t)st * (A_STAGE + B_STAGE);
         unsigned char* b_s = a_s + A_STAGE;
+        const unsigned char* rw = raw_w + (size_t)rs * (kTcRows * kTcBK);
+        const unsigned char* ra = raw_a + (size_t)rs * (NB * kTcBK * 2);
         const float sc = bf16_bits_to_f32(__ldg(p.S + (size_t)(n0 >> 7) * SK + kb));
-        asm volatile("cp.async.wait_group %0;" :: "n"(kTcRaw - 1) : "memory");   // this thread's slots of block `it` landed
-        uint4 wq[WI];
+        uint4 wq[WI], aq[AI];
 #pragma unroll
-        for (int i = 0; i < WI; ++i)
-            wq[i] = *reinterpret_cast<const uint4*>(raw + ((size_t)(rs * WI + i) * kTcThreads + tid) * 16);
+        for (int i = 0; i < WI; ++i) {
+            const int q = i * NW + warp;                      // 32 items: row group q>>1, 64-byte half q&1
+            const int r = 8 * (q >> 1) + rr, pc = (q & 1) * 4 + piece;
+            wq[i] = *reinterpret_cast<const uint4*>(rw + r * 128 + ((pc ^ rr) * 16));
+        }
+#pragma unroll
+        for (int i = 0; i < AI; ++i) {
+            const int q = i * NW + warp;                      // NB/2 items: row group q>>2, 64-byte quarter q&3
+            if (q < NB / 2) {
+                const int m = 8 * (q >> 2) + rr, pc = (q & 3) * 4 + piece;
+                aq[i] = *reinterpret_cast<const uint4*>(ra + m * 256 + ((pc ^ rr) * 16));
+            }
+        }
         // the MMAs that read this BF16 stage two iterations ago must have completed
         if (it >= kTcStages) mbar_wait(&mma_bar[st], (uint32_t)(((it >> 1) - 1) & 1));
         // weights: 16 codes -> 16 bf16 = k chunks c0, c0 + 1 of row r
 #pragma unroll
         for (int i = 0; i < WI; ++i) {
-            const int q = i * 8 + warp;
+            const int q = i * NW + warp;
             const int c0 = (q & 1) * 8 + piece * 2;
             unsigned char* dst = a_s + (size_t)c0 * (kTcRows * 16) + (size_t)(q >> 1) * 128 + rr * 16;
             uint4 o0, o1;
@@ -185,13 +208,10 @@ gemm_fp8_tc_kernel(TcParams p) {
             *reinterpret_cast<uint4*>(dst) = o0;
             *reinterpret_cast<uint4*>(dst + kTcRows * 16) = o1;
         }
-        // refill the raw slot just consumed (own slots only) and keep the group count uniform
-        if (it + kTcRaw < nkb) issue_weights(kb + kTcRaw, rs);
-        asm volatile("cp.async.commit_group;" ::: "memory");
         // activations: 8 bf16 x block scale -> bf16, k chunk c of batch row m
 #pragma unroll
         for (int i = 0; i < AI; ++i) {
-            const int q = i * 8 + warp;
+            const int q = i * NW + warp;
             if (q < NB / 2) {
                 const int c = (q & 3) * 4 + piece;
                 unsigned char* dst = b_s + (size_t)c * (NB * 16) + (size_t)(q >> 2) * 128 + rr * 16;
@@ -203,9 +223,12 @@ gemm_fp8_tc_kernel(TcParams p) {
                 *reinterpret_cast<uint4*>(dst) = o;
             }
         }
-        if (it + 1 < nkb) load_acts(kb + 1);      // L2-resident slab: one block ahead is enough
         fence_proxy_async();              // generic-proxy smem writes -> visible to the tensor core (async proxy)
-        __syncthreads();
+        asm volatile("cp.async.wait_group %0;" :: "n"(kTcRaw - 2) : "memory");   // this thread's part of block it+1 landed
+        __syncthreads();                  // BF16 stage complete; raw slot `rs` fully read; block it+1 visible to all
+        // refill the raw slot that every thread has finished reading, keep the group count uniform
+        if (it + kTcRaw < nkb) { issue_weights(kb + kTcRaw, rs); issue_acts(kb + kTcRaw, rs); }
+        asm volatile("cp.async.commit_group;" ::: "memory");
         if (tid == 0) {
             tc_fence_after();
             const uint32_t a_addr = smem_u32(a_s), b_addr = smem_u32(b_s);
@@ -266,10 +289,10 @@ gemm_fp8_tc_kernel(TcParams p) {
     // last CTA of the tile: fold the split-K partials in split order (deterministic), then the epilogue.
     // thread = (weight row, half of the batch rows); the loads of eight splits are issued together.
     {
-        const int r = tid & (kTcRows - 1), half = tid >> 7;
+        const int r = tid & (kTcRows - 1), half = tid >> 7;      // four batch-row phases with 512 threads
         const float* base = p.ws + (size_t)tile * p.splits * NB * kTcRows;
         const int nn = n0 + r;
-        for (int m = half; m < p.M; m += 2) {
+        for (int m = half; m < p.M; m += kTcThreads / kTcRows) {
             float x = 0.f;
             for (int s0 = 0; s0 < p.splits; s0 += 8) {
                 float v[8];
@@ -322,7 +345,8 @@ static int launch_tc(TcParams p, cudaStream_t st) {
     p.splits = splits;
     p.ws = g_tc_ws;
     p.counters = g_tc_cnt;
-    constexpr size_t kSmem = (size_t)kTcStages * (kTcRows * kTcBK * 2 + NB * kTcBK * 2) + (size_t)kTcRaw * kTcRows * kTcBK;
+    constexpr size_t kSmem = (size_t)kTcStages * (kTcRows * kTcBK * 2 + NB * kTcBK * 2) +
+                             (size_t)kTcRaw * (kTcRows * kTcBK + NB * kTcBK * 2);
     static bool attr_set = false;
     if (!attr_set) {
         PGK_CUDA(cudaFuncSetAttribute(gemm_fp8_tc_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
