@@ -223,6 +223,13 @@ class Dist:
             return obj[0]
         return ex
 
+    def allgather(self):
+        def ag(payload):
+            out = [None] * self.world
+            self.dist.all_gather_object(out, payload)
+            return out
+        return ag
+
     def close(self):
         if self.world > 1:
             self.dist.destroy_process_group()
@@ -323,7 +330,7 @@ def run_ours(args) -> None:
     pdl = os.environ.get("PGK_PDL", "1") == "1"
     api.set_pdl(1 if pdl else 0)               # programmatic dependent launch between the step's kernels
     d = Dist(rank, local_rank, world)
-    comm = llm.TensorParallel(rank, world).init(exchange=d.exchange()) if world > 1 else None
+    comm = llm.TensorParallel(rank, world).init(exchange=d.exchange(), allgather=d.allgather()) if world > 1 else None
     K, W = args.steps, max(3, args.warmup)
     ctx = args.context
     p0 = ctx - (K + W) - 1
@@ -417,7 +424,8 @@ def run_ours(args) -> None:
             "step_roofline": {"bytes_per_step_per_gpu": step_bytes, "achieved": step_bytes / (ms / K) / 1e6,
                               "unit": "GB/s", "frac": step_bytes / (ms / K) / 1e6 / peak,
                               "frac_of_8000": step_bytes / (ms / K) / 1e6 / 8000.0},
-            "pdl": pdl, "clocks": clk, "token_streams_agree": bool(same_tokens), "build_s": t_build,
+            "pdl": pdl, "allreduce": ("p2p-nvlink" if (comm is not None and comm._p2p) else ("nccl" if world > 1 else None)),
+            "clocks": clk, "token_streams_agree": bool(same_tokens), "build_s": t_build,
         }
         if world == 1 and not args.no_cpu_baseline:
             s = cpu_decode_sample(args.model, args.format, ctx, budget_s=15.0)

@@ -264,6 +264,12 @@ int pgk_moe_scatter(const void* expert_out, const void* router_weights, const in
 int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C,
                              const int32_t* row_expert_ids, int M, int K, int N, void* stream);
 
+/* expert-parallel form: this rank holds experts [expert_offset, expert_offset + num_local_experts) in B / S;
+ * rows routed elsewhere are written as zeros (their owner contributes them through the all-reduce) */
+int pgk_moe_grouped_gemv_fp8_ep(const void* A, const void* B_enk, const void* S, void* C,
+                                const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                                int num_local_experts, void* stream);
+
 /* NVF4 experts (net-new; the reference's MoE is FP8-only): B_data u8 [E_local, K/2, N], B_scale u8
  * [E_local, K/32, N] (per-expert reference NVF4 layout); rows whose expert id falls outside
  * [expert_offset, expert_offset + num_local_experts) are written as zeros. */
@@ -288,6 +294,21 @@ int pgk_nccl_init(const void* host_id128, int rank, int world);
 int pgk_nccl_allreduce_bf16(void* buf, size_t count, void* stream);
 int pgk_nccl_allgather(const void* send, void* recv, size_t bytes_per_rank, void* stream);
 int pgk_nccl_destroy(void);
+
+/* ------------------------------------------------------------------ tensor parallel: peer-memory all-reduce
+ * net-new.  One-shot all-reduce fused with the residual add over NVLink peer memory (cudaIpc-mapped
+ * buffers, flag words published with st.release.sys, sums taken in rank order so every rank holds the same
+ * bits): hidden <- bf16(hidden + bf16(sum_r partial_r)).  Replaces ncclAllReduce + add_inplace for the
+ * row-parallel o_proj / down_proj of the decode step (NCCL costs ~10 us per 16 KB message; this is one
+ * kernel of a few us and is CUDA-graph replayable).  Setup: every rank pgk_p2p_create()s its buffer, the
+ * handles are all-gathered over the host channel, every rank pgk_p2p_open()s them. */
+size_t pgk_p2p_handle_bytes(void);
+int pgk_p2p_create(int rank, int world, void* host_handle_out);
+int pgk_p2p_open(const void* host_handles_all);
+int pgk_p2p_ready(void);
+int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream);
+int pgk_p2p_error(int* host_flag);
+int pgk_p2p_destroy(void);
 
 #ifdef __cplusplus
 }

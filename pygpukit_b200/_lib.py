@@ -83,6 +83,7 @@ _SIGS = {
     "pgk_moe_gather": [vp, vp, vp, i32, i32, i32, vp],
     "pgk_moe_scatter": [vp, vp, vp, vp, i32, i32, i32, vp],
     "pgk_moe_grouped_gemv_fp8": [vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "pgk_moe_grouped_gemv_fp8_ep": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_grouped_gemv_nvf4": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
     "pgk_quantize_bf16_to_fp8_block": [vp, vp, vp, i32, i32, vp],
@@ -90,11 +91,13 @@ _SIGS = {
     "pgk_nccl_unique_id": [vp], "pgk_nccl_init": [vp, i32, i32],
     "pgk_nccl_allreduce_bf16": [vp, sz, vp], "pgk_nccl_allgather": [vp, vp, sz, vp],
     "pgk_nccl_destroy": [],
+    "pgk_p2p_create": [i32, i32, vp], "pgk_p2p_open": [vp], "pgk_p2p_allreduce_add_bf16": [vp, vp, vp, sz, vp],
+    "pgk_p2p_error": [vp], "pgk_p2p_destroy": [],
 }
 _RESTYPE = {"pgk_last_error": C.c_char_p, "pgk_launch_count": i64, "pgk_launch_count_reset": None,
-            "pgk_sdpa_workspace_bytes": sz}
+            "pgk_sdpa_workspace_bytes": sz, "pgk_p2p_handle_bytes": sz, "pgk_p2p_ready": i32}
 _EXTRA = {"pgk_last_error": [], "pgk_launch_count": [], "pgk_launch_count_reset": [],
-          "pgk_sdpa_workspace_bytes": [i32, i32, i32, i32]}
+          "pgk_sdpa_workspace_bytes": [i32, i32, i32, i32], "pgk_p2p_handle_bytes": [], "pgk_p2p_ready": []}
 
 
 def load() -> C.CDLL:

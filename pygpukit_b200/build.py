@@ -34,6 +34,7 @@ SOURCES = {
     "attention.cu": [],
     "moe.cu": [],
     "comm.cu": [],
+    "p2p.cu": [],
     "init.cu": [],
     "quant_nvf4.cu": ["--use_fast_math"],
 }

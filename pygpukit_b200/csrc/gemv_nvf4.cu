@@ -23,6 +23,8 @@
 #include "gemv_common.cuh"
 #include "../../include/pgk_b200.h"
 
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -185,7 +187,14 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
         if (single) {
             for (int w = 0; w < wpc; ++w) v += red_f[((size_t)w * M + m) * CW + col];
         } else {
-            for (int s = 0; s < p.KS; ++s) v += __ldcg(grp_ws + ((size_t)s * M + m) * CW + col);
+            for (int s0 = 0; s0 < p.KS; s0 += 8) {           // eight partials requested together, added in split order
+                float t[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    t[u] = (s0 + u < p.KS) ? __ldcg(grp_ws + ((size_t)(s0 + u) * M + m) * CW + col) : 0.f;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v += t[u];
+            }
         }
         return v * inv_s[m];
     };
@@ -304,6 +313,32 @@ static int launch_nvf4(Nvf4Params p, cudaStream_t st) {
                 }
             }
             PGK_REQUIRE(best_score > 0, "gemv_nvf4_bf16 failed: no launch configuration (K=%d N=%d M=%d)", p.K, p.N, M);
+            // Few column groups (N <= 74 x CW, e.g. the 8192-wide o_proj / down_proj of Llama-3-70B): measured on B200
+            // (scripts/sweep_nvf4.py, K = N = 8192) one fat CTA per SM -- 16 warps, floor(SMs / groups) K-splits, at
+            // least 8 scale blocks per CTA -- beats the many-thin-CTA choice of the score above by 2.5x (12.0 vs 29.9 us):
+            // fewer activation stagings and partial folds, same bytes in flight.
+            if (2 * G <= sms && G <= kMaxGroups) {
+                int KS = sms / G;
+                if (KS > KB / 8) KS = KB / 8 > 1 ? KB / 8 : 1;
+                int bpc = (KB + KS - 1) / KS;
+                KS = (KB + bpc - 1) / bpc;
+                int wpc = bpc < 16 ? (bpc < 4 ? 4 : bpc) : 16;
+                size_t body = (size_t)M * p.K * 2, redb = (size_t)wpc * M * CW * 4;
+                size_t smem = kNvf4Hdr + (body > redb ? body : redb);
+                int occ = 0;
+                if (smem <= 227 * 1024 && (size_t)G * KS * M * CW * 4 <= kWsBytes &&
+                    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, wpc * 32, smem) == cudaSuccess && occ >= 1)
+                    best = {wpc, KS, bpc, smem};
+            }
+            if (const char* ov = getenv("PGK_NVF4_CFG")) {       // tuning aid: "warps_per_cta,k_splits"
+                int w = 0, ks = 0;
+                if (sscanf(ov, "%d,%d", &w, &ks) == 2 && w >= 2 && w <= 16 && ks >= 1 && ks <= KB) {
+                    int bpc = (KB + ks - 1) / ks;
+                    ks = (KB + bpc - 1) / bpc;
+                    size_t body = (size_t)M * p.K * 2, redb = (size_t)w * M * CW * 4;
+                    best = {w, ks, bpc, kNvf4Hdr + (body > redb ? body : redb)};
+                }
+            }
             it = cache.emplace(key, best).first;
         }
         cfg = it->second;

@@ -136,14 +136,19 @@ __global__ void moe_scatter_kernel(const uint16_t* __restrict__ expert_out, cons
 // e4m3), scale per 128-k block.  K % 16 == 0 fast path, scalar tail otherwise.
 __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B,
                                             const uint16_t* __restrict__ S, uint16_t* __restrict__ C,
-                                            const int32_t* __restrict__ row_ids, int M, int K, int N) {
+                                            const int32_t* __restrict__ row_ids, int M, int K, int N,
+                                            int expert_offset, int num_local) {
     griddep_wait();
     griddep_launch();
     const int lane = threadIdx.x & 31;
     const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (gw >= (long)M * N) return;
     const int n = (int)(gw % N), m = (int)(gw / N);
-    const int e = row_ids[m];
+    const int e = row_ids[m] - expert_offset;
+    if (e < 0 || e >= num_local) {             // expert lives on another rank: this rank contributes zero
+        if (lane == 0) C[(size_t)m * N + n] = 0;
+        return;
+    }
     const int SN = (N + 127) >> 7, SK = (K + 127) >> 7;
     const uint8_t* brow = B + ((size_t)e * N + n) * K;
     const uint16_t* srow = S + ((size_t)e * SN + (n >> 7)) * SK;
@@ -321,13 +326,18 @@ int pgk_moe_scatter(const void* expert_out, const void* router_weights, const in
                     (const uint16_t*)router_weights, reverse_perm, (uint16_t*)output, num_tokens, hidden_size, k));
     return 0;
 }
-int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C, const int32_t* row_expert_ids,
-                             int M, int K, int N, void* stream) {
+int pgk_moe_grouped_gemv_fp8_ep(const void* A, const void* B_enk, const void* S, void* C, const int32_t* row_expert_ids,
+                                int M, int K, int N, int expert_offset, int num_local_experts, void* stream) {
     if (M <= 0) return 0;
     size_t warps = (size_t)M * N;
     PGK_CUDA(launch(moe_grouped_gemv_fp8_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream),
-                    (const uint16_t*)A, (const uint8_t*)B_enk, (const uint16_t*)S, (uint16_t*)C, row_expert_ids, M, K, N));
+                    (const uint16_t*)A, (const uint8_t*)B_enk, (const uint16_t*)S, (uint16_t*)C, row_expert_ids, M, K, N,
+                    expert_offset, num_local_experts));
     return 0;
+}
+int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C, const int32_t* row_expert_ids,
+                             int M, int K, int N, void* stream) {
+    return pgk_moe_grouped_gemv_fp8_ep(A, B_enk, S, C, row_expert_ids, M, K, N, 0, 0x7fffffff, stream);
 }
 
 int pgk_moe_grouped_gemv_nvf4(const void* A, const void* B_data, const void* B_scale, void* C,

@@ -1,0 +1,206 @@
+// p2p.cu -- one-shot all-reduce (+ residual add) over NVLink peer memory for the row-parallel layers of the
+// tensor-parallel decode step (net-new: the reference is single-GPU; SURVEY.md section 8e names this as the
+// replacement of the NCCL all-reduce, whose ~10 us latency per 16 KB message dominates a batch-1 step).
+//
+//   hidden[M,H] <- bf16( hidden + bf16( sum_r partial_r[M,H] ) )        r = 0 .. world-1, fixed order
+//
+// One process per GPU.  Every rank owns a communication buffer (cudaMalloc + cudaIpc handle, opened by all
+// peers): two data slabs (parity of the call sequence number) and a flag word per (parity, CTA, source rank).
+// A call = one kernel:
+//   1. every CTA copies its slice of the local partial sums into the local slab (plain stores),
+//   2. one thread publishes: __threadfence_system, then stores the call's sequence number into the flag word
+//      of THIS rank in every peer's buffer (remote NVLink stores),
+//   3. `world` threads spin on the local flag words until every source has published the same number,
+//   4. every thread sums its 16-byte vectors over all ranks in rank order (remote NVLink loads, f32
+//      accumulate), rounds to bf16, adds the residual and stores locally.
+// All ranks compute the identical sum in the identical order, so the replicated hidden state stays bit-identical
+// across ranks (greedy tokens cannot diverge between ranks).  Slab reuse is safe with two parities: a rank can
+// only reach call k+2 after every rank has published call k+1, i.e. after every rank finished reading call k.
+// Sequence numbers live in device memory, so the kernel is CUDA-graph replayable.
+#include "common.cuh"
+#include "../../include/pgk_b200.h"
+
+#include <cstring>
+
+namespace pgk {
+
+constexpr int kP2pMaxWorld = 8;
+constexpr int kP2pMaxCtas = 64;
+constexpr size_t kP2pSlabBytes = 4u << 20;                  // per parity: up to 64 rows x 16384 bf16 x 2 B
+constexpr size_t kP2pFlagBytes = 2 * kP2pMaxCtas * kP2pMaxWorld * sizeof(unsigned);
+constexpr size_t kP2pBufBytes = 2 * kP2pSlabBytes + kP2pFlagBytes;
+
+struct P2pState {
+    int rank = 0, world = 1;
+    unsigned char* local = nullptr;                  // this rank's buffer
+    unsigned char* peer[kP2pMaxWorld] = {};          // every rank's buffer as mapped here (peer[rank] == local)
+    unsigned* seq = nullptr;                         // [kP2pMaxCtas] call counters (device)
+    unsigned* err = nullptr;                         // set when a spin timed out
+    bool ready = false;
+};
+static P2pState g_p2p;
+
+struct P2pParams {
+    const uint16_t* partial;     // [n] local partial sums (bf16)
+    uint16_t* out;               // [n] hidden, updated in place (residual == out) or plain output
+    const uint16_t* residual;    // may be null
+    unsigned char* peer[kP2pMaxWorld];
+    unsigned* seq; unsigned* err;
+    int rank, world;
+    long n;                      // elements, multiple of 8
+    long per_cta;                // elements per CTA, multiple of 8
+};
+
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_flag_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_flag_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
+    __shared__ unsigned s_seq;
+    griddep_wait();                                   // the partial sums come from the GEMV just before
+    griddep_launch();
+    const int cta = blockIdx.x, tid = threadIdx.x;
+    if (tid == 0) s_seq = ++p.seq[cta];               // same count on every rank: SPMD, every rank runs every call
+    __syncthreads();
+    const unsigned seq = s_seq;
+    const unsigned par = seq & 1u;
+    const long e0 = (long)cta * p.per_cta, e1 = min(p.n, e0 + p.per_cta);
+    unsigned char* mine = p.peer[p.rank];
+    // 1. local partials -> local slab
+    for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8)
+        *reinterpret_cast<uint4*>(mine + par * kP2pSlabBytes + e * 2) = *reinterpret_cast<const uint4*>(p.partial + e);
+    __syncthreads();
+    // 2. publish to every rank (own flag word included)
+    if (tid < p.world) {
+        __threadfence_system();
+        unsigned* f = reinterpret_cast<unsigned*>(p.peer[tid] + 2 * kP2pSlabBytes) +
+                      ((size_t)par * kP2pMaxCtas + cta) * kP2pMaxWorld + p.rank;
+        st_flag_sys(f, seq);
+    }
+    // 3. wait for every source rank's slice
+    if (tid < p.world) {
+        const unsigned* f = reinterpret_cast<const unsigned*>(mine + 2 * kP2pSlabBytes) +
+                            ((size_t)par * kP2pMaxCtas + cta) * kP2pMaxWorld + tid;
+        const long long t0 = clock64();
+        while (ld_flag_sys(f) != seq) {
+            if (clock64() - t0 > 4000000000LL) { *p.err = 1u; break; }     // ~2 s: a peer is gone; do not hang the GPU
+        }
+    }
+    __syncthreads();
+    // 4. sum in rank order, round, add the residual
+    for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int r = 0; r < p.world; ++r) {
+            const uint4 v = ld_peer16(p.peer[r] + par * kP2pSlabBytes + e * 2);
+            acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
+            acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+        }
+        uint16_t o[8];
+        if (p.residual) {
+            const uint4 rv = *reinterpret_cast<const uint4*>(p.residual + e);
+            const uint16_t* rb = reinterpret_cast<const uint16_t*>(&rv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = hadd_bf16_bits(acc[j], rb[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = f32_to_bf16_bits(acc[j]);
+        }
+        *reinterpret_cast<uint4*>(p.out + e) = *reinterpret_cast<const uint4*>(o);
+    }
+}
+
+}  // namespace pgk
+
+using namespace pgk;
+
+extern "C" {
+
+size_t pgk_p2p_handle_bytes(void) { return sizeof(cudaIpcMemHandle_t); }
+
+/* step 1 (every rank): allocate the local buffer, return its IPC handle (host memory, pgk_p2p_handle_bytes()) */
+int pgk_p2p_create(int rank, int world, void* host_handle_out) {
+    PGK_REQUIRE(world >= 1 && world <= kP2pMaxWorld && rank >= 0 && rank < world, "p2p_create failed: bad rank %d / world %d", rank, world);
+    PGK_REQUIRE(!g_p2p.local, "p2p_create failed: already created");
+    g_p2p.rank = rank; g_p2p.world = world;
+    PGK_CUDA(cudaMalloc(&g_p2p.local, kP2pBufBytes));
+    PGK_CUDA(cudaMemset(g_p2p.local, 0, kP2pBufBytes));
+    PGK_CUDA(cudaMalloc(&g_p2p.seq, (kP2pMaxCtas + 1) * sizeof(unsigned)));
+    PGK_CUDA(cudaMemset(g_p2p.seq, 0, (kP2pMaxCtas + 1) * sizeof(unsigned)));
+    g_p2p.err = g_p2p.seq + kP2pMaxCtas;
+    cudaIpcMemHandle_t h;
+    PGK_CUDA(cudaIpcGetMemHandle(&h, g_p2p.local));
+    memcpy(host_handle_out, &h, sizeof(h));
+    PGK_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+
+/* step 2 (every rank, after an all-gather of the handles over the host channel): map every peer's buffer */
+int pgk_p2p_open(const void* host_handles_all) {
+    PGK_REQUIRE(g_p2p.local && !g_p2p.ready, "p2p_open failed: call p2p_create first (once)");
+    const cudaIpcMemHandle_t* hs = (const cudaIpcMemHandle_t*)host_handles_all;
+    for (int r = 0; r < g_p2p.world; ++r) {
+        if (r == g_p2p.rank) { g_p2p.peer[r] = g_p2p.local; continue; }
+        void* ptr = nullptr;
+        PGK_CUDA(cudaIpcOpenMemHandle(&ptr, hs[r], cudaIpcMemLazyEnablePeerAccess));
+        g_p2p.peer[r] = (unsigned char*)ptr;
+    }
+    g_p2p.ready = true;
+    return 0;
+}
+
+int pgk_p2p_ready(void) { return g_p2p.ready ? 1 : 0; }
+
+/* out[n] = bf16(residual + bf16(sum over ranks of partial)) (residual NULL: plain all-reduce); out may alias
+ * residual.  n % 8 == 0, n * 2 bytes <= 4 MB, 16-byte aligned pointers.  Every rank must make the same calls
+ * in the same order. */
+int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream) {
+    PGK_REQUIRE(g_p2p.ready, "p2p_allreduce failed: peer buffers not opened (pgk_p2p_create / pgk_p2p_open)");
+    PGK_REQUIRE(n % 8 == 0 && n * 2 <= kP2pSlabBytes, "p2p_allreduce failed: n = %zu must be a multiple of 8 and <= %zu", n, kP2pSlabBytes / 2);
+    PGK_REQUIRE(((uintptr_t)partial % 16 == 0) && ((uintptr_t)out % 16 == 0) && ((uintptr_t)residual % 16 == 0),
+                "p2p_allreduce failed: pointers must be 16-byte aligned");
+    P2pParams p = {};
+    p.partial = (const uint16_t*)partial; p.out = (uint16_t*)out; p.residual = (const uint16_t*)residual;
+    for (int r = 0; r < g_p2p.world; ++r) p.peer[r] = g_p2p.peer[r];
+    p.seq = g_p2p.seq; p.err = g_p2p.err; p.rank = g_p2p.rank; p.world = g_p2p.world;
+    p.n = (long)n;
+    // one CTA of 1024 threads per 8192 elements (16 KB): a batch-1 row of H <= 8192 is a single CTA
+    int ctas = (int)((n + 8191) / 8192);
+    if (ctas > kP2pMaxCtas) ctas = kP2pMaxCtas;
+    long per = ((long)n + ctas - 1) / ctas;
+    p.per_cta = (per + 7) / 8 * 8;
+    PGK_CUDA(launch(p2p_allreduce_add_kernel, dim3(ctas), dim3(1024), 0, (cudaStream_t)stream, p));
+    return 0;
+}
+
+/* 1 if a wait timed out since creation (a peer died): results after that are undefined */
+int pgk_p2p_error(int* host_flag) {
+    unsigned v = 0;
+    if (g_p2p.err) PGK_CUDA(cudaMemcpy(&v, g_p2p.err, sizeof(v), cudaMemcpyDeviceToHost));
+    *host_flag = (int)v;
+    return 0;
+}
+
+int pgk_p2p_destroy(void) {
+    if (!g_p2p.local) return 0;
+    cudaDeviceSynchronize();
+    for (int r = 0; r < g_p2p.world; ++r)
+        if (r != g_p2p.rank && g_p2p.peer[r]) cudaIpcCloseMemHandle(g_p2p.peer[r]);
+    cudaFree(g_p2p.local);
+    cudaFree(g_p2p.seq);
+    g_p2p = P2pState();
+    return 0;
+}
+
+}  // extern "C"

@@ -5,7 +5,6 @@ tensor parallelism the row-parallel partial sums are all-reduced BEFORE the resi
 from __future__ import annotations
 
 from ...core.array import GPUArray
-from ...ops.elementwise import add_inplace
 from .attention import Attention
 from .linear import _PF_ATTN, _PF_OPROJ, can_fuse_norm, hint_next, weight_region
 from .mlp import MLP
@@ -40,8 +39,7 @@ class TransformerBlock:
                                  pos_buf=pos_buf, ctx_buf=ctx_buf, prefetch=self._hints()[0])
         if tp:
             part = self.attn.o_proj.forward(a, out=buf("partial"))
-            self.comm.allreduce(part)
-            add_inplace(hidden, part)
+            self.comm.allreduce_add(part, hidden)
         else:
             hint_next(self._hints()[1])
             self.attn.o_proj.forward(a, out=hidden, residual=hidden)
@@ -50,8 +48,7 @@ class TransformerBlock:
         kw = {"norm": nrm} if fuse_mlp else {}
         if tp:
             part = self.mlp.forward(x, out=buf("partial"), act_buf=buf("mlp_act"), **kw)
-            self.comm.allreduce(part)
-            add_inplace(hidden, part)
+            self.comm.allreduce_add(part, hidden)
         else:
             self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"), **kw)
         return hidden

@@ -96,8 +96,8 @@ class MoELayer:
         w, s = self._w[name]
         R = a.shape[0]
         if self.format == "fp8":
-            api.moe_grouped_gemv_fp8(a.device_ptr, w.device_ptr, s.device_ptr, out.device_ptr, row_ids.device_ptr,
-                                     R, K, N, _st())
+            api.moe_grouped_gemv_fp8_ep(a.device_ptr, w.device_ptr, s.device_ptr, out.device_ptr, row_ids.device_ptr,
+                                        R, K, N, self.expert_offset, self.num_local_experts, _st())
         else:
             api.moe_grouped_gemv_nvf4(a.device_ptr, w.device_ptr, s.device_ptr, out.device_ptr, row_ids.device_ptr,
                                       R, K, N, self.expert_offset, self.num_local_experts, _st())

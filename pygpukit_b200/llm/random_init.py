@@ -173,10 +173,9 @@ def _fused_qkv(mk: _Maker, L: int, q_rows: int, kv_rows: int, H: int, n_kv: int 
             off += r * H * 2
         return quantize_fp8(m) if mk.fmt == "fp8" else LinearBF16(m)
     if mk.fmt == "nvf4":
-        mats = []
-        for p in ids:
-            mats.append(np.concatenate([normal_bf16((H, r), _seed(mk.base, L, t, p), mk.std).to_numpy()
-                                        for t, r in (("q", qp), ("k", kp), ("v", kp))], axis=1) if n > 1 else None)
+        # every piece is ONE draw of its fused width with the piece's "q" seed -- exactly what a TP rank draws
+        mats = [normal_bf16((H, qp + 2 * kp), _seed(mk.base, L, "q", p), mk.std).to_numpy() if n > 1 else None
+                for p in ids]
         if n == 1:
             p = ids[0]
             m = GPUArray((H, qp + 2 * kp), bfloat16)

@@ -73,18 +73,30 @@ class TensorParallel:
     def __init__(self, rank: int, world: int):
         self.rank, self.world = rank, world
         self._ready = False
+        self._p2p = False
 
     @classmethod
     def from_env(cls) -> "TensorParallel":
         return cls(int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
 
-    def init(self, exchange=None, id_file: str | None = None) -> "TensorParallel":
+    def init(self, exchange=None, id_file: str | None = None, allgather=None) -> "TensorParallel":
         """exchange(bytes|None) -> bytes: broadcast of rank 0's 128-byte id (e.g. over
-        torch.distributed); or id_file: a path on a shared filesystem."""
+        torch.distributed); or id_file: a path on a shared filesystem.  allgather(bytes) -> list[bytes]
+        (one entry per rank, in rank order) additionally sets up the NVLink peer-memory all-reduce
+        (pgk_p2p_*), which then replaces NCCL for the row-parallel layers (PGK_P2P=0 keeps NCCL)."""
         from .._lib import api
         if self.world == 1 or self._ready:
             self._ready = True
             return self
+        if allgather is not None and os.environ.get("PGK_P2P", "1") != "0":
+            from .._lib import load
+            hb = int(load().pgk_p2p_handle_bytes())
+            mine = (C.c_char * hb)()
+            api.p2p_create(self.rank, self.world, mine)
+            handles = allgather(bytes(mine))
+            blob = (C.c_char * (hb * self.world)).from_buffer_copy(b"".join(handles))
+            api.p2p_open(blob)
+            self._p2p = True
         buf = (C.c_char * 128)()
         if self.rank == 0:
             api.nccl_unique_id(buf)
@@ -117,6 +129,21 @@ class TensorParallel:
         from ..core.stream import current_stream_handle
         api.nccl_allreduce_bf16(x.device_ptr, x.size, current_stream_handle())
 
+    def allreduce_add(self, part, hidden) -> None:
+        """hidden <- hidden + allreduce(part): the tail of a row-parallel layer.  One peer-memory kernel over
+        NVLink when the p2p buffers are set up, else ncclAllReduce followed by the in-place add."""
+        if self.world == 1:
+            return
+        from .._lib import api
+        from ..core.stream import current_stream_handle
+        if self._p2p and part.size % 8 == 0 and part.nbytes <= (4 << 20):
+            api.p2p_allreduce_add_bf16(part.device_ptr, hidden.device_ptr, hidden.device_ptr, part.size,
+                                       current_stream_handle())
+            return
+        from ..ops.elementwise import add_inplace
+        self.allreduce(part)
+        add_inplace(hidden, part)
+
     def allgather_bytes(self, send, recv, nbytes: int) -> None:
         from .._lib import api
         from ..core.stream import current_stream_handle
@@ -125,8 +152,22 @@ class TensorParallel:
     def destroy(self) -> None:
         if self._ready and self.world > 1:
             from .._lib import api
+            if self._p2p:
+                api.p2p_destroy()
+                self._p2p = False
             api.nccl_destroy()
         self._ready = False
+
+
+def torch_allgather():
+    """allgather() over an initialised torch.distributed process group (harness plumbing)."""
+    import torch.distributed as dist
+
+    def ag(payload: bytes):
+        out = [None] * dist.get_world_size()
+        dist.all_gather_object(out, payload)
+        return out
+    return ag
 
 
 def torch_exchange():
@@ -140,4 +181,4 @@ def torch_exchange():
     return ex
 
 
-__all__ = ["shard_range", "shard_plan", "combine_greedy", "TensorParallel", "torch_exchange"]
+__all__ = ["shard_range", "shard_plan", "combine_greedy", "TensorParallel", "torch_exchange", "torch_allgather"]

@@ -19,7 +19,7 @@ import torch.distributed as dist  # noqa: E402
 
 from pygpukit_b200 import llm  # noqa: E402
 from pygpukit_b200._lib import api  # noqa: E402
-from pygpukit_b200.llm.tp import torch_exchange  # noqa: E402
+from pygpukit_b200.llm.tp import torch_allgather, torch_exchange  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "tiny-qwen3"
 fmt = sys.argv[2] if len(sys.argv) > 2 else "fp8"
@@ -28,7 +28,7 @@ layers = int(sys.argv[4]) if len(sys.argv) > 4 else None
 rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 api.device_set(int(os.environ.get("LOCAL_RANK", "0")))
 dist.init_process_group("gloo")          # host plumbing only: the data path is NCCL through libpgk_b200.so
-comm = llm.TensorParallel(rank, world).init(exchange=torch_exchange())
+comm = llm.TensorParallel(rank, world).init(exchange=torch_exchange(), allgather=torch_allgather())
 max_seq = 256
 prompt = [3, 141, 59, 26, 535, 89, 79, 323]
 
@@ -63,6 +63,7 @@ if rank == 0:
             ok = detail["margin_at_divergence"] <= 2.0 ** -5
         else:
             ok = False
+    detail["allreduce"] = "p2p-nvlink" if comm._p2p else "nccl"
     detail["ok"] = ok
     print(json.dumps(detail), flush=True)
 flag = [ok]
