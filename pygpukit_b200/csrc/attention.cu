@@ -522,13 +522,18 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
         const uint4 v = *reinterpret_cast<const uint4*>(&q_s[r][li * 8]);
         q[r][0] = v.x; q[r][1] = v.y; q[r][2] = v.z; q[r][3] = v.w;
     }
-    float m[RT], l[RT], o[RT][8];
+    // Online-softmax state.  The 16 lanes of a group reduce the 16 (position u, row r) score partials of a tile
+    // with a reduce-scatter (15 shuffles instead of 64): lane li ends up owning the score of u = li >> 2,
+    // r = li & 3, so every exp2 is evaluated by ONE lane (the MUFU pipe runs at a quarter of the FMA rate) and
+    // the running max / sum of row r live in the four lanes with li & 3 == r.  Probabilities and the rescale
+    // factors are then broadcast back for the P.V update, which stays lane-local in the head dimension.
+    static_assert(RT == 4 && U == 4, "the reduce-scatter below is written for 4 rows x 4 positions per tile");
+    float m_own = kNegBig, l_own = 0.f, o[RT][8];
 #pragma unroll
-    for (int r = 0; r < RT; ++r) {
-        m[r] = kNegBig; l[r] = 0.f;
+    for (int r = 0; r < RT; ++r)
 #pragma unroll
         for (int e = 0; e < 8; ++e) o[r][e] = 0.f;
-    }
+    const int gbase = lane & 16;
 
     for (int t = 0; t < ntiles; ++t) {
         const int st = t % kFStages;
@@ -558,7 +563,7 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
                 kq[u] = make_uint4(0, 0, 0, 0); vq[u] = make_uint4(0, 0, 0, 0);
             }
         }
-        float sc[U][RT];
+        float val[16];                                        // index v = u * 4 + r: partial over this lane's 8 dims
 #pragma unroll
         for (int u = 0; u < U; ++u) {
 #pragma unroll
@@ -568,42 +573,67 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
                 fhfma_bf16_lo(a0, q[r][1], kq[u].y); fhfma_bf16_hi(a1, q[r][1], kq[u].y);
                 fhfma_bf16_lo(a0, q[r][2], kq[u].z); fhfma_bf16_hi(a1, q[r][2], kq[u].z);
                 fhfma_bf16_lo(a0, q[r][3], kq[u].w); fhfma_bf16_hi(a1, q[r][3], kq[u].w);
-                float tt = a0 + a1;
-#pragma unroll
-                for (int off = LPR / 2; off > 0; off >>= 1) tt += __shfl_xor_sync(0xffffffffu, tt, off);
-                sc[u][r] = valid[u] ? tt * p.scale_log2 : kNegBig;
+                val[u * 4 + r] = a0 + a1;
             }
         }
+        // reduce-scatter over the group: after the stage with offset b a lane keeps the values whose bit b of v
+        // equals bit b of li, summed over twice as many lanes
+        float tot;
+        {
+            const bool b8 = li & 8, b4 = li & 4, b2 = li & 2, b1 = li & 1;
+            float v8[8], v4[4], v2[2];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                v8[i] = (b8 ? val[i + 8] : val[i]) + __shfl_xor_sync(0xffffffffu, b8 ? val[i] : val[i + 8], 8);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                v4[i] = (b4 ? v8[i + 4] : v8[i]) + __shfl_xor_sync(0xffffffffu, b4 ? v8[i] : v8[i + 4], 4);
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                v2[i] = (b2 ? v4[i + 2] : v4[i]) + __shfl_xor_sync(0xffffffffu, b2 ? v4[i] : v4[i + 2], 2);
+            tot = (b1 ? v2[1] : v2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? v2[0] : v2[1], 1);
+        }
+        // this lane's score: position u = li >> 2 of its slot, row r = li & 3
+        const bool own_valid = t0 + warp * 2 + slot + (li >> 2) * (kAttnWarps * 2) < t1;
+        const float s_own = own_valid ? tot * p.scale_log2 : kNegBig;
+        float mx = fmaxf(s_own, __shfl_xor_sync(0xffffffffu, s_own, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        const float mn = fmaxf(m_own, mx);
+        const float corr_own = exp2f(m_own - mn);
+        const float p_own = (s_own > 0.5f * kNegBig) ? exp2f(s_own - mn) : 0.f;
+        float ls = p_own + __shfl_xor_sync(0xffffffffu, p_own, 4);
+        ls += __shfl_xor_sync(0xffffffffu, ls, 8);
+        l_own = l_own * corr_own + ls;
+        m_own = mn;
+        // broadcast back: rescale factors per row, probabilities per (position, row)
 #pragma unroll
         for (int r = 0; r < RT; ++r) {
-            float mn = m[r];
-#pragma unroll
-            for (int u = 0; u < U; ++u) mn = fmaxf(mn, sc[u][r]);
-            const float corr = exp2f(m[r] - mn);
-            m[r] = mn;
-            l[r] *= corr;
+            const float corr = __shfl_sync(0xffffffffu, corr_own, gbase + r);
 #pragma unroll
             for (int e = 0; e < 8; ++e) o[r][e] *= corr;
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const float pj = (sc[u][r] > 0.5f * kNegBig) ? exp2f(sc[u][r] - mn) : 0.f;
-                sc[u][r] = pj;
-                l[r] += pj;
-            }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             float vf[8];
             KvVec<2>::unpack(vq[u], vf);
 #pragma unroll
-            for (int r = 0; r < RT; ++r)
+            for (int r = 0; r < RT; ++r) {
+                const float pj = __shfl_sync(0xffffffffu, p_own, gbase + u * 4 + r);
 #pragma unroll
-                for (int e = 0; e < 8; ++e) o[r][e] = fmaf(sc[u][r], vf[e], o[r][e]);
+                for (int e = 0; e < 8; ++e) o[r][e] = fmaf(pj, vf[e], o[r][e]);
+            }
         }
         if (t + kFStages < ntiles) {                  // refill this stage (CTA-uniform condition)
             __syncthreads();
             if (threadIdx.x == 0) { fence_proxy_async(); issue_tile(t + kFStages); }
         }
+    }
+    // every lane needs (m, l) of all rows for the merges below
+    float m[RT], l[RT];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        m[r] = __shfl_sync(0xffffffffu, m_own, gbase + r);
+        l[r] = __shfl_sync(0xffffffffu, l_own, gbase + r);
     }
     // merge the two position slots of the warp
 #pragma unroll

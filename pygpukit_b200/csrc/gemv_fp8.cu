@@ -320,7 +320,8 @@ __global__ void gemv_fp8_generic_kernel(const uint16_t* __restrict__ A, const ui
     }
 }
 
-// PGK_GEMV_VARIANT: 0 = single buffer (default), 1 = double buffer U=4 / 12 warps, 2 = double buffer U=2 / 16 warps
+// PGK_GEMV_VARIANT: 0 = single buffer (default), 1 = double buffer U=4 / 12 warps, 2 = double buffer U=2 / 16 warps,
+// 3 = double buffer U=4 / 14 warps (register-capped at 146)
 static int gemv_variant() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("PGK_GEMV_VARIANT"); v = e ? atoi(e) : 0; }
@@ -363,10 +364,11 @@ static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void
 template <int M, int NMAT>
 static int launch_fp8(const void* A, const void* B0, const void* S0, const void* B1, const void* S1,
                       void* C, int K, int N, GemvEpilogue epi, cudaStream_t st) {
-    static std::unordered_map<uint64_t, GemvCfg> cache[3];
-    static bool attr[3] = {false, false, false};
+    static std::unordered_map<uint64_t, GemvCfg> cache[4];
+    static bool attr[4] = {false, false, false, false};
     const int v = gemv_variant();
     if (v == 1) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 4, 12>, 12, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[1], attr[1]);
+    if (v == 3) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 4, 14>, 14, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[3], attr[3]);
     if (v == 2) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 2, 16>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[2], attr[2]);
     return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[0], attr[0]);
 }

@@ -99,13 +99,22 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     __syncthreads();
     // 4. sum in rank order, round, add the residual
     for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8) {
+        // all peer loads are issued back to back (an NVLink round trip is ~1 us: never one after the other),
+        // then summed in rank order
+        uint4 pv[kP2pMaxWorld];
+#pragma unroll
+        for (int r = 0; r < kP2pMaxWorld; ++r)
+            if (r < p.world) pv[r] = ld_peer16(p.peer[r] + par * kP2pSlabBytes + e * 2);
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        for (int r = 0; r < p.world; ++r) {
-            const uint4 v = ld_peer16(p.peer[r] + par * kP2pSlabBytes + e * 2);
-            acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
-            acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+#pragma unroll
+        for (int r = 0; r < kP2pMaxWorld; ++r) {
+            if (r < p.world) {
+                const uint4 v = pv[r];
+                acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
+                acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+            }
         }
         uint16_t o[8];
         if (p.residual) {
