@@ -183,6 +183,8 @@ int pgk_rope_inplace(void* q, void* k, const void* cos, const void* sin, int seq
 int pgk_silu(const void* x, void* y, size_t n, int dtype, void* stream);
 int pgk_gelu(const void* x, void* y, size_t n, int dtype, void* stream);
 int pgk_swiglu(const void* gate, const void* up, void* y, size_t n, int dtype, void* stream);
+/* y = bf16(bf16(silu(gate)) * up): pgk_silu followed by pgk_mul_inplace in one launch (two roundings) */
+int pgk_silu_mul(const void* gate, const void* up, void* y, size_t n, int dtype, void* stream);
 int pgk_add(const void* a, const void* b, void* c, size_t n, int dtype, void* stream);
 int pgk_mul(const void* a, const void* b, void* c, size_t n, int dtype, void* stream);
 int pgk_add_inplace(void* a, const void* b, size_t n, int dtype, void* stream);
@@ -276,6 +278,32 @@ int pgk_moe_grouped_gemv_fp8_ep(const void* A, const void* B_enk, const void* S,
 int pgk_moe_grouped_gemv_nvf4(const void* A, const void* B_data, const void* B_scale, void* C,
                               const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
                               int num_local_experts, void* stream);
+/* _ex: a_stride = elements between consecutive rows of A; 0 broadcasts one activation row to all M rows
+ * (decode: every routed expert reads the same token, so no gather launch is needed). */
+int pgk_moe_grouped_gemv_fp8_ex(const void* A, int a_stride, const void* B_enk, const void* S, void* C,
+                                const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                                int num_local_experts, void* stream);
+int pgk_moe_grouped_gemv_nvf4_ex(const void* A, int a_stride, const void* B_data, const void* B_scale, void* C,
+                                 const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                                 int num_local_experts, void* stream);
+
+/* Decode (num_tokens == 1) forms of MoELayer.__call__ (llm/layers/moe.py:153-318).  With one token the k
+ * rows can stay in slot order, so permutation / expand / gather drop out; each entry reproduces the generic
+ * kernels' arithmetic exactly (bf16 only).
+ *   route_t1:          topk_with_indices + softmax_topk; row_expert_ids[j] = indices[j]
+ *   gateup_fp8_t1:     act[j, n] = bf16(bf16(silu(gate_j[n])) * up_j[n])  (gate/up GEMVs + silu + mul)
+ *   down_combine_fp8_t1: out[n] = bf16(sum_j w_j * bf16(down_j[n])) (+ residual[n], second rounding)
+ *   combine_t1:        the scatter + residual add alone, rows in slot order */
+int pgk_moe_route_t1(const void* logits, void* weights, int32_t* indices, int32_t* row_expert_ids, int num_experts,
+                     int k, void* stream);
+int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, const void* Bu_enk, const void* Su,
+                          void* act, const int32_t* row_expert_ids, int k, int K, int N, int expert_offset,
+                          int num_local_experts, void* stream);
+int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
+                                const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
+                                int expert_offset, int num_local_experts, void* stream);
+int pgk_moe_combine_t1(const void* expert_out, const void* router_weights, const void* residual, void* out,
+                       int hidden_size, int k, void* stream);
 
 /* ------------------------------------------------------------------ synthetic init (net-new)
  * The benchmarks use random-init models (no checkpoint I/O): BF16 masters N(0, std^2) are drawn on

@@ -61,7 +61,7 @@ _SIGS = {
     "pgk_rmsnorm_residual": [vp, vp, vp, vp, i32, i32, f32, i32, vp],
     "pgk_rope_inplace": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "pgk_silu": [vp, vp, sz, i32, vp], "pgk_gelu": [vp, vp, sz, i32, vp],
-    "pgk_swiglu": [vp, vp, vp, sz, i32, vp],
+    "pgk_swiglu": [vp, vp, vp, sz, i32, vp], "pgk_silu_mul": [vp, vp, vp, sz, i32, vp],
     "pgk_add": [vp, vp, vp, sz, i32, vp], "pgk_mul": [vp, vp, vp, sz, i32, vp],
     "pgk_add_inplace": [vp, vp, sz, i32, vp], "pgk_mul_inplace": [vp, vp, sz, i32, vp],
     "pgk_bias_add_inplace": [vp, vp, i32, i32, i32, vp],
@@ -85,6 +85,12 @@ _SIGS = {
     "pgk_moe_grouped_gemv_fp8": [vp, vp, vp, vp, vp, i32, i32, i32, vp],
     "pgk_moe_grouped_gemv_fp8_ep": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_grouped_gemv_nvf4": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_grouped_gemv_fp8_ex": [vp, i32, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_grouped_gemv_nvf4_ex": [vp, i32, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_route_t1": [vp, vp, vp, vp, i32, i32, vp],
+    "pgk_moe_gateup_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_down_combine_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_combine_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
     "pgk_quantize_bf16_to_fp8_block": [vp, vp, vp, i32, i32, vp],
     "pgk_decode_advance": [vp, vp, i32, vp],

@@ -149,7 +149,7 @@ __global__ void rope_kernel(void* __restrict__ q, void* __restrict__ k, const vo
 
 // ---------------------------------------------------------------- unary / binary glue
 enum { OP_SILU = 0, OP_GELU = 1 };
-enum { OP_ADD = 0, OP_MUL = 1, OP_SWIGLU = 2 };
+enum { OP_ADD = 0, OP_MUL = 1, OP_SWIGLU = 2, OP_SILU_MUL = 3 };
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }   // activation_kernels.cuh:40-42
 __device__ __forceinline__ float gelu_f(float x) {                                       // activation_kernels.cuh:26-31
@@ -175,6 +175,11 @@ __global__ void binary_kernel(const void* __restrict__ a, const void* __restrict
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float x = Elem<DT>::ld(a, i), y = Elem<DT>::ld(b, i);
+    if (OP == OP_SILU_MUL) {          // silu -> store rounding -> native multiply: the two-launch form's two roundings
+        Elem<DT>::st(c, i, silu_f(x));
+        Elem<DT>::st(c, i, Elem<DT>::ld(c, i) * y);
+        return;
+    }
     Elem<DT>::st(c, i, OP == OP_ADD ? x + y : (OP == OP_MUL ? x * y : silu_f(x) * y));
 }
 
@@ -421,6 +426,12 @@ int pgk_silu(const void* x, void* y, size_t n, int dtype, void* stream) {
 int pgk_gelu(const void* x, void* y, size_t n, int dtype, void* stream) {
     if (n == 0) return 0;
     PGK_DISPATCH_DT(dtype, "gelu", PGK_CUDA(launch(unary_kernel<DT, OP_GELU>, dim3(blocks_for(n, 256)), dim3(256), 0, ST(stream), x, y, n)));
+    return 0;
+}
+/* y = round(round(silu(gate)) * up): silu + mul_inplace of the layer path (two roundings) in one launch */
+int pgk_silu_mul(const void* gate, const void* up, void* y, size_t n, int dtype, void* stream) {
+    if (n == 0) return 0;
+    PGK_DISPATCH_DT(dtype, "silu_mul", PGK_CUDA(launch(binary_kernel<DT, OP_SILU_MUL>, dim3(blocks_for(n, 256)), dim3(256), 0, ST(stream), gate, up, y, n)));
     return 0;
 }
 int pgk_swiglu(const void* gate, const void* up, void* y, size_t n, int dtype, void* stream) {

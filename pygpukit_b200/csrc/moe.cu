@@ -131,13 +131,56 @@ __global__ void moe_scatter_kernel(const uint16_t* __restrict__ expert_out, cons
         }
 }
 
+// Lane-partial dot products of one bf16 activation row with NB FP8 weight rows (block scales per
+// 128 k), then a warp sum: 128-bit weight loads, exact f32 products, lane-strided 16-k chunks.  Every
+// expert GEMV below goes through this one function, so fused and unfused forms agree bit for bit.
+template <int NB>
+__device__ __forceinline__ void fp8_rows_dot(const uint16_t* __restrict__ arow, const uint8_t* const (&brow)[NB],
+                                             const uint16_t* const (&srow)[NB], int K, int lane, float (&acc)[NB]) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b) acc[b] = 0.f;
+    if ((K & 15) == 0) {
+#pragma unroll 4
+        for (int c = lane; c < (K >> 4); c += 32) {
+            uint4 a0 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16));
+            uint4 a1 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16 + 8));
+            const uint32_t aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                uint4 w = ldg_stream(brow[b] + (size_t)c * 16);
+                float sc = bf16_bits_to_f32(srow[b][c >> 3]);
+                const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+                float part = 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint32_t h0 = e4m3x2_to_f16x2_lo(ww[q]), h1 = e4m3x2_to_f16x2_hi(ww[q]);
+                    float2 f0 = __half22float2(*reinterpret_cast<__half2*>(&h0));
+                    float2 f1 = __half22float2(*reinterpret_cast<__half2*>(&h1));
+                    part = fmaf(bf16lo(aa[2 * q]), f0.x, part);
+                    part = fmaf(bf16hi(aa[2 * q]), f0.y, part);
+                    part = fmaf(bf16lo(aa[2 * q + 1]), f1.x, part);
+                    part = fmaf(bf16hi(aa[2 * q + 1]), f1.y, part);
+                }
+                acc[b] = fmaf(part, sc, acc[b]);
+            }
+        }
+    } else {
+        for (int k = lane; k < K; k += 32)
+#pragma unroll
+            for (int b = 0; b < NB; ++b)
+                acc[b] = fmaf(bf16_bits_to_f32(arow[k]), fp8_e4m3_to_f32(brow[b][k]) * bf16_bits_to_f32(srow[b][k >> 7]), acc[b]);
+    }
+#pragma unroll
+    for (int b = 0; b < NB; ++b) acc[b] = warp_sum(acc[b]);
+}
+
 // Expert-grouped FP8 GEMV: row m uses expert row_expert_ids[m] of B[E,N,K], S[E,N/128,K/128].
 // One warp per (m, n): 128-bit weight loads, exact f32 products (bf16 activation x decoded
 // e4m3), scale per 128-k block.  K % 16 == 0 fast path, scalar tail otherwise.
 __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B,
                                             const uint16_t* __restrict__ S, uint16_t* __restrict__ C,
                                             const int32_t* __restrict__ row_ids, int M, int K, int N,
-                                            int expert_offset, int num_local) {
+                                            int a_stride, int expert_offset, int num_local) {
     griddep_wait();
     griddep_launch();
     const int lane = threadIdx.x & 31;
@@ -150,36 +193,11 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
         return;
     }
     const int SN = (N + 127) >> 7, SK = (K + 127) >> 7;
-    const uint8_t* brow = B + ((size_t)e * N + n) * K;
-    const uint16_t* srow = S + ((size_t)e * SN + (n >> 7)) * SK;
-    const uint16_t* arow = A + (size_t)m * K;
-    float acc = 0.f;
-    if ((K & 15) == 0) {
-        for (int c = lane; c < (K >> 4); c += 32) {
-            uint4 w = ldg_stream(brow + (size_t)c * 16);
-            uint4 a0 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16));
-            uint4 a1 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16 + 8));
-            float sc = bf16_bits_to_f32(srow[c >> 3]);
-            const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-            const uint32_t aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            float part = 0.f;
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint32_t h0 = e4m3x2_to_f16x2_lo(ww[q]), h1 = e4m3x2_to_f16x2_hi(ww[q]);
-                float2 f0 = __half22float2(*reinterpret_cast<__half2*>(&h0));
-                float2 f1 = __half22float2(*reinterpret_cast<__half2*>(&h1));
-                part = fmaf(bf16lo(aa[2 * q]), f0.x, part);
-                part = fmaf(bf16hi(aa[2 * q]), f0.y, part);
-                part = fmaf(bf16lo(aa[2 * q + 1]), f1.x, part);
-                part = fmaf(bf16hi(aa[2 * q + 1]), f1.y, part);
-            }
-            acc = fmaf(part, sc, acc);
-        }
-    } else {
-        for (int k = lane; k < K; k += 32)
-            acc = fmaf(bf16_bits_to_f32(arow[k]), fp8_e4m3_to_f32(brow[k]) * bf16_bits_to_f32(srow[k >> 7]), acc);
-    }
-    acc = warp_sum(acc);
+    const uint8_t* brow[1] = {B + ((size_t)e * N + n) * K};
+    const uint16_t* srow[1] = {S + ((size_t)e * SN + (n >> 7)) * SK};
+    float acc1[1];
+    fp8_rows_dot<1>(A + (size_t)m * a_stride, brow, srow, K, lane, acc1);
+    float acc = acc1[0];
     if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
 }
 
@@ -195,8 +213,8 @@ constexpr int kMoeNvf4Warps = 32;
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
 moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd,
                              const uint8_t* __restrict__ Bs, uint16_t* __restrict__ C,
-                             const int32_t* __restrict__ row_expert_ids, int K, int N, int expert_offset,
-                             int num_local) {
+                             const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
+                             int expert_offset, int num_local) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
     float* red = a_s + K;                                             // [warps][128]
@@ -213,7 +231,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
         }
         return;
     }
-    for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * K + k]);
+    for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * a_stride + k]);
     __syncthreads();
     const uint8_t* bd = Bd + (size_t)e * (K >> 1) * N;
     const uint8_t* bs = Bs + (size_t)e * ((K + 31) >> 5) * N;
@@ -265,6 +283,135 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
         for (int w = 0; w < kMoeNvf4Warps; ++w) s += red[w * 128 + threadIdx.x];
         if (col0 + threadIdx.x < N) C[(size_t)r * N + col0 + threadIdx.x] = f32_to_bf16_bits(s);
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Decode (one token) forms.  With T == 1 the permutation is the identity up to the order of the k
+// rows, and the combine sums in SLOT order whatever the row order is, so row r can simply be slot r:
+// routing collapses to one warp and gather / permutation / expand disappear.  Arithmetic is that of
+// the generic kernels above, statement for statement (tests compare the two bit for bit).
+
+// top-k (strict '>', lowest index wins) + softmax over the selected logits + row ids, one warp.
+__global__ void moe_route_t1_kernel(const uint16_t* __restrict__ logits, uint16_t* __restrict__ weights,
+                                    int32_t* __restrict__ indices, int32_t* __restrict__ row_ids, int E, int k) {
+    griddep_wait();
+    griddep_launch();
+    const int lane = threadIdx.x;
+    constexpr int MAXPL = 16;
+    float loc[MAXPL];
+#pragma unroll
+    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? bf16_bits_to_f32(logits[e]) : -INFINITY; }
+    float mine = -INFINITY;                       // lane j keeps selected value j (k <= 32)
+    for (int j = 0; j < k; ++j) {
+        float bv = -1e30f;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (bi == 0x7fffffff) bi = 0;
+        if (lane == j) { mine = bf16_bits_to_f32(f32_to_bf16_bits(bv)); indices[j] = bi; row_ids[j] = bi; }
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
+    }
+    float mx = mine;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const float ex = __expf(mine - mx);
+    float sum = 0.f;
+    for (int i = 0; i < k; ++i) sum += __shfl_sync(0xffffffffu, ex, i);     // slot order, as the serial kernel
+    const float inv = 1.0f / sum;
+    if (lane < k) weights[lane] = f32_to_bf16_bits(ex * inv);
+}
+
+// gate and up GEMVs of the k routed experts + silu + multiply in one launch: one warp per (slot, n)
+// reads x once for both weight rows.  act = bf16(bf16(silu(bf16 gate)) * bf16 up), the three-launch form.
+__global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ Bg,
+                                         const uint16_t* __restrict__ Sg, const uint8_t* __restrict__ Bu,
+                                         const uint16_t* __restrict__ Su, uint16_t* __restrict__ act,
+                                         const int32_t* __restrict__ row_ids, int R, int K, int N, int expert_offset,
+                                         int num_local) {
+    griddep_wait();
+    griddep_launch();
+    const int lane = threadIdx.x & 31;
+    const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= (long)R * N) return;
+    const int n = (int)(gw % N), m = (int)(gw / N);
+    const int e = row_ids[m] - expert_offset;
+    if (e < 0 || e >= num_local) {
+        if (lane == 0) act[(size_t)m * N + n] = 0;
+        return;
+    }
+    const int SN = (N + 127) >> 7, SK = (K + 127) >> 7;
+    const size_t wo = ((size_t)e * N + n) * K, so = ((size_t)e * SN + (n >> 7)) * SK;
+    const uint8_t* brow[2] = {Bg + wo, Bu + wo};
+    const uint16_t* srow[2] = {Sg + so, Su + so};
+    float acc[2];
+    fp8_rows_dot<2>(x, brow, srow, K, lane, acc);
+    if (lane == 0) {
+        const float g = bf16_bits_to_f32(f32_to_bf16_bits(acc[0]));
+        const float u = bf16_bits_to_f32(f32_to_bf16_bits(acc[1]));
+        const float sg = bf16_bits_to_f32(f32_to_bf16_bits(silu_ref(g)));
+        act[(size_t)m * N + n] = f32_to_bf16_bits(sg * u);
+    }
+}
+
+// down GEMV of the k routed experts + weighted combine in slot order (+ residual): CTA = cols x k
+// warps, warp (c, s) owns expert row n0+c of slot s; the k rounded results meet in shared memory.
+__global__ void moe_down_combine_fp8_t1_kernel(const uint16_t* __restrict__ act, const uint8_t* __restrict__ Bd,
+                                               const uint16_t* __restrict__ Sd, const uint16_t* __restrict__ weights,
+                                               const int32_t* __restrict__ row_ids, const uint16_t* __restrict__ residual,
+                                               uint16_t* __restrict__ out, int k, int K, int N, int cols,
+                                               int expert_offset, int num_local) {
+    __shared__ float part_s[32];
+    griddep_wait();
+    griddep_launch();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = warp / k, sl = warp - c * k;
+    const int n = blockIdx.x * cols + c;
+    float d = 0.f;
+    if (n < N) {
+        const int e = row_ids[sl] - expert_offset;
+        if (e >= 0 && e < num_local) {
+            const int SN = (N + 127) >> 7, SK = (K + 127) >> 7;
+            const uint8_t* brow[1] = {Bd + ((size_t)e * N + n) * K};
+            const uint16_t* srow[1] = {Sd + ((size_t)e * SN + (n >> 7)) * SK};
+            float acc[1];
+            fp8_rows_dot<1>(act + (size_t)sl * K, brow, srow, K, lane, acc);
+            d = bf16_bits_to_f32(f32_to_bf16_bits(acc[0]));
+        }
+    }
+    if (lane == 0) part_s[warp] = d;
+    __syncthreads();
+    if (threadIdx.x < cols) {
+        const int nn = blockIdx.x * cols + threadIdx.x;
+        if (nn < N) {
+            float sum = 0.f;
+            for (int s2 = 0; s2 < k; ++s2) sum = fmaf(bf16_bits_to_f32(weights[s2]), part_s[threadIdx.x * k + s2], sum);
+            uint16_t o = f32_to_bf16_bits(sum);
+            if (residual) o = f32_to_bf16_bits(bf16_bits_to_f32(o) + bf16_bits_to_f32(residual[nn]));
+            out[nn] = o;
+        }
+    }
+}
+
+// scatter with identity row order (+ residual) for the formats without a fused down kernel
+__global__ void moe_combine_t1_kernel(const uint16_t* __restrict__ expert_out, const uint16_t* __restrict__ weights,
+                                      const uint16_t* __restrict__ residual, uint16_t* __restrict__ out, int H, int k) {
+    griddep_wait();
+    griddep_launch();
+    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= H) return;
+    float sum = 0.f;
+    for (int s = 0; s < k; ++s)
+        sum = fmaf(bf16_bits_to_f32(weights[s]), bf16_bits_to_f32(expert_out[(size_t)s * H + h]), sum);
+    uint16_t o = f32_to_bf16_bits(sum);
+    if (residual) o = f32_to_bf16_bits(bf16_bits_to_f32(o) + bf16_bits_to_f32(residual[h]));
+    out[h] = o;
 }
 
 static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
@@ -328,11 +475,17 @@ int pgk_moe_scatter(const void* expert_out, const void* router_weights, const in
 }
 int pgk_moe_grouped_gemv_fp8_ep(const void* A, const void* B_enk, const void* S, void* C, const int32_t* row_expert_ids,
                                 int M, int K, int N, int expert_offset, int num_local_experts, void* stream) {
+    return pgk_moe_grouped_gemv_fp8_ex(A, K, B_enk, S, C, row_expert_ids, M, K, N, expert_offset, num_local_experts, stream);
+}
+int pgk_moe_grouped_gemv_fp8_ex(const void* A, int a_stride, const void* B_enk, const void* S, void* C,
+                                const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                                int num_local_experts, void* stream) {
     if (M <= 0) return 0;
+    PGK_REQUIRE(a_stride == 0 || a_stride >= K, "moe_grouped_gemv_fp8 failed: a_stride=%d must be 0 (broadcast) or >= K", a_stride);
     size_t warps = (size_t)M * N;
     PGK_CUDA(launch(moe_grouped_gemv_fp8_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream),
                     (const uint16_t*)A, (const uint8_t*)B_enk, (const uint16_t*)S, (uint16_t*)C, row_expert_ids, M, K, N,
-                    expert_offset, num_local_experts));
+                    a_stride, expert_offset, num_local_experts));
     return 0;
 }
 int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, void* C, const int32_t* row_expert_ids,
@@ -343,7 +496,14 @@ int pgk_moe_grouped_gemv_fp8(const void* A, const void* B_enk, const void* S, vo
 int pgk_moe_grouped_gemv_nvf4(const void* A, const void* B_data, const void* B_scale, void* C,
                               const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
                               int num_local_experts, void* stream) {
+    return pgk_moe_grouped_gemv_nvf4_ex(A, K, B_data, B_scale, C, row_expert_ids, M, K, N, expert_offset,
+                                        num_local_experts, stream);
+}
+int pgk_moe_grouped_gemv_nvf4_ex(const void* A, int a_stride, const void* B_data, const void* B_scale, void* C,
+                                 const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                                 int num_local_experts, void* stream) {
     if (M <= 0) return 0;
+    PGK_REQUIRE(a_stride == 0 || a_stride >= K, "moe_grouped_gemv_nvf4 failed: a_stride=%d must be 0 (broadcast) or >= K", a_stride);
     PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_grouped_gemv_nvf4 failed: K=%d must be a multiple of 32", K);
     size_t smem = (size_t)K * 4 + (size_t)kMoeNvf4Warps * 128 * 4;
     PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
@@ -354,7 +514,45 @@ int pgk_moe_grouped_gemv_nvf4(const void* A, const void* B_data, const void* B_s
     }
     PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel, dim3((N + 127) / 128, M), dim3(kMoeNvf4Warps * 32), smem, ST(stream),
                     (const uint16_t*)A, (const uint8_t*)B_data, (const uint8_t*)B_scale, (uint16_t*)C, row_expert_ids,
-                    K, N, expert_offset, num_local_experts));
+                    K, N, a_stride, expert_offset, num_local_experts));
+    return 0;
+}
+
+/* ---- decode (one token) forms: same results as the generic pipeline, fewer launches ---- */
+int pgk_moe_route_t1(const void* logits, void* weights, int32_t* indices, int32_t* row_expert_ids, int num_experts,
+                     int k, void* stream) {
+    PGK_REQUIRE(num_experts >= 1 && num_experts <= 512 && k >= 1 && k <= num_experts && k <= 32,
+                "moe_route_t1 failed: unsupported num_experts=%d k=%d", num_experts, k);
+    PGK_CUDA(launch(moe_route_t1_kernel, dim3(1), dim3(32), 0, ST(stream), (const uint16_t*)logits, (uint16_t*)weights,
+                    indices, row_expert_ids, num_experts, k));
+    return 0;
+}
+int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, const void* Bu_enk, const void* Su,
+                          void* act, const int32_t* row_expert_ids, int k, int K, int N, int expert_offset,
+                          int num_local_experts, void* stream) {
+    if (k <= 0) return 0;
+    size_t warps = (size_t)k * N;
+    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
+                    (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
+                    (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts));
+    return 0;
+}
+int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
+                                const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
+                                int expert_offset, int num_local_experts, void* stream) {
+    PGK_REQUIRE(k >= 1 && k <= 32, "moe_down_combine_fp8_t1 failed: unsupported k=%d", k);
+    const int cols = k > 16 ? 1 : (16 / k > 4 ? 4 : 16 / k);   // <= 512-thread CTAs (k <= 16), several resident per SM
+    PGK_CUDA(launch(moe_down_combine_fp8_t1_kernel, dim3((N + cols - 1) / cols), dim3(cols * k * 32), 0, ST(stream),
+                    (const uint16_t*)act, (const uint8_t*)Bd_enk, (const uint16_t*)Sd, (const uint16_t*)router_weights,
+                    row_expert_ids, (const uint16_t*)residual, (uint16_t*)out, k, K, N, cols, expert_offset,
+                    num_local_experts));
+    return 0;
+}
+int pgk_moe_combine_t1(const void* expert_out, const void* router_weights, const void* residual, void* out,
+                       int hidden_size, int k, void* stream) {
+    PGK_CUDA(launch(moe_combine_t1_kernel, dim3(nblk(hidden_size, 256)), dim3(256), 0, ST(stream),
+                    (const uint16_t*)expert_out, (const uint16_t*)router_weights, (const uint16_t*)residual,
+                    (uint16_t*)out, hidden_size, k));
     return 0;
 }
 

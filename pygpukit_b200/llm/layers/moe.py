@@ -13,6 +13,7 @@ Under tensor parallelism every rank holds E/tp experts; rows routed to remote ex
 """
 from __future__ import annotations
 
+import os
 from typing import TYPE_CHECKING
 
 import numpy as np
@@ -27,6 +28,9 @@ from .mlp import MLP
 
 if TYPE_CHECKING:
     from ..config import TransformerConfig
+
+
+_DECODE_FORM = os.environ.get("PGK_MOE_T1", "1") != "0"      # 0: always the generic pipeline (A/B, parity tests)
 
 
 def _stack(arrs: list[GPUArray]) -> GPUArray:
@@ -111,6 +115,8 @@ class MoELayer:
         b = self._buffers(T)
         st = _st()
         self.gate.forward(x, out=b["logits"])
+        if T == 1 and _DECODE_FORM and k <= 32:
+            return self._forward_t1(x, b, out, residual, st)
         api.moe_topk(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr, T, E, k, 2, st)
         api.moe_softmax_topk(b["weights"].device_ptr, T, k, 2, st)
         api.moe_compute_permutation(b["indices"].device_ptr, b["counts"].device_ptr, b["offsets"].device_ptr,
@@ -129,6 +135,32 @@ class MoELayer:
                         T, H, k, st)
         if residual is not None:
             api.add(target.device_ptr, residual.device_ptr, y.device_ptr, T * H, 2, st)
+        return y
+
+    def _forward_t1(self, x: GPUArray, b: dict, out: GPUArray | None, residual: GPUArray | None, st) -> GPUArray:
+        """One token: rows stay in slot order (the combine sums in slot order anyway), so routing is one
+        launch and permutation / expand / gather disappear; FP8 experts run as gate+up+silu+mul and
+        down+combine(+residual) kernels.  Bit-identical to the generic pipeline (tests/test_gpu_moe.py)."""
+        H, I, E, k = self.hidden_size, self.intermediate_size, self.num_experts, self.num_experts_per_tok
+        off, nl = self.expert_offset, self.num_local_experts
+        api.moe_route_t1(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr,
+                         b["row_ids"].device_ptr, E, k, st)
+        y = out if out is not None else GPUArray((1, H), bfloat16)
+        res = residual.device_ptr if residual is not None else None
+        if self.format == "fp8":
+            (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
+            api.moe_gateup_fp8_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                                  b["act"].device_ptr, b["row_ids"].device_ptr, k, H, I, off, nl, st)
+            api.moe_down_combine_fp8_t1(b["act"].device_ptr, wd.device_ptr, sd.device_ptr, b["weights"].device_ptr,
+                                        b["row_ids"].device_ptr, res, y.device_ptr, k, I, H, off, nl, st)
+            return y
+        (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
+        rid = b["row_ids"].device_ptr
+        api.moe_grouped_gemv_nvf4_ex(x.device_ptr, 0, wg.device_ptr, sg.device_ptr, b["act"].device_ptr, rid, k, H, I, off, nl, st)
+        api.moe_grouped_gemv_nvf4_ex(x.device_ptr, 0, wu.device_ptr, su.device_ptr, b["up"].device_ptr, rid, k, H, I, off, nl, st)
+        api.silu_mul(b["act"].device_ptr, b["up"].device_ptr, b["act"].device_ptr, b["act"].size, 2, st)
+        api.moe_grouped_gemv_nvf4_ex(b["act"].device_ptr, I, wd.device_ptr, sd.device_ptr, b["down"].device_ptr, rid, k, I, H, off, nl, st)
+        api.moe_combine_t1(b["down"].device_ptr, b["weights"].device_ptr, res, y.device_ptr, H, k, st)
         return y
 
     def __call__(self, x: GPUArray) -> GPUArray:

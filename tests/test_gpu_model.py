@@ -139,3 +139,39 @@ def test_fused_rmsnorm_gemv_is_bit_identical_to_two_launches(fmt):
         two = lin.forward(norm(x)).to_numpy()
         one = lin.forward(x, norm=norm).to_numpy()
         assert np.array_equal(one, two), f"M={M}"
+
+
+@pytest.mark.parametrize("fmt", ["fp8", "nvf4"])
+@pytest.mark.parametrize("offset", [0, 2])
+@pytest.mark.parametrize("wide", [False, True])
+def test_moe_decode_form_equals_generic_pipeline(fmt, offset, wide):
+    """T == 1 MoE fast path (route_t1 / gateup_fp8_t1 / down_combine_fp8_t1 / broadcast rows / silu_mul /
+    combine_t1) against the 13-launch generic pipeline of the same layer: bit-identical output, with
+    and without a residual, also when only part of the experts is local (expert parallel)."""
+    from pygpukit_b200.llm.layers import moe as moe_mod
+
+    kw = {}
+    if wide:                                    # 64 experts, 8 per token, ragged K (384 = 24 chunks of 16)
+        from pygpukit_b200.llm.config import named_config
+        cfg, spec = named_config("tiny-moe", max_seq=MAX_SEQ)
+        cfg.num_experts, cfg.num_experts_per_tok, cfg.moe_intermediate_size, cfg.num_layers = 64, 8, 384, 1
+        kw = {"config": cfg, "spec": spec}
+    model = _build("tiny-moe", fmt, **kw)
+    layer = next(b.mlp for b in model.blocks if isinstance(b.mlp, llm.MoELayer))
+    if offset:                                  # pretend this rank holds experts [offset, offset + local)
+        layer.expert_offset = offset
+    H = layer.hidden_size
+    rng = np.random.default_rng(11)
+    for trial in range(4):
+        x = gk.from_numpy(rng.standard_normal((1, H)).astype(np.float32)).astype(gk.bfloat16)
+        res = gk.from_numpy(rng.standard_normal((1, H)).astype(np.float32)).astype(gk.bfloat16)
+        for residual in (None, res):
+            outs = []
+            for form in (False, True):
+                moe_mod._DECODE_FORM = form
+                try:
+                    outs.append(layer.forward(x, residual=residual).to_numpy().copy())
+                finally:
+                    moe_mod._DECODE_FORM = True
+            assert np.array_equal(outs[0], outs[1]), f"trial {trial} residual={residual is not None}"
+            assert np.any(outs[0] != 0)
