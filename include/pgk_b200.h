@@ -196,6 +196,10 @@ int pgk_embedding_lookup(const void* table, void* out, int hidden, int token, in
                          void* stream);                      /* embedding_kernels.cuh:27-60 */
 int pgk_embedding_lookup_ptr(const void* table, void* out, int hidden, const int32_t* token_buf,
                              int n_tokens, int elem_bytes, void* stream);
+/* GPT-2 input embedding: out[t] = wte[token_buf[t]] + wpe[pos + t] (one rounding; models/causal.py:137-146 adds
+ * the two rows on the host); pos from *pos_buf when not NULL.  dtype 0 f32 / 1 f16 / 2 bf16. */
+int pgk_embedding_lookup_pos(const void* wte, const void* wpe, void* out, int hidden, const int32_t* token_buf,
+                             int n_tokens, int pos, const int32_t* pos_buf, int dtype, void* stream);
 int pgk_argmax(const void* logits, int32_t* out, int n, int dtype, void* stream);
 /* transpose [d0,d1,d2] -> [d1,d0,d2] (transpose_3d_021) */
 int pgk_transpose_021(const void* in, void* out, int d0, int d1, int d2, int elem_bytes,
@@ -213,7 +217,8 @@ int pgk_kv_cache_update(const void* new_kv, void* cache, int seq, int n_kv, int 
  * tables at position *pos_buf (or pos), K/V written into the un-expanded cache
  * [n_kv, max_seq, hd].  Same rounding points as rmsnorm -> rope_inplace_f32table ->
  * kv_cache_update_gqa (layers/attention.py:326-351). qkv = [.., (Hq + 2*Hkv) * hd] bf16, M rows
- * are M consecutive positions of one sequence. */
+ * are M consecutive positions of one sequence.  cos_table == NULL: no rotation (learned-position
+ * models, GPT-2) -- q stays as projected and K/V rows are copied into the cache. */
 int pgk_qk_norm_rope_kv_write(void* qkv, const void* q_gamma, const void* k_gamma, float eps,
                               const float* cos_table, const float* sin_table, void* k_cache,
                               void* v_cache, int M, int n_heads_q, int n_kv, int head_dim,

@@ -68,6 +68,7 @@ _SIGS = {
     "pgk_cast": [vp, vp, sz, i32, i32, vp],
     "pgk_embedding_lookup": [vp, vp, i32, i32, i32, vp],
     "pgk_embedding_lookup_ptr": [vp, vp, i32, vp, i32, i32, vp],
+    "pgk_embedding_lookup_pos": [vp, vp, vp, i32, vp, i32, i32, vp, i32, vp],
     "pgk_argmax": [vp, vp, i32, i32, vp],
     "pgk_transpose_021": [vp, vp, i32, i32, i32, i32, vp],
     "pgk_kv_cache_update": [vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, vp],

@@ -216,6 +216,22 @@ __global__ void cast_kernel(const void* __restrict__ s, void* __restrict__ d, si
     if (i < n) Elem<DDT>::st(d, i, Elem<SDT>::ld(s, i));
 }
 
+// GPT-2 input: hidden[t] = wte[token[t]] + wpe[pos + t], one rounding (models/causal.py:137-146 adds the
+// two rows on the host in the storage dtype); token ids and the position may live in device buffers.
+template <int DT>
+__global__ void embedding_pos_kernel(const void* __restrict__ wte, const void* __restrict__ wpe, void* __restrict__ out,
+                                     int H, const int32_t* __restrict__ token_buf, int n_tokens, int pos,
+                                     const int32_t* __restrict__ pos_buf) {
+    griddep_wait();
+    griddep_launch();
+    const int p0 = pos_buf ? *pos_buf : pos;
+    for (int t = blockIdx.y; t < n_tokens; t += gridDim.y) {
+        const size_t tok = (size_t)token_buf[t] * H, pr = (size_t)(p0 + t) * H, o = (size_t)t * H;
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < H; i += gridDim.x * blockDim.x)
+            Elem<DT>::st(out, o + i, Elem<DT>::ld(wte, tok + i) + Elem<DT>::ld(wpe, pr + i));
+    }
+}
+
 // ---------------------------------------------------------------- gather / argmax / layout
 // embedding_lookup(_ptr,_batch) embedding_kernels.cuh:27-165: row copy; token id from host or device
 __global__ void embedding_kernel(const uint8_t* __restrict__ table, uint8_t* __restrict__ out, size_t row_bytes,
@@ -366,8 +382,13 @@ __global__ void qk_norm_rope_kv_kernel(uint16_t* __restrict__ qkv, const uint16_
             x0 = round_bf16(x0 * inv * bf16_bits_to_f32(gamma[d]));
             x1 = round_bf16(x1 * inv * bf16_bits_to_f32(gamma[d + half]));
         }
-        float c = cs[(size_t)p * hd + d], s = sn[(size_t)p * hd + d];
-        uint16_t y0 = f32_to_bf16_bits(x0 * c - x1 * s), y1 = f32_to_bf16_bits(x1 * c + x0 * s);
+        uint16_t y0, y1;
+        if (cs) {
+            float c = cs[(size_t)p * hd + d], s = sn[(size_t)p * hd + d];
+            y0 = f32_to_bf16_bits(x0 * c - x1 * s); y1 = f32_to_bf16_bits(x1 * c + x0 * s);
+        } else {                                  // no rotary embedding (GPT-2): plain K/V cache write
+            y0 = f32_to_bf16_bits(x0); y1 = f32_to_bf16_bits(x1);
+        }
         row[d] = y0; row[d + half] = y1;
         if (dstk) { dstk[d] = y0; dstk[d + half] = y1; }
     }
@@ -487,6 +508,15 @@ int pgk_embedding_lookup_ptr(const void* table, void* out, int hidden, const int
     size_t rb = (size_t)hidden * elem_bytes;
     PGK_CUDA(launch(embedding_kernel, dim3(blocks_for(rb / 16 + 1, 256), n_tokens > 65535 ? 65535 : n_tokens), dim3(256), 0,
                     ST(stream), (const uint8_t*)table, (uint8_t*)out, rb, 0, token_buf, n_tokens));
+    return 0;
+}
+int pgk_embedding_lookup_pos(const void* wte, const void* wpe, void* out, int hidden, const int32_t* token_buf,
+                             int n_tokens, int pos, const int32_t* pos_buf, int dtype, void* stream) {
+    if (n_tokens <= 0) return 0;
+    PGK_REQUIRE(token_buf != nullptr, "embedding_lookup_pos failed: token_buf is NULL");
+    PGK_DISPATCH_DT(dtype, "embedding_lookup_pos",
+                    PGK_CUDA(launch(embedding_pos_kernel<DT>, dim3(blocks_for(hidden, 256), n_tokens > 65535 ? 65535 : n_tokens),
+                                    dim3(256), 0, ST(stream), wte, wpe, out, hidden, token_buf, n_tokens, pos, pos_buf)));
     return 0;
 }
 int pgk_argmax(const void* logits, int32_t* out, int n, int dtype, void* stream) {

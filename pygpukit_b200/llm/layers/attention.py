@@ -171,16 +171,15 @@ class Attention:
                                  int(position), None if pos_buf is None else pos_buf.device_ptr, int(context_len),
                                  None if ctx_buf is None else ctx_buf.device_ptr, 0.0, _st())
             return attn_buf
-        if self.config.use_rope:
-            api.qk_norm_rope_kv_write(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
-                                      None if self.k_norm is None else self.k_norm.weight.device_ptr,
-                                      float(self.q_norm.eps if self.q_norm is not None else 0.0),
-                                      self._cos_dev.device_ptr, self._sin_dev.device_ptr, self._k_cache.device_ptr,
-                                      self._v_cache.device_ptr, M, H, Hkv, hd, self._max_cache_len, int(position),
-                                      None if pos_buf is None else pos_buf.device_ptr, _st())
-        else:
-            # no RoPE (GPT-2): plain K/V cache writes straight out of the qkv rows
-            raise NotImplementedError("fixed-cache decode without RoPE is not on the B200 path")
+        # QK-norm / RoPE / K,V cache write in one launch; without RoPE (GPT-2) the tables are NULL and the launch
+        # only writes the K/V rows into the cache
+        rope = self.config.use_rope
+        api.qk_norm_rope_kv_write(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
+                                  None if self.k_norm is None else self.k_norm.weight.device_ptr,
+                                  float(self.q_norm.eps if self.q_norm is not None else 0.0),
+                                  self._cos_dev.device_ptr if rope else None, self._sin_dev.device_ptr if rope else None,
+                                  self._k_cache.device_ptr, self._v_cache.device_ptr, M, H, Hkv, hd, self._max_cache_len,
+                                  int(position), None if pos_buf is None else pos_buf.device_ptr, _st())
         # Q read in place from the qkv rows (head stride hd, token stride `width`); out [M, H*hd]
         api.sdpa_decode(qkv.device_ptr, self._k_cache.device_ptr, self._v_cache.device_ptr, attn_buf.device_ptr, H, Hkv,
                         M, hd, self._max_cache_len, int(context_len), None if ctx_buf is None else ctx_buf.device_ptr,

@@ -129,7 +129,14 @@ class MLP:
     def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
                 act_buf: GPUArray | None = None, norm=None) -> GPUArray:
         if self.activation == "gelu":
-            h = gelu(self.fc1(x))
+            M = x.shape[0]
+            h = act_buf
+            if h is None or tuple(h.shape) != (M, self.intermediate_size):   # cached scratch: graph-capture safe
+                h = self._scratch.get(M)
+                if h is None:
+                    h = self._scratch[M] = GPUArray((M, self.intermediate_size), bfloat16)
+            self.fc1.forward(x, out=h)
+            gelu(h, out=h)
             return self.fc2.forward(h, out=out, residual=residual)
         h = self.gate_up_act(x, out=act_buf, norm=norm)
         return self.down_proj.forward(h, out=out, residual=residual)

@@ -97,11 +97,20 @@ class CausalTransformerModel:
             ids = np.asarray(token_ids, np.int32)
             api.memcpy_h2d(b.token_buf.device_ptr, ids.ctypes.data_as(C.c_void_p), ids.nbytes, _st())
             api.stream_sync(_st()) if _st() is not None else api.device_sync()   # ids is pageable
-        api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, self.config.hidden_size,
-                                 b.token_buf.device_ptr, M, 2, _st())
-        if self.position_embed is not None:
-            raise NotImplementedError("learned position embeddings (GPT-2) are not on the fixed-cache B200 path")
+        self._embed_rows(hidden, M, start_position, None, b)
         return hidden
+
+    def _embed_rows(self, hidden: GPUArray, M: int, position: int, pos_buf: GPUArray | None, b: DecodeBuffers) -> None:
+        """hidden[m] = wte[token_buf[m]] (+ wpe[position + m] for learned positions, GPT-2), one launch."""
+        H = self.config.hidden_size
+        if self.position_embed is None:
+            api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, H, b.token_buf.device_ptr, M, 2, _st())
+            return
+        if pos_buf is None and position + M > self.position_embed.shape[0]:
+            raise ValueError(f"position {position + M - 1} exceeds the learned position table ({self.position_embed.shape[0]})")
+        api.embedding_lookup_pos(self.embed_tokens.device_ptr, self.position_embed.device_ptr, hidden.device_ptr, H,
+                                 b.token_buf.device_ptr, M, int(position), None if pos_buf is None else pos_buf.device_ptr,
+                                 2, _st())
 
     def _layers(self, hidden: GPUArray, position: int, context_len: int, b: DecodeBuffers,
                 pos_buf: GPUArray | None = None, ctx_buf: GPUArray | None = None) -> GPUArray:
@@ -179,8 +188,7 @@ class CausalTransformerModel:
         writes the sampled token to next_token AND token_buf, then advances position / context."""
         b = self.buffers
         hidden = b.hidden.slice_rows(1) if b.hidden.shape[0] != 1 else b.hidden
-        api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, self.config.hidden_size,
-                                 b.token_buf.device_ptr, 1, 2, _st())
+        self._embed_rows(hidden, 1, 0, b.position_buf, b)
         self._layers(hidden, 0, self._max_seq, b, b.position_buf, b.context_buf)
         V, H = self._head.shape[0], self.config.hidden_size
         fn = self.final_norm

@@ -27,7 +27,10 @@ from .layers.norm import Norm
 from .models.causal import CausalTransformerModel
 
 _TENSOR_IDS = {"embed": 1, "lm_head": 2, "q": 3, "k": 4, "v": 5, "o": 6, "gate": 7, "up": 8, "down": 9,
-               "router": 10, "e_gate": 11, "e_up": 12, "e_down": 13}
+               "router": 10, "e_gate": 11, "e_up": 12, "e_down": 13,
+               # GPT-2 family
+               "wpe": 14, "qb": 15, "kb": 16, "vb": 17, "ob": 18, "fc1": 19, "fc1b": 20, "fc2": 21, "fc2b": 22,
+               "ln1_b": 23, "ln2_b": 24, "lnf_b": 25}
 
 
 def _seed(base: int, layer: int, tensor: str, piece: int) -> int:
@@ -99,6 +102,8 @@ def build_random_model(name: str = "qwen3-8b", weight_format: str = "fp8", max_s
         config, spec = named_config(name, max_seq=max_seq, tp_size=world, tp_rank=rank)
     if num_layers is not None:
         config.num_layers = num_layers
+    if spec is not None and spec.use_position_embed:
+        return _gpt2(name, config, spec, weight_format, seed, std, world, shards)
     mk = _Maker(weight_format, seed, std, world, rank, shards)
     div = max(world, shards)
     H, hd = config.hidden_size, config.head_dim
@@ -145,6 +150,36 @@ def build_random_model(name: str = "qwen3-8b", weight_format: str = "fp8", max_s
         head = normal_bf16((V, H), _seed(seed, 0, "lm_head", 0), std)
     model = CausalTransformerModel(config, embed, blocks, Norm(gamma(H), None, "rmsnorm", eps), lm_head=head,
                                    spec=spec, comm=comm)
+    model.weight_format = weight_format
+    model.name = name
+    return model
+
+
+def _gpt2(name: str, config: TransformerConfig, spec: ModelSpec, weight_format: str, seed: int, std: float,
+          world: int, shards: int) -> CausalTransformerModel:
+    """GPT-2 family (BASELINE.json configs[0]): LayerNorm with bias, biased q/k/v/o and fc1/fc2, GELU, learned
+    positions, tied lm_head -- BF16 weights on one GPU (the reference runs it in FP32/FP16; there is no quantised
+    GPT-2 checkpoint format upstream)."""
+    if weight_format != "bf16" or world > 1 or shards > 1:
+        raise ValueError("GPT-2 runs with weight_format='bf16' on a single GPU")
+    H, L = config.hidden_size, config.num_layers
+    I, eps = config.intermediate_size, config.norm_eps
+
+    def w(tag, layer, *shape, s=std):
+        return normal_bf16(shape, _seed(seed, layer, tag, 0), s)
+
+    def ln(tag, layer):
+        return Norm(ones((H,), bfloat16), w(tag + "_b", layer, H, s=0.01), "layernorm", eps)
+
+    blocks = []
+    for i in range(L):
+        attn = Attention(w("q", i, H, H), w("k", i, H, H), w("v", i, H, H), w("o", i, H, H), config,
+                         q_bias=w("qb", i, H), k_bias=w("kb", i, H), v_bias=w("vb", i, H), o_bias=w("ob", i, H))
+        mlp = MLP(config, fc1_weight=w("fc1", i, I, H), fc1_bias=w("fc1b", i, I), fc2_weight=w("fc2", i, H, I),
+                  fc2_bias=w("fc2b", i, H))
+        blocks.append(TransformerBlock(ln("ln1", i), attn, ln("ln2", i), mlp))
+    model = CausalTransformerModel(config, w("embed", 0, config.vocab_size, H), blocks, ln("lnf", 0), lm_head=None,
+                                   position_embed=w("wpe", 0, config.max_position_embeddings, H), spec=spec)
     model.weight_format = weight_format
     model.name = name
     return model

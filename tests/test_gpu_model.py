@@ -175,3 +175,101 @@ def test_moe_decode_form_equals_generic_pipeline(fmt, offset, wide):
                     moe_mod._DECODE_FORM = True
             assert np.array_equal(outs[0], outs[1]), f"trial {trial} residual={residual is not None}"
             assert np.any(outs[0] != 0)
+
+
+# ---------------------------------------------------------------------------- GPT-2 (BASELINE.json configs[0] family)
+def _gpt2_tiny_model():
+    """The tiny GPT-2 of tests/golden/gpt2_tiny.py assembled through the reference's constructors
+    (Attention with biases, GELU MLP, LayerNorm, learned positions, tied lm_head), BF16 on the GPU."""
+    from tests.golden import gpt2_tiny as T
+
+    w = T.weights()
+    cfg = llm.GPT2Config(**T.CFG).to_transformer_config()
+
+    def g(a):
+        return gk.from_numpy(np.ascontiguousarray(a, np.float32)).astype(gk.bfloat16)
+
+    def norm(p):
+        return llm.Norm(g(w[p + ".g"]), g(w[p + ".b"]), "layernorm", cfg.norm_eps)
+
+    blocks = []
+    for i in range(cfg.num_layers):
+        p = f"h{i}."
+        attn = llm.Attention(g(w[p + "q.w"]), g(w[p + "k.w"]), g(w[p + "v.w"]), g(w[p + "o.w"]), cfg,
+                             q_bias=g(w[p + "q.b"]), k_bias=g(w[p + "k.b"]), v_bias=g(w[p + "v.b"]), o_bias=g(w[p + "o.b"]))
+        mlp = llm.MLP(cfg, fc1_weight=g(w[p + "fc1.w"]), fc1_bias=g(w[p + "fc1.b"]), fc2_weight=g(w[p + "fc2.w"]),
+                      fc2_bias=g(w[p + "fc2.b"]))
+        blocks.append(llm.TransformerBlock(norm(p + "ln_1"), attn, norm(p + "ln_2"), mlp))
+    model = llm.GPT2Model(cfg, g(w["wte"]), blocks, norm("ln_f"), lm_head=None, position_embed=g(w["wpe"]),
+                          spec=llm.GPT2_SPEC)
+    model.init_decode(T.CFG["n_positions"], max_batch_size=16)
+    return model, T
+
+
+def test_gpt2_matches_reference_cpu_run():
+    """GPT-2 (LayerNorm, biases, GELU, learned positions, no RoPE, MHA head_dim 64) through the B200 decode path
+    in BF16 against the REFERENCE's own FP32 CPU run of the same weights (tests/golden/golden_gpt2.npz).
+    Teacher-forced on the reference's tokens: logits within 2e-2 of the logit scale (BF16 end to end over two
+    layers; the per-op bar is 1e-2), identical argmax wherever the reference's top-2 margin is clear; then free
+    greedy generation (graph replay and eager) identical up to the first near-tie."""
+    import os
+
+    model, T = _gpt2_tiny_model()
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_gpt2.npz"))
+    toks = [int(t) for t in g["tokens"]]
+    P, scale = len(T.PROMPT), float(g["logit_scale"])
+    clear = g["margins"] > 0.12                       # ~2 bf16 ulps at |logit| ~ 8
+    assert clear.sum() >= T.N_NEW - 2
+
+    # (1) whole sequence in slabs of 16 rows (batch path), logits of the generated positions
+    hidden, _ = model(toks[:-1])
+    n_last = (len(toks) - 1) % 16 or 16
+    assert hidden.shape[0] == n_last
+    # (2) single-token steps over the generated positions (M == 1 path), teacher-forced
+    model.init_decode(T.CFG["n_positions"], max_batch_size=16)
+    model(toks[:P - 1])
+    step_logits = []
+    for i in range(P - 1, len(toks) - 1):
+        h = model._decode_step_fixed_cache(toks[i], i, i + 1)
+        step_logits.append(f32(model.get_logits(h).to_numpy())[0])
+    step_logits = np.stack(step_logits)
+    err = np.abs(step_logits - g["logits_teacher_forced"]).max()
+    assert err <= 2e-2 * scale, f"logit error {err} vs scale {scale}"
+    am = step_logits.argmax(-1)
+    assert np.array_equal(am[clear], g["argmax_teacher_forced"][clear])
+    # the batch path's last slab agrees with the single-token path on the same rows
+    slab_logits = f32(model.get_logits(hidden).to_numpy())
+    assert np.abs(slab_logits - step_logits[-n_last:]).max() <= 2e-2 * scale
+
+    # (3) free greedy generation, device-resident graph replay and eager
+    for use_graph in (True, False):
+        model.init_decode(T.CFG["n_positions"], max_batch_size=16)
+        got = model.generate(list(T.PROMPT), T.N_NEW, temperature=0.0, use_graph=use_graph)
+        agreed = 0
+        for i in range(T.N_NEW):
+            if got[P + i] != toks[P + i]:
+                assert not clear[i], f"step {i}: got {got[P + i]}, reference {toks[P + i]}, margin {g['margins'][i]}"
+                break
+            agreed += 1
+        assert agreed >= 3, agreed
+
+
+def test_gpt2_position_table_bound():
+    model, T = _gpt2_tiny_model()
+    with pytest.raises(ValueError):
+        model._decode_step_fixed_cache_batch([1, 2, 3], T.CFG["n_positions"] - 1, T.CFG["n_positions"])
+
+
+def test_gpt2_small_full_size_graph_equals_eager():
+    """BASELINE.json configs[0] at its full size on the GPU path: GPT-2 small (124M, random init), 128-token prompt +
+    128 greedy tokens; the device-resident graph replay and the eager per-op path give the same tokens."""
+    model = llm.build_random_model("gpt2", "bf16", max_seq=1024, seed=3, std=0.02)
+    assert model.config.num_layers == 12 and model.config.hidden_size == 768 and model.position_embed.shape == (1024, 768)
+    rng = np.random.default_rng(9)
+    prompt = [int(t) for t in rng.integers(0, model.config.vocab_size, 128)]
+    model.init_decode(1024, max_batch_size=64)
+    a = model.generate(prompt, 128, temperature=0.0, use_graph=True)
+    assert len(a) == 256 and all(0 <= t < model.config.vocab_size for t in a)
+    model.init_decode(1024, max_batch_size=64)
+    b = model.generate(prompt, 32, temperature=0.0, use_graph=False)
+    assert a[:160] == b
