@@ -100,12 +100,13 @@ int pgk_gemv_fp8_bf16_ex(const void* A, const void* B_nk, const void* S, void* C
 int pgk_gemv_fp8_swiglu_bf16(const void* A, const void* Wg_nk, const void* Sg, const void* Wu_nk,
                              const void* Su, void* C, int M, int K, int N, void* stream);
 
-/* Decode batch 16..64 on the tensor cores (tcgen05.mma kind::f16, BF16 x BF16 -> F32 in TMEM): same operands
+/* Decode batch 5..64 on the tensor cores (tcgen05.mma kind::f16, BF16 x BF16 -> F32 in TMEM): same operands
  * and epilogues as pgk_gemv_fp8_bf16_ex; the weights are read ONCE for all M rows, converted exactly to BF16
  * on the way into shared memory, the 128x128 block scale is folded into the activation slab (rounded to BF16
- * where the reference rounds weight*scale, w8a16_gemm.cu:104-339).  Needs 16 <= M <= 64, K % 128 == 0,
- * N % 128 == 0.  pgk_gemv_fp8_bf16(_ex) dispatch here by themselves when the shape allows
- * (replaces gemv_fp8_bf16_batched for M >= 16, fp8_opt.cuh:220-295, and w8a16_gemm_sm120's mma.sync path). */
+ * where the reference rounds weight*scale, w8a16_gemm.cu:104-339).  Needs 1 <= M <= 64 (rows up to the MMA
+ * width 16/32/64 are zero-filled), K % 128 == 0, N % 128 == 0.  pgk_gemv_fp8_bf16(_ex) dispatch here by
+ * themselves for M >= 5 (measured crossover against the CUDA-core slab GEMV; env PGK_TC_MIN_M) when the shape
+ * allows (replaces gemv_fp8_bf16_batched, fp8_opt.cuh:220-295, and w8a16_gemm_sm120's mma.sync path). */
 int pgk_gemm_fp8_bf16_tc(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N,
                          const void* bias, const void* residual, void* stream);
 

@@ -1,6 +1,6 @@
 // gemm_tc.cu -- W8A16 skinny GEMM for decode batch 16..64 on the 5th-gen tensor cores (tcgen05 + TMEM).
 //
-//   C[M,N] = A[M,K] . dequant(B[N,K])^T     B = FP8-E4M3 codes [N,K], S = bf16 [N/128, K/128], 16 <= M <= 64
+//   C[M,N] = A[M,K] . dequant(B[N,K])^T     B = FP8-E4M3 codes [N,K], S = bf16 [N/128, K/128], 1 <= M <= 64 (used for M >= 5)
 //
 // replaces gemv_fp8_warp_reduce_vec4_batched_kernel (fp8_opt.cuh:220-295, re-reads the weights M times) and
 // the M >= 16 tensor-core path of pygpukit_w8a16_gemm_sm120 (w8a16_gemm.cu:104-339: dequantise to BF16 in
@@ -16,9 +16,11 @@
 //     four raw blocks = 64 KB in flight per SM, requested before the dependency wait), are converted exactly to BF16
 //     (F2FP.F16.E4M3.UNPACK_B -> f32 -> BF16x2 pack; E4M3 fits BF16) and stored to shared memory in the
 //     canonical no-swizzle K-major core-matrix layout; the [M,128] activation slab is multiplied by the block
-//     scale, rounded to BF16 (the reference rounds weight*scale to BF16 instead: same 2^-9 relative step) and
-//     stored in the same layout.
-//   * one elected thread issues 8 x tcgen05.mma.kind::f16 (128 x NB x 16, BF16 in, F32 accumulate in TMEM)
+//     scale in f32 and split into TWO BF16 terms, hi = bf16(a*s) and lo = bf16(a*s - hi), stored in the same
+//     layout: with exact BF16 weights the two MMAs reproduce the f32 product a*s*w to ~2^-17, i.e. the
+//     FP32-accumulate class of the CUDA-core GEMV (the reference's tensor-core path rounds weight*scale to BF16
+//     once, a 2^-9 step).  The second MMA is free: the kernel is bound by the weight stream, not the tensor pipe.
+//   * one elected thread issues 2 x 8 x tcgen05.mma.kind::f16 (128 x NB x 16, BF16 in, F32 accumulate in TMEM)
 //     per k block from shared-memory descriptors, then tcgen05.commit -> mbarrier releases the stage; two
 //     BF16 operand stages per CTA, one CTA per SM.
 //   * epilogue: tcgen05.ld 32x32b -> registers, [split-K partials folded in split order by the last-arriving
@@ -30,7 +32,7 @@ namespace pgk {
 
 constexpr int kTcRows = 128;      // weight rows per CTA = MMA M
 constexpr int kTcBK = 128;        // k block = FP8 scale block
-constexpr int kTcThreads = 512;    // 16 warps: the FP8 -> BF16 conversion is CUDA-core work and needs the warps to hide its latencies
+constexpr int kTcThreads = 512;    // 16 converter warps (+ one MMA-issuing warp per CTA): the FP8 -> BF16 conversion is CUDA-core work and needs the warps to hide its latencies
 constexpr int kTcStages = 2;      // BF16 operand stages (tensor-core side)
 constexpr int kTcRaw = 3;         // raw FP8 weight blocks / activation slabs in flight (cp.async rings)
 
@@ -92,13 +94,14 @@ __device__ __forceinline__ void e4m3x4_to_bf16x4(uint32_t w, uint32_t& lo, uint3
 }
 
 template <int NB>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kTcThreads + 32, 1)
 gemm_fp8_tc_kernel(TcParams p) {
     constexpr int NW = kTcThreads / 32;
     constexpr int WI = 32 / NW;                   // weight items per thread per k block (8 rows x 64 B each per warp)
     constexpr int AI = (NB / 2 + NW - 1) / NW;    // activation items per thread per k block (copy: 2 rows per warp)
     constexpr uint32_t A_STAGE = kTcRows * kTcBK * 2;      // 32 KB of BF16 weights
-    constexpr uint32_t B_STAGE = NB * kTcBK * 2;           // <= 16 KB of BF16 activations
+    constexpr uint32_t B_HALF = NB * kTcBK * 2;            // one BF16 activation tile (<= 16 KB)
+    constexpr uint32_t B_STAGE = 2 * B_HALF;               // hi + lo terms of activation * block scale
     constexpr uint32_t TMEM_COLS = NB < 32 ? 32 : NB;
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) uint64_t mma_bar[kTcStages];
@@ -153,15 +156,16 @@ gemm_fp8_tc_kernel(TcParams p) {
         }
     };
 #pragma unroll
+    const bool conv = warp < NW;                  // 16 converter warps; warp NW only issues the MMAs
     for (int d = 0; d < kTcRaw; ++d) {
-        if (d < nkb) issue_weights(kb0 + d, d);
+        if (conv && d < nkb) issue_weights(kb0 + d, d);
         asm volatile("cp.async.commit_group;" ::: "memory");   // one group per block, empty ones included
     }
     griddep_wait();
     griddep_launch();
 #pragma unroll
     for (int d = 0; d < kTcRaw; ++d) {
-        if (d < nkb) issue_acts(kb0 + d, d);
+        if (conv && d < nkb) issue_acts(kb0 + d, d);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
     asm volatile("cp.async.wait_group %0;" :: "n"(kTcRaw - 1) : "memory");       // block 0 (weights + slab) landed
@@ -179,64 +183,73 @@ gemm_fp8_tc_kernel(TcParams p) {
         const unsigned char* rw = raw_w + (size_t)rs * (kTcRows * kTcBK);
         const unsigned char* ra = raw_a + (size_t)rs * (NB * kTcBK * 2);
         const float sc = bf16_bits_to_f32(__ldg(p.S + (size_t)(n0 >> 7) * SK + kb));
-        uint4 wq[WI], aq[AI];
+        if (conv) {
+            uint4 wq[WI], aq[AI];
 #pragma unroll
-        for (int i = 0; i < WI; ++i) {
-            const int q = i * NW + warp;                      // 32 items: row group q>>1, 64-byte half q&1
-            const int r = 8 * (q >> 1) + rr, pc = (q & 1) * 4 + piece;
-            wq[i] = *reinterpret_cast<const uint4*>(rw + r * 128 + ((pc ^ rr) * 16));
-        }
-#pragma unroll
-        for (int i = 0; i < AI; ++i) {
-            const int q = i * NW + warp;                      // NB/2 items: row group q>>2, 64-byte quarter q&3
-            if (q < NB / 2) {
-                const int m = 8 * (q >> 2) + rr, pc = (q & 3) * 4 + piece;
-                aq[i] = *reinterpret_cast<const uint4*>(ra + m * 256 + ((pc ^ rr) * 16));
+            for (int i = 0; i < WI; ++i) {
+                const int q = i * NW + warp;                      // 32 items: row group q>>1, 64-byte half q&1
+                const int r = 8 * (q >> 1) + rr, pc = (q & 1) * 4 + piece;
+                wq[i] = *reinterpret_cast<const uint4*>(rw + r * 128 + ((pc ^ rr) * 16));
             }
-        }
-        // the MMAs that read this BF16 stage two iterations ago must have completed
-        if (it >= kTcStages) mbar_wait(&mma_bar[st], (uint32_t)(((it >> 1) - 1) & 1));
-        // weights: 16 codes -> 16 bf16 = k chunks c0, c0 + 1 of row r
 #pragma unroll
-        for (int i = 0; i < WI; ++i) {
-            const int q = i * NW + warp;
-            const int c0 = (q & 1) * 8 + piece * 2;
-            unsigned char* dst = a_s + (size_t)c0 * (kTcRows * 16) + (size_t)(q >> 1) * 128 + rr * 16;
-            uint4 o0, o1;
-            e4m3x4_to_bf16x4(wq[i].x, o0.x, o0.y); e4m3x4_to_bf16x4(wq[i].y, o0.z, o0.w);
-            e4m3x4_to_bf16x4(wq[i].z, o1.x, o1.y); e4m3x4_to_bf16x4(wq[i].w, o1.z, o1.w);
-            *reinterpret_cast<uint4*>(dst) = o0;
-            *reinterpret_cast<uint4*>(dst + kTcRows * 16) = o1;
-        }
-        // activations: 8 bf16 x block scale -> bf16, k chunk c of batch row m
-#pragma unroll
-        for (int i = 0; i < AI; ++i) {
-            const int q = i * NW + warp;
-            if (q < NB / 2) {
-                const int c = (q & 3) * 4 + piece;
-                unsigned char* dst = b_s + (size_t)c * (NB * 16) + (size_t)(q >> 2) * 128 + rr * 16;
-                uint4 o;
-                o.x = pack_bf16x2(bf16lo(aq[i].x) * sc, bf16hi(aq[i].x) * sc);
-                o.y = pack_bf16x2(bf16lo(aq[i].y) * sc, bf16hi(aq[i].y) * sc);
-                o.z = pack_bf16x2(bf16lo(aq[i].z) * sc, bf16hi(aq[i].z) * sc);
-                o.w = pack_bf16x2(bf16lo(aq[i].w) * sc, bf16hi(aq[i].w) * sc);
-                *reinterpret_cast<uint4*>(dst) = o;
+            for (int i = 0; i < AI; ++i) {
+                const int q = i * NW + warp;                      // NB/2 items: row group q>>2, 64-byte quarter q&3
+                if (q < NB / 2) {
+                    const int m = 8 * (q >> 2) + rr, pc = (q & 3) * 4 + piece;
+                    aq[i] = *reinterpret_cast<const uint4*>(ra + m * 256 + ((pc ^ rr) * 16));
+                }
             }
+            // the MMAs that read this BF16 stage two iterations ago must have completed
+            if (it >= kTcStages) mbar_wait(&mma_bar[st], (uint32_t)(((it >> 1) - 1) & 1));
+            // weights: 16 codes -> 16 bf16 = k chunks c0, c0 + 1 of row r
+#pragma unroll
+            for (int i = 0; i < WI; ++i) {
+                const int q = i * NW + warp;
+                const int c0 = (q & 1) * 8 + piece * 2;
+                unsigned char* dst = a_s + (size_t)c0 * (kTcRows * 16) + (size_t)(q >> 1) * 128 + rr * 16;
+                uint4 o0, o1;
+                e4m3x4_to_bf16x4(wq[i].x, o0.x, o0.y); e4m3x4_to_bf16x4(wq[i].y, o0.z, o0.w);
+                e4m3x4_to_bf16x4(wq[i].z, o1.x, o1.y); e4m3x4_to_bf16x4(wq[i].w, o1.z, o1.w);
+                *reinterpret_cast<uint4*>(dst) = o0;
+                *reinterpret_cast<uint4*>(dst + kTcRows * 16) = o1;
+            }
+            // activations: 8 bf16 x block scale -> bf16, k chunk c of batch row m
+#pragma unroll
+            for (int i = 0; i < AI; ++i) {
+                const int q = i * NW + warp;
+                if (q < NB / 2) {
+                    const int c = (q & 3) * 4 + piece;
+                    unsigned char* dst = b_s + (size_t)c * (NB * 16) + (size_t)(q >> 2) * 128 + rr * 16;
+                    const uint32_t aw[4] = {aq[i].x, aq[i].y, aq[i].z, aq[i].w};
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float v0 = bf16lo(aw[j]) * sc, v1 = bf16hi(aw[j]) * sc;   // exact-ish f32 (8 x 8 bit product)
+                        hi[j] = pack_bf16x2(v0, v1);
+                        lo[j] = pack_bf16x2(v0 - bf16lo(hi[j]), v1 - bf16hi(hi[j]));    // residual of the BF16 rounding
+                    }
+                    *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    *reinterpret_cast<uint4*>(dst + B_HALF) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+            }
+            fence_proxy_async();          // generic-proxy smem writes -> visible to the tensor core (async proxy)
+            asm volatile("cp.async.wait_group %0;" :: "n"(kTcRaw - 2) : "memory");   // this thread's part of block it+1 landed
         }
-        fence_proxy_async();              // generic-proxy smem writes -> visible to the tensor core (async proxy)
-        asm volatile("cp.async.wait_group %0;" :: "n"(kTcRaw - 2) : "memory");   // this thread's part of block it+1 landed
         __syncthreads();                  // BF16 stage complete; raw slot `rs` fully read; block it+1 visible to all
-        // refill the raw slot that every thread has finished reading, keep the group count uniform
-        if (it + kTcRaw < nkb) { issue_weights(kb + kTcRaw, rs); issue_acts(kb + kTcRaw, rs); }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        if (tid == 0) {
+        if (conv) {
+            // refill the raw slot that every thread has finished reading, keep the group count uniform
+            if (it + kTcRaw < nkb) { issue_weights(kb + kTcRaw, rs); issue_acts(kb + kTcRaw, rs); }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        } else if (lane == 0) {           // the MMA warp: off the converters' critical path
             tc_fence_after();
             const uint32_t a_addr = smem_u32(a_s), b_addr = smem_u32(b_s);
 #pragma unroll
             for (int ks = 0; ks < kTcBK / 16; ++ks) {
                 const uint64_t da = umma_desc(a_addr + ks * 2 * (kTcRows * 16), kTcRows * 16, 128);
                 const uint64_t db = umma_desc(b_addr + ks * 2 * (NB * 16), NB * 16, 128);
+                const uint64_t dl = umma_desc(b_addr + B_HALF + ks * 2 * (NB * 16), NB * 16, 128);
                 umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+                umma_bf16(tmem_d, da, dl, idesc, 1u);
             }
             umma_commit(&mma_bar[st]);    // arrives when every MMA issued so far has completed
         }
@@ -288,7 +301,7 @@ gemm_fp8_tc_kernel(TcParams p) {
     if (s_ticket != (unsigned)(p.splits - 1)) return;
     // last CTA of the tile: fold the split-K partials in split order (deterministic), then the epilogue.
     // thread = (weight row, half of the batch rows); the loads of eight splits are issued together.
-    {
+    if (conv) {
         const int r = tid & (kTcRows - 1), half = tid >> 7;      // four batch-row phases with 512 threads
         const float* base = p.ws + (size_t)tile * p.splits * NB * kTcRows;
         const int nn = n0 + r;
@@ -345,26 +358,41 @@ static int launch_tc(TcParams p, cudaStream_t st) {
     p.splits = splits;
     p.ws = g_tc_ws;
     p.counters = g_tc_cnt;
-    constexpr size_t kSmem = (size_t)kTcStages * (kTcRows * kTcBK * 2 + NB * kTcBK * 2) +
+    constexpr size_t kSmem = (size_t)kTcStages * (kTcRows * kTcBK * 2 + 2 * NB * kTcBK * 2) +
                              (size_t)kTcRaw * (kTcRows * kTcBK + NB * kTcBK * 2);
     static bool attr_set = false;
     if (!attr_set) {
         PGK_CUDA(cudaFuncSetAttribute(gemm_fp8_tc_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
         attr_set = true;
     }
-    PGK_CUDA(launch(gemm_fp8_tc_kernel<NB>, dim3(tiles, splits), dim3(kTcThreads), kSmem, st, p));
+    PGK_CUDA(launch(gemm_fp8_tc_kernel<NB>, dim3(tiles, splits), dim3(kTcThreads + 32), kSmem, st, p));
     return 0;
 }
 
+bool gemm_fp8_tc_shape_ok(int M, int K, int N, const void* A, const void* B);
+
+// Smallest batch sent to the tensor cores.  The kernel zero-fills rows M..NB-1, so any M >= 1 works; the crossover
+// against the CUDA-core slab GEMV (whose time grows linearly with M: dequant + M FMAs per weight) measured on
+// B200 is between M = 4 (15.9 us GEMV vs ~16 us here, qkv shape) and M = 5.  PGK_TC_MIN_M overrides (A/B timing).
+int gemm_fp8_tc_min_m() {
+    static const int v = [] { const char* e = getenv("PGK_TC_MIN_M"); int m = e ? atoi(e) : 5; return m < 1 ? 1 : m; }();
+    return v;
+}
+
+// the dispatcher's test (batch >= crossover); the kernel itself takes any 1 <= M <= 64
 bool gemm_fp8_tc_eligible(int M, int K, int N, const void* A, const void* B) {
-    return M >= 16 && M <= 64 && K % kTcBK == 0 && N % kTcRows == 0 && N / kTcRows <= kTcMaxTiles &&
+    return M >= gemm_fp8_tc_min_m() && gemm_fp8_tc_shape_ok(M, K, N, A, B);
+}
+
+bool gemm_fp8_tc_shape_ok(int M, int K, int N, const void* A, const void* B) {
+    return M >= 1 && M <= 64 && K % kTcBK == 0 && N % kTcRows == 0 && N / kTcRows <= kTcMaxTiles &&
            ((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0);
 }
 
 int gemm_fp8_tc(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N, const void* bias,
                 const void* residual, cudaStream_t st) {
-    PGK_REQUIRE(gemm_fp8_tc_eligible(M, K, N, A, B_nk),
-                "gemm_fp8_tc failed: needs 16 <= M <= 64, K %% 128 == 0, N %% 128 == 0 and 16-byte aligned pointers "
+    PGK_REQUIRE(gemm_fp8_tc_shape_ok(M, K, N, A, B_nk),
+                "gemm_fp8_tc failed: needs 1 <= M <= 64, K %% 128 == 0, N %% 128 == 0 and 16-byte aligned pointers "
                 "(M=%d K=%d N=%d)", M, K, N);
     TcParams p = {};
     p.A = (const uint16_t*)A; p.B = (const uint8_t*)B_nk; p.S = (const uint16_t*)S; p.C = (uint16_t*)C;

@@ -390,7 +390,7 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
     PGK_REQUIRE(!gamma || (fast && K >= 512 && aligned16(gamma)),
                 "rmsnorm_gemv_fp8_bf16 failed: the fused norm needs K %% 32 == 0, K >= 512 and aligned pointers (K=%d)", K);
     const PrefetchHint hint = take_prefetch_hint();   // one-shot, whichever path runs
-    // decode batch >= 16: the weight-streaming tensor-core GEMM (PGK_TC=0 keeps the slab GEMV for A/B timing)
+    // decode batch >= 5 (PGK_TC_MIN_M): the weight-streaming tensor-core GEMM (PGK_TC=0 keeps the slab GEMV for A/B timing)
     static const bool tc_on = !(getenv("PGK_TC") && atoi(getenv("PGK_TC")) == 0);
     if (tc_on && !swiglu && !gamma && gemm_fp8_tc_eligible(M, K, N, A, B0))
         return gemm_fp8_tc(A, B0, S0, C, M, K, N, bias, residual, st);

@@ -77,6 +77,10 @@ def hint_next(regions) -> None:
     api.prefetch_hint(ptrs, sizes, len(regs))
 
 
+# smallest batch served by the tcgen05 skinny GEMM (same default and override as gemm_tc.cu: measured crossover)
+TC_MIN_M = max(1, int(os.environ.get("PGK_TC_MIN_M", "5")))
+
+
 def can_fuse_norm(norm, in_features: int) -> bool:
     """RMSNorm (no bias) can be folded into the GEMV's activation staging (pgk_rmsnorm_gemv_*)."""
     return (norm is not None and getattr(norm, "norm_type", None) == "rmsnorm" and norm.bias is None
@@ -156,8 +160,8 @@ class LinearFP8:
 
     def uses_tensor_cores(self, M: int) -> bool:
         """True when a batch of M rows is served by the tcgen05 skinny GEMM (pgk_gemm_fp8_bf16_tc) instead of
-        the CUDA-core GEMV: 16 <= M <= 64 and 128-aligned shapes (every model shape of BASELINE.json)."""
-        return (16 <= M <= 64 and self.in_features % 128 == 0 and self.out_features % 128 == 0
+        the CUDA-core GEMV: TC_MIN_M <= M <= 64 and 128-aligned shapes (every model shape of BASELINE.json)."""
+        return (TC_MIN_M <= M <= 64 and self.in_features % 128 == 0 and self.out_features % 128 == 0
                 and os.environ.get("PGK_TC", "1") != "0")
 
     def _dequantize_cpu(self) -> np.ndarray:
@@ -171,7 +175,7 @@ class LinearFP8:
         M = x.shape[0]
         y = _out2d(out, M, self.out_features)
         if norm is not None and self.uses_tensor_cores(M):
-            # batch >= 16 goes to the tcgen05 GEMM, which takes plain activations: normalise first (cached scratch)
+            # batch >= TC_MIN_M goes to the tcgen05 GEMM, which takes plain activations: normalise first (cached scratch)
             sc = self._norm_scratch.get(M)
             if sc is None:
                 sc = self._norm_scratch[M] = GPUArray((M, self.in_features), bfloat16)

@@ -85,7 +85,7 @@ class MLP:
             out = GPUArray((M, I), bfloat16)
         if (self.gate_up_proj is None and isinstance(self.gate_proj, LinearFP8) and isinstance(self.up_proj, LinearFP8)
                 and self.gate_proj.uses_tensor_cores(M) and self.up_proj.uses_tensor_cores(M)):
-            # batch >= 16: gate and up on the tcgen05 GEMM, then silu -> mul with the layer path's two roundings
+            # batch >= TC_MIN_M: gate and up on the tcgen05 GEMM, then silu -> mul with the layer path's two roundings
             if norm is not None:
                 xs = self._scratch.get(("x", M))
                 if xs is None:

@@ -29,7 +29,7 @@ for label, K, N in shapes:
         s = gk.empty((N // 128, K // 128), gk.bfloat16)
         api.fill_normal_bf16(s.device_ptr, s.size, 900 + i, 0.01, None)
         Ss.append(s)
-    for M in (1, 4, 8, 16, 32, 64):
+    for M in (1, 2, 4, 5, 8, 12, 16, 32, 64):
         a = gk.empty((M, K), gk.bfloat16)
         api.fill_normal_bf16(a.device_ptr, a.size, 7, 1.0, None)
         c = gk.empty((M, N), gk.bfloat16)

@@ -34,15 +34,25 @@ def test_gemv_fp8_vs_oracle(K, N, M):
         out = ops.gemv_fp8_bf16(gk.from_numpy(A[0]), gB, gS).to_numpy()[None]
     else:
         out = ops.gemv_fp8_bf16_batched(gk.from_numpy(A), gB, gS).to_numpy()
+    if M >= 5 and K % 128 == 0 and N % 128 == 0:
+        # tcgen05 path (pgk_gemm_fp8_bf16_tc): exact BF16 weights x (hi + lo) BF16 split of activation*scale, f32
+        # accumulation in TMEM.  The result is f32-accumulate class, but its ~2^-17 residual flips a BF16 output
+        # rounding now and then, and ONE flip of a large element is already 4e-3..8e-3 of max|ref|: the bar is
+        # <= 1 BF16 ulp on every significant element, few flips, and the BF16 bar on the max-norm error.
+        big = np.abs(f32(ref)) > np.abs(f32(ref)).max() / 64
+        assert ulp_diff_bf16(out[big], ref[big]) <= 1
+        assert rel_err(out, ref) < 1e-2
+        assert np.mean(out != ref) < 0.02
+        return
     assert rel_err(out, ref) < TOL
     assert ulp_diff_bf16(out, ref) <= 64          # near-zero outputs may differ by many ulps; most by <= 1
     assert np.mean(out != ref) < 0.05             # f32 reordering flips few bf16 roundings
 
 
 @pytest.mark.parametrize("K,N", [(4096, 4096), (1024, 256), (12288, 1024), (128, 128), (2048, 768), (256, 6144)])
-@pytest.mark.parametrize("M", [16, 17, 32, 50, 64])
+@pytest.mark.parametrize("M", [1, 5, 8, 13, 16, 17, 32, 50, 64])
 def test_gemm_fp8_tc_vs_oracle(K, N, M):
-    """Decode batch 16..64 on tcgen05 (pgk_gemm_fp8_bf16_tc, reached through gemv_fp8_bf16_batched) vs the
+    """Decode batch (1..)5..64 on tcgen05 (pgk_gemm_fp8_bf16_tc, reached through gemv_fp8_bf16_batched) vs the
     oracle's FP8 GEMV (f32 weights x bf16 activations).  The block scale is folded into the activations and
     rounded to BF16 (the reference's M >= 16 path rounds weight*scale to BF16 instead, w8a16_gemm.cu:104-339):
     BF16-operand tolerance 1e-2 (north_star); and the slab GEMV (PGK_TC=0 semantics, M rows in slabs of 4)
@@ -62,9 +72,13 @@ def test_gemm_fp8_tc_vs_oracle(K, N, M):
     # typical error is far below the bar: the mean relative deviation over the outputs stays under 2e-3
     d = np.abs(f32(got).astype(np.float64) - f32(ref).astype(np.float64))
     assert d.mean() / np.abs(f32(ref).astype(np.float64)).mean() < 4e-3
-    # the public batched entry dispatches to the same kernel
+    # the public batched entry dispatches to the same kernel from the measured crossover (M >= 5) up; below it
+    # the CUDA-core GEMV answers, to the same bar
     out2 = ops.gemv_fp8_bf16_batched(gA, gB, gS).to_numpy()
-    assert np.array_equal(out2, got)
+    if M >= 5:
+        assert np.array_equal(out2, got)
+    else:
+        assert rel_err(out2, ref) < 1e-2 and rel_err(out2, got) < 1e-2
     # epilogues: bias + residual with the reference's rounding points
     bias, res = rand_bf16(rng, (N,), 0.1), rand_bf16(rng, (M, N), 0.5)
     gb, gr = gk.from_numpy(bias), gk.from_numpy(res)

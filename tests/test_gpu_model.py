@@ -74,23 +74,29 @@ def test_decode_m1_logits_vs_oracle(name, fmt):
     assert int(model.buffers.next_token.to_numpy()[0]) == int(np.argmax(f32(lg)))
 
 
-def test_batch_decode_equals_single_steps():
-    """DecodeBatch: M consecutive tokens in one call == M single-token steps (same cache contents)."""
+@pytest.mark.parametrize("M", [4, 8])
+def test_batch_decode_equals_single_steps(M):
+    """DecodeBatch: M consecutive tokens in one call == M single-token steps (same cache contents).  M = 4 stays on
+    the CUDA-core GEMV (same arithmetic as M = 1: the layer-0 cache is a bit-exact copy); M = 8 runs the
+    projections on the tcgen05 GEMM (BF16 operands), compared at the BF16 bar."""
     model = _build("tiny-qwen3", "fp8")
     rng = np.random.default_rng(6)
-    toks = [int(t) for t in rng.integers(0, model.config.vocab_size, 8)]
+    toks = [int(t) for t in rng.integers(0, model.config.vocab_size, M)]
     single = []
     for pos, t in enumerate(toks):
         single.append(model._decode_step_fixed_cache(t, pos, pos + 1).to_numpy()[0].copy())
     model_b = _build("tiny-qwen3", "fp8")
-    b = llm.DecodeBatch(8)
+    b = llm.DecodeBatch(M)
     b.bind(model_b)
     h = b.step_batch(toks, 0, len(toks), None).to_numpy()
     for i in range(len(toks)):
         assert rel_err(h[i], single[i]) < 1e-2
     k1 = model.blocks[0].attn._k_cache.to_numpy()
     k2 = model_b.blocks[0].attn._k_cache.to_numpy()
-    assert np.array_equal(k1[:, :len(toks)], k2[:, :len(toks)])      # layer-0 cache: bit-exact copy path
+    if M <= 4:
+        assert np.array_equal(k1[:, :len(toks)], k2[:, :len(toks)])      # layer-0 cache: bit-exact copy path
+    else:
+        assert rel_err(k2[:, :len(toks)], k1[:, :len(toks)]) < 1e-2
 
 
 def test_fp8_device_quantiser_matches_host():
