@@ -41,9 +41,19 @@ cudaError_t pygpukit_grouped_gemm_fp8_bf16(const void*, const void*, const void*
 }
 
 using bf16 = __nv_bfloat16;
-static inline int done() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess) return (int)e; return (int)cudaDeviceSynchronize(); }
+// every entry synchronises (the reference's bindings end with cuCtxSynchronize, native/ops/common/error.cuh:28-37);
+// ref_set_sync(0) leaves the launches asynchronous on the default stream so that scripts/bench_vs_reference.py
+// can time them with CUDA events exactly like our own kernels
+static int g_sync = 1;
+static inline int done() {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    return g_sync ? (int)cudaDeviceSynchronize() : 0;
+}
 
 extern "C" {
+
+void ref_set_sync(int on) { g_sync = on; }
 
 int ref_gemv_fp8(const void* A, const void* B, const void* S, void* C, int K, int N) {
     cudaError_t e = pygpukit::ops::gemv::launch_gemv_fp8_opt((const bf16*)A, (const uint8_t*)B, (const bf16*)S, (bf16*)C, K, N, 0);

@@ -34,6 +34,11 @@ def _p(a):
     return C.c_void_p(a.device_ptr)
 
 
+def set_sync(on: bool) -> None:
+    """False: launches stay asynchronous on the default stream (event timing); True: every call synchronises."""
+    lib().ref_set_sync(1 if on else 0)
+
+
 def gemv_fp8(A, B, S, Cout, K, N):
     _chk(lib().ref_gemv_fp8(_p(A), _p(B), _p(S), _p(Cout), K, N), "ref_gemv_fp8")
 

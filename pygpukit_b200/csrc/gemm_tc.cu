@@ -33,8 +33,11 @@ namespace pgk {
 constexpr int kTcRows = 128;      // weight rows per CTA = MMA M
 constexpr int kTcBK = 128;        // k block = FP8 scale block
 constexpr int kTcThreads = 512;    // 16 converter warps (+ one MMA-issuing warp per CTA): the FP8 -> BF16 conversion is CUDA-core work and needs the warps to hide its latencies
+constexpr int kTcMaxKb = 256;     // k blocks per CTA (K <= 32768)
 constexpr int kTcStages = 2;      // BF16 operand stages (tensor-core side)
-constexpr int kTcRaw = 3;         // raw FP8 weight blocks / activation slabs in flight (cp.async rings)
+// raw FP8 weight blocks / activation slabs in flight per CTA (cp.async rings): as deep as 227 KB of shared memory
+// allows next to the two BF16 operand stages -- the ring depth is what keeps HBM requests in flight while the CTA converts
+__host__ __device__ constexpr int tc_raw_depth(int nb) { return nb <= 16 ? 6 : (nb <= 32 ? 5 : 3); }
 
 struct TcParams {
     const uint16_t* A; const uint8_t* B; const uint16_t* S; uint16_t* C;
@@ -97,6 +100,7 @@ template <int NB>
 __global__ void __launch_bounds__(kTcThreads + 32, 1)
 gemm_fp8_tc_kernel(TcParams p) {
     constexpr int NW = kTcThreads / 32;
+    constexpr int kTcRaw = tc_raw_depth(NB);
     constexpr int WI = 32 / NW;                   // weight items per thread per k block (8 rows x 64 B each per warp)
     constexpr int AI = (NB / 2 + NW - 1) / NW;    // activation items per thread per k block (copy: 2 rows per warp)
     constexpr uint32_t A_STAGE = kTcRows * kTcBK * 2;      // 32 KB of BF16 weights
@@ -107,6 +111,7 @@ gemm_fp8_tc_kernel(TcParams p) {
     __shared__ __align__(8) uint64_t mma_bar[kTcStages];
     __shared__ uint32_t tmem_base_s;
     __shared__ unsigned s_ticket;
+    __shared__ float sc_s[kTcMaxKb];              // this CTA's block scales (one per k block), staged once
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x, split = blockIdx.y;
@@ -118,6 +123,8 @@ gemm_fp8_tc_kernel(TcParams p) {
     const int SK = nkb_total;                     // scale row length (K % 128 == 0)
     const int rr = lane & 7, piece = lane >> 3;
 
+    // block scales are weights: staged before the dependency wait, off the per-block critical path
+    for (int i = tid; i < nkb; i += blockDim.x) sc_s[i] = bf16_bits_to_f32(__ldg(p.S + (size_t)(n0 >> 7) * SK + kb0 + i));
     if (warp == 0) tmem_alloc(&tmem_base_s, TMEM_COLS);
     if (tid == 0) {
 #pragma unroll
@@ -182,7 +189,7 @@ gemm_fp8_tc_kernel(TcParams p) {
         unsigned char* b_s = a_s + A_STAGE;
         const unsigned char* rw = raw_w + (size_t)rs * (kTcRows * kTcBK);
         const unsigned char* ra = raw_a + (size_t)rs * (NB * kTcBK * 2);
-        const float sc = bf16_bits_to_f32(__ldg(p.S + (size_t)(n0 >> 7) * SK + kb));
+        const float sc = sc_s[it];
         if (conv) {
             uint4 wq[WI], aq[AI];
 #pragma unroll
@@ -359,7 +366,7 @@ static int launch_tc(TcParams p, cudaStream_t st) {
     p.ws = g_tc_ws;
     p.counters = g_tc_cnt;
     constexpr size_t kSmem = (size_t)kTcStages * (kTcRows * kTcBK * 2 + 2 * NB * kTcBK * 2) +
-                             (size_t)kTcRaw * (kTcRows * kTcBK + NB * kTcBK * 2);
+                             (size_t)tc_raw_depth(NB) * (kTcRows * kTcBK + NB * kTcBK * 2);
     static bool attr_set = false;
     if (!attr_set) {
         PGK_CUDA(cudaFuncSetAttribute(gemm_fp8_tc_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
@@ -385,7 +392,7 @@ bool gemm_fp8_tc_eligible(int M, int K, int N, const void* A, const void* B) {
 }
 
 bool gemm_fp8_tc_shape_ok(int M, int K, int N, const void* A, const void* B) {
-    return M >= 1 && M <= 64 && K % kTcBK == 0 && N % kTcRows == 0 && N / kTcRows <= kTcMaxTiles &&
+    return M >= 1 && M <= 64 && K / kTcBK <= kTcMaxKb && K % kTcBK == 0 && N % kTcRows == 0 && N / kTcRows <= kTcMaxTiles &&
            ((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0);
 }
 

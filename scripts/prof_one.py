@@ -1,5 +1,5 @@
 """Launch ONE op of the decode step a few times (for `ncu --set full -k regex:<kernel>`):
-    python scripts/prof_one.py sdpa|fattn|qkv|oproj|gateup|down|rope [model] [format] [context]"""
+    python scripts/prof_one.py sdpa|fattn|qkv|oproj|gateup|down|rope|tc16|tc64 [model] [format] [context]"""
 import os
 import sys
 
@@ -40,6 +40,16 @@ for rep in range(2):
             blk.mlp.gate_up_act(hidden, out=b.mlp_act, norm=blk.mlp_norm)
         elif op == "down":
             blk.mlp.down_proj.forward(b.mlp_act, out=b.partial, residual=hidden)
+        elif op.startswith("tc"):                   # tc16 / tc64: the tcgen05 skinny GEMM on the gate projection weights
+            import pygpukit_b200 as gk
+            Mb = int(op[2:])
+            g = blk.mlp.gate_proj
+            if not hasattr(model, "_tc_x"):
+                model._tc_x = gk.empty((Mb, g.in_features), gk.bfloat16)
+                api.fill_normal_bf16(model._tc_x.device_ptr, model._tc_x.size, 3, 1.0, None)
+                model._tc_y = gk.empty((Mb, g.out_features), gk.bfloat16)
+            api.gemm_fp8_bf16_tc(model._tc_x.device_ptr, g.weight_fp8.device_ptr, g.scale_inv.device_ptr,
+                                 model._tc_y.device_ptr, Mb, g.in_features, g.out_features, None, None, None)
         elif op == "rope":
             api.qk_norm_rope_kv_write(b.qkv_proj_out.device_ptr, None if a.q_norm is None else a.q_norm.weight.device_ptr,
                                       None if a.k_norm is None else a.k_norm.weight.device_ptr, 1e-6, a._cos_dev.device_ptr,
