@@ -305,6 +305,10 @@ int pgk_moe_route_t1(const void* logits, void* weights, int32_t* indices, int32_
 int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, const void* Bu_enk, const void* Su,
                           void* act, const int32_t* row_expert_ids, int k, int K, int N, int expert_offset,
                           int num_local_experts, void* stream);
+/* NVF4 experts: gate/up GEMVs + silu + multiply of the k routed experts in one launch (x broadcast to the k rows) */
+int pgk_moe_gateup_nvf4_t1(const void* x, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
+                           const void* Bu_scale, void* act, const int32_t* row_expert_ids, int k, int K, int N,
+                           int expert_offset, int num_local_experts, void* stream);
 int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
                                 int expert_offset, int num_local_experts, void* stream);

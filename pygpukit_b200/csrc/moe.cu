@@ -210,78 +210,118 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
 // 128-byte line per warp per byte-row), warp w owns scale blocks w, w+32, ... of K; partial sums
 // meet in shared memory and are folded in warp order (deterministic).
 constexpr int kMoeNvf4Warps = 32;
+// NMAT = 1: C[r, :] = A[r, :] . B[e]      NMAT = 2 (decode gate/up pair): C[r, :] = bf16(bf16(silu(g)) * u) with
+// g = bf16(A . Bg[e]), u = bf16(A . Bu[e]) -- the rounding points of gate GEMV -> silu -> up GEMV -> mul_inplace.
+// CPL = columns per lane (4: CTA = 128 columns, 32-bit loads).
+template <int NMAT, int CPL>
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
-moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd,
-                             const uint8_t* __restrict__ Bs, uint16_t* __restrict__ C,
+moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd0,
+                             const uint8_t* __restrict__ Bs0, const uint8_t* __restrict__ Bd1,
+                             const uint8_t* __restrict__ Bs1, uint16_t* __restrict__ C,
                              const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
                              int expert_offset, int num_local) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
-    float* red = a_s + K;                                             // [warps][128]
+    constexpr int TILE = 32 * CPL;
+    float* red = a_s + K;                                             // [NMAT][warps][TILE]
     griddep_wait();
     griddep_launch();
-    const int r = blockIdx.y, col0 = blockIdx.x * 128;
+    const int r = blockIdx.y, col0 = blockIdx.x * TILE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int e = row_expert_ids[r] - expert_offset;
-    const int c = col0 + lane * 4;
+    const int c = col0 + lane * CPL;
     if (e < 0 || e >= num_local) {
         if (warp == 0 && c < N) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) if (c + j < N) C[(size_t)r * N + c + j] = 0;
+            for (int j = 0; j < CPL; ++j) if (c + j < N) C[(size_t)r * N + c + j] = 0;
         }
         return;
     }
     for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * a_stride + k]);
     __syncthreads();
-    const uint8_t* bd = Bd + (size_t)e * (K >> 1) * N;
-    const uint8_t* bs = Bs + (size_t)e * ((K + 31) >> 5) * N;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const uint8_t* bdp[2] = {Bd0 + (size_t)e * (K >> 1) * N, NMAT == 2 ? Bd1 + (size_t)e * (K >> 1) * N : nullptr};
+    const uint8_t* bsp[2] = {Bs0 + (size_t)e * ((K + 31) >> 5) * N, NMAT == 2 ? Bs1 + (size_t)e * ((K + 31) >> 5) * N : nullptr};
+    float acc[NMAT][CPL];
+#pragma unroll
+    for (int m = 0; m < NMAT; ++m)
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) acc[m][j] = 0.f;
     const int KB = K >> 5;
-    const bool full = (c + 3 < N) && ((N & 3) == 0);
+    const bool full = (c + CPL - 1 < N) && ((N & (CPL - 1)) == 0);
     for (int blk = warp; blk < KB; blk += kMoeNvf4Warps) {
-        float part[4] = {0.f, 0.f, 0.f, 0.f};
         if (full) {
-            uint32_t w[16];
+            uint32_t w[NMAT][16], sw[NMAT];
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-                w[i] = __ldg(reinterpret_cast<const uint32_t*>(bd + (size_t)(blk * 16 + i) * N + c));
-            const uint32_t sw = __ldg(reinterpret_cast<const uint32_t*>(bs + (size_t)blk * N + c));
+            for (int m = 0; m < NMAT; ++m) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const float2 a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 2 * i);
-                uint32_t h;
-                float2 f;
-                h = e2m1x2_to_f16x2<0>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                part[0] = fmaf(a.x, f.x, part[0]); part[0] = fmaf(a.y, f.y, part[0]);
-                h = e2m1x2_to_f16x2<1>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                part[1] = fmaf(a.x, f.x, part[1]); part[1] = fmaf(a.y, f.y, part[1]);
-                h = e2m1x2_to_f16x2<2>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                part[2] = fmaf(a.x, f.x, part[2]); part[2] = fmaf(a.y, f.y, part[2]);
-                h = e2m1x2_to_f16x2<3>(w[i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                part[3] = fmaf(a.x, f.x, part[3]); part[3] = fmaf(a.y, f.y, part[3]);
+                for (int i = 0; i < 16; ++i)
+                    w[m][i] = CPL == 4 ? __ldg(reinterpret_cast<const uint32_t*>(bdp[m] + (size_t)(blk * 16 + i) * N + c))
+                                       : (uint32_t)__ldg(bdp[m] + (size_t)(blk * 16 + i) * N + c);
+                sw[m] = CPL == 4 ? __ldg(reinterpret_cast<const uint32_t*>(bsp[m] + (size_t)blk * N + c))
+                                 : (uint32_t)__ldg(bsp[m] + (size_t)blk * N + c);
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) acc[j] = fmaf(part[j], ue4m3_to_f32((sw >> (8 * j)) & 0xff), acc[j]);
-        } else {
-            for (int j = 0; j < 4; ++j) {
-                if (c + j >= N) break;
+            for (int m = 0; m < NMAT; ++m) {
+                float part[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    uint32_t b = bd[(size_t)(blk * 16 + i) * N + c + j];
-                    part[j] = fmaf(a_s[blk * 32 + 2 * i], e2m1_to_f32(b & 0xf), part[j]);
-                    part[j] = fmaf(a_s[blk * 32 + 2 * i + 1], e2m1_to_f32(b >> 4), part[j]);
+                    const float2 a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 2 * i);
+                    uint32_t h;
+                    float2 f;
+                    h = e2m1x2_to_f16x2<0>(w[m][i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                    part[0] = fmaf(a.x, f.x, part[0]); part[0] = fmaf(a.y, f.y, part[0]);
+                    if (CPL == 4) {
+                        h = e2m1x2_to_f16x2<1>(w[m][i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                        part[1] = fmaf(a.x, f.x, part[1]); part[1] = fmaf(a.y, f.y, part[1]);
+                        h = e2m1x2_to_f16x2<2>(w[m][i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                        part[2] = fmaf(a.x, f.x, part[2]); part[2] = fmaf(a.y, f.y, part[2]);
+                        h = e2m1x2_to_f16x2<3>(w[m][i]); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                        part[3] = fmaf(a.x, f.x, part[3]); part[3] = fmaf(a.y, f.y, part[3]);
+                    }
                 }
-                acc[j] = fmaf(part[j], ue4m3_to_f32(bs[(size_t)blk * N + c + j]), acc[j]);
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) acc[m][j] = fmaf(part[j], ue4m3_to_f32((sw[m] >> (8 * j)) & 0xff), acc[m][j]);
+            }
+        } else {
+#pragma unroll
+            for (int m = 0; m < NMAT; ++m) {
+                float part[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int j = 0; j < CPL; ++j) {
+                    if (c + j >= N) break;
+                    for (int i = 0; i < 16; ++i) {
+                        uint32_t b = bdp[m][(size_t)(blk * 16 + i) * N + c + j];
+                        part[j] = fmaf(a_s[blk * 32 + 2 * i], e2m1_to_f32(b & 0xf), part[j]);
+                        part[j] = fmaf(a_s[blk * 32 + 2 * i + 1], e2m1_to_f32(b >> 4), part[j]);
+                    }
+                    acc[m][j] = fmaf(part[j], ue4m3_to_f32(bsp[m][(size_t)blk * N + c + j]), acc[m][j]);
+                }
             }
         }
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) red[warp * 128 + lane * 4 + j] = acc[j];
+    for (int m = 0; m < NMAT; ++m)
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) red[(m * kMoeNvf4Warps + warp) * TILE + lane * CPL + j] = acc[m][j];
     __syncthreads();
-    if (threadIdx.x < 128) {
-        float s = 0.f;
+    if (threadIdx.x < TILE) {
+        float s[NMAT];
+#pragma unroll
+        for (int m = 0; m < NMAT; ++m) {
+            s[m] = 0.f;
 #pragma unroll 8
-        for (int w = 0; w < kMoeNvf4Warps; ++w) s += red[w * 128 + threadIdx.x];
-        if (col0 + threadIdx.x < N) C[(size_t)r * N + col0 + threadIdx.x] = f32_to_bf16_bits(s);
+            for (int w = 0; w < kMoeNvf4Warps; ++w) s[m] += red[(m * kMoeNvf4Warps + w) * TILE + threadIdx.x];
+        }
+        if (col0 + threadIdx.x < N) {
+            uint16_t o;
+            if (NMAT == 2) {
+                const float g = bf16_bits_to_f32(f32_to_bf16_bits(s[0]));
+                const float u = bf16_bits_to_f32(f32_to_bf16_bits(s[NMAT - 1]));
+                o = f32_to_bf16_bits(bf16_bits_to_f32(f32_to_bf16_bits(silu_ref(g))) * u);
+            } else {
+                o = f32_to_bf16_bits(s[0]);
+            }
+            C[(size_t)r * N + col0 + threadIdx.x] = o;
+        }
     }
 }
 
@@ -416,6 +456,33 @@ __global__ void moe_combine_t1_kernel(const uint16_t* __restrict__ expert_out, c
 
 static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
+template <int NMAT, int CPL>
+static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
+                               const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
+                               int expert_offset, int num_local_experts, void* stream) {
+    constexpr int TILE = 32 * CPL;
+    size_t smem = (size_t)K * 4 + (size_t)NMAT * kMoeNvf4Warps * TILE * 4;
+    PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
+    static bool attr = false;
+    if (!attr) {
+        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr = true;
+    }
+    PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel<NMAT, CPL>, dim3((N + TILE - 1) / TILE, M), dim3(kMoeNvf4Warps * 32), smem,
+                    (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
+                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts));
+    return 0;
+}
+template <int NMAT>
+static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1, const void* Bs1,
+                           void* C, const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
+                           int num_local_experts, void* stream) {
+    // 128-column CTAs (lane = 4 columns, 32-bit loads).  With 8 routed experts x 768 columns this is only 48 CTAs:
+    // a narrower tile (more CTAs) is the next step for the NVF4 expert GEMVs (open items).
+    return launch_moe_nvf4_cpl<NMAT, 4>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
+                                        num_local_experts, stream);
+}
+
 }  // namespace pgk
 
 using namespace pgk;
@@ -505,16 +572,16 @@ int pgk_moe_grouped_gemv_nvf4_ex(const void* A, int a_stride, const void* B_data
     if (M <= 0) return 0;
     PGK_REQUIRE(a_stride == 0 || a_stride >= K, "moe_grouped_gemv_nvf4 failed: a_stride=%d must be 0 (broadcast) or >= K", a_stride);
     PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_grouped_gemv_nvf4 failed: K=%d must be a multiple of 32", K);
-    size_t smem = (size_t)K * 4 + (size_t)kMoeNvf4Warps * 128 * 4;
-    PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
-    static bool attr = false;
-    if (!attr) {
-        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr = true;
-    }
-    PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel, dim3((N + 127) / 128, M), dim3(kMoeNvf4Warps * 32), smem, ST(stream),
-                    (const uint16_t*)A, (const uint8_t*)B_data, (const uint8_t*)B_scale, (uint16_t*)C, row_expert_ids,
-                    K, N, a_stride, expert_offset, num_local_experts));
+    return launch_moe_nvf4<1>(A, a_stride, B_data, B_scale, nullptr, nullptr, C, row_expert_ids, M, K, N, expert_offset,
+                              num_local_experts, stream);
+}
+int pgk_moe_gateup_nvf4_t1(const void* x, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
+                           const void* Bu_scale, void* act, const int32_t* row_expert_ids, int k, int K, int N,
+                           int expert_offset, int num_local_experts, void* stream) {
+    if (k <= 0) return 0;
+    PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_gateup_nvf4_t1 failed: K=%d must be a multiple of 32", K);
+    return launch_moe_nvf4<2>(x, 0, Bg_data, Bg_scale, Bu_data, Bu_scale, act, row_expert_ids, k, K, N, expert_offset,
+                              num_local_experts, stream);
     return 0;
 }
 

@@ -139,8 +139,8 @@ class MoELayer:
 
     def _forward_t1(self, x: GPUArray, b: dict, out: GPUArray | None, residual: GPUArray | None, st) -> GPUArray:
         """One token: rows stay in slot order (the combine sums in slot order anyway), so routing is one
-        launch and permutation / expand / gather disappear; FP8 experts run as gate+up+silu+mul and
-        down+combine(+residual) kernels.  Bit-identical to the generic pipeline (tests/test_gpu_moe.py)."""
+        launch and permutation / expand / gather disappear; the experts run as one gate+up+silu+mul kernel and
+        (FP8) one down+combine(+residual) kernel, (NVF4) down then combine(+residual).  Bit-identical to the generic pipeline (tests/test_gpu_moe.py)."""
         H, I, E, k = self.hidden_size, self.intermediate_size, self.num_experts, self.num_experts_per_tok
         off, nl = self.expert_offset, self.num_local_experts
         api.moe_route_t1(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr,
@@ -156,9 +156,8 @@ class MoELayer:
             return y
         (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
         rid = b["row_ids"].device_ptr
-        api.moe_grouped_gemv_nvf4_ex(x.device_ptr, 0, wg.device_ptr, sg.device_ptr, b["act"].device_ptr, rid, k, H, I, off, nl, st)
-        api.moe_grouped_gemv_nvf4_ex(x.device_ptr, 0, wu.device_ptr, su.device_ptr, b["up"].device_ptr, rid, k, H, I, off, nl, st)
-        api.silu_mul(b["act"].device_ptr, b["up"].device_ptr, b["act"].device_ptr, b["act"].size, 2, st)
+        api.moe_gateup_nvf4_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                               b["act"].device_ptr, rid, k, H, I, off, nl, st)
         api.moe_grouped_gemv_nvf4_ex(b["act"].device_ptr, I, wd.device_ptr, sd.device_ptr, b["down"].device_ptr, rid, k, I, H, off, nl, st)
         api.moe_combine_t1(b["down"].device_ptr, b["weights"].device_ptr, res, y.device_ptr, H, k, st)
         return y
