@@ -6,12 +6,14 @@
 //
 // One process per GPU.  Every rank owns a communication buffer (cudaMalloc + cudaIpc handle, opened by all
 // peers): two data slabs (parity of the call sequence number) and a flag word per (parity, CTA, source rank).
-// A call = one kernel:
-//   1. every CTA copies its slice of the local partial sums into the local slab (plain stores),
-//   2. one thread publishes: __threadfence_system, then stores the call's sequence number into the flag word
-//      of THIS rank in every peer's buffer (remote NVLink stores),
-//   3. `world` threads spin on the local flag words until every source has published the same number,
-//   4. every thread sums its 16-byte vectors over all ranks in rank order (remote NVLink loads, f32
+// A call = one kernel, PUSH style (no NVLink round trip on the critical path: remote stores are posted, every
+// load is local):
+//   1. every CTA stores its slice of the local partial sums into the region of THIS rank in EVERY rank's slab
+//      (remote NVLink stores; own buffer included),
+//   2. one thread per destination publishes: __threadfence_system, then stores the call's sequence number into
+//      the flag word of THIS rank in that peer's buffer,
+//   3. `world` threads spin on the LOCAL flag words until every source has published the same number,
+//   4. every thread sums its 16-byte vectors over all source regions of the LOCAL slab in rank order (f32
 //      accumulate), rounds to bf16, adds the residual and stores locally.
 // All ranks compute the identical sum in the identical order, so the replicated hidden state stays bit-identical
 // across ranks (greedy tokens cannot diverge between ranks).  Slab reuse is safe with two parities: a rank can
@@ -26,7 +28,8 @@ namespace pgk {
 
 constexpr int kP2pMaxWorld = 8;
 constexpr int kP2pMaxCtas = 64;
-constexpr size_t kP2pSlabBytes = 4u << 20;                  // per parity: up to 64 rows x 16384 bf16 x 2 B
+constexpr size_t kP2pSlabBytes = 8u << 20;                  // per parity: one region per source rank
+constexpr size_t kP2pRegionBytes = kP2pSlabBytes / kP2pMaxWorld;   // 1 MB: up to 64 rows x 8192 bf16
 constexpr size_t kP2pFlagBytes = 2 * kP2pMaxCtas * kP2pMaxWorld * sizeof(unsigned);
 constexpr size_t kP2pBufBytes = 2 * kP2pSlabBytes + kP2pFlagBytes;
 
@@ -76,9 +79,14 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     const unsigned par = seq & 1u;
     const long e0 = (long)cta * p.per_cta, e1 = min(p.n, e0 + p.per_cta);
     unsigned char* mine = p.peer[p.rank];
-    // 1. local partials -> local slab
-    for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8)
-        *reinterpret_cast<uint4*>(mine + par * kP2pSlabBytes + e * 2) = *reinterpret_cast<const uint4*>(p.partial + e);
+    // 1. local partials -> this rank's region in every rank's slab (posted remote stores)
+    const size_t my_region = par * kP2pSlabBytes + (size_t)p.rank * kP2pRegionBytes;
+    for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8) {
+        const uint4 v = *reinterpret_cast<const uint4*>(p.partial + e);
+#pragma unroll
+        for (int r = 0; r < kP2pMaxWorld; ++r)
+            if (r < p.world) *reinterpret_cast<uint4*>(p.peer[r] + my_region + e * 2) = v;
+    }
     __syncthreads();
     // 2. publish to every rank (own flag word included)
     if (tid < p.world) {
@@ -99,12 +107,11 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     __syncthreads();
     // 4. sum in rank order, round, add the residual
     for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8) {
-        // all peer loads are issued back to back (an NVLink round trip is ~1 us: never one after the other),
-        // then summed in rank order
+        // every source region sits in the local slab; loads issued back to back, then summed in rank order
         uint4 pv[kP2pMaxWorld];
 #pragma unroll
         for (int r = 0; r < kP2pMaxWorld; ++r)
-            if (r < p.world) pv[r] = ld_peer16(p.peer[r] + par * kP2pSlabBytes + e * 2);
+            if (r < p.world) pv[r] = ld_peer16(mine + par * kP2pSlabBytes + (size_t)r * kP2pRegionBytes + e * 2);
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -172,11 +179,11 @@ int pgk_p2p_open(const void* host_handles_all) {
 int pgk_p2p_ready(void) { return g_p2p.ready ? 1 : 0; }
 
 /* out[n] = bf16(residual + bf16(sum over ranks of partial)) (residual NULL: plain all-reduce); out may alias
- * residual.  n % 8 == 0, n * 2 bytes <= 4 MB, 16-byte aligned pointers.  Every rank must make the same calls
+ * residual.  n % 8 == 0, n * 2 bytes <= 1 MB, 16-byte aligned pointers.  Every rank must make the same calls
  * in the same order. */
 int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream) {
     PGK_REQUIRE(g_p2p.ready, "p2p_allreduce failed: peer buffers not opened (pgk_p2p_create / pgk_p2p_open)");
-    PGK_REQUIRE(n % 8 == 0 && n * 2 <= kP2pSlabBytes, "p2p_allreduce failed: n = %zu must be a multiple of 8 and <= %zu", n, kP2pSlabBytes / 2);
+    PGK_REQUIRE(n % 8 == 0 && n * 2 <= kP2pRegionBytes, "p2p_allreduce failed: n = %zu must be a multiple of 8 and <= %zu", n, kP2pRegionBytes / 2);
     PGK_REQUIRE(((uintptr_t)partial % 16 == 0) && ((uintptr_t)out % 16 == 0) && ((uintptr_t)residual % 16 == 0),
                 "p2p_allreduce failed: pointers must be 16-byte aligned");
     P2pParams p = {};
