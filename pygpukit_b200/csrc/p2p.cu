@@ -70,44 +70,46 @@ __device__ __forceinline__ unsigned ld_flag_sys(const unsigned* p) {
 
 __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     __shared__ unsigned s_seq;
+    const int cta = blockIdx.x, tid = threadIdx.x;
+    // Before the dependency wait: the call counter (internal state, last written by the previous all-reduce,
+    // i.e. >= 2 kernels back).  One 16-byte vector per thread: a CTA covers at most 8192 elements.
+    if (tid == 0) s_seq = ++p.seq[cta];               // same count on every rank: SPMD, every rank runs every call
+    const long e0 = (long)cta * p.per_cta, e1 = min(p.n, e0 + p.per_cta);
+    const long e = e0 + (long)tid * 8;
+    const bool active = e < e1;
     griddep_wait();                                   // the partial sums come from the GEMV just before
     griddep_launch();
-    const int cta = blockIdx.x, tid = threadIdx.x;
-    if (tid == 0) s_seq = ++p.seq[cta];               // same count on every rank: SPMD, every rank runs every call
+    uint4 rv = make_uint4(0u, 0u, 0u, 0u);            // residual: requested now, consumed after the flag wait
+    if (active && p.residual) rv = *reinterpret_cast<const uint4*>(p.residual + e);
     __syncthreads();
     const unsigned seq = s_seq;
     const unsigned par = seq & 1u;
-    const long e0 = (long)cta * p.per_cta, e1 = min(p.n, e0 + p.per_cta);
     unsigned char* mine = p.peer[p.rank];
     // 1. local partials -> this rank's region in every rank's slab (posted remote stores)
     const size_t my_region = par * kP2pSlabBytes + (size_t)p.rank * kP2pRegionBytes;
-    for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8) {
+    if (active) {
         const uint4 v = *reinterpret_cast<const uint4*>(p.partial + e);
 #pragma unroll
         for (int r = 0; r < kP2pMaxWorld; ++r)
             if (r < p.world) *reinterpret_cast<uint4*>(p.peer[r] + my_region + e * 2) = v;
     }
     __syncthreads();
-    // 2. publish to every rank (own flag word included)
+    // 2. publish to every rank (own flag word included), 3. wait for every source rank's slice
     if (tid < p.world) {
         __threadfence_system();
         unsigned* f = reinterpret_cast<unsigned*>(p.peer[tid] + 2 * kP2pSlabBytes) +
                       ((size_t)par * kP2pMaxCtas + cta) * kP2pMaxWorld + p.rank;
         st_flag_sys(f, seq);
-    }
-    // 3. wait for every source rank's slice
-    if (tid < p.world) {
-        const unsigned* f = reinterpret_cast<const unsigned*>(mine + 2 * kP2pSlabBytes) +
+        const unsigned* g = reinterpret_cast<const unsigned*>(mine + 2 * kP2pSlabBytes) +
                             ((size_t)par * kP2pMaxCtas + cta) * kP2pMaxWorld + tid;
         const long long t0 = clock64();
-        while (ld_flag_sys(f) != seq) {
+        while (ld_flag_sys(g) != seq) {
             if (clock64() - t0 > 4000000000LL) { *p.err = 1u; break; }     // ~2 s: a peer is gone; do not hang the GPU
         }
     }
     __syncthreads();
-    // 4. sum in rank order, round, add the residual
-    for (long e = e0 + (long)tid * 8; e < e1; e += (long)blockDim.x * 8) {
-        // every source region sits in the local slab; loads issued back to back, then summed in rank order
+    // 4. sum the source regions of the local slab in rank order, round, add the residual
+    if (active) {
         uint4 pv[kP2pMaxWorld];
 #pragma unroll
         for (int r = 0; r < kP2pMaxWorld; ++r)
@@ -125,7 +127,6 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
         }
         uint16_t o[8];
         if (p.residual) {
-            const uint4 rv = *reinterpret_cast<const uint4*>(p.residual + e);
             const uint16_t* rb = reinterpret_cast<const uint16_t*>(&rv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = hadd_bf16_bits(acc[j], rb[j]);
@@ -196,6 +197,7 @@ int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* 
     if (ctas > kP2pMaxCtas) ctas = kP2pMaxCtas;
     long per = ((long)n + ctas - 1) / ctas;
     p.per_cta = (per + 7) / 8 * 8;
+    PGK_REQUIRE(p.per_cta <= 8192, "p2p_allreduce failed: %ld elements per CTA (internal limit 8192)", p.per_cta);
     PGK_CUDA(launch(p2p_allreduce_add_kernel, dim3(ctas), dim3(1024), 0, (cudaStream_t)stream, p));
     return 0;
 }
