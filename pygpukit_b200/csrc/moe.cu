@@ -212,7 +212,9 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
 constexpr int kMoeNvf4Warps = 32;
 // NMAT = 1: C[r, :] = A[r, :] . B[e]      NMAT = 2 (decode gate/up pair): C[r, :] = bf16(bf16(silu(g)) * u) with
 // g = bf16(A . Bg[e]), u = bf16(A . Bu[e]) -- the rounding points of gate GEMV -> silu -> up GEMV -> mul_inplace.
-// CPL = columns per lane (4: CTA = 128 columns, 32-bit loads).
+// CPL = columns per lane: 4 (CTA = 128 columns, 32-bit loads) or 1 (CTA = 32 columns, byte loads: 4x the CTAs when
+// rows x N/128 would leave most SMs idle, e.g. 8 routed experts x 768 columns = 48 CTAs).  Per column the arithmetic
+// and its order are the same for both.
 template <int NMAT, int CPL>
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
 moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd0,
@@ -247,7 +249,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
 #pragma unroll
         for (int j = 0; j < CPL; ++j) acc[m][j] = 0.f;
     const int KB = K >> 5;
-    const bool full = (c + CPL - 1 < N) && ((N & (CPL - 1)) == 0);
+    const bool full = CPL == 4 && (c + CPL - 1 < N) && ((N & (CPL - 1)) == 0);
     for (int blk = warp; blk < KB; blk += kMoeNvf4Warps) {
         if (full) {
             uint32_t w[NMAT][16], sw[NMAT];
@@ -282,16 +284,50 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
 #pragma unroll
                 for (int j = 0; j < CPL; ++j) acc[m][j] = fmaf(part[j], ue4m3_to_f32((sw[m] >> (8 * j)) & 0xff), acc[m][j]);
             }
+        } else if (CPL == 1 && c < N) {
+            // one column per lane: 16 byte loads per scale block, packed four at a time into a word so that the
+            // decode is the same F2FP form as above (the byte-register form of the conversion asm must see a
+            // full 32-bit source)
+#pragma unroll
+            for (int m = 0; m < NMAT; ++m) {
+                uint32_t b[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) b[i] = __ldg(bdp[m] + (size_t)(blk * 16 + i) * N + c);
+                const uint32_t sw = __ldg(bsp[m] + (size_t)blk * N + c);
+                float part = 0.f;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const uint32_t w4 = b[4 * t] | (b[4 * t + 1] << 8) | (b[4 * t + 2] << 16) | (b[4 * t + 3] << 24);
+                    uint32_t h;
+                    float2 f, a;
+                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t);
+                    h = e2m1x2_to_f16x2<0>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
+                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t + 2);
+                    h = e2m1x2_to_f16x2<1>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
+                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t + 4);
+                    h = e2m1x2_to_f16x2<2>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
+                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t + 6);
+                    h = e2m1x2_to_f16x2<3>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
+                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
+                }
+                acc[m][0] = fmaf(part, ue4m3_to_f32(sw), acc[m][0]);
+            }
         } else {
 #pragma unroll
             for (int m = 0; m < NMAT; ++m) {
                 float part[4] = {0.f, 0.f, 0.f, 0.f};
                 for (int j = 0; j < CPL; ++j) {
                     if (c + j >= N) break;
+                    uint32_t b[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) b[i] = __ldg(bdp[m] + (size_t)(blk * 16 + i) * N + c + j);
+#pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        uint32_t b = bdp[m][(size_t)(blk * 16 + i) * N + c + j];
-                        part[j] = fmaf(a_s[blk * 32 + 2 * i], e2m1_to_f32(b & 0xf), part[j]);
-                        part[j] = fmaf(a_s[blk * 32 + 2 * i + 1], e2m1_to_f32(b >> 4), part[j]);
+                        part[j] = fmaf(a_s[blk * 32 + 2 * i], e2m1_to_f32(b[i] & 0xf), part[j]);
+                        part[j] = fmaf(a_s[blk * 32 + 2 * i + 1], e2m1_to_f32(b[i] >> 4), part[j]);
                     }
                     acc[m][j] = fmaf(part[j], ue4m3_to_f32(bsp[m][(size_t)blk * N + c + j]), acc[m][j]);
                 }
@@ -477,8 +513,13 @@ template <int NMAT>
 static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1, const void* Bs1,
                            void* C, const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
                            int num_local_experts, void* stream) {
-    // 128-column CTAs (lane = 4 columns, 32-bit loads).  With 8 routed experts x 768 columns this is only 48 CTAs:
-    // a narrower tile (more CTAs) is the next step for the NVF4 expert GEMVs (open items).
+    // 128-column CTAs by default.  The 32-column form (PGK_MOE_NVF4_CPL=1) gives 4x the CTAs -- 8 routed experts x 768
+    // columns are only 48 CTAs of 128 columns -- but measured SLOWER on B200 (Qwen3-30B-A3B NVF4: 211.7 vs 262.6 tok/s):
+    // its 32-byte requests split every 64-byte DRAM atom between two CTAs.  Kept for A/B; same results bit for bit.
+    static const int force = [] { const char* e = getenv("PGK_MOE_NVF4_CPL"); return e ? atoi(e) : 0; }();
+    if (force == 1)
+        return launch_moe_nvf4_cpl<NMAT, 1>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
+                                            num_local_experts, stream);
     return launch_moe_nvf4_cpl<NMAT, 4>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
                                         num_local_experts, stream);
 }
