@@ -262,7 +262,7 @@ def workload_config(args, world: int) -> dict:
     fmt_name = {"fp8": "w8a16 FP8-E4M3 128x128 block-scaled", "nvf4": "NVF4 (E2M1, UE4M3 scale per 32)", "bf16": "bf16"}
     return {"workload": f"{args.model} {fmt_name[args.format]} weights, BF16 activations, batch-1 greedy decode at "
                         f"{args.context} context, random-init weights, synthetic KV cache",
-            "model": args.model, "weight_format": args.format, "batch": 1, "context": args.context,
+            "shapes": args.model, "weight_format": args.format, "decode_batch": 1, "context": args.context,
             "parallelism": f"tp{world}", "l2_hygiene": "per-step weight stream >> 126 MB L2 (no flush needed)",
             **({"layers_truncated_INVALID": args.layers} if args.layers else {})}
 
