@@ -206,10 +206,10 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
 // Row r of A[R,K] uses expert e = row_expert_ids[r] - expert_offset of B_data[E,K/2,N] /
 // B_scale[E,K/32,N] (the reference NVF4 layout per expert, nvf4_kernels.cu:79-200); rows whose
 // expert is not held by this rank produce zeros (their value arrives through the all-reduce).
-// CTA = 32 warps over one row x 128 columns: lane owns 4 consecutive columns (32-bit loads, one
-// 128-byte line per warp per byte-row), warp w owns scale blocks w, w+32, ... of K; partial sums
+// CTA = 16 warps over one row x 128 columns: lane owns 4 consecutive columns (32-bit loads, one
+// 128-byte line per warp per byte-row), warp w owns scale blocks w, w+16, ... of K; partial sums
 // meet in shared memory and are folded in warp order (deterministic).
-constexpr int kMoeNvf4Warps = 32;
+constexpr int kMoeNvf4Warps = 16;   // 512 threads: 128 registers per thread (32 warps capped the kernel at 64 and spilled ~500 B per thread)
 // NMAT = 1: C[r, :] = A[r, :] . B[e]      NMAT = 2 (decode gate/up pair): C[r, :] = bf16(bf16(silu(g)) * u) with
 // g = bf16(A . Bg[e]), u = bf16(A . Bu[e]) -- the rounding points of gate GEMV -> silu -> up GEMV -> mul_inplace.
 // CPL = columns per lane: 4 (CTA = 128 columns, 32-bit loads) or 1 (CTA = 32 columns, byte loads: 4x the CTAs when
