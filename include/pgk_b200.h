@@ -309,6 +309,16 @@ int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, con
 int pgk_moe_gateup_nvf4_t1(const void* x, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
                            const void* Bu_scale, void* act, const int32_t* row_expert_ids, int k, int K, int N,
                            int expert_offset, int num_local_experts, void* stream);
+/* route_t1 folded into the gate/up launch: every warp recomputes the routing from the router logits (~1 us) and the
+ * first warp publishes weights / indices / row_expert_ids for the launches that follow -- one launch less per layer */
+int pgk_moe_route_gateup_fp8_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
+                                int32_t* row_expert_ids, const void* Bg_enk, const void* Sg, const void* Bu_enk,
+                                const void* Su, void* act, int k, int K, int N, int expert_offset,
+                                int num_local_experts, void* stream);
+int pgk_moe_route_gateup_nvf4_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
+                                 int32_t* row_expert_ids, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
+                                 const void* Bu_scale, void* act, int k, int K, int N, int expert_offset,
+                                 int num_local_experts, void* stream);
 int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
                                 int expert_offset, int num_local_experts, void* stream);

@@ -91,6 +91,8 @@ _SIGS = {
     "pgk_moe_route_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_moe_gateup_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_gateup_nvf4_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_route_gateup_fp8_t1": [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "pgk_moe_route_gateup_nvf4_t1": [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_down_combine_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_combine_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],

@@ -201,6 +201,48 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
     if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
 }
 
+struct MoeRouteArgs {                // logits == NULL: the routing was done by an earlier launch (row_ids given)
+    const uint16_t* logits; uint16_t* weights; int32_t* indices; int32_t* row_ids; int E;
+};
+
+// One-token routing inside a warp: top-k by k passes of strict '>' argmax (lowest index wins ties) over E <= 512
+// router logits, then softmax over the selected values in slot order -- the arithmetic of topk_with_indices +
+// softmax_topk (topk_kernels.cuh:111-147,222-256), statement for statement.  Lane j < k returns expert j and its
+// bf16 weight bits.  Every warp that needs the routing can recompute it (~1 us) instead of waiting for a launch.
+__device__ __forceinline__ void moe_route_warp(const uint16_t* __restrict__ logits, int E, int k, int lane, int& my_idx,
+                                               uint16_t& my_w) {
+    constexpr int MAXPL = 16;
+    float loc[MAXPL];
+#pragma unroll
+    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? bf16_bits_to_f32(logits[e]) : -INFINITY; }
+    float mine = -INFINITY;                       // lane j keeps selected value j (k <= 32)
+    my_idx = 0;
+    for (int j = 0; j < k; ++j) {
+        float bv = -1e30f;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (bi == 0x7fffffff) bi = 0;
+        if (lane == j) { mine = bf16_bits_to_f32(f32_to_bf16_bits(bv)); my_idx = bi; }
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
+    }
+    float mx = mine;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const float ex = __expf(mine - mx);
+    float sum = 0.f;
+    for (int i = 0; i < k; ++i) sum += __shfl_sync(0xffffffffu, ex, i);     // slot order, as the serial kernel
+    const float inv = 1.0f / sum;
+    my_w = f32_to_bf16_bits(ex * inv);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Expert-grouped NVF4 GEMV (net-new: the reference's MoE path is FP8-only, layers/moe.py:86-151).
 // Row r of A[R,K] uses expert e = row_expert_ids[r] - expert_offset of B_data[E,K/2,N] /
@@ -221,7 +263,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
                              const uint8_t* __restrict__ Bs0, const uint8_t* __restrict__ Bd1,
                              const uint8_t* __restrict__ Bs1, uint16_t* __restrict__ C,
                              const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
-                             int expert_offset, int num_local) {
+                             int expert_offset, int num_local, MoeRouteArgs rt) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
     constexpr int TILE = 32 * CPL;
@@ -230,7 +272,19 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     griddep_launch();
     const int r = blockIdx.y, col0 = blockIdx.x * TILE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int e = row_expert_ids[r] - expert_offset;
+    int eid;
+    if (rt.logits) {                 // decode: routing folded into this launch (gridDim.y = k rows in slot order)
+        int idx;
+        uint16_t w;
+        moe_route_warp(rt.logits, rt.E, (int)gridDim.y, lane, idx, w);
+        if (blockIdx.x == 0 && r == 0 && warp == 0 && lane < (int)gridDim.y) {
+            rt.indices[lane] = idx; rt.row_ids[lane] = idx; rt.weights[lane] = w;
+        }
+        eid = __shfl_sync(0xffffffffu, idx, r);
+    } else {
+        eid = row_expert_ids[r];
+    }
+    const int e = eid - expert_offset;
     const int c = col0 + lane * CPL;
     if (e < 0 || e >= num_local) {
         if (warp == 0 && c < N) {
@@ -373,35 +427,10 @@ __global__ void moe_route_t1_kernel(const uint16_t* __restrict__ logits, uint16_
     griddep_wait();
     griddep_launch();
     const int lane = threadIdx.x;
-    constexpr int MAXPL = 16;
-    float loc[MAXPL];
-#pragma unroll
-    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? bf16_bits_to_f32(logits[e]) : -INFINITY; }
-    float mine = -INFINITY;                       // lane j keeps selected value j (k <= 32)
-    for (int j = 0; j < k; ++j) {
-        float bv = -1e30f;
-        int bi = 0x7fffffff;
-#pragma unroll
-        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-        }
-        if (bi == 0x7fffffff) bi = 0;
-        if (lane == j) { mine = bf16_bits_to_f32(f32_to_bf16_bits(bv)); indices[j] = bi; row_ids[j] = bi; }
-#pragma unroll
-        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
-    }
-    float mx = mine;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    const float ex = __expf(mine - mx);
-    float sum = 0.f;
-    for (int i = 0; i < k; ++i) sum += __shfl_sync(0xffffffffu, ex, i);     // slot order, as the serial kernel
-    const float inv = 1.0f / sum;
-    if (lane < k) weights[lane] = f32_to_bf16_bits(ex * inv);
+    int idx;
+    uint16_t w;
+    moe_route_warp(logits, E, k, lane, idx, w);
+    if (lane < k) { indices[lane] = idx; row_ids[lane] = idx; weights[lane] = w; }
 }
 
 // gate and up GEMVs of the k routed experts + silu + multiply in one launch: one warp per (slot, n)
@@ -410,14 +439,24 @@ __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const u
                                          const uint16_t* __restrict__ Sg, const uint8_t* __restrict__ Bu,
                                          const uint16_t* __restrict__ Su, uint16_t* __restrict__ act,
                                          const int32_t* __restrict__ row_ids, int R, int K, int N, int expert_offset,
-                                         int num_local) {
+                                         int num_local, MoeRouteArgs rt) {
     griddep_wait();
     griddep_launch();
     const int lane = threadIdx.x & 31;
     const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (gw >= (long)R * N) return;
     const int n = (int)(gw % N), m = (int)(gw / N);
-    const int e = row_ids[m] - expert_offset;
+    int eid;
+    if (rt.logits) {                 // routing folded into this launch: every warp recomputes it, warp 0 publishes it
+        int idx;
+        uint16_t w;
+        moe_route_warp(rt.logits, rt.E, R, lane, idx, w);
+        if (gw == 0 && lane < R) { rt.indices[lane] = idx; rt.row_ids[lane] = idx; rt.weights[lane] = w; }
+        eid = __shfl_sync(0xffffffffu, idx, m);
+    } else {
+        eid = row_ids[m];
+    }
+    const int e = eid - expert_offset;
     if (e < 0 || e >= num_local) {
         if (lane == 0) act[(size_t)m * N + n] = 0;
         return;
@@ -495,7 +534,7 @@ static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) /
 template <int NMAT, int CPL>
 static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
                                const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
-                               int expert_offset, int num_local_experts, void* stream) {
+                               int expert_offset, int num_local_experts, void* stream, MoeRouteArgs rt) {
     constexpr int TILE = 32 * CPL;
     size_t smem = (size_t)K * 4 + (size_t)NMAT * kMoeNvf4Warps * TILE * 4;
     PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
@@ -506,22 +545,22 @@ static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, con
     }
     PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel<NMAT, CPL>, dim3((N + TILE - 1) / TILE, M), dim3(kMoeNvf4Warps * 32), smem,
                     (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
-                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts));
+                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts, rt));
     return 0;
 }
 template <int NMAT>
 static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1, const void* Bs1,
                            void* C, const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
-                           int num_local_experts, void* stream) {
+                           int num_local_experts, void* stream, MoeRouteArgs rt = MoeRouteArgs{}) {
     // 128-column CTAs by default.  The 32-column form (PGK_MOE_NVF4_CPL=1) gives 4x the CTAs -- 8 routed experts x 768
     // columns are only 48 CTAs of 128 columns -- but measured SLOWER on B200 (Qwen3-30B-A3B NVF4: 211.7 vs 262.6 tok/s):
     // its 32-byte requests split every 64-byte DRAM atom between two CTAs.  Kept for A/B; same results bit for bit.
     static const int force = [] { const char* e = getenv("PGK_MOE_NVF4_CPL"); return e ? atoi(e) : 0; }();
     if (force == 1)
         return launch_moe_nvf4_cpl<NMAT, 1>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
-                                            num_local_experts, stream);
+                                            num_local_experts, stream, rt);
     return launch_moe_nvf4_cpl<NMAT, 4>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
-                                        num_local_experts, stream);
+                                        num_local_experts, stream, rt);
 }
 
 }  // namespace pgk
@@ -642,8 +681,35 @@ int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, con
     size_t warps = (size_t)k * N;
     PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
                     (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
-                    (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts));
+                    (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts, MoeRouteArgs{}));
     return 0;
+}
+static int check_route(int num_experts, int k, const char* fn) {
+    PGK_REQUIRE(num_experts >= 1 && num_experts <= 512 && k >= 1 && k <= num_experts && k <= 32,
+                "%s failed: unsupported num_experts=%d k=%d", fn, num_experts, k);
+    return 0;
+}
+int pgk_moe_route_gateup_fp8_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
+                                int32_t* row_expert_ids, const void* Bg_enk, const void* Sg, const void* Bu_enk,
+                                const void* Su, void* act, int k, int K, int N, int expert_offset,
+                                int num_local_experts, void* stream) {
+    if (check_route(num_experts, k, "moe_route_gateup_fp8_t1")) return 1;
+    MoeRouteArgs rt = {(const uint16_t*)logits, (uint16_t*)weights, indices, row_expert_ids, num_experts};
+    size_t warps = (size_t)k * N;
+    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
+                    (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
+                    (uint16_t*)act, (const int32_t*)nullptr, k, K, N, expert_offset, num_local_experts, rt));
+    return 0;
+}
+int pgk_moe_route_gateup_nvf4_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
+                                 int32_t* row_expert_ids, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
+                                 const void* Bu_scale, void* act, int k, int K, int N, int expert_offset,
+                                 int num_local_experts, void* stream) {
+    if (check_route(num_experts, k, "moe_route_gateup_nvf4_t1")) return 1;
+    PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_route_gateup_nvf4_t1 failed: K=%d must be a multiple of 32", K);
+    MoeRouteArgs rt = {(const uint16_t*)logits, (uint16_t*)weights, indices, row_expert_ids, num_experts};
+    return launch_moe_nvf4<2>(x, 0, Bg_data, Bg_scale, Bu_data, Bu_scale, act, nullptr, k, K, N, expert_offset,
+                              num_local_experts, stream, rt);
 }
 int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,

@@ -30,6 +30,10 @@ if TYPE_CHECKING:
     from ..config import TransformerConfig
 
 
+# 1: routing recomputed by every warp of the gate/up launch instead of a moe_route_t1 launch.  Measured SLOWER on B200
+# (Qwen3-30B-A3B FP8 378.5 -> 320.3, NVF4 348.7 -> 339.2 tok/s): the ~1 us routing chain sits in front of every weight
+# address, which costs more than the launch it saves.  Off by default, kept for A/B (bit-identical either way).
+_ROUTE_FOLD = os.environ.get("PGK_MOE_ROUTE_FOLD", "0") != "0"
 _DECODE_FORM = os.environ.get("PGK_MOE_T1", "1") != "0"      # 0: always the generic pipeline (A/B, parity tests)
 
 
@@ -143,21 +147,32 @@ class MoELayer:
         (FP8) one down+combine(+residual) kernel, (NVF4) down then combine(+residual).  Bit-identical to the generic pipeline (tests/test_gpu_moe.py)."""
         H, I, E, k = self.hidden_size, self.intermediate_size, self.num_experts, self.num_experts_per_tok
         off, nl = self.expert_offset, self.num_local_experts
-        api.moe_route_t1(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr,
-                         b["row_ids"].device_ptr, E, k, st)
+        fold = _ROUTE_FOLD          # routing recomputed inside the gate/up launch (one launch less)
+        if not fold:
+            api.moe_route_t1(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr,
+                             b["row_ids"].device_ptr, E, k, st)
+        route = (b["logits"].device_ptr, E, b["weights"].device_ptr, b["indices"].device_ptr, b["row_ids"].device_ptr)
         y = out if out is not None else GPUArray((1, H), bfloat16)
         res = residual.device_ptr if residual is not None else None
         if self.format == "fp8":
             (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
-            api.moe_gateup_fp8_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
-                                  b["act"].device_ptr, b["row_ids"].device_ptr, k, H, I, off, nl, st)
+            if fold:
+                api.moe_route_gateup_fp8_t1(x.device_ptr, *route, wg.device_ptr, sg.device_ptr, wu.device_ptr,
+                                            su.device_ptr, b["act"].device_ptr, k, H, I, off, nl, st)
+            else:
+                api.moe_gateup_fp8_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                                      b["act"].device_ptr, b["row_ids"].device_ptr, k, H, I, off, nl, st)
             api.moe_down_combine_fp8_t1(b["act"].device_ptr, wd.device_ptr, sd.device_ptr, b["weights"].device_ptr,
                                         b["row_ids"].device_ptr, res, y.device_ptr, k, I, H, off, nl, st)
             return y
         (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
         rid = b["row_ids"].device_ptr
-        api.moe_gateup_nvf4_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
-                               b["act"].device_ptr, rid, k, H, I, off, nl, st)
+        if fold:
+            api.moe_route_gateup_nvf4_t1(x.device_ptr, *route, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                                         b["act"].device_ptr, k, H, I, off, nl, st)
+        else:
+            api.moe_gateup_nvf4_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                                   b["act"].device_ptr, rid, k, H, I, off, nl, st)
         api.moe_grouped_gemv_nvf4_ex(b["act"].device_ptr, I, wd.device_ptr, sd.device_ptr, b["down"].device_ptr, rid, k, I, H, off, nl, st)
         api.moe_combine_t1(b["down"].device_ptr, b["weights"].device_ptr, res, y.device_ptr, H, k, st)
         return y

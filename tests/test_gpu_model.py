@@ -173,13 +173,14 @@ def test_moe_decode_form_equals_generic_pipeline(fmt, offset, wide):
         res = gk.from_numpy(rng.standard_normal((1, H)).astype(np.float32)).astype(gk.bfloat16)
         for residual in (None, res):
             outs = []
-            for form in (False, True):
-                moe_mod._DECODE_FORM = form
+            for form, fold in ((False, False), (True, False), (True, True)):     # generic / decode form / + folded routing
+                moe_mod._DECODE_FORM, moe_mod._ROUTE_FOLD = form, fold
                 try:
                     outs.append(layer.forward(x, residual=residual).to_numpy().copy())
                 finally:
-                    moe_mod._DECODE_FORM = True
+                    moe_mod._DECODE_FORM, moe_mod._ROUTE_FOLD = True, False
             assert np.array_equal(outs[0], outs[1]), f"trial {trial} residual={residual is not None}"
+            assert np.array_equal(outs[0], outs[2]), f"trial {trial} residual={residual is not None} (folded routing)"
             assert np.any(outs[0] != 0)
 
 
