@@ -257,7 +257,7 @@ constexpr int kMoeNvf4Warps = 16;   // 512 threads: 128 registers per thread (32
 // CPL = columns per lane: 4 (CTA = 128 columns, 32-bit loads) or 1 (CTA = 32 columns, byte loads: 4x the CTAs when
 // rows x N/128 would leave most SMs idle, e.g. 8 routed experts x 768 columns = 48 CTAs).  Per column the arithmetic
 // and its order are the same for both.
-template <int NMAT, int CPL>
+template <int NMAT, int CPL, bool ROUTE>
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
 moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd0,
                              const uint8_t* __restrict__ Bs0, const uint8_t* __restrict__ Bd1,
@@ -273,7 +273,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     const int r = blockIdx.y, col0 = blockIdx.x * TILE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int eid;
-    if (rt.logits) {                 // decode: routing folded into this launch (gridDim.y = k rows in slot order)
+    if (ROUTE) {                     // decode: routing folded into this launch (gridDim.y = k rows in slot order)
         int idx;
         uint16_t w;
         moe_route_warp(rt.logits, rt.E, (int)gridDim.y, lane, idx, w);
@@ -435,6 +435,7 @@ __global__ void moe_route_t1_kernel(const uint16_t* __restrict__ logits, uint16_
 
 // gate and up GEMVs of the k routed experts + silu + multiply in one launch: one warp per (slot, n)
 // reads x once for both weight rows.  act = bf16(bf16(silu(bf16 gate)) * bf16 up), the three-launch form.
+template <bool ROUTE>
 __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ Bg,
                                          const uint16_t* __restrict__ Sg, const uint8_t* __restrict__ Bu,
                                          const uint16_t* __restrict__ Su, uint16_t* __restrict__ act,
@@ -447,7 +448,7 @@ __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const u
     if (gw >= (long)R * N) return;
     const int n = (int)(gw % N), m = (int)(gw / N);
     int eid;
-    if (rt.logits) {                 // routing folded into this launch: every warp recomputes it, warp 0 publishes it
+    if (ROUTE) {                     // routing folded into this launch: every warp recomputes it, warp 0 publishes it
         int idx;
         uint16_t w;
         moe_route_warp(rt.logits, rt.E, R, lane, idx, w);
@@ -540,10 +541,12 @@ static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, con
     PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
     static bool attr = false;
     if (!attr) {
-        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr = true;
     }
-    PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel<NMAT, CPL>, dim3((N + TILE - 1) / TILE, M), dim3(kMoeNvf4Warps * 32), smem,
+    auto kern = rt.logits ? moe_grouped_gemv_nvf4_kernel<NMAT, CPL, true> : moe_grouped_gemv_nvf4_kernel<NMAT, CPL, false>;
+    PGK_CUDA(launch(kern, dim3((N + TILE - 1) / TILE, M), dim3(kMoeNvf4Warps * 32), smem,
                     (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
                     (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts, rt));
     return 0;
@@ -679,7 +682,7 @@ int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, con
                           int num_local_experts, void* stream) {
     if (k <= 0) return 0;
     size_t warps = (size_t)k * N;
-    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
+    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel<false>, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
                     (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
                     (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts, MoeRouteArgs{}));
     return 0;
@@ -696,7 +699,7 @@ int pgk_moe_route_gateup_fp8_t1(const void* x, const void* logits, int num_exper
     if (check_route(num_experts, k, "moe_route_gateup_fp8_t1")) return 1;
     MoeRouteArgs rt = {(const uint16_t*)logits, (uint16_t*)weights, indices, row_expert_ids, num_experts};
     size_t warps = (size_t)k * N;
-    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
+    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel<true>, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
                     (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
                     (uint16_t*)act, (const int32_t*)nullptr, k, K, N, expert_offset, num_local_experts, rt));
     return 0;
