@@ -263,8 +263,10 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
                              const uint8_t* __restrict__ Bs0, const uint8_t* __restrict__ Bd1,
                              const uint8_t* __restrict__ Bs1, uint16_t* __restrict__ C,
                              const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
-                             int expert_offset, int num_local, MoeRouteArgs rt) {
+                             int expert_offset, int num_local, MoeRouteArgs rt, float* __restrict__ split_ws,
+                             unsigned* __restrict__ split_cnt) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
+    __shared__ unsigned s_ticket;
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
     constexpr int TILE = 32 * CPL;
     float* red = a_s + K;                                             // [NMAT][warps][TILE]
@@ -303,8 +305,14 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
 #pragma unroll
         for (int j = 0; j < CPL; ++j) acc[m][j] = 0.f;
     const int KB = K >> 5;
+    // K split over gridDim.z CTAs (few rows x few column tiles would leave most SMs idle): CTA z owns a contiguous
+    // range of scale blocks; the per-CTA column sums meet in a workspace and the last-arriving CTA folds them in
+    // z order (deterministic) before the epilogue
+    const int KS = (int)gridDim.z, kz = (int)blockIdx.z;
+    const int kper = (KB + KS - 1) / KS;
+    const int blk0 = kz * kper, blk1 = min(KB, blk0 + kper);
     const bool full = CPL == 4 && (c + CPL - 1 < N) && ((N & (CPL - 1)) == 0);
-    for (int blk = warp; blk < KB; blk += kMoeNvf4Warps) {
+    for (int blk = blk0 + warp; blk < blk1; blk += kMoeNvf4Warps) {
         if (full) {
             uint32_t w[NMAT][16], sw[NMAT];
 #pragma unroll
@@ -393,25 +401,50 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
 #pragma unroll
         for (int j = 0; j < CPL; ++j) red[(m * kMoeNvf4Warps + warp) * TILE + lane * CPL + j] = acc[m][j];
     __syncthreads();
+    float s[NMAT];
     if (threadIdx.x < TILE) {
-        float s[NMAT];
 #pragma unroll
         for (int m = 0; m < NMAT; ++m) {
             s[m] = 0.f;
 #pragma unroll 8
             for (int w = 0; w < kMoeNvf4Warps; ++w) s[m] += red[(m * kMoeNvf4Warps + w) * TILE + threadIdx.x];
         }
-        if (col0 + threadIdx.x < N) {
-            uint16_t o;
-            if (NMAT == 2) {
-                const float g = bf16_bits_to_f32(f32_to_bf16_bits(s[0]));
-                const float u = bf16_bits_to_f32(f32_to_bf16_bits(s[NMAT - 1]));
-                o = f32_to_bf16_bits(bf16_bits_to_f32(f32_to_bf16_bits(silu_ref(g))) * u);
-            } else {
-                o = f32_to_bf16_bits(s[0]);
-            }
-            C[(size_t)r * N + col0 + threadIdx.x] = o;
+    }
+    if (KS > 1) {
+        const size_t cell = (size_t)r * gridDim.x + blockIdx.x;
+        float* wsp = split_ws + cell * KS * NMAT * TILE;
+        if (threadIdx.x < TILE) {
+#pragma unroll
+            for (int m = 0; m < NMAT; ++m) __stcg(wsp + ((size_t)kz * NMAT + m) * TILE + threadIdx.x, s[m]);
         }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            s_ticket = atomicAdd(split_cnt + cell, 1u);
+            __threadfence();
+        }
+        __syncthreads();
+        if (s_ticket != (unsigned)(KS - 1)) return;
+        if (threadIdx.x < TILE) {
+#pragma unroll
+            for (int m = 0; m < NMAT; ++m) {
+                float t = 0.f;
+                for (int zz = 0; zz < KS; ++zz) t += __ldcg(wsp + ((size_t)zz * NMAT + m) * TILE + threadIdx.x);
+                s[m] = t;
+            }
+        }
+        if (threadIdx.x == 0) split_cnt[cell] = 0;
+    }
+    if (threadIdx.x < TILE && col0 + threadIdx.x < N) {
+        uint16_t o;
+        if (NMAT == 2) {
+            const float g = bf16_bits_to_f32(f32_to_bf16_bits(s[0]));
+            const float u = bf16_bits_to_f32(f32_to_bf16_bits(s[NMAT - 1]));
+            o = f32_to_bf16_bits(bf16_bits_to_f32(f32_to_bf16_bits(silu_ref(g))) * u);
+        } else {
+            o = f32_to_bf16_bits(s[0]);
+        }
+        C[(size_t)r * N + col0 + threadIdx.x] = o;
     }
 }
 
@@ -532,6 +565,9 @@ __global__ void moe_combine_t1_kernel(const uint16_t* __restrict__ expert_out, c
 
 static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
+static float* g_moe_split_ws = nullptr;
+static unsigned* g_moe_split_cnt = nullptr;
+
 template <int NMAT, int CPL>
 static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
                                const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
@@ -545,10 +581,36 @@ static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, con
         PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr = true;
     }
+    // K split: when rows x column tiles cover less than half of the SMs, spread the scale blocks of every cell over up
+    // to 4 CTAs (each keeps >= 16 blocks = one per warp).  The workspace is allocated on the first call made outside
+    // graph capture; until then (and when it would not fit) the kernel runs unsplit.  PGK_MOE_NVF4_KS=1 disables.
+    float*& ws = g_moe_split_ws;          // shared by all instantiations: allocated by whichever runs first (prefill, eager)
+    unsigned*& cnt = g_moe_split_cnt;
+    static const int ks_max = [] { const char* e = getenv("PGK_MOE_NVF4_KS"); int v = e ? atoi(e) : 4; return v < 1 ? 1 : (v > 8 ? 8 : v); }();
+    constexpr size_t kCells = 128, kWsFloats = kCells * 8 * 2 * 128;       // split only when cells * 2 <= SM count
+    const int tiles = (N + TILE - 1) / TILE;
+    if (!ws) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        cudaStreamIsCapturing((cudaStream_t)stream, &cs);
+        if (cs == cudaStreamCaptureStatusNone) {
+            PGK_CUDA(cudaMalloc(&ws, kWsFloats * sizeof(float)));
+            PGK_CUDA(cudaMalloc(&cnt, kCells * sizeof(unsigned)));
+            PGK_CUDA(cudaMemset(cnt, 0, kCells * sizeof(unsigned)));
+        }
+    }
+    int ks = 1;
+    const long cells = (long)tiles * M;
+    if (ws && cells * 2 <= sm_count() && cells <= (long)kCells) {
+        ks = (int)(sm_count() / cells);
+        if (ks > ks_max) ks = ks_max;
+        const int kb = K >> 5;
+        while (ks > 1 && kb / ks < kMoeNvf4Warps) --ks;
+    }
     auto kern = rt.logits ? moe_grouped_gemv_nvf4_kernel<NMAT, CPL, true> : moe_grouped_gemv_nvf4_kernel<NMAT, CPL, false>;
-    PGK_CUDA(launch(kern, dim3((N + TILE - 1) / TILE, M), dim3(kMoeNvf4Warps * 32), smem,
+    PGK_CUDA(launch(kern, dim3(tiles, M, ks), dim3(kMoeNvf4Warps * 32), smem,
                     (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
-                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts, rt));
+                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts, rt,
+                    ws, cnt));
     return 0;
 }
 template <int NMAT>
