@@ -71,12 +71,6 @@ int pgk_graph_destroy(void* graph_exec);
 
 /* programmatic dependent launch on/off for all subsequent launches (default off) */
 int pgk_set_pdl(int enabled);
-/* Cross-kernel HBM pipelining (net-new): name the head of the weights that FOLLOWING launches will stream
- * (n <= 4 regions of device memory; host arrays of pointers / byte counts).  The next GEMV / attention
- * launch made by the calling thread prefetches those bytes into L2 (cp.async.bulk.prefetch.L2): the
- * attention kernel is latency-bound and leaves the DRAM pipe idle, so the o_proj / gate / up weights ride in
- * behind its K/V tiles and the GEMVs that follow are fed from L2.  One-shot: consumed by that launch. */
-int pgk_prefetch_hint(const void* const* host_regions, const size_t* host_bytes, int n);
 /* number of kernels this library has launched since load (or since reset) */
 int64_t pgk_launch_count(void);
 void pgk_launch_count_reset(void);
@@ -309,16 +303,6 @@ int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, con
 int pgk_moe_gateup_nvf4_t1(const void* x, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
                            const void* Bu_scale, void* act, const int32_t* row_expert_ids, int k, int K, int N,
                            int expert_offset, int num_local_experts, void* stream);
-/* route_t1 folded into the gate/up launch: every warp recomputes the routing from the router logits (~1 us) and the
- * first warp publishes weights / indices / row_expert_ids for the launches that follow -- one launch less per layer */
-int pgk_moe_route_gateup_fp8_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
-                                int32_t* row_expert_ids, const void* Bg_enk, const void* Sg, const void* Bu_enk,
-                                const void* Su, void* act, int k, int K, int N, int expert_offset,
-                                int num_local_experts, void* stream);
-int pgk_moe_route_gateup_nvf4_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
-                                 int32_t* row_expert_ids, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
-                                 const void* Bu_scale, void* act, int k, int K, int N, int expert_offset,
-                                 int num_local_experts, void* stream);
 int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
                                 int expert_offset, int num_local_experts, void* stream);
@@ -354,6 +338,8 @@ size_t pgk_p2p_handle_bytes(void);
 int pgk_p2p_create(int rank, int world, void* host_handle_out);
 int pgk_p2p_open(const void* host_handles_all);
 int pgk_p2p_ready(void);
+/* largest message in bytes that pgk_p2p_allreduce_add_bf16 accepts (callers fall back to NCCL above it) */
+size_t pgk_p2p_max_bytes(void);
 int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream);
 int pgk_p2p_error(int* host_flag);
 int pgk_p2p_destroy(void);

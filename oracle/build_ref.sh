@@ -31,3 +31,12 @@ if [ ! -f "$h" ] || [ "$HERE/ref_harness.cu" -nt "$h" ]; then nvcc "${FLAGS[@]}"
 wait
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT/libref_cuda.so" "${OBJS[@]}" "$h"
 echo "built $OUT/libref_cuda.so"
+# The reference's pure-Python package, as it lies, for bench.py's config-1 CPU leg (GPT-2 small through the
+# reference's own CausalTransformerModel.generate on its CPUSimulationBackend).  oracle/_ref/ is git-ignored
+# (never part of this repo's history) but travels to the GPU box, where /root/reference does not exist.
+if [ -d "$REF/src/pygpukit" ]; then
+  rm -rf "$OUT/pysrc"; mkdir -p "$OUT/pysrc"
+  cp -r "$REF/src/pygpukit" "$OUT/pysrc/pygpukit"
+  find "$OUT/pysrc" -name '__pycache__' -type d -prune -exec rm -rf {} +
+  echo "staged $OUT/pysrc/pygpukit"
+fi

@@ -14,7 +14,7 @@
  * functions (llm/quant.py, ops/nn/*.py _cpu branches, llm/layers/rope.py,
  * llm/sampling.py) by tests/golden/make_golden.py; (2) the reference's CUDA kernels
  * themselves, compiled in place by oracle/build_ref.sh into oracle/_ref/libref_cuda.so
- * and run on the B200 next to this oracle in tests/test_parity_gpu.py.
+ * and run on the B200 next to this oracle in tests/test_gpu_gemv.py / tests/test_gpu_nn.py.
  *
  * Known, documented deviations from the reference build (native/CMakeLists.txt:122
  * uses --use_fast_math): expf / division here are IEEE; the CUDA reference uses
@@ -163,6 +163,15 @@ int orc_num_threads(void) {
     return omp_get_max_threads();
 #else
     return 1;
+#endif
+}
+
+/* bench.py's CPU legs set the team size themselves: torchrun exports OMP_NUM_THREADS=1 to every rank */
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n >= 1) omp_set_num_threads(n);
+#else
+    (void)n;
 #endif
 }
 

@@ -49,6 +49,12 @@ def num_threads() -> int:
     return int(lib().orc_num_threads())
 
 
+def set_num_threads(n: int) -> int:
+    """OpenMP team size for every later call (bench.py: all host cores, whatever OMP_NUM_THREADS says)."""
+    lib().orc_set_num_threads(int(n))
+    return num_threads()
+
+
 def fp8_table() -> np.ndarray:
     t = np.empty(256, np.float32)
     lib().orc_fp8_e4m3_table(_p(t))

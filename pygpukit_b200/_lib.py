@@ -74,7 +74,6 @@ _SIGS = {
     "pgk_kv_cache_update": [vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, vp],
     "pgk_qk_norm_rope_kv_write": [vp, vp, vp, f32, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp],
     "pgk_gemm_fp8_bf16_tc": [vp, vp, vp, vp, i32, i32, i32, vp, vp, vp],
-    "pgk_prefetch_hint": [vp, vp, i32],
     "pgk_rope_sdpa_decode": [vp, vp, vp, f32, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i32, vp, f32, vp],
     "pgk_sdpa_decode": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, f32, cl, cl, cl, cl, i32, vp],
     "pgk_moe_topk": [vp, vp, vp, i32, i32, i32, i32, vp],
@@ -91,8 +90,6 @@ _SIGS = {
     "pgk_moe_route_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_moe_gateup_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_gateup_nvf4_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
-    "pgk_moe_route_gateup_fp8_t1": [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
-    "pgk_moe_route_gateup_nvf4_t1": [vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_down_combine_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_moe_combine_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
@@ -105,9 +102,10 @@ _SIGS = {
     "pgk_p2p_error": [vp], "pgk_p2p_destroy": [],
 }
 _RESTYPE = {"pgk_last_error": C.c_char_p, "pgk_launch_count": i64, "pgk_launch_count_reset": None,
-            "pgk_sdpa_workspace_bytes": sz, "pgk_p2p_handle_bytes": sz, "pgk_p2p_ready": i32}
+            "pgk_sdpa_workspace_bytes": sz, "pgk_p2p_handle_bytes": sz, "pgk_p2p_ready": i32,
+            "pgk_p2p_max_bytes": sz}
 _EXTRA = {"pgk_last_error": [], "pgk_launch_count": [], "pgk_launch_count_reset": [],
-          "pgk_sdpa_workspace_bytes": [i32, i32, i32, i32], "pgk_p2p_handle_bytes": [], "pgk_p2p_ready": []}
+          "pgk_sdpa_workspace_bytes": [i32, i32, i32, i32], "pgk_p2p_handle_bytes": [], "pgk_p2p_ready": [], "pgk_p2p_max_bytes": []}
 
 
 def load() -> C.CDLL:

@@ -401,7 +401,6 @@ struct RopeSdpaParams {
     float scale_log2;
     int splits;
     float* ws; unsigned* counters;
-    PrefetchHint next;                         // head of the o_proj weights
 };
 constexpr int kFTile = 64;       // KV positions per staged tile (16 KB K + 16 KB V)
 constexpr int kFStages = 2;
@@ -480,11 +479,6 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
         for (int i = 0; i < kFStages; ++i) mbar_init(&full_bar[i], 1);
         mbar_fence_init();
         for (int t = 0; t < min(ntiles, kFStages); ++t) issue_tile(t);
-    }
-    {   // this kernel is latency-bound (16 MB of K/V, a dependent chain of round trips): let the DRAM pipe
-        // carry the weights of the GEMVs that follow into L2 meanwhile (weights never depend on earlier kernels)
-        const long cta = ((long)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        l2_prefetch_share(p.next, cta * blockDim.x + threadIdx.x, (long)gridDim.x * gridDim.y * gridDim.z * blockDim.x);
     }
     // rotation tables and norm weights of this warp's head: constants, requested before the wait as well
     float rc[2] = {1.f, 1.f}, rs[2] = {0.f, 0.f}, rg[4] = {1.f, 1.f, 1.f, 1.f};
@@ -812,7 +806,6 @@ int pgk_rope_sdpa_decode(const void* qkv, const void* q_gamma, const void* k_gam
     p.hq = n_heads_q; p.n_kv = n_kv; p.max_seq = max_seq; p.pos = pos; p.context_len = context_len;
     p.pos_buf = pos_buf; p.ctx_buf = ctx_buf;
     p.scale_log2 = scale * 1.4426950408889634f;
-    p.next = take_prefetch_hint();
     return launch_rope_sdpa(p, (cudaStream_t)stream);
 }
 

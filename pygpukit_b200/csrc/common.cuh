@@ -16,16 +16,12 @@ void count_launch(int n = 1);
 bool pdl_enabled();
 int  sm_count();
 
-// "What streams next": the head of the weights that FOLLOWING kernels will stream (up to four regions),
-// prefetched into L2 by a kernel that leaves the DRAM pipe idle (the latency-bound attention kernel, or a
-// GEMV whose own weights already sit in L2), so HBM keeps streaming across kernel boundaries.  Set by
-// pgk_prefetch_hint(), consumed (and cleared) by the next GEMV / attention launch of the calling thread.
-constexpr unsigned kPrefetchPiece = 4096;
-struct PrefetchHint {
-    const unsigned char* p[4] = {nullptr, nullptr, nullptr, nullptr};
-    unsigned pieces[4] = {0, 0, 0, 0};     // kPrefetchPiece-byte pieces per region
-};
-PrefetchHint take_prefetch_hint();
+// E4M3 codes 0x7F / 0xFF: +-480 in the reference's CUDA tables (fp8.cuh:89,121) but NaN for the hardware conversion
+// (cvt.rn.f16x2.e4m3x2) the streaming kernels use.  Every FP8 weight tensor is scanned ONCE, at its first use
+// (outside graph capture), and remembered by base pointer: tensors that hold such codes are served by the exact
+// table-semantics kernel, so one entry point gives one answer.  pgk_free() forgets the pointer.
+int  fp8_codes_clean(const void* codes, size_t nbytes, cudaStream_t st, bool* clean);
+void fp8_codes_forget(const void* base);
 
 
 #define PGK_CUDA(call)                                                        \
@@ -80,14 +76,6 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-// fire-and-forget L2 prefetch of this thread's share of the hinted regions (cp.async.bulk.prefetch.L2)
-__device__ __forceinline__ void l2_prefetch_share(const PrefetchHint& h, long gthread, long nthreads) {
-#pragma unroll
-    for (int r = 0; r < 4; ++r)
-        for (long i = gthread; i < (long)h.pieces[r]; i += nthreads)
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(h.p[r] + i * kPrefetchPiece), "n"(kPrefetchPiece) : "memory");
-}
-
 __device__ __forceinline__ float bf16_bits_to_f32(uint32_t h) { return __uint_as_float(h << 16); }
 __device__ __forceinline__ float bf16lo(uint32_t p) { return __uint_as_float(p << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
@@ -120,6 +108,18 @@ __device__ __forceinline__ u32x8 ldg_stream256(const void* p) {
                  : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]),
                    "=r"(r.v[6]), "=r"(r.v[7]) : "l"(p));
     return r;
+}
+// activations written by the kernel just before this one (programmatic dependent launch: this kernel's lifetime
+// overlaps its producer's, so the read-only .nc path is formally off limits for them): coherent, L2-cached loads
+__device__ __forceinline__ uint4 ld_act16(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint16_t ld_act2(const uint16_t* p) {
+    uint16_t v;
+    asm volatile("ld.global.cg.u16 %0, [%1];" : "=h"(v) : "l"(p));
+    return v;
 }
 __device__ __forceinline__ uint4 ldg_stream(const void* p) {
     uint4 v;

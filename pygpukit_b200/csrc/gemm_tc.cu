@@ -414,5 +414,9 @@ int gemm_fp8_tc(const void* A, const void* B_nk, const void* S, void* C, int M, 
 
 extern "C" int pgk_gemm_fp8_bf16_tc(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N,
                                     const void* bias, const void* residual, void* stream) {
+    bool clean = true;
+    if (int rc = pgk::fp8_codes_clean(B_nk, (size_t)N * K, (cudaStream_t)stream, &clean)) return rc;
+    PGK_REQUIRE(clean, "gemm_fp8_bf16_tc failed: the weights hold E4M3 codes 0x7F/0xFF (+-480 in the reference's tables, "
+                "NaN for the tensor-core conversion); use pgk_gemv_fp8_bf16, which serves them exactly");
     return pgk::gemm_fp8_tc(A, B_nk, S, C, M, K, N, bias, residual, (cudaStream_t)stream);
 }

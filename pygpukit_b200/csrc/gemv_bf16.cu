@@ -35,7 +35,7 @@ __device__ __forceinline__ void stage_activations_bf16(const uint16_t* __restric
         const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
         uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)m * K);
         for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
-            uint4 v = __ldg(src + j);
+            uint4 v = ld_act16(src + j);
             if (gamma) v = norm8_bf16(v, __ldg(gv + j), rinv[m]);
             dst[(j & 1) * nchunk + (j >> 1)] = v;
         }
@@ -86,7 +86,6 @@ gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
         }
     };
     if (row_begin < N) load_group(row_begin, 0);
-    l2_prefetch_share(epi.next, gwarp * 32 + lane, nwarps * 32);
     griddep_wait();
     griddep_launch();
     stage_activations_bf16<M>(A, K, a_s, epi.norm_gamma, epi.norm_eps);
@@ -227,7 +226,6 @@ static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, in
     const bool fast = (K % 16 == 0) && al(A, 16) && al(B, 32) && ((size_t)K * 2 <= 200 * 1024);
     PGK_REQUIRE(!gamma || (fast && K >= 512 && al(gamma, 16)),
                 "rmsnorm_gemv_bf16 failed: the fused norm needs K %% 16 == 0, K >= 512 and aligned pointers (K=%d)", K);
-    const PrefetchHint hint = take_prefetch_hint();   // one-shot, whichever path runs
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
         long warps = (long)N * M;
@@ -242,7 +240,6 @@ static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, in
         if (mt == 3) mt = 2;
         GemvEpilogue epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
                             (const uint16_t*)gamma, eps};
-        if (m0 + mt >= M) epi.next = hint;
         int rc;
         if (mt == 1)      rc = launch_bf16<1, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
         else if (mt == 2) rc = launch_bf16<2, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
@@ -271,7 +268,6 @@ int pgk_gemv_bf16_argmax(const void* A, const void* B_nk, void* logits, int32_t*
     PGK_REQUIRE(K % 16 == 0 && al(A, 16) && al(B_nk, 32) && (size_t)K * 2 <= 200 * 1024,
                 "gemv_bf16_argmax failed: needs K%%16==0 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr};
-    epi.next = take_prefetch_hint();
     return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
 }
@@ -286,7 +282,6 @@ int pgk_rmsnorm_gemv_bf16_argmax(const void* A, const void* gamma, float eps, co
     PGK_REQUIRE(K % 16 == 0 && K >= 512 && al(A, 16) && al(B_nk, 32) && al(gamma, 16) && (size_t)K * 2 <= 200 * 1024,
                 "rmsnorm_gemv_bf16_argmax failed: needs K%%16==0, K>=512 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr, (const uint16_t*)gamma, eps};
-    epi.next = take_prefetch_hint();
     return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
 }

@@ -40,7 +40,6 @@ struct GemvEpilogue {
     const uint16_t* residual;  // [M,N] bf16 or null
     const uint16_t* norm_gamma = nullptr;  // [K] bf16: A <- bf16(rmsnorm(A) * gamma) while staging, or null
     float norm_eps = 0.f;
-    PrefetchHint next;                     // head of the next kernel's weights (L2 prefetch as warps drain)
 };
 
 // ---- fused RMSNorm prologue -------------------------------------------------------------------
@@ -60,12 +59,12 @@ __device__ __forceinline__ float row_inv_rms_ref_order(const uint16_t* __restric
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
             const int i = v + e * bs;
-            xv[e] = (i < K) ? bf16_bits_to_f32(__ldg(row + i)) : 0.f;
+            xv[e] = (i < K) ? bf16_bits_to_f32(ld_act2(row + i)) : 0.f;
         }
         float part = 0.f;
 #pragma unroll
         for (int e = 0; e < 16; ++e) part = fmaf(xv[e], xv[e], part);
-        for (int i = v + 16 * bs; i < K; i += bs) { float x = bf16_bits_to_f32(__ldg(row + i)); part = fmaf(x, x, part); }
+        for (int i = v + 16 * bs; i < K; i += bs) { float x = bf16_bits_to_f32(ld_act2(row + i)); part = fmaf(x, x, part); }
         scratch[v] = part;
     }
     __syncthreads();
@@ -112,7 +111,7 @@ __device__ __forceinline__ void stage_activations_f16_3pass(const uint16_t* __re
     for (int m = 0; m < M; ++m) {
         const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
         for (int j = tid; j < nvec; j += nthr) {
-            uint4 v = __ldg(src + j);
+            uint4 v = ld_act16(src + j);
             if (gamma) v = norm8_bf16(v, __ldg(gv + j), rinv[m]);
             uint32_t t = __vmaxu2(__vmaxu2(v.x & 0x7fff7fffu, v.y & 0x7fff7fffu),
                                   __vmaxu2(v.z & 0x7fff7fffu, v.w & 0x7fff7fffu));
@@ -143,7 +142,7 @@ __device__ __forceinline__ void stage_activations_f16_3pass(const uint16_t* __re
         const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)m * K);
         uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)m * K);
         for (int j = tid; j < nvec; j += nthr) {
-            uint4 v = __ldg(src + j);
+            uint4 v = ld_act16(src + j);
             if (gamma) v = norm8_bf16(v, __ldg(gv + j), rinv[m]);
             uint4 o;
             __half2 h;
@@ -198,7 +197,7 @@ __device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict
         for (int e = 0; e < VY; ++e) {
             const int j = tid + e * nthr;
             if (j < nvec) {
-                v[e] = __ldg(src + j);
+                v[e] = ld_act16(src + j);
                 if (gamma) g[e] = __ldg(gv + j);
             }
         }

@@ -37,6 +37,54 @@ int gemm_fp8_tc(const void* A, const void* B_nk, const void* S, void* C, int M, 
 
 constexpr int kUnroll = 4;
 
+// ---- one-time scan of a weight tensor for the codes the hardware conversion decodes differently (see common.cuh)
+__global__ void fp8_scan_codes_kernel(const uint8_t* __restrict__ B, size_t n, unsigned* __restrict__ flag) {
+    const size_t nvec = n >> 4, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
+    unsigned hit = 0;
+    if ((reinterpret_cast<uintptr_t>(B) & 15) == 0) {
+        for (size_t i = tid; i < nvec; i += nthr) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(B) + i);
+            // a byte whose low seven bits are all ones carries into bit 7 when 1 is added (no carry crosses bytes)
+            hit |= ((v.x & 0x7f7f7f7fu) + 0x01010101u) | ((v.y & 0x7f7f7f7fu) + 0x01010101u) |
+                   ((v.z & 0x7f7f7f7fu) + 0x01010101u) | ((v.w & 0x7f7f7f7fu) + 0x01010101u);
+        }
+        for (size_t i = (nvec << 4) + tid; i < n; i += nthr) hit |= ((B[i] & 0x7fu) == 0x7fu) ? 0x80u : 0u;
+    } else {
+        for (size_t i = tid; i < n; i += nthr) hit |= ((B[i] & 0x7fu) == 0x7fu) ? 0x80u : 0u;
+    }
+    if (hit & 0x80808080u) atomicOr(flag, 1u);
+}
+
+static std::mutex g_scan_mu;
+static std::unordered_map<const void*, bool> g_scan_clean;
+static unsigned* g_scan_flag = nullptr;
+
+int fp8_codes_clean(const void* codes, size_t nbytes, cudaStream_t st, bool* clean) {
+    std::lock_guard<std::mutex> lk(g_scan_mu);
+    auto it = g_scan_clean.find(codes);
+    if (it != g_scan_clean.end()) { *clean = it->second; return 0; }
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cs);
+    PGK_REQUIRE(cs == cudaStreamCaptureStatusNone,
+                "gemv_fp8_bf16 failed: the first use of an FP8 weight tensor must happen outside graph capture (one-time code scan)");
+    if (!g_scan_flag) PGK_CUDA(cudaMalloc(&g_scan_flag, sizeof(unsigned)));
+    PGK_CUDA(cudaMemsetAsync(g_scan_flag, 0, sizeof(unsigned), st));
+    const size_t want = (nbytes / 16 + 255) / 256;
+    const unsigned grid = (unsigned)(want < 1 ? 1 : (want > 4096 ? 4096 : want));
+    fp8_scan_codes_kernel<<<grid, 256, 0, st>>>((const uint8_t*)codes, nbytes, g_scan_flag);
+    PGK_LAUNCH_CHECK("fp8_scan_codes");
+    unsigned h = 0;
+    PGK_CUDA(cudaMemcpyAsync(&h, g_scan_flag, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    PGK_CUDA(cudaStreamSynchronize(st));
+    *clean = (h == 0);
+    g_scan_clean.emplace(codes, *clean);
+    return 0;
+}
+void fp8_codes_forget(const void* base) {
+    std::lock_guard<std::mutex> lk(g_scan_mu);
+    g_scan_clean.erase(base);
+}
+
 // 8 e4m3 weights (two 32-bit words) x 8 staged f16 activations (one uint4)
 __device__ __forceinline__ void dot8_e4m3(float& s0, float& s1, uint32_t w0, uint32_t w1, const uint4& a) {
     uint32_t h;
@@ -55,129 +103,8 @@ __device__ __forceinline__ float dot32_e4m3(const u32x8& w, const uint4* ap, int
 
 // NMAT = 1: plain GEMV; NMAT = 2: gate/up pair with SiLU*up epilogue.
 //
-// Work = the sequence of "groups" (row n, chunk block cb) of this warp: rows n = gwarp, gwarp + nwarps, ...
-// (round-robin over the warps of the grid: at any moment the grid streams one contiguous band of the matrix),
-// inside a row blocks of 32*U chunks of 32 weights.  Two groups are in flight per warp (register double
-// buffer, 2 x U x 256-bit loads per lane = 8 KB per warp, ~96 KB per SM), and BOTH are requested before
-// griddepcontrol.wait -- weights never depend on the previous kernel -- so under PDL the first ~14 MB of
-// the matrix are already on their way while the predecessor drains and the activations are staged.
-template <int M, int NMAT, int UT, int MAXW>
-__global__ void __launch_bounds__(MAXW * 32)
-gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
-                const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
-                const uint16_t* __restrict__ S1, uint16_t* __restrict__ C, int K, int N, int rho,
-                GemvEpilogue epi) {
-    constexpr int U = UT / NMAT;   // 256-bit loads per lane per matrix per group
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    __half* a_s = reinterpret_cast<__half*>(smem_raw);
-    float* inv_s = reinterpret_cast<float*>(smem_raw + (size_t)M * K * 2);
-    uint32_t* red = reinterpret_cast<uint32_t*>(inv_s + 8);
-
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    const int wpc = blockDim.x >> 5;
-    const long gwarp = (long)blockIdx.x * wpc + warp;
-    const long nwarps = (long)gridDim.x * wpc;
-    const int nchunk = K >> 5;
-    const int SK = (K + 127) >> 7;
-    (void)rho;
-
-    struct Buf { u32x8 w[NMAT][U]; };
-    Buf bufA, bufB;
-    auto load_group = [&](Buf& b, long n, int cb) {
-        if (n >= N) return;
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            int c = cb + lane + 32 * u;
-            if (c < nchunk) {
-                b.w[0][u] = ldg_stream256(B0 + (size_t)n * K + (size_t)c * 32);
-                if (NMAT == 2) b.w[NMAT - 1][u] = ldg_stream256(B1 + (size_t)n * K + (size_t)c * 32);
-            }
-        }
-    };
-    auto advance = [&](long& n, int& cb) {
-        cb += 32 * U;
-        if (cb >= nchunk) { cb = 0; n += nwarps; }
-    };
-    long nA = gwarp; int cbA = 0;
-    long nB = nA; int cbB = cbA;
-    advance(nB, cbB);
-    load_group(bufA, nA, cbA);
-    load_group(bufB, nB, cbB);
-    l2_prefetch_share(epi.next, gwarp * 32 + lane, nwarps * 32);   // only hinted when this launch is L2-fed itself
-    griddep_wait();
-    griddep_launch();
-    stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
-
-    const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
-    float acc[NMAT][M];
-#pragma unroll
-    for (int t = 0; t < NMAT; ++t)
-#pragma unroll
-        for (int m = 0; m < M; ++m) acc[t][m] = 0.f;
-
-    auto compute_group = [&](const Buf& b, int n, int cb) {
-        const uint16_t* s0 = S0 + (size_t)(n >> 7) * SK;
-        const uint16_t* s1 = (NMAT == 2) ? S1 + (size_t)(n >> 7) * SK : nullptr;
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            int c = cb + lane + 32 * u;
-            if (c < nchunk) {
-                float sc0 = bf16_bits_to_f32(__ldg(s0 + (c >> 2)));
-                float sc1 = (NMAT == 2) ? bf16_bits_to_f32(__ldg(s1 + (c >> 2))) : 0.f;
-#pragma unroll
-                for (int m = 0; m < M; ++m) {
-                    const uint4* ap = a_lo + (size_t)m * (K >> 3);
-                    acc[0][m] = fmaf(dot32_e4m3(b.w[0][u], ap, nchunk, c), sc0, acc[0][m]);
-                    if (NMAT == 2)
-                        acc[NMAT - 1][m] = fmaf(dot32_e4m3(b.w[NMAT - 1][u], ap, nchunk, c), sc1, acc[NMAT - 1][m]);
-                }
-            }
-        }
-    };
-    auto finish_row = [&](int n) {
-#pragma unroll
-        for (int t = 0; t < NMAT; ++t)
-#pragma unroll
-            for (int m = 0; m < M; ++m) acc[t][m] = warp_sum(acc[t][m]);
-        if (lane == 0) {
-#pragma unroll
-            for (int m = 0; m < M; ++m) {
-                float v = acc[0][m] * inv_s[m];
-                size_t o = (size_t)m * N + n;
-                if (NMAT == 2) {
-                    float g = round_bf16(v);
-                    float u = round_bf16(acc[NMAT - 1][m] * inv_s[m]);
-                    float s = round_bf16(silu_ref(g));
-                    C[o] = f32_to_bf16_bits(s * u);
-                } else {
-                    if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
-                    C[o] = epi.residual ? hadd_bf16_bits(v, epi.residual[o]) : f32_to_bf16_bits(v);
-                }
-            }
-        }
-#pragma unroll
-        for (int t = 0; t < NMAT; ++t)
-#pragma unroll
-            for (int m = 0; m < M; ++m) acc[t][m] = 0.f;
-    };
-
-    while (nA < N) {
-        compute_group(bufA, (int)nA, cbA);
-        const int doneA = (cbA + 32 * U >= nchunk) ? (int)nA : -1;
-        nA = nB; cbA = cbB; advance(nA, cbA);            // the group after B refills buffer A
-        load_group(bufA, nA, cbA);
-        if (doneA >= 0) finish_row(doneA);
-        if (nB >= N) break;
-        compute_group(bufB, (int)nB, cbB);
-        const int doneB = (cbB + 32 * U >= nchunk) ? (int)nB : -1;
-        nB = nA; cbB = cbA; advance(nB, cbB);
-        load_group(bufB, nB, cbB);
-        if (doneB >= 0) finish_row(doneB);
-    }
-}
-
-// Single-buffered variant: one group (U x 256-bit loads per lane) in flight per warp, up to 16 warps per CTA.
+// One group (U x 256-bit loads per lane) in flight per warp, up to 16 warps per CTA.  (A register double-buffered
+// form was measured slower on B200 -- 168 registers cap the CTA at 12 warps -- see profiles/r01_*; removed.)
 template <int M, int NMAT>
 __global__ void __launch_bounds__(512)
 gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
@@ -218,7 +145,6 @@ gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B
     };
     // weights never depend on the previous kernel: start pulling the first row now
     if (row_begin < N) load_group(row_begin, 0);
-    l2_prefetch_share(epi.next, gwarp * 32 + lane, nwarps * 32);   // only hinted when this launch is L2-fed itself
     griddep_wait();
     griddep_launch();
     stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
@@ -320,14 +246,6 @@ __global__ void gemv_fp8_generic_kernel(const uint16_t* __restrict__ A, const ui
     }
 }
 
-// PGK_GEMV_VARIANT: 0 = single buffer (default), 1 = double buffer U=4 / 12 warps, 2 = double buffer U=2 / 16 warps,
-// 3 = double buffer U=4 / 14 warps (register-capped at 146)
-static int gemv_variant() {
-    static int v = -1;
-    if (v < 0) { const char* e = getenv("PGK_GEMV_VARIANT"); v = e ? atoi(e) : 0; }
-    return v;
-}
-
 template <typename Kern>
 static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void* B0, const void* S0, const void* B1,
                            const void* S1, void* C, int K, int N, GemvEpilogue epi, cudaStream_t st,
@@ -364,13 +282,9 @@ static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void
 template <int M, int NMAT>
 static int launch_fp8(const void* A, const void* B0, const void* S0, const void* B1, const void* S1,
                       void* C, int K, int N, GemvEpilogue epi, cudaStream_t st) {
-    static std::unordered_map<uint64_t, GemvCfg> cache[4];
-    static bool attr[4] = {false, false, false, false};
-    const int v = gemv_variant();
-    if (v == 1) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 4, 12>, 12, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[1], attr[1]);
-    if (v == 3) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 4, 14>, 14, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[3], attr[3]);
-    if (v == 2) return launch_fp8_kern(gemv_fp8_kernel<M, NMAT, 2, 16>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[2], attr[2]);
-    return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache[0], attr[0]);
+    static std::unordered_map<uint64_t, GemvCfg> cache;
+    static bool attr = false;
+    return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache, attr);
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -383,16 +297,22 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
                              const void* residual, bool swiglu, cudaStream_t st, const void* gamma = nullptr,
                              float eps = 0.f) {
     PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_fp8_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
-    const bool fast = (K % 32 == 0) && aligned16(A) && aligned32(B0) && (!swiglu || aligned32(B1)) &&
-                      ((size_t)K * 2 + 1024 <= 200 * 1024);
+    bool fast = (K % 32 == 0) && aligned16(A) && aligned32(B0) && (!swiglu || aligned32(B1)) &&
+                ((size_t)K * 2 + 1024 <= 200 * 1024);
+    // weights holding codes 0x7F / 0xFF keep the reference's table semantics (+-480): exact kernel, never the cvt path
+    bool clean = true;
+    if (int rc = fp8_codes_clean(B0, (size_t)N * K, st, &clean)) return rc;
+    if (clean && swiglu) { if (int rc = fp8_codes_clean(B1, (size_t)N * K, st, &clean)) return rc; }
+    PGK_REQUIRE(clean || !gamma, "rmsnorm_gemv_fp8_bf16 failed: weights with E4M3 codes 0x7F/0xFF take the exact path, "
+                "which has no fused norm (run pgk_rmsnorm first)");
+    if (!clean) fast = false;
     const uint16_t* a = (const uint16_t*)A;
     uint16_t* c = (uint16_t*)C;
     PGK_REQUIRE(!gamma || (fast && K >= 512 && aligned16(gamma)),
                 "rmsnorm_gemv_fp8_bf16 failed: the fused norm needs K %% 32 == 0, K >= 512 and aligned pointers (K=%d)", K);
-    const PrefetchHint hint = take_prefetch_hint();   // one-shot, whichever path runs
     // decode batch >= 5 (PGK_TC_MIN_M): the weight-streaming tensor-core GEMM (PGK_TC=0 keeps the slab GEMV for A/B timing)
     static const bool tc_on = !(getenv("PGK_TC") && atoi(getenv("PGK_TC")) == 0);
-    if (tc_on && !swiglu && !gamma && gemm_fp8_tc_eligible(M, K, N, A, B0))
+    if (tc_on && clean && !swiglu && !gamma && gemm_fp8_tc_eligible(M, K, N, A, B0))
         return gemm_fp8_tc(A, B0, S0, C, M, K, N, bias, residual, st);
     if (!fast) {
         GemvEpilogue epi = {(const uint16_t*)bias, (const uint16_t*)residual};
@@ -419,7 +339,6 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
         GemvEpilogue epi = {(const uint16_t*)bias,
                             residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
                             (const uint16_t*)gamma, eps};
-        if (m0 + mt >= M) epi.next = hint;
         const uint16_t* am = a + (size_t)m0 * K;
         uint16_t* cm = c + (size_t)m0 * N;
         int rc = 0;

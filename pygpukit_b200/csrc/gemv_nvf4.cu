@@ -356,7 +356,6 @@ static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) =
 static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C, int M, int K, int N,
                          float alpha, const void* bias, const void* residual, bool swiglu,
                          cudaStream_t st, const void* gamma = nullptr, float eps = 0.f) {
-    (void)take_prefetch_hint();   // column-panel streaming: the prefix hint does not apply (one-shot, dropped)
     PGK_REQUIRE(M >= 1 && K >= 1 && N >= 1, "gemv_nvf4_bf16 failed: invalid shape M=%d K=%d N=%d", M, K, N);
     const bool fast = (K % 32 == 0) && (N % 16 == 0) && al16(A) && al16(Bd) && al16(Bs) &&
                       ((size_t)K * 2 + kNvf4Hdr <= 200 * 1024);

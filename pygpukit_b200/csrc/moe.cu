@@ -142,8 +142,8 @@ __device__ __forceinline__ void fp8_rows_dot(const uint16_t* __restrict__ arow, 
     if ((K & 15) == 0) {
 #pragma unroll 4
         for (int c = lane; c < (K >> 4); c += 32) {
-            uint4 a0 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16));
-            uint4 a1 = __ldg(reinterpret_cast<const uint4*>(arow + c * 16 + 8));
+            uint4 a0 = ld_act16(arow + c * 16);
+            uint4 a1 = ld_act16(arow + c * 16 + 8);
             const uint32_t aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
             for (int b = 0; b < NB; ++b) {
@@ -156,6 +156,12 @@ __device__ __forceinline__ void fp8_rows_dot(const uint16_t* __restrict__ arow, 
                     uint32_t h0 = e4m3x2_to_f16x2_lo(ww[q]), h1 = e4m3x2_to_f16x2_hi(ww[q]);
                     float2 f0 = __half22float2(*reinterpret_cast<__half2*>(&h0));
                     float2 f1 = __half22float2(*reinterpret_cast<__half2*>(&h1));
+                    // codes 0x7F / 0xFF are +-480 in the reference's tables (fp8.cuh:89,121), NaN for the hardware
+                    // conversion: a byte whose low seven bits are all ones carries into bit 7 when 1 is added
+                    if (((ww[q] & 0x7f7f7f7fu) + 0x01010101u) & 0x80808080u) {
+                        f0.x = fp8_e4m3_to_f32(ww[q] & 0xffu); f0.y = fp8_e4m3_to_f32((ww[q] >> 8) & 0xffu);
+                        f1.x = fp8_e4m3_to_f32((ww[q] >> 16) & 0xffu); f1.y = fp8_e4m3_to_f32(ww[q] >> 24);
+                    }
                     part = fmaf(bf16lo(aa[2 * q]), f0.x, part);
                     part = fmaf(bf16hi(aa[2 * q]), f0.y, part);
                     part = fmaf(bf16lo(aa[2 * q + 1]), f1.x, part);
@@ -201,14 +207,10 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
     if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
 }
 
-struct MoeRouteArgs {                // logits == NULL: the routing was done by an earlier launch (row_ids given)
-    const uint16_t* logits; uint16_t* weights; int32_t* indices; int32_t* row_ids; int E;
-};
-
 // One-token routing inside a warp: top-k by k passes of strict '>' argmax (lowest index wins ties) over E <= 512
 // router logits, then softmax over the selected values in slot order -- the arithmetic of topk_with_indices +
 // softmax_topk (topk_kernels.cuh:111-147,222-256), statement for statement.  Lane j < k returns expert j and its
-// bf16 weight bits.  Every warp that needs the routing can recompute it (~1 us) instead of waiting for a launch.
+// bf16 weight bits.
 __device__ __forceinline__ void moe_route_warp(const uint16_t* __restrict__ logits, int E, int k, int lane, int& my_idx,
                                                uint16_t& my_w) {
     constexpr int MAXPL = 16;
@@ -254,39 +256,27 @@ __device__ __forceinline__ void moe_route_warp(const uint16_t* __restrict__ logi
 constexpr int kMoeNvf4Warps = 16;   // 512 threads: 128 registers per thread (32 warps capped the kernel at 64 and spilled ~500 B per thread)
 // NMAT = 1: C[r, :] = A[r, :] . B[e]      NMAT = 2 (decode gate/up pair): C[r, :] = bf16(bf16(silu(g)) * u) with
 // g = bf16(A . Bg[e]), u = bf16(A . Bu[e]) -- the rounding points of gate GEMV -> silu -> up GEMV -> mul_inplace.
-// CPL = columns per lane: 4 (CTA = 128 columns, 32-bit loads) or 1 (CTA = 32 columns, byte loads: 4x the CTAs when
-// rows x N/128 would leave most SMs idle, e.g. 8 routed experts x 768 columns = 48 CTAs).  Per column the arithmetic
-// and its order are the same for both.
-template <int NMAT, int CPL, bool ROUTE>
+// (A 32-column CTA form with byte loads and a form that recomputed the routing in every warp were measured slower on
+// B200 and removed; numbers in profiles/r01_bench_qwen3-30b-a3b_*.json and DESIGN.md.)
+template <int NMAT>
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
 moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd0,
                              const uint8_t* __restrict__ Bs0, const uint8_t* __restrict__ Bd1,
                              const uint8_t* __restrict__ Bs1, uint16_t* __restrict__ C,
                              const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
-                             int expert_offset, int num_local, MoeRouteArgs rt, float* __restrict__ split_ws,
+                             int expert_offset, int num_local, float* __restrict__ split_ws,
                              unsigned* __restrict__ split_cnt) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
     __shared__ unsigned s_ticket;
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
+    constexpr int CPL = 4;                                            // columns per lane: CTA = 128 columns, 32-bit loads
     constexpr int TILE = 32 * CPL;
     float* red = a_s + K;                                             // [NMAT][warps][TILE]
     griddep_wait();
     griddep_launch();
     const int r = blockIdx.y, col0 = blockIdx.x * TILE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int eid;
-    if (ROUTE) {                     // decode: routing folded into this launch (gridDim.y = k rows in slot order)
-        int idx;
-        uint16_t w;
-        moe_route_warp(rt.logits, rt.E, (int)gridDim.y, lane, idx, w);
-        if (blockIdx.x == 0 && r == 0 && warp == 0 && lane < (int)gridDim.y) {
-            rt.indices[lane] = idx; rt.row_ids[lane] = idx; rt.weights[lane] = w;
-        }
-        eid = __shfl_sync(0xffffffffu, idx, r);
-    } else {
-        eid = row_expert_ids[r];
-    }
-    const int e = eid - expert_offset;
+    const int e = row_expert_ids[r] - expert_offset;
     const int c = col0 + lane * CPL;
     if (e < 0 || e >= num_local) {
         if (warp == 0 && c < N) {
@@ -345,37 +335,6 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
                 }
 #pragma unroll
                 for (int j = 0; j < CPL; ++j) acc[m][j] = fmaf(part[j], ue4m3_to_f32((sw[m] >> (8 * j)) & 0xff), acc[m][j]);
-            }
-        } else if (CPL == 1 && c < N) {
-            // one column per lane: 16 byte loads per scale block, packed four at a time into a word so that the
-            // decode is the same F2FP form as above (the byte-register form of the conversion asm must see a
-            // full 32-bit source)
-#pragma unroll
-            for (int m = 0; m < NMAT; ++m) {
-                uint32_t b[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) b[i] = __ldg(bdp[m] + (size_t)(blk * 16 + i) * N + c);
-                const uint32_t sw = __ldg(bsp[m] + (size_t)blk * N + c);
-                float part = 0.f;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const uint32_t w4 = b[4 * t] | (b[4 * t + 1] << 8) | (b[4 * t + 2] << 16) | (b[4 * t + 3] << 24);
-                    uint32_t h;
-                    float2 f, a;
-                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t);
-                    h = e2m1x2_to_f16x2<0>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
-                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t + 2);
-                    h = e2m1x2_to_f16x2<1>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
-                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t + 4);
-                    h = e2m1x2_to_f16x2<2>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
-                    a = *reinterpret_cast<const float2*>(a_s + blk * 32 + 8 * t + 6);
-                    h = e2m1x2_to_f16x2<3>(w4); f = __half22float2(*reinterpret_cast<__half2*>(&h));
-                    part = fmaf(a.x, f.x, part); part = fmaf(a.y, f.y, part);
-                }
-                acc[m][0] = fmaf(part, ue4m3_to_f32(sw), acc[m][0]);
             }
         } else {
 #pragma unroll
@@ -468,29 +427,18 @@ __global__ void moe_route_t1_kernel(const uint16_t* __restrict__ logits, uint16_
 
 // gate and up GEMVs of the k routed experts + silu + multiply in one launch: one warp per (slot, n)
 // reads x once for both weight rows.  act = bf16(bf16(silu(bf16 gate)) * bf16 up), the three-launch form.
-template <bool ROUTE>
 __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ Bg,
                                          const uint16_t* __restrict__ Sg, const uint8_t* __restrict__ Bu,
                                          const uint16_t* __restrict__ Su, uint16_t* __restrict__ act,
                                          const int32_t* __restrict__ row_ids, int R, int K, int N, int expert_offset,
-                                         int num_local, MoeRouteArgs rt) {
+                                         int num_local) {
     griddep_wait();
     griddep_launch();
     const int lane = threadIdx.x & 31;
     const long gw = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (gw >= (long)R * N) return;
     const int n = (int)(gw % N), m = (int)(gw / N);
-    int eid;
-    if (ROUTE) {                     // routing folded into this launch: every warp recomputes it, warp 0 publishes it
-        int idx;
-        uint16_t w;
-        moe_route_warp(rt.logits, rt.E, R, lane, idx, w);
-        if (gw == 0 && lane < R) { rt.indices[lane] = idx; rt.row_ids[lane] = idx; rt.weights[lane] = w; }
-        eid = __shfl_sync(0xffffffffu, idx, m);
-    } else {
-        eid = row_ids[m];
-    }
-    const int e = eid - expert_offset;
+    const int e = row_ids[m] - expert_offset;
     if (e < 0 || e >= num_local) {
         if (lane == 0) act[(size_t)m * N + n] = 0;
         return;
@@ -568,17 +516,16 @@ static inline unsigned nblk(size_t n, int bs) { return (unsigned)((n + bs - 1) /
 static float* g_moe_split_ws = nullptr;
 static unsigned* g_moe_split_cnt = nullptr;
 
-template <int NMAT, int CPL>
-static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
-                               const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
-                               int expert_offset, int num_local_experts, void* stream, MoeRouteArgs rt) {
-    constexpr int TILE = 32 * CPL;
+template <int NMAT>
+static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
+                           const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
+                           int expert_offset, int num_local_experts, void* stream) {
+    constexpr int TILE = 128;
     size_t smem = (size_t)K * 4 + (size_t)NMAT * kMoeNvf4Warps * TILE * 4;
     PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
     static bool attr = false;
     if (!attr) {
-        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT, CPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        PGK_CUDA(cudaFuncSetAttribute(moe_grouped_gemv_nvf4_kernel<NMAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         attr = true;
     }
     // K split: when rows x column tiles cover less than half of the SMs, spread the scale blocks of every cell over up
@@ -606,28 +553,12 @@ static int launch_moe_nvf4_cpl(const void* A, int a_stride, const void* Bd0, con
         const int kb = K >> 5;
         while (ks > 1 && kb / ks < kMoeNvf4Warps) --ks;
     }
-    auto kern = rt.logits ? moe_grouped_gemv_nvf4_kernel<NMAT, CPL, true> : moe_grouped_gemv_nvf4_kernel<NMAT, CPL, false>;
-    PGK_CUDA(launch(kern, dim3(tiles, M, ks), dim3(kMoeNvf4Warps * 32), smem,
+    PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel<NMAT>, dim3(tiles, M, ks), dim3(kMoeNvf4Warps * 32), smem,
                     (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
-                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts, rt,
+                    (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts,
                     ws, cnt));
     return 0;
 }
-template <int NMAT>
-static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1, const void* Bs1,
-                           void* C, const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
-                           int num_local_experts, void* stream, MoeRouteArgs rt = MoeRouteArgs{}) {
-    // 128-column CTAs by default.  The 32-column form (PGK_MOE_NVF4_CPL=1) gives 4x the CTAs -- 8 routed experts x 768
-    // columns are only 48 CTAs of 128 columns -- but measured SLOWER on B200 (Qwen3-30B-A3B NVF4: 211.7 vs 262.6 tok/s):
-    // its 32-byte requests split every 64-byte DRAM atom between two CTAs.  Kept for A/B; same results bit for bit.
-    static const int force = [] { const char* e = getenv("PGK_MOE_NVF4_CPL"); return e ? atoi(e) : 0; }();
-    if (force == 1)
-        return launch_moe_nvf4_cpl<NMAT, 1>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
-                                            num_local_experts, stream, rt);
-    return launch_moe_nvf4_cpl<NMAT, 4>(A, a_stride, Bd0, Bs0, Bd1, Bs1, C, row_expert_ids, M, K, N, expert_offset,
-                                        num_local_experts, stream, rt);
-}
-
 }  // namespace pgk
 
 using namespace pgk;
@@ -744,37 +675,10 @@ int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, con
                           int num_local_experts, void* stream) {
     if (k <= 0) return 0;
     size_t warps = (size_t)k * N;
-    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel<false>, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
+    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
                     (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
-                    (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts, MoeRouteArgs{}));
+                    (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts));
     return 0;
-}
-static int check_route(int num_experts, int k, const char* fn) {
-    PGK_REQUIRE(num_experts >= 1 && num_experts <= 512 && k >= 1 && k <= num_experts && k <= 32,
-                "%s failed: unsupported num_experts=%d k=%d", fn, num_experts, k);
-    return 0;
-}
-int pgk_moe_route_gateup_fp8_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
-                                int32_t* row_expert_ids, const void* Bg_enk, const void* Sg, const void* Bu_enk,
-                                const void* Su, void* act, int k, int K, int N, int expert_offset,
-                                int num_local_experts, void* stream) {
-    if (check_route(num_experts, k, "moe_route_gateup_fp8_t1")) return 1;
-    MoeRouteArgs rt = {(const uint16_t*)logits, (uint16_t*)weights, indices, row_expert_ids, num_experts};
-    size_t warps = (size_t)k * N;
-    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel<true>, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
-                    (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
-                    (uint16_t*)act, (const int32_t*)nullptr, k, K, N, expert_offset, num_local_experts, rt));
-    return 0;
-}
-int pgk_moe_route_gateup_nvf4_t1(const void* x, const void* logits, int num_experts, void* weights, int32_t* indices,
-                                 int32_t* row_expert_ids, const void* Bg_data, const void* Bg_scale, const void* Bu_data,
-                                 const void* Bu_scale, void* act, int k, int K, int N, int expert_offset,
-                                 int num_local_experts, void* stream) {
-    if (check_route(num_experts, k, "moe_route_gateup_nvf4_t1")) return 1;
-    PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_route_gateup_nvf4_t1 failed: K=%d must be a multiple of 32", K);
-    MoeRouteArgs rt = {(const uint16_t*)logits, (uint16_t*)weights, indices, row_expert_ids, num_experts};
-    return launch_moe_nvf4<2>(x, 0, Bg_data, Bg_scale, Bu_data, Bu_scale, act, nullptr, k, K, N, expert_offset,
-                              num_local_experts, stream, rt);
 }
 int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void* Sd, const void* router_weights,
                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,

@@ -74,6 +74,8 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     // Before the dependency wait: the call counter (internal state, last written by the previous all-reduce,
     // i.e. >= 2 kernels back).  One 16-byte vector per thread: a CTA covers at most 8192 elements.
     if (tid == 0) s_seq = ++p.seq[cta];               // same count on every rank: SPMD, every rank runs every call
+    // CTA c always owns elements [c * 8192, (c + 1) * 8192): a slab byte is only ever touched by the same CTA index on
+    // every rank, so the per-CTA sequence / parity argument holds whatever the size of the previous call was
     const long e0 = (long)cta * p.per_cta, e1 = min(p.n, e0 + p.per_cta);
     const long e = e0 + (long)tid * 8;
     const bool active = e < e1;
@@ -178,6 +180,8 @@ int pgk_p2p_open(const void* host_handles_all) {
 }
 
 int pgk_p2p_ready(void) { return g_p2p.ready ? 1 : 0; }
+/* largest message (bytes) pgk_p2p_allreduce_add_bf16 takes; larger ones go through NCCL */
+size_t pgk_p2p_max_bytes(void) { return kP2pRegionBytes; }
 
 /* out[n] = bf16(residual + bf16(sum over ranks of partial)) (residual NULL: plain all-reduce); out may alias
  * residual.  n % 8 == 0, n * 2 bytes <= 1 MB, 16-byte aligned pointers.  Every rank must make the same calls
@@ -192,12 +196,11 @@ int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* 
     for (int r = 0; r < g_p2p.world; ++r) p.peer[r] = g_p2p.peer[r];
     p.seq = g_p2p.seq; p.err = g_p2p.err; p.rank = g_p2p.rank; p.world = g_p2p.world;
     p.n = (long)n;
-    // one CTA of 1024 threads per 8192 elements (16 KB): a batch-1 row of H <= 8192 is a single CTA
-    int ctas = (int)((n + 8191) / 8192);
-    if (ctas > kP2pMaxCtas) ctas = kP2pMaxCtas;
-    long per = ((long)n + ctas - 1) / ctas;
-    p.per_cta = (per + 7) / 8 * 8;
-    PGK_REQUIRE(p.per_cta <= 8192, "p2p_allreduce failed: %ld elements per CTA (internal limit 8192)", p.per_cta);
+    // one CTA of 1024 threads per 8192 elements (a fixed 16 KB slot per CTA index): a batch-1 row of H <= 8192 is a
+    // single CTA, 1 MB is 64 CTAs
+    const int ctas = (int)((n + 8191) / 8192);
+    p.per_cta = 8192;
+    PGK_REQUIRE(ctas <= kP2pMaxCtas, "p2p_allreduce failed: %d CTAs (internal limit %d)", ctas, kP2pMaxCtas);
     PGK_CUDA(launch(p2p_allreduce_add_kernel, dim3(ctas), dim3(1024), 0, (cudaStream_t)stream, p));
     return 0;
 }

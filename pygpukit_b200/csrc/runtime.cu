@@ -32,13 +32,6 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
     return (int)e ? (int)e : 1;
 }
 
-static thread_local PrefetchHint g_hint;
-PrefetchHint take_prefetch_hint() {
-    PrefetchHint h = g_hint;
-    g_hint = PrefetchHint();
-    return h;
-}
-
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 bool pdl_enabled() { return g_pdl.load(std::memory_order_relaxed) != 0; }
 
@@ -64,17 +57,6 @@ extern "C" {
 
 const char* pgk_last_error(void) { return g_err; }
 
-int pgk_prefetch_hint(const void* const* host_regions, const size_t* host_bytes, int n) {
-    PGK_REQUIRE(n >= 0 && n <= 4, "prefetch_hint failed: at most 4 regions (got %d)", n);
-    PrefetchHint h;
-    for (int i = 0; i < n; ++i) {
-        PGK_REQUIRE((uintptr_t)host_regions[i] % 16 == 0, "prefetch_hint failed: regions must be 16-byte aligned");
-        h.p[i] = (const unsigned char*)host_regions[i];
-        h.pieces[i] = host_regions[i] ? (unsigned)(host_bytes[i] / kPrefetchPiece) : 0;
-    }
-    g_hint = h;
-    return 0;
-}
 int pgk_version(void) { return 100; }
 
 int pgk_device_count(int* count) {
@@ -119,7 +101,10 @@ int pgk_malloc(void** ptr, size_t bytes) {
     return 0;
 }
 int pgk_free(void* ptr) {
-    if (ptr) PGK_CUDA(cudaFree(ptr));
+    if (ptr) {
+        fp8_codes_forget(ptr);
+        PGK_CUDA(cudaFree(ptr));
+    }
     return 0;
 }
 int pgk_host_alloc(void** host_ptr, size_t bytes) {

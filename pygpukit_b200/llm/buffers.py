@@ -49,7 +49,8 @@ class DecodeBuffers:
         M = max(1, max_batch_size)
         tp = max(1, config.tp_size)
         H, hd = config.hidden_size, config.head_dim
-        hq, hkv = config.num_heads // tp, config.num_kv_heads // tp
+        # tp > num_kv_heads: ranks replicate a whole KV head (same rule as Attention.__init__)
+        hq, hkv = config.num_heads // tp, max(1, config.num_kv_heads // tp)
         inter = (config.moe_intermediate_size if config.is_moe else config.intermediate_size) // (1 if config.is_moe else tp)
         V = vocab_size if vocab_size is not None else config.vocab_size
         state = zeros((2 + M,), int32)

@@ -28,7 +28,7 @@ from ...core.array import GPUArray
 from ...core.dtypes import bfloat16, float32, uint8
 from ...core.factory import from_numpy, zeros
 from ...core.stream import current_stream_handle as _st
-from .linear import LinearBF16, LinearFP8, LinearNVF4, hint_next
+from .linear import LinearBF16, LinearFP8, LinearNVF4
 from .norm import Norm
 from .rope import precompute_freqs_cis
 
@@ -124,9 +124,13 @@ class Attention:
             if rope_tables is not None:           # shared across layers (same head_dim / theta)
                 self._cos_dev, self._sin_dev = rope_tables
             else:
-                n = min(max_seq_len, self._cos.shape[0])
-                self._cos_dev = from_numpy(np.ascontiguousarray(self._cos[:n], np.float32))
-                self._sin_dev = from_numpy(np.ascontiguousarray(self._sin[:n], np.float32))
+                # the kernels index the tables by position and validate position < max_seq_len only, so the tables
+                # always cover the whole cache (a cache longer than max_position_embeddings extends them with the
+                # same float32 recipe, llm/layers/rope.py:13-24)
+                if max_seq_len > self._cos.shape[0]:
+                    self._cos, self._sin = precompute_freqs_cis(self.head_dim, max_seq_len, self.config.rope_theta)
+                self._cos_dev = from_numpy(np.ascontiguousarray(self._cos[:max_seq_len], np.float32))
+                self._sin_dev = from_numpy(np.ascontiguousarray(self._sin[:max_seq_len], np.float32))
 
     def set_confirmed_pos(self, pos: int) -> None:
         assert 0 <= pos <= self._max_cache_len, f"Invalid pos {pos}"
@@ -146,7 +150,7 @@ class Attention:
     # ---- decode
     def attend(self, x: GPUArray, position: int, context_len: int, *, qkv_buf: GPUArray | None = None,
                attn_buf: GPUArray | None = None, pos_buf: GPUArray | None = None,
-               ctx_buf: GPUArray | None = None, norm=None, prefetch=None) -> GPUArray:
+               ctx_buf: GPUArray | None = None, norm=None) -> GPUArray:
         """qkv projection -> QK-norm/RoPE/KV-write -> split-KV attention; returns [M, q_dim]
         (the input of o_proj).  M rows = M consecutive positions of one sequence."""
         assert self._k_cache is not None, "Call init_fixed_cache first"
@@ -162,7 +166,6 @@ class Attention:
             attn_buf = attn_buf.slice_rows(M)
         if M == 1 and hd == 128 and self.config.use_rope and _FUSED_BRACKET:
             # one launch: QK-norm + RoPE + KV write + split-KV attention (pgk_rope_sdpa_decode)
-            hint_next(prefetch)
             api.rope_sdpa_decode(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
                                  None if self.k_norm is None else self.k_norm.weight.device_ptr,
                                  float(self.q_norm.eps if self.q_norm is not None else 0.0),

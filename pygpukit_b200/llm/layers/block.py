@@ -6,7 +6,7 @@ from __future__ import annotations
 
 from ...core.array import GPUArray
 from .attention import Attention
-from .linear import _PF_ATTN, _PF_OPROJ, can_fuse_norm, hint_next, weight_region
+from .linear import can_fuse_norm
 from .mlp import MLP
 from .moe import MoELayer
 from .norm import Norm
@@ -32,41 +32,28 @@ class TransformerBlock:
         # pre-norms ride inside the qkv / gate-up GEMV launches when the formats allow it
         if can_fuse_norm(self.attn_norm, hidden.shape[1]):
             a = self.attn.attend(hidden, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
-                                 pos_buf=pos_buf, ctx_buf=ctx_buf, norm=self.attn_norm, prefetch=self._hints()[0])
+                                 pos_buf=pos_buf, ctx_buf=ctx_buf, norm=self.attn_norm)
         else:
             x = self.attn_norm(hidden, out=buf("norm_out"))
             a = self.attn.attend(x, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
-                                 pos_buf=pos_buf, ctx_buf=ctx_buf, prefetch=self._hints()[0])
+                                 pos_buf=pos_buf, ctx_buf=ctx_buf)
         if tp:
             part = self.attn.o_proj.forward(a, out=buf("partial"))
             self.comm.allreduce_add(part, hidden)
         else:
-            hint_next(self._hints()[1])
             self.attn.o_proj.forward(a, out=hidden, residual=hidden)
         fuse_mlp = isinstance(self.mlp, MLP) and self.mlp.fuses_norm(self.mlp_norm)
         x, nrm = (hidden, self.mlp_norm) if fuse_mlp else (self.mlp_norm(hidden, out=buf("norm_out")), None)
         kw = {"norm": nrm} if fuse_mlp else {}
-        if tp:
+        if tp and isinstance(self.mlp, MoELayer):
+            # expert parallel: the exchange happens inside the layer, on the un-combined rows (bit-identical to 1 GPU)
+            self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"), comm=self.comm)
+        elif tp:
             part = self.mlp.forward(x, out=buf("partial"), act_buf=buf("mlp_act"), **kw)
             self.comm.allreduce_add(part, hidden)
         else:
             self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"), **kw)
         return hidden
-
-    def _hints(self):
-        """(what the attention launch prefetches into L2, what the o_proj launch adds): o_proj in full plus the
-        head of the gate/up pair, then the next slice of gate/up (see linear.py, pgk_prefetch_hint)."""
-        h = getattr(self, "_hint_regions", None)
-        if h is None:
-            m = self.mlp
-            attn = [weight_region(self.attn.o_proj, 0, 32 << 20)]
-            oproj = []
-            if isinstance(m, MLP) and getattr(m, "activation", "") == "silu" and getattr(m, "gate_up_proj", None) is None:
-                attn += [weight_region(m.gate_proj, 0, _PF_ATTN // 2), weight_region(m.up_proj, 0, _PF_ATTN // 2)]
-                oproj = [weight_region(m.gate_proj, _PF_ATTN // 2, _PF_OPROJ // 2),
-                         weight_region(m.up_proj, _PF_ATTN // 2, _PF_OPROJ // 2)]
-            h = self._hint_regions = (attn, oproj)
-        return h
 
     def __call__(self, x: GPUArray, position_ids: list[int] | None = None, past_kv=None, use_cache: bool = False):
         start = position_ids[0] if position_ids else (past_kv or 0)

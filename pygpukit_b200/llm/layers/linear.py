@@ -12,7 +12,6 @@ NVF4 layer).  Differences, all on the dispatch side:
 """
 from __future__ import annotations
 
-import ctypes as C
 import os
 
 import numpy as np
@@ -42,39 +41,6 @@ def _out2d(out: GPUArray | None, M: int, N: int) -> GPUArray:
 
 def _ptr(a: GPUArray | None):
     return None if a is None else a.device_ptr
-
-
-# Cross-kernel HBM pipelining (pgk_prefetch_hint): a launch that leaves the DRAM pipe idle -- the latency-bound
-# attention kernel, or a GEMV whose own weights were prefetched -- carries the head of the weights that
-# FOLLOWING launches stream into L2.  Budgets in MB (0 = off): what the attention launch prefetches of the
-# gate/up pair (o_proj always rides along in full), and what the then L2-fed o_proj launch adds on top.
-_PF_ATTN = int(float(os.environ.get("PGK_PREFETCH_ATTN_MB", "40")) * (1 << 20))
-_PF_OPROJ = int(float(os.environ.get("PGK_PREFETCH_OPROJ_MB", "0")) * (1 << 20))
-_PF_ON = os.environ.get("PGK_PREFETCH", "0") != "0"   # measured negative on B200 so far: off
-
-
-def weight_region(lin, start: int = 0, nbytes: int | None = None):
-    """(device pointer, bytes) of bytes [start, start + nbytes) of a row-streamed weight tensor (FP8 codes or
-    BF16 rows: the GEMV deals rows round-robin, so 'what is read first' is a prefix); None for NVF4, which
-    streams column panels."""
-    w = getattr(lin, "weight_fp8", None) if isinstance(lin, LinearFP8) else (
-        lin.weight if isinstance(lin, LinearBF16) else None)
-    if w is None:
-        return None
-    start = min(start, w.nbytes) // 4096 * 4096
-    n = w.nbytes - start if nbytes is None else min(nbytes, w.nbytes - start)
-    n = n // 4096 * 4096
-    return (w.device_ptr + start, n) if n > 0 else None
-
-
-def hint_next(regions) -> None:
-    """Attach up to four regions (from weight_region) to the next GEMV / attention launch of this thread."""
-    regs = [r for r in (regions or []) if r is not None][:4]
-    if not regs or not _PF_ON:
-        return
-    ptrs = (C.c_void_p * len(regs))(*[r[0] for r in regs])
-    sizes = (C.c_size_t * len(regs))(*[r[1] for r in regs])
-    api.prefetch_hint(ptrs, sizes, len(regs))
 
 
 # smallest batch served by the tcgen05 skinny GEMM (same default and override as gemm_tc.cu: measured crossover)
@@ -245,4 +211,4 @@ class LinearNVF4:
         return self.data.nbytes + self.scale.nbytes
 
 
-__all__ = ["LinearBF16", "LinearFP8", "LinearNVF4", "Linear", "can_fuse_norm", "weight_region", "hint_next"]
+__all__ = ["LinearBF16", "LinearFP8", "LinearNVF4", "Linear", "can_fuse_norm"]

@@ -8,8 +8,12 @@ on the current stream; no host synchronisation, no per-call allocation when `buf
 
 Experts are held STACKED ([E, N, K] FP8 + [E, N/128, K/128] scales as the reference's
 `_stack_fp8_weights`, moe.py:86-151; or [E, K/2, N] + [E, K/32, N] for the net-new NVF4 experts).
-Under tensor parallelism every rank holds E/tp experts; rows routed to remote experts are skipped
-(their contribution arrives through the block's all-reduce).
+Under tensor parallelism every rank holds E/tp experts and the router is replicated.  Rows routed to
+remote experts come out as zeros; the UN-COMBINED down-projection rows [T*k, H] are then all-reduced
+(every row has exactly one non-zero contributor, so the sum is exact in any order) and the
+slot-ordered weighted combine + the single BF16 rounding + the residual add run identically on every
+rank -- the same arithmetic, in the same order, as on one GPU (scatter_with_reverse_perm_kernel,
+permute_kernels.cuh:218-242), so greedy tokens cannot depend on the number of ranks.
 """
 from __future__ import annotations
 
@@ -30,10 +34,6 @@ if TYPE_CHECKING:
     from ..config import TransformerConfig
 
 
-# 1: routing recomputed by every warp of the gate/up launch instead of a moe_route_t1 launch.  Measured SLOWER on B200
-# (Qwen3-30B-A3B FP8 378.5 -> 320.3, NVF4 348.7 -> 339.2 tok/s): the ~1 us routing chain sits in front of every weight
-# address, which costs more than the launch it saves.  Off by default, kept for A/B (bit-identical either way).
-_ROUTE_FOLD = os.environ.get("PGK_MOE_ROUTE_FOLD", "0") != "0"
 _DECODE_FORM = os.environ.get("PGK_MOE_T1", "1") != "0"      # 0: always the generic pipeline (A/B, parity tests)
 
 
@@ -111,16 +111,19 @@ class MoELayer:
                                       R, K, N, self.expert_offset, self.num_local_experts, _st())
 
     def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
-                act_buf: GPUArray | None = None) -> GPUArray:
+                act_buf: GPUArray | None = None, comm=None) -> GPUArray:
+        """comm: the TensorParallel communicator when the experts are sharded over ranks -- the result is then the
+        COMPLETE layer output on every rank (the exchange happens inside, on the un-combined rows)."""
         if x.ndim != 2:
             raise ValueError("MoELayer expects [tokens, hidden]")
         T, H = x.shape
         k, I, E = self.num_experts_per_tok, self.intermediate_size, self.num_experts
         b = self._buffers(T)
         st = _st()
+        tp = comm is not None and comm.world > 1
         self.gate.forward(x, out=b["logits"])
         if T == 1 and _DECODE_FORM and k <= 32:
-            return self._forward_t1(x, b, out, residual, st)
+            return self._forward_t1(x, b, out, residual, st, comm if tp else None)
         api.moe_topk(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr, T, E, k, 2, st)
         api.moe_softmax_topk(b["weights"].device_ptr, T, k, 2, st)
         api.moe_compute_permutation(b["indices"].device_ptr, b["counts"].device_ptr, b["offsets"].device_ptr,
@@ -133,6 +136,8 @@ class MoELayer:
         self._grouped("up", b["gathered"], b["up"], b["row_ids"], H, I)
         api.mul_inplace(b["act"].device_ptr, b["up"].device_ptr, b["act"].size, 2, st)
         self._grouped("down", b["act"], b["down"], b["row_ids"], I, H)
+        if tp:
+            comm.allreduce_rows(b["down"])       # rows of remote experts are zeros here: exact sum, any order
         y = out if out is not None else GPUArray((T, H), bfloat16)
         target = y if residual is None else b["combine"]
         api.moe_scatter(b["down"].device_ptr, b["weights"].device_ptr, b["reverse"].device_ptr, target.device_ptr,
@@ -141,39 +146,38 @@ class MoELayer:
             api.add(target.device_ptr, residual.device_ptr, y.device_ptr, T * H, 2, st)
         return y
 
-    def _forward_t1(self, x: GPUArray, b: dict, out: GPUArray | None, residual: GPUArray | None, st) -> GPUArray:
+    def _forward_t1(self, x: GPUArray, b: dict, out: GPUArray | None, residual: GPUArray | None, st,
+                    comm=None) -> GPUArray:
         """One token: rows stay in slot order (the combine sums in slot order anyway), so routing is one
         launch and permutation / expand / gather disappear; the experts run as one gate+up+silu+mul kernel and
         (FP8) one down+combine(+residual) kernel, (NVF4) down then combine(+residual).  Bit-identical to the generic pipeline (tests/test_gpu_moe.py)."""
         H, I, E, k = self.hidden_size, self.intermediate_size, self.num_experts, self.num_experts_per_tok
         off, nl = self.expert_offset, self.num_local_experts
-        fold = _ROUTE_FOLD          # routing recomputed inside the gate/up launch (one launch less)
-        if not fold:
-            api.moe_route_t1(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr,
-                             b["row_ids"].device_ptr, E, k, st)
-        route = (b["logits"].device_ptr, E, b["weights"].device_ptr, b["indices"].device_ptr, b["row_ids"].device_ptr)
+        api.moe_route_t1(b["logits"].device_ptr, b["weights"].device_ptr, b["indices"].device_ptr,
+                         b["row_ids"].device_ptr, E, k, st)
         y = out if out is not None else GPUArray((1, H), bfloat16)
         res = residual.device_ptr if residual is not None else None
         if self.format == "fp8":
             (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
-            if fold:
-                api.moe_route_gateup_fp8_t1(x.device_ptr, *route, wg.device_ptr, sg.device_ptr, wu.device_ptr,
-                                            su.device_ptr, b["act"].device_ptr, k, H, I, off, nl, st)
-            else:
-                api.moe_gateup_fp8_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
-                                      b["act"].device_ptr, b["row_ids"].device_ptr, k, H, I, off, nl, st)
-            api.moe_down_combine_fp8_t1(b["act"].device_ptr, wd.device_ptr, sd.device_ptr, b["weights"].device_ptr,
-                                        b["row_ids"].device_ptr, res, y.device_ptr, k, I, H, off, nl, st)
+            api.moe_gateup_fp8_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                                  b["act"].device_ptr, b["row_ids"].device_ptr, k, H, I, off, nl, st)
+            if comm is None:
+                api.moe_down_combine_fp8_t1(b["act"].device_ptr, wd.device_ptr, sd.device_ptr, b["weights"].device_ptr,
+                                            b["row_ids"].device_ptr, res, y.device_ptr, k, I, H, off, nl, st)
+                return y
+            # expert parallel: down rows (zeros for remote experts) -> exact all-reduce -> the same combine everywhere
+            api.moe_grouped_gemv_fp8_ex(b["act"].device_ptr, I, wd.device_ptr, sd.device_ptr, b["down"].device_ptr,
+                                        b["row_ids"].device_ptr, k, I, H, off, nl, st)
+            comm.allreduce_rows(b["down"])
+            api.moe_combine_t1(b["down"].device_ptr, b["weights"].device_ptr, res, y.device_ptr, H, k, st)
             return y
         (wg, sg), (wu, su), (wd, sd) = self._w["gate"], self._w["up"], self._w["down"]
         rid = b["row_ids"].device_ptr
-        if fold:
-            api.moe_route_gateup_nvf4_t1(x.device_ptr, *route, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
-                                         b["act"].device_ptr, k, H, I, off, nl, st)
-        else:
-            api.moe_gateup_nvf4_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
-                                   b["act"].device_ptr, rid, k, H, I, off, nl, st)
+        api.moe_gateup_nvf4_t1(x.device_ptr, wg.device_ptr, sg.device_ptr, wu.device_ptr, su.device_ptr,
+                               b["act"].device_ptr, rid, k, H, I, off, nl, st)
         api.moe_grouped_gemv_nvf4_ex(b["act"].device_ptr, I, wd.device_ptr, sd.device_ptr, b["down"].device_ptr, rid, k, I, H, off, nl, st)
+        if comm is not None:
+            comm.allreduce_rows(b["down"])
         api.moe_combine_t1(b["down"].device_ptr, b["weights"].device_ptr, res, y.device_ptr, H, k, st)
         return y
 

@@ -74,6 +74,7 @@ class TensorParallel:
         self.rank, self.world = rank, world
         self._ready = False
         self._p2p = False
+        self._p2p_max_bytes = 0
 
     @classmethod
     def from_env(cls) -> "TensorParallel":
@@ -97,6 +98,7 @@ class TensorParallel:
             blob = (C.c_char * (hb * self.world)).from_buffer_copy(b"".join(handles))
             api.p2p_open(blob)
             self._p2p = True
+            self._p2p_max_bytes = int(load().pgk_p2p_max_bytes())   # the kernel's own limit (one region per source rank)
         buf = (C.c_char * 128)()
         if self.rank == 0:
             api.nccl_unique_id(buf)
@@ -136,13 +138,25 @@ class TensorParallel:
             return
         from .._lib import api
         from ..core.stream import current_stream_handle
-        if self._p2p and part.size % 8 == 0 and part.nbytes <= (4 << 20):
+        if self._p2p and part.size % 8 == 0 and part.nbytes <= self._p2p_max_bytes:
             api.p2p_allreduce_add_bf16(part.device_ptr, hidden.device_ptr, hidden.device_ptr, part.size,
                                        current_stream_handle())
             return
         from ..ops.elementwise import add_inplace
         self.allreduce(part)
         add_inplace(hidden, part)
+
+    def allreduce_rows(self, x) -> None:
+        """x <- bf16(sum over ranks of x), in place, no residual (the MoE layers exchange their un-combined
+        down-projection rows with it: one non-zero contributor per row, so the sum is exact)."""
+        if self.world == 1:
+            return
+        from .._lib import api
+        from ..core.stream import current_stream_handle
+        if self._p2p and x.size % 8 == 0 and x.nbytes <= self._p2p_max_bytes:
+            api.p2p_allreduce_add_bf16(x.device_ptr, None, x.device_ptr, x.size, current_stream_handle())
+            return
+        self.allreduce(x)
 
     def allgather_bytes(self, send, recv, nbytes: int) -> None:
         from .._lib import api

@@ -257,6 +257,56 @@ def test_gemv_nvf4_vs_oracle(K, N, M):
         assert np.array_equal(o2.to_numpy(), ref[0])       # oracle pinned on the reference kernel
 
 
+@pytest.mark.parametrize("K,N", [(8192, 1024), (2048, 768), (768, 2048), (1024, 7168), (4096, 512), (96, 40)])
+@pytest.mark.parametrize("M", [5, 8, 16, 32, 64])
+def test_gemv_nvf4_batched_vs_oracle(K, N, M):
+    """NVF4 decode batch 5..64 (BASELINE.json configs[4]: batch 1-32) vs the oracle's serial-K restatement of
+    gemv_nvf4_bf16_kernel (nvf4_kernels.cu:79-200), row by row.  128-aligned shapes go to the tcgen05 GEMM
+    (E2M1 x UE4M3 is exact in BF16, the activations are BF16: exact products, f32 accumulation in TMEM -- the
+    f32-accumulate bar 2e-3 applies); the others stay on the CUDA-core GEMV in slabs of 4 rows."""
+    rng = np.random.default_rng(977 + K + N + M)
+    (data, scale), _ = _nvf4_weights(rng, K, N)
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_nvf4_bf16(A, data, scale, 1.0)
+    out = ops.gemv_nvf4_bf16_batched(gk.from_numpy(A), gk.from_numpy(data), gk.from_numpy(scale)).to_numpy()
+    assert rel_err(out, ref) < TOL
+    assert np.mean(out != ref) < 0.05             # f32 reordering flips few bf16 roundings
+    assert ulp_diff_bf16(out[np.abs(f32(ref)) > np.abs(f32(ref)).max() / 64], ref[np.abs(f32(ref)) > np.abs(f32(ref)).max() / 64]) <= 1
+
+
+@pytest.mark.parametrize("M", [1, 2, 4, 8, 33])
+@pytest.mark.parametrize("K,N", [(1024, 256), (4096, 512), (160, 96)])
+def test_gemv_fp8_codes_7f_ff_follow_the_reference_table(K, N, M):
+    """E4M3 codes 0x7F / 0xFF are +-480 in every CUDA table of the reference (fp8.cuh:89,121) -- the hardware
+    conversion the streaming kernels use would give NaN.  A weight tensor that holds them must produce the
+    reference's values from the SAME entry point (pgk_gemv_fp8_bf16*), for every batch size: the library scans each
+    weight tensor once and serves such tensors with the exact table-semantics kernel."""
+    rng = np.random.default_rng(7 + K + N + M)
+    codes, scale = rand_fp8_weights(rng, N, K)
+    hot = rng.integers(0, codes.size, 64)
+    codes.reshape(-1)[hot[:32]] = 0x7F
+    codes.reshape(-1)[hot[32:]] = 0xFF
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_fp8_bf16(A, codes, scale)
+    assert np.isfinite(f32(ref)).all()
+    gB, gS = gk.from_numpy(codes), gk.from_numpy(scale)
+    if M == 1:
+        out = ops.gemv_fp8_bf16(gk.from_numpy(A[0]), gB, gS).to_numpy()[None]
+    else:
+        out = ops.gemv_fp8_bf16_batched(gk.from_numpy(A), gB, gS).to_numpy()
+    assert np.isfinite(f32(out)).all()
+    assert rel_err(out, ref) < TOL
+    # the same shapes without those codes still take the streaming path and agree as well
+    codes2 = codes.copy()
+    codes2.reshape(-1)[hot] = 0x30
+    out2 = ops.gemv_fp8_bf16_batched(gk.from_numpy(A), gk.from_numpy(codes2), gS).to_numpy()
+    assert rel_err(out2, orc.gemv_fp8_bf16(A, codes2, scale)) < (1e-2 if M >= 5 else TOL)
+    if refcuda.available() and M == 1 and K % 128 == 0:
+        o2 = gk.empty((N,), gk.bfloat16)
+        refcuda.gemv_fp8(gk.from_numpy(A[0]), gB, gS, o2, K, N)
+        assert np.array_equal(o2.to_numpy(), ref[0])       # the oracle's +-480 is the reference kernel's
+
+
 @pytest.mark.parametrize("K,N", [(8192, 1024), (4096, 4096), (64, 48), (96, 40), (2048, 768)])
 def test_quantize_nvf4_bit_exact(K, N):
     rng = np.random.default_rng(8 + K + N)

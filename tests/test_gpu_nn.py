@@ -193,8 +193,29 @@ def test_oracle_vs_reference_cuda_attention():
     assert rel_err(ob.to_numpy(), orc.sdpa_causal_fixed_cache(Qb, Kb, Vb, ctx)) < 1e-2
 
 
+@pytest.mark.parametrize("H,Hkv", [(32, 8), (64, 8)])
+def test_sdpa_decode_vs_oracle_32k(H, Hkv):
+    """BASELINE.json configs[2]'s attention at its full size: bf16, head_dim 128, one query token over a 32 768-token
+    cache (Llama-3-8B 32/8 heads, Llama-3-70B 64/8), against oracle.c's restatement of sdpa_causal_bf16_kernel
+    (attention_kernels.cuh:259-370, OpenMP over heads) on the GQA-expanded cache the reference reads.  BF16 bar 1e-2;
+    the context also comes from device memory (_ptr form) and, one token short of the cache, exercises a ragged tail."""
+    hd, S = 128, 32768
+    rng = np.random.default_rng(32 + H)
+    Q, K, V = _sdpa_case(rng, H, Hkv, 1, hd, S, S, np.uint16)
+    gQ, gK, gV = gk.from_numpy(Q), gk.from_numpy(K), gk.from_numpy(V)
+    Ke, Ve = _expand(K, H // Hkv), _expand(V, H // Hkv)
+    for ctx in (S, S - 1):
+        out = gk.empty((H, 1, hd), gk.bfloat16)
+        ops.sdpa_causal_fixed_cache(gQ, gK, gV, out, ctx)
+        ref = orc.sdpa_causal_fixed_cache(Q, Ke, Ve, ctx)
+        assert rel_err(out.to_numpy(), ref) < 1e-2, ctx
+    out2 = gk.empty((H, 1, hd), gk.bfloat16)
+    ops.sdpa_causal_fixed_cache_ptr(gQ, gK, gV, out2, gk.from_numpy(np.array([S - 1], np.int32)), S)
+    assert rel_err(out2.to_numpy(), ref) < 1e-2
+
+
 def test_sdpa_long_context_properties():
-    """32k context (no CPU oracle at this size): uniform keys -> output = mean of V; a single
+    """32k context, size-independent properties: uniform keys -> output = mean of V; a single
     dominant key -> output = that V row; the reference's SDPA cannot launch here (smem > 48 KB)."""
     H, Hkv, hd, ctx = 32, 8, 128, 32768
     rng = np.random.default_rng(6)

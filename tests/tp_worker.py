@@ -1,0 +1,70 @@
+"""Tensor-parallel parity worker (SURVEY.md section 8e "Parity under TP"); launched by tests/test_gpu_tp.py as
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tests/tp_worker.py name:format:steps[:layers] [more cases ...]
+
+Every rank builds its shard of the random-init model (piece `rank` of N); rank 0 additionally builds the SAME
+global model in one process (`shards=N` concatenates the N pieces).  Both decode greedily from the same prompt.
+The all-reduce changes the summation order of the row-parallel projections, so the check is north_star's:
+identical greedy tokens for `steps` steps, unless the single-GPU top-2 logit margin at the first divergence is
+below 2^-5 (a tie at BF16 logit resolution).  Rank 0 prints one JSON line per case; exit code 1 on a real mismatch."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import numpy as np  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from pygpukit_b200 import llm  # noqa: E402
+from pygpukit_b200._lib import api  # noqa: E402
+from pygpukit_b200.llm.tp import torch_allgather, torch_exchange  # noqa: E402
+
+rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+api.device_set(int(os.environ.get("LOCAL_RANK", "0")))
+api.set_pdl(int(os.environ.get("PGK_PDL", "1")))
+dist.init_process_group("gloo")          # host plumbing only: the data path is NCCL / NVLink through libpgk_b200.so
+comm = llm.TensorParallel(rank, world).init(exchange=torch_exchange(), allgather=torch_allgather())
+MAX_SEQ = 256
+PROMPT = [3, 141, 59, 26, 535, 89, 79, 323]
+
+
+def run(model, steps):
+    model.init_decode(MAX_SEQ)
+    return model.generate(PROMPT, steps, temperature=0.0)[len(PROMPT):]
+
+
+all_ok = True
+for case in sys.argv[1:]:
+    f = case.split(":")
+    name, fmt, steps = f[0], f[1], int(f[2])
+    layers = int(f[3]) if len(f) > 3 else None
+    tp_tokens = run(llm.build_random_model(name, fmt, max_seq=MAX_SEQ, comm=comm, std=0.05, num_layers=layers), steps)
+    api.device_sync()
+    dist.barrier()
+    ok, detail = True, {}
+    if rank == 0:
+        single = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, shards=world, std=0.05, num_layers=layers)
+        ref_tokens = run(single, steps)
+        same = int(np.argmin([a == b for a, b in zip(tp_tokens, ref_tokens)] + [False]))
+        detail = {"case": case, "model": name, "format": fmt, "world": world, "steps": steps, "identical_prefix": same,
+                  "tp_tokens": tp_tokens[:16], "single_tokens": ref_tokens[:16]}
+        if same < steps:        # a divergence is only acceptable at a near-tie of the single-GPU logits
+            single.init_decode(MAX_SEQ)
+            hidden = single.prefill(PROMPT + ref_tokens[:same])
+            logits = single.get_logits(hidden).to_numpy().reshape(-1, single._head.shape[0])[-1]
+            from pygpukit_b200.core.dtypes import bf16_bits_to_f32
+            top2 = np.sort(bf16_bits_to_f32(logits))[-2:]
+            detail.update(tp_token=tp_tokens[same], single_token=ref_tokens[same], margin_at_divergence=float(top2[1] - top2[0]))
+            ok = detail["margin_at_divergence"] <= 2.0 ** -5
+        detail["allreduce"] = "p2p-nvlink" if comm._p2p else "nccl"
+        detail["ok"] = ok
+        print(json.dumps(detail), flush=True)
+        del single
+    flag = [ok]
+    dist.broadcast_object_list(flag, src=0)
+    all_ok = all_ok and flag[0]
+comm.destroy()
+dist.destroy_process_group()
+sys.exit(0 if all_ok else 1)
