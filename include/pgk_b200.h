@@ -319,6 +319,52 @@ int pgk_quantize_bf16_to_fp8_block(const void* w_nk, void* codes, void* scale, i
  * graph-replayed decode step (position_buf of llm/decode/m1_graph.py:329-331,505-506). */
 int pgk_decode_advance(int32_t* pos_buf, int32_t* ctx_buf, int delta, void* stream);
 
+/* ------------------------------------------------------------------ one-launch decode step ("step program")
+ * net-new orchestration, same math.  Replaces the per-layer launch sequence of DecodeM1.step
+ * (src/pygpukit/llm/decode/m1.py:40-121: ~25 launches per layer upstream, 5 per layer with the fused per-op
+ * kernels above) by ONE persistent kernel per token: one CTA per SM, a producer warp streams every weight row
+ * and K/V tile of the token through a shared-memory ring with cp.async.bulk (TMA) + mbarriers and runs ahead of
+ * the consumer warps across op boundaries, so the HBM stream never stops while the grid synchronises (device-side
+ * barrier) and re-stages the activation vector between ops.  The host describes the token's op sequence once;
+ * the GEMV ops use the same per-row instruction sequences as pgk_gemv_fp8_bf16_ex / pgk_rmsnorm_gemv_* /
+ * pgk_gemv_bf16_argmax, so their outputs are bit-identical to those entry points.
+ *
+ * kinds: 1 = W8A16 FP8 GEMV (W [N,K] e4m3, S bf16 [N/128,K/128]), 2 = BF16 GEMV (W [N,K]), 3 = NVF4 GEMV over
+ * ROW-PACKED weights (pgk_nvf4_pack_rows: per output row K/2 nibble bytes then K/32 UE4M3 scale bytes),
+ * 4 = QK-norm + RoPE + KV-cache write + split-KV attention (+ combine) of ONE new token (= pgk_rope_sdpa_decode).
+ * flags: 1 = SWIGLU (out[n] = bf16(bf16(silu(bf16(W0 row n . x))) * bf16(W1 row n . x)), pgk_gemv_fp8_swiglu_bf16),
+ * 2 = ACT_EMBED (act is an embedding table [V,K]; the row is token_buf[0]), 4 = RES_EMBED (same for residual),
+ * 8 = ARGMAX (greedy token over the bf16-rounded outputs, lowest index wins ties; written to next_token AND
+ * token_buf, position/context advanced by one when the program was created with advance = 1). */
+typedef struct {
+    int32_t kind, flags, K, N;
+    const void* act;        /* bf16 [K] input vector (kind 4: the qkv row [(hq + 2 n_kv) * 128]) */
+    const void* gamma;      /* bf16 [K]: RMSNorm fused into the staging (pgk_rmsnorm_gemv_*), or NULL */
+    float eps, alpha;       /* alpha: NVF4 output scale */
+    const void* W0; const void* S0; const void* W1; const void* S1;
+    const void* residual;   /* bf16 [N] or NULL: out = bf16(acc) + residual with one rounding (hadd) */
+    void* out;              /* bf16 [N] (kind 4: [hq * 128]); may be NULL with ARGMAX */
+    const void* q_gamma; const void* k_gamma;         /* kind 4: QK-norm weights [128] or NULL */
+    const float* cos_table; const float* sin_table;   /* kind 4: f32 [max_seq, 128] */
+    void* k_cache; void* v_cache;                     /* kind 4: bf16 [n_kv, max_seq, 128] */
+    int32_t hq, n_kv, max_seq, reserved;
+    float scale;            /* kind 4: softmax scale (<= 0: 1/sqrt(128)) */
+    float attn_eps;         /* kind 4: QK-norm eps */
+} pgk_step_op_t;
+/* host_ops: HOST array (copied).  token_buf / pos_buf / ctx_buf / next_token: int32 device words of the decode state
+ * (position_buf of llm/decode/m1_graph.py:329-331).  Fails with a message when an op does not fit the kernel. */
+int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf, int32_t* pos_buf, int32_t* ctx_buf,
+                    int32_t* next_token, int vocab, int advance, void** handle);
+int pgk_step_run(void* handle, void* stream);           /* ONE kernel launch; CUDA-graph capturable */
+int pgk_step_error(void* handle, int* host_code);       /* synchronises; 0 = every wait of the last runs completed */
+int pgk_step_info(void* handle, int* ring_slots, int* act_bytes, int* smem_bytes, int* ctas);
+int pgk_step_destroy(void* handle);
+/* reference NVF4 layout (data u8 [K/2,ld], scale u8 [K/32,ld], ops/matmul/nvf4.py:14-26) -> row-packed [N, K/2 + K/32];
+ * output row n takes source column (n / group) * stride + n % group + col0 (plain matrix: ld = group = N, col0 = 0;
+ * the gate half of a gate/up tensor interleaved in groups of 8 columns: ld = 2N, group = 8, stride = 16, col0 = 0 / 8) */
+int pgk_nvf4_pack_rows(const void* data_kn, const void* scale_kn, void* packed, int K, int N, int ld, int col0, int group,
+                       int stride, void* stream);
+
 /* ------------------------------------------------------------------ tensor parallel (NCCL)
  * net-new (the reference is single-GPU): one communicator per process. unique id is 128 bytes. */
 int pgk_nccl_unique_id(void* host_id128);

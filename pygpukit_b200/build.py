@@ -35,6 +35,7 @@ SOURCES = {
     "moe.cu": [],
     "comm.cu": [],
     "p2p.cu": [],
+    "step.cu": [],
     "init.cu": [],
     "quant_nvf4.cu": ["--use_fast_math"],
 }

@@ -43,19 +43,6 @@ __device__ __forceinline__ void stage_activations_bf16(const uint16_t* __restric
     __syncthreads();
 }
 
-__device__ __forceinline__ void dot8_bf16(float& s0, float& s1, const uint32_t* w, const uint4& a) {
-    fhfma_bf16_lo(s0, w[0], a.x); fhfma_bf16_hi(s1, w[0], a.x);
-    fhfma_bf16_lo(s0, w[1], a.y); fhfma_bf16_hi(s1, w[1], a.y);
-    fhfma_bf16_lo(s0, w[2], a.z); fhfma_bf16_hi(s1, w[2], a.z);
-    fhfma_bf16_lo(s0, w[3], a.w); fhfma_bf16_hi(s1, w[3], a.w);
-}
-
-__device__ __forceinline__ unsigned long long argmax_key(float v, int idx) {
-    uint32_t u = __float_as_uint(v);
-    u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // monotone float -> uint
-    return ((unsigned long long)u << 32) | (uint32_t)(0x7fffffff - idx);
-}
-
 struct ArgmaxOut {
     unsigned long long* key;   // scratch, zero between launches
     unsigned* done;            // CTA arrival counter, zero between launches

@@ -253,6 +253,37 @@ __device__ __forceinline__ void stage_activations_f16(const uint16_t* __restrict
     __syncthreads();
 }
 
+// ---- dot-product bodies shared by the per-op GEMV kernels and the one-launch step kernel (step.cu): the same
+// instruction sequence, hence the same bits, on both paths
+// 8 e4m3 weights (two 32-bit words) x 8 staged f16 activations (one uint4)
+__device__ __forceinline__ void dot8_e4m3(float& s0, float& s1, uint32_t w0, uint32_t w1, const uint4& a) {
+    uint32_t h;
+    h = e4m3x2_to_f16x2_lo(w0); fhfma_f16_lo(s0, h, a.x); fhfma_f16_hi(s1, h, a.x);
+    h = e4m3x2_to_f16x2_hi(w0); fhfma_f16_lo(s0, h, a.y); fhfma_f16_hi(s1, h, a.y);
+    h = e4m3x2_to_f16x2_lo(w1); fhfma_f16_lo(s0, h, a.z); fhfma_f16_hi(s1, h, a.z);
+    h = e4m3x2_to_f16x2_hi(w1); fhfma_f16_lo(s0, h, a.w); fhfma_f16_hi(s1, h, a.w);
+}
+// sum over 32 weights (one 256-bit load) x 32 staged activations (4 planes)
+__device__ __forceinline__ float dot32_e4m3(const u32x8& w, const uint4* ap, int nchunk, int c) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) dot8_e4m3(s0, s1, w.v[2 * p], w.v[2 * p + 1], ap[p * nchunk + c]);
+    return s0 + s1;
+}
+
+__device__ __forceinline__ void dot8_bf16(float& s0, float& s1, const uint32_t* w, const uint4& a) {
+    fhfma_bf16_lo(s0, w[0], a.x); fhfma_bf16_hi(s1, w[0], a.x);
+    fhfma_bf16_lo(s0, w[1], a.y); fhfma_bf16_hi(s1, w[1], a.y);
+    fhfma_bf16_lo(s0, w[2], a.z); fhfma_bf16_hi(s1, w[2], a.z);
+    fhfma_bf16_lo(s0, w[3], a.w); fhfma_bf16_hi(s1, w[3], a.w);
+}
+
+__device__ __forceinline__ unsigned long long argmax_key(float v, int idx) {
+    uint32_t u = __float_as_uint(v);
+    u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // monotone float -> uint
+    return ((unsigned long long)u << 32) | (uint32_t)(0x7fffffff - idx);
+}
+
 __device__ __forceinline__ float silu_ref(float x) {
     // silu_bf16_kernel: x / (1 + expf(-x)) in f32 (activation_kernels.cuh:40-42)
     return x / (1.0f + __expf(-x));

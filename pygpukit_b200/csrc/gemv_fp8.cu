@@ -85,22 +85,6 @@ void fp8_codes_forget(const void* base) {
     g_scan_clean.erase(base);
 }
 
-// 8 e4m3 weights (two 32-bit words) x 8 staged f16 activations (one uint4)
-__device__ __forceinline__ void dot8_e4m3(float& s0, float& s1, uint32_t w0, uint32_t w1, const uint4& a) {
-    uint32_t h;
-    h = e4m3x2_to_f16x2_lo(w0); fhfma_f16_lo(s0, h, a.x); fhfma_f16_hi(s1, h, a.x);
-    h = e4m3x2_to_f16x2_hi(w0); fhfma_f16_lo(s0, h, a.y); fhfma_f16_hi(s1, h, a.y);
-    h = e4m3x2_to_f16x2_lo(w1); fhfma_f16_lo(s0, h, a.z); fhfma_f16_hi(s1, h, a.z);
-    h = e4m3x2_to_f16x2_hi(w1); fhfma_f16_lo(s0, h, a.w); fhfma_f16_hi(s1, h, a.w);
-}
-// sum over 32 weights (one 256-bit load) x 32 staged activations (4 planes)
-__device__ __forceinline__ float dot32_e4m3(const u32x8& w, const uint4* ap, int nchunk, int c) {
-    float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-    for (int p = 0; p < 4; ++p) dot8_e4m3(s0, s1, w.v[2 * p], w.v[2 * p + 1], ap[p * nchunk + c]);
-    return s0 + s1;
-}
-
 // NMAT = 1: plain GEMV; NMAT = 2: gate/up pair with SiLU*up epilogue.
 //
 // One group (U x 256-bit loads per lane) in flight per warp, up to 16 warps per CTA.  (A register double-buffered

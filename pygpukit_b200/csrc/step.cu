@@ -1,0 +1,1046 @@
+// step.cu -- the one-launch decode step: a persistent kernel that runs a whole token (every layer's fused
+// RMSNorm + W8A16/NVF4 GEMV, QK-norm + RoPE + KV write + split-KV attention, SwiGLU, residual GEMVs, final norm +
+// lm_head + greedy argmax) as a "step program" of ops with device-side grid barriers between them.
+//
+// replaces the launch sequence of DecodeM1.step (src/pygpukit/llm/decode/m1.py:40-121) and, on this repo's own
+// path, the 5-launches-per-layer graph of llm/models/causal.py::decode_step_device.
+//
+// Design (HBM-bound; DESIGN.md "step program"):
+//   * grid = one CTA per SM, 16 consumer warps + 1 producer warp.  The producer walks the SAME op list as the
+//     consumers and streams every byte the CTA will need (weight rows, K/V tiles) into a ring of 8 KB shared-memory
+//     slots with cp.async.bulk (TMA, SASS UBLKCP) completing on per-slot mbarriers.  Weights and old KV rows are
+//     constants of the step, so the producer never waits for a grid barrier: while the consumers synchronise and
+//     re-stage the activation vector (~2 us per op boundary) the ring keeps filling (up to ~190 KB per SM = 28 MB
+//     in flight on the GPU), and the HBM stream does not stop at op boundaries.
+//   * work split: an op's rows are cut into items (the rows that fit one slot, or one row cut into <= 4 slot-sized
+//     segments), CTAs own contiguous item ranges (= contiguous byte ranges of the weight matrix), items are dealt
+//     round-robin to the consumer warps.  One warp owns a row, lane l owns the 32-byte chunks l, l+32, ... in
+//     increasing order -- exactly the per-row order of gemv_fp8_sb_kernel / gemv_bf16_kernel, so results are
+//     bit-identical to the per-op entry points.
+//   * attention: units of 16 KV positions (4 KB of K + 4 KB of V = one slot) over the flattened (kv head, tile)
+//     space, contiguous unit ranges per CTA, one warp per unit with the full online-softmax state of the G <= 8
+//     query heads of the group in registers (lane = 4 head dims); per-(kv head, CTA) partial records in L2, then a
+//     grid barrier and a distributed fold in CTA order (deterministic).
+//   * grid barrier: one monotone counter per step parity (red.release.gpu + ld.acquire.gpu spin by one thread,
+//     named barrier for the 512 consumer threads).  Every wait is bounded: on a timeout the kernel records an error
+//     code and runs to completion without waiting any more (results are then garbage; pgk_step_error reports it).
+#include "common.cuh"
+#include "gemv_common.cuh"
+#include "../../include/pgk_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace pgk {
+
+constexpr int kCW = 15;                 // consumer warps (+ 1 producer warp = 512 threads: 128 registers each)
+constexpr int kCT = kCW * 32;           // consumer threads
+constexpr int kStepThreads = kCT + 32;  // + the producer warp
+constexpr int kSlotB = 8192;            // ring slot bytes
+constexpr int kMaxSlots = 26;
+constexpr int kAttnT = 16;              // KV positions per attention unit (K tile 4 KB + V tile 4 KB)
+constexpr int kRec = 130;               // partial record: o[128], m, l
+constexpr int kPartStride = 132;        // shared-memory copy of a record (float4 aligned)
+constexpr long long kSpinLimit = 3000000000LL;   // cycles (~1.5 s): far beyond any legitimate wait
+constexpr float kNeg = -1e30f;
+
+enum : int { OP_FP8 = 1, OP_BF16 = 2, OP_NVF4R = 3, OP_ATTN = 4 };
+enum : int { F_SWIGLU = 1, F_ACT_EMBED = 2, F_RES_EMBED = 4, F_ARGMAX = 8 };
+
+struct StepHeader {
+    const pgk_step_op_t* ops;
+    int n_ops, ns, act_bytes, vocab, advance;
+    int32_t* token_buf; int32_t* pos_buf; int32_t* ctx_buf; int32_t* next_token;
+    unsigned* bar;                 // [0],[1] grid-barrier counters by step parity, [2] step counter
+    float* attn_ws;                // [n_kv][ctas][RT][kRec]
+    unsigned long long* am_key;    // argmax scratch (zero between steps)
+    int* error;
+};
+
+// ---------------------------------------------------------------- work split, shared by host validation, the
+// producer and the consumers (all three must agree exactly)
+struct GemvPlan {
+    int RB, nmat, R, nseg, seg_bytes, spi, items_total, item0, n_items;
+};
+__host__ __device__ inline int op_row_bytes(int kind, int K) {
+    return kind == OP_FP8 ? K : (kind == OP_BF16 ? 2 * K : (K / 2 + K / 32));
+}
+__host__ __device__ inline GemvPlan gemv_plan(int kind, int flags, int K, int N, int cta, int ncta) {
+    GemvPlan p;
+    p.RB = op_row_bytes(kind, K);
+    p.nmat = (flags & F_SWIGLU) ? 2 : 1;
+    if (p.nmat * p.RB <= kSlotB) {
+        p.R = kSlotB / (p.nmat * p.RB); p.nseg = 1; p.seg_bytes = p.RB; p.spi = 1;
+    } else {
+        p.R = 1; p.nseg = (p.RB + kSlotB - 1) / kSlotB; p.seg_bytes = p.RB / p.nseg; p.spi = p.nmat * p.nseg;
+    }
+    p.items_total = (N + p.R - 1) / p.R;
+    p.item0 = (int)((long long)cta * p.items_total / ncta);
+    p.n_items = (int)((long long)(cta + 1) * p.items_total / ncta) - p.item0;
+    return p;
+}
+__host__ __device__ inline int attn_ntile(int ctx) { return (ctx + kAttnT - 1) / kAttnT; }
+__host__ __device__ inline int attn_ctx(int ctx, int max_seq) { return ctx < 1 ? 1 : (ctx > max_seq ? max_seq : ctx); }
+__host__ __device__ inline int part_lo(long long total, int cta, int ncta) { return (int)(total * cta / ncta); }
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- bounded waits
+struct Abort {
+    volatile int* s_abort;   // shared: this CTA gave up waiting
+    int* gerr;               // global error word
+};
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __noinline__ void mbar_wait_slow(uint64_t* bar, uint32_t parity, Abort ab, int code) {
+    const long long t0 = clock64();
+    while (!mbar_try(bar, parity)) {
+        if (*ab.s_abort) return;
+        if (clock64() - t0 > kSpinLimit) { *ab.s_abort = 1; atomicCAS(ab.gerr, 0, code); return; }
+    }
+}
+__device__ __forceinline__ void mbar_wait_b(uint64_t* bar, uint32_t parity, Abort ab, int code) {
+    if (mbar_try(bar, parity)) return;
+    mbar_wait_slow(bar, parity, ab, code);
+}
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(kCT) : "memory"); }
+
+// all 512 consumer threads of every CTA: arrive + wait on the step's monotone counter
+__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned target, int tid, Abort ab) {
+    consumer_sync();                         // every consumer thread's global writes are ordered before thread 0's fence
+    if (tid == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1u);
+        if ((int)(ld_acquire_gpu(ctr) - target) < 0) {
+            const long long t0 = clock64();
+            while ((int)(ld_acquire_gpu(ctr) - target) < 0) {
+                if (*ab.s_abort) break;
+                if (clock64() - t0 > kSpinLimit) { *ab.s_abort = 1; atomicCAS(ab.gerr, 0, 100); break; }
+                __nanosleep(20);
+            }
+        }
+        __threadfence();
+    }
+    consumer_sync();
+}
+
+__device__ __forceinline__ uint64_t make_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_copy_g2s_hint(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar,
+                                                   uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+
+// this lane's 32-byte chunk (lane stride 32 bytes) without bank conflicts: the lanes of a quarter warp read the
+// two 16-byte halves in opposite order (lanes 0-3 low half first, lanes 4-7 high half first, ...), so the eight
+// 16-byte requests of a phase fall into eight different bank groups; the halves are swapped back in registers
+__device__ __forceinline__ u32x8 lds_chunk32(const unsigned char* p, int lane) {
+    const int sw = (lane >> 2) & 1;
+    const uint4 a = *reinterpret_cast<const uint4*>(p + 16 * sw);
+    const uint4 b = *reinterpret_cast<const uint4*>(p + 16 * (sw ^ 1));
+    u32x8 r;
+    r.v[0] = sw ? b.x : a.x; r.v[1] = sw ? b.y : a.y; r.v[2] = sw ? b.z : a.z; r.v[3] = sw ? b.w : a.w;
+    r.v[4] = sw ? a.x : b.x; r.v[5] = sw ? a.y : b.y; r.v[6] = sw ? a.z : b.z; r.v[7] = sw ? a.w : b.w;
+    return r;
+}
+
+// where the bytes of an item live in the ring
+struct ItemView {
+    const unsigned char* ring;
+    int ns, qmod;                 // ring slots, first slot of the item (already reduced mod ns)
+    int R, RB, nseg, seg_bytes, spi;
+    __device__ __forceinline__ const unsigned char* ptr(int t, int r, int off) const {
+        if (spi == 1) return ring + (size_t)qmod * kSlotB + (size_t)(t * R + r) * RB + off;
+        const int seg = (off >= seg_bytes) + (off >= 2 * seg_bytes) + (off >= 3 * seg_bytes);
+        int idx = qmod + t * nseg + seg;
+        if (idx >= ns) idx -= ns;
+        return ring + (size_t)idx * kSlotB + (off - seg * seg_bytes);
+    }
+};
+
+// ---------------------------------------------------------------- activation staging by the 512 consumer threads
+// Same arithmetic as stage_activations_f16 / stage_activations_bf16 (gemv_common.cuh, gemv_bf16.cu): the row is read
+// once, the RMSNorm statistics follow the reference's summation tree (row_inv_rms_ref_order), elements are
+// normalised as bf16(x * inv * gamma), then either kept as bf16 (TO_F16 = false) or range-shifted to f16.
+// Vector j (8 elements) lands in plane j % PL at chunk j / PL.   red: 80 words of shared scratch.
+template <int PL, bool TO_F16, int VY>
+__device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
+                                            float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid) {
+    const int nvec = K >> 3, lane = tid & 31, warp = tid >> 5;
+    const int nchunk = nvec / PL;
+    const uint4* src = reinterpret_cast<const uint4*>(A);
+    const uint4* gv = reinterpret_cast<const uint4*>(gamma);
+    uint4* dst = reinterpret_cast<uint4*>(act);
+    float* red_f = reinterpret_cast<float*>(red) + 64;
+    uint4 v[VY];
+#pragma unroll
+    for (int e = 0; e < VY; ++e) {
+        const int j = tid + e * kCT;
+        if (j < nvec) v[e] = ld_act16(src + j);
+    }
+    if (gamma) {
+#pragma unroll
+        for (int e = 0; e < VY; ++e) {
+            const int j = tid + e * kCT;
+            if (j < nvec) dst[j] = v[e];
+        }
+        consumer_sync();
+        const uint16_t* raw = reinterpret_cast<const uint16_t*>(dst);
+        const int bs = min(256, (K + 31) & ~31), nvw = bs >> 5;
+        for (int w = warp; w < nvw; w += kCW) {
+            float part = 0.f;
+            for (int i = w * 32 + lane; i < K; i += bs) { float x = bf16_bits_to_f32(raw[i]); part = fmaf(x, x, part); }
+            part = warp_sum(part);
+            if (lane == 0) red_f[w] = part;
+        }
+        consumer_sync();
+        const float ss = warp_sum(lane < nvw ? red_f[lane] : 0.f);
+        const float rinv = rsqrtf(ss / (float)K + eps);
+#pragma unroll
+        for (int e = 0; e < VY; ++e)
+            if (tid + e * kCT < nvec) v[e] = norm8_bf16(v[e], __ldg(gv + tid + e * kCT), rinv);
+    }
+    float mult = 1.f;
+    if (TO_F16) {
+        uint32_t mx = 0;
+#pragma unroll
+        for (int e = 0; e < VY; ++e) {
+            if (tid + e * kCT < nvec) {
+                uint32_t t = __vmaxu2(__vmaxu2(v[e].x & 0x7fff7fffu, v[e].y & 0x7fff7fffu),
+                                      __vmaxu2(v[e].z & 0x7fff7fffu, v[e].w & 0x7fff7fffu));
+                mx = max(mx, max(t & 0xffffu, t >> 16));
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (lane == 0) red[warp] = mx;
+        consumer_sync();                 // also: every thread is done reading the raw row
+        uint32_t bm = 0;
+        for (int w = 0; w < kCW; ++w) bm = max(bm, red[w]);
+        int ex = (int)(bm >> 7);
+        ex = min(max(ex, 15), 254);
+        if ((bm >> 7) == 255) ex = 141;
+        mult = __uint_as_float((uint32_t)(268 - ex) << 23);
+        if (tid == 0) inv_s[0] = __uint_as_float((uint32_t)(ex - 14) << 23);
+    } else {
+        consumer_sync();                 // every thread is done reading the raw row
+    }
+#pragma unroll
+    for (int e = 0; e < VY; ++e) {
+        const int j = tid + e * kCT;
+        if (j < nvec) dst[(j % PL) * nchunk + (j / PL)] = TO_F16 ? bf16x8_to_f16x8_scaled(v[e], mult) : v[e];
+    }
+    consumer_sync();
+}
+// few vectors per thread for the common K <= 11520 (no spills), eight for the long rows (K up to 30720)
+template <int PL, bool TO_F16>
+__device__ __forceinline__ void stage_act(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
+                                          float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid) {
+    if ((K >> 3) <= 3 * kCT) stage_act_v<PL, TO_F16, 3>(A, K, gamma, eps, act, red, inv_s, tid);
+    else                     stage_act_v<PL, TO_F16, 8>(A, K, gamma, eps, act, red, inv_s, tid);
+}
+
+// ---------------------------------------------------------------- row dot products
+__device__ __forceinline__ float dot32_e4m3_regs(const u32x8& w, const uint4 (&a)[4]) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) dot8_e4m3(s0, s1, w.v[2 * p], w.v[2 * p + 1], a[p]);
+    return s0 + s1;
+}
+// 8 e2m1 weights (one 32-bit word: byte b = k 2b (low nibble), 2b+1) x 8 staged f16 activations
+__device__ __forceinline__ void dot8_e2m1(float& s0, float& s1, uint32_t w, const uint4& a) {
+    uint32_t h;
+    h = e2m1x2_to_f16x2<0>(w); fhfma_f16_lo(s0, h, a.x); fhfma_f16_hi(s1, h, a.x);
+    h = e2m1x2_to_f16x2<1>(w); fhfma_f16_lo(s0, h, a.y); fhfma_f16_hi(s1, h, a.y);
+    h = e2m1x2_to_f16x2<2>(w); fhfma_f16_lo(s0, h, a.z); fhfma_f16_hi(s1, h, a.z);
+    h = e2m1x2_to_f16x2<3>(w); fhfma_f16_lo(s0, h, a.w); fhfma_f16_hi(s1, h, a.w);
+}
+
+struct RowOut {
+    uint16_t* C; const uint16_t* residual; float inv, alpha; int flags;
+};
+// lane 0: one finished output row (the epilogue of gemv_fp8_sb_kernel / gemv_bf16_kernel)
+__device__ __forceinline__ uint16_t finish_row(const RowOut& ro, int n, float v) {
+    const uint16_t ob = ro.residual ? hadd_bf16_bits(v, ld_act2(ro.residual + n)) : f32_to_bf16_bits(v);
+    if (ro.C) ro.C[n] = ob;
+    return ob;
+}
+__device__ __forceinline__ void finish_swiglu(const RowOut& ro, int n, float vg, float vu) {
+    const float g = round_bf16(vg), u = round_bf16(vu);
+    const float s = round_bf16(silu_ref(g));
+    ro.C[n] = f32_to_bf16_bits(s * u);
+}
+
+// FP8: RR rows of NMAT matrices share one read of the activation chunk.  Per row: acc = fma(dot32(chunk), scale, acc)
+// over the lane's chunks in increasing order, then the butterfly sum (= gemv_fp8_sb_kernel).
+template <int NMAT, int RR>
+__device__ __forceinline__ void fp8_rows(const pgk_step_op_t& op, const ItemView& iv, const uint4* a_lo, int nchunk,
+                                         int n, int r0, int lane, const RowOut& ro) {
+    const int SK = (op.K + 127) >> 7;
+    const uint16_t* S[2] = {(const uint16_t*)op.S0, (const uint16_t*)op.S1};
+    float acc[NMAT][RR];
+#pragma unroll
+    for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) acc[t][rr] = 0.f;
+#pragma unroll 2
+    for (int c = lane; c < nchunk; c += 32) {
+        uint4 a[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) a[p] = a_lo[p * nchunk + c];
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) {
+#pragma unroll
+            for (int t = 0; t < NMAT; ++t) {
+                const u32x8 w = lds_chunk32(iv.ptr(t, r0 + rr, c * 32), lane);
+                const float sc = bf16_bits_to_f32(__ldg(S[t] + (size_t)((n + rr) >> 7) * SK + (c >> 2)));
+                acc[t][rr] = fmaf(dot32_e4m3_regs(w, a), sc, acc[t][rr]);
+            }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) acc[t][rr] = warp_sum(acc[t][rr]);
+    if (lane == 0) {
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) {
+            if (NMAT == 2) finish_swiglu(ro, n + rr, acc[0][rr] * ro.inv, acc[NMAT - 1][rr] * ro.inv);
+            else finish_row(ro, n + rr, acc[0][rr] * ro.inv);
+        }
+    }
+}
+
+// NVF4 over row-packed weights: chunk = 32 data bytes = 64 weights = two scale blocks; per block the f16 products are
+// summed in f32 and scaled by the UE4M3 block scale (exact decode), acc = fma(blocksum, scale, acc)
+template <int NMAT, int RR>
+__device__ __forceinline__ void nvf4_rows(const pgk_step_op_t& op, const ItemView& iv, const uint4* a_lo, int nchunk,
+                                          int n, int r0, int lane, const RowOut& ro) {
+    const int soff = op.K >> 1;       // scale bytes follow the data bytes of the row
+    float acc[NMAT][RR];
+#pragma unroll
+    for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) acc[t][rr] = 0.f;
+#pragma unroll 1
+    for (int c = lane; c < nchunk; c += 32) {
+        uint4 a[8];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) a[p] = a_lo[p * nchunk + c];
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) {
+#pragma unroll
+            for (int t = 0; t < NMAT; ++t) {
+                const u32x8 w = lds_chunk32(iv.ptr(t, r0 + rr, c * 32), lane);
+                const uint32_t sc2 = *reinterpret_cast<const uint16_t*>(iv.ptr(t, r0 + rr, soff + 2 * c));
+                float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) dot8_e2m1(s0, s1, w.v[p], a[p]);
+                acc[t][rr] = fmaf(s0 + s1, ue4m3_to_f32(sc2 & 0xffu), acc[t][rr]);
+                s0 = 0.f; s1 = 0.f;
+#pragma unroll
+                for (int p = 4; p < 8; ++p) dot8_e2m1(s0, s1, w.v[p], a[p]);
+                acc[t][rr] = fmaf(s0 + s1, ue4m3_to_f32(sc2 >> 8), acc[t][rr]);
+            }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < NMAT; ++t)
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) acc[t][rr] = warp_sum(acc[t][rr]);
+    if (lane == 0) {
+#pragma unroll
+        for (int rr = 0; rr < RR; ++rr) {
+            if (NMAT == 2) finish_swiglu(ro, n + rr, ro.alpha * (acc[0][rr] * ro.inv), ro.alpha * (acc[NMAT - 1][rr] * ro.inv));
+            else finish_row(ro, n + rr, ro.alpha * (acc[0][rr] * ro.inv));
+        }
+    }
+}
+
+// BF16 (lm_head): chunk = 16 elements; acc += dot16 per chunk in increasing order (= gemv_bf16_kernel)
+__device__ __forceinline__ float bf16_row(const ItemView& iv, const uint4* a_lo, int nchunk, int r, int lane) {
+    float acc = 0.f;
+#pragma unroll 2
+    for (int c = lane; c < nchunk; c += 32) {
+        const u32x8 w = lds_chunk32(iv.ptr(0, r, c * 32), lane);
+        float s0 = 0.f, s1 = 0.f;
+        dot8_bf16(s0, s1, &w.v[0], a_lo[c]);
+        dot8_bf16(s0, s1, &w.v[4], a_lo[nchunk + c]);
+        acc += s0 + s1;
+    }
+    return warp_sum(acc);
+}
+
+struct Shared {
+    uint64_t full_bar[kMaxSlots];
+    uint64_t empty_bar[kMaxSlots];
+    uint16_t q_s[8][128];
+    uint16_t new_s[2][128];
+    uint32_t red[80];
+    float inv_s[4];
+    unsigned long long key;
+    int abort_flag;
+};
+
+// ---------------------------------------------------------------- one GEMV-type op, consumer side
+__device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const StepHeader& h, Shared& sh, unsigned char* ring,
+                                        unsigned char* act, uint32_t q_base, int cta, int ncta, int token, int tid, Abort ab,
+                                        float& best_v, int& best_i) {
+    const int lane = tid & 31, warp = tid >> 5;
+    const int K = op.K, N = op.N;
+    const GemvPlan pl = gemv_plan(op.kind, op.flags, K, N, cta, ncta);
+    const uint16_t* A = (const uint16_t*)op.act + ((op.flags & F_ACT_EMBED) ? (size_t)token * K : 0);
+    const uint16_t* gam = (const uint16_t*)op.gamma;
+    if (op.kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    else if (op.kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    else                          stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    RowOut ro;
+    ro.C = (uint16_t*)op.out;
+    ro.residual = op.residual ? (const uint16_t*)op.residual + ((op.flags & F_RES_EMBED) ? (size_t)token * N : 0) : nullptr;
+    ro.inv = (op.kind == OP_BF16) ? 1.f : sh.inv_s[0];
+    ro.alpha = op.alpha;
+    ro.flags = op.flags;
+    const uint4* a_lo = reinterpret_cast<const uint4*>(act);
+    const int nchunk = (op.kind == OP_FP8) ? (K >> 5) : (op.kind == OP_NVF4R ? (K >> 6) : (K >> 4));
+    ItemView iv;
+    iv.ring = ring; iv.ns = h.ns; iv.R = pl.R; iv.RB = pl.RB; iv.nseg = pl.nseg; iv.seg_bytes = pl.seg_bytes; iv.spi = pl.spi;
+    for (int i = warp; i < pl.n_items; i += kCW) {
+        const uint32_t q0 = q_base + (uint32_t)i * pl.spi;
+        iv.qmod = (int)(q0 % (uint32_t)h.ns);
+        for (int s = 0; s < pl.spi; ++s) {
+            const uint32_t q = q0 + s;
+            mbar_wait_b(&sh.full_bar[q % h.ns], (q / h.ns) & 1, ab, 200 + op.kind);
+        }
+        const int n0 = (pl.item0 + i) * pl.R;
+        const int rows = min(pl.R, N - n0);
+        if (op.kind == OP_FP8) {
+            if (op.flags & F_SWIGLU) {
+                for (int r = 0; r < rows; ++r) fp8_rows<2, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+            } else {
+                int r = 0;
+                for (; r + 2 <= rows; r += 2) fp8_rows<1, 2>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+                if (r < rows) fp8_rows<1, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+            }
+        } else if (op.kind == OP_NVF4R) {
+            if (op.flags & F_SWIGLU) {
+                for (int r = 0; r < rows; ++r) nvf4_rows<2, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+            } else {
+                int r = 0;
+                for (; r + 2 <= rows; r += 2) nvf4_rows<1, 2>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+                if (r < rows) nvf4_rows<1, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+            }
+        } else {
+            for (int r = 0; r < rows; ++r) {
+                const float v = bf16_row(iv, a_lo, nchunk, r, lane);
+                if (lane == 0) {
+                    const uint16_t ob = finish_row(ro, n0 + r, v);
+                    if (op.flags & F_ARGMAX) {
+                        const float rv = bf16_bits_to_f32(ob);
+                        if (rv > best_v) { best_v = rv; best_i = n0 + r; }   // rows ascend within a warp: first max kept
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0)
+            for (int s = 0; s < pl.spi; ++s) mbar_arrive(&sh.empty_bar[(q0 + s) % h.ns]);
+    }
+}
+
+// ---------------------------------------------------------------- attention op, consumer side
+// one warp, one unit of <= 16 KV positions, RT query rows: lane owns head dims 4*lane .. 4*lane+3; the 32 score
+// partials of an iteration (U = 32/RT positions x RT rows) are reduce-scattered so that lane v owns the score of
+// (position v / RT, row v % RT).
+template <int RT>
+struct AttnState {
+    float m_own, l_own;
+    float o[RT][4];
+};
+
+template <int RT>
+__device__ __forceinline__ void attn_unit(AttnState<RT>& st, const unsigned char* tile, int npos, const uint32_t (&q)[RT][2],
+                                          float scale_log2, int lane) {
+    constexpr int U = 32 / RT;
+    const unsigned char* kp = tile + lane * 8;
+    const unsigned char* vp = kp + kAttnT * 256;
+#pragma unroll 1
+    for (int it = 0; it < kAttnT / U; ++it) {
+        if (it * U >= npos) break;            // warp-uniform
+        uint2 kq[U], vq[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int j = it * U + u;
+            if (j < npos) {
+                kq[u] = *reinterpret_cast<const uint2*>(kp + j * 256);
+                vq[u] = *reinterpret_cast<const uint2*>(vp + j * 256);
+            } else {
+                kq[u] = make_uint2(0u, 0u); vq[u] = make_uint2(0u, 0u);
+            }
+        }
+        float val[32];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+                float a0 = 0.f, a1 = 0.f;
+                fhfma_bf16_lo(a0, q[r][0], kq[u].x); fhfma_bf16_hi(a1, q[r][0], kq[u].x);
+                fhfma_bf16_lo(a0, q[r][1], kq[u].y); fhfma_bf16_hi(a1, q[r][1], kq[u].y);
+                val[u * RT + r] = a0 + a1;
+            }
+        }
+        float tot;
+        {
+            const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2, b1 = lane & 1;
+            float v16[16], v8[8], v4[4], v2[2];
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                v16[i] = (b16 ? val[i + 16] : val[i]) + __shfl_xor_sync(0xffffffffu, b16 ? val[i] : val[i + 16], 16);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                v8[i] = (b8 ? v16[i + 8] : v16[i]) + __shfl_xor_sync(0xffffffffu, b8 ? v16[i] : v16[i + 8], 8);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                v4[i] = (b4 ? v8[i + 4] : v8[i]) + __shfl_xor_sync(0xffffffffu, b4 ? v8[i] : v8[i + 4], 4);
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                v2[i] = (b2 ? v4[i + 2] : v4[i]) + __shfl_xor_sync(0xffffffffu, b2 ? v4[i] : v4[i + 2], 2);
+            tot = (b1 ? v2[1] : v2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? v2[0] : v2[1], 1);
+        }
+        const bool own_valid = it * U + lane / RT < npos;
+        const float s_own = own_valid ? tot * scale_log2 : kNeg;
+        float mx = s_own;
+#pragma unroll
+        for (int off = RT; off < 32; off <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        const float mn = fmaxf(st.m_own, mx);
+        const float corr_own = exp2f(st.m_own - mn);
+        const float p_own = own_valid ? exp2f(s_own - mn) : 0.f;
+        float ls = p_own;
+#pragma unroll
+        for (int off = RT; off < 32; off <<= 1) ls += __shfl_xor_sync(0xffffffffu, ls, off);
+        st.l_own = st.l_own * corr_own + ls;
+        st.m_own = mn;
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            const float corr = __shfl_sync(0xffffffffu, corr_own, r);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) st.o[r][e] *= corr;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const float vf[4] = {bf16lo(vq[u].x), bf16hi(vq[u].x), bf16lo(vq[u].y), bf16hi(vq[u].y)};
+#pragma unroll
+            for (int r = 0; r < RT; ++r) {
+                const float pj = __shfl_sync(0xffffffffu, p_own, u * RT + r);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) st.o[r][e] = fmaf(pj, vf[e], st.o[r][e]);
+            }
+        }
+    }
+}
+
+// one warp: [RMSNorm] + NeoX rotation of one 128-wide head row (same arithmetic as norm_rope_head128 in attention.cu)
+__device__ __forceinline__ void step_norm_rope128(const uint16_t* row, const uint16_t* gamma, float eps, const float* cs,
+                                                  const float* sn, int lane, uint16_t* dst_s, uint16_t* dst_g) {
+    float x[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[i] = bf16_bits_to_f32(ld_act2(row + lane + 32 * i));
+    if (gamma) {
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            float part = warp_sum(fmaf(x[w], x[w], 0.f));
+            if (lane == w) tot = part;
+        }
+        const float inv = rsqrtf(warp_sum(tot) / 128.f + eps);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = round_bf16(x[i] * inv * bf16_bits_to_f32(__ldg(gamma + lane + 32 * i)));
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const float c = __ldg(cs + lane + 32 * i), s = __ldg(sn + lane + 32 * i);
+        const float x0 = x[i], x1 = x[i + 2];
+        const uint16_t y0 = f32_to_bf16_bits(x0 * c - x1 * s), y1 = f32_to_bf16_bits(x1 * c + x0 * s);
+        dst_s[lane + 32 * i] = y0; dst_s[lane + 32 * i + 64] = y1;
+        if (dst_g) { dst_g[lane + 32 * i] = y0; dst_g[lane + 32 * i + 64] = y1; }
+    }
+}
+
+template <int RT>
+__device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const StepHeader& h, Shared& sh, unsigned char* ring,
+                                        unsigned char* act, uint32_t q_base, int cta, int ncta, int pos, int ctx_in, int tid,
+                                        Abort ab) {
+    const int lane = tid & 31, warp = tid >> 5;
+    const int hq = op.hq, n_kv = op.n_kv, G = hq / n_kv, max_seq = op.max_seq;
+    const int ctx = attn_ctx(ctx_in, max_seq);
+    const int ntile = attn_ntile(ctx);
+    const long long Utot = (long long)n_kv * ntile;
+    const int u0 = part_lo(Utot, cta, ncta), u1 = part_lo(Utot, cta + 1, ncta);
+    const uint16_t* qkv = (const uint16_t*)op.act;
+    uint16_t* kc = (uint16_t*)op.k_cache;
+    uint16_t* vc = (uint16_t*)op.v_cache;
+    const bool has_new = pos < ctx;
+    const int tpos = min(pos, max_seq - 1);
+    const float* cs = op.cos_table + (size_t)tpos * 128;
+    const float* sn = op.sin_table + (size_t)tpos * 128;
+    const float scale = op.scale > 0.f ? op.scale : 0.08838834764831845f;   // 1/sqrt(128)
+    const float scale_log2 = scale * 1.4426950408889634f;
+    float* part = reinterpret_cast<float*>(act);     // [8][RT][kPartStride]
+
+    int u = u0;
+    while (u < u1) {
+        const int kvh = u / ntile;
+        const int seg_end = min(u1, (kvh + 1) * ntile);
+        // ---- the group's query rows and the new K / V row
+        const int uw = kvh * ntile + (has_new ? pos / kAttnT : 0);
+        const bool writer = pos < max_seq && uw >= u0 && uw < u1;
+        if (warp < RT) {
+            if (warp < G) step_norm_rope128(qkv + (size_t)(kvh * G + warp) * 128, (const uint16_t*)op.q_gamma, op.attn_eps, cs, sn,
+                                            lane, sh.q_s[warp], nullptr);
+            else for (int d = lane; d < 128; d += 32) sh.q_s[warp][d] = 0;
+        } else if (warp == RT) {
+            uint16_t* dst = writer ? kc + ((size_t)kvh * max_seq + pos) * 128 : nullptr;
+            step_norm_rope128(qkv + (size_t)(hq + kvh) * 128, (const uint16_t*)op.k_gamma, op.attn_eps, cs, sn, lane,
+                              sh.new_s[0], dst);
+        } else if (warp == RT + 1) {
+            const uint16_t* src = qkv + (size_t)(hq + n_kv + kvh) * 128;
+            uint16_t* dst = writer ? vc + ((size_t)kvh * max_seq + pos) * 128 : nullptr;
+            for (int d = lane; d < 128; d += 32) { const uint16_t v = ld_act2(src + d); sh.new_s[1][d] = v; if (dst) dst[d] = v; }
+        }
+        consumer_sync();
+        uint32_t q[RT][2];
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            const uint2 v = *reinterpret_cast<const uint2*>(&sh.q_s[r][lane * 4]);
+            q[r][0] = v.x; q[r][1] = v.y;
+        }
+        AttnState<RT> st;
+        st.m_own = kNeg; st.l_own = 0.f;
+#pragma unroll
+        for (int r = 0; r < RT; ++r)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) st.o[r][e] = 0.f;
+        const int i0 = u - u0, i1 = seg_end - u0;
+        int first = i0 + (((warp - i0) % kCW) + kCW) % kCW;
+        for (int i = first; i < i1; i += kCW) {
+            const uint32_t qn = q_base + (uint32_t)i;
+            const int slot = (int)(qn % (uint32_t)h.ns);
+            mbar_wait_b(&sh.full_bar[slot], (qn / h.ns) & 1, ab, 204);
+            unsigned char* tile = ring + (size_t)slot * kSlotB;
+            const int t0 = (u0 + i - kvh * ntile) * kAttnT;
+            const int npos = min(kAttnT, ctx - t0);
+            if (has_new && pos >= t0 && pos < t0 + npos) {          // warp-uniform: patch the new row into the staged tile
+                *reinterpret_cast<uint2*>(tile + (size_t)(pos - t0) * 256 + lane * 8) =
+                    *reinterpret_cast<const uint2*>(&sh.new_s[0][lane * 4]);
+                *reinterpret_cast<uint2*>(tile + kAttnT * 256 + (size_t)(pos - t0) * 256 + lane * 8) =
+                    *reinterpret_cast<const uint2*>(&sh.new_s[1][lane * 4]);
+                __syncwarp();
+            }
+            attn_unit<RT>(st, tile, npos, q, scale_log2, lane);
+            fence_proxy_async();          // the patch above was a generic-proxy write; the slot's next fill is a TMA write
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sh.empty_bar[slot]);
+        }
+        // ---- fold the warps' states (8 warps at a time through shared memory), write the CTA's record
+        constexpr int NX = (RT * 128 + kCT - 1) / kCT;       // outputs (row, dim) per thread
+        float Mr[NX], Or[NX], Lr[NX];
+#pragma unroll
+        for (int x = 0; x < NX; ++x) { Mr[x] = kNeg; Or[x] = 0.f; Lr[x] = 0.f; }
+        for (int grp = 0; grp < (kCW + 7) / 8; ++grp) {
+            const int nw = min(8, kCW - grp * 8);
+            if ((warp >> 3) == grp) {
+                const int w8 = warp & 7;
+#pragma unroll
+                for (int r = 0; r < RT; ++r)
+                    *reinterpret_cast<float4*>(&part[(w8 * RT + r) * kPartStride + 4 * lane]) =
+                        make_float4(st.o[r][0], st.o[r][1], st.o[r][2], st.o[r][3]);
+                if (lane < RT) {
+                    part[(w8 * RT + lane) * kPartStride + 128] = st.m_own;
+                    part[(w8 * RT + lane) * kPartStride + 129] = st.l_own;
+                }
+            }
+            consumer_sync();
+#pragma unroll
+            for (int x = 0; x < NX; ++x) {
+                const int idx = tid + x * kCT;
+                if (idx < RT * 128) {
+                    const int r = idx >> 7, d = idx & 127;
+                    float mn = kNeg;
+                    for (int w = 0; w < nw; ++w) mn = fmaxf(mn, part[(w * RT + r) * kPartStride + 128]);
+                    float ov = 0.f, lv = 0.f;
+                    for (int w = 0; w < nw; ++w) {
+                        const float c = exp2f(part[(w * RT + r) * kPartStride + 128] - mn);
+                        ov = fmaf(part[(w * RT + r) * kPartStride + d], c, ov);
+                        lv = fmaf(part[(w * RT + r) * kPartStride + 129], c, lv);
+                    }
+                    const float Mn = fmaxf(Mr[x], mn);
+                    const float c1 = exp2f(Mr[x] - Mn), c2 = exp2f(mn - Mn);
+                    Or[x] = Or[x] * c1 + ov * c2;
+                    Lr[x] = Lr[x] * c1 + lv * c2;
+                    Mr[x] = Mn;
+                }
+            }
+            consumer_sync();
+        }
+        float* rec = h.attn_ws + ((size_t)kvh * ncta + cta) * RT * kRec;
+#pragma unroll
+        for (int x = 0; x < NX; ++x) {
+            const int idx = tid + x * kCT;
+            if (idx < RT * 128) {
+                const int r = idx >> 7, d = idx & 127;
+                __stcg(rec + r * kRec + d, Or[x]);
+                if (d == 0) { __stcg(rec + r * kRec + 128, Mr[x]); __stcg(rec + r * kRec + 129, Lr[x]); }
+            }
+        }
+        u = seg_end;
+    }
+}
+
+// after the grid barrier: out[h, :] = fold over the CTAs that hold units of kv head h / G, in CTA order
+template <int RT>
+__device__ __forceinline__ void attn_combine(const pgk_step_op_t& op, const StepHeader& h, int cta, int ncta, int ctx_in, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    const int hq = op.hq, n_kv = op.n_kv, G = hq / n_kv;
+    const int ctx = attn_ctx(ctx_in, op.max_seq);
+    const int ntile = attn_ntile(ctx);
+    const long long Utot = (long long)n_kv * ntile;
+    const int items = hq * 4;
+    const int i0 = part_lo(items, cta, ncta), i1 = part_lo(items, cta + 1, ncta);
+    uint16_t* out = (uint16_t*)op.out;
+    for (int i = i0 + warp; i < i1; i += kCW) {
+        const int head = i >> 2, qd = i & 3;
+        const int kvh = head / G, g = head % G;
+        const int lo = kvh * ntile, hi = lo + ntile;
+        // CTA c owns units [floor(Utot c / ncta), floor(Utot (c+1) / ncta)): first / last CTA that meets [lo, hi)
+        int cf = (int)((((long long)lo + 1) * ncta + Utot - 1) / Utot) - 1;
+        int cl = (int)(((long long)hi * ncta + Utot - 1) / Utot) - 1;
+        cf = max(0, min(cf, ncta - 1));
+        cl = max(0, min(cl, ncta - 1));
+        const float* base = h.attn_ws + ((size_t)kvh * ncta) * RT * kRec + (size_t)g * kRec;
+        float M = kNeg;
+        for (int cc = cf + lane; cc <= cl; cc += 32) {
+            const int a = max(part_lo(Utot, cc, ncta), lo), b = min(part_lo(Utot, cc + 1, ncta), hi);
+            if (a < b) M = fmaxf(M, __ldcg(base + (size_t)cc * RT * kRec + 128));
+        }
+        M = warp_max(M);
+        float O = 0.f, L = 0.f;
+        for (int cc = cf; cc <= cl; ++cc) {
+            const int a = max(part_lo(Utot, cc, ncta), lo), b = min(part_lo(Utot, cc + 1, ncta), hi);
+            if (a >= b) continue;
+            const float* rr = base + (size_t)cc * RT * kRec;
+            const float c = exp2f(__ldcg(rr + 128) - M);
+            O = fmaf(__ldcg(rr + qd * 32 + lane), c, O);
+            L = fmaf(__ldcg(rr + 129), c, L);
+        }
+        out[(size_t)head * 128 + qd * 32 + lane] = f32_to_bf16_bits(L > 0.f ? O / L : 0.f);
+    }
+}
+
+// ---------------------------------------------------------------- producer: one thread per CTA
+__device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsigned char* ring, int cta, int ncta, int token,
+                                         int ctx_in, Abort ab) {
+    const uint64_t pol = make_evict_first_policy();
+    uint32_t q = 0;
+    auto acquire = [&](uint32_t bytes) -> unsigned char* {
+        const int slot = (int)(q % (uint32_t)h.ns);
+        mbar_wait_b(&sh.empty_bar[slot], ((q / h.ns) & 1) ^ 1, ab, 300);
+        mbar_arrive_expect_tx(&sh.full_bar[slot], bytes);
+        ++q;
+        return ring + (size_t)slot * kSlotB;
+    };
+    for (int oi = 0; oi < h.n_ops; ++oi) {
+        const pgk_step_op_t& op = h.ops[oi];
+        if (op.kind == OP_ATTN) {
+            const int ctx = attn_ctx(ctx_in, op.max_seq);
+            const int ntile = attn_ntile(ctx);
+            const long long Utot = (long long)op.n_kv * ntile;
+            const int u0 = part_lo(Utot, cta, ncta), u1 = part_lo(Utot, cta + 1, ncta);
+            const unsigned char* kc = (const unsigned char*)op.k_cache;
+            const unsigned char* vc = (const unsigned char*)op.v_cache;
+            for (int u = u0; u < u1; ++u) {
+                const int kvh = u / ntile, t0 = (u - kvh * ntile) * kAttnT;
+                const uint32_t bytes = (uint32_t)min(kAttnT, ctx - t0) * 256u;
+                const int slot = (int)(q % (uint32_t)h.ns);
+                unsigned char* dst = acquire(2 * bytes);
+                const size_t off = ((size_t)kvh * op.max_seq + t0) * 256;
+                bulk_copy_g2s(dst, kc + off, bytes, &sh.full_bar[slot]);
+                bulk_copy_g2s(dst + kAttnT * 256, vc + off, bytes, &sh.full_bar[slot]);
+            }
+            continue;
+        }
+        const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, cta, ncta);
+        const unsigned char* W[2] = {(const unsigned char*)op.W0, (const unsigned char*)op.W1};
+        for (int i = 0; i < pl.n_items; ++i) {
+            const int n0 = (pl.item0 + i) * pl.R;
+            const int rows = min(pl.R, op.N - n0);
+            if (pl.spi == 1) {
+                const uint32_t bytes = (uint32_t)rows * pl.RB;
+                const int slot = (int)(q % (uint32_t)h.ns);
+                unsigned char* dst = acquire(bytes * pl.nmat);
+                for (int t = 0; t < pl.nmat; ++t)
+                    bulk_copy_g2s_hint(dst + (size_t)t * pl.R * pl.RB, W[t] + (size_t)n0 * pl.RB, bytes, &sh.full_bar[slot], pol);
+            } else {
+                for (int t = 0; t < pl.nmat; ++t)
+                    for (int s = 0; s < pl.nseg; ++s) {
+                        const int slot = (int)(q % (uint32_t)h.ns);
+                        unsigned char* dst = acquire((uint32_t)pl.seg_bytes);
+                        bulk_copy_g2s_hint(dst, W[t] + (size_t)n0 * pl.RB + (size_t)s * pl.seg_bytes, (uint32_t)pl.seg_bytes,
+                                           &sh.full_bar[slot], pol);
+                    }
+            }
+        }
+    }
+    (void)token;
+}
+
+__global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader h) {
+    extern __shared__ __align__(1024) unsigned char dyn[];
+    __shared__ Shared sh;
+    unsigned char* ring = dyn;
+    unsigned char* act = dyn + (size_t)h.ns * kSlotB;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int cta = blockIdx.x, ncta = gridDim.x;
+    griddep_wait();
+    if (tid == 0) {
+        for (int i = 0; i < h.ns; ++i) { mbar_init(&sh.full_bar[i], 1); mbar_init(&sh.empty_bar[i], 1); }
+        mbar_fence_init();
+        sh.key = 0ull;
+        sh.abort_flag = 0;
+    }
+    __syncthreads();
+    Abort ab = {&sh.abort_flag, h.error};
+    const int pos = *h.pos_buf;
+    const int ctx_raw = *h.ctx_buf;
+    int token = *h.token_buf;
+    if (token < 0 || token >= h.vocab) token = 0;
+    const unsigned parity = h.bar[2] & 1u;
+
+    if (warp == kCW) {                                   // ---- producer warp
+        if (lane == 0) producer(h, sh, ring, cta, ncta, token, ctx_raw, ab);   // attention ops clamp the context themselves
+        return;
+    }
+    // ---- consumers
+    unsigned* ctr = h.bar + parity;
+    if (cta == 0 && tid == 0) h.bar[parity ^ 1u] = 0u;   // the other parity's counter: idle during this step
+    unsigned target = 0;
+    uint32_t q_base = 0;
+    float best_v = -INFINITY;
+    int best_i = 0x7fffffff;
+    bool any_argmax = false;
+    const int ctx = ctx_raw;
+    for (int oi = 0; oi < h.n_ops; ++oi) {
+        const pgk_step_op_t& op = h.ops[oi];
+        if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab); }
+        if (op.kind == OP_ATTN) {
+            const int G = op.hq / op.n_kv;
+            if (G <= 4) attn_op<4>(op, h, sh, ring, act, q_base, cta, ncta, pos, ctx, tid, ab);
+            else        attn_op<8>(op, h, sh, ring, act, q_base, cta, ncta, pos, ctx, tid, ab);
+            const long long Utot = (long long)op.n_kv * attn_ntile(attn_ctx(ctx, op.max_seq));
+            q_base += (uint32_t)(part_lo(Utot, cta + 1, ncta) - part_lo(Utot, cta, ncta));
+            target += (unsigned)ncta;
+            grid_sync(ctr, target, tid, ab);
+            if (G <= 4) attn_combine<4>(op, h, cta, ncta, ctx, tid);
+            else        attn_combine<8>(op, h, cta, ncta, ctx, tid);
+        } else {
+            gemv_op(op, h, sh, ring, act, q_base, cta, ncta, token, tid, ab, best_v, best_i);
+            const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, cta, ncta);
+            q_base += (uint32_t)pl.n_items * pl.spi;
+            any_argmax |= (op.flags & F_ARGMAX) != 0;
+        }
+    }
+    if (any_argmax) {
+        if (lane == 0 && best_i != 0x7fffffff) atomicMax(&sh.key, argmax_key(best_v, best_i));
+        consumer_sync();
+        if (tid == 0 && sh.key != 0ull) atomicMax(h.am_key, sh.key);
+    }
+    target += (unsigned)ncta;
+    grid_sync(ctr, target, tid, ab);
+    if (cta == 0 && tid == 0) {
+        if (any_argmax) {
+            const unsigned long long k = atomicExch(h.am_key, 0ull);
+            int tok = 0x7fffffff - (int)(uint32_t)(k & 0xffffffffull);
+            if (tok < 0 || tok >= h.vocab || *ab.s_abort) tok = 0;
+            *h.next_token = tok;
+            *h.token_buf = tok;
+        }
+        if (h.advance) { *h.pos_buf = pos + 1; *h.ctx_buf = ctx_raw + 1; }
+        h.bar[2] = h.bar[2] + 1u;
+    }
+    griddep_launch();
+}
+
+// reference NVF4 layout -> row-packed: one thread per (row n, byte j of the packed row); the source column of output
+// row n is (n / group) * stride + n % group + col0 (plain: group = N; a gate/up tensor interleaved in groups of 8: 8, 16)
+__global__ void nvf4_pack_rows_kernel(const uint8_t* __restrict__ data, const uint8_t* __restrict__ scale,
+                                      uint8_t* __restrict__ packed, int K, int N, int ld, int col0, int group, int stride) {
+    griddep_wait();
+    griddep_launch();
+    const int RB = K / 2 + K / 32;
+    const size_t total = (size_t)N * RB;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int n = (int)(i / RB), j = (int)(i % RB);
+        const size_t col = (size_t)(n / group) * stride + (n % group) + col0;
+        packed[i] = j < K / 2 ? data[(size_t)j * ld + col] : scale[(size_t)(j - K / 2) * ld + col];
+    }
+}
+#endif  // __CUDACC__
+
+struct StepProgram {
+    StepHeader h;
+    pgk_step_op_t* d_ops = nullptr;
+    unsigned* d_bar = nullptr;
+    float* d_ws = nullptr;
+    unsigned long long* d_key = nullptr;
+    int* d_err = nullptr;
+    int ctas = 0;
+    size_t smem = 0;
+};
+
+}  // namespace pgk
+
+using namespace pgk;
+
+extern "C" {
+
+int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf, int32_t* pos_buf, int32_t* ctx_buf,
+                    int32_t* next_token, int vocab, int advance, void** handle) {
+    PGK_REQUIRE(host_ops && n_ops >= 1 && handle, "step_create failed: empty program");
+    PGK_REQUIRE(token_buf && pos_buf && ctx_buf && next_token, "step_create failed: decode state buffers must not be NULL");
+    const int ctas = sm_count();
+    // ---- shared-memory budget: activation area (largest staged vector, or the attention fold scratch), ring = the rest
+    size_t act = 1024, ws_floats = 0;
+    for (int i = 0; i < n_ops; ++i) {
+        const pgk_step_op_t& op = host_ops[i];
+        if (op.kind == OP_ATTN) {
+            PGK_REQUIRE(op.hq > 0 && op.n_kv > 0 && op.hq % op.n_kv == 0 && op.hq / op.n_kv <= 8,
+                        "step_create failed: op %d: attention needs hq %% n_kv == 0 and at most 8 query heads per KV head (hq=%d n_kv=%d)",
+                        i, op.hq, op.n_kv);
+            PGK_REQUIRE(op.act && op.out && op.cos_table && op.sin_table && op.k_cache && op.v_cache && op.max_seq >= 1,
+                        "step_create failed: op %d: attention pointers must not be NULL", i);
+            const int RT = op.hq / op.n_kv <= 4 ? 4 : 8;
+            act = std::max(act, (size_t)8 * RT * kPartStride * sizeof(float));
+            ws_floats = std::max(ws_floats, (size_t)op.n_kv * ctas * RT * kRec);
+            continue;
+        }
+        PGK_REQUIRE(op.kind == OP_FP8 || op.kind == OP_BF16 || op.kind == OP_NVF4R, "step_create failed: op %d: unknown kind %d", i, op.kind);
+        PGK_REQUIRE(op.K >= 64 && op.N >= 1 && op.act && op.W0, "step_create failed: op %d: invalid GEMV (K=%d N=%d)", i, op.K, op.N);
+        const int kmul = op.kind == OP_NVF4R ? 512 : (op.kind == OP_FP8 ? 32 : 16);
+        PGK_REQUIRE(op.K % kmul == 0, "step_create failed: op %d: K=%d must be a multiple of %d for this weight format", i, op.K, kmul);
+        PGK_REQUIRE(op.K / 8 <= 8 * kCT, "step_create failed: op %d: K=%d too large", i, op.K);
+        PGK_REQUIRE(op.kind == OP_NVF4R || (op.kind == OP_FP8 ? op.S0 != nullptr : true), "step_create failed: op %d: missing scales", i);
+        PGK_REQUIRE(!(op.flags & F_SWIGLU) || (op.kind != OP_BF16 && op.W1 && (op.kind == OP_NVF4R || op.S1) && op.out && !op.residual),
+                    "step_create failed: op %d: SWIGLU needs W1 (+S1), out, no residual, FP8 or NVF4 weights", i);
+        PGK_REQUIRE(!(op.flags & F_ARGMAX) || op.kind == OP_BF16, "step_create failed: op %d: ARGMAX rides on a BF16 GEMV", i);
+        PGK_REQUIRE(op.out || (op.flags & F_ARGMAX), "step_create failed: op %d: out is NULL", i);
+        const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, 0, ctas);
+        PGK_REQUIRE(pl.RB % 16 == 0, "step_create failed: op %d: row bytes %d not a multiple of 16", i, pl.RB);
+        PGK_REQUIRE(pl.nseg <= 4 && (pl.nseg == 1 || (pl.RB % pl.nseg == 0 && pl.seg_bytes % 32 == 0)),
+                    "step_create failed: op %d: a row of %d bytes cannot be cut into <= 4 equal 32-byte-aligned slot segments", i, pl.RB);
+        for (const void* w : {op.W0, (op.flags & F_SWIGLU) ? op.W1 : op.W0})
+            PGK_REQUIRE(((uintptr_t)w & 15) == 0, "step_create failed: op %d: weights must be 16-byte aligned", i);
+        PGK_REQUIRE(((uintptr_t)op.act & 15) == 0 && (!op.gamma || ((uintptr_t)op.gamma & 15) == 0),
+                    "step_create failed: op %d: act / gamma must be 16-byte aligned", i);
+        if (op.kind == OP_FP8) {
+            // codes 0x7F / 0xFF are +-480 in the reference's tables but NaN for the hardware conversion this kernel uses
+            // (common.cuh): such tensors stay on the per-op path, which serves them with the exact table kernel
+            bool clean = true;
+            if (int rc = fp8_codes_clean(op.W0, (size_t)op.N * op.K, nullptr, &clean)) return rc;
+            if (clean && (op.flags & F_SWIGLU)) { if (int rc = fp8_codes_clean(op.W1, (size_t)op.N * op.K, nullptr, &clean)) return rc; }
+            PGK_REQUIRE(clean, "step_create failed: op %d: FP8 weights hold E4M3 codes 0x7F/0xFF (table semantics need the per-op path)", i);
+        }
+        act = std::max(act, (size_t)op.K * 2);
+    }
+    act = (act + 1023) & ~(size_t)1023;
+    cudaDeviceProp prop;
+    int dev = 0;
+    PGK_CUDA(cudaGetDevice(&dev));
+    PGK_CUDA(cudaGetDeviceProperties(&prop, dev));
+    cudaFuncAttributes fa;
+    PGK_CUDA(cudaFuncGetAttributes(&fa, step_kernel));
+    const size_t avail = (size_t)prop.sharedMemPerBlockOptin - fa.sharedSizeBytes - 1024;   // 1024: alignment slack of dyn[]
+    PGK_REQUIRE(avail > act + 4 * (size_t)kSlotB, "step_create failed: activation area of %zu bytes leaves no room for the ring", act);
+    int ns = (int)((avail - act) / kSlotB);
+    if (ns > kMaxSlots) ns = kMaxSlots;
+    for (int i = 0; i < n_ops; ++i) {
+        if (host_ops[i].kind == OP_ATTN) continue;
+        const GemvPlan pl = gemv_plan(host_ops[i].kind, host_ops[i].flags, host_ops[i].K, host_ops[i].N, 0, ctas);
+        PGK_REQUIRE(pl.spi <= ns, "step_create failed: op %d needs %d ring slots per item, %d available", i, pl.spi, ns);
+    }
+    StepProgram* sp = new StepProgram();
+    sp->ctas = ctas;
+    sp->smem = (size_t)ns * kSlotB + act;
+    PGK_CUDA(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp->smem));
+    PGK_CUDA(cudaMalloc(&sp->d_ops, sizeof(pgk_step_op_t) * n_ops));
+    PGK_CUDA(cudaMemcpy(sp->d_ops, host_ops, sizeof(pgk_step_op_t) * n_ops, cudaMemcpyHostToDevice));
+    PGK_CUDA(cudaMalloc(&sp->d_bar, 4 * sizeof(unsigned)));
+    PGK_CUDA(cudaMemset(sp->d_bar, 0, 4 * sizeof(unsigned)));
+    PGK_CUDA(cudaMalloc(&sp->d_ws, std::max(ws_floats, (size_t)1) * sizeof(float)));
+    PGK_CUDA(cudaMalloc(&sp->d_key, sizeof(unsigned long long)));
+    PGK_CUDA(cudaMemset(sp->d_key, 0, sizeof(unsigned long long)));
+    PGK_CUDA(cudaMalloc(&sp->d_err, sizeof(int)));
+    PGK_CUDA(cudaMemset(sp->d_err, 0, sizeof(int)));
+    PGK_CUDA(cudaDeviceSynchronize());
+    StepHeader& h = sp->h;
+    h.ops = sp->d_ops; h.n_ops = n_ops; h.ns = ns; h.act_bytes = (int)act; h.vocab = vocab; h.advance = advance;
+    h.token_buf = token_buf; h.pos_buf = pos_buf; h.ctx_buf = ctx_buf; h.next_token = next_token;
+    h.bar = sp->d_bar; h.attn_ws = sp->d_ws; h.am_key = sp->d_key; h.error = sp->d_err;
+    *handle = sp;
+    return 0;
+}
+
+int pgk_step_run(void* handle, void* stream) {
+    PGK_REQUIRE(handle, "step_run failed: NULL program");
+    StepProgram* sp = (StepProgram*)handle;
+    PGK_CUDA(launch(step_kernel, dim3(sp->ctas), dim3(kStepThreads), sp->smem, (cudaStream_t)stream, sp->h));
+    return 0;
+}
+
+int pgk_step_error(void* handle, int* host_code) {
+    PGK_REQUIRE(handle && host_code, "step_error failed: NULL argument");
+    StepProgram* sp = (StepProgram*)handle;
+    PGK_CUDA(cudaDeviceSynchronize());
+    PGK_CUDA(cudaMemcpy(host_code, sp->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int pgk_step_info(void* handle, int* ring_slots, int* act_bytes, int* smem_bytes, int* ctas) {
+    PGK_REQUIRE(handle, "step_info failed: NULL program");
+    StepProgram* sp = (StepProgram*)handle;
+    if (ring_slots) *ring_slots = sp->h.ns;
+    if (act_bytes) *act_bytes = sp->h.act_bytes;
+    if (smem_bytes) *smem_bytes = (int)sp->smem;
+    if (ctas) *ctas = sp->ctas;
+    return 0;
+}
+
+int pgk_step_destroy(void* handle) {
+    if (!handle) return 0;
+    StepProgram* sp = (StepProgram*)handle;
+    cudaFree(sp->d_ops); cudaFree(sp->d_bar); cudaFree(sp->d_ws); cudaFree(sp->d_key); cudaFree(sp->d_err);
+    delete sp;
+    return 0;
+}
+
+int pgk_nvf4_pack_rows(const void* data_kn, const void* scale_kn, void* packed, int K, int N, int ld, int col0, int group,
+                       int stride, void* stream) {
+    PGK_REQUIRE(K >= 32 && K % 32 == 0 && N >= 1 && group >= 1 && ld >= 1, "nvf4_pack_rows failed: invalid shape K=%d N=%d", K, N);
+    const size_t total = (size_t)N * (K / 2 + K / 32);
+    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, 148 * 16);
+    PGK_CUDA(launch(nvf4_pack_rows_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const uint8_t*)data_kn,
+                    (const uint8_t*)scale_kn, (uint8_t*)packed, K, N, ld, col0, group, stride));
+    return 0;
+}
+
+}  // extern "C"

@@ -15,6 +15,7 @@ CUDA graph (`init_decode_graph`) that replays for every position with no host ro
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -55,6 +56,12 @@ class CausalTransformerModel:
         self._graph: CudaGraph | None = None
         self._graph_stream: Stream | None = None
         self._gathered_logits: GPUArray | None = None
+        # one-launch step kernel (llm/step_program.py): built on first use when the model fits it; PGK_STEP=0 or
+        # `use_step_program = False` keeps the per-op launches
+        self.use_step_program = os.environ.get("PGK_STEP", "1") != "0"
+        self._step = None
+        self._step_tried = False
+        self.step_unsupported_reason: str | None = None
 
     # ------------------------------------------------------------------ setup
     @property
@@ -83,7 +90,26 @@ class CausalTransformerModel:
         if self.tp > 1:
             self._gathered_logits = GPUArray((self.tp * v_local,), bfloat16)
         self._graph = None
+        self._step, self._step_tried = None, False
         return self._buffers
+
+    def step_program(self):
+        """The one-launch decode step of this model, or None when the model does not fit it (reason kept in
+        `step_unsupported_reason`) or it is switched off."""
+        if not self.use_step_program:
+            return None
+        if not self._step_tried:
+            from ..step_program import StepProgram, Unsupported
+            self._step_tried = True
+            try:
+                self._step = StepProgram.from_model(self)
+            except Unsupported as e:
+                self._step, self.step_unsupported_reason = None, str(e)
+            except RuntimeError as e:    # the library refused an op shape (message says which)
+                if "step_create failed" not in str(e):
+                    raise
+                self._step, self.step_unsupported_reason = None, str(e)
+        return self._step
 
     @property
     def buffers(self) -> DecodeBuffers:
@@ -187,6 +213,10 @@ class CausalTransformerModel:
         """One greedy token entirely on the device: reads token_buf / position_buf / context_buf,
         writes the sampled token to next_token AND token_buf, then advances position / context."""
         b = self.buffers
+        step = self.step_program()
+        if step is not None:             # ONE persistent kernel: embedding .. argmax .. position advance
+            step.run(_st())
+            return
         hidden = b.hidden.slice_rows(1) if b.hidden.shape[0] != 1 else b.hidden
         self._embed_rows(hidden, 1, 0, b.position_buf, b)
         self._layers(hidden, 0, self._max_seq, b, b.position_buf, b.context_buf)
