@@ -165,9 +165,11 @@ class OracleModel:
     def generate(self, prompt: list[int], n_new: int):
         """Greedy generation token by token (the prompt is also fed one token at a time, which the
         fixed-cache path defines as the same computation as a batched prefill).  Returns
-        (tokens, per-step logits margins top1-top2 in f32)."""
+        (tokens, per-step logits margins top1-top2 in f32); `self.top_logits` keeps the top-1 logit of every step
+        (a margin of one BF16 ulp of that value means the two candidates are ADJACENT BF16 numbers)."""
         toks = list(prompt)
         margins = []
+        self.top_logits = []
         logits = None
         for pos, t in enumerate(prompt):
             logits, nxt = self.step(t, pos, pos + 1)
@@ -175,6 +177,7 @@ class OracleModel:
             f = _f32(logits)
             top2 = np.partition(f, -2)[-2:]
             margins.append(float(top2[1] - top2[0]))
+            self.top_logits.append(float(top2[1]))
             nxt = orc.argmax_bf16(logits)
             toks.append(nxt)
             logits, _ = self.step(nxt, len(toks) - 1, len(toks))

@@ -39,6 +39,12 @@ constexpr int kCT = kCW * 32;           // consumer threads
 constexpr int kStepThreads = kCT + 32;  // + the producer warp
 constexpr int kSlotB = 8192;            // ring slot bytes
 constexpr int kMaxSlots = 26;
+// "full" barriers per slot, used round-robin by ring round.  A parity wait is only meaningful when the waiter is at
+// most one phase ahead of the barrier; a consumer warp jumps kCW items ahead after each item, i.e. up to
+// (kCW - 1) * spi + 1 slots beyond the fills it has seen complete, which can exceed one ring round when an item spans
+// several slots.  With kPhases barriers per slot a warp would have to run kPhases rounds ahead before a wait could be
+// misread (pgk_step_create checks kPhases * slots >= (kCW - 1) * spi + 1).
+constexpr int kPhases = 8;
 constexpr int kAttnT = 16;              // KV positions per attention unit (K tile 4 KB + V tile 4 KB)
 constexpr int kRec = 130;               // partial record: o[128], m, l
 constexpr int kPartStride = 132;        // shared-memory copy of a record (float4 aligned)
@@ -56,6 +62,7 @@ struct StepHeader {
     float* attn_ws;                // [n_kv][ctas][RT][kRec]
     unsigned long long* am_key;    // argmax scratch (zero between steps)
     int* error;
+    unsigned long long* trace;     // [n_ops + 2] globaltimer (ns) when CTA 0 starts each op / finishes the step
 };
 
 // ---------------------------------------------------------------- work split, shared by host validation, the
@@ -111,6 +118,11 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
     unsigned v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(kCT) : "memory"); }
 
@@ -385,7 +397,7 @@ __device__ __forceinline__ float bf16_row(const ItemView& iv, const uint4* a_lo,
 }
 
 struct Shared {
-    uint64_t full_bar[kMaxSlots];
+    uint64_t full_bar[kPhases][kMaxSlots];
     uint64_t empty_bar[kMaxSlots];
     uint16_t q_s[8][128];
     uint16_t new_s[2][128];
@@ -422,7 +434,8 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const StepHeade
         iv.qmod = (int)(q0 % (uint32_t)h.ns);
         for (int s = 0; s < pl.spi; ++s) {
             const uint32_t q = q0 + s;
-            mbar_wait_b(&sh.full_bar[q % h.ns], (q / h.ns) & 1, ab, 200 + op.kind);
+            const uint32_t rnd = q / (uint32_t)h.ns;
+            mbar_wait_b(&sh.full_bar[rnd % kPhases][q % h.ns], (rnd / kPhases) & 1, ab, 200 + op.kind);
         }
         const int n0 = (pl.item0 + i) * pl.R;
         const int rows = min(pl.R, N - n0);
@@ -637,7 +650,8 @@ __device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const StepHeade
         for (int i = first; i < i1; i += kCW) {
             const uint32_t qn = q_base + (uint32_t)i;
             const int slot = (int)(qn % (uint32_t)h.ns);
-            mbar_wait_b(&sh.full_bar[slot], (qn / h.ns) & 1, ab, 204);
+            const uint32_t rnd = qn / (uint32_t)h.ns;
+            mbar_wait_b(&sh.full_bar[rnd % kPhases][slot], (rnd / kPhases) & 1, ab, 204);
             unsigned char* tile = ring + (size_t)slot * kSlotB;
             const int t0 = (u0 + i - kvh * ntile) * kAttnT;
             const int npos = min(kAttnT, ctx - t0);
@@ -753,10 +767,13 @@ __device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsign
                                          int ctx_in, Abort ab) {
     const uint64_t pol = make_evict_first_policy();
     uint32_t q = 0;
+    uint64_t* fb = nullptr;          // the full barrier of the slot handed out last
     auto acquire = [&](uint32_t bytes) -> unsigned char* {
         const int slot = (int)(q % (uint32_t)h.ns);
-        mbar_wait_b(&sh.empty_bar[slot], ((q / h.ns) & 1) ^ 1, ab, 300);
-        mbar_arrive_expect_tx(&sh.full_bar[slot], bytes);
+        const uint32_t rnd = q / (uint32_t)h.ns;
+        mbar_wait_b(&sh.empty_bar[slot], (rnd & 1) ^ 1, ab, 300);
+        fb = &sh.full_bar[rnd % kPhases][slot];
+        mbar_arrive_expect_tx(fb, bytes);
         ++q;
         return ring + (size_t)slot * kSlotB;
     };
@@ -772,11 +789,10 @@ __device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsign
             for (int u = u0; u < u1; ++u) {
                 const int kvh = u / ntile, t0 = (u - kvh * ntile) * kAttnT;
                 const uint32_t bytes = (uint32_t)min(kAttnT, ctx - t0) * 256u;
-                const int slot = (int)(q % (uint32_t)h.ns);
                 unsigned char* dst = acquire(2 * bytes);
                 const size_t off = ((size_t)kvh * op.max_seq + t0) * 256;
-                bulk_copy_g2s(dst, kc + off, bytes, &sh.full_bar[slot]);
-                bulk_copy_g2s(dst + kAttnT * 256, vc + off, bytes, &sh.full_bar[slot]);
+                bulk_copy_g2s(dst, kc + off, bytes, fb);
+                bulk_copy_g2s(dst + kAttnT * 256, vc + off, bytes, fb);
             }
             continue;
         }
@@ -787,17 +803,15 @@ __device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsign
             const int rows = min(pl.R, op.N - n0);
             if (pl.spi == 1) {
                 const uint32_t bytes = (uint32_t)rows * pl.RB;
-                const int slot = (int)(q % (uint32_t)h.ns);
                 unsigned char* dst = acquire(bytes * pl.nmat);
                 for (int t = 0; t < pl.nmat; ++t)
-                    bulk_copy_g2s_hint(dst + (size_t)t * pl.R * pl.RB, W[t] + (size_t)n0 * pl.RB, bytes, &sh.full_bar[slot], pol);
+                    bulk_copy_g2s_hint(dst + (size_t)t * pl.R * pl.RB, W[t] + (size_t)n0 * pl.RB, bytes, fb, pol);
             } else {
                 for (int t = 0; t < pl.nmat; ++t)
                     for (int s = 0; s < pl.nseg; ++s) {
-                        const int slot = (int)(q % (uint32_t)h.ns);
                         unsigned char* dst = acquire((uint32_t)pl.seg_bytes);
                         bulk_copy_g2s_hint(dst, W[t] + (size_t)n0 * pl.RB + (size_t)s * pl.seg_bytes, (uint32_t)pl.seg_bytes,
-                                           &sh.full_bar[slot], pol);
+                                           fb, pol);
                     }
             }
         }
@@ -813,12 +827,12 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int cta = blockIdx.x, ncta = gridDim.x;
     griddep_wait();
-    if (tid == 0) {
-        for (int i = 0; i < h.ns; ++i) { mbar_init(&sh.full_bar[i], 1); mbar_init(&sh.empty_bar[i], 1); }
-        mbar_fence_init();
-        sh.key = 0ull;
-        sh.abort_flag = 0;
+    for (int i = tid; i < h.ns * (kPhases + 1); i += kStepThreads) {
+        const int slot = i % h.ns, ph = i / h.ns;
+        mbar_init(ph == kPhases ? &sh.empty_bar[slot] : &sh.full_bar[ph][slot], 1);
     }
+    if (tid == 0) { sh.key = 0ull; sh.abort_flag = 0; }
+    mbar_fence_init();
     __syncthreads();
     Abort ab = {&sh.abort_flag, h.error};
     const int pos = *h.pos_buf;
@@ -843,6 +857,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     for (int oi = 0; oi < h.n_ops; ++oi) {
         const pgk_step_op_t& op = h.ops[oi];
         if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab); }
+        if (cta == 0 && tid == 0) h.trace[oi] = globaltimer_ns();
         if (op.kind == OP_ATTN) {
             const int G = op.hq / op.n_kv;
             if (G <= 4) attn_op<4>(op, h, sh, ring, act, q_base, cta, ncta, pos, ctx, tid, ab);
@@ -868,6 +883,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     target += (unsigned)ncta;
     grid_sync(ctr, target, tid, ab);
     if (cta == 0 && tid == 0) {
+        h.trace[h.n_ops] = globaltimer_ns();
         if (any_argmax) {
             const unsigned long long k = atomicExch(h.am_key, 0ull);
             int tok = 0x7fffffff - (int)(uint32_t)(k & 0xffffffffull);
@@ -904,6 +920,7 @@ struct StepProgram {
     float* d_ws = nullptr;
     unsigned long long* d_key = nullptr;
     int* d_err = nullptr;
+    unsigned long long* d_trace = nullptr;
     int ctas = 0;
     size_t smem = 0;
 };
@@ -976,7 +993,8 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
     for (int i = 0; i < n_ops; ++i) {
         if (host_ops[i].kind == OP_ATTN) continue;
         const GemvPlan pl = gemv_plan(host_ops[i].kind, host_ops[i].flags, host_ops[i].K, host_ops[i].N, 0, ctas);
-        PGK_REQUIRE(pl.spi <= ns, "step_create failed: op %d needs %d ring slots per item, %d available", i, pl.spi, ns);
+        PGK_REQUIRE(pl.spi <= ns && kPhases * ns >= (kCW - 1) * pl.spi + 1,
+                    "step_create failed: op %d needs %d ring slots per item, %d available", i, pl.spi, ns);
     }
     StepProgram* sp = new StepProgram();
     sp->ctas = ctas;
@@ -989,13 +1007,15 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
     PGK_CUDA(cudaMalloc(&sp->d_ws, std::max(ws_floats, (size_t)1) * sizeof(float)));
     PGK_CUDA(cudaMalloc(&sp->d_key, sizeof(unsigned long long)));
     PGK_CUDA(cudaMemset(sp->d_key, 0, sizeof(unsigned long long)));
+    PGK_CUDA(cudaMalloc(&sp->d_trace, sizeof(unsigned long long) * (n_ops + 2)));
+    PGK_CUDA(cudaMemset(sp->d_trace, 0, sizeof(unsigned long long) * (n_ops + 2)));
     PGK_CUDA(cudaMalloc(&sp->d_err, sizeof(int)));
     PGK_CUDA(cudaMemset(sp->d_err, 0, sizeof(int)));
     PGK_CUDA(cudaDeviceSynchronize());
     StepHeader& h = sp->h;
     h.ops = sp->d_ops; h.n_ops = n_ops; h.ns = ns; h.act_bytes = (int)act; h.vocab = vocab; h.advance = advance;
     h.token_buf = token_buf; h.pos_buf = pos_buf; h.ctx_buf = ctx_buf; h.next_token = next_token;
-    h.bar = sp->d_bar; h.attn_ws = sp->d_ws; h.am_key = sp->d_key; h.error = sp->d_err;
+    h.bar = sp->d_bar; h.attn_ws = sp->d_ws; h.am_key = sp->d_key; h.error = sp->d_err; h.trace = sp->d_trace;
     *handle = sp;
     return 0;
 }
@@ -1025,9 +1045,20 @@ int pgk_step_info(void* handle, int* ring_slots, int* act_bytes, int* smem_bytes
     return 0;
 }
 
+/* globaltimer (ns) at which CTA 0 started each op of the LAST run, then the end of the step: n_ops + 1 values */
+int pgk_step_trace(void* handle, unsigned long long* host_out, int count) {
+    PGK_REQUIRE(handle && host_out, "step_trace failed: NULL argument");
+    StepProgram* sp = (StepProgram*)handle;
+    PGK_REQUIRE(count >= 1 && count <= sp->h.n_ops + 1, "step_trace failed: count %d out of range", count);
+    PGK_CUDA(cudaDeviceSynchronize());
+    PGK_CUDA(cudaMemcpy(host_out, sp->d_trace, sizeof(unsigned long long) * count, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 int pgk_step_destroy(void* handle) {
     if (!handle) return 0;
     StepProgram* sp = (StepProgram*)handle;
+    cudaFree(sp->d_trace);
     cudaFree(sp->d_ops); cudaFree(sp->d_bar); cudaFree(sp->d_ws); cudaFree(sp->d_key); cudaFree(sp->d_err);
     delete sp;
     return 0;

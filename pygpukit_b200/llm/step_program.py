@@ -122,6 +122,13 @@ class StepProgram:
         api.step_error(self._h, C.byref(code))
         return int(code.value)
 
+    def trace(self):
+        """Start time (ns, GPU globaltimer) of every op of the last run as seen by CTA 0, plus the step's end."""
+        import numpy as np
+        buf = np.zeros(self.n_ops + 1, np.uint64)
+        api.step_trace(self._h, buf.ctypes.data_as(C.c_void_p), self.n_ops + 1)
+        return buf
+
     def info(self) -> dict:
         v = [C.c_int32(0) for _ in range(4)]
         api.step_info(self._h, *[C.byref(x) for x in v])

@@ -1,0 +1,73 @@
+"""Per-op timing INSIDE the one-launch step kernel (pgk_step_trace: globaltimer at which CTA 0 starts each op).
+
+    python scripts/step_trace.py --model llama3-8b --format fp8 --context 4096 [--steps 16]
+
+Prints, per op slot of a layer (qkv, attention, o_proj, gate/up, down) and for the lm_head, the mean duration over layers
+and steps with the bytes the op streams and the resulting GB/s.  A duration includes the grid barrier that ends the op."""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from pygpukit_b200 import llm  # noqa: E402
+from pygpukit_b200._lib import api  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="llama3-8b")
+    ap.add_argument("--format", default="fp8")
+    ap.add_argument("--context", type=int, default=4096)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--layers", type=int, default=None)
+    a = ap.parse_args()
+    api.set_pdl(1)
+    m = llm.build_random_model(a.model, a.format, max_seq=a.context, num_layers=a.layers)
+    m.init_decode(a.context)
+    for blk in m.blocks:
+        for c in (blk.attn._k_cache, blk.attn._v_cache):
+            api.fill_normal_bf16(c.device_ptr, c.size, 7, 0.1, None)
+    m.init_decode_graph()
+    prog = m.step_program()
+    if prog is None:
+        raise SystemExit(f"no step program: {m.step_unsupported_reason}")
+    print("info", prog.info())
+    L = len(m.blocks)
+    p0 = a.context - a.steps - 4
+    m.set_decode_state(123, p0)
+    acc = []
+    for _ in range(a.steps):
+        m.decode_graph_replay()
+        t = prog.trace().astype(np.int64)
+        acc.append(np.diff(t))
+    assert prog.error() == 0
+    d = np.array(acc[2:], np.float64) / 1e3          # us, [steps, n_ops]
+    per_layer = d[:, :5 * L].reshape(-1, L, 5)
+    blk = m.blocks[0]
+    cfg = m.config
+    H = cfg.hidden_size
+    kvb = 2 * blk.attn.num_kv_heads * a.context * 128 * 2
+    names = ["qkv (+norm)", "attention (+fold)", "o_proj (+res)", "gate/up (+norm, swiglu)", "down (+res)"]
+    byts = [blk.attn.qkv_proj.weight_bytes, kvb, blk.attn.o_proj.weight_bytes,
+            blk.mlp.weight_bytes - blk.mlp.down_proj.weight_bytes, blk.mlp.down_proj.weight_bytes]
+    tot_us, tot_b = 0.0, 0.0
+    for i, (n, b) in enumerate(zip(names, byts)):
+        us = per_layer[:, :, i].mean()
+        tot_us += us
+        tot_b += b
+        print(f"{n:26s} {b / 1e6:8.2f} MB {us:7.2f} us {b / us / 1e3:7.0f} GB/s   (min {per_layer[:, :, i].min():.2f} max {per_layer[:, :, i].max():.2f})")
+    print(f"{'layer':26s} {tot_b / 1e6:8.2f} MB {tot_us:7.2f} us {tot_b / tot_us / 1e3:7.0f} GB/s")
+    hb = m._head.nbytes
+    us = d[:, 5 * L].mean()
+    print(f"{'lm_head (+norm, argmax)':26s} {hb / 1e6:8.2f} MB {us:7.2f} us {hb / us / 1e3:7.0f} GB/s")
+    print(f"step {d.sum(axis=1).mean():.1f} us (CTA 0, first op start .. end)")
+    _ = H
+
+
+if __name__ == "__main__":
+    main()

@@ -207,13 +207,17 @@ def test_step_model_tokens_match_oracle_and_graph_equals_eager(name, fmt):
     model.init_decode(MAX_SEQ, max_batch_size=16)
     rng = np.random.default_rng(3)
     prompt = [int(t) for t in rng.integers(0, model.config.vocab_size, 12)]
-    exp, margins = OracleModel(model, MAX_SEQ).generate(prompt, 128)
+    om = OracleModel(model, MAX_SEQ)
+    exp, margins = om.generate(prompt, 128)
     got = model.generate(prompt, 128, temperature=0.0, use_graph=True)
     assert model.step_program() is not None, model.step_unsupported_reason
     assert model.step_program().error() == 0
     for i, (a, e) in enumerate(zip(got[len(prompt):], exp[len(prompt):])):
         if a != e:
-            assert margins[i] <= 2.0 ** -6, f"token {i}: got {a}, oracle {e}, margin {margins[i]}"
+            # a divergence is a tie only when the oracle's two best logits are equal or ADJACENT BF16 numbers (one flipped
+            # rounding of either swaps them); it ends the comparison
+            ulp = 2.0 ** (np.floor(np.log2(max(abs(om.top_logits[i]), 1e-30))) - 7)
+            assert margins[i] <= ulp, f"token {i}: got {a}, oracle {e}, margin {margins[i]} (> one BF16 ulp {ulp})"
             assert i >= 32
             break
     model2 = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, seed=7, std=0.05)
