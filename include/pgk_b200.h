@@ -358,7 +358,7 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
 int pgk_step_run(void* handle, void* stream);           /* ONE kernel launch; CUDA-graph capturable */
 int pgk_step_error(void* handle, int* host_code);       /* synchronises; 0 = every wait of the last runs completed */
 int pgk_step_info(void* handle, int* ring_slots, int* act_bytes, int* smem_bytes, int* ctas);
-/* profiling aid: globaltimer (ns) at which CTA 0 started each op of the last run, then the step's end (n_ops + 1 values) */
+/* profiling aid: (n_ops + 1) x 8 globaltimer (ns) stamps taken by CTA 0 during the last run (see csrc/step.cu) */
 int pgk_step_trace(void* handle, unsigned long long* host_out, int count);
 int pgk_step_destroy(void* handle);
 /* reference NVF4 layout (data u8 [K/2,ld], scale u8 [K/32,ld], ops/matmul/nvf4.py:14-26) -> row-packed [N, K/2 + K/32];

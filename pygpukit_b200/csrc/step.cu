@@ -22,7 +22,7 @@
 //     query heads of the group in registers (lane = 4 head dims); per-(kv head, CTA) partial records in L2, then a
 //     grid barrier and a distributed fold in CTA order (deterministic).
 //   * grid barrier: one monotone counter per step parity (red.release.gpu + ld.acquire.gpu spin by one thread,
-//     named barrier for the 512 consumer threads).  Every wait is bounded: on a timeout the kernel records an error
+//     named barrier for the consumer threads).  Every wait is bounded: on a timeout the kernel records an error
 //     code and runs to completion without waiting any more (results are then garbage; pgk_step_error reports it).
 #include "common.cuh"
 #include "gemv_common.cuh"
@@ -34,20 +34,22 @@
 
 namespace pgk {
 
-constexpr int kCW = 15;                 // consumer warps (+ 1 producer warp = 512 threads: 128 registers each)
+constexpr int kCW = 14;                 // consumer warps
+constexpr int kNP = 2;                  // producer warps (one issuing thread each; slot q belongs to producer q % kNP)
 constexpr int kCT = kCW * 32;           // consumer threads
-constexpr int kStepThreads = kCT + 32;  // + the producer warp
-constexpr int kSlotB = 8192;            // ring slot bytes
-constexpr int kMaxSlots = 26;
+constexpr int kStepThreads = kCT + 32 * kNP;   // 512 threads: 128 registers each
+constexpr int kSlotB = 16384;           // ring slot bytes
+constexpr int kMaxSlots = 13;
 // "full" barriers per slot, used round-robin by ring round.  A parity wait is only meaningful when the waiter is at
 // most one phase ahead of the barrier; a consumer warp jumps kCW items ahead after each item, i.e. up to
 // (kCW - 1) * spi + 1 slots beyond the fills it has seen complete, which can exceed one ring round when an item spans
 // several slots.  With kPhases barriers per slot a warp would have to run kPhases rounds ahead before a wait could be
 // misread (pgk_step_create checks kPhases * slots >= (kCW - 1) * spi + 1).
 constexpr int kPhases = 8;
-constexpr int kAttnT = 16;              // KV positions per attention unit (K tile 4 KB + V tile 4 KB)
+constexpr int kAttnT = 32;              // KV positions per attention unit (K tile 8 KB + V tile 8 KB = one slot)
 constexpr int kRec = 130;               // partial record: o[128], m, l
 constexpr int kPartStride = 132;        // shared-memory copy of a record (float4 aligned)
+constexpr int kTracePts = 8;            // trace stamps per op (CTA 0)
 constexpr long long kSpinLimit = 3000000000LL;   // cycles (~1.5 s): far beyond any legitimate wait
 constexpr float kNeg = -1e30f;
 
@@ -59,20 +61,22 @@ struct StepHeader {
     int n_ops, ns, act_bytes, vocab, advance;
     int32_t* token_buf; int32_t* pos_buf; int32_t* ctx_buf; int32_t* next_token;
     unsigned* bar;                 // [0],[1] grid-barrier counters by step parity, [2] step counter
-    float* attn_ws;                // [n_kv][ctas][RT][kRec]
+    float* attn_ws;                // [ctas][RT][kRec]
     unsigned long long* am_key;    // argmax scratch (zero between steps)
     int* error;
-    unsigned long long* trace;     // [n_ops + 2] globaltimer (ns) when CTA 0 starts each op / finishes the step
+    unsigned long long* trace;     // [(n_ops + 1) * kTracePts] globaltimer (ns) stamps of CTA 0
 };
 
 // ---------------------------------------------------------------- work split, shared by host validation, the
-// producer and the consumers (all three must agree exactly)
+// producers and the consumers (all must agree exactly).  32-bit arithmetic only: 64-bit division is a ~100-instruction
+// routine on the GPU.
 struct GemvPlan {
     int RB, nmat, R, nseg, seg_bytes, spi, items_total, item0, n_items;
 };
 __host__ __device__ inline int op_row_bytes(int kind, int K) {
     return kind == OP_FP8 ? K : (kind == OP_BF16 ? 2 * K : (K / 2 + K / 32));
 }
+__host__ __device__ inline unsigned part_lo(unsigned total, unsigned cta, unsigned ncta) { return total * cta / ncta; }
 __host__ __device__ inline GemvPlan gemv_plan(int kind, int flags, int K, int N, int cta, int ncta) {
     GemvPlan p;
     p.RB = op_row_bytes(kind, K);
@@ -83,13 +87,28 @@ __host__ __device__ inline GemvPlan gemv_plan(int kind, int flags, int K, int N,
         p.R = 1; p.nseg = (p.RB + kSlotB - 1) / kSlotB; p.seg_bytes = p.RB / p.nseg; p.spi = p.nmat * p.nseg;
     }
     p.items_total = (N + p.R - 1) / p.R;
-    p.item0 = (int)((long long)cta * p.items_total / ncta);
-    p.n_items = (int)((long long)(cta + 1) * p.items_total / ncta) - p.item0;
+    p.item0 = (int)part_lo((unsigned)p.items_total, (unsigned)cta, (unsigned)ncta);
+    p.n_items = (int)part_lo((unsigned)p.items_total, (unsigned)cta + 1u, (unsigned)ncta) - p.item0;
     return p;
 }
-__host__ __device__ inline int attn_ntile(int ctx) { return (ctx + kAttnT - 1) / kAttnT; }
+// attention: the CTAs are dealt to the KV heads in contiguous groups (CTA c serves head c * n_kv / ncta), the head's
+// tiles of kAttnT positions are dealt evenly over the CTAs of its group
+struct AttnPlan {
+    int kvh, cfirst, gs, ntile, u0, u1;
+};
 __host__ __device__ inline int attn_ctx(int ctx, int max_seq) { return ctx < 1 ? 1 : (ctx > max_seq ? max_seq : ctx); }
-__host__ __device__ inline int part_lo(long long total, int cta, int ncta) { return (int)(total * cta / ncta); }
+__host__ __device__ inline int attn_cfirst(int k, int n_kv, int ncta) { return (k * ncta + n_kv - 1) / n_kv; }
+__host__ __device__ inline AttnPlan attn_plan(int n_kv, int ctx, int cta, int ncta) {
+    AttnPlan a;
+    a.kvh = cta * n_kv / ncta;
+    a.cfirst = attn_cfirst(a.kvh, n_kv, ncta);
+    a.gs = attn_cfirst(a.kvh + 1, n_kv, ncta) - a.cfirst;
+    a.ntile = (ctx + kAttnT - 1) / kAttnT;
+    const int lc = cta - a.cfirst;
+    a.u0 = lc * a.ntile / a.gs;
+    a.u1 = (lc + 1) * a.ntile / a.gs;
+    return a;
+}
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- bounded waits
@@ -119,6 +138,9 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void red_release_gpu_inc(unsigned* p) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(p) : "memory");
+}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -126,21 +148,21 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(kCT) : "memory"); }
 
-// all 512 consumer threads of every CTA: arrive + wait on the step's monotone counter
-__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned target, int tid, Abort ab) {
-    consumer_sync();                         // every consumer thread's global writes are ordered before thread 0's fence
+// all consumer threads of every CTA: arrive + wait on the step's monotone counter.  The CTA barrier orders every
+// consumer thread's global writes before thread 0's release (cumulativity); the acquire + second CTA barrier order the
+// other CTAs' writes before every thread's later loads (which bypass L1: ld.global.cg / ld.global.nc of constants only).
+__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned target, int tid, Abort ab, unsigned long long* tr) {
+    consumer_sync();
     if (tid == 0) {
-        __threadfence();
-        atomicAdd(ctr, 1u);
+        if (tr) tr[0] = globaltimer_ns();
+        red_release_gpu_inc(ctr);
         if ((int)(ld_acquire_gpu(ctr) - target) < 0) {
             const long long t0 = clock64();
             while ((int)(ld_acquire_gpu(ctr) - target) < 0) {
                 if (*ab.s_abort) break;
                 if (clock64() - t0 > kSpinLimit) { *ab.s_abort = 1; atomicCAS(ab.gerr, 0, 100); break; }
-                __nanosleep(20);
             }
         }
-        __threadfence();
     }
     consumer_sync();
 }
@@ -150,10 +172,17 @@ __device__ __forceinline__ uint64_t make_evict_first_policy() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
-__device__ __forceinline__ void bulk_copy_g2s_hint(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar,
-                                                   uint64_t pol) {
+__device__ __forceinline__ void bulk_copy_hint(uint32_t smem_dst, const void* gmem_src, uint32_t bytes, uint32_t bar,
+                                               uint64_t pol) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                 :: "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+                 :: "r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_plain(uint32_t smem_dst, const void* gmem_src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_u32(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
 }
 
 // this lane's 32-byte chunk (lane stride 32 bytes) without bank conflicts: the lanes of a quarter warp read the
@@ -183,7 +212,7 @@ struct ItemView {
     }
 };
 
-// ---------------------------------------------------------------- activation staging by the 512 consumer threads
+// ---------------------------------------------------------------- activation staging by the consumer threads
 // Same arithmetic as stage_activations_f16 / stage_activations_bf16 (gemv_common.cuh, gemv_bf16.cu): the row is read
 // once, the RMSNorm statistics follow the reference's summation tree (row_inv_rms_ref_order), elements are
 // normalised as bf16(x * inv * gamma), then either kept as bf16 (TO_F16 = false) or range-shifted to f16.
@@ -257,11 +286,11 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
     }
     consumer_sync();
 }
-// few vectors per thread for the common K <= 11520 (no spills), eight for the long rows (K up to 30720)
+// four vectors per thread for K <= 14336 (no spills), eight for the long rows (K up to 28672)
 template <int PL, bool TO_F16>
 __device__ __forceinline__ void stage_act(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
                                           float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid) {
-    if ((K >> 3) <= 3 * kCT) stage_act_v<PL, TO_F16, 3>(A, K, gamma, eps, act, red, inv_s, tid);
+    if ((K >> 3) <= 4 * kCT) stage_act_v<PL, TO_F16, 4>(A, K, gamma, eps, act, red, inv_s, tid);
     else                     stage_act_v<PL, TO_F16, 8>(A, K, gamma, eps, act, red, inv_s, tid);
 }
 
@@ -399,6 +428,7 @@ __device__ __forceinline__ float bf16_row(const ItemView& iv, const uint4* a_lo,
 struct Shared {
     uint64_t full_bar[kPhases][kMaxSlots];
     uint64_t empty_bar[kMaxSlots];
+    pgk_step_op_t op[2];             // descriptor of the current / next op (double buffered)
     uint16_t q_s[8][128];
     uint16_t new_s[2][128];
     uint32_t red[80];
@@ -407,48 +437,57 @@ struct Shared {
     int abort_flag;
 };
 
+// slot bookkeeping without divisions: (slot index in the ring, ring round)
+struct SlotPos {
+    int s; uint32_t r;
+    __device__ __forceinline__ void advance(int n, int ns) { s += n; while (s >= ns) { s -= ns; ++r; } }
+};
+
 // ---------------------------------------------------------------- one GEMV-type op, consumer side
-__device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const StepHeader& h, Shared& sh, unsigned char* ring,
-                                        unsigned char* act, uint32_t q_base, int cta, int ncta, int token, int tid, Abort ab,
-                                        float& best_v, int& best_i) {
+__device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan& pl, const StepHeader& h, Shared& sh,
+                                        unsigned char* ring, unsigned char* act, SlotPos base, int token, int tid, Abort ab,
+                                        float& best_v, int& best_i, unsigned long long* tr) {
     const int lane = tid & 31, warp = tid >> 5;
-    const int K = op.K, N = op.N;
-    const GemvPlan pl = gemv_plan(op.kind, op.flags, K, N, cta, ncta);
-    const uint16_t* A = (const uint16_t*)op.act + ((op.flags & F_ACT_EMBED) ? (size_t)token * K : 0);
+    const int K = op.K, N = op.N, kind = op.kind, flags = op.flags;
+    const uint16_t* A = (const uint16_t*)op.act + ((flags & F_ACT_EMBED) ? (size_t)token * K : 0);
     const uint16_t* gam = (const uint16_t*)op.gamma;
-    if (op.kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
-    else if (op.kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
-    else                          stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    if (kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    else if (kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    else                       stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    if (tr && tid == 0) tr[1] = globaltimer_ns();
     RowOut ro;
     ro.C = (uint16_t*)op.out;
-    ro.residual = op.residual ? (const uint16_t*)op.residual + ((op.flags & F_RES_EMBED) ? (size_t)token * N : 0) : nullptr;
-    ro.inv = (op.kind == OP_BF16) ? 1.f : sh.inv_s[0];
+    ro.residual = op.residual ? (const uint16_t*)op.residual + ((flags & F_RES_EMBED) ? (size_t)token * N : 0) : nullptr;
+    ro.inv = (kind == OP_BF16) ? 1.f : sh.inv_s[0];
     ro.alpha = op.alpha;
-    ro.flags = op.flags;
+    ro.flags = flags;
     const uint4* a_lo = reinterpret_cast<const uint4*>(act);
-    const int nchunk = (op.kind == OP_FP8) ? (K >> 5) : (op.kind == OP_NVF4R ? (K >> 6) : (K >> 4));
+    const int nchunk = (kind == OP_FP8) ? (K >> 5) : (kind == OP_NVF4R ? (K >> 6) : (K >> 4));
     ItemView iv;
     iv.ring = ring; iv.ns = h.ns; iv.R = pl.R; iv.RB = pl.RB; iv.nseg = pl.nseg; iv.seg_bytes = pl.seg_bytes; iv.spi = pl.spi;
+    SlotPos sp = base;
+    sp.advance(warp * pl.spi, h.ns);
     for (int i = warp; i < pl.n_items; i += kCW) {
-        const uint32_t q0 = q_base + (uint32_t)i * pl.spi;
-        iv.qmod = (int)(q0 % (uint32_t)h.ns);
-        for (int s = 0; s < pl.spi; ++s) {
-            const uint32_t q = q0 + s;
-            const uint32_t rnd = q / (uint32_t)h.ns;
-            mbar_wait_b(&sh.full_bar[rnd % kPhases][q % h.ns], (rnd / kPhases) & 1, ab, 200 + op.kind);
+        iv.qmod = sp.s;
+        {
+            SlotPos w = sp;
+            for (int j = 0; j < pl.spi; ++j) {
+                mbar_wait_b(&sh.full_bar[w.r & (kPhases - 1)][w.s], (w.r / kPhases) & 1, ab, 200 + kind);
+                w.advance(1, h.ns);
+            }
         }
         const int n0 = (pl.item0 + i) * pl.R;
         const int rows = min(pl.R, N - n0);
-        if (op.kind == OP_FP8) {
-            if (op.flags & F_SWIGLU) {
+        if (kind == OP_FP8) {
+            if (flags & F_SWIGLU) {
                 for (int r = 0; r < rows; ++r) fp8_rows<2, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
             } else {
                 int r = 0;
                 for (; r + 2 <= rows; r += 2) fp8_rows<1, 2>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
                 if (r < rows) fp8_rows<1, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
             }
-        } else if (op.kind == OP_NVF4R) {
-            if (op.flags & F_SWIGLU) {
+        } else if (kind == OP_NVF4R) {
+            if (flags & F_SWIGLU) {
                 for (int r = 0; r < rows; ++r) nvf4_rows<2, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
             } else {
                 int r = 0;
@@ -460,7 +499,7 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const StepHeade
                 const float v = bf16_row(iv, a_lo, nchunk, r, lane);
                 if (lane == 0) {
                     const uint16_t ob = finish_row(ro, n0 + r, v);
-                    if (op.flags & F_ARGMAX) {
+                    if (flags & F_ARGMAX) {
                         const float rv = bf16_bits_to_f32(ob);
                         if (rv > best_v) { best_v = rv; best_i = n0 + r; }   // rows ascend within a warp: first max kept
                     }
@@ -468,9 +507,13 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const StepHeade
             }
         }
         __syncwarp();
-        if (lane == 0)
-            for (int s = 0; s < pl.spi; ++s) mbar_arrive(&sh.empty_bar[(q0 + s) % h.ns]);
+        if (lane == 0) {
+            SlotPos w = sp;
+            for (int j = 0; j < pl.spi; ++j) { mbar_arrive(&sh.empty_bar[w.s]); w.advance(1, h.ns); }
+        }
+        sp.advance(kCW * pl.spi, h.ns);
     }
+    if (tr && tid == 0) tr[2] = globaltimer_ns();
 }
 
 // ---------------------------------------------------------------- attention op, consumer side
@@ -592,15 +635,11 @@ __device__ __forceinline__ void step_norm_rope128(const uint16_t* row, const uin
 }
 
 template <int RT>
-__device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const StepHeader& h, Shared& sh, unsigned char* ring,
-                                        unsigned char* act, uint32_t q_base, int cta, int ncta, int pos, int ctx_in, int tid,
-                                        Abort ab) {
+__device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const AttnPlan& ap, const StepHeader& h, Shared& sh,
+                                        unsigned char* ring, unsigned char* act, SlotPos base, int cta, int pos, int ctx, int tid,
+                                        Abort ab, unsigned long long* tr) {
     const int lane = tid & 31, warp = tid >> 5;
     const int hq = op.hq, n_kv = op.n_kv, G = hq / n_kv, max_seq = op.max_seq;
-    const int ctx = attn_ctx(ctx_in, max_seq);
-    const int ntile = attn_ntile(ctx);
-    const long long Utot = (long long)n_kv * ntile;
-    const int u0 = part_lo(Utot, cta, ncta), u1 = part_lo(Utot, cta + 1, ncta);
     const uint16_t* qkv = (const uint16_t*)op.act;
     uint16_t* kc = (uint16_t*)op.k_cache;
     uint16_t* vc = (uint16_t*)op.v_cache;
@@ -611,149 +650,144 @@ __device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const StepHeade
     const float scale = op.scale > 0.f ? op.scale : 0.08838834764831845f;   // 1/sqrt(128)
     const float scale_log2 = scale * 1.4426950408889634f;
     float* part = reinterpret_cast<float*>(act);     // [8][RT][kPartStride]
-
-    int u = u0;
-    while (u < u1) {
-        const int kvh = u / ntile;
-        const int seg_end = min(u1, (kvh + 1) * ntile);
-        // ---- the group's query rows and the new K / V row
-        const int uw = kvh * ntile + (has_new ? pos / kAttnT : 0);
-        const bool writer = pos < max_seq && uw >= u0 && uw < u1;
-        if (warp < RT) {
-            if (warp < G) step_norm_rope128(qkv + (size_t)(kvh * G + warp) * 128, (const uint16_t*)op.q_gamma, op.attn_eps, cs, sn,
-                                            lane, sh.q_s[warp], nullptr);
-            else for (int d = lane; d < 128; d += 32) sh.q_s[warp][d] = 0;
-        } else if (warp == RT) {
-            uint16_t* dst = writer ? kc + ((size_t)kvh * max_seq + pos) * 128 : nullptr;
-            step_norm_rope128(qkv + (size_t)(hq + kvh) * 128, (const uint16_t*)op.k_gamma, op.attn_eps, cs, sn, lane,
-                              sh.new_s[0], dst);
-        } else if (warp == RT + 1) {
-            const uint16_t* src = qkv + (size_t)(hq + n_kv + kvh) * 128;
-            uint16_t* dst = writer ? vc + ((size_t)kvh * max_seq + pos) * 128 : nullptr;
-            for (int d = lane; d < 128; d += 32) { const uint16_t v = ld_act2(src + d); sh.new_s[1][d] = v; if (dst) dst[d] = v; }
+    const int kvh = ap.kvh, u0 = ap.u0, u1 = ap.u1;
+    if (u0 >= u1) return;                             // CTA-uniform: more CTAs than tiles in this head's group
+    // ---- the group's query rows and the new K / V row
+    const int tw = has_new ? pos / kAttnT : 0;
+    const bool writer = pos < max_seq && tw >= u0 && tw < u1;
+    if (warp < RT) {
+        if (warp < G) step_norm_rope128(qkv + (size_t)(kvh * G + warp) * 128, (const uint16_t*)op.q_gamma, op.attn_eps, cs, sn,
+                                        lane, sh.q_s[warp], nullptr);
+        else for (int d = lane; d < 128; d += 32) sh.q_s[warp][d] = 0;
+    } else if (warp == RT) {
+        uint16_t* dst = writer ? kc + ((size_t)kvh * max_seq + pos) * 128 : nullptr;
+        step_norm_rope128(qkv + (size_t)(hq + kvh) * 128, (const uint16_t*)op.k_gamma, op.attn_eps, cs, sn, lane,
+                          sh.new_s[0], dst);
+    } else if (warp == RT + 1) {
+        const uint16_t* src = qkv + (size_t)(hq + n_kv + kvh) * 128;
+        uint16_t* dst = writer ? vc + ((size_t)kvh * max_seq + pos) * 128 : nullptr;
+        for (int d = lane; d < 128; d += 32) { const uint16_t v = ld_act2(src + d); sh.new_s[1][d] = v; if (dst) dst[d] = v; }
+    }
+    consumer_sync();
+    if (tr && tid == 0) tr[1] = globaltimer_ns();
+    uint32_t q[RT][2];
+#pragma unroll
+    for (int r = 0; r < RT; ++r) {
+        const uint2 v = *reinterpret_cast<const uint2*>(&sh.q_s[r][lane * 4]);
+        q[r][0] = v.x; q[r][1] = v.y;
+    }
+    AttnState<RT> st;
+    st.m_own = kNeg; st.l_own = 0.f;
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) st.o[r][e] = 0.f;
+    SlotPos sp = base;
+    sp.advance(warp, h.ns);
+    for (int t = u0 + warp; t < u1; t += kCW) {
+        mbar_wait_b(&sh.full_bar[sp.r & (kPhases - 1)][sp.s], (sp.r / kPhases) & 1, ab, 204);
+        unsigned char* tile = ring + (size_t)sp.s * kSlotB;
+        const int t0 = t * kAttnT;
+        const int npos = min(kAttnT, ctx - t0);
+        const bool patch = has_new && pos >= t0 && pos < t0 + npos;     // warp-uniform
+        if (patch) {
+            *reinterpret_cast<uint2*>(tile + (size_t)(pos - t0) * 256 + lane * 8) =
+                *reinterpret_cast<const uint2*>(&sh.new_s[0][lane * 4]);
+            *reinterpret_cast<uint2*>(tile + kAttnT * 256 + (size_t)(pos - t0) * 256 + lane * 8) =
+                *reinterpret_cast<const uint2*>(&sh.new_s[1][lane * 4]);
+            __syncwarp();
+        }
+        attn_unit<RT>(st, tile, npos, q, scale_log2, lane);
+        if (patch) fence_proxy_async();   // the patch was a generic-proxy write; the slot's next fill is a TMA write
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh.empty_bar[sp.s]);
+        sp.advance(kCW, h.ns);
+    }
+    if (tr && tid == 0) tr[2] = globaltimer_ns();
+    // ---- fold the warps' states (8 warps at a time through shared memory), write the CTA's record
+    constexpr int NX = (RT * 128 + kCT - 1) / kCT;       // outputs (row, dim) per thread
+    float Mr[NX], Or[NX], Lr[NX];
+#pragma unroll
+    for (int x = 0; x < NX; ++x) { Mr[x] = kNeg; Or[x] = 0.f; Lr[x] = 0.f; }
+    for (int grp = 0; grp < (kCW + 7) / 8; ++grp) {
+        const int nw = min(8, kCW - grp * 8);
+        if ((warp >> 3) == grp) {
+            const int w8 = warp & 7;
+#pragma unroll
+            for (int r = 0; r < RT; ++r)
+                *reinterpret_cast<float4*>(&part[(w8 * RT + r) * kPartStride + 4 * lane]) =
+                    make_float4(st.o[r][0], st.o[r][1], st.o[r][2], st.o[r][3]);
+            if (lane < RT) {
+                part[(w8 * RT + lane) * kPartStride + 128] = st.m_own;
+                part[(w8 * RT + lane) * kPartStride + 129] = st.l_own;
+            }
         }
         consumer_sync();
-        uint32_t q[RT][2];
-#pragma unroll
-        for (int r = 0; r < RT; ++r) {
-            const uint2 v = *reinterpret_cast<const uint2*>(&sh.q_s[r][lane * 4]);
-            q[r][0] = v.x; q[r][1] = v.y;
-        }
-        AttnState<RT> st;
-        st.m_own = kNeg; st.l_own = 0.f;
-#pragma unroll
-        for (int r = 0; r < RT; ++r)
-#pragma unroll
-            for (int e = 0; e < 4; ++e) st.o[r][e] = 0.f;
-        const int i0 = u - u0, i1 = seg_end - u0;
-        int first = i0 + (((warp - i0) % kCW) + kCW) % kCW;
-        for (int i = first; i < i1; i += kCW) {
-            const uint32_t qn = q_base + (uint32_t)i;
-            const int slot = (int)(qn % (uint32_t)h.ns);
-            const uint32_t rnd = qn / (uint32_t)h.ns;
-            mbar_wait_b(&sh.full_bar[rnd % kPhases][slot], (rnd / kPhases) & 1, ab, 204);
-            unsigned char* tile = ring + (size_t)slot * kSlotB;
-            const int t0 = (u0 + i - kvh * ntile) * kAttnT;
-            const int npos = min(kAttnT, ctx - t0);
-            if (has_new && pos >= t0 && pos < t0 + npos) {          // warp-uniform: patch the new row into the staged tile
-                *reinterpret_cast<uint2*>(tile + (size_t)(pos - t0) * 256 + lane * 8) =
-                    *reinterpret_cast<const uint2*>(&sh.new_s[0][lane * 4]);
-                *reinterpret_cast<uint2*>(tile + kAttnT * 256 + (size_t)(pos - t0) * 256 + lane * 8) =
-                    *reinterpret_cast<const uint2*>(&sh.new_s[1][lane * 4]);
-                __syncwarp();
-            }
-            attn_unit<RT>(st, tile, npos, q, scale_log2, lane);
-            fence_proxy_async();          // the patch above was a generic-proxy write; the slot's next fill is a TMA write
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sh.empty_bar[slot]);
-        }
-        // ---- fold the warps' states (8 warps at a time through shared memory), write the CTA's record
-        constexpr int NX = (RT * 128 + kCT - 1) / kCT;       // outputs (row, dim) per thread
-        float Mr[NX], Or[NX], Lr[NX];
-#pragma unroll
-        for (int x = 0; x < NX; ++x) { Mr[x] = kNeg; Or[x] = 0.f; Lr[x] = 0.f; }
-        for (int grp = 0; grp < (kCW + 7) / 8; ++grp) {
-            const int nw = min(8, kCW - grp * 8);
-            if ((warp >> 3) == grp) {
-                const int w8 = warp & 7;
-#pragma unroll
-                for (int r = 0; r < RT; ++r)
-                    *reinterpret_cast<float4*>(&part[(w8 * RT + r) * kPartStride + 4 * lane]) =
-                        make_float4(st.o[r][0], st.o[r][1], st.o[r][2], st.o[r][3]);
-                if (lane < RT) {
-                    part[(w8 * RT + lane) * kPartStride + 128] = st.m_own;
-                    part[(w8 * RT + lane) * kPartStride + 129] = st.l_own;
-                }
-            }
-            consumer_sync();
-#pragma unroll
-            for (int x = 0; x < NX; ++x) {
-                const int idx = tid + x * kCT;
-                if (idx < RT * 128) {
-                    const int r = idx >> 7, d = idx & 127;
-                    float mn = kNeg;
-                    for (int w = 0; w < nw; ++w) mn = fmaxf(mn, part[(w * RT + r) * kPartStride + 128]);
-                    float ov = 0.f, lv = 0.f;
-                    for (int w = 0; w < nw; ++w) {
-                        const float c = exp2f(part[(w * RT + r) * kPartStride + 128] - mn);
-                        ov = fmaf(part[(w * RT + r) * kPartStride + d], c, ov);
-                        lv = fmaf(part[(w * RT + r) * kPartStride + 129], c, lv);
-                    }
-                    const float Mn = fmaxf(Mr[x], mn);
-                    const float c1 = exp2f(Mr[x] - Mn), c2 = exp2f(mn - Mn);
-                    Or[x] = Or[x] * c1 + ov * c2;
-                    Lr[x] = Lr[x] * c1 + lv * c2;
-                    Mr[x] = Mn;
-                }
-            }
-            consumer_sync();
-        }
-        float* rec = h.attn_ws + ((size_t)kvh * ncta + cta) * RT * kRec;
 #pragma unroll
         for (int x = 0; x < NX; ++x) {
             const int idx = tid + x * kCT;
             if (idx < RT * 128) {
                 const int r = idx >> 7, d = idx & 127;
-                __stcg(rec + r * kRec + d, Or[x]);
-                if (d == 0) { __stcg(rec + r * kRec + 128, Mr[x]); __stcg(rec + r * kRec + 129, Lr[x]); }
+                float mn = kNeg;
+                for (int w = 0; w < nw; ++w) mn = fmaxf(mn, part[(w * RT + r) * kPartStride + 128]);
+                float ov = 0.f, lv = 0.f;
+                for (int w = 0; w < nw; ++w) {
+                    const float c = exp2f(part[(w * RT + r) * kPartStride + 128] - mn);
+                    ov = fmaf(part[(w * RT + r) * kPartStride + d], c, ov);
+                    lv = fmaf(part[(w * RT + r) * kPartStride + 129], c, lv);
+                }
+                const float Mn = fmaxf(Mr[x], mn);
+                const float c1 = exp2f(Mr[x] - Mn), c2 = exp2f(mn - Mn);
+                Or[x] = Or[x] * c1 + ov * c2;
+                Lr[x] = Lr[x] * c1 + lv * c2;
+                Mr[x] = Mn;
             }
         }
-        u = seg_end;
+        consumer_sync();
     }
+    float* rec = h.attn_ws + (size_t)cta * RT * kRec;
+#pragma unroll
+    for (int x = 0; x < NX; ++x) {
+        const int idx = tid + x * kCT;
+        if (idx < RT * 128) {
+            const int r = idx >> 7, d = idx & 127;
+            __stcg(rec + r * kRec + d, Or[x]);
+            if (d == 0) { __stcg(rec + r * kRec + 128, Mr[x]); __stcg(rec + r * kRec + 129, Lr[x]); }
+        }
+    }
+    if (tr && tid == 0) tr[3] = globaltimer_ns();
 }
 
-// after the grid barrier: out[h, :] = fold over the CTAs that hold units of kv head h / G, in CTA order
+// after the grid barrier: out[head, :] = fold over the CTAs of the head's KV group, in CTA order
 template <int RT>
-__device__ __forceinline__ void attn_combine(const pgk_step_op_t& op, const StepHeader& h, int cta, int ncta, int ctx_in, int tid) {
+__device__ __forceinline__ void attn_combine(const pgk_step_op_t& op, const StepHeader& h, int cta, int ncta, int ctx, int tid) {
     const int lane = tid & 31, warp = tid >> 5;
     const int hq = op.hq, n_kv = op.n_kv, G = hq / n_kv;
-    const int ctx = attn_ctx(ctx_in, op.max_seq);
-    const int ntile = attn_ntile(ctx);
-    const long long Utot = (long long)n_kv * ntile;
+    const int ntile = (ctx + kAttnT - 1) / kAttnT;
     const int items = hq * 4;
-    const int i0 = part_lo(items, cta, ncta), i1 = part_lo(items, cta + 1, ncta);
+    const int i0 = (int)part_lo((unsigned)items, (unsigned)cta, (unsigned)ncta);
+    const int i1 = (int)part_lo((unsigned)items, (unsigned)cta + 1u, (unsigned)ncta);
     uint16_t* out = (uint16_t*)op.out;
     for (int i = i0 + warp; i < i1; i += kCW) {
         const int head = i >> 2, qd = i & 3;
-        const int kvh = head / G, g = head % G;
-        const int lo = kvh * ntile, hi = lo + ntile;
-        // CTA c owns units [floor(Utot c / ncta), floor(Utot (c+1) / ncta)): first / last CTA that meets [lo, hi)
-        int cf = (int)((((long long)lo + 1) * ncta + Utot - 1) / Utot) - 1;
-        int cl = (int)(((long long)hi * ncta + Utot - 1) / Utot) - 1;
-        cf = max(0, min(cf, ncta - 1));
-        cl = max(0, min(cl, ncta - 1));
-        const float* base = h.attn_ws + ((size_t)kvh * ncta) * RT * kRec + (size_t)g * kRec;
+        const int kvh = head / G, g = head - kvh * G;
+        const int cf = attn_cfirst(kvh, n_kv, ncta);
+        const int gs = attn_cfirst(kvh + 1, n_kv, ncta) - cf;
+        const int live = min(gs, ntile);      // with fewer tiles than CTAs only some CTAs of the group hold a record
+        const float* base = h.attn_ws + (size_t)cf * RT * kRec + (size_t)g * kRec;
+        // CTA lc of the group holds tiles [lc * ntile / gs, (lc + 1) * ntile / gs): non-empty for every lc when ntile >= gs
         float M = kNeg;
-        for (int cc = cf + lane; cc <= cl; cc += 32) {
-            const int a = max(part_lo(Utot, cc, ncta), lo), b = min(part_lo(Utot, cc + 1, ncta), hi);
-            if (a < b) M = fmaxf(M, __ldcg(base + (size_t)cc * RT * kRec + 128));
+        for (int lc = lane; lc < gs; lc += 32) {
+            const bool has = (live == gs) || (lc * ntile / gs < (lc + 1) * ntile / gs);
+            if (has) M = fmaxf(M, __ldcg(base + (size_t)lc * RT * kRec + 128));
         }
         M = warp_max(M);
         float O = 0.f, L = 0.f;
-        for (int cc = cf; cc <= cl; ++cc) {
-            const int a = max(part_lo(Utot, cc, ncta), lo), b = min(part_lo(Utot, cc + 1, ncta), hi);
-            if (a >= b) continue;
-            const float* rr = base + (size_t)cc * RT * kRec;
+#pragma unroll 4
+        for (int lc = 0; lc < gs; ++lc) {
+            const bool has = (live == gs) || (lc * ntile / gs < (lc + 1) * ntile / gs);
+            if (!has) continue;
+            const float* rr = base + (size_t)lc * RT * kRec;
             const float c = exp2f(__ldcg(rr + 128) - M);
             O = fmaf(__ldcg(rr + qd * 32 + lane), c, O);
             L = fmaf(__ldcg(rr + 129), c, L);
@@ -762,61 +796,81 @@ __device__ __forceinline__ void attn_combine(const pgk_step_op_t& op, const Step
     }
 }
 
-// ---------------------------------------------------------------- producer: one thread per CTA
-__device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsigned char* ring, int cta, int ncta, int token,
+// ---------------------------------------------------------------- producers: one thread per producer warp; producer p
+// fills the slots whose sequence number is p (mod kNP).  Both walk the whole op list (same plans as the consumers).
+__device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsigned char* ring, int p, int cta, int ncta,
                                          int ctx_in, Abort ab) {
     const uint64_t pol = make_evict_first_policy();
-    uint32_t q = 0;
-    uint64_t* fb = nullptr;          // the full barrier of the slot handed out last
-    auto acquire = [&](uint32_t bytes) -> unsigned char* {
-        const int slot = (int)(q % (uint32_t)h.ns);
-        const uint32_t rnd = q / (uint32_t)h.ns;
-        mbar_wait_b(&sh.empty_bar[slot], (rnd & 1) ^ 1, ab, 300);
-        fb = &sh.full_bar[rnd % kPhases][slot];
-        mbar_arrive_expect_tx(fb, bytes);
-        ++q;
-        return ring + (size_t)slot * kSlotB;
+    const uint32_t ring_u = smem_u32(ring);
+    const int ns = h.ns;
+    SlotPos sp = {0, 0u};
+    int turn = 0;                      // sequence number of the next slot, mod kNP
+    // claim the next slot if it is this producer's: returns its shared address (0 = not mine) and arms the barrier
+    auto next_slot = [&](uint32_t bytes, uint32_t& bar) -> uint32_t {
+        uint32_t dst = 0;
+        if (turn == p) {
+            mbar_wait_b(&sh.empty_bar[sp.s], (sp.r & 1) ^ 1, ab, 300);
+            bar = smem_u32(&sh.full_bar[sp.r & (kPhases - 1)][sp.s]);
+            mbar_expect_tx_u32(bar, bytes);
+            dst = ring_u + (uint32_t)sp.s * kSlotB;
+        }
+        turn = (turn + 1 == kNP) ? 0 : turn + 1;
+        sp.advance(1, ns);
+        return dst;
     };
     for (int oi = 0; oi < h.n_ops; ++oi) {
-        const pgk_step_op_t& op = h.ops[oi];
-        if (op.kind == OP_ATTN) {
-            const int ctx = attn_ctx(ctx_in, op.max_seq);
-            const int ntile = attn_ntile(ctx);
-            const long long Utot = (long long)op.n_kv * ntile;
-            const int u0 = part_lo(Utot, cta, ncta), u1 = part_lo(Utot, cta + 1, ncta);
-            const unsigned char* kc = (const unsigned char*)op.k_cache;
-            const unsigned char* vc = (const unsigned char*)op.v_cache;
-            for (int u = u0; u < u1; ++u) {
-                const int kvh = u / ntile, t0 = (u - kvh * ntile) * kAttnT;
+        const pgk_step_op_t* op = h.ops + oi;
+        const int kind = op->kind;
+        if (kind == OP_ATTN) {
+            const int max_seq = op->max_seq;
+            const int ctx = attn_ctx(ctx_in, max_seq);
+            const AttnPlan a = attn_plan(op->n_kv, ctx, cta, ncta);
+            const unsigned char* kc = (const unsigned char*)op->k_cache + (size_t)a.kvh * max_seq * 256;
+            const unsigned char* vc = (const unsigned char*)op->v_cache + (size_t)a.kvh * max_seq * 256;
+            for (int t = a.u0; t < a.u1; ++t) {
+                const int t0 = t * kAttnT;
                 const uint32_t bytes = (uint32_t)min(kAttnT, ctx - t0) * 256u;
-                unsigned char* dst = acquire(2 * bytes);
-                const size_t off = ((size_t)kvh * op.max_seq + t0) * 256;
-                bulk_copy_g2s(dst, kc + off, bytes, fb);
-                bulk_copy_g2s(dst + kAttnT * 256, vc + off, bytes, fb);
+                uint32_t bar = 0;
+                const uint32_t dst = next_slot(2 * bytes, bar);
+                if (dst) {
+                    bulk_copy_plain(dst, kc + (size_t)t0 * 256, bytes, bar);
+                    bulk_copy_plain(dst + kAttnT * 256, vc + (size_t)t0 * 256, bytes, bar);
+                }
             }
             continue;
         }
-        const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, cta, ncta);
-        const unsigned char* W[2] = {(const unsigned char*)op.W0, (const unsigned char*)op.W1};
-        for (int i = 0; i < pl.n_items; ++i) {
-            const int n0 = (pl.item0 + i) * pl.R;
-            const int rows = min(pl.R, op.N - n0);
-            if (pl.spi == 1) {
-                const uint32_t bytes = (uint32_t)rows * pl.RB;
-                unsigned char* dst = acquire(bytes * pl.nmat);
+        const int N = op->N;
+        const GemvPlan pl = gemv_plan(kind, op->flags, op->K, N, cta, ncta);
+        const unsigned char* W0 = (const unsigned char*)op->W0;
+        const unsigned char* W1 = (const unsigned char*)op->W1;
+        if (pl.spi == 1) {
+            const uint32_t item_bytes = (uint32_t)pl.R * pl.RB;
+            const unsigned char* s0 = W0 + (size_t)pl.item0 * item_bytes;
+            const unsigned char* s1 = W1 + (size_t)pl.item0 * item_bytes;
+            const int last = pl.items_total - 1 - pl.item0;          // local index of the matrix's last (possibly short) item
+            const uint32_t last_bytes = (uint32_t)(N - (pl.items_total - 1) * pl.R) * pl.RB;
+            for (int i = 0; i < pl.n_items; ++i) {
+                const uint32_t bytes = (i == last) ? last_bytes : item_bytes;
+                uint32_t bar = 0;
+                const uint32_t dst = next_slot(bytes * pl.nmat, bar);
+                if (dst) {
+                    bulk_copy_hint(dst, s0, bytes, bar, pol);
+                    if (pl.nmat == 2) bulk_copy_hint(dst + item_bytes, s1, bytes, bar, pol);
+                }
+                s0 += item_bytes; s1 += item_bytes;
+            }
+        } else {
+            for (int i = 0; i < pl.n_items; ++i) {
+                const size_t row = (size_t)(pl.item0 + i) * pl.RB;
                 for (int t = 0; t < pl.nmat; ++t)
-                    bulk_copy_g2s_hint(dst + (size_t)t * pl.R * pl.RB, W[t] + (size_t)n0 * pl.RB, bytes, fb, pol);
-            } else {
-                for (int t = 0; t < pl.nmat; ++t)
-                    for (int s = 0; s < pl.nseg; ++s) {
-                        unsigned char* dst = acquire((uint32_t)pl.seg_bytes);
-                        bulk_copy_g2s_hint(dst, W[t] + (size_t)n0 * pl.RB + (size_t)s * pl.seg_bytes, (uint32_t)pl.seg_bytes,
-                                           fb, pol);
+                    for (int sgi = 0; sgi < pl.nseg; ++sgi) {
+                        uint32_t bar = 0;
+                        const uint32_t dst = next_slot((uint32_t)pl.seg_bytes, bar);
+                        if (dst) bulk_copy_hint(dst, (t ? W1 : W0) + row + (size_t)sgi * pl.seg_bytes, (uint32_t)pl.seg_bytes, bar, pol);
                     }
             }
         }
     }
-    (void)token;
 }
 
 __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader h) {
@@ -831,6 +885,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
         const int slot = i % h.ns, ph = i / h.ns;
         mbar_init(ph == kPhases ? &sh.empty_bar[slot] : &sh.full_bar[ph][slot], 1);
     }
+    constexpr int kOpWords = (int)(sizeof(pgk_step_op_t) / 4);
+    if (tid < kOpWords) reinterpret_cast<uint32_t*>(&sh.op[0])[tid] = reinterpret_cast<const uint32_t*>(h.ops)[tid];
     if (tid == 0) { sh.key = 0ull; sh.abort_flag = 0; }
     mbar_fence_init();
     __syncthreads();
@@ -841,37 +897,43 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     if (token < 0 || token >= h.vocab) token = 0;
     const unsigned parity = h.bar[2] & 1u;
 
-    if (warp == kCW) {                                   // ---- producer warp
-        if (lane == 0) producer(h, sh, ring, cta, ncta, token, ctx_raw, ab);   // attention ops clamp the context themselves
+    if (warp >= kCW) {                                   // ---- producer warps
+        if (lane == 0) producer(h, sh, ring, warp - kCW, cta, ncta, ctx_raw, ab);   // attention ops clamp the context themselves
         return;
     }
     // ---- consumers
     unsigned* ctr = h.bar + parity;
     if (cta == 0 && tid == 0) h.bar[parity ^ 1u] = 0u;   // the other parity's counter: idle during this step
     unsigned target = 0;
-    uint32_t q_base = 0;
+    SlotPos base = {0, 0u};
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
     bool any_argmax = false;
-    const int ctx = ctx_raw;
     for (int oi = 0; oi < h.n_ops; ++oi) {
-        const pgk_step_op_t& op = h.ops[oi];
-        if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab); }
-        if (cta == 0 && tid == 0) h.trace[oi] = globaltimer_ns();
+        unsigned long long* tr = (cta == 0) ? h.trace + (size_t)oi * kTracePts : nullptr;
+        if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab, tr ? tr - kTracePts + 4 : nullptr); }
+        if (tr && tid == 0) tr[0] = globaltimer_ns();
+        const pgk_step_op_t& op = sh.op[oi & 1];
+        if (warp == 0 && lane < kOpWords && oi + 1 < h.n_ops)         // stage the next descriptor (read after the next grid barrier)
+            reinterpret_cast<uint32_t*>(&sh.op[(oi + 1) & 1])[lane] = reinterpret_cast<const uint32_t*>(h.ops + oi + 1)[lane];
+        if (warp == 0 && lane + 32 < kOpWords && oi + 1 < h.n_ops)
+            reinterpret_cast<uint32_t*>(&sh.op[(oi + 1) & 1])[lane + 32] = reinterpret_cast<const uint32_t*>(h.ops + oi + 1)[lane + 32];
         if (op.kind == OP_ATTN) {
+            const int ctx = attn_ctx(ctx_raw, op.max_seq);
+            const AttnPlan ap = attn_plan(op.n_kv, ctx, cta, ncta);
             const int G = op.hq / op.n_kv;
-            if (G <= 4) attn_op<4>(op, h, sh, ring, act, q_base, cta, ncta, pos, ctx, tid, ab);
-            else        attn_op<8>(op, h, sh, ring, act, q_base, cta, ncta, pos, ctx, tid, ab);
-            const long long Utot = (long long)op.n_kv * attn_ntile(attn_ctx(ctx, op.max_seq));
-            q_base += (uint32_t)(part_lo(Utot, cta + 1, ncta) - part_lo(Utot, cta, ncta));
+            if (G <= 4) attn_op<4>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr);
+            else        attn_op<8>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr);
+            base.advance(ap.u1 - ap.u0, h.ns);
             target += (unsigned)ncta;
-            grid_sync(ctr, target, tid, ab);
+            grid_sync(ctr, target, tid, ab, tr ? tr + 5 : nullptr);
+            if (tr && tid == 0) tr[6] = globaltimer_ns();
             if (G <= 4) attn_combine<4>(op, h, cta, ncta, ctx, tid);
             else        attn_combine<8>(op, h, cta, ncta, ctx, tid);
         } else {
-            gemv_op(op, h, sh, ring, act, q_base, cta, ncta, token, tid, ab, best_v, best_i);
             const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, cta, ncta);
-            q_base += (uint32_t)pl.n_items * pl.spi;
+            gemv_op(op, pl, h, sh, ring, act, base, token, tid, ab, best_v, best_i, tr);
+            base.advance(pl.n_items * pl.spi, h.ns);
             any_argmax |= (op.flags & F_ARGMAX) != 0;
         }
     }
@@ -881,9 +943,10 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
         if (tid == 0 && sh.key != 0ull) atomicMax(h.am_key, sh.key);
     }
     target += (unsigned)ncta;
-    grid_sync(ctr, target, tid, ab);
+    unsigned long long* trl = (cta == 0) ? h.trace + (size_t)h.n_ops * kTracePts : nullptr;
+    grid_sync(ctr, target, tid, ab, trl ? trl - kTracePts + 4 : nullptr);
     if (cta == 0 && tid == 0) {
-        h.trace[h.n_ops] = globaltimer_ns();
+        trl[0] = globaltimer_ns();
         if (any_argmax) {
             const unsigned long long k = atomicExch(h.am_key, 0ull);
             int tok = 0x7fffffff - (int)(uint32_t)(k & 0xffffffffull);
@@ -946,9 +1009,10 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
                         i, op.hq, op.n_kv);
             PGK_REQUIRE(op.act && op.out && op.cos_table && op.sin_table && op.k_cache && op.v_cache && op.max_seq >= 1,
                         "step_create failed: op %d: attention pointers must not be NULL", i);
+            PGK_REQUIRE(op.n_kv <= ctas, "step_create failed: op %d: more KV heads (%d) than CTAs (%d)", i, op.n_kv, ctas);
             const int RT = op.hq / op.n_kv <= 4 ? 4 : 8;
             act = std::max(act, (size_t)8 * RT * kPartStride * sizeof(float));
-            ws_floats = std::max(ws_floats, (size_t)op.n_kv * ctas * RT * kRec);
+            ws_floats = std::max(ws_floats, (size_t)ctas * RT * kRec);
             continue;
         }
         PGK_REQUIRE(op.kind == OP_FP8 || op.kind == OP_BF16 || op.kind == OP_NVF4R, "step_create failed: op %d: unknown kind %d", i, op.kind);
@@ -1007,8 +1071,8 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
     PGK_CUDA(cudaMalloc(&sp->d_ws, std::max(ws_floats, (size_t)1) * sizeof(float)));
     PGK_CUDA(cudaMalloc(&sp->d_key, sizeof(unsigned long long)));
     PGK_CUDA(cudaMemset(sp->d_key, 0, sizeof(unsigned long long)));
-    PGK_CUDA(cudaMalloc(&sp->d_trace, sizeof(unsigned long long) * (n_ops + 2)));
-    PGK_CUDA(cudaMemset(sp->d_trace, 0, sizeof(unsigned long long) * (n_ops + 2)));
+    PGK_CUDA(cudaMalloc(&sp->d_trace, sizeof(unsigned long long) * (n_ops + 1) * kTracePts));
+    PGK_CUDA(cudaMemset(sp->d_trace, 0, sizeof(unsigned long long) * (n_ops + 1) * kTracePts));
     PGK_CUDA(cudaMalloc(&sp->d_err, sizeof(int)));
     PGK_CUDA(cudaMemset(sp->d_err, 0, sizeof(int)));
     PGK_CUDA(cudaDeviceSynchronize());
@@ -1045,11 +1109,14 @@ int pgk_step_info(void* handle, int* ring_slots, int* act_bytes, int* smem_bytes
     return 0;
 }
 
-/* globaltimer (ns) at which CTA 0 started each op of the LAST run, then the end of the step: n_ops + 1 values */
+/* profiling aid: (n_ops + 1) x 8 globaltimer (ns) stamps of CTA 0 for the LAST run.  Per op: [0] start (grid barrier
+ * passed), [1] activations staged / attention prologue done, [2] warp 0 finished its items, [3] attention fold done,
+ * [4] CTA 0 arrived at the barrier that ends the op, [5] arrival at the attention's inner barrier, [6] attention combine
+ * start; row n_ops: [0] = end of the step. */
 int pgk_step_trace(void* handle, unsigned long long* host_out, int count) {
     PGK_REQUIRE(handle && host_out, "step_trace failed: NULL argument");
     StepProgram* sp = (StepProgram*)handle;
-    PGK_REQUIRE(count >= 1 && count <= sp->h.n_ops + 1, "step_trace failed: count %d out of range", count);
+    PGK_REQUIRE(count >= 1 && count <= (sp->h.n_ops + 1) * kTracePts, "step_trace failed: count %d out of range", count);
     PGK_CUDA(cudaDeviceSynchronize());
     PGK_CUDA(cudaMemcpy(host_out, sp->d_trace, sizeof(unsigned long long) * count, cudaMemcpyDeviceToHost));
     return 0;

@@ -123,11 +123,13 @@ class StepProgram:
         return int(code.value)
 
     def trace(self):
-        """Start time (ns, GPU globaltimer) of every op of the last run as seen by CTA 0, plus the step's end."""
+        """[n_ops + 1, 8] GPU globaltimer stamps (ns) of CTA 0 for the last run: per op [0] start, [1] staged,
+        [2] warp 0 done, [3] attention fold done, [4] arrived at the closing barrier, [5]/[6] attention inner barrier /
+        combine start; the last row's [0] is the end of the step."""
         import numpy as np
-        buf = np.zeros(self.n_ops + 1, np.uint64)
-        api.step_trace(self._h, buf.ctypes.data_as(C.c_void_p), self.n_ops + 1)
-        return buf
+        buf = np.zeros((self.n_ops + 1) * 8, np.uint64)
+        api.step_trace(self._h, buf.ctypes.data_as(C.c_void_p), buf.size)
+        return buf.reshape(self.n_ops + 1, 8)
 
     def info(self) -> dict:
         v = [C.c_int32(0) for _ in range(4)]

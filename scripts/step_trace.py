@@ -43,11 +43,16 @@ def main():
     acc = []
     for _ in range(a.steps):
         m.decode_graph_replay()
-        t = prog.trace().astype(np.int64)
-        acc.append(np.diff(t))
+        acc.append(prog.trace().astype(np.int64))
     assert prog.error() == 0
-    d = np.array(acc[2:], np.float64) / 1e3          # us, [steps, n_ops]
+    tr = np.array(acc[2:], np.float64) / 1e3             # us, [steps, n_ops + 1, 8]
+    d = np.diff(tr[:, :, 0], axis=1)                     # op start -> next op start
+    staged = tr[:, :-1, 1] - tr[:, :-1, 0]               # barrier passed -> activations staged / attention prologue done
+    w0 = tr[:, :-1, 2] - tr[:, :-1, 1]                   # -> warp 0 finished its items
+    cta0 = tr[:, :-1, 4] - tr[:, :-1, 0]                 # -> CTA 0 arrived at the closing barrier
+    wait = tr[:, 1:, 0] - tr[:, :-1, 4]                  # closing barrier: CTA 0's arrival -> released
     per_layer = d[:, :5 * L].reshape(-1, L, 5)
+    brk = [x[:, :5 * L].reshape(-1, L, 5).mean(axis=(0, 1)) for x in (staged, w0, cta0, wait)]
     blk = m.blocks[0]
     cfg = m.config
     H = cfg.hidden_size
@@ -60,12 +65,17 @@ def main():
         us = per_layer[:, :, i].mean()
         tot_us += us
         tot_b += b
-        print(f"{n:26s} {b / 1e6:8.2f} MB {us:7.2f} us {b / us / 1e3:7.0f} GB/s   (min {per_layer[:, :, i].min():.2f} max {per_layer[:, :, i].max():.2f})")
+        print(f"{n:26s} {b / 1e6:8.2f} MB {us:7.2f} us {b / us / 1e3:7.0f} GB/s   staged {brk[0][i]:5.2f}  warp0 items {brk[1][i]:5.2f}  "
+              f"CTA0 busy {brk[2][i]:5.2f}  barrier wait {brk[3][i]:5.2f}")
     print(f"{'layer':26s} {tot_b / 1e6:8.2f} MB {tot_us:7.2f} us {tot_b / tot_us / 1e3:7.0f} GB/s")
     hb = m._head.nbytes
     us = d[:, 5 * L].mean()
     print(f"{'lm_head (+norm, argmax)':26s} {hb / 1e6:8.2f} MB {us:7.2f} us {hb / us / 1e3:7.0f} GB/s")
     print(f"step {d.sum(axis=1).mean():.1f} us (CTA 0, first op start .. end)")
+    at = tr[:, 1:5 * L:5, :]                              # attention ops
+    print("attention: prologue %.2f  units(warp0) %.2f  fold %.2f  inner barrier %.2f  combine+closing %.2f" % (
+        (at[:, :, 1] - at[:, :, 0]).mean(), (at[:, :, 2] - at[:, :, 1]).mean(), (at[:, :, 3] - at[:, :, 2]).mean(),
+        (at[:, :, 6] - at[:, :, 3]).mean(), (tr[:, 2:5 * L + 1:5, 0] - at[:, :, 6]).mean()))
     _ = H
 
 
