@@ -355,6 +355,12 @@ typedef struct {
  * (position_buf of llm/decode/m1_graph.py:329-331).  Fails with a message when an op does not fit the kernel. */
 int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf, int32_t* pos_buf, int32_t* ctx_buf,
                     int32_t* next_token, int vocab, int advance, void** handle);
+/* flag 16 = XCHG (tensor parallel, needs pgk_p2p_open): the op is a row-parallel GEMV whose rows are partial sums; the
+ * kernel pushes them to every rank as 8-byte {payload, exchange number} words over NVLink peer memory (no fence, no
+ * separate flag: one hop of latency), sums every rank's partials in rank order and writes out = bf16(sum) (+ residual)
+ * -- the all-reduce of the row-parallel layers without a launch.  With a sharded lm_head (ARGMAX) the ranks exchange
+ * their (value, global index) pairs the same way; `vocab` is then the global size and this sets the shard's offset. */
+int pgk_step_set_vocab_offset(void* handle, int vocab_offset);
 int pgk_step_run(void* handle, void* stream);           /* ONE kernel launch; CUDA-graph capturable */
 int pgk_step_error(void* handle, int* host_code);       /* synchronises; 0 = every wait of the last runs completed */
 int pgk_step_info(void* handle, int* ring_slots, int* act_bytes, int* smem_bytes, int* ctas);

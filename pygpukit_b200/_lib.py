@@ -97,7 +97,7 @@ _SIGS = {
     "pgk_decode_advance": [vp, vp, i32, vp],
     "pgk_step_create": [vp, i32, vp, vp, vp, vp, i32, i32, C.POINTER(vp)], "pgk_step_run": [vp, vp],
     "pgk_step_error": [vp, C.POINTER(i32)], "pgk_step_info": [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)],
-    "pgk_step_destroy": [vp], "pgk_step_trace": [vp, vp, i32],
+    "pgk_step_destroy": [vp], "pgk_step_trace": [vp, vp, i32], "pgk_step_set_vocab_offset": [vp, i32],
     "pgk_nvf4_pack_rows": [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp],
     "pgk_nccl_unique_id": [vp], "pgk_nccl_init": [vp, i32, i32],
     "pgk_nccl_allreduce_bf16": [vp, sz, vp], "pgk_nccl_allgather": [vp, vp, sz, vp],

@@ -31,7 +31,12 @@ constexpr int kP2pMaxCtas = 64;
 constexpr size_t kP2pSlabBytes = 8u << 20;                  // per parity: one region per source rank
 constexpr size_t kP2pRegionBytes = kP2pSlabBytes / kP2pMaxWorld;   // 1 MB: up to 64 rows x 8192 bf16
 constexpr size_t kP2pFlagBytes = 2 * kP2pMaxCtas * kP2pMaxWorld * sizeof(unsigned);
-constexpr size_t kP2pBufBytes = 2 * kP2pSlabBytes + kP2pFlagBytes;
+// LL ("low latency") region used by the one-launch step kernel (step.cu): per parity and source rank 8192 words of
+// 8 bytes {payload, sequence number}; a word is valid when its sequence number matches, so no fence or flag is needed
+constexpr size_t kP2pLLWords = 8192;
+constexpr size_t kP2pLLBytes = 2 * kP2pMaxWorld * kP2pLLWords * 8;
+constexpr size_t kP2pLLOffset = 2 * kP2pSlabBytes + kP2pFlagBytes;
+constexpr size_t kP2pBufBytes = kP2pLLOffset + kP2pLLBytes;
 
 struct P2pState {
     int rank = 0, world = 1;
@@ -140,6 +145,17 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     }
 }
 
+// step.cu: the LL regions of every rank as mapped here, and the device word that numbers the exchanges (every rank runs
+// the same programs in the same order, so the numbering agrees without communication)
+bool p2p_ll_info(int* rank, int* world, unsigned char** ll_peers, unsigned** epoch, size_t* words_per_source) {
+    if (!g_p2p.ready) return false;
+    *rank = g_p2p.rank; *world = g_p2p.world;
+    for (int r = 0; r < kP2pMaxWorld; ++r) ll_peers[r] = r < g_p2p.world ? g_p2p.peer[r] + kP2pLLOffset : nullptr;
+    *epoch = g_p2p.seq + kP2pMaxCtas + 1;
+    *words_per_source = kP2pLLWords;
+    return true;
+}
+
 }  // namespace pgk
 
 using namespace pgk;
@@ -155,8 +171,8 @@ int pgk_p2p_create(int rank, int world, void* host_handle_out) {
     g_p2p.rank = rank; g_p2p.world = world;
     PGK_CUDA(cudaMalloc(&g_p2p.local, kP2pBufBytes));
     PGK_CUDA(cudaMemset(g_p2p.local, 0, kP2pBufBytes));
-    PGK_CUDA(cudaMalloc(&g_p2p.seq, (kP2pMaxCtas + 1) * sizeof(unsigned)));
-    PGK_CUDA(cudaMemset(g_p2p.seq, 0, (kP2pMaxCtas + 1) * sizeof(unsigned)));
+    PGK_CUDA(cudaMalloc(&g_p2p.seq, (kP2pMaxCtas + 2) * sizeof(unsigned)));
+    PGK_CUDA(cudaMemset(g_p2p.seq, 0, (kP2pMaxCtas + 2) * sizeof(unsigned)));
     g_p2p.err = g_p2p.seq + kP2pMaxCtas;
     cudaIpcMemHandle_t h;
     PGK_CUDA(cudaIpcGetMemHandle(&h, g_p2p.local));

@@ -34,6 +34,9 @@
 
 namespace pgk {
 
+// p2p.cu: LL regions of the peer-memory buffers (tensor parallelism)
+bool p2p_ll_info(int* rank, int* world, unsigned char** ll_peers, unsigned** epoch, size_t* words_per_source);
+
 constexpr int kCW = 14;                 // consumer warps
 constexpr int kNP = 2;                  // producer warps (one issuing thread each; slot q belongs to producer q % kNP)
 constexpr int kCT = kCW * 32;           // consumer threads
@@ -54,7 +57,9 @@ constexpr long long kSpinLimit = 3000000000LL;   // cycles (~1.5 s): far beyond 
 constexpr float kNeg = -1e30f;
 
 enum : int { OP_FP8 = 1, OP_BF16 = 2, OP_NVF4R = 3, OP_ATTN = 4 };
-enum : int { F_SWIGLU = 1, F_ACT_EMBED = 2, F_RES_EMBED = 4, F_ARGMAX = 8 };
+enum : int { F_SWIGLU = 1, F_ACT_EMBED = 2, F_RES_EMBED = 4, F_ARGMAX = 8, F_XCHG = 16 };
+constexpr int kXMax = 128;              // rows of a row-parallel op one CTA may own under tensor parallelism
+constexpr int kMaxWorld = 8;
 
 struct StepHeader {
     const pgk_step_op_t* ops;
@@ -65,6 +70,12 @@ struct StepHeader {
     unsigned long long* am_key;    // argmax scratch (zero between steps)
     int* error;
     unsigned long long* trace;     // [(n_ops + 1) * kTracePts] globaltimer (ns) stamps of CTA 0
+    // tensor parallelism (tp_world == 1: unused).  ll[r] = the LL region of rank r as mapped here; per parity and
+    // source rank `ll_words` words of 8 bytes {payload, exchange number}
+    int tp_rank, tp_world, vocab_offset, n_xchg;
+    unsigned char* ll[kMaxWorld];
+    unsigned* ll_epoch;            // device word: exchanges completed so far (identical on every rank)
+    unsigned ll_words;
 };
 
 // ---------------------------------------------------------------- work split, shared by host validation, the
@@ -312,9 +323,11 @@ __device__ __forceinline__ void dot8_e2m1(float& s0, float& s1, uint32_t w, cons
 
 struct RowOut {
     uint16_t* C; const uint16_t* residual; float inv, alpha; int flags;
+    uint16_t* xout; int xlo;     // tensor-parallel partial sums: row n goes to xout[n - xlo] (shared memory) instead of C
 };
 // lane 0: one finished output row (the epilogue of gemv_fp8_sb_kernel / gemv_bf16_kernel)
 __device__ __forceinline__ uint16_t finish_row(const RowOut& ro, int n, float v) {
+    if (ro.xout) { const uint16_t pb = f32_to_bf16_bits(v); ro.xout[n - ro.xlo] = pb; return pb; }
     const uint16_t ob = ro.residual ? hadd_bf16_bits(v, ld_act2(ro.residual + n)) : f32_to_bf16_bits(v);
     if (ro.C) ro.C[n] = ob;
     return ob;
@@ -435,7 +448,53 @@ struct Shared {
     float inv_s[4];
     unsigned long long key;
     int abort_flag;
+    uint16_t xout[kXMax];            // this CTA's partial sums of a row-parallel op (tensor parallel)
+    float xin[kMaxWorld][kXMax];     // every rank's partial sums of this CTA's rows
 };
+
+// ---------------------------------------------------------------- tensor-parallel exchange over NVLink peer memory
+// LL protocol: every 8-byte word carries {payload, exchange number}; an 8-byte store is delivered atomically, so a
+// word whose number matches is valid -- no fence, no separate flag, one NVLink hop of latency.
+__device__ __forceinline__ void st_ll(unsigned char* p, uint32_t data, uint32_t seq) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(data), "r"(seq) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_ll_wait(const unsigned char* p, uint32_t seq, Abort ab) {
+    uint32_t d, f;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(d), "=r"(f) : "l"(p) : "memory");
+    if (f == seq) return d;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(d), "=r"(f) : "l"(p) : "memory");
+        if (f == seq) return d;
+        if (*ab.s_abort) return 0u;
+        if (clock64() - t0 > kSpinLimit) { *ab.s_abort = 1; atomicCAS(ab.gerr, 0, 400); return 0u; }
+    }
+}
+// after a row-parallel GEMV whose partial sums of rows [lo, lo + len) sit in sh.xout: push them to every rank, collect
+// every rank's partial sums of the same rows, out[n] = bf16(sum over ranks in rank order) (+ residual, one rounding)
+__device__ __forceinline__ void xchg_rows(const StepHeader& h, Shared& sh, const pgk_step_op_t& op, int token, int lo, int len,
+                                          uint32_t seq, int tid, Abort ab) {
+    const int world = h.tp_world;
+    const size_t par_off = (size_t)(seq & 1u) * kMaxWorld * h.ll_words;
+    consumer_sync();                                   // every row of the CTA is in sh.xout
+    for (int idx = tid; idx < len * world; idx += kCT) {
+        const int peer = idx / len, j = idx - peer * len;
+        st_ll(h.ll[peer] + (par_off + (size_t)h.tp_rank * h.ll_words + lo + j) * 8, sh.xout[j], seq);
+    }
+    for (int idx = tid; idx < len * world; idx += kCT) {
+        const int src = idx / len, j = idx - src * len;
+        const uint32_t d = ld_ll_wait(h.ll[h.tp_rank] + (par_off + (size_t)src * h.ll_words + lo + j) * 8, seq, ab);
+        sh.xin[src][j] = bf16_bits_to_f32(d & 0xffffu);
+    }
+    consumer_sync();
+    const uint16_t* res = op.residual ? (const uint16_t*)op.residual + ((op.flags & F_RES_EMBED) ? (size_t)token * op.N : 0) : nullptr;
+    uint16_t* out = (uint16_t*)op.out;
+    for (int j = tid; j < len; j += kCT) {
+        float acc = 0.f;
+        for (int r = 0; r < world; ++r) acc += sh.xin[r][j];
+        out[lo + j] = res ? hadd_bf16_bits(acc, ld_act2(res + lo + j)) : f32_to_bf16_bits(acc);
+    }
+}
 
 // slot bookkeeping without divisions: (slot index in the ring, ring round)
 struct SlotPos {
@@ -461,6 +520,8 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan&
     ro.inv = (kind == OP_BF16) ? 1.f : sh.inv_s[0];
     ro.alpha = op.alpha;
     ro.flags = flags;
+    ro.xout = (flags & F_XCHG) ? sh.xout : nullptr;
+    ro.xlo = pl.item0 * pl.R;
     const uint4* a_lo = reinterpret_cast<const uint4*>(act);
     const int nchunk = (kind == OP_FP8) ? (K >> 5) : (kind == OP_NVF4R ? (K >> 6) : (K >> 4));
     ItemView iv;
@@ -896,6 +957,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     int token = *h.token_buf;
     if (token < 0 || token >= h.vocab) token = 0;
     const unsigned parity = h.bar[2] & 1u;
+    const uint32_t ll_base = h.tp_world > 1 ? *h.ll_epoch : 0u;      // exchanges completed before this step
 
     if (warp >= kCW) {                                   // ---- producer warps
         if (lane == 0) producer(h, sh, ring, warp - kCW, cta, ncta, ctx_raw, ab);   // attention ops clamp the context themselves
@@ -909,6 +971,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
     bool any_argmax = false;
+    uint32_t xi = 0;                                     // exchanges done in this step
     for (int oi = 0; oi < h.n_ops; ++oi) {
         unsigned long long* tr = (cta == 0) ? h.trace + (size_t)oi * kTracePts : nullptr;
         if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab, tr ? tr - kTracePts + 4 : nullptr); }
@@ -933,12 +996,16 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
         } else {
             const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, cta, ncta);
             gemv_op(op, pl, h, sh, ring, act, base, token, tid, ab, best_v, best_i, tr);
+            if (op.flags & F_XCHG) {
+                const int lo = pl.item0 * pl.R;
+                xchg_rows(h, sh, op, token, lo, min(op.N, (pl.item0 + pl.n_items) * pl.R) - lo, ll_base + (++xi), tid, ab);
+            }
             base.advance(pl.n_items * pl.spi, h.ns);
             any_argmax |= (op.flags & F_ARGMAX) != 0;
         }
     }
     if (any_argmax) {
-        if (lane == 0 && best_i != 0x7fffffff) atomicMax(&sh.key, argmax_key(best_v, best_i));
+        if (lane == 0 && best_i != 0x7fffffff) atomicMax(&sh.key, argmax_key(best_v, best_i + h.vocab_offset));
         consumer_sync();
         if (tid == 0 && sh.key != 0ull) atomicMax(h.am_key, sh.key);
     }
@@ -948,13 +1015,33 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     if (cta == 0 && tid == 0) {
         trl[0] = globaltimer_ns();
         if (any_argmax) {
-            const unsigned long long k = atomicExch(h.am_key, 0ull);
+            unsigned long long k = atomicExch(h.am_key, 0ull);
+            if (h.tp_world > 1) {
+                // every rank publishes its best (value, global index) key as two LL words and takes the maximum of all:
+                // identical on every rank, lowest index wins ties
+                const uint32_t seq = ll_base + (++xi);
+                const size_t par_off = (size_t)(seq & 1u) * kMaxWorld * h.ll_words;
+                for (int r = 0; r < h.tp_world; ++r) {
+                    unsigned char* dst = h.ll[r] + (par_off + (size_t)h.tp_rank * h.ll_words) * 8;
+                    st_ll(dst, (uint32_t)(k & 0xffffffffull), seq);
+                    st_ll(dst + 8, (uint32_t)(k >> 32), seq);
+                }
+                unsigned long long best = 0ull;
+                for (int r = 0; r < h.tp_world; ++r) {
+                    const unsigned char* src = h.ll[h.tp_rank] + (par_off + (size_t)r * h.ll_words) * 8;
+                    const unsigned long long lo32 = ld_ll_wait(src, seq, ab), hi32 = ld_ll_wait(src + 8, seq, ab);
+                    const unsigned long long kr = (hi32 << 32) | lo32;
+                    best = kr > best ? kr : best;
+                }
+                k = best;
+            }
             int tok = 0x7fffffff - (int)(uint32_t)(k & 0xffffffffull);
             if (tok < 0 || tok >= h.vocab || *ab.s_abort) tok = 0;
             *h.next_token = tok;
             *h.token_buf = tok;
         }
         if (h.advance) { *h.pos_buf = pos + 1; *h.ctx_buf = ctx_raw + 1; }
+        if (h.tp_world > 1) *h.ll_epoch = ll_base + (uint32_t)h.n_xchg;
         h.bar[2] = h.bar[2] + 1u;
     }
     griddep_launch();
@@ -1043,6 +1130,28 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
         }
         act = std::max(act, (size_t)op.K * 2);
     }
+    // ---- tensor parallelism: row-parallel ops exchange their partial sums inside the kernel (LL words over NVLink)
+    int n_xchg = 0, tp_rank = 0, tp_world = 1;
+    unsigned char* ll[kMaxWorld] = {};
+    unsigned* ll_epoch = nullptr;
+    size_t ll_words = 0;
+    bool any_argmax = false;
+    for (int i = 0; i < n_ops; ++i) {
+        const pgk_step_op_t& op = host_ops[i];
+        any_argmax |= op.kind != OP_ATTN && (op.flags & F_ARGMAX);
+        if (op.kind == OP_ATTN || !(op.flags & F_XCHG)) continue;
+        if (n_xchg == 0) {
+            PGK_REQUIRE(p2p_ll_info(&tp_rank, &tp_world, ll, &ll_epoch, &ll_words) && tp_world > 1,
+                        "step_create failed: op %d exchanges partial sums but the peer-memory buffers are not open (pgk_p2p_create / pgk_p2p_open)", i);
+        }
+        ++n_xchg;
+        PGK_REQUIRE(!(op.flags & (F_SWIGLU | F_ARGMAX)) && op.out, "step_create failed: op %d: an exchanged op is a plain row-parallel GEMV", i);
+        PGK_REQUIRE((size_t)op.N <= ll_words, "step_create failed: op %d: N=%d exceeds the exchange region (%zu rows)", i, op.N, ll_words);
+        const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, 0, ctas);
+        PGK_REQUIRE((pl.items_total / ctas + 1) * pl.R <= kXMax, "step_create failed: op %d: %d rows per CTA exceed the exchange buffer (%d)",
+                    i, (pl.items_total / ctas + 1) * pl.R, kXMax);
+    }
+    if (n_xchg > 0 && any_argmax) ++n_xchg;      // the (value, index) exchange of the sharded lm_head
     act = (act + 1023) & ~(size_t)1023;
     cudaDeviceProp prop;
     int dev = 0;
@@ -1080,7 +1189,18 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
     h.ops = sp->d_ops; h.n_ops = n_ops; h.ns = ns; h.act_bytes = (int)act; h.vocab = vocab; h.advance = advance;
     h.token_buf = token_buf; h.pos_buf = pos_buf; h.ctx_buf = ctx_buf; h.next_token = next_token;
     h.bar = sp->d_bar; h.attn_ws = sp->d_ws; h.am_key = sp->d_key; h.error = sp->d_err; h.trace = sp->d_trace;
+    h.tp_rank = tp_rank; h.tp_world = n_xchg > 0 ? tp_world : 1; h.vocab_offset = 0; h.n_xchg = n_xchg;
+    for (int r = 0; r < kMaxWorld; ++r) h.ll[r] = ll[r];
+    h.ll_epoch = ll_epoch; h.ll_words = (unsigned)ll_words;
     *handle = sp;
+    return 0;
+}
+
+/* tensor parallel: global index of this rank's first lm_head row (the argmax of a sharded lm_head is exchanged as
+ * (value, global index) pairs; `vocab` of pgk_step_create is then the GLOBAL vocabulary size) */
+int pgk_step_set_vocab_offset(void* handle, int vocab_offset) {
+    PGK_REQUIRE(handle && vocab_offset >= 0, "step_set_vocab_offset failed: bad argument");
+    ((StepProgram*)handle)->h.vocab_offset = vocab_offset;
     return 0;
 }
 

@@ -56,9 +56,12 @@ class CausalTransformerModel:
         self._graph: CudaGraph | None = None
         self._graph_stream: Stream | None = None
         self._gathered_logits: GPUArray | None = None
-        # one-launch step kernel (llm/step_program.py): built on first use when the model fits it; PGK_STEP=0 or
-        # `use_step_program = False` keeps the per-op launches
-        self.use_step_program = os.environ.get("PGK_STEP", "1") != "0"
+        # one-launch step kernel (llm/step_program.py), built on first use when the model fits it.  PGK_STEP=1 /
+        # `use_step_program = True` forces it on, 0 / False off; the default (auto) takes it for tensor-parallel shards,
+        # where it removes the per-layer launches AND the all-reduce launches (measured: the per-op path is faster on
+        # one GPU, where the CUDA-core dequantisation rate, not the launch boundaries, bounds the step)
+        env = os.environ.get("PGK_STEP", "auto")
+        self.use_step_program = None if env == "auto" else env != "0"
         self._step = None
         self._step_tried = False
         self.step_unsupported_reason: str | None = None
@@ -96,13 +99,15 @@ class CausalTransformerModel:
     def step_program(self):
         """The one-launch decode step of this model, or None when the model does not fit it (reason kept in
         `step_unsupported_reason`) or it is switched off."""
-        if not self.use_step_program:
+        use = self.use_step_program if self.use_step_program is not None else self.tp > 1
+        if not use:
             return None
         if not self._step_tried:
             from ..step_program import StepProgram, Unsupported
             self._step_tried = True
             try:
                 self._step = StepProgram.from_model(self)
+                self.fused_exchange = self.tp > 1        # the row-parallel all-reduces happen inside the step kernel
             except Unsupported as e:
                 self._step, self.step_unsupported_reason = None, str(e)
             except RuntimeError as e:    # the library refused an op shape (message says which)

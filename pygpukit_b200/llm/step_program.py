@@ -19,7 +19,7 @@ from .layers.linear import LinearBF16, LinearFP8, LinearNVF4
 from .layers.mlp import MLP
 
 OP_FP8, OP_BF16, OP_NVF4R, OP_ATTN = 1, 2, 3, 4
-F_SWIGLU, F_ACT_EMBED, F_RES_EMBED, F_ARGMAX = 1, 2, 4, 8
+F_SWIGLU, F_ACT_EMBED, F_RES_EMBED, F_ARGMAX, F_XCHG = 1, 2, 4, 8, 16
 
 
 class StepOp(C.Structure):
@@ -114,6 +114,9 @@ class StepProgram:
         self._keep = (list(keep), token_buf, pos_buf, ctx_buf, next_token)   # arrays the program points into
         self.n_ops = len(ops)
 
+    def set_vocab_offset(self, offset: int) -> None:
+        api.step_set_vocab_offset(self._h, int(offset))
+
     def run(self, stream=None) -> None:
         api.step_run(self._h, stream if stream is not None else _st())
 
@@ -150,8 +153,10 @@ class StepProgram:
         """The greedy decode step of `model` (init_decode must have run): embedding -> layers -> final norm ->
         lm_head -> argmax -> advance position.  Raises Unsupported when a layer does not fit."""
         cfg, b = model.config, model.buffers
-        if model.tp > 1:
-            raise Unsupported("tensor-parallel shards keep the per-op path")
+        tp = model.tp
+        if tp > 1 and not getattr(model.comm, "_p2p", False):
+            raise Unsupported("tensor-parallel shards need the NVLink peer-memory buffers (TensorParallel.init(allgather=...))")
+        xf = F_XCHG if tp > 1 else 0          # row-parallel o_proj / down_proj exchange their partial sums in the kernel
         if model.position_embed is not None or not cfg.use_rope:
             raise Unsupported("learned position embeddings (GPT-2 family)")
         H = cfg.hidden_size
@@ -195,15 +200,19 @@ class StepProgram:
                                eps=float(blk.attn_norm.eps), flags=F_ACT_EMBED if first else 0, **kw_qkv))
             ops.append(attn_op(at, qkv_buf, attn_buf))
             ops.append(gemv_op(at.o_proj, attn_buf, hidden, residual=embed if first else hidden,
-                               flags=F_RES_EMBED if first else 0, **kw_o))
+                               flags=(F_RES_EMBED if first else 0) | xf, **kw_o))
             ops.append(gemv_op(gate, hidden, act_buf, gamma=blk.mlp_norm.weight, eps=float(blk.mlp_norm.eps),
                                flags=F_SWIGLU, **kw_gu))
-            ops.append(gemv_op(mlp.down_proj, act_buf, hidden, residual=hidden, **kw_down))
+            ops.append(gemv_op(mlp.down_proj, act_buf, hidden, residual=hidden, flags=xf, **kw_down))
         head = LinearBF16(model._head)
         ops.append(gemv_op(head, hidden, b.logits, gamma=fn.weight, eps=float(fn.eps), flags=F_ARGMAX))
         keep += [hidden, qkv_buf, attn_buf, act_buf, b.logits]
-        return cls(ops, b.token_buf, b.position_buf, b.context_buf, b.next_token, model._head.shape[0], True, keep)
+        v_global = cfg.vocab_size if tp > 1 else model._head.shape[0]
+        prog = cls(ops, b.token_buf, b.position_buf, b.context_buf, b.next_token, v_global, True, keep)
+        if tp > 1:
+            prog.set_vocab_offset(model.comm.rank * (cfg.vocab_size // tp))   # consecutive vocabulary shards (random_init)
+        return prog
 
 
 __all__ = ["StepProgram", "StepOp", "Unsupported", "gemv_op", "attn_op", "pack_nvf4_rows",
-           "OP_FP8", "OP_BF16", "OP_NVF4R", "OP_ATTN", "F_SWIGLU", "F_ACT_EMBED", "F_RES_EMBED", "F_ARGMAX"]
+           "OP_FP8", "OP_BF16", "OP_NVF4R", "OP_ATTN", "F_SWIGLU", "F_ACT_EMBED", "F_RES_EMBED", "F_ARGMAX", "F_XCHG"]

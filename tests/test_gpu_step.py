@@ -204,6 +204,7 @@ MAX_SEQ = 160
 @pytest.mark.parametrize("name,fmt", [("small-qwen3", "fp8"), ("small-qwen3", "nvf4")])
 def test_step_model_tokens_match_oracle_and_graph_equals_eager(name, fmt):
     model = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, seed=7, std=0.05)
+    model.use_step_program = True
     model.init_decode(MAX_SEQ, max_batch_size=16)
     rng = np.random.default_rng(3)
     prompt = [int(t) for t in rng.integers(0, model.config.vocab_size, 12)]
@@ -221,6 +222,7 @@ def test_step_model_tokens_match_oracle_and_graph_equals_eager(name, fmt):
             assert i >= 32
             break
     model2 = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, seed=7, std=0.05)
+    model2.use_step_program = True
     model2.init_decode(MAX_SEQ, max_batch_size=16)
     assert model2.generate(prompt, 128, temperature=0.0, use_graph=False) == got
     # the per-op path decodes the same tokens up to a logit tie
@@ -234,8 +236,10 @@ def test_step_model_tokens_match_oracle_and_graph_equals_eager(name, fmt):
 
 def test_step_program_rejects_what_it_cannot_run():
     model = llm.build_random_model("tiny-llama", "fp8", max_seq=64, seed=1, std=0.05)      # head_dim 64
+    model.use_step_program = True
     model.init_decode(64)
     assert model.step_program() is None and "head_dim" in model.step_unsupported_reason
     model = llm.build_random_model("tiny-moe", "fp8", max_seq=64, seed=1, std=0.05)
+    model.use_step_program = True
     model.init_decode(64)
     assert model.step_program() is None

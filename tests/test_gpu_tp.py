@@ -16,6 +16,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 # name, format, steps, (heads, kv heads, column-parallel dims that must split in 128s)
 CASES = {
     "small-qwen3:fp8:128": (8, 2, 1024),
+    "small-qwen3:fp8:128::step": (8, 2, 1024),       # one-launch step kernel with the in-kernel NVLink exchange
+    "small-qwen3:nvf4:128::step": (8, 2, 1024),
+    "small-qwen3:fp8:128::perop": (8, 2, 1024),      # per-op launches + peer-memory all-reduce kernel
     "small-llama:nvf4:128": (8, 4, 1536),
     "small-qwen3:bf16:128": (8, 2, 1024),
     "tiny-moe:fp8:128": (4, 2, None),
@@ -32,6 +35,8 @@ def _shardable(case: str, world: int) -> bool:
         return False
     if inter is None and 8 % world:          # tiny-moe: 8 experts
         return False
+    if case.endswith("step") and ":nvf4:" in case and (inter // world) % 512:
+        return False                         # row-packed NVF4 rows of the step kernel: K % 512 == 0 per rank
     return True
 
 

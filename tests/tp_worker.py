@@ -35,12 +35,24 @@ def run(model, steps):
     return model.generate(PROMPT, steps, temperature=0.0)[len(PROMPT):]
 
 
+def step_state(model):
+    """'step' when the decode ran as the one-launch step kernel (in-kernel NVLink exchange), else why not."""
+    prog = model.step_program()
+    if prog is None:
+        return "per-op: " + str(model.step_unsupported_reason)
+    return "step" if prog.error() == 0 else f"step ERROR {prog.error()}"
+
+
 all_ok = True
 for case in sys.argv[1:]:
     f = case.split(":")
     name, fmt, steps = f[0], f[1], int(f[2])
-    layers = int(f[3]) if len(f) > 3 else None
-    tp_tokens = run(llm.build_random_model(name, fmt, max_seq=MAX_SEQ, comm=comm, std=0.05, num_layers=layers), steps)
+    layers = int(f[3]) if len(f) > 3 and f[3] else None
+    tp_model = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, comm=comm, std=0.05, num_layers=layers)
+    if len(f) > 4:                          # fifth field: "step" / "perop" pins the decode path
+        tp_model.use_step_program = f[4] == "step"
+    tp_tokens = run(tp_model, steps)
+    path = step_state(tp_model)
     api.device_sync()
     dist.barrier()
     ok, detail = True, {}
@@ -59,6 +71,9 @@ for case in sys.argv[1:]:
             detail.update(tp_token=tp_tokens[same], single_token=ref_tokens[same], margin_at_divergence=float(top2[1] - top2[0]))
             ok = detail["margin_at_divergence"] <= 2.0 ** -5
         detail["allreduce"] = "p2p-nvlink" if comm._p2p else "nccl"
+        detail["decode_path"] = path
+        if "ERROR" in path or (len(f) > 4 and f[4] == "step" and path != "step"):
+            ok = False
         detail["ok"] = ok
         print(json.dumps(detail), flush=True)
         del single
