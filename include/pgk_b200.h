@@ -395,6 +395,12 @@ int pgk_p2p_ready(void);
 /* largest message in bytes that pgk_p2p_allreduce_add_bf16 accepts (callers fall back to NCCL above it) */
 size_t pgk_p2p_max_bytes(void);
 int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream);
+/* LL ("low latency") forms for the decode step: every 8-byte word carries {payload, exchange number}, so there is no
+ * system fence and no separate flag -- one NVLink hop.  One decode row (n <= 8192); same result as the call above. */
+int pgk_p2p_ll_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream);
+/* greedy token of a vocabulary-sharded lm_head: token_buf[0] = local argmax index in, global token out (16 bytes per
+ * rank over NVLink instead of an all-gather of the logits) */
+int pgk_p2p_ll_argmax_bf16(const void* logits_local, int32_t* token_buf, int vocab_offset, void* stream);
 int pgk_p2p_error(int* host_flag);
 int pgk_p2p_destroy(void);
 

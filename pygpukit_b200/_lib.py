@@ -103,6 +103,7 @@ _SIGS = {
     "pgk_nccl_allreduce_bf16": [vp, sz, vp], "pgk_nccl_allgather": [vp, vp, sz, vp],
     "pgk_nccl_destroy": [],
     "pgk_p2p_create": [i32, i32, vp], "pgk_p2p_open": [vp], "pgk_p2p_allreduce_add_bf16": [vp, vp, vp, sz, vp],
+    "pgk_p2p_ll_allreduce_add_bf16": [vp, vp, vp, sz, vp], "pgk_p2p_ll_argmax_bf16": [vp, vp, i32, vp],
     "pgk_p2p_error": [vp], "pgk_p2p_destroy": [],
 }
 _RESTYPE = {"pgk_last_error": C.c_char_p, "pgk_launch_count": i64, "pgk_launch_count_reset": None,

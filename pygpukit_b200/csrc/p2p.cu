@@ -20,6 +20,7 @@
 // only reach call k+2 after every rank has published call k+1, i.e. after every rank finished reading call k.
 // Sequence numbers live in device memory, so the kernel is CUDA-graph replayable.
 #include "common.cuh"
+#include "gemv_common.cuh"
 #include "../../include/pgk_b200.h"
 
 #include <cstring>
@@ -145,6 +146,106 @@ __global__ void __launch_bounds__(1024) p2p_allreduce_add_kernel(P2pParams p) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// LL ("low latency") form for one decode row (n <= 8192): every 8-byte word carries {two bf16 partial sums, exchange
+// number}.  An aligned 8-byte store is delivered atomically, so a word whose number matches is valid: no system fence,
+// no separate flag, the critical path is ONE NVLink hop (the flag form above pays a fence round trip before its flag).
+// Exchange numbers come from one device word per rank (shared with the step kernel, step.cu) that every rank advances
+// identically (SPMD).  One CTA; thread t owns elements 8t .. 8t+7 = words 4t .. 4t+3 of its rank's region.
+struct P2pLLParams {
+    const uint16_t* partial; uint16_t* out; const uint16_t* residual;
+    unsigned char* ll[kP2pMaxWorld];
+    unsigned* epoch; unsigned* err;
+    int rank, world, n;
+};
+__device__ __forceinline__ void st_ll16(unsigned char* p, uint32_t d0, uint32_t d1, uint32_t seq) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(d0), "r"(seq), "r"(d1), "r"(seq) : "memory");
+}
+__device__ __forceinline__ uint4 ld_ll16(const unsigned char* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__global__ void __launch_bounds__(1024) p2p_ll_allreduce_add_kernel(P2pLLParams p) {
+    const int tid = threadIdx.x;
+    const int e = tid * 8;
+    const bool active = e < p.n;
+    griddep_wait();                                   // the partial sums come from the GEMV just before
+    griddep_launch();
+    const unsigned seq = *p.epoch + 1u;
+    const size_t par_off = (size_t)(seq & 1u) * kP2pMaxWorld * kP2pLLWords * 8;
+    if (active) {
+        const uint4 v = *reinterpret_cast<const uint4*>(p.partial + e);
+        uint4 rv = make_uint4(0u, 0u, 0u, 0u);
+        if (p.residual) rv = *reinterpret_cast<const uint4*>(p.residual + e);
+        const size_t mine = par_off + ((size_t)p.rank * kP2pLLWords + (size_t)tid * 4) * 8;
+#pragma unroll
+        for (int r = 0; r < kP2pMaxWorld; ++r) {
+            if (r < p.world) {
+                st_ll16(p.ll[r] + mine, v.x, v.y, seq);
+                st_ll16(p.ll[r] + mine + 16, v.z, v.w, seq);
+            }
+        }
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        const unsigned char* base = p.ll[p.rank] + par_off + (size_t)tid * 32;
+        const long long t0 = clock64();
+#pragma unroll 1
+        for (int r = 0; r < p.world; ++r) {
+            const unsigned char* src = base + (size_t)r * kP2pLLWords * 8;
+            uint4 a = ld_ll16(src), b = ld_ll16(src + 16);
+            while (a.y != seq || a.w != seq || b.y != seq || b.w != seq) {
+                if (clock64() - t0 > 4000000000LL) { *p.err = 1u; break; }       // ~2 s: a peer is gone; do not hang the GPU
+                a = ld_ll16(src); b = ld_ll16(src + 16);
+            }
+            acc[0] += bf16lo(a.x); acc[1] += bf16hi(a.x); acc[2] += bf16lo(a.z); acc[3] += bf16hi(a.z);
+            acc[4] += bf16lo(b.x); acc[5] += bf16hi(b.x); acc[6] += bf16lo(b.z); acc[7] += bf16hi(b.z);
+        }
+        uint16_t o[8];
+        if (p.residual) {
+            const uint16_t* rb = reinterpret_cast<const uint16_t*>(&rv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = hadd_bf16_bits(acc[j], rb[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = f32_to_bf16_bits(acc[j]);
+        }
+        *reinterpret_cast<uint4*>(p.out + e) = *reinterpret_cast<const uint4*>(o);
+    }
+    __syncthreads();
+    if (tid == 0) *p.epoch = seq;
+}
+
+// greedy token of a vocabulary-sharded lm_head: every rank publishes (its best logit, global index) as two LL words and
+// takes the maximum of all keys (identical on every rank; the lowest index wins ties) -- 16 bytes per rank instead of
+// an all-gather of the logits
+__global__ void p2p_ll_argmax_kernel(const uint16_t* __restrict__ logits, int32_t* token_buf, int vocab_offset, P2pLLParams p) {
+    griddep_wait();
+    griddep_launch();
+    if (threadIdx.x != 0) return;
+    const unsigned seq = *p.epoch + 1u;
+    const size_t par_off = (size_t)(seq & 1u) * kP2pMaxWorld * kP2pLLWords * 8;
+    const int idx = token_buf[0];
+    const unsigned long long k = argmax_key(bf16_bits_to_f32(logits[idx]), idx + vocab_offset);
+    for (int r = 0; r < p.world; ++r)
+        st_ll16(p.ll[r] + par_off + (size_t)p.rank * kP2pLLWords * 8, (uint32_t)(k & 0xffffffffull), (uint32_t)(k >> 32), seq);
+    unsigned long long best = 0ull;
+    const long long t0 = clock64();
+    for (int r = 0; r < p.world; ++r) {
+        const unsigned char* src = p.ll[p.rank] + par_off + (size_t)r * kP2pLLWords * 8;
+        uint4 a = ld_ll16(src);
+        while (a.y != seq || a.w != seq) {
+            if (clock64() - t0 > 4000000000LL) { *p.err = 1u; break; }
+            a = ld_ll16(src);
+        }
+        const unsigned long long kr = ((unsigned long long)a.z << 32) | a.x;
+        best = kr > best ? kr : best;
+    }
+    token_buf[0] = 0x7fffffff - (int)(uint32_t)(best & 0xffffffffull);
+    *p.epoch = seq;
+}
+
 // step.cu: the LL regions of every rank as mapped here, and the device word that numbers the exchanges (every rank runs
 // the same programs in the same order, so the numbering agrees without communication)
 bool p2p_ll_info(int* rank, int* world, unsigned char** ll_peers, unsigned** epoch, size_t* words_per_source) {
@@ -218,6 +319,33 @@ int pgk_p2p_allreduce_add_bf16(const void* partial, const void* residual, void* 
     p.per_cta = 8192;
     PGK_REQUIRE(ctas <= kP2pMaxCtas, "p2p_allreduce failed: %d CTAs (internal limit %d)", ctas, kP2pMaxCtas);
     PGK_CUDA(launch(p2p_allreduce_add_kernel, dim3(ctas), dim3(1024), 0, (cudaStream_t)stream, p));
+    return 0;
+}
+
+/* one decode row (n <= 8192, n % 8 == 0): the LL form of pgk_p2p_allreduce_add_bf16 -- same result, one NVLink hop */
+int pgk_p2p_ll_allreduce_add_bf16(const void* partial, const void* residual, void* out, size_t n, void* stream) {
+    PGK_REQUIRE(g_p2p.ready, "p2p_ll_allreduce failed: peer buffers not opened (pgk_p2p_create / pgk_p2p_open)");
+    PGK_REQUIRE(n % 8 == 0 && n >= 8 && n <= 8192, "p2p_ll_allreduce failed: n = %zu must be a multiple of 8 and <= 8192", n);
+    PGK_REQUIRE(((uintptr_t)partial % 16 == 0) && ((uintptr_t)out % 16 == 0) && ((uintptr_t)residual % 16 == 0),
+                "p2p_ll_allreduce failed: pointers must be 16-byte aligned");
+    P2pLLParams p = {};
+    p.partial = (const uint16_t*)partial; p.out = (uint16_t*)out; p.residual = (const uint16_t*)residual;
+    for (int r = 0; r < g_p2p.world; ++r) p.ll[r] = g_p2p.peer[r] + kP2pLLOffset;
+    p.epoch = g_p2p.seq + kP2pMaxCtas + 1; p.err = g_p2p.err; p.rank = g_p2p.rank; p.world = g_p2p.world; p.n = (int)n;
+    const int threads = (int)(((n / 8) + 31) / 32 * 32);
+    PGK_CUDA(launch(p2p_ll_allreduce_add_kernel, dim3(1), dim3(threads), 0, (cudaStream_t)stream, p));
+    return 0;
+}
+
+/* token_buf[0] holds this rank's LOCAL argmax index over logits_local (bf16 [V_local]); on return it holds the global
+ * greedy token (identical on every rank).  Replaces the all-gather of the logits + argmax over world * V_local. */
+int pgk_p2p_ll_argmax_bf16(const void* logits_local, int32_t* token_buf, int vocab_offset, void* stream) {
+    PGK_REQUIRE(g_p2p.ready, "p2p_ll_argmax failed: peer buffers not opened (pgk_p2p_create / pgk_p2p_open)");
+    P2pLLParams p = {};
+    for (int r = 0; r < g_p2p.world; ++r) p.ll[r] = g_p2p.peer[r] + kP2pLLOffset;
+    p.epoch = g_p2p.seq + kP2pMaxCtas + 1; p.err = g_p2p.err; p.rank = g_p2p.rank; p.world = g_p2p.world;
+    PGK_CUDA(launch(p2p_ll_argmax_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, (const uint16_t*)logits_local, token_buf,
+                    vocab_offset, p));
     return 0;
 }
 

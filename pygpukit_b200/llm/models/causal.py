@@ -198,9 +198,21 @@ class CausalTransformerModel:
             api.gemv_bf16_argmax(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
                                  H, V, _st())
             return
+        if self._ll_greedy():
+            api.gemv_bf16_argmax(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr, H, V, _st())
+            self.comm.greedy_token(b.logits, b.token_buf, self._vocab_offset())
+            return
         api.gemv_bf16(last.device_ptr, self._head.device_ptr, b.logits.device_ptr, 1, H, V, _st())
         self.comm.allgather_bytes(b.logits, self._gathered_logits, V * 2)
         api.argmax(self._gathered_logits.device_ptr, b.token_buf.device_ptr, self.tp * V, 2, _st())
+
+    def _vocab_offset(self) -> int:
+        return self.comm.rank * (self.config.vocab_size // self.tp) if self.tp > 1 else 0
+
+    def _ll_greedy(self) -> bool:
+        """Sharded lm_head: exchange (best logit, global index) pairs over NVLink (16 bytes per rank) instead of
+        gathering the logits -- needs the peer-memory buffers."""
+        return self.tp > 1 and getattr(self.comm, "_p2p", False) and getattr(self.comm, "_ll", False)
 
     def __call__(self, input_ids: list[int], position_ids: list[int] | None = None, past_key_values=None,
                  use_cache: bool = False):
@@ -227,9 +239,10 @@ class CausalTransformerModel:
         self._layers(hidden, 0, self._max_seq, b, b.position_buf, b.context_buf)
         V, H = self._head.shape[0], self.config.hidden_size
         fn = self.final_norm
+        ll = self._ll_greedy()
         if can_fuse_norm(fn, H):        # final RMSNorm rides inside the lm_head launch
             g, e = fn.weight.device_ptr, float(fn.eps)
-            if self.tp == 1:
+            if self.tp == 1 or ll:
                 api.rmsnorm_gemv_bf16_argmax(hidden.device_ptr, g, e, self._head.device_ptr, b.logits.device_ptr,
                                              b.token_buf.device_ptr, H, V, _st())
             else:
@@ -237,12 +250,14 @@ class CausalTransformerModel:
                                       None, None, _st())
         else:
             x = self._final(hidden, b)
-            if self.tp == 1:
+            if self.tp == 1 or ll:
                 api.gemv_bf16_argmax(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, b.token_buf.device_ptr,
                                      H, V, _st())
             else:
                 api.gemv_bf16(x.device_ptr, self._head.device_ptr, b.logits.device_ptr, 1, H, V, _st())
-        if self.tp > 1:
+        if ll:
+            self.comm.greedy_token(b.logits, b.token_buf, self._vocab_offset())
+        elif self.tp > 1:
             self.comm.allgather_bytes(b.logits, self._gathered_logits, V * 2)
             api.argmax(self._gathered_logits.device_ptr, b.token_buf.device_ptr, self.tp * V, 2, _st())
         api.memcpy_d2d(b.next_token.device_ptr, b.token_buf.device_ptr, 4, _st())

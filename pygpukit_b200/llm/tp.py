@@ -75,6 +75,17 @@ class TensorParallel:
         self._ready = False
         self._p2p = False
         self._p2p_max_bytes = 0
+        self._ll = os.environ.get("PGK_P2P_LL", "1") != "0"      # LL form of the decode-row all-reduce (A/B switch)
+
+    def greedy_token(self, logits_local, token_buf, vocab_offset: int) -> bool:
+        """token_buf[0]: local argmax index -> global greedy token over all ranks' shards (16 bytes per rank over
+        NVLink).  False when the peer buffers are not set up (the caller gathers the logits instead)."""
+        if not (self._p2p and self._ll):
+            return False
+        from .._lib import api
+        from ..core.stream import current_stream_handle
+        api.p2p_ll_argmax_bf16(logits_local.device_ptr, token_buf.device_ptr, int(vocab_offset), current_stream_handle())
+        return True
 
     @classmethod
     def from_env(cls) -> "TensorParallel":
@@ -138,6 +149,11 @@ class TensorParallel:
             return
         from .._lib import api
         from ..core.stream import current_stream_handle
+        if self._p2p and part.size % 8 == 0 and part.size <= 8192 and self._ll:
+            # one decode row: LL words (payload + exchange number in one 8-byte store), one NVLink hop, no fence
+            api.p2p_ll_allreduce_add_bf16(part.device_ptr, hidden.device_ptr, hidden.device_ptr, part.size,
+                                          current_stream_handle())
+            return
         if self._p2p and part.size % 8 == 0 and part.nbytes <= self._p2p_max_bytes:
             api.p2p_allreduce_add_bf16(part.device_ptr, hidden.device_ptr, hidden.device_ptr, part.size,
                                        current_stream_handle())
