@@ -60,6 +60,7 @@ enum : int { OP_FP8 = 1, OP_BF16 = 2, OP_NVF4R = 3, OP_ATTN = 4 };
 enum : int { F_SWIGLU = 1, F_ACT_EMBED = 2, F_RES_EMBED = 4, F_ARGMAX = 8, F_XCHG = 16 };
 constexpr int kXMax = 128;              // rows of a row-parallel op one CTA may own under tensor parallelism
 constexpr int kMaxWorld = 8;
+constexpr int kScalePad = 256;           // k blocks per staged scale row (K <= 32768)
 
 struct StepHeader {
     const pgk_step_op_t* ops;
@@ -104,6 +105,7 @@ __host__ __device__ inline GemvPlan gemv_plan(int kind, int flags, int K, int N,
 }
 // attention: the CTAs are dealt to the KV heads in contiguous groups (CTA c serves head c * n_kv / ncta), the head's
 // tiles of kAttnT positions are dealt evenly over the CTAs of its group
+constexpr int kAttnMaxGroup = 48;       // CTAs that share one KV head (= partial records the fold reads per head)
 struct AttnPlan {
     int kvh, cfirst, gs, ntile, u0, u1;
 };
@@ -114,10 +116,11 @@ __host__ __device__ inline AttnPlan attn_plan(int n_kv, int ctx, int cta, int nc
     a.kvh = cta * n_kv / ncta;
     a.cfirst = attn_cfirst(a.kvh, n_kv, ncta);
     a.gs = attn_cfirst(a.kvh + 1, n_kv, ncta) - a.cfirst;
+    if (a.gs > kAttnMaxGroup) a.gs = kAttnMaxGroup;      // the other CTAs of the group sit this op out
     a.ntile = (ctx + kAttnT - 1) / kAttnT;
     const int lc = cta - a.cfirst;
-    a.u0 = lc * a.ntile / a.gs;
-    a.u1 = (lc + 1) * a.ntile / a.gs;
+    a.u0 = lc < a.gs ? lc * a.ntile / a.gs : 0;
+    a.u1 = lc < a.gs ? (lc + 1) * a.ntile / a.gs : 0;
     return a;
 }
 
@@ -237,11 +240,15 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
     const uint4* gv = reinterpret_cast<const uint4*>(gamma);
     uint4* dst = reinterpret_cast<uint4*>(act);
     float* red_f = reinterpret_cast<float*>(red) + 64;
-    uint4 v[VY];
+    constexpr bool EARLY_G = VY <= 4;      // gamma in flight together with the activations (one L2 round trip, not two)
+    uint4 v[VY], g[EARLY_G ? VY : 1];
 #pragma unroll
     for (int e = 0; e < VY; ++e) {
         const int j = tid + e * kCT;
-        if (j < nvec) v[e] = ld_act16(src + j);
+        if (j < nvec) {
+            v[e] = ld_act16(src + j);
+            if (EARLY_G && gamma) g[e] = __ldg(gv + j);
+        }
     }
     if (gamma) {
 #pragma unroll
@@ -263,7 +270,7 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
         const float rinv = rsqrtf(ss / (float)K + eps);
 #pragma unroll
         for (int e = 0; e < VY; ++e)
-            if (tid + e * kCT < nvec) v[e] = norm8_bf16(v[e], __ldg(gv + tid + e * kCT), rinv);
+            if (tid + e * kCT < nvec) v[e] = norm8_bf16(v[e], EARLY_G ? g[e] : __ldg(gv + tid + e * kCT), rinv);
     }
     float mult = 1.f;
     if (TO_F16) {
@@ -326,9 +333,11 @@ struct RowOut {
     uint16_t* xout; int xlo;     // tensor-parallel partial sums: row n goes to xout[n - xlo] (shared memory) instead of C
 };
 // lane 0: one finished output row (the epilogue of gemv_fp8_sb_kernel / gemv_bf16_kernel)
-__device__ __forceinline__ uint16_t finish_row(const RowOut& ro, int n, float v) {
+// `res` = the residual of row n, requested by the caller BEFORE the dot product (an L2 round trip that would otherwise
+// sit at the end of every row)
+__device__ __forceinline__ uint16_t finish_row(const RowOut& ro, int n, float v, uint16_t res) {
     if (ro.xout) { const uint16_t pb = f32_to_bf16_bits(v); ro.xout[n - ro.xlo] = pb; return pb; }
-    const uint16_t ob = ro.residual ? hadd_bf16_bits(v, ld_act2(ro.residual + n)) : f32_to_bf16_bits(v);
+    const uint16_t ob = ro.residual ? hadd_bf16_bits(v, res) : f32_to_bf16_bits(v);
     if (ro.C) ro.C[n] = ob;
     return ob;
 }
@@ -341,10 +350,11 @@ __device__ __forceinline__ void finish_swiglu(const RowOut& ro, int n, float vg,
 // FP8: RR rows of NMAT matrices share one read of the activation chunk.  Per row: acc = fma(dot32(chunk), scale, acc)
 // over the lane's chunks in increasing order, then the butterfly sum (= gemv_fp8_sb_kernel).
 template <int NMAT, int RR>
-__device__ __forceinline__ void fp8_rows(const pgk_step_op_t& op, const ItemView& iv, const uint4* a_lo, int nchunk,
+__device__ __forceinline__ void fp8_rows(const float* sc_s, int sk_pad, int rb0, const ItemView& iv, const uint4* a_lo, int nchunk,
                                          int n, int r0, int lane, const RowOut& ro) {
-    const int SK = (op.K + 127) >> 7;
-    const uint16_t* S[2] = {(const uint16_t*)op.S0, (const uint16_t*)op.S1};
+    uint16_t res[RR];
+#pragma unroll
+    for (int rr = 0; rr < RR; ++rr) res[rr] = (lane == 0 && ro.residual && !ro.xout) ? ld_act2(ro.residual + n + rr) : (uint16_t)0;
     float acc[NMAT][RR];
 #pragma unroll
     for (int t = 0; t < NMAT; ++t)
@@ -360,7 +370,8 @@ __device__ __forceinline__ void fp8_rows(const pgk_step_op_t& op, const ItemView
 #pragma unroll
             for (int t = 0; t < NMAT; ++t) {
                 const u32x8 w = lds_chunk32(iv.ptr(t, r0 + rr, c * 32), lane);
-                const float sc = bf16_bits_to_f32(__ldg(S[t] + (size_t)((n + rr) >> 7) * SK + (c >> 2)));
+                // block scales of the CTA's (at most two) 128-row blocks, staged in shared memory: [matrix][row block][k block]
+                const float sc = sc_s[(t * 2 + (((n + rr) >> 7) - rb0)) * sk_pad + (c >> 2)];
                 acc[t][rr] = fmaf(dot32_e4m3_regs(w, a), sc, acc[t][rr]);
             }
         }
@@ -373,7 +384,7 @@ __device__ __forceinline__ void fp8_rows(const pgk_step_op_t& op, const ItemView
 #pragma unroll
         for (int rr = 0; rr < RR; ++rr) {
             if (NMAT == 2) finish_swiglu(ro, n + rr, acc[0][rr] * ro.inv, acc[NMAT - 1][rr] * ro.inv);
-            else finish_row(ro, n + rr, acc[0][rr] * ro.inv);
+            else finish_row(ro, n + rr, acc[0][rr] * ro.inv, res[rr]);
         }
     }
 }
@@ -384,6 +395,9 @@ template <int NMAT, int RR>
 __device__ __forceinline__ void nvf4_rows(const pgk_step_op_t& op, const ItemView& iv, const uint4* a_lo, int nchunk,
                                           int n, int r0, int lane, const RowOut& ro) {
     const int soff = op.K >> 1;       // scale bytes follow the data bytes of the row
+    uint16_t res[RR];
+#pragma unroll
+    for (int rr = 0; rr < RR; ++rr) res[rr] = (lane == 0 && ro.residual && !ro.xout) ? ld_act2(ro.residual + n + rr) : (uint16_t)0;
     float acc[NMAT][RR];
 #pragma unroll
     for (int t = 0; t < NMAT; ++t)
@@ -419,7 +433,7 @@ __device__ __forceinline__ void nvf4_rows(const pgk_step_op_t& op, const ItemVie
 #pragma unroll
         for (int rr = 0; rr < RR; ++rr) {
             if (NMAT == 2) finish_swiglu(ro, n + rr, ro.alpha * (acc[0][rr] * ro.inv), ro.alpha * (acc[NMAT - 1][rr] * ro.inv));
-            else finish_row(ro, n + rr, ro.alpha * (acc[0][rr] * ro.inv));
+            else finish_row(ro, n + rr, ro.alpha * (acc[0][rr] * ro.inv), res[rr]);
         }
     }
 }
@@ -448,6 +462,7 @@ struct Shared {
     float inv_s[4];
     unsigned long long key;
     int abort_flag;
+    float scales[4 * kScalePad];     // FP8 block scales of this CTA's rows: [matrix 0/1][row block 0/1][k block]
     uint16_t xout[kXMax];            // this CTA's partial sums of a row-parallel op (tensor parallel)
     float xin[kMaxWorld][kXMax];     // every rank's partial sums of this CTA's rows
 };
@@ -503,17 +518,38 @@ struct SlotPos {
 };
 
 // ---------------------------------------------------------------- one GEMV-type op, consumer side
+// warp 0 copies the next op's descriptor into the other shared buffer (read after the next grid barrier); called after
+// the staging so that its L2 round trip is off the critical path of the op boundary
+__device__ __forceinline__ void prefetch_next_op(const StepHeader& h, Shared& sh, int oi, int tid) {
+    constexpr int kOpWords = (int)(sizeof(pgk_step_op_t) / 4);
+    if (tid < kOpWords && oi + 1 < h.n_ops)
+        reinterpret_cast<uint32_t*>(&sh.op[(oi + 1) & 1])[tid] = reinterpret_cast<const uint32_t*>(h.ops + oi + 1)[tid];
+}
+
 __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan& pl, const StepHeader& h, Shared& sh,
                                         unsigned char* ring, unsigned char* act, SlotPos base, int token, int tid, Abort ab,
-                                        float& best_v, int& best_i, unsigned long long* tr) {
+                                        float& best_v, int& best_i, unsigned long long* tr, int oi) {
     const int lane = tid & 31, warp = tid >> 5;
     const int K = op.K, N = op.N, kind = op.kind, flags = op.flags;
     const uint16_t* A = (const uint16_t*)op.act + ((flags & F_ACT_EMBED) ? (size_t)token * K : 0);
     const uint16_t* gam = (const uint16_t*)op.gamma;
+    // FP8 block scales of the rows this CTA owns (they lie in at most two 128-row blocks): requested now, in flight together
+    // with the activation vector, read from shared memory in the row loop
+    const int rb0 = (pl.item0 * pl.R) >> 7;
+    if (kind == OP_FP8) {
+        const int SK = (K + 127) >> 7, nrb = (N + 127) >> 7;
+        const int nm = (flags & F_SWIGLU) ? 2 : 1;
+        for (int i = tid; i < nm * 2 * SK; i += kCT) {
+            const int t = i / (2 * SK), rem = i - t * 2 * SK, b = rem / SK, kb = rem - b * SK;
+            const uint16_t* S = (const uint16_t*)(t ? op.S1 : op.S0);
+            sh.scales[(t * 2 + b) * kScalePad + kb] = (rb0 + b < nrb) ? bf16_bits_to_f32(__ldg(S + (size_t)(rb0 + b) * SK + kb)) : 0.f;
+        }
+    }
     if (kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
     else if (kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
     else                       stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
     if (tr && tid == 0) tr[1] = globaltimer_ns();
+    prefetch_next_op(h, sh, oi, tid);
     RowOut ro;
     ro.C = (uint16_t*)op.out;
     ro.residual = op.residual ? (const uint16_t*)op.residual + ((flags & F_RES_EMBED) ? (size_t)token * N : 0) : nullptr;
@@ -541,11 +577,11 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan&
         const int rows = min(pl.R, N - n0);
         if (kind == OP_FP8) {
             if (flags & F_SWIGLU) {
-                for (int r = 0; r < rows; ++r) fp8_rows<2, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+                for (int r = 0; r < rows; ++r) fp8_rows<2, 1>(sh.scales, kScalePad, rb0, iv, a_lo, nchunk, n0 + r, r, lane, ro);
             } else {
                 int r = 0;
-                for (; r + 2 <= rows; r += 2) fp8_rows<1, 2>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
-                if (r < rows) fp8_rows<1, 1>(op, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+                for (; r + 2 <= rows; r += 2) fp8_rows<1, 2>(sh.scales, kScalePad, rb0, iv, a_lo, nchunk, n0 + r, r, lane, ro);
+                if (r < rows) fp8_rows<1, 1>(sh.scales, kScalePad, rb0, iv, a_lo, nchunk, n0 + r, r, lane, ro);
             }
         } else if (kind == OP_NVF4R) {
             if (flags & F_SWIGLU) {
@@ -557,9 +593,10 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan&
             }
         } else {
             for (int r = 0; r < rows; ++r) {
+                const uint16_t res = (lane == 0 && ro.residual && !ro.xout) ? ld_act2(ro.residual + n0 + r) : (uint16_t)0;
                 const float v = bf16_row(iv, a_lo, nchunk, r, lane);
                 if (lane == 0) {
-                    const uint16_t ob = finish_row(ro, n0 + r, v);
+                    const uint16_t ob = finish_row(ro, n0 + r, v, res);
                     if (flags & F_ARGMAX) {
                         const float rv = bf16_bits_to_f32(ob);
                         if (rv > best_v) { best_v = rv; best_i = n0 + r; }   // rows ascend within a warp: first max kept
@@ -698,7 +735,7 @@ __device__ __forceinline__ void step_norm_rope128(const uint16_t* row, const uin
 template <int RT>
 __device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const AttnPlan& ap, const StepHeader& h, Shared& sh,
                                         unsigned char* ring, unsigned char* act, SlotPos base, int cta, int pos, int ctx, int tid,
-                                        Abort ab, unsigned long long* tr) {
+                                        Abort ab, unsigned long long* tr, int oi) {
     const int lane = tid & 31, warp = tid >> 5;
     const int hq = op.hq, n_kv = op.n_kv, G = hq / n_kv, max_seq = op.max_seq;
     const uint16_t* qkv = (const uint16_t*)op.act;
@@ -712,7 +749,7 @@ __device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const AttnPlan&
     const float scale_log2 = scale * 1.4426950408889634f;
     float* part = reinterpret_cast<float*>(act);     // [8][RT][kPartStride]
     const int kvh = ap.kvh, u0 = ap.u0, u1 = ap.u1;
-    if (u0 >= u1) return;                             // CTA-uniform: more CTAs than tiles in this head's group
+    if (u0 >= u1) { prefetch_next_op(h, sh, oi, tid); return; }   // CTA-uniform: more CTAs than tiles in this head's group
     // ---- the group's query rows and the new K / V row
     const int tw = has_new ? pos / kAttnT : 0;
     const bool writer = pos < max_seq && tw >= u0 && tw < u1;
@@ -731,6 +768,7 @@ __device__ __forceinline__ void attn_op(const pgk_step_op_t& op, const AttnPlan&
     }
     consumer_sync();
     if (tr && tid == 0) tr[1] = globaltimer_ns();
+    prefetch_next_op(h, sh, oi, tid);
     uint32_t q[RT][2];
 #pragma unroll
     for (int r = 0; r < RT; ++r) {
@@ -833,25 +871,30 @@ __device__ __forceinline__ void attn_combine(const pgk_step_op_t& op, const Step
         const int head = i >> 2, qd = i & 3;
         const int kvh = head / G, g = head - kvh * G;
         const int cf = attn_cfirst(kvh, n_kv, ncta);
-        const int gs = attn_cfirst(kvh + 1, n_kv, ncta) - cf;
-        const int live = min(gs, ntile);      // with fewer tiles than CTAs only some CTAs of the group hold a record
+        const int gs = min(attn_cfirst(kvh + 1, n_kv, ncta) - cf, kAttnMaxGroup);
+        const bool all_live = ntile >= gs;    // with fewer tiles than CTAs only some CTAs of the group hold a record
         const float* base = h.attn_ws + (size_t)cf * RT * kRec + (size_t)g * kRec;
-        // CTA lc of the group holds tiles [lc * ntile / gs, (lc + 1) * ntile / gs): non-empty for every lc when ntile >= gs
-        float M = kNeg;
-        for (int lc = lane; lc < gs; lc += 32) {
-            const bool has = (live == gs) || (lc * ntile / gs < (lc + 1) * ntile / gs);
-            if (has) M = fmaxf(M, __ldcg(base + (size_t)lc * RT * kRec + 128));
-        }
-        M = warp_max(M);
-        float O = 0.f, L = 0.f;
-#pragma unroll 4
-        for (int lc = 0; lc < gs; ++lc) {
-            const bool has = (live == gs) || (lc * ntile / gs < (lc + 1) * ntile / gs);
-            if (!has) continue;
-            const float* rr = base + (size_t)lc * RT * kRec;
-            const float c = exp2f(__ldcg(rr + 128) - M);
-            O = fmaf(__ldcg(rr + qd * 32 + lane), c, O);
-            L = fmaf(__ldcg(rr + 129), c, L);
+        // one pass, records in CTA order, 16 records' loads in flight at a time; online rescale of (O, L)
+        float M = kNeg, O = 0.f, L = 0.f;
+        for (int l0 = 0; l0 < gs; l0 += 16) {
+            float mv[16], lv[16], ov[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+                const int lc = l0 + u;
+                const bool has = lc < gs && (all_live || (lc * ntile / gs < (lc + 1) * ntile / gs));
+                const float* rr = base + (size_t)lc * RT * kRec;
+                mv[u] = has ? __ldcg(rr + 128) : kNeg;
+                lv[u] = has ? __ldcg(rr + 129) : 0.f;
+                ov[u] = has ? __ldcg(rr + qd * 32 + lane) : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+                const float Mn = fmaxf(M, mv[u]);
+                const float c1 = exp2f(M - Mn), c2 = exp2f(mv[u] - Mn);
+                O = O * c1 + ov[u] * c2;
+                L = L * c1 + lv[u] * c2;
+                M = Mn;
+            }
         }
         out[(size_t)head * 128 + qd * 32 + lane] = f32_to_bf16_bits(L > 0.f ? O / L : 0.f);
     }
@@ -977,16 +1020,12 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
         if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab, tr ? tr - kTracePts + 4 : nullptr); }
         if (tr && tid == 0) tr[0] = globaltimer_ns();
         const pgk_step_op_t& op = sh.op[oi & 1];
-        if (warp == 0 && lane < kOpWords && oi + 1 < h.n_ops)         // stage the next descriptor (read after the next grid barrier)
-            reinterpret_cast<uint32_t*>(&sh.op[(oi + 1) & 1])[lane] = reinterpret_cast<const uint32_t*>(h.ops + oi + 1)[lane];
-        if (warp == 0 && lane + 32 < kOpWords && oi + 1 < h.n_ops)
-            reinterpret_cast<uint32_t*>(&sh.op[(oi + 1) & 1])[lane + 32] = reinterpret_cast<const uint32_t*>(h.ops + oi + 1)[lane + 32];
         if (op.kind == OP_ATTN) {
             const int ctx = attn_ctx(ctx_raw, op.max_seq);
             const AttnPlan ap = attn_plan(op.n_kv, ctx, cta, ncta);
             const int G = op.hq / op.n_kv;
-            if (G <= 4) attn_op<4>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr);
-            else        attn_op<8>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr);
+            if (G <= 4) attn_op<4>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr, oi);
+            else        attn_op<8>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr, oi);
             base.advance(ap.u1 - ap.u0, h.ns);
             target += (unsigned)ncta;
             grid_sync(ctr, target, tid, ab, tr ? tr + 5 : nullptr);
@@ -995,7 +1034,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
             else        attn_combine<8>(op, h, cta, ncta, ctx, tid);
         } else {
             const GemvPlan pl = gemv_plan(op.kind, op.flags, op.K, op.N, cta, ncta);
-            gemv_op(op, pl, h, sh, ring, act, base, token, tid, ab, best_v, best_i, tr);
+            gemv_op(op, pl, h, sh, ring, act, base, token, tid, ab, best_v, best_i, tr, oi);
             if (op.flags & F_XCHG) {
                 const int lo = pl.item0 * pl.R;
                 xchg_rows(h, sh, op, token, lo, min(op.N, (pl.item0 + pl.n_items) * pl.R) - lo, ll_base + (++xi), tid, ab);
@@ -1121,6 +1160,9 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
         PGK_REQUIRE(((uintptr_t)op.act & 15) == 0 && (!op.gamma || ((uintptr_t)op.gamma & 15) == 0),
                     "step_create failed: op %d: act / gamma must be 16-byte aligned", i);
         if (op.kind == OP_FP8) {
+            const GemvPlan plf = gemv_plan(op.kind, op.flags, op.K, op.N, 0, ctas);
+            PGK_REQUIRE((plf.items_total / ctas + 1) * plf.R <= 128 && (op.K + 127) / 128 <= kScalePad,
+                        "step_create failed: op %d: more than 128 FP8 rows per CTA or K > 32768 (block scales are staged per CTA)", i);
             // codes 0x7F / 0xFF are +-480 in the reference's tables but NaN for the hardware conversion this kernel uses
             // (common.cuh): such tensors stay on the per-op path, which serves them with the exact table kernel
             bool clean = true;

@@ -27,7 +27,16 @@ def main():
     ap.add_argument("--layers", type=int, default=None)
     a = ap.parse_args()
     api.set_pdl(1)
-    m = llm.build_random_model(a.model, a.format, max_seq=a.context, num_layers=a.layers)
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    comm = None
+    if world > 1:                     # torchrun: tensor-parallel shards, the exchanges happen inside the step kernel
+        import torch.distributed as dist
+        from pygpukit_b200.llm.tp import torch_allgather, torch_exchange
+        api.device_set(int(os.environ.get("LOCAL_RANK", "0")))
+        dist.init_process_group("gloo")
+        comm = llm.TensorParallel(rank, world).init(exchange=torch_exchange(), allgather=torch_allgather())
+    m = llm.build_random_model(a.model, a.format, max_seq=a.context, num_layers=a.layers, comm=comm)
+    m.use_step_program = True
     m.init_decode(a.context)
     for blk in m.blocks:
         for c in (blk.attn._k_cache, blk.attn._v_cache):
@@ -36,7 +45,9 @@ def main():
     prog = m.step_program()
     if prog is None:
         raise SystemExit(f"no step program: {m.step_unsupported_reason}")
-    print("info", prog.info())
+    if rank != 0:
+        sys.stdout = open(os.devnull, "w")
+    print("info", prog.info(), "world", world)
     L = len(m.blocks)
     p0 = a.context - a.steps - 4
     m.set_decode_state(123, p0)
