@@ -30,6 +30,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace pgk {
@@ -65,6 +66,7 @@ constexpr int kScalePad = 256;           // k blocks per staged scale row (K <= 
 struct StepHeader {
     const pgk_step_op_t* ops;
     int n_ops, ns, act_bytes, vocab, advance;
+    int inflight;                  // fills a producer may have outstanding (issued, not landed): bounds the memory queue
     int32_t* token_buf; int32_t* pos_buf; int32_t* ctx_buf; int32_t* next_token;
     unsigned* bar;                 // [0],[1] grid-barrier counters by step parity, [2] step counter
     float* attn_ws;                // [ctas][RT][kRec]
@@ -231,9 +233,17 @@ struct ItemView {
 // once, the RMSNorm statistics follow the reference's summation tree (row_inv_rms_ref_order), elements are
 // normalised as bf16(x * inv * gamma), then either kept as bf16 (TO_F16 = false) or range-shifted to f16.
 // Vector j (8 elements) lands in plane j % PL at chunk j / PL.   red: 80 words of shared scratch.
+// FP8 block scales of the rows a CTA owns (at most two 128-row blocks, one or two matrices): loaded together with the
+// activation vector (one L2 round trip for both) and parked in shared memory for the row loop
+struct ScaleJob {
+    const uint16_t* S0; const uint16_t* S1;
+    int count, SK, rb0, nrb;       // count = matrices * 2 * SK values (0 = no job)
+    float* dst;                    // [matrix][row block 0/1][kScalePad]
+};
 template <int PL, bool TO_F16, int VY>
 __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
-                                            float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid) {
+                                            float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid,
+                                            const ScaleJob& sj) {
     const int nvec = K >> 3, lane = tid & 31, warp = tid >> 5;
     const int nchunk = nvec / PL;
     const uint4* src = reinterpret_cast<const uint4*>(A);
@@ -248,6 +258,17 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
         if (j < nvec) {
             v[e] = ld_act16(src + j);
             if (EARLY_G && gamma) g[e] = __ldg(gv + j);
+        }
+    }
+    float scv[2] = {0.f, 0.f};
+    int sci[2] = {-1, -1};
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int i = tid + u * kCT;
+        if (i < sj.count) {
+            const int t = i / (2 * sj.SK), rem = i - t * 2 * sj.SK, b = rem / sj.SK, kb = rem - b * sj.SK;
+            sci[u] = (t * 2 + b) * kScalePad + kb;
+            if (sj.rb0 + b < sj.nrb) scv[u] = bf16_bits_to_f32(__ldg((t ? sj.S1 : sj.S0) + (size_t)(sj.rb0 + b) * sj.SK + kb));
         }
     }
     if (gamma) {
@@ -302,14 +323,18 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
         const int j = tid + e * kCT;
         if (j < nvec) dst[(j % PL) * nchunk + (j / PL)] = TO_F16 ? bf16x8_to_f16x8_scaled(v[e], mult) : v[e];
     }
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+        if (sci[u] >= 0) sj.dst[sci[u]] = scv[u];
     consumer_sync();
 }
 // four vectors per thread for K <= 14336 (no spills), eight for the long rows (K up to 28672)
 template <int PL, bool TO_F16>
 __device__ __forceinline__ void stage_act(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
-                                          float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid) {
-    if ((K >> 3) <= 4 * kCT) stage_act_v<PL, TO_F16, 4>(A, K, gamma, eps, act, red, inv_s, tid);
-    else                     stage_act_v<PL, TO_F16, 8>(A, K, gamma, eps, act, red, inv_s, tid);
+                                          float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid,
+                                          const ScaleJob& sj) {
+    if ((K >> 3) <= 4 * kCT) stage_act_v<PL, TO_F16, 4>(A, K, gamma, eps, act, red, inv_s, tid, sj);
+    else                     stage_act_v<PL, TO_F16, 8>(A, K, gamma, eps, act, red, inv_s, tid, sj);
 }
 
 // ---------------------------------------------------------------- row dot products
@@ -533,21 +558,17 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan&
     const int K = op.K, N = op.N, kind = op.kind, flags = op.flags;
     const uint16_t* A = (const uint16_t*)op.act + ((flags & F_ACT_EMBED) ? (size_t)token * K : 0);
     const uint16_t* gam = (const uint16_t*)op.gamma;
-    // FP8 block scales of the rows this CTA owns (they lie in at most two 128-row blocks): requested now, in flight together
-    // with the activation vector, read from shared memory in the row loop
     const int rb0 = (pl.item0 * pl.R) >> 7;
+    ScaleJob sj = {};
     if (kind == OP_FP8) {
-        const int SK = (K + 127) >> 7, nrb = (N + 127) >> 7;
-        const int nm = (flags & F_SWIGLU) ? 2 : 1;
-        for (int i = tid; i < nm * 2 * SK; i += kCT) {
-            const int t = i / (2 * SK), rem = i - t * 2 * SK, b = rem / SK, kb = rem - b * SK;
-            const uint16_t* S = (const uint16_t*)(t ? op.S1 : op.S0);
-            sh.scales[(t * 2 + b) * kScalePad + kb] = (rb0 + b < nrb) ? bf16_bits_to_f32(__ldg(S + (size_t)(rb0 + b) * SK + kb)) : 0.f;
-        }
+        sj.S0 = (const uint16_t*)op.S0; sj.S1 = (const uint16_t*)op.S1;
+        sj.SK = (K + 127) >> 7; sj.nrb = (N + 127) >> 7; sj.rb0 = rb0;
+        sj.count = ((flags & F_SWIGLU) ? 2 : 1) * 2 * sj.SK;
+        sj.dst = sh.scales;
     }
-    if (kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
-    else if (kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
-    else                       stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid);
+    if (kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj);
+    else if (kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj);
+    else                       stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj);
     if (tr && tid == 0) tr[1] = globaltimer_ns();
     prefetch_next_op(h, sh, oi, tid);
     RowOut ro;
@@ -909,14 +930,24 @@ __device__ __forceinline__ void producer(const StepHeader& h, Shared& sh, unsign
     const int ns = h.ns;
     SlotPos sp = {0, 0u};
     int turn = 0;                      // sequence number of the next slot, mod kNP
+    // Outstanding fills are capped: every byte in flight queues in front of the loads on the op boundaries' critical
+    // path (grid-barrier polls, activation vectors) -- bandwidth needs ~35 KB in flight per SM, not the whole ring.
+    uint32_t win_bar[3] = {0u, 0u, 0u}, win_par[3] = {0u, 0u, 0u};     // full barrier + parity of the last fills, newest first
+    const int depth = h.inflight < 1 ? 1 : (h.inflight > 3 ? 3 : h.inflight);
     // claim the next slot if it is this producer's: returns its shared address (0 = not mine) and arms the barrier
     auto next_slot = [&](uint32_t bytes, uint32_t& bar) -> uint32_t {
         uint32_t dst = 0;
         if (turn == p) {
+            const uint32_t ob = depth == 1 ? win_bar[0] : (depth == 2 ? win_bar[1] : win_bar[2]);
+            const uint32_t op_ = depth == 1 ? win_par[0] : (depth == 2 ? win_par[1] : win_par[2]);
+            if (ob) mbar_wait_b(reinterpret_cast<uint64_t*>(__cvta_shared_to_generic(ob)), op_, ab, 301);
             mbar_wait_b(&sh.empty_bar[sp.s], (sp.r & 1) ^ 1, ab, 300);
             bar = smem_u32(&sh.full_bar[sp.r & (kPhases - 1)][sp.s]);
             mbar_expect_tx_u32(bar, bytes);
             dst = ring_u + (uint32_t)sp.s * kSlotB;
+            win_bar[2] = win_bar[1]; win_par[2] = win_par[1];
+            win_bar[1] = win_bar[0]; win_par[1] = win_par[0];
+            win_bar[0] = bar; win_par[0] = (sp.r / kPhases) & 1;
         }
         turn = (turn + 1 == kNP) ? 0 : turn + 1;
         sp.advance(1, ns);
@@ -1161,7 +1192,8 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
                     "step_create failed: op %d: act / gamma must be 16-byte aligned", i);
         if (op.kind == OP_FP8) {
             const GemvPlan plf = gemv_plan(op.kind, op.flags, op.K, op.N, 0, ctas);
-            PGK_REQUIRE((plf.items_total / ctas + 1) * plf.R <= 128 && (op.K + 127) / 128 <= kScalePad,
+            PGK_REQUIRE((plf.items_total / ctas + 1) * plf.R <= 128 && (op.K + 127) / 128 <= kScalePad &&
+                        ((op.flags & F_SWIGLU) ? 2 : 1) * 2 * ((op.K + 127) / 128) <= 2 * kCT,
                         "step_create failed: op %d: more than 128 FP8 rows per CTA or K > 32768 (block scales are staged per CTA)", i);
             // codes 0x7F / 0xFF are +-480 in the reference's tables but NaN for the hardware conversion this kernel uses
             // (common.cuh): such tensors stay on the per-op path, which serves them with the exact table kernel
@@ -1228,6 +1260,10 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
     PGK_CUDA(cudaMemset(sp->d_err, 0, sizeof(int)));
     PGK_CUDA(cudaDeviceSynchronize());
     StepHeader& h = sp->h;
+    {
+        const char* e = getenv("PGK_STEP_INFLIGHT");
+        h.inflight = e ? atoi(e) : 2;
+    }
     h.ops = sp->d_ops; h.n_ops = n_ops; h.ns = ns; h.act_bytes = (int)act; h.vocab = vocab; h.advance = advance;
     h.token_buf = token_buf; h.pos_buf = pos_buf; h.ctx_buf = ctx_buf; h.next_token = next_token;
     h.bar = sp->d_bar; h.attn_ws = sp->d_ws; h.am_key = sp->d_key; h.error = sp->d_err; h.trace = sp->d_trace;
