@@ -66,6 +66,7 @@ constexpr int kScalePad = 256;           // k blocks per staged scale row (K <= 
 struct StepHeader {
     const pgk_step_op_t* ops;
     int n_ops, ns, act_bytes, vocab, advance;
+    int bar_mode;                  // grid-barrier variant (A/B switch, PGK_STEP_BAR)
     int inflight;                  // fills a producer may have outstanding (issued, not landed): bounds the memory queue
     int32_t* token_buf; int32_t* pos_buf; int32_t* ctx_buf; int32_t* next_token;
     unsigned* bar;                 // [0],[1] grid-barrier counters by step parity, [2] step counter
@@ -167,18 +168,36 @@ __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;"
 // all consumer threads of every CTA: arrive + wait on the step's monotone counter.  The CTA barrier orders every
 // consumer thread's global writes before thread 0's release (cumulativity); the acquire + second CTA barrier order the
 // other CTAs' writes before every thread's later loads (which bypass L1: ld.global.cg / ld.global.nc of constants only).
-__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned target, int tid, Abort ab, unsigned long long* tr) {
+__device__ __forceinline__ unsigned ld_relaxed_gpu(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// mode 0: red.release + ld.acquire polls.  mode 1: fence, relaxed atomic, relaxed polls, fence.  mode 2: as 1 with a
+// 64 ns back-off between polls.  mode 3: as 1, the atomic returns (its round trip is the first poll).
+__device__ __forceinline__ void grid_sync(unsigned* ctr, unsigned target, int tid, Abort ab, unsigned long long* tr, int mode) {
     consumer_sync();
     if (tid == 0) {
         if (tr) tr[0] = globaltimer_ns();
-        red_release_gpu_inc(ctr);
-        if ((int)(ld_acquire_gpu(ctr) - target) < 0) {
+        unsigned seen = 0;
+        if (mode == 0) {
+            red_release_gpu_inc(ctr);
+            seen = ld_acquire_gpu(ctr);
+        } else {
+            __threadfence();
+            seen = atomicAdd(ctr, 1u) + 1u;
+        }
+        if ((int)(seen - target) < 0) {
             const long long t0 = clock64();
-            while ((int)(ld_acquire_gpu(ctr) - target) < 0) {
+            while (true) {
+                seen = mode == 0 ? ld_acquire_gpu(ctr) : ld_relaxed_gpu(ctr);
+                if ((int)(seen - target) >= 0) break;
                 if (*ab.s_abort) break;
                 if (clock64() - t0 > kSpinLimit) { *ab.s_abort = 1; atomicCAS(ab.gerr, 0, 100); break; }
+                if (mode == 2) __nanosleep(64);
             }
         }
+        if (mode != 0) __threadfence();
     }
     consumer_sync();
 }
@@ -243,7 +262,7 @@ struct ScaleJob {
 template <int PL, bool TO_F16, int VY>
 __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
                                             float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid,
-                                            const ScaleJob& sj) {
+                                            const ScaleJob& sj, unsigned long long* tr) {
     const int nvec = K >> 3, lane = tid & 31, warp = tid >> 5;
     const int nchunk = nvec / PL;
     const uint4* src = reinterpret_cast<const uint4*>(A);
@@ -278,6 +297,7 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
             if (j < nvec) dst[j] = v[e];
         }
         consumer_sync();
+        if (tr && tid == 0) tr[5] = globaltimer_ns();
         const uint16_t* raw = reinterpret_cast<const uint16_t*>(dst);
         const int bs = min(256, (K + 31) & ~31), nvw = bs >> 5;
         for (int w = warp; w < nvw; w += kCW) {
@@ -287,6 +307,7 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
             if (lane == 0) red_f[w] = part;
         }
         consumer_sync();
+        if (tr && tid == 0) tr[6] = globaltimer_ns();
         const float ss = warp_sum(lane < nvw ? red_f[lane] : 0.f);
         const float rinv = rsqrtf(ss / (float)K + eps);
 #pragma unroll
@@ -308,6 +329,7 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
         for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
         if (lane == 0) red[warp] = mx;
         consumer_sync();                 // also: every thread is done reading the raw row
+        if (tr && tid == 0) tr[7] = globaltimer_ns();
         uint32_t bm = 0;
         for (int w = 0; w < kCW; ++w) bm = max(bm, red[w]);
         int ex = (int)(bm >> 7);
@@ -332,9 +354,9 @@ __device__ __forceinline__ void stage_act_v(const uint16_t* __restrict__ A, int 
 template <int PL, bool TO_F16>
 __device__ __forceinline__ void stage_act(const uint16_t* __restrict__ A, int K, const uint16_t* __restrict__ gamma,
                                           float eps, unsigned char* act, uint32_t* red, float* inv_s, int tid,
-                                          const ScaleJob& sj) {
-    if ((K >> 3) <= 4 * kCT) stage_act_v<PL, TO_F16, 4>(A, K, gamma, eps, act, red, inv_s, tid, sj);
-    else                     stage_act_v<PL, TO_F16, 8>(A, K, gamma, eps, act, red, inv_s, tid, sj);
+                                          const ScaleJob& sj, unsigned long long* tr) {
+    if ((K >> 3) <= 4 * kCT) stage_act_v<PL, TO_F16, 4>(A, K, gamma, eps, act, red, inv_s, tid, sj, tr);
+    else                     stage_act_v<PL, TO_F16, 8>(A, K, gamma, eps, act, red, inv_s, tid, sj, tr);
 }
 
 // ---------------------------------------------------------------- row dot products
@@ -566,9 +588,9 @@ __device__ __forceinline__ void gemv_op(const pgk_step_op_t& op, const GemvPlan&
         sj.count = ((flags & F_SWIGLU) ? 2 : 1) * 2 * sj.SK;
         sj.dst = sh.scales;
     }
-    if (kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj);
-    else if (kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj);
-    else                       stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj);
+    if (kind == OP_FP8)        stage_act<4, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj, tr);
+    else if (kind == OP_NVF4R) stage_act<8, true>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj, tr);
+    else                       stage_act<2, false>(A, K, gam, op.eps, act, sh.red, sh.inv_s, tid, sj, tr);
     if (tr && tid == 0) tr[1] = globaltimer_ns();
     prefetch_next_op(h, sh, oi, tid);
     RowOut ro;
@@ -1048,7 +1070,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     uint32_t xi = 0;                                     // exchanges done in this step
     for (int oi = 0; oi < h.n_ops; ++oi) {
         unsigned long long* tr = (cta == 0) ? h.trace + (size_t)oi * kTracePts : nullptr;
-        if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab, tr ? tr - kTracePts + 4 : nullptr); }
+        if (oi > 0) { target += (unsigned)ncta; grid_sync(ctr, target, tid, ab, tr ? tr - kTracePts + 4 : nullptr, h.bar_mode); }
         if (tr && tid == 0) tr[0] = globaltimer_ns();
         const pgk_step_op_t& op = sh.op[oi & 1];
         if (op.kind == OP_ATTN) {
@@ -1059,7 +1081,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
             else        attn_op<8>(op, ap, h, sh, ring, act, base, cta, pos, ctx, tid, ab, tr, oi);
             base.advance(ap.u1 - ap.u0, h.ns);
             target += (unsigned)ncta;
-            grid_sync(ctr, target, tid, ab, tr ? tr + 5 : nullptr);
+            grid_sync(ctr, target, tid, ab, tr ? tr + 5 : nullptr, h.bar_mode);
             if (tr && tid == 0) tr[6] = globaltimer_ns();
             if (G <= 4) attn_combine<4>(op, h, cta, ncta, ctx, tid);
             else        attn_combine<8>(op, h, cta, ncta, ctx, tid);
@@ -1081,7 +1103,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) step_kernel(const StepHeader 
     }
     target += (unsigned)ncta;
     unsigned long long* trl = (cta == 0) ? h.trace + (size_t)h.n_ops * kTracePts : nullptr;
-    grid_sync(ctr, target, tid, ab, trl ? trl - kTracePts + 4 : nullptr);
+    grid_sync(ctr, target, tid, ab, trl ? trl - kTracePts + 4 : nullptr, h.bar_mode);
     if (cta == 0 && tid == 0) {
         trl[0] = globaltimer_ns();
         if (any_argmax) {
@@ -1263,6 +1285,8 @@ int pgk_step_create(const pgk_step_op_t* host_ops, int n_ops, int32_t* token_buf
     {
         const char* e = getenv("PGK_STEP_INFLIGHT");
         h.inflight = e ? atoi(e) : 2;
+        const char* b = getenv("PGK_STEP_BAR");
+        h.bar_mode = b ? atoi(b) : 0;
     }
     h.ops = sp->d_ops; h.n_ops = n_ops; h.ns = ns; h.act_bytes = (int)act; h.vocab = vocab; h.advance = advance;
     h.token_buf = token_buf; h.pos_buf = pos_buf; h.ctx_buf = ctx_buf; h.next_token = next_token;

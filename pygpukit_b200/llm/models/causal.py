@@ -56,12 +56,13 @@ class CausalTransformerModel:
         self._graph: CudaGraph | None = None
         self._graph_stream: Stream | None = None
         self._gathered_logits: GPUArray | None = None
-        # one-launch step kernel (llm/step_program.py), built on first use when the model fits it.  PGK_STEP=1 /
-        # `use_step_program = True` forces it on, 0 / False off; the default (auto) takes it for tensor-parallel shards,
-        # where it removes the per-layer launches AND the all-reduce launches (measured: the per-op path is faster on
-        # one GPU, where the CUDA-core dequantisation rate, not the launch boundaries, bounds the step)
-        env = os.environ.get("PGK_STEP", "auto")
-        self.use_step_program = None if env == "auto" else env != "0"
+        # one-launch step kernel (llm/step_program.py), built on first use when the model fits it.  Opt-in: PGK_STEP=1 or
+        # `use_step_program = True`.  Measured on B200 (DESIGN.md "step program"): its ring streams the BF16 lm_head at the
+        # HBM peak, but an op boundary inside the kernel (device-side grid barrier + re-staging the activation vector)
+        # costs ~7 us against ~3.3 us for a programmatic-dependent-launch boundary, and the CUDA-core dequantisation of the
+        # FP8 / NVF4 rows runs at about the HBM rate, so it cannot catch up -- the per-op launches stay the default.
+        env = os.environ.get("PGK_STEP", "0")
+        self.use_step_program = env not in ("0", "", "auto")
         self._step = None
         self._step_tried = False
         self.step_unsupported_reason: str | None = None
@@ -99,8 +100,7 @@ class CausalTransformerModel:
     def step_program(self):
         """The one-launch decode step of this model, or None when the model does not fit it (reason kept in
         `step_unsupported_reason`) or it is switched off."""
-        use = self.use_step_program if self.use_step_program is not None else self.tp > 1
-        if not use:
+        if not self.use_step_program:
             return None
         if not self._step_tried:
             from ..step_program import StepProgram, Unsupported

@@ -83,6 +83,11 @@ def main():
     us = d[:, 5 * L].mean()
     print(f"{'lm_head (+norm, argmax)':26s} {hb / 1e6:8.2f} MB {us:7.2f} us {hb / us / 1e3:7.0f} GB/s")
     print(f"step {d.sum(axis=1).mean():.1f} us (CTA 0, first op start .. end)")
+    for nm, idx in (("qkv", 0), ("gate/up", 3), ("o_proj", 2), ("down", 4)):
+        o = tr[:, idx:5 * L:5, :]
+        print(f"staging of {nm}: loads+raw {(o[:, :, 5] - o[:, :, 0]).mean():.2f}  sumsq {(o[:, :, 6] - o[:, :, 5]).mean():.2f}  "
+              f"norm+max {(o[:, :, 7] - o[:, :, 6]).mean():.2f}  planes {(o[:, :, 1] - o[:, :, 7]).mean():.2f}   (no norm: only [7]-[0] = "
+              f"{(o[:, :, 7] - o[:, :, 0]).mean():.2f} and planes are meaningful)")
     at = tr[:, 1:5 * L:5, :]                              # attention ops
     print("attention: prologue %.2f  units(warp0) %.2f  fold %.2f  inner barrier %.2f  combine+closing %.2f" % (
         (at[:, :, 1] - at[:, :, 0]).mean(), (at[:, :, 2] - at[:, :, 1]).mean(), (at[:, :, 3] - at[:, :, 2]).mean(),

@@ -69,9 +69,14 @@ def _run_world(world: int) -> dict:
         if ln.startswith("{") and '"case"' in ln:
             d = json.loads(ln)
             out[d["case"]] = d
-    out["_rc"], out["_tail"] = r.returncode, (r.stdout[-1500:] + r.stderr[-2500:])
+    # the first traceback of a failing rank sits ahead of torchrun's own summary
+    err = r.stderr
+    i = err.find("Traceback")
+    out["_rc"], out["_tail"] = r.returncode, (r.stdout[-1500:] + (err[i:i + 3000] if i >= 0 else err[-2500:]))
     log = os.path.join(ROOT, "gpurun_out")
     if os.path.isdir(log):
+        with open(os.path.join(log, f"tp_worker_{world}gpu.err"), "w") as f:
+            f.write(err[-20000:])
         with open(os.path.join(log, f"tp_parity_{world}gpu.jsonl"), "w") as f:
             for k, v in out.items():
                 if not k.startswith("_"):
