@@ -319,6 +319,20 @@ int pgk_quantize_bf16_to_fp8_block(const void* w_nk, void* codes, void* scale, i
  * graph-replayed decode step (position_buf of llm/decode/m1_graph.py:329-331,505-506). */
 int pgk_decode_advance(int32_t* pos_buf, int32_t* ctx_buf, int delta, void* stream);
 
+/* Multi-sequence decode (continuous batching; replaces native/ops/attention/paged_attention.cuh:46-283 and
+ * native/ops/batch/continuous_batching.cuh:70-245 on the decode path): n_seq independent sequences in ONE launch of the
+ * fused bracket above.  Row s of qkv [n_seq, (Hq + 2 Hkv) * 128] / out [n_seq, Hq * 128] belongs to sequence s, whose
+ * cache region starts cache_stride elements after the previous one (k_cache / v_cache = [n_seq, n_kv, max_seq, 128]) and
+ * whose position / context length are pos_buf[s] / ctx_buf[s] (device arrays, so one CUDA graph serves every step). */
+int pgk_rope_sdpa_decode_batch(const void* qkv, const void* q_gamma, const void* k_gamma, float eps,
+                               const float* cos_table, const float* sin_table, void* k_cache, void* v_cache, void* out,
+                               int n_heads_q, int n_kv, int head_dim, int max_seq, int n_seq, const int32_t* pos_buf,
+                               const int32_t* ctx_buf, long cache_stride, float scale, void* stream);
+/* greedy tokens of a decode batch: out[r] (and out2[r] when not NULL) = argmax of row r of logits [rows, n], first
+ * maximum wins (llm/sampling.py:59-61) */
+int pgk_argmax_rows(const void* logits, int32_t* out, int32_t* out2, int rows, int n, int dtype, void* stream);
+int pgk_decode_advance_n(int32_t* pos_buf, int32_t* ctx_buf, int delta, int n, void* stream);
+
 /* ------------------------------------------------------------------ one-launch decode step ("step program")
  * net-new orchestration, same math.  Replaces the per-layer launch sequence of DecodeM1.step
  * (src/pygpukit/llm/decode/m1.py:40-121: ~25 launches per layer upstream, 5 per layer with the fused per-op

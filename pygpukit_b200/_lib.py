@@ -94,7 +94,9 @@ _SIGS = {
     "pgk_moe_combine_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
     "pgk_quantize_bf16_to_fp8_block": [vp, vp, vp, i32, i32, vp],
-    "pgk_decode_advance": [vp, vp, i32, vp],
+    "pgk_decode_advance": [vp, vp, i32, vp], "pgk_decode_advance_n": [vp, vp, i32, i32, vp],
+    "pgk_rope_sdpa_decode_batch": [vp, vp, vp, f32, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, cl, f32, vp],
+    "pgk_argmax_rows": [vp, vp, vp, i32, i32, i32, vp],
     "pgk_step_create": [vp, i32, vp, vp, vp, vp, i32, i32, C.POINTER(vp)], "pgk_step_run": [vp, vp],
     "pgk_step_error": [vp, C.POINTER(i32)], "pgk_step_info": [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)],
     "pgk_step_destroy": [vp], "pgk_step_trace": [vp, vp, i32], "pgk_step_set_vocab_offset": [vp, i32],

@@ -401,6 +401,10 @@ struct RopeSdpaParams {
     float scale_log2;
     int splits;
     float* ws; unsigned* counters;
+    // multi-sequence decode (continuous batching, native/ops/batch/continuous_batching.cuh:70-245): n_seq independent
+    // sequences, each with its own cache region, position and context length (pos_buf / ctx_buf are then arrays)
+    int n_seq;
+    long qkv_stride, out_stride, cache_stride;     // elements between consecutive sequences
 };
 constexpr int kFTile = 64;       // KV positions per staged tile (16 KB K + 16 KB V)
 constexpr int kFStages = 2;
@@ -451,11 +455,15 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
     const int li = lane & 15, slot = lane >> 4;
     const int G = p.hq / p.n_kv;
     const int row_tiles = (G + RT - 1) / RT;
-    const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z;
+    const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z % p.n_kv, seq = blockIdx.z / p.n_kv;
+    p.qkv += (size_t)seq * p.qkv_stride;
+    p.out += (size_t)seq * p.out_stride;
+    p.kc += (size_t)seq * p.cache_stride;
+    p.vc += (size_t)seq * p.cache_stride;
 
     // ---- independent of the previous kernel: position, barriers, the first K/V tiles
-    const int pos = p.pos_buf ? *p.pos_buf : p.pos;
-    const int ctx = min(p.ctx_buf ? *p.ctx_buf : p.context_len, p.max_seq);
+    const int pos = p.pos_buf ? p.pos_buf[seq] : p.pos;
+    const int ctx = min(p.ctx_buf ? p.ctx_buf[seq] : p.context_len, p.max_seq);
     int chunk = (ctx + p.splits - 1) / p.splits;
     chunk = (chunk + kFTile - 1) & ~(kFTile - 1);
     const int c0 = split * chunk, c1 = min(ctx, c0 + chunk);
@@ -650,7 +658,7 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
         }
     }
     __syncthreads();
-    const size_t tile_id = (size_t)kvh * row_tiles + rt;
+    const size_t tile_id = ((size_t)seq * p.n_kv + kvh) * row_tiles + rt;
     float* rec = p.ws + (tile_id * p.splits + split) * RT * REC;
     for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
         const int r = idx / HD, d = idx % HD;
@@ -728,7 +736,8 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
 static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
     const int G = p.hq / p.n_kv;
     const int row_tiles = (G + kFRT - 1) / kFRT;
-    const int base_ctas = p.n_kv * row_tiles;
+    if (p.n_seq < 1) p.n_seq = 1;
+    const int base_ctas = p.n_kv * row_tiles * p.n_seq;
     int splits = (2 * sm_count() + base_ctas - 1) / base_ctas;
     const int hint = p.ctx_buf ? p.max_seq : p.context_len;
     const int max_splits = (hint + 2 * kFTile - 1) / (2 * kFTile);
@@ -744,7 +753,8 @@ static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
         PGK_CUDA(cudaMalloc(&g_attn_cnt, kAttnMaxTiles * sizeof(unsigned)));
         PGK_CUDA(cudaMemset(g_attn_cnt, 0, kAttnMaxTiles * sizeof(unsigned)));
     }
-    PGK_REQUIRE(base_ctas <= kAttnMaxTiles, "rope_sdpa_decode failed: too many heads (%d)", p.hq);
+    PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * kFRT * 130 * 4 <= kAttnWsBytes,
+                "rope_sdpa_decode failed: too many (sequence, head) tiles (%d)", base_ctas);
     p.splits = splits;
     p.ws = g_attn_ws;
     p.counters = g_attn_cnt;
@@ -754,7 +764,7 @@ static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
         PGK_CUDA(cudaFuncSetAttribute(rope_sdpa_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
         attr_set = true;
     }
-    PGK_CUDA(launch(rope_sdpa_decode_kernel, dim3(splits, row_tiles, p.n_kv), dim3(kAttnWarps * 32), kSmem, st, p));
+    PGK_CUDA(launch(rope_sdpa_decode_kernel, dim3(splits, row_tiles, p.n_kv * p.n_seq), dim3(kAttnWarps * 32), kSmem, st, p));
     return 0;
 }
 
@@ -805,6 +815,27 @@ int pgk_rope_sdpa_decode(const void* qkv, const void* q_gamma, const void* k_gam
     p.cos_t = cos_table; p.sin_t = sin_table; p.kc = (uint16_t*)k_cache; p.vc = (uint16_t*)v_cache; p.out = (uint16_t*)out;
     p.hq = n_heads_q; p.n_kv = n_kv; p.max_seq = max_seq; p.pos = pos; p.context_len = context_len;
     p.pos_buf = pos_buf; p.ctx_buf = ctx_buf;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    return launch_rope_sdpa(p, (cudaStream_t)stream);
+}
+
+/* n_seq independent sequences in one launch (continuous batching): row s of qkv / out, cache region s (cache_stride
+ * elements apart: [n_seq, n_kv, max_seq, 128]), pos_buf[s], ctx_buf[s] */
+int pgk_rope_sdpa_decode_batch(const void* qkv, const void* q_gamma, const void* k_gamma, float eps, const float* cos_table,
+                               const float* sin_table, void* k_cache, void* v_cache, void* out, int n_heads_q, int n_kv,
+                               int head_dim, int max_seq, int n_seq, const int32_t* pos_buf, const int32_t* ctx_buf,
+                               long cache_stride, float scale, void* stream) {
+    PGK_REQUIRE(head_dim == 128, "rope_sdpa_decode_batch failed: head_dim %d (the fused bracket is built for 128)", head_dim);
+    PGK_REQUIRE(n_kv > 0 && n_heads_q % n_kv == 0, "rope_sdpa_decode_batch failed: n_heads %d not a multiple of n_kv_heads %d", n_heads_q, n_kv);
+    PGK_REQUIRE(n_seq >= 1 && pos_buf && ctx_buf, "rope_sdpa_decode_batch failed: needs n_seq >= 1 and per-sequence position / context arrays");
+    PGK_REQUIRE(((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) && ((uintptr_t)qkv % 16 == 0) && cache_stride % 8 == 0,
+                "rope_sdpa_decode_batch failed: qkv / K / V must be 16-byte aligned");
+    if (scale <= 0.f) scale = 1.0f / sqrtf((float)head_dim);
+    RopeSdpaParams p = {};
+    p.qkv = (const uint16_t*)qkv; p.q_gamma = (const uint16_t*)q_gamma; p.k_gamma = (const uint16_t*)k_gamma; p.eps = eps;
+    p.cos_t = cos_table; p.sin_t = sin_table; p.kc = (uint16_t*)k_cache; p.vc = (uint16_t*)v_cache; p.out = (uint16_t*)out;
+    p.hq = n_heads_q; p.n_kv = n_kv; p.max_seq = max_seq; p.pos_buf = pos_buf; p.ctx_buf = ctx_buf;
+    p.n_seq = n_seq; p.qkv_stride = (long)(n_heads_q + 2 * n_kv) * 128; p.out_stride = (long)n_heads_q * 128; p.cache_stride = cache_stride;
     p.scale_log2 = scale * 1.4426950408889634f;
     return launch_rope_sdpa(p, (cudaStream_t)stream);
 }

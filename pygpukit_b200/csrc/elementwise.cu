@@ -278,6 +278,36 @@ __global__ void argmax_kernel(const void* __restrict__ x, int32_t* __restrict__ 
         *out = (bi == 0x7fffffff) ? 0 : bi;
     }
 }
+// one CTA per row of a [rows, n] matrix (greedy tokens of a decode batch); out2 (optional) receives the same tokens
+template <int DT>
+__global__ void argmax_rows_kernel(const void* __restrict__ x, int32_t* __restrict__ out, int32_t* __restrict__ out2, int n) {
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    griddep_wait();
+    griddep_launch();
+    const size_t base = (size_t)blockIdx.x * n;
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        float v = Elem<DT>::ld(x, base + i);
+        if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)((blockDim.x + 31) >> 5); ++w)
+            if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+        const int t = (bi == 0x7fffffff) ? 0 : bi;
+        out[blockIdx.x] = t;
+        if (out2) out2[blockIdx.x] = t;
+    }
+}
 
 // transpose_3d_021: [d0,d1,d2] -> [d1,d0,d2]
 template <typename T>
@@ -522,6 +552,11 @@ int pgk_embedding_lookup_pos(const void* wte, const void* wpe, void* out, int hi
 int pgk_argmax(const void* logits, int32_t* out, int n, int dtype, void* stream) {
     PGK_REQUIRE(n > 0, "argmax failed: empty input");
     PGK_DISPATCH_DT(dtype, "argmax", PGK_CUDA(launch(argmax_kernel<DT>, dim3(1), dim3(1024), 0, ST(stream), logits, out, n)));
+    return 0;
+}
+int pgk_argmax_rows(const void* logits, int32_t* out, int32_t* out2, int rows, int n, int dtype, void* stream) {
+    PGK_REQUIRE(n > 0 && rows >= 1, "argmax_rows failed: empty input");
+    PGK_DISPATCH_DT(dtype, "argmax_rows", PGK_CUDA(launch(argmax_rows_kernel<DT>, dim3(rows), dim3(1024), 0, ST(stream), logits, out, out2, n)));
     return 0;
 }
 int pgk_transpose_021(const void* in, void* out, int d0, int d1, int d2, int elem_bytes, void* stream) {

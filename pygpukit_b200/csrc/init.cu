@@ -74,12 +74,12 @@ quantize_fp8_block_kernel(const uint16_t* __restrict__ W, uint8_t* __restrict__ 
     }
 }
 
-__global__ void decode_advance_kernel(int32_t* a, int32_t* b, int delta) {
+__global__ void decode_advance_kernel(int32_t* a, int32_t* b, int delta, int n) {
     griddep_wait();
     griddep_launch();
-    if (threadIdx.x == 0) {
-        if (a) *a += delta;
-        if (b) *b += delta;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        if (a) a[i] += delta;
+        if (b) b[i] += delta;
     }
 }
 
@@ -108,7 +108,12 @@ int pgk_quantize_bf16_to_fp8_block(const void* w_nk, void* codes, void* scale, i
 }
 
 int pgk_decode_advance(int32_t* pos_buf, int32_t* ctx_buf, int delta, void* stream) {
-    PGK_CUDA(launch(decode_advance_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, pos_buf, ctx_buf, delta));
+    PGK_CUDA(launch(decode_advance_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, pos_buf, ctx_buf, delta, 1));
+    return 0;
+}
+/* the same for n sequences (arrays of n positions / contexts) */
+int pgk_decode_advance_n(int32_t* pos_buf, int32_t* ctx_buf, int delta, int n, void* stream) {
+    PGK_CUDA(launch(decode_advance_kernel, dim3(1), dim3(64), 0, (cudaStream_t)stream, pos_buf, ctx_buf, delta, n));
     return 0;
 }
 

@@ -26,7 +26,8 @@ class DecodeBuffers:
     context_buf: GPUArray     # int32 [1]
     next_token: GPUArray      # int32 [M]  greedy result
     max_batch_size: int = 1
-    state_buf: GPUArray | None = None   # int32 [2 + M] = [position, context, tokens...]: ONE H2D copy per step
+    num_sequences: int = 1
+    state_buf: GPUArray | None = None   # int32 [2 S + M] = [positions, contexts, tokens...]: ONE H2D copy per step
 
     # aliases with the reference's member names (buffers.py:26-188)
     @property
@@ -43,7 +44,8 @@ class DecodeBuffers:
 
     @classmethod
     def allocate(cls, config: TransformerConfig, dtype: str = "bfloat16", use_qk_norm: bool = False,
-                 vocab_size: int | None = None, max_batch_size: int = 0, moe_config: dict | None = None) -> "DecodeBuffers":
+                 vocab_size: int | None = None, max_batch_size: int = 0, moe_config: dict | None = None,
+                 num_sequences: int = 1) -> "DecodeBuffers":
         if dtype != "bfloat16":
             raise ValueError("the B200 decode path runs in bfloat16")
         M = max(1, max_batch_size)
@@ -53,15 +55,17 @@ class DecodeBuffers:
         hq, hkv = config.num_heads // tp, max(1, config.num_kv_heads // tp)
         inter = (config.moe_intermediate_size if config.is_moe else config.intermediate_size) // (1 if config.is_moe else tp)
         V = vocab_size if vocab_size is not None else config.vocab_size
-        state = zeros((2 + M,), int32)
+        S = max(1, num_sequences)
+        # decode state, ONE host-to-device copy per step: [position x S | context x S | token x M]
+        state = zeros((2 * S + M,), int32)
         return cls(
             state_buf=state,
             hidden=zeros((M, H), bfloat16), norm_out=zeros((M, H), bfloat16),
             qkv_proj_out=zeros((M, (hq + 2 * hkv) * hd), bfloat16), attn_flat=zeros((M, hq * hd), bfloat16),
             mlp_act=zeros((M, inter), bfloat16), partial=zeros((M, H), bfloat16),
             logits=zeros((M, V), bfloat16) if V else None,
-            token_buf=state.narrow(2, M), position_buf=state.narrow(0, 1), context_buf=state.narrow(1, 1),
-            next_token=zeros((M,), int32), max_batch_size=M)
+            token_buf=state.narrow(2 * S, M), position_buf=state.narrow(0, S), context_buf=state.narrow(S, S),
+            next_token=zeros((M,), int32), max_batch_size=M, num_sequences=S)
 
 
 @dataclass

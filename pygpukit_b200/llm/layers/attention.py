@@ -112,12 +112,15 @@ class Attention:
         self._logical_pos = 0
 
     # ---- fixed KV cache
-    def init_fixed_cache(self, max_seq_len: int, dtype: str = "bfloat16", rope_tables=None) -> None:
-        """Allocate the fixed-length KV cache (attention.py:128-146) -- un-expanded layout."""
+    def init_fixed_cache(self, max_seq_len: int, dtype: str = "bfloat16", rope_tables=None, num_sequences: int = 1) -> None:
+        """Allocate the fixed-length KV cache (attention.py:128-146) -- un-expanded layout.  num_sequences > 1:
+        one region per independent sequence, [S * n_kv, max_seq, hd] (multi-sequence decode, net-new on this path;
+        the reference's paged / continuous-batching kernels are not wired to its Python layers)."""
         if dtype != "bfloat16":
             raise ValueError("the B200 decode path keeps the KV cache in bfloat16")
-        shape = (self.num_kv_heads, max_seq_len, self.head_dim)
+        shape = (num_sequences * self.num_kv_heads, max_seq_len, self.head_dim)
         self._k_cache, self._v_cache = zeros(shape, bfloat16), zeros(shape, bfloat16)
+        self._num_sequences, self._cur_seq = num_sequences, 0
         self._max_cache_len = max_seq_len
         self._confirmed_pos = self._logical_pos = 0
         if self.config.use_rope:
@@ -131,6 +134,42 @@ class Attention:
                     self._cos, self._sin = precompute_freqs_cis(self.head_dim, max_seq_len, self.config.rope_theta)
                 self._cos_dev = from_numpy(np.ascontiguousarray(self._cos[:max_seq_len], np.float32))
                 self._sin_dev = from_numpy(np.ascontiguousarray(self._sin[:max_seq_len], np.float32))
+
+    @property
+    def _seq_stride(self) -> int:
+        """elements between the cache regions of consecutive sequences"""
+        return self.num_kv_heads * self._max_cache_len * self.head_dim
+
+    def select_sequence(self, s: int) -> None:
+        """Single-sequence entry points (prefill, forward_fixed_cache) work on sequence `s`'s cache region."""
+        if not 0 <= s < getattr(self, "_num_sequences", 1):
+            raise ValueError(f"sequence {s} out of range")
+        self._cur_seq = s
+
+    def _kv_ptrs(self) -> tuple[int, int]:
+        off = getattr(self, "_cur_seq", 0) * self._seq_stride * 2
+        return self._k_cache.device_ptr + off, self._v_cache.device_ptr + off
+
+    def attend_multi(self, x: GPUArray, pos_buf: GPUArray, ctx_buf: GPUArray, *, qkv_buf: GPUArray | None = None,
+                     attn_buf: GPUArray | None = None, norm=None) -> GPUArray:
+        """Row s of x [S, hidden] is the new token of independent sequence s (its own cache region, position
+        pos_buf[s], context ctx_buf[s]); returns [S, q_dim].  One qkv projection for all rows, ONE attention launch."""
+        S = x.shape[0]
+        if S != getattr(self, "_num_sequences", 1):
+            raise ValueError(f"{S} rows for {getattr(self, '_num_sequences', 1)} sequences (init_decode num_sequences)")
+        if self.head_dim != 128 or not self.config.use_rope:
+            raise ValueError("multi-sequence decode needs head_dim 128 and RoPE")
+        H, Hkv, hd = self.num_heads, self.num_kv_heads, self.head_dim
+        qkv = self.qkv_proj.forward(x, out=qkv_buf, norm=norm)
+        if attn_buf is None:
+            attn_buf = GPUArray((S, H * hd), bfloat16)
+        api.rope_sdpa_decode_batch(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
+                                   None if self.k_norm is None else self.k_norm.weight.device_ptr,
+                                   float(self.q_norm.eps if self.q_norm is not None else 0.0),
+                                   self._cos_dev.device_ptr, self._sin_dev.device_ptr, self._k_cache.device_ptr,
+                                   self._v_cache.device_ptr, attn_buf.device_ptr, H, Hkv, hd, self._max_cache_len, S,
+                                   pos_buf.device_ptr, ctx_buf.device_ptr, self._seq_stride, 0.0, _st())
+        return attn_buf
 
     def set_confirmed_pos(self, pos: int) -> None:
         assert 0 <= pos <= self._max_cache_len, f"Invalid pos {pos}"
@@ -166,25 +205,27 @@ class Attention:
             attn_buf = attn_buf.slice_rows(M)
         if M == 1 and hd == 128 and self.config.use_rope and _FUSED_BRACKET:
             # one launch: QK-norm + RoPE + KV write + split-KV attention (pgk_rope_sdpa_decode)
+            kp, vp = self._kv_ptrs()
             api.rope_sdpa_decode(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
                                  None if self.k_norm is None else self.k_norm.weight.device_ptr,
                                  float(self.q_norm.eps if self.q_norm is not None else 0.0),
-                                 self._cos_dev.device_ptr, self._sin_dev.device_ptr, self._k_cache.device_ptr,
-                                 self._v_cache.device_ptr, attn_buf.device_ptr, H, Hkv, hd, self._max_cache_len,
+                                 self._cos_dev.device_ptr, self._sin_dev.device_ptr, kp,
+                                 vp, attn_buf.device_ptr, H, Hkv, hd, self._max_cache_len,
                                  int(position), None if pos_buf is None else pos_buf.device_ptr, int(context_len),
                                  None if ctx_buf is None else ctx_buf.device_ptr, 0.0, _st())
             return attn_buf
         # QK-norm / RoPE / K,V cache write in one launch; without RoPE (GPT-2) the tables are NULL and the launch
         # only writes the K/V rows into the cache
         rope = self.config.use_rope
+        kp, vp = self._kv_ptrs()
         api.qk_norm_rope_kv_write(qkv.device_ptr, None if self.q_norm is None else self.q_norm.weight.device_ptr,
                                   None if self.k_norm is None else self.k_norm.weight.device_ptr,
                                   float(self.q_norm.eps if self.q_norm is not None else 0.0),
                                   self._cos_dev.device_ptr if rope else None, self._sin_dev.device_ptr if rope else None,
-                                  self._k_cache.device_ptr, self._v_cache.device_ptr, M, H, Hkv, hd, self._max_cache_len,
+                                  kp, vp, M, H, Hkv, hd, self._max_cache_len,
                                   int(position), None if pos_buf is None else pos_buf.device_ptr, _st())
         # Q read in place from the qkv rows (head stride hd, token stride `width`); out [M, H*hd]
-        api.sdpa_decode(qkv.device_ptr, self._k_cache.device_ptr, self._v_cache.device_ptr, attn_buf.device_ptr, H, Hkv,
+        api.sdpa_decode(qkv.device_ptr, kp, vp, attn_buf.device_ptr, H, Hkv,
                         M, hd, self._max_cache_len, int(context_len), None if ctx_buf is None else ctx_buf.device_ptr,
                         0.0, hd, width, hd, H * hd, 2, _st())
         return attn_buf

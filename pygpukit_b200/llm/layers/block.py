@@ -20,8 +20,10 @@ class TransformerBlock:
         self.mlp = mlp
         self.comm = comm   # TensorParallel communicator or None
 
-    def decode(self, hidden: GPUArray, position: int, context_len: int, bufs=None, pos_buf=None, ctx_buf=None) -> GPUArray:
-        """hidden [M, H] -> hidden [M, H], updated IN PLACE (M consecutive tokens of one sequence)."""
+    def decode(self, hidden: GPUArray, position: int, context_len: int, bufs=None, pos_buf=None, ctx_buf=None,
+               multi: bool = False) -> GPUArray:
+        """hidden [M, H] -> hidden [M, H], updated IN PLACE (M consecutive tokens of one sequence; multi = True: the
+        new tokens of M independent sequences, pos_buf / ctx_buf are then arrays of M)."""
         M = hidden.shape[0]
 
         def buf(name):
@@ -30,7 +32,12 @@ class TransformerBlock:
 
         tp = self.comm is not None and self.comm.world > 1
         # pre-norms ride inside the qkv / gate-up GEMV launches when the formats allow it
-        if can_fuse_norm(self.attn_norm, hidden.shape[1]):
+        if multi:
+            fuse = can_fuse_norm(self.attn_norm, hidden.shape[1])
+            x = hidden if fuse else self.attn_norm(hidden, out=buf("norm_out"))
+            a = self.attn.attend_multi(x, pos_buf, ctx_buf, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
+                                       norm=self.attn_norm if fuse else None)
+        elif can_fuse_norm(self.attn_norm, hidden.shape[1]):
             a = self.attn.attend(hidden, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
                                  pos_buf=pos_buf, ctx_buf=ctx_buf, norm=self.attn_norm)
         else:

@@ -80,22 +80,39 @@ class CausalTransformerModel:
     def tp(self) -> int:
         return self.comm.world if self.comm is not None else 1
 
-    def init_decode(self, max_seq_len: int, max_batch_size: int = 1) -> DecodeBuffers:
-        """Allocate the fixed KV caches (all layers), the shared RoPE tables and the step buffers."""
+    def init_decode(self, max_seq_len: int, max_batch_size: int = 1, num_sequences: int = 1) -> DecodeBuffers:
+        """Allocate the fixed KV caches (all layers), the shared RoPE tables and the step buffers.
+        num_sequences = S > 1: S independent sequences decode together (one row each per step; continuous batching,
+        SURVEY.md section 8f-2): every layer holds S cache regions, position / context are arrays of S."""
+        S = max(1, int(num_sequences))
+        if S > 1:
+            a0 = self.blocks[0].attn
+            need = 2 * len(self.blocks) * S * a0.num_kv_heads * max_seq_len * a0.head_dim * 2
+            free, total = C.c_size_t(0), C.c_size_t(0)
+            api.mem_info(C.byref(free), C.byref(total))
+            if need > free.value - (2 << 30):
+                raise MemoryError(f"{S} sequences x {max_seq_len} positions need {need / 2**30:.1f} GiB of KV cache, "
+                                  f"{free.value / 2**30:.1f} GiB free")
         tables = None
         for blk in self.blocks:
-            blk.attn.init_fixed_cache(max_seq_len, "bfloat16", rope_tables=tables)
+            blk.attn.init_fixed_cache(max_seq_len, "bfloat16", rope_tables=tables, num_sequences=S)
             if tables is None and self.config.use_rope:
                 tables = (blk.attn._cos_dev, blk.attn._sin_dev)
         v_local = self._head.shape[0]
         self._buffers = DecodeBuffers.allocate(self.config, "bfloat16", vocab_size=v_local,
-                                               max_batch_size=max_batch_size)
+                                               max_batch_size=max(max_batch_size, S), num_sequences=S)
         self._max_seq = max_seq_len
+        self._num_sequences = S
         if self.tp > 1:
             self._gathered_logits = GPUArray((self.tp * v_local,), bfloat16)
         self._graph = None
         self._step, self._step_tried = None, False
         return self._buffers
+
+    def select_sequence(self, s: int) -> None:
+        """The single-sequence entry points (prefill, __call__, forward_fixed_cache) work on sequence `s`."""
+        for blk in self.blocks:
+            blk.attn.select_sequence(s)
 
     def step_program(self):
         """The one-launch decode step of this model, or None when the model does not fit it (reason kept in
@@ -230,6 +247,8 @@ class CausalTransformerModel:
         """One greedy token entirely on the device: reads token_buf / position_buf / context_buf,
         writes the sampled token to next_token AND token_buf, then advances position / context."""
         b = self.buffers
+        if getattr(self, "_num_sequences", 1) > 1:
+            return self._decode_step_device_multi()
         step = self.step_program()
         if step is not None:             # ONE persistent kernel: embedding .. argmax .. position advance
             step.run(_st())
@@ -263,43 +282,79 @@ class CausalTransformerModel:
         api.memcpy_d2d(b.next_token.device_ptr, b.token_buf.device_ptr, 4, _st())
         api.decode_advance(b.position_buf.device_ptr, b.context_buf.device_ptr, 1, _st())
 
-    def set_decode_state(self, token_id: int, position: int) -> None:
-        """position_buf = position, context_buf = position + 1, token_buf = token_id (one 12-byte copy)."""
+    def _decode_step_device_multi(self) -> None:
+        """One greedy token for each of the S independent sequences, entirely on the device: S rows through every
+        linear layer (the weights are read once for all rows), ONE attention launch per layer over the S cache regions,
+        per-row argmax, positions / contexts advanced."""
         b = self.buffers
-        st = np.array([position, position + 1, token_id], np.int32)
-        api.memcpy_h2d(b.state_buf.device_ptr, st.ctypes.data_as(C.c_void_p), 12, _st())
+        S = self._num_sequences
+        if self.tp > 1:
+            raise ValueError("multi-sequence decode runs on unsharded models")
+        hidden = b.hidden if b.hidden.shape[0] == S else b.hidden.slice_rows(S)
+        H, V = self.config.hidden_size, self._head.shape[0]
+        api.embedding_lookup_ptr(self.embed_tokens.device_ptr, hidden.device_ptr, H, b.token_buf.device_ptr, S, 2, _st())
+        for blk in self.blocks:
+            blk.decode(hidden, 0, self._max_seq, b, b.position_buf, b.context_buf, multi=True)
+        logits = b.logits if b.logits.shape[0] == S else b.logits.slice_rows(S)
+        fn = self.final_norm
+        if can_fuse_norm(fn, H):
+            api.rmsnorm_gemv_bf16(hidden.device_ptr, fn.weight.device_ptr, float(fn.eps), self._head.device_ptr,
+                                  logits.device_ptr, S, H, V, None, None, _st())
+        else:
+            x = self._final(hidden, b)
+            api.gemv_bf16(x.device_ptr, self._head.device_ptr, logits.device_ptr, S, H, V, _st())
+        api.argmax_rows(logits.device_ptr, b.next_token.device_ptr, b.token_buf.device_ptr, S, V, 2, _st())
+        api.decode_advance_n(b.position_buf.device_ptr, b.context_buf.device_ptr, 1, S, _st())
+
+    def set_decode_state(self, token_id, position) -> None:
+        """position_buf = position, context_buf = position + 1, token_buf = token_id (one small copy).  With S
+        sequences token_id is a list of S tokens and position an int (the same for all) or a list of S."""
+        b = self.buffers
+        S = getattr(self, "_num_sequences", 1)
+        toks = [int(t) for t in token_id] if isinstance(token_id, (list, tuple, np.ndarray)) else [int(token_id)]
+        pos = [int(p) for p in position] if isinstance(position, (list, tuple, np.ndarray)) else [int(position)] * S
+        if len(toks) != S or len(pos) != S:
+            raise ValueError(f"decode state needs {S} tokens / positions")
+        st = np.array(pos + [p + 1 for p in pos] + toks, np.int32)
+        api.memcpy_h2d(b.state_buf.device_ptr, st.ctypes.data_as(C.c_void_p), st.nbytes, _st())
         api.stream_sync(_st()) if _st() is not None else api.device_sync()
 
     def _pinned_state(self):
-        """Pinned host staging: int32[3] step inputs + int32[1] result (allocated once)."""
-        if getattr(self, "_pin", None) is None:
+        """Pinned host staging: int32[3 S] step inputs + int32[S] results (allocated once per S)."""
+        S = getattr(self, "_num_sequences", 1)
+        if getattr(self, "_pin", None) is None or getattr(self, "_pin_S", 0) != S:
             h = C.c_void_p()
-            api.host_alloc(C.byref(h), 16)
-            self._pin = h
-            self._pin_np = np.ctypeslib.as_array(C.cast(h, C.POINTER(C.c_int32)), shape=(4,))
+            api.host_alloc(C.byref(h), 16 * S)
+            self._pin, self._pin_S = h, S
+            self._pin_np = np.ctypeslib.as_array(C.cast(h, C.POINTER(C.c_int32)), shape=(4 * S,))
         return self._pin, self._pin_np
 
-    def decode_step_host(self, token_id: int, position: int) -> int:
-        """One greedy decode step with the HOST in the loop (what a serving loop does): token id and
-        position go host -> device from pinned memory (12 bytes), the step graph replays, the sampled
-        token comes back device -> host (4 bytes).  Returns the next token."""
+    def decode_step_host(self, token_id, position: int):
+        """One greedy decode step with the HOST in the loop (what a serving loop does): token ids and positions go
+        host -> device from pinned memory (12 bytes per sequence), the step graph replays, the sampled tokens come back
+        device -> host (4 bytes per sequence).  Returns the next token (a list with S sequences)."""
         assert self._graph is not None, "Call init_decode_graph first"
+        S = getattr(self, "_num_sequences", 1)
         pin, arr = self._pinned_state()
-        arr[0], arr[1], arr[2] = position, position + 1, token_id
+        toks = list(token_id) if S > 1 else [token_id]
+        arr[0:S] = position
+        arr[S:2 * S] = position + 1
+        arr[2 * S:3 * S] = toks
         b = self.buffers
         sh = self._graph_stream.handle
-        api.memcpy_h2d(b.state_buf.device_ptr, pin, 12, sh)
+        api.memcpy_h2d(b.state_buf.device_ptr, pin, 12 * S, sh)
         self._graph.replay(self._graph_stream)
-        api.memcpy_d2h(pin.value + 12, b.next_token.device_ptr, 4, sh)
+        api.memcpy_d2h(pin.value + 12 * S, b.next_token.device_ptr, 4 * S, sh)
         api.stream_sync(sh)
-        return int(arr[3])
+        return [int(t) for t in arr[3 * S:4 * S]] if S > 1 else int(arr[3])
 
     def init_decode_graph(self) -> None:
         """Capture decode_step_device into one CUDA graph (replaces the reference's per-layer
         pre/post-SDPA graphs with syncs in between, decode/m1_graph.py:248-457)."""
         self._graph_stream = Stream()
         with use_stream(self._graph_stream):
-            self.set_decode_state(0, 0)
+            S = getattr(self, "_num_sequences", 1)
+            self.set_decode_state([0] * S if S > 1 else 0, 0)
             self.decode_step_device()            # warm-up outside capture (workspaces, attributes)
             self._graph_stream.synchronize()
             g = CudaGraph()

@@ -328,3 +328,50 @@ def test_gpt2_small_full_size_graph_equals_eager():
     model.init_decode(1024, max_batch_size=64)
     b = model.generate(prompt, 32, temperature=0.0, use_graph=False)
     assert a[:160] == b
+
+
+@pytest.mark.parametrize("name,fmt,S", [("small-qwen3", "fp8", 3), ("small-qwen3", "nvf4", 3), ("small-qwen3", "fp8", 8)])
+def test_multi_sequence_decode_matches_single_sequence_runs(name, fmt, S):
+    """Multi-sequence decode (replaces the reference's unused paged_attention.cuh:46-283 /
+    continuous_batching.cuh:70-245): S independent sequences with different prompt lengths decode together -- one row
+    per sequence through every linear layer, ONE attention launch per layer over the S cache regions with per-sequence
+    positions -- and must produce the tokens each sequence produces when it decodes alone (the split-KV fold order and,
+    from 5 rows, the tensor-core GEMM differ, so a divergence is accepted only where the lone run's two best logits are
+    equal or adjacent BF16 numbers)."""
+    n_new = 48
+    rng = np.random.default_rng(17)
+    model = llm.build_random_model(name, fmt, max_seq=MAX_SEQ, seed=7, std=0.05)
+    V = model.config.vocab_size
+    prompts = [[int(t) for t in rng.integers(0, V, 5 + 3 * (s % 4))] for s in range(S)]
+    # ---- each sequence alone
+    alone = []
+    for p in prompts:
+        model.init_decode(MAX_SEQ, max_batch_size=16)
+        alone.append(model.generate(p, n_new, temperature=0.0)[len(p):])
+    # ---- together: graph first (its warm-up step writes cache row 0), then the prompts, then S-row steps
+    model.init_decode(MAX_SEQ, max_batch_size=16, num_sequences=S)
+    model.init_decode_graph()
+    firsts = []
+    for s, p in enumerate(prompts):
+        model.select_sequence(s)
+        hidden = model.prefill(p)
+        lg = model.get_logits(hidden.row(hidden.shape[0] - 1).view((1, hidden.shape[1]))).to_numpy()[0]
+        firsts.append(int(np.argmax(f32(lg))))
+    model.set_decode_state(firsts, [len(p) for p in prompts])
+    together = [[t] for t in firsts]
+    from pygpukit_b200._lib import api
+    for _ in range(n_new - 1):
+        model.decode_graph_replay()
+        api.stream_sync(model._graph_stream.handle)
+        for s, t in enumerate(model.buffers.next_token.to_numpy()[:S]):
+            together[s].append(int(t))
+    # ---- compare
+    for s, p in enumerate(prompts):
+        same = next((i for i, (a, b) in enumerate(zip(together[s], alone[s])) if a != b), n_new)
+        if same < n_new:
+            model.init_decode(MAX_SEQ, max_batch_size=16)
+            hidden = model.prefill(p + alone[s][:same])
+            lg = np.sort(f32(model.get_logits(hidden.row(hidden.shape[0] - 1).view((1, hidden.shape[1]))).to_numpy()[0]))
+            ulp = 2.0 ** (np.floor(np.log2(max(abs(lg[-1]), 1e-30))) - 7)
+            assert lg[-1] - lg[-2] <= ulp, f"sequence {s}: token {same} differs ({together[s][same]} vs {alone[s][same]}), margin {lg[-1] - lg[-2]}"
+        assert same >= 8, f"sequence {s}: only {same} identical tokens"
