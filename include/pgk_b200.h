@@ -119,6 +119,16 @@ int pgk_gemv_nvf4_bf16(const void* A, const void* B_data, const void* B_scale, v
 int pgk_gemv_nvf4_bf16_ex(const void* A, const void* B_data, const void* B_scale, void* C, int M,
                           int K, int N, float alpha, const void* bias, const void* residual,
                           void* stream);
+/* Decode batch 5..64 on the tensor cores: E2M1 x UE4M3 has <= 6 significant bits, so the converter warps write EXACT BF16
+ * weight tiles (F2FP.E2M1 unpack, HMUL2 by the scale) and one tcgen05.mma.kind::f16 per 16 k computes exact products with
+ * F32 accumulation in TMEM -- the FP32-accumulate class of the GEMV, weights read once for all M rows.  Needs
+ * 1 <= M <= 64, K % 128 == 0, N % 128 == 0; pgk_gemv_nvf4_bf16(_ex) dispatch here for M >= 5.  Replaces the per-row use of
+ * gemv_nvf4_bf16_kernel (nvf4_kernels.cu:79-233) and the CUTLASS NVF4 GEMM of gemm/w4a16_bf16/sm120/nvf4_cutlass.cu. */
+int pgk_gemm_nvf4_bf16_tc(const void* A, const void* B_data, const void* B_scale, void* C, int M, int K, int N,
+                          float alpha, const void* bias, const void* residual, void* stream);
+/* out[M,I] = bf16(bf16(silu(g)) * u) from a [M, 2I] tensor whose columns are gate/up interleaved in groups of 8 (the
+ * fused NVF4 MLP layout below): the epilogue of the batched (tensor-core) gate/up projection */
+int pgk_swiglu_interleaved8_bf16(const void* gate_up, void* out, int M, int I, void* stream);
 /* gate/up GEMV + SiLU*up on ONE fused weight tensor: Wgu_data u8 [K/2, 2I], Wgu_scale
  * [K/32, 2I] whose columns are gate/up interleaved in groups of 8
  * ([g0..g7, u0..u7, g8..g15, u8..]); N2 = 2I, C = [M, I].  The layout is produced by

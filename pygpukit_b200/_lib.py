@@ -47,6 +47,8 @@ _SIGS = {
     "pgk_gemv_nvf4_bf16_ex": [vp, vp, vp, vp, i32, i32, i32, f32, vp, vp, vp],
     "pgk_gemv_nvf4_swiglu_bf16": [vp, vp, vp, vp, i32, i32, i32, vp],
     "pgk_quantize_bf16_to_nvf4": [vp, vp, vp, i32, i32, vp],
+    "pgk_gemm_nvf4_bf16_tc": [vp, vp, vp, vp, i32, i32, i32, f32, vp, vp, vp],
+    "pgk_swiglu_interleaved8_bf16": [vp, vp, i32, i32, vp],
     "pgk_gemv_bf16": [vp, vp, vp, i32, i32, i32, vp],
     "pgk_gemv_bf16_ex": [vp, vp, vp, i32, i32, i32, vp, vp, vp],
     "pgk_gemv_bf16_argmax": [vp, vp, vp, vp, i32, i32, vp],

@@ -30,6 +30,7 @@ SOURCES = {
     "gemv_bf16.cu": [],
     "gemm_w8a16.cu": [],
     "gemm_tc.cu": [],
+    "gemm_tc_nvf4.cu": [],
     "elementwise.cu": [],
     "attention.cu": [],
     "moe.cu": [],

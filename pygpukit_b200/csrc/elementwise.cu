@@ -278,6 +278,22 @@ __global__ void argmax_kernel(const void* __restrict__ x, int32_t* __restrict__ 
         *out = (bi == 0x7fffffff) ? 0 : bi;
     }
 }
+// gate/up columns interleaved in groups of 8 ([g0..g7, u0..u7, g8..], the fused NVF4 MLP tensor): out[m, j] =
+// bf16( bf16(silu(g)) * u ) -- silu_bf16_kernel then mul_inplace_bf16_kernel of the reference (activation_kernels.cuh:164-171,
+// elementwise_kernels.cuh:429-438), two roundings
+__global__ void swiglu_interleaved8_kernel(const uint16_t* __restrict__ gu, uint16_t* __restrict__ out, int M, int I) {
+    griddep_wait();
+    griddep_launch();
+    const size_t total = (size_t)M * I;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t m = i / I;
+        const int j = (int)(i - m * I);
+        const uint16_t* row = gu + m * (size_t)(2 * I) + (size_t)(j >> 3) * 16 + (j & 7);
+        const float g = bf16_bits_to_f32(row[0]), u = bf16_bits_to_f32(row[8]);
+        const float sl = round_bf16(g / (1.0f + __expf(-g)));
+        out[i] = f32_to_bf16_bits(sl * u);
+    }
+}
 // one CTA per row of a [rows, n] matrix (greedy tokens of a decode batch); out2 (optional) receives the same tokens
 template <int DT>
 __global__ void argmax_rows_kernel(const void* __restrict__ x, int32_t* __restrict__ out, int32_t* __restrict__ out2, int n) {
@@ -552,6 +568,12 @@ int pgk_embedding_lookup_pos(const void* wte, const void* wpe, void* out, int hi
 int pgk_argmax(const void* logits, int32_t* out, int n, int dtype, void* stream) {
     PGK_REQUIRE(n > 0, "argmax failed: empty input");
     PGK_DISPATCH_DT(dtype, "argmax", PGK_CUDA(launch(argmax_kernel<DT>, dim3(1), dim3(1024), 0, ST(stream), logits, out, n)));
+    return 0;
+}
+int pgk_swiglu_interleaved8_bf16(const void* gate_up, void* out, int M, int I, void* stream) {
+    PGK_REQUIRE(M >= 1 && I >= 8 && I % 8 == 0, "swiglu_interleaved8 failed: invalid shape M=%d I=%d", M, I);
+    PGK_CUDA(launch(swiglu_interleaved8_kernel, dim3(blocks_for((size_t)M * I, 256)), dim3(256), 0, ST(stream),
+                    (const uint16_t*)gate_up, (uint16_t*)out, M, I));
     return 0;
 }
 int pgk_argmax_rows(const void* logits, int32_t* out, int32_t* out2, int rows, int n, int dtype, void* stream) {

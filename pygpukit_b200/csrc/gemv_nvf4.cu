@@ -353,6 +353,12 @@ static int launch_nvf4(Nvf4Params p, cudaStream_t st) {
 
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
+// gemm_tc_nvf4.cu: tcgen05 skinny GEMM (exact BF16 dequantisation, weights read once for up to 64 rows)
+bool gemm_nvf4_tc_shape_ok(int M, int K, int N, const void* A, const void* Bd, const void* Bs);
+int gemm_nvf4_tc(const void* A, const void* Bd, const void* Bs, void* C, int M, int K, int N, float alpha, const void* bias,
+                 const void* residual, cudaStream_t st);
+int gemm_fp8_tc_min_m();    // gemm_tc.cu: smallest batch sent to the tensor cores (PGK_TC_MIN_M, default 5)
+
 static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C, int M, int K, int N,
                          float alpha, const void* bias, const void* residual, bool swiglu,
                          cudaStream_t st, const void* gamma = nullptr, float eps = 0.f) {
@@ -371,6 +377,10 @@ static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C,
                         alpha, epi));
         return 0;
     }
+    // decode batch >= 5: the tensor-core GEMM reads the weights once for all rows (PGK_TC=0 keeps the slabs of four rows)
+    static const bool tc_on = !(getenv("PGK_TC") && atoi(getenv("PGK_TC")) == 0);
+    if (tc_on && !swiglu && !gamma && M >= gemm_fp8_tc_min_m() && gemm_nvf4_tc_shape_ok(M, K, N, A, Bd, Bs))
+        return gemm_nvf4_tc(A, Bd, Bs, C, M, K, N, alpha, bias, residual, st);
     if (int rc = ensure_workspace(st)) return rc;
     int max_m = 4;
     while (max_m > 1 && (size_t)max_m * K * 2 + kNvf4Hdr > 200 * 1024) max_m >>= 1;

@@ -178,6 +178,7 @@ class LinearNVF4:
         self.data, self.scale = data, scale
         self.in_features, self.out_features = in_features, out_features
         self.bias, self.alpha = bias, float(alpha)
+        self._norm_scratch: dict[int, GPUArray] = {}
 
     @classmethod
     def from_bf16(cls, weight_kn: GPUArray, bias: GPUArray | None = None) -> "LinearNVF4":
@@ -189,11 +190,22 @@ class LinearNVF4:
         quantize_bf16_to_nvf4(weight_kn, data, scale)
         return cls(data, scale, K, N, bias)
 
+    def uses_tensor_cores(self, M: int) -> bool:
+        """True when a batch of M rows is served by the tcgen05 skinny GEMM (pgk_gemm_nvf4_bf16_tc)."""
+        return (TC_MIN_M <= M <= 64 and self.in_features % 128 == 0 and self.out_features % 128 == 0
+                and os.environ.get("PGK_TC", "1") != "0")
+
     def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,
                 norm=None) -> GPUArray:
         _check_x(x, self.in_features)
         M = x.shape[0]
         y = _out2d(out, M, self.out_features)
+        if norm is not None and self.uses_tensor_cores(M):
+            # the tensor-core GEMM takes plain activations: normalise first (cached scratch, graph-capture safe)
+            sc = self._norm_scratch.get(M)
+            if sc is None:
+                sc = self._norm_scratch[M] = GPUArray((M, self.in_features), bfloat16)
+            x, norm = norm(x, out=sc), None
         if norm is not None:
             api.rmsnorm_gemv_nvf4_bf16(x.device_ptr, norm.weight.device_ptr, float(norm.eps), self.data.device_ptr,
                                        self.scale.device_ptr, y.device_ptr, M, self.in_features, self.out_features,

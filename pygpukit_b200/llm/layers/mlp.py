@@ -96,6 +96,15 @@ class MLP:
                 sc = self._scratch[M] = (GPUArray((M, I), bfloat16), GPUArray((M, I), bfloat16))
             gate = silu(self.gate_proj.forward(x, out=sc[0]), out=sc[0])
             return mul(gate, self.up_proj.forward(x, out=sc[1]), out=out)
+        if self.gate_up_proj is not None and self.gate_up_proj.uses_tensor_cores(M):
+            # batch >= TC_MIN_M: the fused gate/up tensor on the tcgen05 GEMM (weights read once for all rows), then
+            # silu -> mul over the interleaved columns with the layer path's two roundings
+            sc = self._scratch.get(("gu", M))
+            if sc is None:
+                sc = self._scratch[("gu", M)] = GPUArray((M, 2 * I), bfloat16)
+            self.gate_up_proj.forward(x, out=sc, norm=norm)
+            api.swiglu_interleaved8_bf16(sc.device_ptr, out.device_ptr, M, I, _st())
+            return out
         if norm is not None:
             g, e = norm.weight.device_ptr, float(norm.eps)
             if self.gate_up_proj is not None:

@@ -381,3 +381,38 @@ def test_validation_errors_match_reference():
         ops.gemv_fp8_bf16(a, b, s, out=gk.zeros((31,), gk.bfloat16))
     out = gk.zeros((32,), gk.bfloat16)
     assert ops.gemv_fp8_bf16(a, b, s, out=out) is out
+
+
+@pytest.mark.parametrize("K,N", [(1024, 256), (8192, 1024), (3584, 512), (128, 128), (2048, 768)])
+@pytest.mark.parametrize("M", [1, 5, 16, 17, 33, 64])
+def test_gemm_nvf4_tc_vs_oracle(K, N, M):
+    """The tcgen05 NVF4 GEMM called directly (pgk_gemm_nvf4_bf16_tc): nibble x scale is exact in BF16, activations are
+    BF16, products exact, F32 accumulation in TMEM -> the f32-accumulate bar against the oracle's serial-K restatement of
+    gemv_nvf4_bf16_kernel (nvf4_kernels.cu:79-200), with alpha and the residual epilogue; deterministic across calls."""
+    rng = np.random.default_rng(4242 + K + N + M)
+    (data, scale), _ = _nvf4_weights(rng, K, N)
+    A = rand_bf16(rng, (M, K))
+    res = rand_bf16(rng, (M, N))
+    ref = orc.add_inplace_bf16(orc.gemv_nvf4_bf16(A, data, scale, 0.5), res)
+    gA, gD, gS, gR = gk.from_numpy(A), gk.from_numpy(data), gk.from_numpy(scale), gk.from_numpy(res)
+    outs = []
+    for _ in range(2):
+        out = gk.zeros((M, N), gk.bfloat16)
+        api.gemm_nvf4_bf16_tc(gA.device_ptr, gD.device_ptr, gS.device_ptr, out.device_ptr, M, K, N, 0.5, None, gR.device_ptr, None)
+        outs.append(out.to_numpy())
+    assert np.array_equal(outs[0], outs[1])
+    assert f32acc_mismatch(outs[0], ref, TOL) == 0
+    assert rel_err(outs[0], ref) < 1e-2
+
+
+def test_swiglu_interleaved8_matches_oracle():
+    rng = np.random.default_rng(5)
+    M, I = 7, 1024
+    gu = rand_bf16(rng, (M, 2 * I))
+    out = gk.zeros((M, I), gk.bfloat16)
+    api.swiglu_interleaved8_bf16(gk.from_numpy(gu).device_ptr, out.device_ptr, M, I, None)
+    v = gu.reshape(M, I // 8, 2, 8)
+    g, u = v[:, :, 0, :].reshape(M, I), v[:, :, 1, :].reshape(M, I)
+    ref = orc.mul_inplace_bf16(orc.silu_bf16(np.ascontiguousarray(g)), np.ascontiguousarray(u))
+    assert ulp_diff_bf16(out.to_numpy(), ref) <= 1          # __expf on both sides
+    assert np.mean(out.to_numpy() != ref) < 0.01
