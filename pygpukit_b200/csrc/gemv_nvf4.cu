@@ -379,7 +379,8 @@ static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C,
     }
     // decode batch >= 5: the tensor-core GEMM reads the weights once for all rows (PGK_TC=0 keeps the slabs of four rows)
     static const bool tc_on = !(getenv("PGK_TC") && atoi(getenv("PGK_TC")) == 0);
-    if (tc_on && !swiglu && !gamma && M >= gemm_fp8_tc_min_m() && gemm_nvf4_tc_shape_ok(M, K, N, A, Bd, Bs))
+    // measured crossover (profiles/r02_batch_nvf4_*.txt): five rows are still faster as 4 + 1 on the CUDA cores
+    if (tc_on && !swiglu && !gamma && M >= gemm_fp8_tc_min_m() + 1 && gemm_nvf4_tc_shape_ok(M, K, N, A, Bd, Bs))
         return gemm_nvf4_tc(A, Bd, Bs, C, M, K, N, alpha, bias, residual, st);
     if (int rc = ensure_workspace(st)) return rc;
     int max_m = 4;

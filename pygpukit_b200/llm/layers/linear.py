@@ -191,8 +191,9 @@ class LinearNVF4:
         return cls(data, scale, K, N, bias)
 
     def uses_tensor_cores(self, M: int) -> bool:
-        """True when a batch of M rows is served by the tcgen05 skinny GEMM (pgk_gemm_nvf4_bf16_tc)."""
-        return (TC_MIN_M <= M <= 64 and self.in_features % 128 == 0 and self.out_features % 128 == 0
+        """True when a batch of M rows is served by the tcgen05 skinny GEMM (pgk_gemm_nvf4_bf16_tc): one row later
+        than FP8 (measured crossover against 4 + 1 rows on the CUDA cores)."""
+        return (TC_MIN_M + 1 <= M <= 64 and self.in_features % 128 == 0 and self.out_features % 128 == 0
                 and os.environ.get("PGK_TC", "1") != "0")
 
     def forward(self, x: GPUArray, *, out: GPUArray | None = None, residual: GPUArray | None = None,

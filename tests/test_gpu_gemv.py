@@ -9,6 +9,7 @@ import pygpukit_b200 as gk
 from oracle import oracle as orc
 from oracle import refcuda
 from pygpukit_b200 import ops
+from pygpukit_b200._lib import api
 from tests.util import bf16, f32, f32acc_mismatch, rand_bf16, rand_fp8_weights, rel_err, ulp_diff_bf16
 
 pytestmark = pytest.mark.gpu
