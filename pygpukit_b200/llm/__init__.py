@@ -9,7 +9,10 @@ from .decode import DecodeBatch, DecodeM1, DecodeM1Graph, DecodeStrategy
 from .layers import (MLP, Attention, Linear, LinearBF16, LinearFP8, LinearNVF4, MoELayer, Norm, TransformerBlock,
                      apply_rotary_pos_emb_numpy, precompute_freqs_cis)
 from .models import CausalTransformerModel, GPT2Model, LlamaModel, QwenModel
+from .loader import (load_gpt2_from_safetensors, load_llama_from_safetensors, load_model_from_safetensors,
+                     load_qwen3_from_safetensors, save_model_to_safetensors)
 from .random_init import build_random_model
+from .safetensors import SafeTensorsFile, load_safetensors, save_safetensors
 from .sampling import sample_token
 from .tp import TensorParallel, shard_plan, shard_range
 
