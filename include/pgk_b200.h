@@ -104,6 +104,14 @@ int pgk_gemv_fp8_swiglu_bf16(const void* A, const void* Wg_nk, const void* Sg, c
 int pgk_gemm_fp8_bf16_tc(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N,
                          const void* bias, const void* residual, void* stream);
 
+/* The same contract with NO CUDA-core work on the weight stream: raw E4M3 tiles by TMA (cp.async.bulk.tensor, 2-D tensor
+ * map over the [N,K] matrix, 128-byte swizzle) straight into tcgen05.mma.kind::f8f6f4; the activations are split once
+ * (pre-kernel) into two exact E4M3 terms a' = t0 + t1/16 after a per-row power-of-two shift; the 128x128 block scale is
+ * applied per k block when the partial products are promoted from TMEM to FP32 registers.  1 <= M <= 64, K % 128 == 0,
+ * N % 128 == 0, needs cuTensorMapEncodeTiled (driver >= 12.0). */
+int pgk_gemm_fp8_bf16_f8mma(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N,
+                            const void* bias, const void* residual, void* stream);
+
 /* W8A16 GEMM with the reference's [K,N] weight layout: C[M,N] = A[M,K] . dequant(B[K,N]),
  * S = bf16 [ceil(K/128), ceil(N/128)].  replaces pygpukit_w8a16_gemm_sm120
  * (w8a16_gemm.cu:417-456, ops/matmul/w8a16.py:38-119). */

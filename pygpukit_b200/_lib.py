@@ -76,6 +76,7 @@ _SIGS = {
     "pgk_kv_cache_update": [vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, vp],
     "pgk_qk_norm_rope_kv_write": [vp, vp, vp, f32, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp],
     "pgk_gemm_fp8_bf16_tc": [vp, vp, vp, vp, i32, i32, i32, vp, vp, vp],
+    "pgk_gemm_fp8_bf16_f8mma": [vp, vp, vp, vp, i32, i32, i32, vp, vp, vp],
     "pgk_rope_sdpa_decode": [vp, vp, vp, f32, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i32, vp, f32, vp],
     "pgk_sdpa_decode": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, f32, cl, cl, cl, cl, i32, vp],
     "pgk_moe_topk": [vp, vp, vp, i32, i32, i32, i32, vp],

@@ -31,6 +31,7 @@ SOURCES = {
     "gemm_w8a16.cu": [],
     "gemm_tc.cu": [],
     "gemm_tc_nvf4.cu": [],
+    "gemm_tc_f8.cu": [],
     "elementwise.cu": [],
     "attention.cu": [],
     "moe.cu": [],

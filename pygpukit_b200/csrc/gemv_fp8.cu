@@ -35,6 +35,12 @@ bool gemm_fp8_tc_eligible(int M, int K, int N, const void* A, const void* B);
 int gemm_fp8_tc(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N, const void* bias,
                 const void* residual, cudaStream_t st);
 
+// gemm_tc_f8.cu: raw E4M3 tiles by tensor-map TMA into tcgen05.mma.kind::f8f6f4 (PGK_TC_IMPL=2)
+bool gemm_fp8_f8_shape_ok(int M, int K, int N, const void* A, const void* B);
+int gemm_fp8_f8(const void* A, const void* B_nk, const void* S, void* C, int M, int K, int N, const void* bias,
+                const void* residual, cudaStream_t st);
+int gemm_fp8_tc_min_m();
+
 constexpr int kUnroll = 4;
 
 // ---- one-time scan of a weight tensor for the codes the hardware conversion decodes differently (see common.cuh)
@@ -296,6 +302,9 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
                 "rmsnorm_gemv_fp8_bf16 failed: the fused norm needs K %% 32 == 0, K >= 512 and aligned pointers (K=%d)", K);
     // decode batch >= 5 (PGK_TC_MIN_M): the weight-streaming tensor-core GEMM (PGK_TC=0 keeps the slab GEMV for A/B timing)
     static const bool tc_on = !(getenv("PGK_TC") && atoi(getenv("PGK_TC")) == 0);
+    static const int tc_impl = getenv("PGK_TC_IMPL") ? atoi(getenv("PGK_TC_IMPL")) : 1;
+    if (tc_on && clean && !swiglu && !gamma && tc_impl == 2 && M >= gemm_fp8_tc_min_m() && gemm_fp8_f8_shape_ok(M, K, N, A, B0))
+        return gemm_fp8_f8(A, B0, S0, C, M, K, N, bias, residual, st);
     if (tc_on && clean && !swiglu && !gamma && gemm_fp8_tc_eligible(M, K, N, A, B0))
         return gemm_fp8_tc(A, B0, S0, C, M, K, N, bias, residual, st);
     if (!fast) {
