@@ -116,9 +116,14 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* src,
 __device__ __forceinline__ void mbar_expect(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
 }
+// bounded: a wait that cannot complete (a pipeline bug, a lost TMA) traps instead of hanging the GPU
 __device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
-    asm volatile("{\n\t.reg .pred p;\n\tW_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}"
-                 :: "r"(bar), "r"(parity) : "memory");
+    uint32_t ok = 0;
+    for (int spin = 0; !ok; ++spin) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (!ok && spin > (1 << 24)) __trap();
+    }
 }
 __device__ __forceinline__ void umma_commit_u32(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");

@@ -417,3 +417,50 @@ def test_swiglu_interleaved8_matches_oracle():
     ref = orc.mul_inplace_bf16(orc.silu_bf16(np.ascontiguousarray(g)), np.ascontiguousarray(u))
     assert ulp_diff_bf16(out.to_numpy(), ref) <= 1          # __expf on both sides
     assert np.mean(out.to_numpy() != ref) < 0.01
+
+
+@pytest.mark.parametrize("K,N", [(4096, 4096), (1024, 256), (12288, 1024), (128, 128), (2048, 768), (256, 6144)])
+@pytest.mark.parametrize("M", [1, 4, 5, 8, 13, 16, 17, 32, 50, 64])
+def test_gemm_fp8_f8mma_vs_oracle(K, N, M):
+    """pgk_gemm_fp8_bf16_f8mma: raw E4M3 tiles by tensor-map TMA into tcgen05.mma.kind::f8f6f4, activations as two exact
+    E4M3 terms, block scales applied when the partial products are promoted out of TMEM -- against the oracle's FP8 GEMV
+    (fp8_opt.cuh:133-212 restated).  FP32-accumulate class: <= 1 BF16 ulp on every significant element, the f32-accumulate
+    bar on the rest, few flipped roundings; deterministic; bias / residual epilogues."""
+    if K * N * M > 4096 * 4096 * 16 * 2:
+        pytest.skip("oracle time")
+    rng = np.random.default_rng(99 + K + N + M)
+    codes, scale = rand_fp8_weights(rng, N, K)
+    A = rand_bf16(rng, (M, K))
+    ref = orc.gemv_fp8_bf16(A, codes, scale)
+    gA, gB, gS = gk.from_numpy(A), gk.from_numpy(codes), gk.from_numpy(scale)
+    outs = []
+    for _ in range(2):
+        out = gk.zeros((M, N), gk.bfloat16)
+        api.gemm_fp8_bf16_f8mma(gA.device_ptr, gB.device_ptr, gS.device_ptr, out.device_ptr, M, K, N, None, None, None)
+        outs.append(out.to_numpy())
+    assert np.array_equal(outs[0], outs[1])
+    out = outs[0]
+    assert f32acc_mismatch(out, ref, TOL) == 0
+    big = np.abs(f32(ref)) > np.abs(f32(ref)).max() / 64
+    assert ulp_diff_bf16(out[big], ref[big]) <= 1
+    assert np.mean(out != ref) < 0.03
+    # residual epilogue: bf16(acc) + residual with one rounding
+    res = rand_bf16(rng, (M, N))
+    out2 = gk.zeros((M, N), gk.bfloat16)
+    api.gemm_fp8_bf16_f8mma(gA.device_ptr, gB.device_ptr, gS.device_ptr, out2.device_ptr, M, K, N, None, gk.from_numpy(res).device_ptr, None)
+    assert np.array_equal(out2.to_numpy(), orc.add_inplace_bf16(out, res))
+
+
+def test_gemm_fp8_f8mma_wide_dynamic_range():
+    """Activation rows whose elements span 20 binades (the two-term split keeps elements within 2^-10 of the row maximum
+    exact and bounds the absolute error of the rest by 2^-18 of the maximum)."""
+    rng = np.random.default_rng(7)
+    K, N, M = 2048, 512, 6
+    codes, scale = rand_fp8_weights(rng, N, K)
+    a = rng.standard_normal((M, K)) * np.exp2(rng.integers(-18, 2, (M, K)))
+    A = bf16(a.astype(np.float32))
+    ref = orc.gemv_fp8_bf16(A, codes, scale)
+    out = gk.zeros((M, N), gk.bfloat16)
+    api.gemm_fp8_bf16_f8mma(gk.from_numpy(A).device_ptr, gk.from_numpy(codes).device_ptr, gk.from_numpy(scale).device_ptr,
+                            out.device_ptr, M, K, N, None, None, None)
+    assert f32acc_mismatch(out.to_numpy(), ref, TOL) == 0
