@@ -410,8 +410,8 @@ def test_swiglu_interleaved8_matches_oracle():
     rng = np.random.default_rng(5)
     M, I = 7, 1024
     gu = rand_bf16(rng, (M, 2 * I))
-    out = gk.zeros((M, I), gk.bfloat16)
-    api.swiglu_interleaved8_bf16(gk.from_numpy(gu).device_ptr, out.device_ptr, M, I, None)
+    out, ggu = gk.zeros((M, I), gk.bfloat16), gk.from_numpy(gu)
+    api.swiglu_interleaved8_bf16(ggu.device_ptr, out.device_ptr, M, I, None)
     v = gu.reshape(M, I // 8, 2, 8)
     g, u = v[:, :, 0, :].reshape(M, I), v[:, :, 1, :].reshape(M, I)
     ref = orc.mul_inplace_bf16(orc.silu_bf16(np.ascontiguousarray(g)), np.ascontiguousarray(u))
@@ -446,8 +446,8 @@ def test_gemm_fp8_f8mma_vs_oracle(K, N, M):
     assert np.mean(out != ref) < 0.03
     # residual epilogue: bf16(acc) + residual with one rounding
     res = rand_bf16(rng, (M, N))
-    out2 = gk.zeros((M, N), gk.bfloat16)
-    api.gemm_fp8_bf16_f8mma(gA.device_ptr, gB.device_ptr, gS.device_ptr, out2.device_ptr, M, K, N, None, gk.from_numpy(res).device_ptr, None)
+    out2, gR = gk.zeros((M, N), gk.bfloat16), gk.from_numpy(res)
+    api.gemm_fp8_bf16_f8mma(gA.device_ptr, gB.device_ptr, gS.device_ptr, out2.device_ptr, M, K, N, None, gR.device_ptr, None)
     assert np.array_equal(out2.to_numpy(), orc.add_inplace_bf16(out, res))
 
 
@@ -460,7 +460,6 @@ def test_gemm_fp8_f8mma_wide_dynamic_range():
     a = rng.standard_normal((M, K)) * np.exp2(rng.integers(-18, 2, (M, K)))
     A = bf16(a.astype(np.float32))
     ref = orc.gemv_fp8_bf16(A, codes, scale)
-    out = gk.zeros((M, N), gk.bfloat16)
-    api.gemm_fp8_bf16_f8mma(gk.from_numpy(A).device_ptr, gk.from_numpy(codes).device_ptr, gk.from_numpy(scale).device_ptr,
-                            out.device_ptr, M, K, N, None, None, None)
+    out, gA, gB, gS = gk.zeros((M, N), gk.bfloat16), gk.from_numpy(A), gk.from_numpy(codes), gk.from_numpy(scale)
+    api.gemm_fp8_bf16_f8mma(gA.device_ptr, gB.device_ptr, gS.device_ptr, out.device_ptr, M, K, N, None, None, None)
     assert f32acc_mismatch(out.to_numpy(), ref, TOL) == 0
