@@ -12,6 +12,7 @@ import numpy as np  # noqa: E402
 import pygpukit_b200 as gk  # noqa: E402
 from pygpukit_b200._lib import api  # noqa: E402
 from pygpukit_b200.core.stream import CudaEvent, Stream, event_elapsed_ms, use_stream  # noqa: E402
+from pygpukit_b200.llm.random_init import normal_bf16, quantize_fp8  # noqa: E402
 
 L = int(sys.argv[1]) if len(sys.argv) > 1 else 12
 api.set_pdl(1)
@@ -22,13 +23,11 @@ print(f"PGK_TC={os.environ.get('PGK_TC', '1')}  L={L} weight sets per shape")
 for label, K, N in shapes:
     Ws, Ss = [], []
     for i in range(L):
-        w = gk.empty((N, K), gk.uint8)
-        api.fill_normal_bf16(w.device_ptr, N * K // 2, 100 + i, 1.0, None)      # random bytes (any code is a valid weight)
-        # scrub NaN codes 0x7f / 0xff is unnecessary for timing
-        Ws.append(w)
-        s = gk.empty((N // 128, K // 128), gk.bfloat16)
-        api.fill_normal_bf16(s.device_ptr, s.size, 900 + i, 0.01, None)
-        Ss.append(s)
+        # real block-quantised weights (random bytes would hold the codes 0x7F / 0xFF, which the entry point serves with the
+        # exact table kernel instead of the streaming ones)
+        lin = quantize_fp8(normal_bf16((N, K), 100 + i, 0.02))
+        Ws.append(lin.weight_fp8)
+        Ss.append(lin.scale_inv)
     for M in (1, 2, 4, 5, 8, 12, 16, 32, 64):
         a = gk.empty((M, K), gk.bfloat16)
         api.fill_normal_bf16(a.device_ptr, a.size, 7, 1.0, None)
