@@ -129,17 +129,25 @@ __device__ __forceinline__ void umma_commit_u32(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
 
+// Several CTAs per SM (3 up to 16 batch rows, else 2): a CTA's fixed costs -- TMEM allocation, first TMA round trip, the
+// split-K hand-over -- are as long as its stream of ~10 k blocks, so they must overlap another CTA's streaming.  Shared
+// memory (4 / 3 stages) and TMEM (4 / 2 accumulator buffers: at most 512 columns per SM in total) are sized for that.
+__host__ __device__ constexpr int f8_occ(int nb) { return nb <= 32 ? 3 : 2; }
+__host__ __device__ constexpr int f8_stages(int nb) { return nb <= 64 ? 4 : 3; }
+__host__ __device__ constexpr int f8_nbuf(int nb) { return nb <= 64 ? 4 : 2; }
+
 template <int NB>      // NB = 2 * Mpad: MMA N (TMEM columns per accumulator buffer)
-__global__ void __launch_bounds__(kF8Threads, 1)
+__global__ void __launch_bounds__(kF8Threads, f8_occ(NB))
 gemm_fp8_f8mma_kernel(const __grid_constant__ CUtensorMap wmap, F8Params p) {
     constexpr int MP = NB / 2;
     constexpr uint32_t A_BYTES = kTcRows * kF8BK;               // 16 KB of E4M3 codes
     constexpr uint32_t B_BYTES = NB * 128;                      // activation terms
     constexpr uint32_t STAGE = A_BYTES + ((B_BYTES + 1023) & ~1023u);
-    constexpr int S = (200 * 1024) / STAGE > 8 ? 8 : (200 * 1024) / STAGE;
-    constexpr uint32_t TMEM_COLS = 2 * NB < 32 ? 32 : 2 * NB;
+    constexpr int S = f8_stages(NB);
+    constexpr int NBUF = f8_nbuf(NB);
+    constexpr uint32_t TMEM_COLS = NBUF * NB < 32 ? 32 : NBUF * NB;
     extern __shared__ __align__(1024) unsigned char smem[];
-    __shared__ __align__(8) uint64_t full_bar[8], empty_bar[8], dfull_bar[2], dempty_bar[2];
+    __shared__ __align__(8) uint64_t full_bar[8], empty_bar[8], dfull_bar[8], dempty_bar[8];
     __shared__ uint32_t tmem_base_s;
     __shared__ unsigned s_ticket;
     __shared__ float sc_s[kF8MaxKb];
@@ -157,7 +165,7 @@ gemm_fp8_f8mma_kernel(const __grid_constant__ CUtensorMap wmap, F8Params p) {
     if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
     if (tid == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int t = 0; t < 2; ++t) { mbar_init(&dfull_bar[t], 1); mbar_init(&dempty_bar[t], 4); }
+        for (int t = 0; t < NBUF; ++t) { mbar_init(&dfull_bar[t], 1); mbar_init(&dempty_bar[t], 4); }
         mbar_fence_init();
         asm volatile("prefetch.tensormap [%0];" :: "l"(&wmap) : "memory");
     }
@@ -191,8 +199,8 @@ gemm_fp8_f8mma_kernel(const __grid_constant__ CUtensorMap wmap, F8Params p) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_e4m3(NB);
             for (int i = 0; i < nkb; ++i) {
-                const int s = i % S, t = i & 1;
-                mbar_wait_u32(smem_u32(&dempty_bar[t]), (uint32_t)(((i >> 1) & 1) ^ 1));     // promotion drained this buffer
+                const int s = i % S, t = i % NBUF;
+                mbar_wait_u32(smem_u32(&dempty_bar[t]), (uint32_t)(((i / NBUF) & 1) ^ 1));   // promotion drained this buffer
                 mbar_wait_u32(smem_u32(&full_bar[s]), (uint32_t)((i / S) & 1));              // weights + terms landed
                 tc_fence_after();
                 const uint32_t a_addr = smem_base + (uint32_t)s * STAGE, b_addr = a_addr + A_BYTES;
@@ -211,8 +219,8 @@ gemm_fp8_f8mma_kernel(const __grid_constant__ CUtensorMap wmap, F8Params p) {
 #pragma unroll
         for (int m = 0; m < MP; ++m) acc[m] = 0.f;
         for (int i = 0; i < nkb; ++i) {
-            const int t = i & 1;
-            mbar_wait_u32(smem_u32(&dfull_bar[t]), (uint32_t)((i >> 1) & 1));
+            const int t = i % NBUF;
+            mbar_wait_u32(smem_u32(&dfull_bar[t]), (uint32_t)((i / NBUF) & 1));
             tc_fence_after();
             const float sc = sc_s[i];
             const uint32_t base = tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)t * NB;
@@ -316,7 +324,7 @@ static const size_t kF8ImgBytes = (size_t)32768 * 128;      // K <= 32768, 2 * M
 template <int NB>
 static int launch_f8(const CUtensorMap& map, F8Params p, cudaStream_t st) {
     constexpr uint32_t STAGE = kTcRows * kF8BK + ((NB * 128 + 1023) & ~1023u);
-    constexpr int S = (200 * 1024) / STAGE > 8 ? 8 : (200 * 1024) / STAGE;
+    constexpr int S = f8_stages(NB);
     constexpr size_t kSmem = (size_t)S * STAGE + 1024;
     static bool attr_set = false;
     if (!attr_set) {
@@ -371,17 +379,12 @@ int gemm_fp8_f8(const void* A, const void* B_nk, const void* Sc, void* C, int M,
     const int mpad = M <= 8 ? 8 : (M <= 16 ? 16 : (M <= 32 ? 32 : 64));
     PGK_CUDA(launch(fp8_act_terms_kernel, dim3(mpad), dim3(256), 0, st, (const uint16_t*)A, g_f8_img, g_f8_unshift, M, K, mpad));
     const int tiles = N / kTcRows, nkb = K / kF8BK;
-    const int sms = sm_count();
-    int splits = 1;
-    double best = -1.0;
-    for (int s = 1; s <= 16 && s <= nkb; ++s) {
-        const long ctas = (long)tiles * s;
-        const long waves = (ctas + sms - 1) / sms;
-        const int per = (nkb + s - 1) / s;
-        const double t = (double)waves * (per + 3.0);      // whole waves; ~3 blocks of fixed cost per CTA
-        const double score = 1.0 / t - 1e-6 * s;
-        if (score > best) { best = score; splits = s; }
-    }
+    // split-K so that one wave of resident CTAs (f8_occ per SM) covers the problem, every split keeping >= 2 k blocks
+    const int slots = sm_count() * f8_occ(2 * mpad);
+    int splits = slots / tiles;                            // floor: never a partial second wave
+    if (splits > nkb / 2) splits = nkb / 2;
+    if (splits > 16) splits = 16;
+    if (splits < 1) splits = 1;
     while (splits > 1 && (size_t)tiles * splits * mpad * kTcRows * sizeof(float) > kF8WsBytes) --splits;
     F8Params p = {};
     p.img = g_f8_img; p.unshift = g_f8_unshift; p.S = (const uint16_t*)Sc; p.C = (uint16_t*)C;
