@@ -193,8 +193,20 @@ def _fused_qkv(mk: _Maker, L: int, q_rows: int, kv_rows: int, H: int, n_kv: int 
     qp, kp = q_rows // div, kv_rows // div
     if n_kv and div > n_kv:
         # more ranks than KV heads: div / n_kv ranks replicate one whole KV head (same seed -> same weights)
-        if n != 1 or div % n_kv:
+        if div % n_kv:
             raise ValueError(f"cannot place {n_kv} KV heads on {div} shards")
+        if n != 1:
+            # the one-process model the ranks jointly hold: every rank's query piece, each KV head ONCE (piece j of the
+            # k / v seeds is KV head j, the one ranks j * rep .. j * rep + rep - 1 replicate)
+            kph = kv_rows // n_kv
+            if mk.fmt == "nvf4":
+                cols = [normal_bf16((H, qp), _seed(mk.base, L, "q", p), mk.std).to_numpy() for p in ids]
+                cols += [normal_bf16((H, kph), _seed(mk.base, L, t, j), mk.std).to_numpy() for t in ("k", "v") for j in range(n_kv)]
+                return quantize_nvf4(from_numpy(np.ascontiguousarray(np.concatenate(cols, axis=1))))
+            rows = [normal_bf16((qp, H), _seed(mk.base, L, "q", p), mk.std).to_numpy() for p in ids]
+            rows += [normal_bf16((kph, H), _seed(mk.base, L, t, j), mk.std).to_numpy() for t in ("k", "v") for j in range(n_kv)]
+            m = from_numpy(np.ascontiguousarray(np.concatenate(rows, axis=0)))
+            return quantize_fp8(m) if mk.fmt == "fp8" else LinearBF16(m)
         rep, kp, p = div // n_kv, kv_rows // n_kv, ids[0]
         width = qp + 2 * kp
         if mk.fmt == "nvf4":
