@@ -100,5 +100,6 @@ def test_tp_greedy_tokens_match_single_gpu(world, case):
     assert d["ok"], d
     # MoE layers exchange un-combined rows (exact), dense layers differ by summation order only: a real model keeps
     # most of the 128 tokens before the first BF16-resolution tie
-    if not d.get("router_tie_before_divergence"):
+    # an EXACT tie of the two best logits (margin 0.0) may fall anywhere; otherwise a sane model keeps a good prefix
+    if not d.get("router_tie_before_divergence") and d.get("margin_at_divergence", 1.0) != 0.0:
         assert d["identical_prefix"] >= min(14, d["steps"]), d
