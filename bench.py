@@ -13,7 +13,8 @@ activations, batch 1, 8k context.  It fits ONE B200 (36 GB of weights), so the s
 N (tensor parallel, strong scaling) and the driver's 1 -> 8 GPU curve measures the claim itself.  The other
 single-GPU configurations of BASELINE.json ride in the `configs` object of the same line (each with tokens/s and
 the step's HBM roofline fraction): Llama-3-8B FP8 @4k (north_star's >= 70 % target), Qwen3-8B w8a16 @4k
-(configs[1]), Llama-3-8B FP8 @32k at batch 1 / 8 / 64 sequences (configs[2]), Qwen3-30B-A3B NVF4 (configs[3]).
+(configs[1]), Llama-3-8B FP8 @32k at 1 / 8 sequences and @16k at 64 sequences (configs[2]; 64 x 32k of KV cache is
+275 GB and does not fit one B200), Qwen3-30B-A3B NVF4 (configs[3]).
 
   value   device-timed tokens/s: K replays of the one-graph step with every input resident in HBM
           (CUDA events on the launching stream, barrier + sync on both sides, max over ranks).

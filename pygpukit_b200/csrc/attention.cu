@@ -20,6 +20,11 @@
 //     row, two positions per warp iteration, two iterations in flight).
 #include "common.cuh"
 #include "../../include/pgk_b200.h"
+#include <cuda.h>
+#include <cstdlib>
+#include <mutex>
+#include <utility>
+#include <vector>
 
 namespace pgk {
 
@@ -733,6 +738,433 @@ rope_sdpa_decode_kernel(RopeSdpaParams p) {
     if (threadIdx.x == 0) p.counters[tile_id] = 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Round 2: the same fused bracket with the score and P.V products on the tensor cores (mma.sync m16n8k16, SASS HMMA)
+// and the K/V tiles fetched by tensor-map TMA (cp.async.bulk.tensor.4d, SWIZZLE_128B, SASS UTMALDG) so that ldmatrix
+// reads them without bank conflicts.  Decode attention is HBM / latency bound; what the CUDA-core loop above spends
+// per 64 positions (unpacking V, 15 shuffles of the score reduce-scatter, 450 issue slots per warp) was a third of the
+// launch at 4k and the whole of it at 32k.  Here a warp owns 16 positions of a 64-position tile:
+//     S[8 heads (+8 zero rows), 16 pos]  = Q[16, 128] . K^T      16 HMMA, B fragments by ldmatrix from the swizzled tile
+//     online softmax on the 4 scores a thread holds (row = lane / 4), quad shuffles only
+//     O[16, 128] += P[16, 16] . V[16, 128]                       16 HMMA, V fragments by ldmatrix.trans
+// The probabilities go to the tensor cores as TWO bf16 terms, p = hi + lo, hi in rows 0..7 and lo in rows 8..15 of the
+// A fragment (the rows the <= 8 query heads leave empty), so one MMA accumulates both and O = O[0..7] + O[8..15] carries
+// 16 bits of p: the products q.k are exact and p.v is as accurate as the f32 loop it replaces.
+// One CTA = 4 consumer warps + 1 TMA producer warp, 3 stages x 32 KB, 2 CTAs per SM; up to 8 query heads per CTA, so a
+// GQA group of 8 (Llama-3-70B, Qwen3-30B-A3B) reads its K/V once instead of twice.
+constexpr int kMW = 4;                          // consumer warps
+constexpr int kMTile = 64;                      // KV positions per stage
+constexpr int kMStages = 3;
+constexpr int kMRT = 8;                         // query heads per CTA
+constexpr int kMThreads = (kMW + 1) * 32;
+constexpr uint32_t kMBox = 64 * 128;            // one TMA box: 64 positions x 64 dims (128 bytes, the swizzle span)
+constexpr uint32_t kMStageB = 4 * kMBox;        // K dims 0..63 | K dims 64..127 | V dims 0..63 | V dims 64..127
+constexpr int kMRec = 130;                      // partial record: o[128], m, l
+
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t smem_dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+                 :: "r"(smem_dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(bar)) : "memory");
+}
+// a wait that cannot hang the device: a protocol bug traps instead of spinning forever
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+// [RMSNorm] + NeoX rotation of one 128-wide head row already in registers (x[i] = row[lane + 32 i]); same arithmetic
+// and rounding points as norm_rope_head128 above
+__device__ __forceinline__ void norm_rope_regs(float (&x)[4], bool use_gamma, const float (&g)[4], float eps, const float (&c)[2],
+                                               const float (&s)[2], int lane, uint16_t* __restrict__ dst_s, uint16_t* __restrict__ dst_g) {
+    if (use_gamma) {
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            float part = warp_sum(fmaf(x[w], x[w], 0.f));
+            if (lane == w) tot = part;
+        }
+        const float inv = rsqrtf(warp_sum(tot) / 128.f + eps);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = round_bf16(x[i] * inv * g[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const float x0 = x[i], x1 = x[i + 2];
+        const uint16_t y0 = f32_to_bf16_bits(x0 * c[i] - x1 * s[i]), y1 = f32_to_bf16_bits(x1 * c[i] + x0 * s[i]);
+        dst_s[lane + 32 * i] = y0; dst_s[lane + 32 * i + 64] = y1;
+        if (dst_g) { dst_g[lane + 32 * i] = y0; dst_g[lane + 32 * i + 64] = y1; }
+    }
+}
+
+__global__ void __launch_bounds__(kMThreads, 2)
+rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant__ CUtensorMap vmap, RopeSdpaParams p) {
+    constexpr int HD = 128, RT = kMRT, REC = kMRec;
+    extern __shared__ unsigned char dyn_raw[];
+    __shared__ __align__(16) uint16_t q_s[RT][HD];
+    __shared__ __align__(16) uint16_t new_s[2][HD];           // new K row, new V row
+    __shared__ __align__(8) uint64_t full_bar[kMStages];
+    __shared__ __align__(8) uint64_t empty_bar[kMStages];
+    __shared__ unsigned s_ticket;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int G = p.hq / p.n_kv;
+    const int row_tiles = (G + RT - 1) / RT;
+    const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z % p.n_kv, seq = blockIdx.z / p.n_kv;
+    const int rows = min(RT, G - rt * RT);                    // query heads this CTA serves
+    p.qkv += (size_t)seq * p.qkv_stride;
+    p.out += (size_t)seq * p.out_stride;
+    p.kc += (size_t)seq * p.cache_stride;
+    p.vc += (size_t)seq * p.cache_stride;
+    const uint32_t tiles_s = (smem_u32(dyn_raw) + 1023u) & ~1023u;      // the swizzle pattern repeats every 1024 bytes
+    unsigned char* tiles_g = dyn_raw + (tiles_s - smem_u32(dyn_raw));
+
+    // ---- independent of the previous kernel: position, barriers, the first K/V tiles, tables
+    const int pos = p.pos_buf ? p.pos_buf[seq] : p.pos;
+    const int ctx = min(p.ctx_buf ? p.ctx_buf[seq] : p.context_len, p.max_seq);
+    int chunk = (ctx + p.splits - 1) / p.splits;
+    chunk = (chunk + 15) & ~15;
+    const int c0 = split * chunk, c1 = min(ctx, c0 + chunk);
+    const int ntiles = (c1 > c0) ? (c1 - c0 + kMTile - 1) / kMTile : 0;
+    const bool has_new = pos >= c0 && pos < c1;
+    const bool writer = rt == 0 && pos < p.max_seq && (has_new || (pos >= ctx && split == 0));
+    auto issue_tile = [&](int t) {
+        const int st = t % kMStages;
+        const int t0 = c0 + t * kMTile;
+        const uint32_t dst = tiles_s + (uint32_t)st * kMStageB;
+        mbar_arrive_expect_tx(&full_bar[st], kMStageB);        // out-of-range rows are zero-filled and still counted
+        tma_load_4d(dst, &kmap, 0, t0, kvh, seq, &full_bar[st]);
+        tma_load_4d(dst + kMBox, &kmap, 64, t0, kvh, seq, &full_bar[st]);
+        tma_load_4d(dst + 2 * kMBox, &vmap, 0, t0, kvh, seq, &full_bar[st]);
+        tma_load_4d(dst + 3 * kMBox, &vmap, 64, t0, kvh, seq, &full_bar[st]);
+    };
+    if (threadIdx.x == kMW * 32) {
+#pragma unroll
+        for (int i = 0; i < kMStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], kMW); }
+        mbar_fence_init();
+        for (int t = 0; t < min(ntiles, kMStages); ++t) issue_tile(t);
+    }
+    float rc[2], rs[2], rg[4] = {1.f, 1.f, 1.f, 1.f};
+    const uint16_t* my_gamma = (warp < kMW) ? p.q_gamma : p.k_gamma;
+    {
+        const float* cs = p.cos_t + (size_t)pos * HD;
+        const float* sn = p.sin_t + (size_t)pos * HD;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) { rc[i] = __ldg(cs + lane + 32 * i); rs[i] = __ldg(sn + lane + 32 * i); }
+        if (my_gamma) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) rg[i] = bf16_bits_to_f32(__ldg(my_gamma + lane + 32 * i));
+        }
+    }
+    griddep_wait();
+    griddep_launch();
+
+    // ---- the new token: consumer warp w rotates query heads w and w + 4, the producer warp the new K / V rows
+    if (warp < kMW) {
+        float x[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int h = warp + j * kMW;
+            const uint16_t* row = p.qkv + (size_t)(kvh * G + rt * RT + min(h, rows - 1)) * HD;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[j][i] = bf16_bits_to_f32(row[lane + 32 * i]);
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int h = warp + j * kMW;
+            if (h < rows) norm_rope_regs(x[j], my_gamma != nullptr, rg, p.eps, rc, rs, lane, q_s[h], nullptr);
+            else for (int d = lane; d < HD; d += 32) q_s[h][d] = 0;
+        }
+    } else if (has_new || writer) {
+        float x[4];
+        const uint16_t* krow = p.qkv + (size_t)(p.hq + kvh) * HD;
+        const uint16_t* vrow = p.qkv + (size_t)(p.hq + p.n_kv + kvh) * HD;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = bf16_bits_to_f32(krow[lane + 32 * i]);
+        uint16_t vv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) vv[i] = vrow[lane + 32 * i];
+        uint16_t* kdst = writer ? p.kc + ((size_t)kvh * p.max_seq + pos) * HD : nullptr;
+        uint16_t* vdst = writer ? p.vc + ((size_t)kvh * p.max_seq + pos) * HD : nullptr;
+        norm_rope_regs(x, my_gamma != nullptr, rg, p.eps, rc, rs, lane, new_s[0], kdst);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { new_s[1][lane + 32 * i] = vv[i]; if (vdst) vdst[lane + 32 * i] = vv[i]; }
+    }
+    __syncthreads();   // q_s / new_s visible; also orders the mbarrier init before every wait
+
+    float o[16][4];                                            // [dim tile of 8][c0 c1: hi rows | c2 c3: lo rows]
+    float m_run = kNegBig, l_run = 0.f;
+    if (warp == kMW) {
+        // ---- producer: refill a stage as soon as the four consumer warps have released it
+        if (lane == 0) {
+            for (int t = kMStages; t < ntiles; ++t) {
+                mbar_wait_bounded(&empty_bar[t % kMStages], (uint32_t)((t / kMStages - 1) & 1));
+                issue_tile(t);
+            }
+        }
+    } else {
+        const int qrow = lane >> 2, kk = (lane & 3) * 2;
+        uint32_t qa[8][2];
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+            qa[ks][0] = *reinterpret_cast<const uint32_t*>(&q_s[qrow][ks * 16 + kk]);
+            qa[ks][1] = *reinterpret_cast<const uint32_t*>(&q_s[qrow][ks * 16 + kk + 8]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o[nt][e] = 0.f;
+        // ldmatrix row addresses of this lane (matrix j = lane / 8, row i = lane % 8), relative to the tile
+        const int lj = lane >> 3, lr8 = lane & 7;
+        const int k_row = warp * 16 + (lj >> 1) * 8 + lr8;      // K: matrices (n-tile 0, k lo) (n-tile 0, k hi) (n-tile 1, k lo) (n-tile 1, k hi)
+        const int v_row = warp * 16 + (lj & 1) * 8 + lr8;       // V: (pos 0..7, dims) (pos 8..15, dims) (pos 0..7, dims + 8) (pos 8..15, dims + 8)
+        const uint32_t k_off = (uint32_t)k_row * 128u, v_off = 2 * kMBox + (uint32_t)v_row * 128u;
+        const uint32_t k_sw = (uint32_t)(k_row & 7), v_sw = (uint32_t)(v_row & 7);
+
+        for (int t = 0; t < ntiles; ++t) {
+            const int st = t % kMStages;
+            const int t0 = c0 + t * kMTile;
+            const int wbase = t0 + warp * 16;
+            mbar_wait_bounded(&full_bar[st], (uint32_t)((t / kMStages) & 1));
+            const uint32_t tile = tiles_s + (uint32_t)st * kMStageB;
+            unsigned char* tile_g = tiles_g + (size_t)st * kMStageB;
+            bool wrote = false;
+            if (wbase + 16 > ctx && wbase < c1) {               // warp-uniform: V rows past the context may hold anything
+                for (int i = lane; i < 16 * 16; i += 32) {
+                    const int r = warp * 16 + (i >> 4), ch = i & 15;
+                    if (t0 + r >= ctx)
+                        *reinterpret_cast<uint4*>(tile_g + 2 * kMBox + (ch >> 3) * kMBox + r * 128 + (ch & 7) * 16) = make_uint4(0, 0, 0, 0);
+                }
+                wrote = true;
+            }
+            if (has_new && pos >= wbase && pos < wbase + 16) {  // warp-uniform: patch the new row into the staged tile
+                const int r = pos - t0, which = lane >> 4, ch = lane & 15;
+                *reinterpret_cast<uint4*>(tile_g + which * 2 * kMBox + (ch >> 3) * kMBox + r * 128 + (((ch & 7) ^ (r & 7)) * 16)) =
+                    reinterpret_cast<const uint4*>(new_s[which])[ch];
+                wrote = true;
+            }
+            if (wrote) __syncwarp();
+            if (wbase < c1) {
+                // ---- scores of 16 positions x 8 heads
+                float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    const uint32_t ch = (uint32_t)(ks * 2 + (lj & 1));
+                    uint32_t b[4];
+                    ldsm_x4(tile + (ch >> 3) * kMBox + k_off + (((ch & 7) ^ k_sw) << 4), b);
+                    mma_bf16_16816(s0, qa[ks][0], 0u, qa[ks][1], 0u, b[0], b[1]);
+                    mma_bf16_16816(s1, qa[ks][0], 0u, qa[ks][1], 0u, b[2], b[3]);
+                }
+                const int pj = wbase + kk;                       // positions pj, pj + 1 (s0) and pj + 8, pj + 9 (s1)
+                float sc[4];
+                sc[0] = pj < c1 ? s0[0] * p.scale_log2 : kNegBig;
+                sc[1] = pj + 1 < c1 ? s0[1] * p.scale_log2 : kNegBig;
+                sc[2] = pj + 8 < c1 ? s1[0] * p.scale_log2 : kNegBig;
+                sc[3] = pj + 9 < c1 ? s1[1] * p.scale_log2 : kNegBig;
+                float mx = fmaxf(fmaxf(sc[0], sc[1]), fmaxf(sc[2], sc[3]));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+                mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+                const float mn = fmaxf(m_run, mx);
+                const float corr = exp2f(m_run - mn);
+                float pr[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) pr[j] = (sc[j] > 0.5f * kNegBig) ? exp2f(sc[j] - mn) : 0.f;
+                l_run = l_run * corr + ((pr[0] + pr[1]) + (pr[2] + pr[3]));
+                m_run = mn;
+                if (__any_sync(0xffffffffu, corr != 1.f)) {
+#pragma unroll
+                    for (int nt = 0; nt < 16; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) o[nt][e] *= corr;
+                }
+                // p = hi + lo as two bf16 terms: hi in rows 0..7, lo in rows 8..15 of the A fragment
+                float lo[4];
+                uint32_t hb[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { hb[j] = f32_to_bf16_bits(pr[j]); lo[j] = pr[j] - bf16_bits_to_f32(hb[j]); }
+                const uint32_t a0 = hb[0] | (hb[1] << 16), a2 = hb[2] | (hb[3] << 16);
+                const uint32_t a1 = pack_bf16x2(lo[0], lo[1]), a3 = pack_bf16x2(lo[2], lo[3]);
+                // ---- O += P . V
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const uint32_t ch = (uint32_t)(q * 2 + (lj >> 1));
+                    uint32_t b[4];
+                    ldsm_x4_t(tile + (ch >> 3) * kMBox + v_off + (((ch & 7) ^ v_sw) << 4), b);
+                    mma_bf16_16816(o[2 * q], a0, a1, a2, a3, b[0], b[1]);
+                    mma_bf16_16816(o[2 * q + 1], a0, a1, a2, a3, b[2], b[3]);
+                }
+            }
+            if (t + kMStages < ntiles) {                        // hand the stage back to the producer
+                if (wrote) fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[st]);
+            }
+        }
+        l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+        l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    }
+    __syncthreads();                                           // every stage is consumed: its memory is free for the merge
+    float (*sm_part)[RT][REC] = reinterpret_cast<float (*)[RT][REC]>(tiles_g);
+    if (warp < kMW) {
+        const int qrow = lane >> 2, kk = (lane & 3) * 2;
+#pragma unroll
+        for (int nt = 0; nt < 16; ++nt)
+            *reinterpret_cast<float2*>(&sm_part[warp][qrow][nt * 8 + kk]) = make_float2(o[nt][0] + o[nt][2], o[nt][1] + o[nt][3]);
+        if ((lane & 3) == 0) { sm_part[warp][qrow][HD] = m_run; sm_part[warp][qrow][HD + 1] = l_run; }
+    }
+    __syncthreads();
+    const size_t tile_id = ((size_t)seq * p.n_kv + kvh) * row_tiles + rt;
+    float* rec = p.ws + (tile_id * p.splits + split) * RT * REC;
+    for (int idx = threadIdx.x; idx < rows * HD; idx += kMThreads) {
+        const int r = idx / HD, d = idx % HD;
+        float mn = kNegBig;
+#pragma unroll
+        for (int w = 0; w < kMW; ++w) mn = fmaxf(mn, sm_part[w][r][HD]);
+        float ov = 0.f, lv = 0.f;
+#pragma unroll
+        for (int w = 0; w < kMW; ++w) {
+            const float c = exp2f(sm_part[w][r][HD] - mn);
+            ov = fmaf(sm_part[w][r][d], c, ov);
+            lv = fmaf(sm_part[w][r][HD + 1], c, lv);
+        }
+        if (p.splits == 1) {
+            p.out[(size_t)(kvh * G + rt * RT + r) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
+        } else {
+            __stcg(rec + r * REC + d, ov);
+            if (d == 0) { __stcg(rec + r * REC + HD, mn); __stcg(rec + r * REC + HD + 1, lv); }
+        }
+    }
+    if (p.splits == 1) return;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_ticket = atomicAdd(p.counters + tile_id, 1u);
+        __threadfence();
+    }
+    __syncthreads();
+    if (s_ticket != (unsigned)(p.splits - 1)) return;
+    // last CTA of the (kv head, row tile): fold the partials in split order (deterministic)
+    const float* base = p.ws + tile_id * p.splits * RT * REC;
+    float* s_m = &sm_part[0][0][0];                            // [RT][kAttnMaxSplits] (the merge buffer is free again)
+    float* s_l = s_m + RT * kAttnMaxSplits;
+    for (int idx = threadIdx.x; idx < rows * p.splits; idx += kMThreads) {
+        const int r = idx / p.splits, sp = idx % p.splits;
+        const float* rr = base + ((size_t)sp * RT + r) * REC;
+        s_m[r * kAttnMaxSplits + sp] = __ldcg(rr + HD);
+        s_l[r * kAttnMaxSplits + sp] = __ldcg(rr + HD + 1);
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < rows * HD; idx += kMThreads) {
+        const int r = idx / HD, d = idx % HD;
+        const float* sm_r = s_m + r * kAttnMaxSplits;
+        const float* sl_r = s_l + r * kAttnMaxSplits;
+        float mn = kNegBig;
+        for (int sp = 0; sp < p.splits; ++sp) mn = fmaxf(mn, sm_r[sp]);
+        float ov = 0.f, lv = 0.f;
+        int sp = 0;
+        for (; sp + 16 <= p.splits; sp += 16) {
+            float v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = __ldcg(base + ((size_t)(sp + u) * RT + r) * REC + d);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+                const float c = exp2f(sm_r[sp + u] - mn);
+                ov = fmaf(v[u], c, ov);
+                lv = fmaf(sl_r[sp + u], c, lv);
+            }
+        }
+        for (; sp < p.splits; ++sp) {
+            const float c = exp2f(sm_r[sp] - mn);
+            ov = fmaf(__ldcg(base + ((size_t)sp * RT + r) * REC + d), c, ov);
+            lv = fmaf(sl_r[sp], c, lv);
+        }
+        p.out[(size_t)(kvh * G + rt * RT + r) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
+    }
+    if (threadIdx.x == 0) p.counters[tile_id] = 0;
+}
+
+// ---- host side of the tensor-map path
+typedef CUresult (*AttnEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                      const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                      CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static AttnEncodeTiledFn attn_encode() {
+    static AttnEncodeTiledFn fn = [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return (AttnEncodeTiledFn)f;
+    }();
+    return fn;
+}
+// [n_seq, n_kv, max_seq, 128] bf16 cache as a 4-D tensor, box = 64 dims x 64 positions, 128-byte swizzle (cached per cache)
+static int attn_cache_map(const void* cache, int max_seq, int n_kv, int n_seq, long cache_stride, CUtensorMap* out) {
+    struct Key { const void* p; int a, b, c; long s; };
+    static std::mutex mu;
+    static std::vector<std::pair<Key, CUtensorMap>> maps;
+    std::lock_guard<std::mutex> lk(mu);
+    for (auto& e : maps)
+        if (e.first.p == cache && e.first.a == max_seq && e.first.b == n_kv && e.first.c == n_seq && e.first.s == cache_stride) { *out = e.second; return 0; }
+    CUtensorMap m;
+    const cuuint64_t dims[4] = {128, (cuuint64_t)max_seq, (cuuint64_t)n_kv, (cuuint64_t)n_seq};
+    const cuuint64_t strides[3] = {256, (cuuint64_t)max_seq * 256, (cuuint64_t)(n_seq > 1 ? cache_stride * 2 : (long)n_kv * max_seq * 256)};
+    const cuuint32_t box[4] = {64, 64, 1, 1}, estr[4] = {1, 1, 1, 1};
+    const CUresult r = attn_encode()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(cache), dims, strides, box, estr,
+                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    PGK_REQUIRE(r == CUDA_SUCCESS, "rope_sdpa_decode failed: cuTensorMapEncodeTiled returned %d", (int)r);
+    if (maps.size() >= 4096) maps.clear();
+    maps.emplace_back(Key{cache, max_seq, n_kv, n_seq, cache_stride}, m);
+    *out = m;
+    return 0;
+}
+
+static int launch_rope_sdpa_mma(RopeSdpaParams p, cudaStream_t st) {
+    const int G = p.hq / p.n_kv;
+    const int row_tiles = (G + kMRT - 1) / kMRT;
+    const int base_ctas = p.n_kv * row_tiles * p.n_seq;
+    static const int env_splits = [] { const char* e = getenv("PGK_ATTN_SPLITS"); return e ? atoi(e) : 0; }();
+    static const int env_waves = [] { const char* e = getenv("PGK_ATTN_WAVES"); return e ? atoi(e) : 2; }();
+    int splits = (env_waves * sm_count() + base_ctas - 1) / base_ctas;
+    const int hint = p.ctx_buf ? p.max_seq : p.context_len;
+    const int max_splits = (hint + kMTile - 1) / kMTile;
+    if (splits > max_splits) splits = max_splits;
+    if (env_splits > 0) splits = env_splits;
+    if (splits < 1) splits = 1;
+    if (splits > kAttnMaxSplits) splits = kAttnMaxSplits;
+    PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * kMRT * kMRec * 4 <= kAttnWsBytes,
+                "rope_sdpa_decode failed: too many (sequence, head) tiles (%d)", base_ctas);
+    CUtensorMap kmap, vmap;
+    if (attn_cache_map(p.kc, p.max_seq, p.n_kv, p.n_seq, p.cache_stride, &kmap)) return 1;
+    if (attn_cache_map(p.vc, p.max_seq, p.n_kv, p.n_seq, p.cache_stride, &vmap)) return 1;
+    p.splits = splits;
+    p.ws = g_attn_ws;
+    p.counters = g_attn_cnt;
+    constexpr size_t kSmem = (size_t)kMStages * kMStageB + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PGK_CUDA(cudaFuncSetAttribute(rope_sdpa_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        attr_set = true;
+    }
+    PGK_CUDA(launch(rope_sdpa_mma_kernel, dim3(splits, row_tiles, p.n_kv * p.n_seq), dim3(kMThreads), kSmem, st, kmap, vmap, p));
+    return 0;
+}
+
 static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
     const int G = p.hq / p.n_kv;
     const int row_tiles = (G + kFRT - 1) / kFRT;
@@ -753,6 +1185,8 @@ static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
         PGK_CUDA(cudaMalloc(&g_attn_cnt, kAttnMaxTiles * sizeof(unsigned)));
         PGK_CUDA(cudaMemset(g_attn_cnt, 0, kAttnMaxTiles * sizeof(unsigned)));
     }
+    static const int impl = [] { const char* e = getenv("PGK_ATTN_IMPL"); return e ? atoi(e) : 2; }();
+    if (impl == 2 && attn_encode() != nullptr && p.max_seq >= kMTile) return launch_rope_sdpa_mma(p, st);
     PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * kFRT * 130 * 4 <= kAttnWsBytes,
                 "rope_sdpa_decode failed: too many (sequence, head) tiles (%d)", base_ctas);
     p.splits = splits;
