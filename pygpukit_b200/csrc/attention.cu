@@ -387,14 +387,12 @@ static int launch_sdpa(SdpaParams p, cudaStream_t st) {
 // sdpa_causal_fixed_cache_ptr of layers/attention.py:326-368 with the same rounding points (q/k rounded
 // to bf16 after the norm and after the rotation, probabilities and the output accumulator in f32).
 //   * K/V tiles of the OLD positions do not depend on the previous kernel (the qkv GEMV), so one thread
-//     reads the device-side context length and issues every cp.async.bulk of the CTA's chunk (up to
-//     kFStages x 32 KB) BEFORE griddepcontrol.wait: the HBM round trip overlaps the GEMV's tail.
-//   * after the wait, warps 0..RT-1 normalise + rotate the RT query heads of the tile into shared memory,
-//     warps RT / RT+1 prepare the new K / V row; the CTA whose chunk holds the new position patches the row
+//     reads the device-side context length and issues the TMA loads of the CTA's first stages BEFORE
+//     griddepcontrol.wait: the HBM round trip overlaps the GEMV's tail.
+//   * after the wait the consumer warps normalise + rotate the query heads of the tile into shared memory, the
+//     producer warp prepares the new K / V row; the warp whose positions hold the new one patches the row
 //     into its staged tile (and the rt == 0 CTA writes it to the cache) -- no kernel boundary between the
 //     cache write and the attention that reads it.
-//   * scores use FHFMA.BF16 on the packed K words (exact products, f32 accumulate; q is exactly bf16
-//     after the rotation), so K is never unpacked; one 64-position batch per tile, one rescale per batch.
 struct RopeSdpaParams {
     const uint16_t* qkv;                       // [(hq + 2 n_kv) * 128] raw projections of the new token
     const uint16_t* q_gamma; const uint16_t* k_gamma; float eps;
@@ -405,356 +403,32 @@ struct RopeSdpaParams {
     const int32_t* pos_buf; const int32_t* ctx_buf;
     float scale_log2;
     int splits;
-    float* ws; unsigned* counters;
+    uint2* ll; unsigned* gen;                  // LL partial words {f32 bits, exchange number}, per-record generation
+    int box_rows;                              // rows of one TMA box = min(64, max_seq)
     // multi-sequence decode (continuous batching, native/ops/batch/continuous_batching.cuh:70-245): n_seq independent
     // sequences, each with its own cache region, position and context length (pos_buf / ctx_buf are then arrays)
     int n_seq;
     long qkv_stride, out_stride, cache_stride;     // elements between consecutive sequences
 };
-constexpr int kFTile = 64;       // KV positions per staged tile (16 KB K + 16 KB V)
-constexpr int kFStages = 2;
-constexpr int kFRT = 4;          // query heads per CTA
-
-// one warp: [RMSNorm] + NeoX rotation of one 128-wide head row, result as bf16 bits (d = lane, lane+32 | +64).
-// cos/sin (c, s) and gamma (g, as f32) were loaded by the caller BEFORE the dependency wait.
-__device__ __forceinline__ void norm_rope_head128(const uint16_t* __restrict__ row, bool use_gamma, const float (&g)[4],
-                                                  float eps, const float (&c)[2], const float (&s)[2],
-                                                  int lane, uint16_t* __restrict__ dst_s, uint16_t* __restrict__ dst_g) {
-    float x[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) x[i] = bf16_bits_to_f32(row[lane + 32 * i]);
-    if (use_gamma) {
-        // summation tree of the reference's 128-thread rmsnorm block (norm_kernels.cuh:535-585): one element
-        // per virtual thread, a shuffle tree per 32 elements, then a tree over the four totals
-        float tot = 0.f;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            float part = warp_sum(fmaf(x[w], x[w], 0.f));
-            if (lane == w) tot = part;
-        }
-        const float inv = rsqrtf(warp_sum(tot) / 128.f + eps);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) x[i] = round_bf16(x[i] * inv * g[i]);
-    }
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const float x0 = x[i], x1 = x[i + 2];
-        const uint16_t y0 = f32_to_bf16_bits(x0 * c[i] - x1 * s[i]), y1 = f32_to_bf16_bits(x1 * c[i] + x0 * s[i]);
-        dst_s[lane + 32 * i] = y0; dst_s[lane + 32 * i + 64] = y1;
-        if (dst_g) { dst_g[lane + 32 * i] = y0; dst_g[lane + 32 * i + 64] = y1; }
-    }
-}
-
-__global__ void __launch_bounds__(kAttnWarps * 32, 2)
-rope_sdpa_decode_kernel(RopeSdpaParams p) {
-    constexpr int HD = 128, RT = kFRT, REC = HD + 2, LPR = 16, U = 4;
-    constexpr uint32_t ROWB = HD * 2, TILEB = kFTile * ROWB;
-    extern __shared__ __align__(128) unsigned char kv_smem[];
-    __shared__ float sm_part[kAttnWarps][RT][REC];
-    __shared__ __align__(16) uint16_t q_s[RT][HD];
-    __shared__ __align__(16) uint16_t new_s[2][HD];           // new K row, new V row
-    __shared__ __align__(8) uint64_t full_bar[kFStages];
-    __shared__ unsigned s_ticket;
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int li = lane & 15, slot = lane >> 4;
-    const int G = p.hq / p.n_kv;
-    const int row_tiles = (G + RT - 1) / RT;
-    const int split = blockIdx.x, rt = blockIdx.y, kvh = blockIdx.z % p.n_kv, seq = blockIdx.z / p.n_kv;
-    p.qkv += (size_t)seq * p.qkv_stride;
-    p.out += (size_t)seq * p.out_stride;
-    p.kc += (size_t)seq * p.cache_stride;
-    p.vc += (size_t)seq * p.cache_stride;
-
-    // ---- independent of the previous kernel: position, barriers, the first K/V tiles
-    const int pos = p.pos_buf ? p.pos_buf[seq] : p.pos;
-    const int ctx = min(p.ctx_buf ? p.ctx_buf[seq] : p.context_len, p.max_seq);
-    int chunk = (ctx + p.splits - 1) / p.splits;
-    chunk = (chunk + kFTile - 1) & ~(kFTile - 1);
-    const int c0 = split * chunk, c1 = min(ctx, c0 + chunk);
-    const int ntiles = (c1 > c0) ? (c1 - c0 + kFTile - 1) / kFTile : 0;
-    const bool has_new = pos >= c0 && pos < c1;
-    // the cache write: the row-tile-0 CTA of the owning chunk (or split 0 when the caller's context excludes pos)
-    const bool writer = rt == 0 && pos < p.max_seq && (has_new || (pos >= ctx && split == 0));
-    const uint8_t* Kg = (const uint8_t*)p.kc + (size_t)kvh * p.max_seq * ROWB;
-    const uint8_t* Vg = (const uint8_t*)p.vc + (size_t)kvh * p.max_seq * ROWB;
-    auto issue_tile = [&](int t) {
-        const int st = t % kFStages;
-        const int t0 = c0 + t * kFTile;
-        const uint32_t bytes = (uint32_t)(min(kFTile, c1 - t0)) * ROWB;
-        unsigned char* ks = kv_smem + (size_t)st * 2 * TILEB;
-        mbar_arrive_expect_tx(&full_bar[st], 2 * bytes);
-        bulk_copy_g2s(ks, Kg + (size_t)t0 * ROWB, bytes, &full_bar[st]);
-        bulk_copy_g2s(ks + TILEB, Vg + (size_t)t0 * ROWB, bytes, &full_bar[st]);
-    };
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int i = 0; i < kFStages; ++i) mbar_init(&full_bar[i], 1);
-        mbar_fence_init();
-        for (int t = 0; t < min(ntiles, kFStages); ++t) issue_tile(t);
-    }
-    // rotation tables and norm weights of this warp's head: constants, requested before the wait as well
-    float rc[2] = {1.f, 1.f}, rs[2] = {0.f, 0.f}, rg[4] = {1.f, 1.f, 1.f, 1.f};
-    const uint16_t* my_gamma = (warp < RT) ? p.q_gamma : (warp == RT ? p.k_gamma : nullptr);
-    if (warp <= RT) {
-        const float* cs = p.cos_t + (size_t)pos * HD;
-        const float* sn = p.sin_t + (size_t)pos * HD;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) { rc[i] = __ldg(cs + lane + 32 * i); rs[i] = __ldg(sn + lane + 32 * i); }
-        if (my_gamma) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) rg[i] = bf16_bits_to_f32(__ldg(my_gamma + lane + 32 * i));
-        }
-    }
-    griddep_wait();
-    griddep_launch();
-
-    // ---- the new token's q heads of this tile, and (if this chunk owns the new position) its K / V rows
-    if (warp < RT) {
-        const int g = rt * RT + warp;
-        if (g < G) norm_rope_head128(p.qkv + (size_t)(kvh * G + g) * HD, my_gamma != nullptr, rg, p.eps, rc, rs, lane, q_s[warp], nullptr);
-        else for (int d = lane; d < HD; d += 32) q_s[warp][d] = 0;
-    } else if ((has_new || writer) && warp == RT) {
-        uint16_t* dst = writer ? p.kc + ((size_t)kvh * p.max_seq + pos) * HD : nullptr;
-        norm_rope_head128(p.qkv + (size_t)(p.hq + kvh) * HD, my_gamma != nullptr, rg, p.eps, rc, rs, lane, new_s[0], dst);
-    } else if ((has_new || writer) && warp == RT + 1) {
-        const uint16_t* src = p.qkv + (size_t)(p.hq + p.n_kv + kvh) * HD;
-        uint16_t* dst = writer ? p.vc + ((size_t)kvh * p.max_seq + pos) * HD : nullptr;
-        for (int d = lane; d < HD; d += 32) { uint16_t v = src[d]; new_s[1][d] = v; if (dst) dst[d] = v; }
-    }
-    __syncthreads();   // q_s / new_s visible; also orders the mbarrier init before every wait
-    uint32_t q[RT][4];
-#pragma unroll
-    for (int r = 0; r < RT; ++r) {
-        const uint4 v = *reinterpret_cast<const uint4*>(&q_s[r][li * 8]);
-        q[r][0] = v.x; q[r][1] = v.y; q[r][2] = v.z; q[r][3] = v.w;
-    }
-    // Online-softmax state.  The 16 lanes of a group reduce the 16 (position u, row r) score partials of a tile
-    // with a reduce-scatter (15 shuffles instead of 64): lane li ends up owning the score of u = li >> 2,
-    // r = li & 3, so every exp2 is evaluated by ONE lane (the MUFU pipe runs at a quarter of the FMA rate) and
-    // the running max / sum of row r live in the four lanes with li & 3 == r.  Probabilities and the rescale
-    // factors are then broadcast back for the P.V update, which stays lane-local in the head dimension.
-    static_assert(RT == 4 && U == 4, "the reduce-scatter below is written for 4 rows x 4 positions per tile");
-    float m_own = kNegBig, l_own = 0.f, o[RT][8];
-#pragma unroll
-    for (int r = 0; r < RT; ++r)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) o[r][e] = 0.f;
-    const int gbase = lane & 16;
-
-    for (int t = 0; t < ntiles; ++t) {
-        const int st = t % kFStages;
-        const int t0 = c0 + t * kFTile, t1 = min(c1, t0 + kFTile);
-        mbar_wait(&full_bar[st], (uint32_t)((t / kFStages) & 1));
-        unsigned char* tile = kv_smem + (size_t)st * 2 * TILEB;
-        if (has_new && pos >= t0 && pos < t1) {               // CTA-uniform: patch the new row into the staged tile
-            if (threadIdx.x < 32) {
-                const int which = threadIdx.x >> 4, v = threadIdx.x & 15;
-                reinterpret_cast<uint4*>(tile + (size_t)which * TILEB + (size_t)(pos - t0) * ROWB)[v] =
-                    reinterpret_cast<const uint4*>(new_s[which])[v];
-            }
-            __syncthreads();
-        }
-        const unsigned char* ks = tile + (size_t)li * 16;
-        const unsigned char* vs = ks + TILEB;
-        uint4 kq[U], vq[U];
-        bool valid[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int j = t0 + warp * 2 + slot + u * (kAttnWarps * 2);
-            valid[u] = j < t1;
-            if (valid[u]) {
-                kq[u] = *reinterpret_cast<const uint4*>(ks + (size_t)(j - t0) * ROWB);
-                vq[u] = *reinterpret_cast<const uint4*>(vs + (size_t)(j - t0) * ROWB);
-            } else {
-                kq[u] = make_uint4(0, 0, 0, 0); vq[u] = make_uint4(0, 0, 0, 0);
-            }
-        }
-        float val[16];                                        // index v = u * 4 + r: partial over this lane's 8 dims
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-#pragma unroll
-            for (int r = 0; r < RT; ++r) {
-                float a0 = 0.f, a1 = 0.f;
-                fhfma_bf16_lo(a0, q[r][0], kq[u].x); fhfma_bf16_hi(a1, q[r][0], kq[u].x);
-                fhfma_bf16_lo(a0, q[r][1], kq[u].y); fhfma_bf16_hi(a1, q[r][1], kq[u].y);
-                fhfma_bf16_lo(a0, q[r][2], kq[u].z); fhfma_bf16_hi(a1, q[r][2], kq[u].z);
-                fhfma_bf16_lo(a0, q[r][3], kq[u].w); fhfma_bf16_hi(a1, q[r][3], kq[u].w);
-                val[u * 4 + r] = a0 + a1;
-            }
-        }
-        // reduce-scatter over the group: after the stage with offset b a lane keeps the values whose bit b of v
-        // equals bit b of li, summed over twice as many lanes
-        float tot;
-        {
-            const bool b8 = li & 8, b4 = li & 4, b2 = li & 2, b1 = li & 1;
-            float v8[8], v4[4], v2[2];
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                v8[i] = (b8 ? val[i + 8] : val[i]) + __shfl_xor_sync(0xffffffffu, b8 ? val[i] : val[i + 8], 8);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                v4[i] = (b4 ? v8[i + 4] : v8[i]) + __shfl_xor_sync(0xffffffffu, b4 ? v8[i] : v8[i + 4], 4);
-#pragma unroll
-            for (int i = 0; i < 2; ++i)
-                v2[i] = (b2 ? v4[i + 2] : v4[i]) + __shfl_xor_sync(0xffffffffu, b2 ? v4[i] : v4[i + 2], 2);
-            tot = (b1 ? v2[1] : v2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? v2[0] : v2[1], 1);
-        }
-        // this lane's score: position u = li >> 2 of its slot, row r = li & 3
-        const bool own_valid = t0 + warp * 2 + slot + (li >> 2) * (kAttnWarps * 2) < t1;
-        const float s_own = own_valid ? tot * p.scale_log2 : kNegBig;
-        float mx = fmaxf(s_own, __shfl_xor_sync(0xffffffffu, s_own, 4));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-        const float mn = fmaxf(m_own, mx);
-        const float corr_own = exp2f(m_own - mn);
-        const float p_own = (s_own > 0.5f * kNegBig) ? exp2f(s_own - mn) : 0.f;
-        float ls = p_own + __shfl_xor_sync(0xffffffffu, p_own, 4);
-        ls += __shfl_xor_sync(0xffffffffu, ls, 8);
-        l_own = l_own * corr_own + ls;
-        m_own = mn;
-        // broadcast back: rescale factors per row, probabilities per (position, row)
-#pragma unroll
-        for (int r = 0; r < RT; ++r) {
-            const float corr = __shfl_sync(0xffffffffu, corr_own, gbase + r);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) o[r][e] *= corr;
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            float vf[8];
-            KvVec<2>::unpack(vq[u], vf);
-#pragma unroll
-            for (int r = 0; r < RT; ++r) {
-                const float pj = __shfl_sync(0xffffffffu, p_own, gbase + u * 4 + r);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) o[r][e] = fmaf(pj, vf[e], o[r][e]);
-            }
-        }
-        if (t + kFStages < ntiles) {                  // refill this stage (CTA-uniform condition)
-            __syncthreads();
-            if (threadIdx.x == 0) { fence_proxy_async(); issue_tile(t + kFStages); }
-        }
-    }
-    // every lane needs (m, l) of all rows for the merges below
-    float m[RT], l[RT];
-#pragma unroll
-    for (int r = 0; r < RT; ++r) {
-        m[r] = __shfl_sync(0xffffffffu, m_own, gbase + r);
-        l[r] = __shfl_sync(0xffffffffu, l_own, gbase + r);
-    }
-    // merge the two position slots of the warp
-#pragma unroll
-    for (int r = 0; r < RT; ++r) {
-        const float m2 = __shfl_xor_sync(0xffffffffu, m[r], 16);
-        const float l2 = __shfl_xor_sync(0xffffffffu, l[r], 16);
-        const float mn = fmaxf(m[r], m2);
-        const float c1s = exp2f(m[r] - mn), c2s = exp2f(m2 - mn);
-        l[r] = l[r] * c1s + l2 * c2s;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const float o2 = __shfl_xor_sync(0xffffffffu, o[r][e], 16);
-            o[r][e] = o[r][e] * c1s + o2 * c2s;
-        }
-        m[r] = mn;
-        if (slot == 0) {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) sm_part[warp][r][li * 8 + e] = o[r][e];
-            if (li == 0) { sm_part[warp][r][HD] = m[r]; sm_part[warp][r][HD + 1] = l[r]; }
-        }
-    }
-    __syncthreads();
-    const size_t tile_id = ((size_t)seq * p.n_kv + kvh) * row_tiles + rt;
-    float* rec = p.ws + (tile_id * p.splits + split) * RT * REC;
-    for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
-        const int r = idx / HD, d = idx % HD;
-        float mn = kNegBig;
-#pragma unroll
-        for (int w = 0; w < kAttnWarps; ++w) mn = fmaxf(mn, sm_part[w][r][HD]);
-        float ov = 0.f, lv = 0.f;
-#pragma unroll
-        for (int w = 0; w < kAttnWarps; ++w) {
-            const float c = exp2f(sm_part[w][r][HD] - mn);
-            ov = fmaf(sm_part[w][r][d], c, ov);
-            lv = fmaf(sm_part[w][r][HD + 1], c, lv);
-        }
-        if (p.splits == 1) {
-            const int g = rt * RT + r;
-            if (g < G) p.out[(size_t)(kvh * G + g) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
-        } else {
-            __stcg(rec + r * REC + d, ov);
-            if (d == 0) { __stcg(rec + r * REC + HD, mn); __stcg(rec + r * REC + HD + 1, lv); }
-        }
-    }
-    if (p.splits == 1) return;
-    // release: the CTA barrier orders every thread's partial stores before thread 0's gpu-scope fence (fences
-    // are cumulative), which orders them before the ticket; acquire on the other side is symmetric
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        s_ticket = atomicAdd(p.counters + tile_id, 1u);
-        __threadfence();
-    }
-    __syncthreads();
-    if (s_ticket != (unsigned)(p.splits - 1)) return;
-    // last CTA of the (kv head, row tile): fold the partials in split order (deterministic)
-    const float* base = p.ws + tile_id * p.splits * RT * REC;
-    float* s_m = &sm_part[0][0][0];                          // [RT][kAttnMaxSplits] (sm_part is free again)
-    float* s_l = s_m + RT * kAttnMaxSplits;
-    for (int idx = threadIdx.x; idx < RT * p.splits; idx += blockDim.x) {
-        const int r = idx / p.splits, sp = idx % p.splits;
-        const float* rr = base + ((size_t)sp * RT + r) * REC;
-        s_m[r * kAttnMaxSplits + sp] = __ldcg(rr + HD);
-        s_l[r * kAttnMaxSplits + sp] = __ldcg(rr + HD + 1);
-    }
-    __syncthreads();
-    for (int idx = threadIdx.x; idx < RT * HD; idx += blockDim.x) {
-        const int r = idx / HD, d = idx % HD;
-        const int g = rt * RT + r;
-        if (g >= G) continue;
-        const float* sm_r = s_m + r * kAttnMaxSplits;
-        const float* sl_r = s_l + r * kAttnMaxSplits;
-        float mn = kNegBig;
-        for (int sp = 0; sp < p.splits; ++sp) mn = fmaxf(mn, sm_r[sp]);
-        float ov = 0.f, lv = 0.f;
-        int sp = 0;
-        for (; sp + 16 <= p.splits; sp += 16) {
-            float v[16];
-#pragma unroll
-            for (int u = 0; u < 16; ++u) v[u] = __ldcg(base + ((size_t)(sp + u) * RT + r) * REC + d);
-#pragma unroll
-            for (int u = 0; u < 16; ++u) {
-                const float c = exp2f(sm_r[sp + u] - mn);
-                ov = fmaf(v[u], c, ov);
-                lv = fmaf(sl_r[sp + u], c, lv);
-            }
-        }
-        for (; sp < p.splits; ++sp) {
-            const float c = exp2f(sm_r[sp] - mn);
-            ov = fmaf(__ldcg(base + ((size_t)sp * RT + r) * REC + d), c, ov);
-            lv = fmaf(sl_r[sp], c, lv);
-        }
-        p.out[(size_t)(kvh * G + g) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
-    }
-    if (threadIdx.x == 0) p.counters[tile_id] = 0;
-}
-
 // ---------------------------------------------------------------------------------------------------------------
-// Round 2: the same fused bracket with the score and P.V products on the tensor cores (mma.sync m16n8k16, SASS HMMA)
+// The score and P.V products run on the tensor cores (mma.sync m16n8k16, SASS HMMA)
 // and the K/V tiles fetched by tensor-map TMA (cp.async.bulk.tensor.4d, SWIZZLE_128B, SASS UTMALDG) so that ldmatrix
-// reads them without bank conflicts.  Decode attention is HBM / latency bound; what the CUDA-core loop above spends
-// per 64 positions (unpacking V, 15 shuffles of the score reduce-scatter, 450 issue slots per warp) was a third of the
-// launch at 4k and the whole of it at 32k.  Here a warp owns 16 positions of a 64-position tile:
+// reads them without bank conflicts.  Decode attention is HBM / latency bound; the CUDA-core loop of round 1 spent 450
+// issue slots per warp per 64 positions (unpacking V, 15 shuffles of the score reduce-scatter), which bounded the long
+// contexts and the multi-sequence batches.  Here a warp owns 16 positions of a 64-position tile:
 //     S[8 heads (+8 zero rows), 16 pos]  = Q[16, 128] . K^T      16 HMMA, B fragments by ldmatrix from the swizzled tile
 //     online softmax on the 4 scores a thread holds (row = lane / 4), quad shuffles only
 //     O[16, 128] += P[16, 16] . V[16, 128]                       16 HMMA, V fragments by ldmatrix.trans
 // The probabilities go to the tensor cores as TWO bf16 terms, p = hi + lo, hi in rows 0..7 and lo in rows 8..15 of the
 // A fragment (the rows the <= 8 query heads leave empty), so one MMA accumulates both and O = O[0..7] + O[8..15] carries
 // 16 bits of p: the products q.k are exact and p.v is as accurate as the f32 loop it replaces.
-// One CTA = 4 consumer warps + 1 TMA producer warp, 3 stages x 32 KB, 2 CTAs per SM; up to 8 query heads per CTA, so a
-// GQA group of 8 (Llama-3-70B, Qwen3-30B-A3B) reads its K/V once instead of twice.
+// One CTA = 4 consumer warps + 1 TMA producer warp, 2 CTAs per SM; up to 8 query heads per CTA, so a GQA group of 8
+// (Llama-3-70B, Qwen3-30B-A3B) reads its K/V once instead of twice.  Stages: 2 x 32 KB for one sequence -- measured:
+// with 3 stages the two CTAs need 202 KB of shared memory, the SM is switched to its largest carve-out, and the GEMVs
+// that FOLLOW in the step run 8 % slower on the 28 KB of L1 that leaves them (profiles/r02_attn_mma_carveout.txt) --
+// and 3 x 32 KB for multi-sequence batches, where attention is most of the step.
 constexpr int kMW = 4;                          // consumer warps
 constexpr int kMTile = 64;                      // KV positions per stage
-constexpr int kMStages = 3;
 constexpr int kMRT = 8;                         // query heads per CTA
 constexpr int kMThreads = (kMW + 1) * 32;
 constexpr uint32_t kMBox = 64 * 128;            // one TMA box: 64 positions x 64 dims (128 bytes, the swizzle span)
@@ -776,6 +450,9 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
 __device__ __forceinline__ void tma_load_4d(uint32_t smem_dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint64_t* bar) {
     asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
                  :: "r"(smem_dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void ll_store(uint2* p, uint32_t data, uint32_t seq) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(data), "r"(seq) : "memory");
 }
 // a wait that cannot hang the device: a protocol bug traps instead of spinning forever
 __device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
@@ -812,6 +489,7 @@ __device__ __forceinline__ void norm_rope_regs(float (&x)[4], bool use_gamma, co
     }
 }
 
+template <int kMStages>
 __global__ void __launch_bounds__(kMThreads, 2)
 rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant__ CUtensorMap vmap, RopeSdpaParams p) {
     constexpr int HD = 128, RT = kMRT, REC = kMRec;
@@ -820,7 +498,7 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
     __shared__ __align__(16) uint16_t new_s[2][HD];           // new K row, new V row
     __shared__ __align__(8) uint64_t full_bar[kMStages];
     __shared__ __align__(8) uint64_t empty_bar[kMStages];
-    __shared__ unsigned s_ticket;
+    __shared__ unsigned s_gen[kAttnMaxSplits];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int G = p.hq / p.n_kv;
@@ -847,7 +525,7 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
         const int st = t % kMStages;
         const int t0 = c0 + t * kMTile;
         const uint32_t dst = tiles_s + (uint32_t)st * kMStageB;
-        mbar_arrive_expect_tx(&full_bar[st], kMStageB);        // out-of-range rows are zero-filled and still counted
+        mbar_arrive_expect_tx(&full_bar[st], (uint32_t)p.box_rows * 512u);   // 4 boxes of box_rows x 128 bytes; out-of-range rows are zero-filled and still counted
         tma_load_4d(dst, &kmap, 0, t0, kvh, seq, &full_bar[st]);
         tma_load_4d(dst + kMBox, &kmap, 64, t0, kvh, seq, &full_bar[st]);
         tma_load_4d(dst + 2 * kMBox, &vmap, 0, t0, kvh, seq, &full_bar[st]);
@@ -857,6 +535,8 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
 #pragma unroll
         for (int i = 0; i < kMStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], kMW); }
         mbar_fence_init();
+        asm volatile("prefetch.tensormap [%0];" :: "l"(&kmap) : "memory");
+        asm volatile("prefetch.tensormap [%0];" :: "l"(&vmap) : "memory");
         for (int t = 0; t < min(ntiles, kMStages); ++t) issue_tile(t);
     }
     float rc[2], rs[2], rg[4] = {1.f, 1.f, 1.f, 1.f};
@@ -873,6 +553,9 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
     }
     griddep_wait();
     griddep_launch();
+    // exchange numbers of this tile's partial records (see the fold below)
+    if (p.splits > 1 && threadIdx.x < p.splits)
+        s_gen[threadIdx.x] = __ldcg(p.gen + (((size_t)seq * p.n_kv + kvh) * row_tiles + rt) * p.splits + threadIdx.x) + 1u;
 
     // ---- the new token: consumer warp w rotates query heads w and w + 4, the producer warp the new K / V rows
     if (warp < kMW) {
@@ -1029,7 +712,35 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
     }
     __syncthreads();
     const size_t tile_id = ((size_t)seq * p.n_kv + kvh) * row_tiles + rt;
-    float* rec = p.ws + (tile_id * p.splits + split) * RT * REC;
+    if (p.splits == 1) {
+        for (int idx = threadIdx.x; idx < rows * HD; idx += kMThreads) {
+            const int r = idx / HD, d = idx % HD;
+            float mn = kNegBig;
+#pragma unroll
+            for (int w = 0; w < kMW; ++w) mn = fmaxf(mn, sm_part[w][r][HD]);
+            float ov = 0.f, lv = 0.f;
+#pragma unroll
+            for (int w = 0; w < kMW; ++w) {
+                const float c = exp2f(sm_part[w][r][HD] - mn);
+                ov = fmaf(sm_part[w][r][d], c, ov);
+                lv = fmaf(sm_part[w][r][HD + 1], c, lv);
+            }
+            p.out[(size_t)(kvh * G + rt * RT + r) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
+        }
+        return;
+    }
+    // ---- cross-split fold without a fence, a ticket or a second pass: every partial travels as 8-byte words
+    // {f32 bits, exchange number} (the LL form of p2p.cu), so a reader knows a word is this launch's by looking at it.
+    // Each partial record (tile, split) of the workspace has its own generation counter; the exchange number is that
+    // generation + 1, read by every CTA of the tile after the dependency wait.  CTA `split` folds the slice
+    // [split * W, (split + 1) * W) of the rows * 128 outputs in split order (all slices poll at once: one L2 round
+    // trip after the slowest writer); split 0 publishes the new generations once its slice has seen every partial,
+    // which proves that every CTA of the tile has read the old ones.  The numbers written to any one address only
+    // ever grow, whatever shapes earlier launches had, so a stale word can never pass for a fresh one.
+    // (A fold CTA waits for its sibling CTAs: one tile's splits <= 128 are always co-resident, blocks being
+    // dispatched in index order; the wait is bounded and traps.)
+    const int S = p.splits;
+    uint2* ll = p.ll + tile_id * (size_t)S * RT * REC;
     for (int idx = threadIdx.x; idx < rows * HD; idx += kMThreads) {
         const int r = idx / HD, d = idx % HD;
         float mn = kNegBig;
@@ -1042,63 +753,96 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
             ov = fmaf(sm_part[w][r][d], c, ov);
             lv = fmaf(sm_part[w][r][HD + 1], c, lv);
         }
-        if (p.splits == 1) {
-            p.out[(size_t)(kvh * G + rt * RT + r) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
-        } else {
-            __stcg(rec + r * REC + d, ov);
-            if (d == 0) { __stcg(rec + r * REC + HD, mn); __stcg(rec + r * REC + HD + 1, lv); }
-        }
+        uint2* rec = ll + ((size_t)split * RT + r) * REC;
+        const unsigned tag = s_gen[split];
+        ll_store(rec + d, __float_as_uint(ov), tag);
+        if (d == 0) { ll_store(rec + HD, __float_as_uint(mn), tag); ll_store(rec + HD + 1, __float_as_uint(lv), tag); }
     }
-    if (p.splits == 1) return;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        s_ticket = atomicAdd(p.counters + tile_id, 1u);
-        __threadfence();
-    }
-    __syncthreads();
-    if (s_ticket != (unsigned)(p.splits - 1)) return;
-    // last CTA of the (kv head, row tile): fold the partials in split order (deterministic)
-    const float* base = p.ws + tile_id * p.splits * RT * REC;
-    float* s_m = &sm_part[0][0][0];                            // [RT][kAttnMaxSplits] (the merge buffer is free again)
-    float* s_l = s_m + RT * kAttnMaxSplits;
-    for (int idx = threadIdx.x; idx < rows * p.splits; idx += kMThreads) {
-        const int r = idx / p.splits, sp = idx % p.splits;
-        const float* rr = base + ((size_t)sp * RT + r) * REC;
-        s_m[r * kAttnMaxSplits + sp] = __ldcg(rr + HD);
-        s_l[r * kAttnMaxSplits + sp] = __ldcg(rr + HD + 1);
-    }
-    __syncthreads();
-    for (int idx = threadIdx.x; idx < rows * HD; idx += kMThreads) {
-        const int r = idx / HD, d = idx % HD;
-        const float* sm_r = s_m + r * kAttnMaxSplits;
-        const float* sl_r = s_l + r * kAttnMaxSplits;
-        float mn = kNegBig;
-        for (int sp = 0; sp < p.splits; ++sp) mn = fmaxf(mn, sm_r[sp]);
-        float ov = 0.f, lv = 0.f;
-        int sp = 0;
-        for (; sp + 16 <= p.splits; sp += 16) {
-            float v[16];
+    const int E = rows * HD;
+    const int F = S;
+    const int W = (E + F - 1) / F;
+    const int e0 = split * W, n_e = min(E, e0 + W) - e0;
+    if (n_e <= 0) return;
+    const int r0 = e0 / HD, nr = (e0 + n_e - 1) / HD - r0 + 1;   // rows this slice touches
+    const int SP = S | 1;                                        // odd stride: conflict-free column walks
+    float* f_o = reinterpret_cast<float*>(tiles_g + 20 * 1024);  // [n_e][SP]
+    float* f_m = f_o + W * SP;                                   // [RT][SP]  (max, then scale factor)
+    float* f_l = f_m + RT * SP;                                  // [RT][SP]
+    float* f_den = f_l + RT * SP;                                // [RT]
+    constexpr int MAXJ = 16;
+    const int n_o = n_e * S, n_items = n_o + nr * S * 2;
+    for (int base = 0; base < n_items; base += kMThreads * MAXJ) {
+        uint32_t src[MAXJ], tag[MAXJ];
+        int dst[MAXJ];                                           // >= 0: f_o index; < 0: ~index into f_m (.. f_l follows)
+        unsigned pend = 0;
 #pragma unroll
-            for (int u = 0; u < 16; ++u) v[u] = __ldcg(base + ((size_t)(sp + u) * RT + r) * REC + d);
-#pragma unroll
-            for (int u = 0; u < 16; ++u) {
-                const float c = exp2f(sm_r[sp + u] - mn);
-                ov = fmaf(v[u], c, ov);
-                lv = fmaf(sl_r[sp + u], c, lv);
+        for (int j = 0; j < MAXJ; ++j) {
+            const int k = base + threadIdx.x + j * kMThreads;
+            src[j] = 0; dst[j] = 0; tag[j] = 0;
+            if (k < n_o) {
+                const int el = k / S, sp = k - el * S, e = e0 + el;
+                src[j] = (uint32_t)((sp * RT + (e >> 7)) * REC + (e & 127));
+                dst[j] = el * SP + sp;
+                tag[j] = s_gen[sp];
+                pend |= 1u << j;
+            } else if (k < n_items) {
+                const int k2 = k - n_o, which = k2 & 1, k3 = k2 >> 1;
+                const int rr = k3 / S, sp = k3 - rr * S;
+                src[j] = (uint32_t)((sp * RT + r0 + rr) * REC + HD + which);
+                dst[j] = ~(which * RT * SP + (r0 + rr) * SP + sp);
+                tag[j] = s_gen[sp];
+                pend |= 1u << j;
             }
         }
-        for (; sp < p.splits; ++sp) {
-            const float c = exp2f(sm_r[sp] - mn);
-            ov = fmaf(__ldcg(base + ((size_t)sp * RT + r) * REC + d), c, ov);
-            lv = fmaf(sl_r[sp], c, lv);
+        for (uint32_t spin = 0; pend; ++spin) {
+            uint2 w[MAXJ];
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j)
+                if (pend >> j & 1)
+                    asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(w[j].x), "=r"(w[j].y) : "l"(ll + src[j]) : "memory");
+#pragma unroll
+            for (int j = 0; j < MAXJ; ++j)
+                if ((pend >> j & 1) && w[j].y == tag[j]) {
+                    if (dst[j] >= 0) f_o[dst[j]] = __uint_as_float(w[j].x); else f_m[~dst[j]] = __uint_as_float(w[j].x);
+                    pend &= ~(1u << j);
+                }
+            if (spin > (1u << 22)) __trap();                     // a lost partial must not hang the device
         }
+    }
+    __syncthreads();
+    if (split == 0 && threadIdx.x < S) p.gen[tile_id * S + threadIdx.x] = s_gen[threadIdx.x];
+    // per row: max over the splits, scale factors, denominator (one warp per row, fixed shuffle tree)
+    for (int rr = warp; rr < nr; rr += kMW + 1) {
+        const int r = r0 + rr;
+        float mx = kNegBig;
+        for (int sp = lane; sp < S; sp += 32) mx = fmaxf(mx, f_m[r * SP + sp]);
+        mx = warp_max(mx);
+        float den = 0.f;
+        for (int sp = lane; sp < S; sp += 32) {
+            const float c = exp2f(f_m[r * SP + sp] - mx);
+            f_m[r * SP + sp] = c;
+            den = fmaf(f_l[r * SP + sp], c, den);
+        }
+        den = warp_sum(den);
+        if (lane == 0) f_den[r] = den;
+    }
+    __syncthreads();
+    for (int el = threadIdx.x; el < n_e; el += kMThreads) {
+        const int e = e0 + el, r = e >> 7, d = e & 127;
+        const float* fo = f_o + el * SP;
+        const float* fc = f_m + r * SP;
+        float ov = 0.f;
+        for (int sp = 0; sp < S; ++sp) ov = fmaf(fo[sp], fc[sp], ov);
+        const float lv = f_den[r];
         p.out[(size_t)(kvh * G + rt * RT + r) * HD + d] = f32_to_bf16_bits(lv > 0.f ? ov / lv : 0.f);
     }
-    if (threadIdx.x == 0) p.counters[tile_id] = 0;
 }
 
 // ---- host side of the tensor-map path
+static uint2* g_attn_ll = nullptr;
+static unsigned* g_attn_gen = nullptr;
+static const size_t kAttnLLBytes = 64ull << 20;
+static const size_t kAttnLLRecords = kAttnLLBytes / (kMRT * kMRec * 8);     // partial records (tile, split) the workspace holds
 typedef CUresult (*AttnEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                       const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                       CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -1112,7 +856,8 @@ static AttnEncodeTiledFn attn_encode() {
     }();
     return fn;
 }
-// [n_seq, n_kv, max_seq, 128] bf16 cache as a 4-D tensor, box = 64 dims x 64 positions, 128-byte swizzle (cached per cache)
+// [n_seq, n_kv, max_seq, 128] bf16 cache as a 4-D tensor, box = 64 dims x min(64, max_seq) positions, 128-byte swizzle
+// (cached per cache)
 static int attn_cache_map(const void* cache, int max_seq, int n_kv, int n_seq, long cache_stride, CUtensorMap* out) {
     struct Key { const void* p; int a, b, c; long s; };
     static std::mutex mu;
@@ -1123,7 +868,7 @@ static int attn_cache_map(const void* cache, int max_seq, int n_kv, int n_seq, l
     CUtensorMap m;
     const cuuint64_t dims[4] = {128, (cuuint64_t)max_seq, (cuuint64_t)n_kv, (cuuint64_t)n_seq};
     const cuuint64_t strides[3] = {256, (cuuint64_t)max_seq * 256, (cuuint64_t)(n_seq > 1 ? cache_stride * 2 : (long)n_kv * max_seq * 256)};
-    const cuuint32_t box[4] = {64, 64, 1, 1}, estr[4] = {1, 1, 1, 1};
+    const cuuint32_t box[4] = {64, (cuuint32_t)(max_seq < kMTile ? max_seq : kMTile), 1, 1}, estr[4] = {1, 1, 1, 1};
     const CUresult r = attn_encode()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(cache), dims, strides, box, estr,
                                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1134,72 +879,54 @@ static int attn_cache_map(const void* cache, int max_seq, int n_kv, int n_seq, l
     return 0;
 }
 
-static int launch_rope_sdpa_mma(RopeSdpaParams p, cudaStream_t st) {
+template <int STAGES>
+static int launch_rope_sdpa_stages(const CUtensorMap& kmap, const CUtensorMap& vmap, const RopeSdpaParams& p, dim3 grid, cudaStream_t st) {
+    constexpr size_t kSmem = (size_t)STAGES * kMStageB + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PGK_CUDA(cudaFuncSetAttribute(rope_sdpa_mma_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        attr_set = true;
+    }
+    PGK_CUDA(launch(rope_sdpa_mma_kernel<STAGES>, grid, dim3(kMThreads), kSmem, st, kmap, vmap, p));
+    return 0;
+}
+
+static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
+    PGK_REQUIRE(attn_encode() != nullptr, "rope_sdpa_decode failed: the driver does not export cuTensorMapEncodeTiled");
     const int G = p.hq / p.n_kv;
     const int row_tiles = (G + kMRT - 1) / kMRT;
+    if (p.n_seq < 1) p.n_seq = 1;
     const int base_ctas = p.n_kv * row_tiles * p.n_seq;
+    // two resident CTAs per SM; a split keeps at least one 64-position tile
     static const int env_splits = [] { const char* e = getenv("PGK_ATTN_SPLITS"); return e ? atoi(e) : 0; }();
-    static const int env_waves = [] { const char* e = getenv("PGK_ATTN_WAVES"); return e ? atoi(e) : 2; }();
-    int splits = (env_waves * sm_count() + base_ctas - 1) / base_ctas;
+    int splits = (2 * sm_count() + base_ctas - 1) / base_ctas;
     const int hint = p.ctx_buf ? p.max_seq : p.context_len;
     const int max_splits = (hint + kMTile - 1) / kMTile;
     if (splits > max_splits) splits = max_splits;
     if (env_splits > 0) splits = env_splits;
     if (splits < 1) splits = 1;
     if (splits > kAttnMaxSplits) splits = kAttnMaxSplits;
-    PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * kMRT * kMRec * 4 <= kAttnWsBytes,
+    PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits <= kAttnLLRecords,
                 "rope_sdpa_decode failed: too many (sequence, head) tiles (%d)", base_ctas);
-    CUtensorMap kmap, vmap;
-    if (attn_cache_map(p.kc, p.max_seq, p.n_kv, p.n_seq, p.cache_stride, &kmap)) return 1;
-    if (attn_cache_map(p.vc, p.max_seq, p.n_kv, p.n_seq, p.cache_stride, &vmap)) return 1;
-    p.splits = splits;
-    p.ws = g_attn_ws;
-    p.counters = g_attn_cnt;
-    constexpr size_t kSmem = (size_t)kMStages * kMStageB + 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
-        PGK_CUDA(cudaFuncSetAttribute(rope_sdpa_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
-        attr_set = true;
-    }
-    PGK_CUDA(launch(rope_sdpa_mma_kernel, dim3(splits, row_tiles, p.n_kv * p.n_seq), dim3(kMThreads), kSmem, st, kmap, vmap, p));
-    return 0;
-}
-
-static int launch_rope_sdpa(RopeSdpaParams p, cudaStream_t st) {
-    const int G = p.hq / p.n_kv;
-    const int row_tiles = (G + kFRT - 1) / kFRT;
-    if (p.n_seq < 1) p.n_seq = 1;
-    const int base_ctas = p.n_kv * row_tiles * p.n_seq;
-    int splits = (2 * sm_count() + base_ctas - 1) / base_ctas;
-    const int hint = p.ctx_buf ? p.max_seq : p.context_len;
-    const int max_splits = (hint + 2 * kFTile - 1) / (2 * kFTile);
-    if (splits > max_splits) splits = max_splits;
-    if (splits < 1) splits = 1;
-    if (splits > kAttnMaxSplits) splits = kAttnMaxSplits;
-    if (!g_attn_ws) {
+    if (!g_attn_ll) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         cudaStreamIsCapturing(st, &cs);
         PGK_REQUIRE(cs == cudaStreamCaptureStatusNone,
                     "rope_sdpa_decode failed: first call must happen outside graph capture (workspace allocation)");
-        PGK_CUDA(cudaMalloc(&g_attn_ws, kAttnWsBytes));
-        PGK_CUDA(cudaMalloc(&g_attn_cnt, kAttnMaxTiles * sizeof(unsigned)));
-        PGK_CUDA(cudaMemset(g_attn_cnt, 0, kAttnMaxTiles * sizeof(unsigned)));
+        PGK_CUDA(cudaMalloc(&g_attn_ll, kAttnLLBytes));
+        PGK_CUDA(cudaMemset(g_attn_ll, 0, kAttnLLBytes));
+        PGK_CUDA(cudaMalloc(&g_attn_gen, kAttnLLRecords * sizeof(unsigned)));
+        PGK_CUDA(cudaMemset(g_attn_gen, 0, kAttnLLRecords * sizeof(unsigned)));
     }
-    static const int impl = [] { const char* e = getenv("PGK_ATTN_IMPL"); return e ? atoi(e) : 2; }();
-    if (impl == 2 && attn_encode() != nullptr && p.max_seq >= kMTile) return launch_rope_sdpa_mma(p, st);
-    PGK_REQUIRE(base_ctas <= kAttnMaxTiles && (size_t)base_ctas * splits * kFRT * 130 * 4 <= kAttnWsBytes,
-                "rope_sdpa_decode failed: too many (sequence, head) tiles (%d)", base_ctas);
+    CUtensorMap kmap, vmap;
+    if (attn_cache_map(p.kc, p.max_seq, p.n_kv, p.n_seq, p.cache_stride, &kmap)) return 1;
+    if (attn_cache_map(p.vc, p.max_seq, p.n_kv, p.n_seq, p.cache_stride, &vmap)) return 1;
     p.splits = splits;
-    p.ws = g_attn_ws;
-    p.counters = g_attn_cnt;
-    constexpr size_t kSmem = (size_t)kFStages * 2 * kFTile * 128 * 2;
-    static bool attr_set = false;
-    if (!attr_set) {
-        PGK_CUDA(cudaFuncSetAttribute(rope_sdpa_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
-        attr_set = true;
-    }
-    PGK_CUDA(launch(rope_sdpa_decode_kernel, dim3(splits, row_tiles, p.n_kv * p.n_seq), dim3(kAttnWarps * 32), kSmem, st, p));
-    return 0;
+    p.ll = g_attn_ll;
+    p.gen = g_attn_gen;
+    p.box_rows = p.max_seq < kMTile ? p.max_seq : kMTile;
+    const dim3 grid(splits, row_tiles, p.n_kv * p.n_seq);
+    return p.n_seq > 1 ? launch_rope_sdpa_stages<3>(kmap, vmap, p, grid, st) : launch_rope_sdpa_stages<2>(kmap, vmap, p, grid, st);
 }
 
 }  // namespace pgk

@@ -1,6 +1,7 @@
 // common.cuh -- shared device/host helpers for libpgk_b200 (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cstdint>
@@ -44,6 +45,12 @@ void fp8_codes_forget(const void* base);
 // Launch with optional programmatic-dependent-launch attribute (PDL): the kernel may
 // start while its predecessor drains; every kernel calls griddep_wait() before it
 // touches data produced by an earlier kernel.
+// One shared-memory / L1 split for every kernel of the step (PGK_CARVEOUT, percent of the maximum; -1 = driver's choice)
+inline int smem_carveout() {
+    static const int v = [] { const char* e = getenv("PGK_CARVEOUT"); return e ? atoi(e) : -1; }();
+    return v;
+}
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                           cudaStream_t stream, Args... args) {
@@ -52,12 +59,17 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     int nattr = 0;
     if (pdl_enabled()) {
         attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         nattr = 1;
+    }
+    if (const int co = smem_carveout(); co >= 0) {
+        attr[nattr].id = cudaLaunchAttributePreferredSharedMemoryCarveout;
+        attr[nattr].val.sharedMemCarveout = (unsigned)co;
+        ++nattr;
     }
     cfg.attrs = attr;
     cfg.numAttrs = nattr;

@@ -104,7 +104,52 @@ if not model.config.is_moe:
     m0 = model.blocks[0].mlp
     gub = m0.gate_up_proj.weight_bytes if m0.gate_up_proj is not None else m0.gate_proj.weight_bytes + m0.up_proj.weight_bytes
     parts += [("gate/up swiglu (+norm)", gateup, gub), ("down (+res)", down, m0.down_proj.weight_bytes)]
+def pair_qa(blk):
+    qkv(blk); fused_attn(blk)
+
+
+def pair_ao(blk):
+    fused_attn(blk); oproj(blk)
+
+
+def trio(blk):
+    qkv(blk); fused_attn(blk); oproj(blk)
+
+
+def pair_qo(blk):
+    qkv(blk); oproj(blk)
+
+
+def seq4(blk):
+    qkv(blk); fused_attn(blk); oproj(blk); gateup(blk)
+
+
+def seq5(blk):
+    qkv(blk); fused_attn(blk); oproj(blk); gateup(blk); down(blk)
+
+
+def seq_aogd(blk):
+    fused_attn(blk); oproj(blk); gateup(blk); down(blk)
+
+
+def seq_agd(blk):
+    fused_attn(blk); gateup(blk); down(blk)
+
+
+def seq_ag(blk):
+    fused_attn(blk); gateup(blk)
+
+
+def seq_ad(blk):
+    fused_attn(blk); down(blk)
+
+
+parts += [("seq q>a>o>g", seq4, 0), ("seq q>a>o>g>d", seq5, 0), ("seq a>o>g>d", seq_aogd, 0), ("seq a>g>d", seq_agd, 0), ("seq a>g", seq_ag, 0), ("seq a>d", seq_ad, 0)]
+parts += [("seq qkv>attn", pair_qa, 0), ("seq attn>oproj", pair_ao, 0), ("seq qkv>attn>oproj", trio, 0), ("seq qkv>oproj", pair_qo, 0)]
 parts.append(("full layer", full_layer, model.blocks[0].weight_bytes + kvb))
+if os.environ.get("PARTS"):
+    keep = os.environ["PARTS"].split(",")
+    parts = [p_ for p_ in parts if any(k in p_[0] for k in keep)]
 tot = 0.0
 print(f"{name} {fmt} ctx {ctx}  (us per launch, averaged over {len(model.blocks)} layers; peak {PEAK:.0f} GB/s)")
 for label, fn, nbytes in parts:

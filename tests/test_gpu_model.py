@@ -31,14 +31,17 @@ def pdl(request):
 
 
 def _check_tokens(got, exp, margins, n_prompt, tops=None):
-    """identical greedy tokens; a divergence is tolerated only at a step whose oracle top-1 / top-2 logits are equal
-    or ADJACENT BF16 numbers (margin <= one BF16 ulp of the top logit: a single flipped rounding swaps them -- a genuine
-    tie), and ends the comparison.  Without the top logits the bar is 2^-6 (one ulp for logits in [2, 4))."""
+    """identical greedy tokens; a divergence is tolerated only at a step whose oracle top-1 / top-2 logits are a genuine
+    tie at BF16 resolution, and ends the comparison.  Both logits are BF16-rounded dot products over a hidden state that
+    went through an f32 summation order different from the oracle's (split-KV attention, tensor-core accumulation): a
+    flipped final rounding moves EITHER of them by one ulp, so two candidates swap only if they are at most TWO BF16
+    ulps of the top logit apart -- far inside the 1e-2 relative bar of the floating-point ops themselves (0.06 for a
+    logit of 6).  Without the top logits the bar is 2^-5 (two ulps for logits in [2, 4))."""
     for i, (g, e) in enumerate(zip(got[n_prompt:], exp[n_prompt:])):
         if g != e:
-            bar = 2.0 ** -6
+            bar = 2.0 ** -5
             if tops is not None:
-                bar = max(bar, 2.0 ** (np.floor(np.log2(max(abs(tops[i]), 1e-30))) - 7))
+                bar = max(bar, 2.0 ** (np.floor(np.log2(max(abs(tops[i]), 1e-30))) - 6))
             assert margins[i] <= bar, f"token {i}: got {g}, oracle {e}, margin {margins[i]} (bar {bar})"
             return i
     return len(exp) - n_prompt
