@@ -207,43 +207,8 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
     if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
 }
 
-// One-token routing inside a warp: top-k by k passes of strict '>' argmax (lowest index wins ties) over E <= 512
-// router logits, then softmax over the selected values in slot order -- the arithmetic of topk_with_indices +
-// softmax_topk (topk_kernels.cuh:111-147,222-256), statement for statement.  Lane j < k returns expert j and its
-// bf16 weight bits.
-__device__ __forceinline__ void moe_route_warp(const uint16_t* __restrict__ logits, int E, int k, int lane, int& my_idx,
-                                               uint16_t& my_w) {
-    constexpr int MAXPL = 16;
-    float loc[MAXPL];
-#pragma unroll
-    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? bf16_bits_to_f32(logits[e]) : -INFINITY; }
-    float mine = -INFINITY;                       // lane j keeps selected value j (k <= 32)
-    my_idx = 0;
-    for (int j = 0; j < k; ++j) {
-        float bv = -1e30f;
-        int bi = 0x7fffffff;
-#pragma unroll
-        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-        }
-        if (bi == 0x7fffffff) bi = 0;
-        if (lane == j) { mine = bf16_bits_to_f32(f32_to_bf16_bits(bv)); my_idx = bi; }
-#pragma unroll
-        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
-    }
-    float mx = mine;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    const float ex = __expf(mine - mx);
-    float sum = 0.f;
-    for (int i = 0; i < k; ++i) sum += __shfl_sync(0xffffffffu, ex, i);     // slot order, as the serial kernel
-    const float inv = 1.0f / sum;
-    my_w = f32_to_bf16_bits(ex * inv);
-}
+// moe_route_warp (top-k + softmax of one token's router logits, one warp) lives in gemv_common.cuh: the router GEMV
+// runs it in its last CTA (pgk_moe_router_t1).
 
 // ---------------------------------------------------------------------------------------------
 // Expert-grouped NVF4 GEMV (net-new: the reference's MoE path is FP8-only, layers/moe.py:86-151).
@@ -258,6 +223,14 @@ constexpr int kMoeNvf4Warps = 16;   // 512 threads: 128 registers per thread (32
 // g = bf16(A . Bg[e]), u = bf16(A . Bu[e]) -- the rounding points of gate GEMV -> silu -> up GEMV -> mul_inplace.
 // (A 32-column CTA form with byte loads and a form that recomputed the routing in every warp were measured slower on
 // B200 and removed; numbers in profiles/r01_bench_qwen3-30b-a3b_*.json and DESIGN.md.)
+// Decode-form fusions (one token, round 2): `gamma` = the RMSNorm before the layer, applied while the activation row is
+// staged (bit-identical to the stand-alone norm: row_inv_rms_ref_order); `comb_out` = the weighted combine after the down
+// GEMV: the R x KS CTAs of a column tile meet in the workspace and the last one sums the R bf16-rounded expert rows
+// in slot order with the router weights (+ residual) -- moe_combine_t1_kernel's arithmetic without its launch.
+struct MoeFuse {
+    const uint16_t* gamma; float eps;
+    const uint16_t* comb_w; const uint16_t* comb_res; uint16_t* comb_out;
+};
 template <int NMAT>
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
 moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd0,
@@ -265,7 +238,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
                              const uint8_t* __restrict__ Bs1, uint16_t* __restrict__ C,
                              const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
                              int expert_offset, int num_local, float* __restrict__ split_ws,
-                             unsigned* __restrict__ split_cnt) {
+                             unsigned* __restrict__ split_cnt, MoeFuse fz) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
     __shared__ unsigned s_ticket;
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
@@ -278,14 +251,23 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int e = row_expert_ids[r] - expert_offset;
     const int c = col0 + lane * CPL;
-    if (e < 0 || e >= num_local) {
+    const bool comb = NMAT == 1 && fz.comb_out != nullptr;
+    const bool local = e >= 0 && e < num_local;
+    if (!local && !comb) {
         if (warp == 0 && c < N) {
 #pragma unroll
             for (int j = 0; j < CPL; ++j) if (c + j < N) C[(size_t)r * N + c + j] = 0;
         }
         return;
     }
-    for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * a_stride + k]);
+    if (fz.gamma) {
+        const uint16_t* row = A + (size_t)r * a_stride;
+        const float inv = row_inv_rms_ref_order(row, K, fz.eps, a_s);
+        for (int k = threadIdx.x; k < K; k += blockDim.x)
+            a_s[k] = round_bf16(bf16_bits_to_f32(row[k]) * inv * bf16_bits_to_f32(__ldg(fz.gamma + k)));
+    } else {
+        for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * a_stride + k]);
+    }
     __syncthreads();
     const uint8_t* bdp[2] = {Bd0 + (size_t)e * (K >> 1) * N, NMAT == 2 ? Bd1 + (size_t)e * (K >> 1) * N : nullptr};
     const uint8_t* bsp[2] = {Bs0 + (size_t)e * ((K + 31) >> 5) * N, NMAT == 2 ? Bs1 + (size_t)e * ((K + 31) >> 5) * N : nullptr};
@@ -302,7 +284,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     const int kper = (KB + KS - 1) / KS;
     const int blk0 = kz * kper, blk1 = min(KB, blk0 + kper);
     const bool full = CPL == 4 && (c + CPL - 1 < N) && ((N & (CPL - 1)) == 0);
-    for (int blk = blk0 + warp; blk < blk1; blk += kMoeNvf4Warps) {
+    for (int blk = blk0 + warp; local && blk < blk1; blk += kMoeNvf4Warps) {
         if (full) {
             uint32_t w[NMAT][16], sw[NMAT];
 #pragma unroll
@@ -369,12 +351,14 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
             for (int w = 0; w < kMoeNvf4Warps; ++w) s[m] += red[(m * kMoeNvf4Warps + w) * TILE + threadIdx.x];
         }
     }
-    if (KS > 1) {
-        const size_t cell = (size_t)r * gridDim.x + blockIdx.x;
-        float* wsp = split_ws + cell * KS * NMAT * TILE;
+    if (KS > 1 || comb) {
+        const int R = (int)gridDim.y;
+        const size_t cell = comb ? (size_t)blockIdx.x : (size_t)r * gridDim.x + blockIdx.x;
+        const int slots = comb ? R * KS : KS, my = comb ? r * KS + kz : kz;
+        float* wsp = split_ws + cell * slots * NMAT * TILE;
         if (threadIdx.x < TILE) {
 #pragma unroll
-            for (int m = 0; m < NMAT; ++m) __stcg(wsp + ((size_t)kz * NMAT + m) * TILE + threadIdx.x, s[m]);
+            for (int m = 0; m < NMAT; ++m) __stcg(wsp + ((size_t)my * NMAT + m) * TILE + threadIdx.x, s[m]);
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -383,7 +367,22 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
             __threadfence();
         }
         __syncthreads();
-        if (s_ticket != (unsigned)(KS - 1)) return;
+        if (s_ticket != (unsigned)(slots - 1)) return;
+        if (comb) {
+            if (threadIdx.x < TILE && col0 + threadIdx.x < N) {
+                float sum = 0.f;
+                for (int rr = 0; rr < R; ++rr) {
+                    float t = 0.f;
+                    for (int zz = 0; zz < KS; ++zz) t += __ldcg(wsp + (size_t)(rr * KS + zz) * TILE + threadIdx.x);
+                    sum = fmaf(bf16_bits_to_f32(fz.comb_w[rr]), round_bf16(t), sum);
+                }
+                uint16_t o = f32_to_bf16_bits(sum);
+                if (fz.comb_res) o = f32_to_bf16_bits(bf16_bits_to_f32(o) + bf16_bits_to_f32(fz.comb_res[col0 + threadIdx.x]));
+                fz.comb_out[col0 + threadIdx.x] = o;
+            }
+            if (threadIdx.x == 0) split_cnt[cell] = 0;
+            return;
+        }
         if (threadIdx.x < TILE) {
 #pragma unroll
             for (int m = 0; m < NMAT; ++m) {
@@ -519,7 +518,7 @@ static unsigned* g_moe_split_cnt = nullptr;
 template <int NMAT>
 static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
                            const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
-                           int expert_offset, int num_local_experts, void* stream) {
+                           int expert_offset, int num_local_experts, void* stream, MoeFuse fz = MoeFuse{}) {
     constexpr int TILE = 128;
     size_t smem = (size_t)K * 4 + (size_t)NMAT * kMoeNvf4Warps * TILE * 4;
     PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
@@ -545,6 +544,9 @@ static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const v
             PGK_CUDA(cudaMemset(cnt, 0, kCells * sizeof(unsigned)));
         }
     }
+    PGK_REQUIRE(!fz.gamma || (K >= 512 && a_stride == 0), "moe_gateup_nvf4_t1 failed: the fused norm needs K >= 512 (K=%d)", K);
+    PGK_REQUIRE(!fz.comb_out || (ws && tiles <= (int)kCells && (size_t)tiles * M * 8 * TILE <= kWsFloats),
+                "moe_down_combine_nvf4_t1 failed: the first call must happen outside graph capture (workspace allocation)");
     int ks = 1;
     const long cells = (long)tiles * M;
     if (ws && cells * 2 <= sm_count() && cells <= (long)kCells) {
@@ -556,7 +558,7 @@ static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const v
     PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel<NMAT>, dim3(tiles, M, ks), dim3(kMoeNvf4Warps * 32), smem,
                     (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
                     (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts,
-                    ws, cnt));
+                    ws, cnt, fz));
     return 0;
 }
 }  // namespace pgk
@@ -659,6 +661,28 @@ int pgk_moe_gateup_nvf4_t1(const void* x, const void* Bg_data, const void* Bg_sc
     return launch_moe_nvf4<2>(x, 0, Bg_data, Bg_scale, Bu_data, Bu_scale, act, row_expert_ids, k, K, N, expert_offset,
                               num_local_experts, stream);
     return 0;
+}
+
+/* gate/up of the routed experts with the layer's RMSNorm applied while x is staged (gamma may be NULL) */
+int pgk_moe_gateup_nvf4_t1_norm(const void* x, const void* gamma, float eps, const void* Bg_data, const void* Bg_scale,
+                                const void* Bu_data, const void* Bu_scale, void* act, const int32_t* row_expert_ids, int k,
+                                int K, int N, int expert_offset, int num_local_experts, void* stream) {
+    if (k <= 0) return 0;
+    PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_gateup_nvf4_t1 failed: K=%d must be a multiple of 32", K);
+    MoeFuse fz = {(const uint16_t*)gamma, eps, nullptr, nullptr, nullptr};
+    return launch_moe_nvf4<2>(x, 0, Bg_data, Bg_scale, Bu_data, Bu_scale, act, row_expert_ids, k, K, N, expert_offset,
+                              num_local_experts, stream, fz);
+}
+/* down GEMV of the k routed experts + weighted combine in slot order (+ residual) in one launch (NVF4 form of
+ * pgk_moe_down_combine_fp8_t1); every expert must be local (no expert parallelism between down and combine) */
+int pgk_moe_down_combine_nvf4_t1(const void* act, const void* Bd_data, const void* Bd_scale, const void* router_weights,
+                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
+                                 int expert_offset, int num_local_experts, void* stream) {
+    if (k <= 0) return 0;
+    PGK_REQUIRE(K % 32 == 0 && K >= 32 && out && router_weights, "moe_down_combine_nvf4_t1 failed: K=%d must be a multiple of 32", K);
+    MoeFuse fz = {nullptr, 0.f, (const uint16_t*)router_weights, (const uint16_t*)residual, (uint16_t*)out};
+    return launch_moe_nvf4<1>(act, K, Bd_data, Bd_scale, nullptr, nullptr, nullptr, row_expert_ids, k, K, N, expert_offset,
+                              num_local_experts, stream, fz);
 }
 
 /* ---- decode (one token) forms: same results as the generic pipeline, fewer launches ---- */
