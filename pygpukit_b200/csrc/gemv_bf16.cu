@@ -47,17 +47,13 @@ struct ArgmaxOut {
     unsigned long long* key;   // scratch, zero between launches
     unsigned* done;            // CTA arrival counter, zero between launches
     int32_t* token;            // result
-    // MODE 2 (MoE router of one token): top-k + softmax of the N logits by the last CTA
-    uint16_t* r_weights = nullptr; int32_t* r_indices = nullptr; int32_t* r_row_ids = nullptr; int r_k = 0;
 };
-// MODE: 0 = GEMV, 1 = + greedy argmax over the rows (lm_head), 2 = + MoE routing of the N logits (router)
 
-template <int M, int MODE>
+template <int M, bool ARGMAX>
 __global__ void __launch_bounds__(512)
 gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B, uint16_t* __restrict__ C,
                  int K, int N, int rho, GemvEpilogue epi, ArgmaxOut am) {
     constexpr int U = 4;
-    constexpr bool ARGMAX = MODE == 1;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint16_t* a_s = reinterpret_cast<uint16_t*>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpc = blockDim.x >> 5;
@@ -139,27 +135,6 @@ gemv_bf16_kernel(const uint16_t* __restrict__ A, const uint16_t* __restrict__ B,
             *am.done = 0;
         }
     }
-    if (MODE == 2) {
-        // the last CTA to finish routes the token: top-k + softmax over the bf16 logits every CTA has stored
-        // (moe_route_t1_kernel's arithmetic, one warp) -- the router and the routing are one launch
-        __shared__ unsigned s_last;
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) s_last = (atomicAdd(am.done, 1u) == gridDim.x - 1);
-        __syncthreads();
-        if (s_last) {
-            __threadfence();
-            for (int e = threadIdx.x; e < N; e += blockDim.x) a_s[e] = __ldcg(C + e);     // the activation row is no longer needed
-            __syncthreads();
-            if (warp == 0) {
-                int idx;
-                uint16_t w;
-                moe_route_warp(a_s, N, am.r_k, lane, idx, w);
-                if (lane < am.r_k) { am.r_indices[lane] = idx; am.r_row_ids[lane] = idx; am.r_weights[lane] = w; }
-                if (lane == 0) *am.done = 0;
-            }
-        }
-    }
 }
 
 template <bool ARGMAX>
@@ -185,12 +160,11 @@ __global__ void gemv_bf16_generic_kernel(const uint16_t* __restrict__ A, const u
 
 static unsigned long long* g_am_scratch = nullptr;  // [0] key, [1] done counter
 
-template <int M, int MODE>
+template <int M, bool ARGMAX>
 static int launch_bf16(const uint16_t* A, const uint16_t* B, uint16_t* C, int K, int N, GemvEpilogue epi,
-                       int32_t* token, cudaStream_t st, const ArgmaxOut* route = nullptr) {
-    constexpr bool ARGMAX = MODE != 0;     // both tails need the arrival counter
+                       int32_t* token, cudaStream_t st) {
     size_t smem = (size_t)M * K * 2;
-    auto kern = gemv_bf16_kernel<M, MODE>;
+    auto kern = gemv_bf16_kernel<M, ARGMAX>;
     static std::mutex mu;
     static std::unordered_map<uint64_t, GemvCfg> cache;
     static bool attr_set = false;
@@ -212,7 +186,6 @@ static int launch_bf16(const uint16_t* A, const uint16_t* B, uint16_t* C, int K,
         cfg = it->second;
     }
     ArgmaxOut am = {nullptr, nullptr, token};
-    if (route) am = *route;
     if (ARGMAX) {
         if (!g_am_scratch) {
             cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
@@ -255,9 +228,9 @@ static int bf16_dispatch(const void* A, const void* B, void* C, int M, int K, in
         GemvEpilogue epi = {(const uint16_t*)bias, residual ? (const uint16_t*)residual + (size_t)m0 * N : nullptr,
                             (const uint16_t*)gamma, eps};
         int rc;
-        if (mt == 1)      rc = launch_bf16<1, 0>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
-        else if (mt == 2) rc = launch_bf16<2, 0>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
-        else              rc = launch_bf16<4, 0>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
+        if (mt == 1)      rc = launch_bf16<1, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
+        else if (mt == 2) rc = launch_bf16<2, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
+        else              rc = launch_bf16<4, false>(a + (size_t)m0 * K, b, c + (size_t)m0 * N, K, N, epi, nullptr, st);
         if (rc) return rc;
         m0 += mt;
     }
@@ -282,7 +255,7 @@ int pgk_gemv_bf16_argmax(const void* A, const void* B_nk, void* logits, int32_t*
     PGK_REQUIRE(K % 16 == 0 && al(A, 16) && al(B_nk, 32) && (size_t)K * 2 <= 200 * 1024,
                 "gemv_bf16_argmax failed: needs K%%16==0 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr};
-    return launch_bf16<1, 1>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
+    return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
 }
 
@@ -296,23 +269,8 @@ int pgk_rmsnorm_gemv_bf16_argmax(const void* A, const void* gamma, float eps, co
     PGK_REQUIRE(K % 16 == 0 && K >= 512 && al(A, 16) && al(B_nk, 32) && al(gamma, 16) && (size_t)K * 2 <= 200 * 1024,
                 "rmsnorm_gemv_bf16_argmax failed: needs K%%16==0, K>=512 and aligned pointers (K=%d)", K);
     GemvEpilogue epi = {nullptr, nullptr, (const uint16_t*)gamma, eps};
-    return launch_bf16<1, 1>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
+    return launch_bf16<1, true>((const uint16_t*)A, (const uint16_t*)B_nk, (uint16_t*)logits, K, N, epi,
                                 token, (cudaStream_t)stream);
-}
-
-/* MoE router of ONE token in one launch: [rmsnorm(x, gamma) ->] logits = x . Wg^T (bf16, stored) -> top-k -> softmax over
- * the selected logits -> router weights / expert indices / row ids (slot order).  Replaces gate GEMV + topk_with_indices
- * + softmax_topk (layers/moe.py:177-200, topk_kernels.cuh:111-256) and, with gamma, the rmsnorm before them. */
-int pgk_moe_router_t1(const void* x, const void* gamma, float eps, const void* Wg_nk, void* logits, void* weights,
-                      int32_t* indices, int32_t* row_expert_ids, int K, int num_experts, int k, void* stream) {
-    PGK_REQUIRE(K % 16 == 0 && al(x, 16) && al(Wg_nk, 32) && (size_t)K * 2 <= 200 * 1024 && (!gamma || (K >= 512 && al(gamma, 16))),
-                "moe_router_t1 failed: needs K%%16==0 (K >= 512 with a fused norm) and aligned pointers (K=%d)", K);
-    PGK_REQUIRE(num_experts >= 1 && num_experts <= 512 && num_experts * 2 <= K * 2 && k >= 1 && k <= 32 && k <= num_experts && logits,
-                "moe_router_t1 failed: needs 1 <= k <= min(32, E), E <= 512 and a logits buffer (E=%d, k=%d)", num_experts, k);
-    GemvEpilogue epi = {nullptr, nullptr, (const uint16_t*)gamma, eps};
-    ArgmaxOut r = {nullptr, nullptr, nullptr, (uint16_t*)weights, indices, row_expert_ids, k};
-    return launch_bf16<1, 2>((const uint16_t*)x, (const uint16_t*)Wg_nk, (uint16_t*)logits, K, num_experts, epi, nullptr,
-                             (cudaStream_t)stream, &r);
 }
 
 }  // extern "C"

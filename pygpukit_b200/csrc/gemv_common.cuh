@@ -291,42 +291,4 @@ __device__ __forceinline__ float silu_ref(float x) {
 
 
 
-// One-token routing inside a warp: top-k by k passes of strict '>' argmax (lowest index wins ties) over E <= 512
-// router logits, then softmax over the selected values in slot order -- the arithmetic of topk_with_indices +
-// softmax_topk (topk_kernels.cuh:111-147,222-256), statement for statement.  Lane j < k returns expert j and its
-// bf16 weight bits.
-__device__ __forceinline__ void moe_route_warp(const uint16_t* __restrict__ logits, int E, int k, int lane, int& my_idx,
-                                               uint16_t& my_w) {
-    constexpr int MAXPL = 16;
-    float loc[MAXPL];
-#pragma unroll
-    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? bf16_bits_to_f32(logits[e]) : -INFINITY; }
-    float mine = -INFINITY;                       // lane j keeps selected value j (k <= 32)
-    my_idx = 0;
-    for (int j = 0; j < k; ++j) {
-        float bv = -1e30f;
-        int bi = 0x7fffffff;
-#pragma unroll
-        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-        }
-        if (bi == 0x7fffffff) bi = 0;
-        if (lane == j) { mine = bf16_bits_to_f32(f32_to_bf16_bits(bv)); my_idx = bi; }
-#pragma unroll
-        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
-    }
-    float mx = mine;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    const float ex = __expf(mine - mx);
-    float sum = 0.f;
-    for (int i = 0; i < k; ++i) sum += __shfl_sync(0xffffffffu, ex, i);     // slot order, as the serial kernel
-    const float inv = 1.0f / sum;
-    my_w = f32_to_bf16_bits(ex * inv);
-}
-
 }  // namespace pgk

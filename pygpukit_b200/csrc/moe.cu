@@ -134,7 +134,7 @@ __global__ void moe_scatter_kernel(const uint16_t* __restrict__ expert_out, cons
 // Lane-partial dot products of one bf16 activation row with NB FP8 weight rows (block scales per
 // 128 k), then a warp sum: 128-bit weight loads, exact f32 products, lane-strided 16-k chunks.  Every
 // expert GEMV below goes through this one function, so fused and unfused forms agree bit for bit.
-template <int NB>
+template <int NB, bool CLEAN>
 __device__ __forceinline__ void fp8_rows_dot(const uint16_t* __restrict__ arow, const uint8_t* const (&brow)[NB],
                                              const uint16_t* const (&srow)[NB], int K, int lane, float (&acc)[NB]) {
 #pragma unroll
@@ -158,7 +158,8 @@ __device__ __forceinline__ void fp8_rows_dot(const uint16_t* __restrict__ arow, 
                     float2 f1 = __half22float2(*reinterpret_cast<__half2*>(&h1));
                     // codes 0x7F / 0xFF are +-480 in the reference's tables (fp8.cuh:89,121), NaN for the hardware
                     // conversion: a byte whose low seven bits are all ones carries into bit 7 when 1 is added
-                    if (((ww[q] & 0x7f7f7f7fu) + 0x01010101u) & 0x80808080u) {
+                    // (CLEAN: the tensor was scanned once on the host side and holds neither code -- gemv_fp8.cu::fp8_codes_clean)
+                    if (!CLEAN && (((ww[q] & 0x7f7f7f7fu) + 0x01010101u) & 0x80808080u)) {
                         f0.x = fp8_e4m3_to_f32(ww[q] & 0xffu); f0.y = fp8_e4m3_to_f32((ww[q] >> 8) & 0xffu);
                         f1.x = fp8_e4m3_to_f32((ww[q] >> 16) & 0xffu); f1.y = fp8_e4m3_to_f32(ww[q] >> 24);
                     }
@@ -183,6 +184,7 @@ __device__ __forceinline__ void fp8_rows_dot(const uint16_t* __restrict__ arow, 
 // Expert-grouped FP8 GEMV: row m uses expert row_expert_ids[m] of B[E,N,K], S[E,N/128,K/128].
 // One warp per (m, n): 128-bit weight loads, exact f32 products (bf16 activation x decoded
 // e4m3), scale per 128-k block.  K % 16 == 0 fast path, scalar tail otherwise.
+template <bool CLEAN>
 __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B,
                                             const uint16_t* __restrict__ S, uint16_t* __restrict__ C,
                                             const int32_t* __restrict__ row_ids, int M, int K, int N,
@@ -202,13 +204,48 @@ __global__ void moe_grouped_gemv_fp8_kernel(const uint16_t* __restrict__ A, cons
     const uint8_t* brow[1] = {B + ((size_t)e * N + n) * K};
     const uint16_t* srow[1] = {S + ((size_t)e * SN + (n >> 7)) * SK};
     float acc1[1];
-    fp8_rows_dot<1>(A + (size_t)m * a_stride, brow, srow, K, lane, acc1);
+    fp8_rows_dot<1, CLEAN>(A + (size_t)m * a_stride, brow, srow, K, lane, acc1);
     float acc = acc1[0];
     if (lane == 0) C[(size_t)m * N + n] = f32_to_bf16_bits(acc);
 }
 
-// moe_route_warp (top-k + softmax of one token's router logits, one warp) lives in gemv_common.cuh: the router GEMV
-// runs it in its last CTA (pgk_moe_router_t1).
+// One-token routing inside a warp: top-k by k passes of strict '>' argmax (lowest index wins ties) over E <= 512
+// router logits, then softmax over the selected values in slot order -- the arithmetic of topk_with_indices +
+// softmax_topk (topk_kernels.cuh:111-147,222-256), statement for statement.  Lane j < k returns expert j and its
+// bf16 weight bits.
+__device__ __forceinline__ void moe_route_warp(const uint16_t* __restrict__ logits, int E, int k, int lane, int& my_idx,
+                                               uint16_t& my_w) {
+    constexpr int MAXPL = 16;
+    float loc[MAXPL];
+#pragma unroll
+    for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; loc[i] = (e < E) ? bf16_bits_to_f32(logits[e]) : -INFINITY; }
+    float mine = -INFINITY;                       // lane j keeps selected value j (k <= 32)
+    my_idx = 0;
+    for (int j = 0; j < k; ++j) {
+        float bv = -1e30f;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) { int e = lane + 32 * i; if (e < E && loc[i] > bv) { bv = loc[i]; bi = e; } }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (bi == 0x7fffffff) bi = 0;
+        if (lane == j) { mine = bf16_bits_to_f32(f32_to_bf16_bits(bv)); my_idx = bi; }
+#pragma unroll
+        for (int i = 0; i < MAXPL; ++i) if (lane + 32 * i == bi) loc[i] = -1e30f;
+    }
+    float mx = mine;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const float ex = __expf(mine - mx);
+    float sum = 0.f;
+    for (int i = 0; i < k; ++i) sum += __shfl_sync(0xffffffffu, ex, i);     // slot order, as the serial kernel
+    const float inv = 1.0f / sum;
+    my_w = f32_to_bf16_bits(ex * inv);
+}
 
 // ---------------------------------------------------------------------------------------------
 // Expert-grouped NVF4 GEMV (net-new: the reference's MoE path is FP8-only, layers/moe.py:86-151).
@@ -223,14 +260,6 @@ constexpr int kMoeNvf4Warps = 16;   // 512 threads: 128 registers per thread (32
 // g = bf16(A . Bg[e]), u = bf16(A . Bu[e]) -- the rounding points of gate GEMV -> silu -> up GEMV -> mul_inplace.
 // (A 32-column CTA form with byte loads and a form that recomputed the routing in every warp were measured slower on
 // B200 and removed; numbers in profiles/r01_bench_qwen3-30b-a3b_*.json and DESIGN.md.)
-// Decode-form fusions (one token, round 2): `gamma` = the RMSNorm before the layer, applied while the activation row is
-// staged (bit-identical to the stand-alone norm: row_inv_rms_ref_order); `comb_out` = the weighted combine after the down
-// GEMV: the R x KS CTAs of a column tile meet in the workspace and the last one sums the R bf16-rounded expert rows
-// in slot order with the router weights (+ residual) -- moe_combine_t1_kernel's arithmetic without its launch.
-struct MoeFuse {
-    const uint16_t* gamma; float eps;
-    const uint16_t* comb_w; const uint16_t* comb_res; uint16_t* comb_out;
-};
 template <int NMAT>
 __global__ void __launch_bounds__(kMoeNvf4Warps * 32)
 moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ Bd0,
@@ -238,7 +267,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
                              const uint8_t* __restrict__ Bs1, uint16_t* __restrict__ C,
                              const int32_t* __restrict__ row_expert_ids, int K, int N, int a_stride,
                              int expert_offset, int num_local, float* __restrict__ split_ws,
-                             unsigned* __restrict__ split_cnt, MoeFuse fz) {
+                             unsigned* __restrict__ split_cnt) {
     extern __shared__ __align__(16) unsigned char moe_smem[];
     __shared__ unsigned s_ticket;
     float* a_s = reinterpret_cast<float*>(moe_smem);                  // [K]
@@ -251,23 +280,14 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int e = row_expert_ids[r] - expert_offset;
     const int c = col0 + lane * CPL;
-    const bool comb = NMAT == 1 && fz.comb_out != nullptr;
-    const bool local = e >= 0 && e < num_local;
-    if (!local && !comb) {
+    if (e < 0 || e >= num_local) {
         if (warp == 0 && c < N) {
 #pragma unroll
             for (int j = 0; j < CPL; ++j) if (c + j < N) C[(size_t)r * N + c + j] = 0;
         }
         return;
     }
-    if (fz.gamma) {
-        const uint16_t* row = A + (size_t)r * a_stride;
-        const float inv = row_inv_rms_ref_order(row, K, fz.eps, a_s);
-        for (int k = threadIdx.x; k < K; k += blockDim.x)
-            a_s[k] = round_bf16(bf16_bits_to_f32(row[k]) * inv * bf16_bits_to_f32(__ldg(fz.gamma + k)));
-    } else {
-        for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * a_stride + k]);
-    }
+    for (int k = threadIdx.x; k < K; k += blockDim.x) a_s[k] = bf16_bits_to_f32(A[(size_t)r * a_stride + k]);
     __syncthreads();
     const uint8_t* bdp[2] = {Bd0 + (size_t)e * (K >> 1) * N, NMAT == 2 ? Bd1 + (size_t)e * (K >> 1) * N : nullptr};
     const uint8_t* bsp[2] = {Bs0 + (size_t)e * ((K + 31) >> 5) * N, NMAT == 2 ? Bs1 + (size_t)e * ((K + 31) >> 5) * N : nullptr};
@@ -284,7 +304,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
     const int kper = (KB + KS - 1) / KS;
     const int blk0 = kz * kper, blk1 = min(KB, blk0 + kper);
     const bool full = CPL == 4 && (c + CPL - 1 < N) && ((N & (CPL - 1)) == 0);
-    for (int blk = blk0 + warp; local && blk < blk1; blk += kMoeNvf4Warps) {
+    for (int blk = blk0 + warp; blk < blk1; blk += kMoeNvf4Warps) {
         if (full) {
             uint32_t w[NMAT][16], sw[NMAT];
 #pragma unroll
@@ -351,14 +371,12 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
             for (int w = 0; w < kMoeNvf4Warps; ++w) s[m] += red[(m * kMoeNvf4Warps + w) * TILE + threadIdx.x];
         }
     }
-    if (KS > 1 || comb) {
-        const int R = (int)gridDim.y;
-        const size_t cell = comb ? (size_t)blockIdx.x : (size_t)r * gridDim.x + blockIdx.x;
-        const int slots = comb ? R * KS : KS, my = comb ? r * KS + kz : kz;
-        float* wsp = split_ws + cell * slots * NMAT * TILE;
+    if (KS > 1) {
+        const size_t cell = (size_t)r * gridDim.x + blockIdx.x;
+        float* wsp = split_ws + cell * KS * NMAT * TILE;
         if (threadIdx.x < TILE) {
 #pragma unroll
-            for (int m = 0; m < NMAT; ++m) __stcg(wsp + ((size_t)my * NMAT + m) * TILE + threadIdx.x, s[m]);
+            for (int m = 0; m < NMAT; ++m) __stcg(wsp + ((size_t)kz * NMAT + m) * TILE + threadIdx.x, s[m]);
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -367,22 +385,7 @@ moe_grouped_gemv_nvf4_kernel(const uint16_t* __restrict__ A, const uint8_t* __re
             __threadfence();
         }
         __syncthreads();
-        if (s_ticket != (unsigned)(slots - 1)) return;
-        if (comb) {
-            if (threadIdx.x < TILE && col0 + threadIdx.x < N) {
-                float sum = 0.f;
-                for (int rr = 0; rr < R; ++rr) {
-                    float t = 0.f;
-                    for (int zz = 0; zz < KS; ++zz) t += __ldcg(wsp + (size_t)(rr * KS + zz) * TILE + threadIdx.x);
-                    sum = fmaf(bf16_bits_to_f32(fz.comb_w[rr]), round_bf16(t), sum);
-                }
-                uint16_t o = f32_to_bf16_bits(sum);
-                if (fz.comb_res) o = f32_to_bf16_bits(bf16_bits_to_f32(o) + bf16_bits_to_f32(fz.comb_res[col0 + threadIdx.x]));
-                fz.comb_out[col0 + threadIdx.x] = o;
-            }
-            if (threadIdx.x == 0) split_cnt[cell] = 0;
-            return;
-        }
+        if (s_ticket != (unsigned)(KS - 1)) return;
         if (threadIdx.x < TILE) {
 #pragma unroll
             for (int m = 0; m < NMAT; ++m) {
@@ -426,6 +429,7 @@ __global__ void moe_route_t1_kernel(const uint16_t* __restrict__ logits, uint16_
 
 // gate and up GEMVs of the k routed experts + silu + multiply in one launch: one warp per (slot, n)
 // reads x once for both weight rows.  act = bf16(bf16(silu(bf16 gate)) * bf16 up), the three-launch form.
+template <bool CLEAN>
 __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ Bg,
                                          const uint16_t* __restrict__ Sg, const uint8_t* __restrict__ Bu,
                                          const uint16_t* __restrict__ Su, uint16_t* __restrict__ act,
@@ -447,7 +451,7 @@ __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const u
     const uint8_t* brow[2] = {Bg + wo, Bu + wo};
     const uint16_t* srow[2] = {Sg + so, Su + so};
     float acc[2];
-    fp8_rows_dot<2>(x, brow, srow, K, lane, acc);
+    fp8_rows_dot<2, CLEAN>(x, brow, srow, K, lane, acc);
     if (lane == 0) {
         const float g = bf16_bits_to_f32(f32_to_bf16_bits(acc[0]));
         const float u = bf16_bits_to_f32(f32_to_bf16_bits(acc[1]));
@@ -458,6 +462,7 @@ __global__ void moe_gateup_fp8_t1_kernel(const uint16_t* __restrict__ x, const u
 
 // down GEMV of the k routed experts + weighted combine in slot order (+ residual): CTA = cols x k
 // warps, warp (c, s) owns expert row n0+c of slot s; the k rounded results meet in shared memory.
+template <bool CLEAN>
 __global__ void moe_down_combine_fp8_t1_kernel(const uint16_t* __restrict__ act, const uint8_t* __restrict__ Bd,
                                                const uint16_t* __restrict__ Sd, const uint16_t* __restrict__ weights,
                                                const int32_t* __restrict__ row_ids, const uint16_t* __restrict__ residual,
@@ -477,7 +482,7 @@ __global__ void moe_down_combine_fp8_t1_kernel(const uint16_t* __restrict__ act,
             const uint8_t* brow[1] = {Bd + ((size_t)e * N + n) * K};
             const uint16_t* srow[1] = {Sd + ((size_t)e * SN + (n >> 7)) * SK};
             float acc[1];
-            fp8_rows_dot<1>(act + (size_t)sl * K, brow, srow, K, lane, acc);
+            fp8_rows_dot<1, CLEAN>(act + (size_t)sl * K, brow, srow, K, lane, acc);
             d = bf16_bits_to_f32(f32_to_bf16_bits(acc[0]));
         }
     }
@@ -518,7 +523,7 @@ static unsigned* g_moe_split_cnt = nullptr;
 template <int NMAT>
 static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const void* Bs0, const void* Bd1,
                            const void* Bs1, void* C, const int32_t* row_expert_ids, int M, int K, int N,
-                           int expert_offset, int num_local_experts, void* stream, MoeFuse fz = MoeFuse{}) {
+                           int expert_offset, int num_local_experts, void* stream) {
     constexpr int TILE = 128;
     size_t smem = (size_t)K * 4 + (size_t)NMAT * kMoeNvf4Warps * TILE * 4;
     PGK_REQUIRE(smem <= 200 * 1024, "moe_grouped_gemv_nvf4 failed: K=%d too large", K);
@@ -544,9 +549,6 @@ static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const v
             PGK_CUDA(cudaMemset(cnt, 0, kCells * sizeof(unsigned)));
         }
     }
-    PGK_REQUIRE(!fz.gamma || (K >= 512 && a_stride == 0), "moe_gateup_nvf4_t1 failed: the fused norm needs K >= 512 (K=%d)", K);
-    PGK_REQUIRE(!fz.comb_out || (ws && tiles <= (int)kCells && (size_t)tiles * M * 8 * TILE <= kWsFloats),
-                "moe_down_combine_nvf4_t1 failed: the first call must happen outside graph capture (workspace allocation)");
     int ks = 1;
     const long cells = (long)tiles * M;
     if (ws && cells * 2 <= sm_count() && cells <= (long)kCells) {
@@ -558,13 +560,21 @@ static int launch_moe_nvf4(const void* A, int a_stride, const void* Bd0, const v
     PGK_CUDA(launch(moe_grouped_gemv_nvf4_kernel<NMAT>, dim3(tiles, M, ks), dim3(kMoeNvf4Warps * 32), smem,
                     (cudaStream_t)stream, (const uint16_t*)A, (const uint8_t*)Bd0, (const uint8_t*)Bs0, (const uint8_t*)Bd1,
                     (const uint8_t*)Bs1, (uint16_t*)C, row_expert_ids, K, N, a_stride, expert_offset, num_local_experts,
-                    ws, cnt, fz));
+                    ws, cnt));
     return 0;
 }
 }  // namespace pgk
 
 using namespace pgk;
 #define ST(s) ((cudaStream_t)(s))
+
+// One scan per stacked expert tensor (cached by pointer): tensors without the codes 0x7F / 0xFF take the kernels
+// without the per-word test for them.  An unknown expert count (0x7fffffff) keeps the exact kernels.
+static int moe_fp8_clean(const void* B_enk, int num_local, int N, int K, void* stream, bool* clean) {
+    *clean = false;
+    if (num_local <= 0 || num_local == 0x7fffffff) return 0;
+    return pgk::fp8_codes_clean(B_enk, (size_t)num_local * N * K, ST(stream), clean);
+}
 
 extern "C" {
 
@@ -628,7 +638,10 @@ int pgk_moe_grouped_gemv_fp8_ex(const void* A, int a_stride, const void* B_enk, 
     if (M <= 0) return 0;
     PGK_REQUIRE(a_stride == 0 || a_stride >= K, "moe_grouped_gemv_fp8 failed: a_stride=%d must be 0 (broadcast) or >= K", a_stride);
     size_t warps = (size_t)M * N;
-    PGK_CUDA(launch(moe_grouped_gemv_fp8_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream),
+    bool clean;
+    if (int rc = moe_fp8_clean(B_enk, num_local_experts, N, K, stream, &clean)) return rc;
+    auto kern = clean ? moe_grouped_gemv_fp8_kernel<true> : moe_grouped_gemv_fp8_kernel<false>;
+    PGK_CUDA(launch(kern, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream),
                     (const uint16_t*)A, (const uint8_t*)B_enk, (const uint16_t*)S, (uint16_t*)C, row_expert_ids, M, K, N,
                     a_stride, expert_offset, num_local_experts));
     return 0;
@@ -663,28 +676,6 @@ int pgk_moe_gateup_nvf4_t1(const void* x, const void* Bg_data, const void* Bg_sc
     return 0;
 }
 
-/* gate/up of the routed experts with the layer's RMSNorm applied while x is staged (gamma may be NULL) */
-int pgk_moe_gateup_nvf4_t1_norm(const void* x, const void* gamma, float eps, const void* Bg_data, const void* Bg_scale,
-                                const void* Bu_data, const void* Bu_scale, void* act, const int32_t* row_expert_ids, int k,
-                                int K, int N, int expert_offset, int num_local_experts, void* stream) {
-    if (k <= 0) return 0;
-    PGK_REQUIRE(K % 32 == 0 && K >= 32, "moe_gateup_nvf4_t1 failed: K=%d must be a multiple of 32", K);
-    MoeFuse fz = {(const uint16_t*)gamma, eps, nullptr, nullptr, nullptr};
-    return launch_moe_nvf4<2>(x, 0, Bg_data, Bg_scale, Bu_data, Bu_scale, act, row_expert_ids, k, K, N, expert_offset,
-                              num_local_experts, stream, fz);
-}
-/* down GEMV of the k routed experts + weighted combine in slot order (+ residual) in one launch (NVF4 form of
- * pgk_moe_down_combine_fp8_t1); every expert must be local (no expert parallelism between down and combine) */
-int pgk_moe_down_combine_nvf4_t1(const void* act, const void* Bd_data, const void* Bd_scale, const void* router_weights,
-                                 const int32_t* row_expert_ids, const void* residual, void* out, int k, int K, int N,
-                                 int expert_offset, int num_local_experts, void* stream) {
-    if (k <= 0) return 0;
-    PGK_REQUIRE(K % 32 == 0 && K >= 32 && out && router_weights, "moe_down_combine_nvf4_t1 failed: K=%d must be a multiple of 32", K);
-    MoeFuse fz = {nullptr, 0.f, (const uint16_t*)router_weights, (const uint16_t*)residual, (uint16_t*)out};
-    return launch_moe_nvf4<1>(act, K, Bd_data, Bd_scale, nullptr, nullptr, nullptr, row_expert_ids, k, K, N, expert_offset,
-                              num_local_experts, stream, fz);
-}
-
 /* ---- decode (one token) forms: same results as the generic pipeline, fewer launches ---- */
 int pgk_moe_route_t1(const void* logits, void* weights, int32_t* indices, int32_t* row_expert_ids, int num_experts,
                      int k, void* stream) {
@@ -699,7 +690,11 @@ int pgk_moe_gateup_fp8_t1(const void* x, const void* Bg_enk, const void* Sg, con
                           int num_local_experts, void* stream) {
     if (k <= 0) return 0;
     size_t warps = (size_t)k * N;
-    PGK_CUDA(launch(moe_gateup_fp8_t1_kernel, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
+    bool cg, cu;
+    if (int rc = moe_fp8_clean(Bg_enk, num_local_experts, N, K, stream, &cg)) return rc;
+    if (int rc = moe_fp8_clean(Bu_enk, num_local_experts, N, K, stream, &cu)) return rc;
+    auto kern = (cg && cu) ? moe_gateup_fp8_t1_kernel<true> : moe_gateup_fp8_t1_kernel<false>;
+    PGK_CUDA(launch(kern, dim3(nblk(warps * 32, 256)), dim3(256), 0, ST(stream), (const uint16_t*)x,
                     (const uint8_t*)Bg_enk, (const uint16_t*)Sg, (const uint8_t*)Bu_enk, (const uint16_t*)Su,
                     (uint16_t*)act, row_expert_ids, k, K, N, expert_offset, num_local_experts));
     return 0;
@@ -709,7 +704,10 @@ int pgk_moe_down_combine_fp8_t1(const void* act, const void* Bd_enk, const void*
                                 int expert_offset, int num_local_experts, void* stream) {
     PGK_REQUIRE(k >= 1 && k <= 32, "moe_down_combine_fp8_t1 failed: unsupported k=%d", k);
     const int cols = k > 16 ? 1 : (16 / k > 4 ? 4 : 16 / k);   // <= 512-thread CTAs (k <= 16), several resident per SM
-    PGK_CUDA(launch(moe_down_combine_fp8_t1_kernel, dim3((N + cols - 1) / cols), dim3(cols * k * 32), 0, ST(stream),
+    bool clean;
+    if (int rc = moe_fp8_clean(Bd_enk, num_local_experts, N, K, stream, &clean)) return rc;
+    auto kern = clean ? moe_down_combine_fp8_t1_kernel<true> : moe_down_combine_fp8_t1_kernel<false>;
+    PGK_CUDA(launch(kern, dim3((N + cols - 1) / cols), dim3(cols * k * 32), 0, ST(stream),
                     (const uint16_t*)act, (const uint8_t*)Bd_enk, (const uint16_t*)Sd, (const uint16_t*)router_weights,
                     row_expert_ids, (const uint16_t*)residual, (uint16_t*)out, k, K, N, cols, expert_offset,
                     num_local_experts));

@@ -446,6 +446,34 @@ def test_moe_routing_bit_exact():
     assert np.array_equal(outp.to_numpy(), orc.moe_scatter_bf16(eo, vals.to_numpy(), rr, T, k))
 
 
+@pytest.mark.parametrize("hot", [False, True])
+def test_grouped_gemv_fp8_scanned_tensor_paths(hot):
+    """The expert-parallel entry (which knows how many experts the stacked tensor holds) scans the tensor once: without
+    the codes 0x7F / 0xFF it runs the kernel without the per-word test for them, with them the exact kernel -- both give
+    what the unscanned entry gives (bit for bit) and what the oracle's table semantics say."""
+    from tests.util import rand_fp8_weights
+    rng = np.random.default_rng(15)
+    E, N, K, M = 4, 256, 384, 9
+    cs = [rand_fp8_weights(rng, N, K) for _ in range(E)]
+    B = np.stack([c[0] for c in cs])
+    S = np.stack([c[1] for c in cs])
+    if hot:
+        idx = rng.integers(0, B.size, 64)
+        B.reshape(-1)[idx[:32]] = 0x7F
+        B.reshape(-1)[idx[32:]] = 0xFF
+    else:
+        assert not np.any((B & 0x7F) == 0x7F)
+    ids = np.sort(rng.integers(0, E, M)).astype(np.int32)
+    A = rand_bf16(rng, (M, K))
+    gA, gB, gS, gI = gk.from_numpy(A), gk.from_numpy(B), gk.from_numpy(S), gk.from_numpy(ids)
+    plain = ops.grouped_gemm_fp8_bf16(gA, gB, gS, gI).to_numpy()
+    out = gk.empty((M, N), gk.bfloat16)
+    api.moe_grouped_gemv_fp8_ep(gA.device_ptr, gB.device_ptr, gS.device_ptr, out.device_ptr, gI.device_ptr, M, K, N, 0, E, None)
+    assert np.array_equal(out.to_numpy(), plain)
+    ref = orc.grouped_gemm_fp8_bf16(A, B, S, ids)
+    assert np.isfinite(f32(ref)).all() and rel_err(out.to_numpy(), ref) < 2e-3
+
+
 def test_grouped_gemm_fp8():
     from tests.util import rand_fp8_weights
     rng = np.random.default_rng(14)
