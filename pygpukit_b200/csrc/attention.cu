@@ -493,8 +493,9 @@ template <int kMStages>
 __global__ void __launch_bounds__(kMThreads, 2)
 rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_constant__ CUtensorMap vmap, RopeSdpaParams p) {
     constexpr int HD = 128, RT = kMRT, REC = kMRec;
+    constexpr int SREC = 136;                                  // row stride of the CTA merge buffer: float2 stores of a half-warp stay conflict-free
     extern __shared__ unsigned char dyn_raw[];
-    __shared__ __align__(16) uint16_t q_s[RT][HD];
+    __shared__ __align__(16) uint16_t q_s[RT][HD + 8];          // +16 bytes per row: the fragment loads of 8 rows x 4 words hit 32 banks
     __shared__ __align__(16) uint16_t new_s[2][HD];           // new K row, new V row
     __shared__ __align__(8) uint64_t full_bar[kMStages];
     __shared__ __align__(8) uint64_t empty_bar[kMStages];
@@ -702,7 +703,7 @@ rope_sdpa_mma_kernel(const __grid_constant__ CUtensorMap kmap, const __grid_cons
         l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
     }
     __syncthreads();                                           // every stage is consumed: its memory is free for the merge
-    float (*sm_part)[RT][REC] = reinterpret_cast<float (*)[RT][REC]>(tiles_g);
+    float (*sm_part)[RT][SREC] = reinterpret_cast<float (*)[RT][SREC]>(tiles_g);
     if (warp < kMW) {
         const int qrow = lane >> 2, kk = (lane & 3) * 2;
 #pragma unroll

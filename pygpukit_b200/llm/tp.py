@@ -67,6 +67,8 @@ def combine_greedy(pairs: np.ndarray, vocab_offsets: list[int]) -> int:
     return int(vocab_offsets[best] + int(idx[best]))
 
 
+_TIMING_SKIP_EXCHANGE = __import__("os").environ.get("PGK_TP_SKIP_EXCHANGE", "0") == "1"
+
 class TensorParallel:
     """NCCL communicator of this process (rank <-> GPU)."""
 
@@ -149,6 +151,8 @@ class TensorParallel:
             return
         from .._lib import api
         from ..core.stream import current_stream_handle
+        if _TIMING_SKIP_EXCHANGE:       # timing experiment only (wrong tokens): what the step costs without any exchange
+            return
         if self._p2p and part.size % 8 == 0 and part.size <= 8192 and self._ll:
             # one decode row: LL words (payload + exchange number in one 8-byte store), one NVLink hop, no fence
             api.p2p_ll_allreduce_add_bf16(part.device_ptr, hidden.device_ptr, hidden.device_ptr, part.size,
