@@ -137,9 +137,12 @@ def build_random_model(name: str = "qwen3-8b", weight_format: str = "fp8", max_s
                                        mlp, comm=comm))
     # lm_head: column-parallel over the vocabulary (rank keeps V/world rows)
     V = config.vocab_size
+    if V % max(world, shards, 1):
+        raise ValueError(f"vocab_size {V} is not a multiple of the tensor-parallel world size {max(world, shards)} "
+                         "(equal lm_head shards only: pad the vocabulary)")
     if world > 1:
         lo = rank * (V // world)
-        hi = V if rank == world - 1 else lo + V // world
+        hi = lo + V // world
         head = normal_bf16((hi - lo, H), _seed(seed, 0, "lm_head", rank), std)
     elif shards > 1:
         per = V // shards

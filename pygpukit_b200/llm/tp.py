@@ -44,11 +44,14 @@ def shard_plan(config, world: int, rank: int) -> dict:
         kv1 = kv0 + 1
     else:
         kv0, kv1 = shard_range(config.num_kv_heads, world, rank)
+    if config.vocab_size % world != 0:
+        # equal lm_head shards only: the logits all-gather and the (local argmax, global index) exchange both assume
+        # V / world rows per rank -- pad the vocabulary (rows of -inf logits) rather than giving one rank the remainder
+        raise ValueError(f"vocab_size {config.vocab_size} is not a multiple of the tensor-parallel world size {world}")
     plan = {
         "q_rows": (q0 * hd, q1 * hd), "k_rows": (kv0 * hd, kv1 * hd), "v_rows": (kv0 * hd, kv1 * hd),
         "o_cols": (q0 * hd, q1 * hd),
-        "vocab_rows": shard_range(config.vocab_size, world, rank) if config.vocab_size % world == 0 else
-        (rank * (config.vocab_size // world), config.vocab_size if rank == world - 1 else (rank + 1) * (config.vocab_size // world)),
+        "vocab_rows": shard_range(config.vocab_size, world, rank),
     }
     if config.is_moe:
         plan["experts"] = shard_range(config.num_experts, world, rank)
