@@ -433,6 +433,15 @@ int pgk_p2p_ll_allreduce_add_bf16(const void* partial, const void* residual, voi
 /* greedy token of a vocabulary-sharded lm_head: token_buf[0] = local argmax index in, global token out (16 bytes per
  * rank over NVLink instead of an all-gather of the logits) */
 int pgk_p2p_ll_argmax_bf16(const void* logits_local, int32_t* token_buf, int vocab_offset, void* stream);
+/* Row-parallel linear of ONE token + the all-reduce after it (+ residual) in ONE launch: the thread that finishes output
+ * element n publishes its bf16 partial to every rank as an LL word over peer memory and sums the ranks' words in rank order
+ * -- pgk_gemv_*_bf16 followed by pgk_p2p_ll_allreduce_add_bf16, bit for bit, without the second launch and with the NVLink
+ * hop hidden behind the rows still being computed.  `out` may alias `residual` (the hidden state updated in place).
+ * Needs pgk_p2p_open, N <= 8192 and the streaming kernels' shape rules (they fail loudly otherwise). */
+int pgk_gemv_fp8_allreduce_bf16(const void* A, const void* B_nk, const void* S, const void* residual, void* out, int K,
+                                int N, void* stream);
+int pgk_gemv_nvf4_allreduce_bf16(const void* A, const void* B_data, const void* B_scale, const void* residual, void* out,
+                                 int K, int N, float alpha, void* stream);
 int pgk_p2p_error(int* host_flag);
 int pgk_p2p_destroy(void);
 

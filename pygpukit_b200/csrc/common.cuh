@@ -22,6 +22,20 @@ int  sm_count();
 // (outside graph capture), and remembered by base pointer: tensors that hold such codes are served by the exact
 // table-semantics kernel, so one entry point gives one answer.  pgk_free() forgets the pointer.
 int  fp8_codes_clean(const void* codes, size_t nbytes, cudaStream_t st, bool* clean);
+// A row-parallel GEMV and the all-reduce after it in ONE launch (tensor parallel decode): the thread that finishes output
+// element n publishes its bf16 partial to every rank as an 8-byte LL word {bits, exchange number} over peer memory and
+// sums the words of all ranks in rank order (+ residual) -- the arithmetic of p2p_ll_allreduce_add_kernel (p2p.cu),
+// without its launch.  world == 0: no exchange.
+struct GemvXchg {
+    unsigned char* ll[8];     // LL region of every rank (peer-mapped pointers)
+    unsigned* epoch;          // exchange number of the last completed exchange (device word, advanced identically on every rank)
+    unsigned* done;           // arrival counter of the CTAs that take part in the exchange (zero between launches)
+    unsigned* err;            // set when a wait timed out (a peer is gone)
+    int rank, world;
+    unsigned slot_words;      // words per source rank in a region
+    unsigned par_bytes;       // bytes between the two parity halves of a region
+};
+bool p2p_gemv_xchg(GemvXchg* x);     // p2p.cu: false until the peer buffers are open
 void fp8_codes_forget(const void* base);
 
 

@@ -40,7 +40,42 @@ struct GemvEpilogue {
     const uint16_t* residual;  // [M,N] bf16 or null
     const uint16_t* norm_gamma = nullptr;  // [K] bf16: A <- bf16(rmsnorm(A) * gamma) while staging, or null
     float norm_eps = 0.f;
+    GemvXchg xchg = {};                    // world > 1: all-reduce over the ranks before the residual add (M == 1)
 };
+
+// ---- in-kernel all-reduce of one output element (see GemvXchg).  `lanes` cooperating threads (lane index `l`): lane r
+// publishes to rank r and fetches rank r's word; the caller sums `vals` in rank order.  Returns this lane's fetched value
+// (its own partial for r == rank); lanes >= world return 0.
+__device__ __forceinline__ void xchg_publish(const GemvXchg& x, unsigned seq, int n, uint16_t mine, int r) {
+    unsigned char* dst = x.ll[r] + (size_t)(seq & 1u) * x.par_bytes + ((size_t)x.rank * x.slot_words + (size_t)n) * 8;
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(dst), "r"((uint32_t)mine), "r"(seq) : "memory");
+}
+__device__ __forceinline__ float xchg_fetch(const GemvXchg& x, unsigned seq, int n, int r) {
+    const unsigned char* src = x.ll[x.rank] + (size_t)(seq & 1u) * x.par_bytes + ((size_t)r * x.slot_words + (size_t)n) * 8;
+    uint32_t d, f;
+    const long long t0 = clock64();
+    for (;;) {
+        asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(d), "=r"(f) : "l"(src) : "memory");
+        if (f == seq) break;
+        if (clock64() - t0 > 4000000000LL) { *x.err = 1u; break; }        // ~2 s: a peer is gone; do not hang the GPU
+    }
+    return bf16_bits_to_f32(d & 0xffffu);
+}
+// one thread does the whole element (used where a thread, not a warp, owns an output column)
+__device__ __forceinline__ uint16_t xchg_reduce_1t(const GemvXchg& x, unsigned seq, int n, uint16_t mine, const uint16_t* residual) {
+    for (int r = 0; r < x.world; ++r)
+        if (r != x.rank) xchg_publish(x, seq, n, mine, r);
+    float acc = 0.f;
+    for (int r = 0; r < x.world; ++r) acc += (r == x.rank) ? bf16_bits_to_f32(mine) : xchg_fetch(x, seq, n, r);
+    return residual ? hadd_bf16_bits(acc, residual[n]) : f32_to_bf16_bits(acc);
+}
+// Advancing the exchange number: every CTA reads `epoch` after the dependency wait and then counts itself in
+// (xchg_arrive, one atomic whose result is not needed until the CTA ends, so its latency hides behind the GEMV); the CTA
+// that was the last to read stores the new number when it finishes (xchg_finish) -- no CTA can still need the old one.
+__device__ __forceinline__ unsigned xchg_arrive(const GemvXchg& x) { return atomicAdd(x.done, 1u); }
+__device__ __forceinline__ void xchg_finish(const GemvXchg& x, unsigned seq, unsigned ticket, unsigned participants) {
+    if (ticket == participants - 1) { *x.done = 0; *x.epoch = seq; }
+}
 
 // ---- fused RMSNorm prologue -------------------------------------------------------------------
 // inv_rms of one activation row in EXACTLY the summation order of the stand-alone rmsnorm kernel

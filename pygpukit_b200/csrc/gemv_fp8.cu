@@ -137,6 +137,12 @@ gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B
     if (row_begin < N) load_group(row_begin, 0);
     griddep_wait();
     griddep_launch();
+    const bool xchg = M == 1 && NMAT == 1 && epi.xchg.world > 1;
+    const unsigned xseq = xchg ? *epi.xchg.epoch + 1u : 0u;
+    unsigned xticket = 0;
+    if (xchg && threadIdx.x == 0) xticket = xchg_arrive(epi.xchg);
+    __shared__ uint16_t xrow[1024];              // exchange: the CTA's partials, [row iteration][warp]
+    int xit = 0;
     stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
 
     const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
@@ -187,12 +193,37 @@ gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B
                     float u = round_bf16(acc[NMAT - 1][m] * inv_s[m]);
                     float s = round_bf16(silu_ref(g));
                     C[o] = f32_to_bf16_bits(s * u);
+                } else if (xchg) {
+                    xrow[xit * wpc + warp] = f32_to_bf16_bits(v);      // published after the last row, 16 rows per store
                 } else {
                     if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
                     C[o] = epi.residual ? hadd_bf16_bits(v, res[m]) : f32_to_bf16_bits(v);
                 }
             }
         }
+        ++xit;
+    }
+    if (xchg) {
+        // Row-parallel layer under tensor parallelism.  In row iteration i the warps of this CTA own the consecutive rows
+        // i * nwarps + blockIdx.x * wpc + (0 .. wpc-1): warp i publishes them to every rank as contiguous LL words (one
+        // coalesced store per rank instead of wpc scattered 8-byte NVLink writes), then sums the ranks' words for the
+        // same rows in rank order (+ residual) -- pgk_p2p_ll_allreduce_add_bf16's arithmetic.
+        __syncthreads();
+        const int iters = (int)((N - (long)blockIdx.x * wpc + nwarps - 1) / nwarps);       // row iterations of this CTA (<= 0: none)
+        for (int i = warp; i < iters; i += wpc) {
+            const int n = (int)((long)i * nwarps + (long)blockIdx.x * wpc + lane);
+            const bool own = lane < wpc && n < N;
+            if (own) {
+                const uint16_t mine = xrow[i * wpc + lane];
+                for (int r = 0; r < epi.xchg.world; ++r)
+                    if (r != epi.xchg.rank) xchg_publish(epi.xchg, xseq, n, mine, r);
+                float acc = 0.f;
+                for (int r = 0; r < epi.xchg.world; ++r)
+                    acc += (r == epi.xchg.rank) ? bf16_bits_to_f32(mine) : xchg_fetch(epi.xchg, xseq, n, r);
+                C[n] = epi.residual ? hadd_bf16_bits(acc, epi.residual[n]) : f32_to_bf16_bits(acc);
+            }
+        }
+        if (threadIdx.x == 0) xchg_finish(epi.xchg, xseq, xticket, gridDim.x);
     }
 }
 
@@ -246,7 +277,7 @@ static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void
     {
         std::lock_guard<std::mutex> lk(mu);
         if (!attr_set) {
-            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024));     // + 2 KB static (xrow) + the 1 KB the system reserves <= 227 KB
             attr_set = true;
         }
         uint64_t key = ((uint64_t)(uint32_t)K << 32) | (uint32_t)N;
@@ -372,6 +403,25 @@ int pgk_gemv_fp8_swiglu_bf16(const void* A, const void* Wg_nk, const void* Sg, c
                              const void* Su, void* C, int M, int K, int N, void* stream) {
     return gemv_fp8_dispatch(A, Wg_nk, Sg, Wu_nk, Su, C, M, K, N, nullptr, nullptr, true,
                              (cudaStream_t)stream);
+}
+
+/* Row-parallel linear of ONE token under tensor parallelism: out = bf16(sum over ranks of bf16(x_r . W_r^T)) + residual in ONE
+ * launch (out may alias residual) -- pgk_gemv_fp8_bf16 followed by pgk_p2p_ll_allreduce_add_bf16, bit for bit, without
+ * the second launch.  Needs the peer buffers (pgk_p2p_open), N <= 8192 and the streaming kernel's shape rules. */
+int pgk_gemv_fp8_allreduce_bf16(const void* A, const void* B_nk, const void* S, const void* residual, void* out, int K,
+                                int N, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    GemvEpilogue epi = {nullptr, (const uint16_t*)residual};
+    PGK_REQUIRE(p2p_gemv_xchg(&epi.xchg), "gemv_fp8_allreduce failed: peer buffers not opened (pgk_p2p_create / pgk_p2p_open)");
+    bool clean = true;
+    if (int rc = fp8_codes_clean(B_nk, (size_t)N * K, st, &clean)) return rc;
+    PGK_REQUIRE(clean && K % 32 == 0 && aligned16(A) && aligned32(B_nk) && (size_t)K * 2 + 1024 <= 200 * 1024 && N >= 1 &&
+                (unsigned)N <= epi.xchg.slot_words,
+                "gemv_fp8_allreduce failed: needs K %% 32 == 0, N <= %u, aligned pointers and weights without the codes 0x7F / 0xFF "
+                "(K=%d N=%d)", epi.xchg.slot_words, K, N);
+    if (epi.xchg.world <= 1) epi.xchg.world = 0;
+    PGK_REQUIRE(N <= 1024 * sm_count(), "gemv_fp8_allreduce failed: N=%d", N);      // xrow: <= 1024 rows per CTA (>= one CTA per SM)
+    return launch_fp8<1, 1>((const uint16_t*)A, B_nk, S, nullptr, nullptr, (uint16_t*)out, K, N, epi, st);
 }
 
 /* rmsnorm(x, gamma, eps) -> W8A16 GEMV in ONE launch: every CTA normalises the activation rows while it

@@ -111,6 +111,10 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
     }
     griddep_wait();
     griddep_launch();
+    const bool xchg = M == 1 && !SWIGLU && p.epi.xchg.world > 1;
+    const unsigned xseq = xchg ? *p.epi.xchg.epoch + 1u : 0u;
+    unsigned xticket = 0;
+    if (xchg && threadIdx.x == 0) xticket = xchg_arrive(p.epi.xchg);
     stage_activations_f16<M, false>(p.A, K, a_s, inv_s, red_u, p.epi.norm_gamma, p.epi.norm_eps);
 
     float acc[M][COLS];
@@ -177,7 +181,10 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
         __syncthreads();
         if (threadIdx.x == 0) s_ticket = atomicAdd(p.counters + g, 1u);
         __syncthreads();
-        if (s_ticket != (unsigned)(p.KS - 1)) return;
+        if (s_ticket != (unsigned)(p.KS - 1)) {
+            if (xchg && threadIdx.x == 0) xchg_finish(p.epi.xchg, xseq, xticket, gridDim.x);
+            return;
+        }
         __threadfence();
     }
     // ---- final fold (this CTA is the only / the last one of its column group)
@@ -204,9 +211,14 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
             if (n >= N) continue;
             float v = p.alpha * total(m, col);
             size_t o = (size_t)m * N + n;
+            if (xchg) {                // row-parallel layer under tensor parallelism: all-reduce, then the residual
+                p.C[o] = xchg_reduce_1t(p.epi.xchg, xseq, n, f32_to_bf16_bits(v), p.epi.residual);
+                continue;
+            }
             if (p.epi.bias) v = round_bf16(v) + bf16_bits_to_f32(p.epi.bias[n]);
             p.C[o] = p.epi.residual ? hadd_bf16_bits(v, p.epi.residual[o]) : f32_to_bf16_bits(v);
         }
+        if (xchg && threadIdx.x == 0) xchg_finish(p.epi.xchg, xseq, xticket, gridDim.x);
     } else {
         const int I = N >> 1;
         for (int t = threadIdx.x; t < M * (CW / 2); t += blockDim.x) {
@@ -429,6 +441,24 @@ int pgk_gemv_nvf4_bf16_ex(const void* A, const void* B_data, const void* B_scale
 int pgk_gemv_nvf4_swiglu_bf16(const void* A, const void* Wgu_data, const void* Wgu_scale, void* C, int M,
                               int K, int N2, void* stream) {
     return nvf4_dispatch(A, Wgu_data, Wgu_scale, C, M, K, N2, 1.0f, nullptr, nullptr, true, (cudaStream_t)stream);
+}
+
+/* NVF4 form of pgk_gemv_fp8_allreduce_bf16: row-parallel linear of one token + all-reduce over the ranks + residual in one launch */
+int pgk_gemv_nvf4_allreduce_bf16(const void* A, const void* B_data, const void* B_scale, const void* residual, void* out,
+                                 int K, int N, float alpha, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    Nvf4Params p = {};
+    p.epi = {nullptr, (const uint16_t*)residual};
+    PGK_REQUIRE(p2p_gemv_xchg(&p.epi.xchg), "gemv_nvf4_allreduce failed: peer buffers not opened (pgk_p2p_create / pgk_p2p_open)");
+    PGK_REQUIRE(K % 32 == 0 && N % 16 == 0 && al16(A) && al16(B_data) && al16(B_scale) && (size_t)K * 2 + kNvf4Hdr <= 200 * 1024 &&
+                N >= 16 && (unsigned)N <= p.epi.xchg.slot_words,
+                "gemv_nvf4_allreduce failed: needs K %% 32 == 0, N %% 16 == 0, N <= %u and 16-byte aligned pointers (K=%d N=%d)",
+                p.epi.xchg.slot_words, K, N);
+    if (p.epi.xchg.world <= 1) p.epi.xchg.world = 0;
+    if (int rc = ensure_workspace(st)) return rc;
+    p.A = (const uint16_t*)A; p.Bd = (const uint8_t*)B_data; p.Bs = (const uint8_t*)B_scale; p.C = (uint16_t*)out;
+    p.K = K; p.N = N; p.alpha = alpha;
+    return launch_nvf4<1, 16, false>(p, st);
 }
 
 /* rmsnorm(x, gamma, eps) -> NVF4 GEMV in one launch (see pgk_rmsnorm_gemv_fp8_bf16). */

@@ -257,6 +257,19 @@ bool p2p_ll_info(int* rank, int* world, unsigned char** ll_peers, unsigned** epo
     return true;
 }
 
+// gemv_fp8.cu / gemv_nvf4.cu: the same regions and exchange numbering for the GEMV kernels that do their own all-reduce
+bool p2p_gemv_xchg(GemvXchg* x) {
+    if (!g_p2p.ready) return false;
+    for (int r = 0; r < kP2pMaxWorld; ++r) x->ll[r] = r < g_p2p.world ? g_p2p.peer[r] + kP2pLLOffset : nullptr;
+    x->epoch = g_p2p.seq + kP2pMaxCtas + 1;
+    x->done = g_p2p.seq + kP2pMaxCtas + 2;
+    x->err = g_p2p.err;
+    x->rank = g_p2p.rank; x->world = g_p2p.world;
+    x->slot_words = (unsigned)kP2pLLWords;
+    x->par_bytes = (unsigned)(kP2pMaxWorld * kP2pLLWords * 8);
+    return true;
+}
+
 }  // namespace pgk
 
 using namespace pgk;
@@ -272,8 +285,8 @@ int pgk_p2p_create(int rank, int world, void* host_handle_out) {
     g_p2p.rank = rank; g_p2p.world = world;
     PGK_CUDA(cudaMalloc(&g_p2p.local, kP2pBufBytes));
     PGK_CUDA(cudaMemset(g_p2p.local, 0, kP2pBufBytes));
-    PGK_CUDA(cudaMalloc(&g_p2p.seq, (kP2pMaxCtas + 2) * sizeof(unsigned)));
-    PGK_CUDA(cudaMemset(g_p2p.seq, 0, (kP2pMaxCtas + 2) * sizeof(unsigned)));
+    PGK_CUDA(cudaMalloc(&g_p2p.seq, (kP2pMaxCtas + 3) * sizeof(unsigned)));
+    PGK_CUDA(cudaMemset(g_p2p.seq, 0, (kP2pMaxCtas + 3) * sizeof(unsigned)));
     g_p2p.err = g_p2p.seq + kP2pMaxCtas;
     cudaIpcMemHandle_t h;
     PGK_CUDA(cudaIpcGetMemHandle(&h, g_p2p.local));

@@ -44,7 +44,9 @@ class TransformerBlock:
             x = self.attn_norm(hidden, out=buf("norm_out"))
             a = self.attn.attend(x, position, context_len, qkv_buf=buf("qkv_proj_out"), attn_buf=buf("attn_flat"),
                                  pos_buf=pos_buf, ctx_buf=ctx_buf)
-        if tp:
+        if tp and self.comm.fuses_allreduce(self.attn.o_proj, M):
+            self.attn.o_proj.forward_allreduce(a, hidden)          # GEMV + all-reduce + residual: one launch
+        elif tp:
             part = self.attn.o_proj.forward(a, out=buf("partial"))
             self.comm.allreduce_add(part, hidden)
         else:
@@ -55,6 +57,8 @@ class TransformerBlock:
         if tp and isinstance(self.mlp, MoELayer):
             # expert parallel: the exchange happens inside the layer, on the un-combined rows (bit-identical to 1 GPU)
             self.mlp.forward(x, out=hidden, residual=hidden, act_buf=buf("mlp_act"), comm=self.comm)
+        elif tp and isinstance(self.mlp, MLP) and self.mlp.activation != "gelu" and self.comm.fuses_allreduce(self.mlp.down_proj, M):
+            self.mlp.forward_allreduce(x, hidden, act_buf=buf("mlp_act"), **kw)
         elif tp:
             part = self.mlp.forward(x, out=buf("partial"), act_buf=buf("mlp_act"), **kw)
             self.comm.allreduce_add(part, hidden)

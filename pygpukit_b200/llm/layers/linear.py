@@ -155,6 +155,14 @@ class LinearFP8:
                              self.in_features, self.out_features, _ptr(self.bias), _ptr(residual), _st())
         return y
 
+    def forward_allreduce(self, x: GPUArray, hidden: GPUArray) -> GPUArray:
+        """Row-parallel layer of one token under tensor parallelism: hidden <- hidden + sum over ranks of (x . W^T), GEMV and
+        all-reduce in ONE launch (`pgk_gemv_fp8_allreduce_bf16`; see TensorParallel.fuses_allreduce)."""
+        _check_x(x, self.in_features)
+        api.gemv_fp8_allreduce_bf16(x.device_ptr, self.weight_fp8.device_ptr, self.scale_inv.device_ptr, hidden.device_ptr,
+                                    hidden.device_ptr, self.in_features, self.out_features, _st())
+        return hidden
+
     def __call__(self, x: GPUArray, *, out: GPUArray | None = None) -> GPUArray:
         return self.forward(x, out=out)
 
@@ -215,6 +223,13 @@ class LinearNVF4:
         api.gemv_nvf4_bf16_ex(x.device_ptr, self.data.device_ptr, self.scale.device_ptr, y.device_ptr, M,
                               self.in_features, self.out_features, self.alpha, _ptr(self.bias), _ptr(residual), _st())
         return y
+
+    def forward_allreduce(self, x: GPUArray, hidden: GPUArray) -> GPUArray:
+        """NVF4 form of LinearFP8.forward_allreduce (`pgk_gemv_nvf4_allreduce_bf16`)."""
+        _check_x(x, self.in_features)
+        api.gemv_nvf4_allreduce_bf16(x.device_ptr, self.data.device_ptr, self.scale.device_ptr, hidden.device_ptr,
+                                     hidden.device_ptr, self.in_features, self.out_features, self.alpha, _st())
+        return hidden
 
     def __call__(self, x: GPUArray, *, out: GPUArray | None = None) -> GPUArray:
         return self.forward(x, out=out)

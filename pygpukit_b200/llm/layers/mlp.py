@@ -150,6 +150,12 @@ class MLP:
         h = self.gate_up_act(x, out=act_buf, norm=norm)
         return self.down_proj.forward(h, out=out, residual=residual)
 
+    def forward_allreduce(self, x: GPUArray, hidden: GPUArray, *, act_buf: GPUArray | None = None, norm=None) -> GPUArray:
+        """Tensor parallel, one token: hidden <- hidden + sum over ranks of the shard's MLP output, the down projection and the
+        all-reduce being one launch (TensorParallel.fuses_allreduce(self.down_proj, 1) must hold)."""
+        h = self.gate_up_act(x, out=act_buf, norm=norm)
+        return self.down_proj.forward_allreduce(h, hidden)
+
     def __call__(self, x: GPUArray) -> GPUArray:
         return self.forward(x)
 

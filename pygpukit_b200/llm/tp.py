@@ -71,6 +71,7 @@ def combine_greedy(pairs: np.ndarray, vocab_offsets: list[int]) -> int:
 
 
 _TIMING_SKIP_EXCHANGE = __import__("os").environ.get("PGK_TP_SKIP_EXCHANGE", "0") == "1"
+_FUSED_AR = __import__("os").environ.get("PGK_TP_FUSED_AR", "1") != "0"
 
 class TensorParallel:
     """NCCL communicator of this process (rank <-> GPU)."""
@@ -146,6 +147,19 @@ class TensorParallel:
         from .._lib import api
         from ..core.stream import current_stream_handle
         api.nccl_allreduce_bf16(x.device_ptr, x.size, current_stream_handle())
+
+    def fuses_allreduce(self, linear, M: int) -> bool:
+        """True when a row-parallel layer can run its GEMV and the all-reduce after it as ONE launch
+        (`linear.forward_allreduce`): one token, FP8 / NVF4 weights without bias, peer buffers with the LL regions open.
+        PGK_TP_FUSED_AR=0 keeps the two launches (A/B timing, parity tests)."""
+        from .layers.linear import LinearFP8, LinearNVF4
+        if not (_FUSED_AR and self.world > 1 and self._p2p and self._ll and M == 1 and not _TIMING_SKIP_EXCHANGE):
+            return False
+        if not isinstance(linear, (LinearFP8, LinearNVF4)) or linear.bias is not None:
+            return False
+        if linear.out_features > 8192 or linear.in_features % 32 or linear.in_features * 2 + 1024 > 200 * 1024:
+            return False
+        return not isinstance(linear, LinearNVF4) or linear.out_features % 16 == 0
 
     def allreduce_add(self, part, hidden) -> None:
         """hidden <- hidden + allreduce(part): the tail of a row-parallel layer.  One peer-memory kernel over

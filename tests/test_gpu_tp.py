@@ -25,6 +25,8 @@ CASES = {
     "tiny-moe:nvf4:128": (4, 2, None),
     "moe-layer:fp8:0": (4, 2, None),                 # expert parallelism in isolation: bit-identical layer output
     "moe-layer:nvf4:0": (4, 2, None),
+    "linear-allreduce:fp8:0": (8, 8, 1024),          # GEMV + all-reduce in one launch == the two launches, bit for bit
+    "linear-allreduce:nvf4:0": (8, 8, 1024),
 }
 _results: dict[int, dict] = {}
 

@@ -73,6 +73,39 @@ def moe_layer_case(case, fmt):
     return ok
 
 
+def linear_allreduce_case(case, fmt):
+    """Row-parallel GEMV + all-reduce + residual in ONE launch (pgk_gemv_*_allreduce_bf16) against the two launches it
+    replaces (GEMV -> pgk_p2p_ll_allreduce_add_bf16): the SAME BITS on every rank, for several shapes, repeated so that both
+    parity halves of the LL regions and a changing hidden state are exercised."""
+    from pygpukit_b200.core.factory import from_numpy
+    from pygpukit_b200.llm.random_init import normal_bf16, quantize_fp8, quantize_nvf4
+    rng = np.random.default_rng(100 + rank)
+    same = []
+    for K, N in ((1024, 512), (2048, 4096), (3584, 8192), (512, 1536)):
+        if fmt == "fp8":
+            lin = quantize_fp8(normal_bf16((N, K), 40 + rank, 0.05))
+        else:
+            lin = quantize_nvf4(normal_bf16((K, N), 40 + rank, 0.05))
+        assert comm.fuses_allreduce(lin, 1), (fmt, K, N)
+        hid0 = ((np.random.default_rng(7).standard_normal((1, N)) * 0.5).astype(np.float32).view(np.uint32) >> 16).astype(np.uint16)
+        h_two, h_one = from_numpy(hid0.copy()), from_numpy(hid0.copy())
+        part = from_numpy(np.zeros((1, N), np.uint16))
+        for it in range(5):
+            x = from_numpy(((rng.standard_normal((1, K))).astype(np.float32).view(np.uint32) >> 16).astype(np.uint16))
+            lin.forward(x, out=part)
+            comm.allreduce_add(part, h_two)
+            lin.forward_allreduce(x, h_one)
+            api.device_sync()
+            same.append(bool(np.array_equal(h_two.to_numpy(), h_one.to_numpy())))
+    flags = [None] * world
+    dist.all_gather_object(flags, all(same))
+    ok = all(flags)
+    if rank == 0:
+        print(json.dumps({"case": case, "world": world, "format": fmt, "bit_identical": same, "all_ranks": flags, "ok": ok,
+                          "steps": 0, "identical_prefix": 0}), flush=True)
+    return ok
+
+
 def router_tie_before(single, tokens, upto):
     """True when, while the one-process model decodes `tokens[:upto + 1]` after the prompt, some MoE layer's router sees
     its k-th and (k+1)-th logits equal or ADJACENT in BF16: the tensor-parallel run (different summation order in the
@@ -98,8 +131,8 @@ def router_tie_before(single, tokens, upto):
 all_ok = True
 for case in sys.argv[1:]:
     f = case.split(":")
-    if f[0] == "moe-layer":
-        ok = moe_layer_case(case, f[1])
+    if f[0] in ("moe-layer", "linear-allreduce"):
+        ok = moe_layer_case(case, f[1]) if f[0] == "moe-layer" else linear_allreduce_case(case, f[1])
         flag = [ok]
         dist.broadcast_object_list(flag, src=0)
         all_ok = all_ok and flag[0]
