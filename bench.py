@@ -491,6 +491,10 @@ def measure(model_name, fmt, ctx, batch, K, W, d, comm, rank, local_rank, peak, 
         out["clocks"] = clocks.stop(t0, t1)
     out["p2p"] = bool(comm is not None and comm._p2p)
     out["fused_exchange"] = bool(getattr(model, "fused_exchange", False))
+    # per-op path: do the row-parallel GEMVs of the layers do their own all-reduce (pgk_gemv_*_allreduce_bf16)?
+    blk0 = model.blocks[0]
+    if not out["fused_exchange"] and getattr(blk0, "comm", None) is not None and blk0.comm.world > 1:
+        out["fused_exchange"] = bool(blk0.comm.fuses_allreduce(blk0.attn.o_proj, 1))
     model._graph = None
     api.device_sync()
     del model
@@ -535,7 +539,7 @@ def run_ours(args) -> None:
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "bytes_per_launch": kbytes, "us_per_launch": kus, "frac_of_8000": achieved / 8000.0},
         "step_roofline": main["step_roofline"],
-        "pdl": pdl, "allreduce": (("p2p-nvlink" + ("+fused" if main["fused_exchange"] else "")) if main["p2p"]
+        "pdl": pdl, "allreduce": (("p2p-nvlink" + ("+in-gemv" if main["fused_exchange"] else "")) if main["p2p"]
                                   else ("nccl" if world > 1 else None)),
         "clocks": main.get("clocks"), "token_streams_agree": main["token_streams_agree"], "build_s": main["build_s"],
         "configs": {},
