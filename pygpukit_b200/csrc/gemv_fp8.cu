@@ -142,7 +142,9 @@ gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B
     unsigned xticket = 0;
     if (xchg && threadIdx.x == 0) xticket = xchg_arrive(epi.xchg);
     __shared__ uint16_t xrow[1024];              // exchange: the CTA's partials, [row iteration][warp]
+    __shared__ int xcnt[64];                     // exchange: warps of the CTA done with row iteration i (N <= 8192: <= 28 iterations)
     int xit = 0;
+    if (xchg && threadIdx.x < 64) xcnt[threadIdx.x] = 0;       // visible after the barriers of the staging below
     stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
 
     const uint4* a_lo = reinterpret_cast<const uint4*>(a_s);
@@ -194,32 +196,48 @@ gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B
                     float s = round_bf16(silu_ref(g));
                     C[o] = f32_to_bf16_bits(s * u);
                 } else if (xchg) {
-                    xrow[xit * wpc + warp] = f32_to_bf16_bits(v);      // published after the last row, 16 rows per store
+                    xrow[xit * wpc + warp] = f32_to_bf16_bits(v);
                 } else {
                     if (epi.bias) v = round_bf16(v) + bf16_bits_to_f32(epi.bias[n]);
                     C[o] = epi.residual ? hadd_bf16_bits(v, res[m]) : f32_to_bf16_bits(v);
                 }
             }
         }
+        if (xchg) {
+            // Row-parallel layer under tensor parallelism.  In row iteration i the warps of this CTA own the consecutive
+            // rows i * nwarps + blockIdx.x * wpc + (0 .. wpc-1).  The warp that completes the group publishes it to every
+            // rank as contiguous LL words (one coalesced store per rank instead of wpc scattered 8-byte NVLink writes)
+            // while the other rows are still being computed: the NVLink hop hides behind the rest of the GEMV.
+            const int base = (int)((long)xit * nwarps + (long)blockIdx.x * wpc);
+            const int expect = min(wpc, N - base);
+            int last = 0;
+            if (lane == 0) {
+                __threadfence_block();
+                last = atomicAdd(&xcnt[xit], 1) == expect - 1;
+            }
+            last = __shfl_sync(0xffffffffu, last, 0);
+            if (last) {
+                __threadfence_block();
+                if (lane < expect) {
+                    const uint16_t mine = *reinterpret_cast<volatile uint16_t*>(&xrow[xit * wpc + lane]);
+                    for (int r = 0; r < epi.xchg.world; ++r)
+                        if (r != epi.xchg.rank) xchg_publish(epi.xchg, xseq, base + lane, mine, r);
+                }
+            }
+        }
         ++xit;
     }
     if (xchg) {
-        // Row-parallel layer under tensor parallelism.  In row iteration i the warps of this CTA own the consecutive rows
-        // i * nwarps + blockIdx.x * wpc + (0 .. wpc-1): warp i publishes them to every rank as contiguous LL words (one
-        // coalesced store per rank instead of wpc scattered 8-byte NVLink writes), then sums the ranks' words for the
-        // same rows in rank order (+ residual) -- pgk_p2p_ll_allreduce_add_bf16's arithmetic.
+        // every group of this CTA has been published: sum the ranks' words for the same rows in rank order (+ residual)
+        // -- pgk_p2p_ll_allreduce_add_bf16's arithmetic
         __syncthreads();
         const int iters = (int)((N - (long)blockIdx.x * wpc + nwarps - 1) / nwarps);       // row iterations of this CTA (<= 0: none)
         for (int i = warp; i < iters; i += wpc) {
             const int n = (int)((long)i * nwarps + (long)blockIdx.x * wpc + lane);
-            const bool own = lane < wpc && n < N;
-            if (own) {
-                const uint16_t mine = xrow[i * wpc + lane];
-                for (int r = 0; r < epi.xchg.world; ++r)
-                    if (r != epi.xchg.rank) xchg_publish(epi.xchg, xseq, n, mine, r);
+            if (lane < wpc && n < N) {
                 float acc = 0.f;
                 for (int r = 0; r < epi.xchg.world; ++r)
-                    acc += (r == epi.xchg.rank) ? bf16_bits_to_f32(mine) : xchg_fetch(epi.xchg, xseq, n, r);
+                    acc += (r == epi.xchg.rank) ? bf16_bits_to_f32(xrow[i * wpc + lane]) : xchg_fetch(epi.xchg, xseq, n, r);
                 C[n] = epi.residual ? hadd_bf16_bits(acc, epi.residual[n]) : f32_to_bf16_bits(acc);
             }
         }
@@ -277,7 +295,7 @@ static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void
     {
         std::lock_guard<std::mutex> lk(mu);
         if (!attr_set) {
-            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024));     // + 2 KB static (xrow) + the 1 KB the system reserves <= 227 KB
+            PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024));     // + 2.3 KB static (xrow, xcnt) + the 1 KB the system reserves <= 227 KB
             attr_set = true;
         }
         uint64_t key = ((uint64_t)(uint32_t)K << 32) | (uint32_t)N;
@@ -420,7 +438,7 @@ int pgk_gemv_fp8_allreduce_bf16(const void* A, const void* B_nk, const void* S, 
                 "gemv_fp8_allreduce failed: needs K %% 32 == 0, N <= %u, aligned pointers and weights without the codes 0x7F / 0xFF "
                 "(K=%d N=%d)", epi.xchg.slot_words, K, N);
     if (epi.xchg.world <= 1) epi.xchg.world = 0;
-    PGK_REQUIRE(N <= 1024 * sm_count(), "gemv_fp8_allreduce failed: N=%d", N);      // xrow: <= 1024 rows per CTA (>= one CTA per SM)
+    PGK_REQUIRE(N <= 8192, "gemv_fp8_allreduce failed: N=%d", N);      // xrow / xcnt: <= 28 row iterations of <= 16 warps per CTA
     return launch_fp8<1, 1>((const uint16_t*)A, B_nk, S, nullptr, nullptr, (uint16_t*)out, K, N, epi, st);
 }
 
