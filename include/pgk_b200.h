@@ -442,6 +442,17 @@ int pgk_gemv_fp8_allreduce_bf16(const void* A, const void* B_nk, const void* S, 
                                 int N, void* stream);
 int pgk_gemv_nvf4_allreduce_bf16(const void* A, const void* B_data, const void* B_scale, const void* residual, void* out,
                                  int K, int N, float alpha, void* stream);
+
+/* Allocation-free variant of pgk_gemv_nvf4_bf16.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It calls no cudaMalloc / cudaFree / allocating library routine: the split-K scratch is a file-scope device array of
+ * 1028 KB (1 MB of partial sums + 1024 arrival counters) that every GPU loading the library holds until exit and that
+ * all calls share -- calls that overlap on the GPU race on it.  C[M, N] = alpha * A[M, K] . dequant(B) (rows served one at
+ * a time by the M = 1 kernel), same storage as pgk_gemv_nvf4_bf16.  Limits, rejected with an error otherwise:
+ * K % 32 == 0, 32 <= K <= 101888, N % 16 == 0, 16 <= N <= 524288, 16-byte aligned pointers.  Results agree with
+ * pgk_gemv_nvf4_bf16 within its f32-accumulate bar (the K split may differ, so the summation order may). */
+int pgk_gemv_nvf4_bf16_noalloc(const void* A, const void* B_data, const void* B_scale, void* C, int M, int K, int N,
+                               float alpha, void* stream);
 int pgk_p2p_error(int* host_flag);
 int pgk_p2p_destroy(void);
 

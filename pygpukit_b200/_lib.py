@@ -96,6 +96,7 @@ _SIGS = {
     "pgk_moe_down_combine_fp8_t1": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "pgk_gemv_fp8_allreduce_bf16": [vp, vp, vp, vp, vp, i32, i32, vp],
     "pgk_gemv_nvf4_allreduce_bf16": [vp, vp, vp, vp, vp, i32, i32, f32, vp],
+    "pgk_gemv_nvf4_bf16_noalloc": [vp, vp, vp, vp, i32, i32, i32, f32, vp],
     "pgk_moe_combine_t1": [vp, vp, vp, vp, i32, i32, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
     "pgk_quantize_bf16_to_fp8_block": [vp, vp, vp, i32, i32, vp],

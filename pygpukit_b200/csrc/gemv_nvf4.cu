@@ -424,6 +424,66 @@ static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C,
     return 0;
 }
 
+// ---------------------------------------------------------------- allocation-free variant (pgk_gemv_nvf4_bf16_noalloc)
+// The split-K partials and the per-column-group arrival counters of gemv_nvf4_kernel live in a file-scope device array
+// instead of the cudaMalloc'ed workspace above: 1 MB of f32 partials (<= 512 CTAs x 512 columns) + 1024 counters.  Every
+// GPU that loads the library holds these 1028 KB until exit.  All calls share the array: calls that overlap on the GPU
+// (different streams, or two processes' worth of work on one context) race on it.
+constexpr int kNaMaxCtas = 512;                      // CTAs that write partials (column groups x K splits)
+constexpr int kNaMaxGroups = 1024;                   // column groups of 512 columns: N <= 524288
+constexpr size_t kNaWsFloats = (size_t)kNaMaxCtas * 512;
+static __device__ __align__(256) unsigned char g_na_scratch[kNaWsFloats * 4 + kNaMaxGroups * 4];
+
+// The array's name is a host-side stand-in in host code: its device address is looked up once per device, with that
+// device current.
+static int na_scratch_ptr(unsigned char** out) {
+    static std::mutex mu;
+    static unsigned char* ptrs[64] = {};
+    int dev = 0;
+    PGK_CUDA(cudaGetDevice(&dev));
+    PGK_REQUIRE(dev >= 0 && dev < 64, "gemv_nvf4_bf16_noalloc failed: device ordinal %d", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[dev]) {
+        void* ptr = nullptr;
+        PGK_CUDA(cudaGetSymbolAddress(&ptr, g_na_scratch));
+        PGK_REQUIRE(ptr != nullptr, "gemv_nvf4_bf16_noalloc failed: cudaGetSymbolAddress returned a null address");
+        ptrs[dev] = (unsigned char*)ptr;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+static int launch_nvf4_noalloc(Nvf4Params p, cudaStream_t st) {
+    constexpr int CW = 512;
+    auto kern = gemv_nvf4_kernel<1, 16, false>;
+    const int G = (p.N + CW - 1) / CW, KB = p.K >> 5;
+    PGK_REQUIRE(G <= kNaMaxGroups, "gemv_nvf4_bf16_noalloc failed: N=%d exceeds the static scratch (N <= %d)", p.N, kNaMaxGroups * CW);
+    unsigned char* scratch = nullptr;
+    if (int rc = na_scratch_ptr(&scratch)) return rc;
+    // one fat CTA per SM where the column groups are few (the choice launch_nvf4 measured best), never more partial
+    // records than the scratch holds; more than 512 column groups run unsplit and use no partials at all
+    int KS = sm_count() / G;
+    if (KS > KB / 8) KS = KB / 8;
+    if (KS > kNaMaxCtas / G) KS = kNaMaxCtas / G;
+    if (KS < 1) KS = 1;
+    const int bpc = (KB + KS - 1) / KS;
+    KS = (KB + bpc - 1) / bpc;
+    const int wpc = bpc < 16 ? (bpc < 4 ? 4 : bpc) : 16;
+    const size_t body = (size_t)p.K * 2, redb = (size_t)wpc * CW * 4;
+    const size_t smem = kNvf4Hdr + (body > redb ? body : redb);
+    PGK_REQUIRE(smem <= 226 * 1024, "gemv_nvf4_bf16_noalloc failed: K=%d too large", p.K);
+    PGK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    p.KS = KS;
+    p.bpc = bpc;
+    p.ws = reinterpret_cast<float*>(scratch);
+    p.counters = reinterpret_cast<unsigned*>(scratch + kNaWsFloats * 4);
+    // the array keeps the last call's contents: the counters must start at zero (the partials are overwritten before
+    // they are read)
+    if (KS > 1) PGK_CUDA(cudaMemsetAsync(p.counters, 0, (size_t)G * sizeof(unsigned), st));
+    PGK_CUDA(launch(kern, dim3(G * KS), dim3(wpc * 32), smem, st, p));
+    return 0;
+}
+
 }  // namespace pgk
 
 using namespace pgk;
@@ -459,6 +519,25 @@ int pgk_gemv_nvf4_allreduce_bf16(const void* A, const void* B_data, const void* 
     p.A = (const uint16_t*)A; p.Bd = (const uint8_t*)B_data; p.Bs = (const uint8_t*)B_scale; p.C = (uint16_t*)out;
     p.K = K; p.N = N; p.alpha = alpha;
     return launch_nvf4<1, 16, false>(p, st);
+}
+
+/* pgk_gemv_nvf4_bf16 for callers that cannot allocate (CUDA graph capture, tight serving loops): no cudaMalloc / cudaFree,
+ * the split-K scratch is a 1028 KB file-scope device array shared by every call (overlapping calls race).  Rows are
+ * served one at a time by the M = 1 kernel.  Limits: K % 32 == 0, K <= 100 K, N % 16 == 0, N <= 524288, 16-byte aligned. */
+int pgk_gemv_nvf4_bf16_noalloc(const void* A, const void* B_data, const void* B_scale, void* C, int M, int K, int N,
+                               float alpha, void* stream) {
+    PGK_REQUIRE(M >= 1 && K >= 32 && N >= 16, "gemv_nvf4_bf16_noalloc failed: invalid shape M=%d K=%d N=%d", M, K, N);
+    PGK_REQUIRE(K % 32 == 0 && N % 16 == 0 && al16(A) && al16(B_data) && al16(B_scale) && (size_t)K * 2 + kNvf4Hdr <= 200 * 1024,
+                "gemv_nvf4_bf16_noalloc failed: needs K %% 32 == 0, K <= 101888, N %% 16 == 0 and 16-byte aligned pointers (K=%d N=%d)", K, N);
+    PGK_REQUIRE(N <= kNaMaxGroups * 512, "gemv_nvf4_bf16_noalloc failed: N=%d exceeds the static scratch (N <= %d)", N, kNaMaxGroups * 512);
+    for (int m = 0; m < M; ++m) {
+        Nvf4Params p = {};
+        p.A = (const uint16_t*)A + (size_t)m * K; p.Bd = (const uint8_t*)B_data; p.Bs = (const uint8_t*)B_scale;
+        p.C = (uint16_t*)C + (size_t)m * N;
+        p.K = K; p.N = N; p.alpha = alpha;
+        if (int rc = launch_nvf4_noalloc(p, (cudaStream_t)stream)) return rc;
+    }
+    return 0;
 }
 
 /* rmsnorm(x, gamma, eps) -> NVF4 GEMV in one launch (see pgk_rmsnorm_gemv_fp8_bf16). */
