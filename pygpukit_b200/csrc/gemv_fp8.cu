@@ -95,7 +95,8 @@ void fp8_codes_forget(const void* base) {
 //
 // One group (U x 256-bit loads per lane) in flight per warp, up to 16 warps per CTA.  (A register double-buffered
 // form was measured slower on B200 -- 168 registers cap the CTA at 12 warps -- see profiles/r01_*; removed.)
-template <int M, int NMAT>
+// XCHG: the tensor-parallel form with the all-reduce inside (a separate instantiation: the plain kernel pays nothing for it)
+template <int M, int NMAT, bool XCHG = false>
 __global__ void __launch_bounds__(512)
 gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B0,
                 const uint16_t* __restrict__ S0, const uint8_t* __restrict__ B1,
@@ -137,12 +138,12 @@ gemv_fp8_sb_kernel(const uint16_t* __restrict__ A, const uint8_t* __restrict__ B
     if (row_begin < N) load_group(row_begin, 0);
     griddep_wait();
     griddep_launch();
-    const bool xchg = M == 1 && NMAT == 1 && epi.xchg.world > 1;
+    const bool xchg = XCHG && M == 1 && NMAT == 1 && epi.xchg.world > 1;
     const unsigned xseq = xchg ? *epi.xchg.epoch + 1u : 0u;
     unsigned xticket = 0;
     if (xchg && threadIdx.x == 0) xticket = xchg_arrive(epi.xchg);
-    __shared__ uint16_t xrow[1024];              // exchange: the CTA's partials, [row iteration][warp]
-    __shared__ int xcnt[64];                     // exchange: warps of the CTA done with row iteration i (N <= 8192: <= 28 iterations)
+    __shared__ uint16_t xrow[XCHG ? 1024 : 1];              // exchange: the CTA's partials, [row iteration][warp]
+    __shared__ int xcnt[XCHG ? 64 : 1];                     // exchange: warps of the CTA done with row iteration i (N <= 8192: <= 28 iterations)
     int xit = 0;
     if (xchg && threadIdx.x < 64) xcnt[threadIdx.x] = 0;       // visible after the barriers of the staging below
     stage_activations_f16<M>(A, K, a_s, inv_s, red, epi.norm_gamma, epi.norm_eps);
@@ -318,12 +319,12 @@ static int launch_fp8_kern(Kern kern, int maxw, int M, const void* A, const void
     return 0;
 }
 
-template <int M, int NMAT>
+template <int M, int NMAT, bool XCHG = false>
 static int launch_fp8(const void* A, const void* B0, const void* S0, const void* B1, const void* S1,
                       void* C, int K, int N, GemvEpilogue epi, cudaStream_t st) {
     static std::unordered_map<uint64_t, GemvCfg> cache;
     static bool attr = false;
-    return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache, attr);
+    return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT, XCHG>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache, attr);
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -439,7 +440,7 @@ int pgk_gemv_fp8_allreduce_bf16(const void* A, const void* B_nk, const void* S, 
                 "(K=%d N=%d)", epi.xchg.slot_words, K, N);
     if (epi.xchg.world <= 1) epi.xchg.world = 0;
     PGK_REQUIRE(N <= 8192, "gemv_fp8_allreduce failed: N=%d", N);      // xrow / xcnt: <= 28 row iterations of <= 16 warps per CTA
-    return launch_fp8<1, 1>((const uint16_t*)A, B_nk, S, nullptr, nullptr, (uint16_t*)out, K, N, epi, st);
+    return launch_fp8<1, 1, true>((const uint16_t*)A, B_nk, S, nullptr, nullptr, (uint16_t*)out, K, N, epi, st);
 }
 
 /* rmsnorm(x, gamma, eps) -> W8A16 GEMV in ONE launch: every CTA normalises the activation rows while it

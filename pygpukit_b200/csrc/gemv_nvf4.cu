@@ -83,7 +83,7 @@ constexpr int kNvf4Hdr = 1024;  // smem header: inv_s[8] floats, reduction scrat
 
 // SWIGLU: columns are gate/up interleaved in groups of 8 ([g0..g7,u0..u7,g8..]); the output
 // has N/2 columns: C = bf16( bf16(silu(bf16(g))) * bf16(u) ).
-template <int M, int COLS, bool SWIGLU>
+template <int M, int COLS, bool SWIGLU, bool XCHG = false>    // XCHG: tensor-parallel form with the all-reduce inside
 __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
     constexpr int CW = 32 * COLS;  // columns per warp / per CTA
     constexpr int RH = 8;          // byte-rows in flight per lane
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
     }
     griddep_wait();
     griddep_launch();
-    const bool xchg = M == 1 && !SWIGLU && p.epi.xchg.world > 1;
+    const bool xchg = XCHG && M == 1 && !SWIGLU && p.epi.xchg.world > 1;
     const unsigned xseq = xchg ? *p.epi.xchg.epoch + 1u : 0u;
     unsigned xticket = 0;
     if (xchg && threadIdx.x == 0) xticket = xchg_arrive(p.epi.xchg);
@@ -279,10 +279,10 @@ static int ensure_workspace(cudaStream_t st) {
 
 struct Nvf4Cfg { int wpc, KS, bpc; size_t smem; };
 
-template <int M, int COLS, bool SWIGLU>
+template <int M, int COLS, bool SWIGLU, bool XCHG = false>
 static int launch_nvf4(Nvf4Params p, cudaStream_t st) {
     constexpr int CW = 32 * COLS;
-    auto kern = gemv_nvf4_kernel<M, COLS, SWIGLU>;
+    auto kern = gemv_nvf4_kernel<M, COLS, SWIGLU, XCHG>;
     static std::mutex mu;
     static std::unordered_map<uint64_t, Nvf4Cfg> cache;
     static bool attr_set = false;
@@ -518,7 +518,7 @@ int pgk_gemv_nvf4_allreduce_bf16(const void* A, const void* B_data, const void* 
     if (int rc = ensure_workspace(st)) return rc;
     p.A = (const uint16_t*)A; p.Bd = (const uint8_t*)B_data; p.Bs = (const uint8_t*)B_scale; p.C = (uint16_t*)out;
     p.K = K; p.N = N; p.alpha = alpha;
-    return launch_nvf4<1, 16, false>(p, st);
+    return launch_nvf4<1, 16, false, true>(p, st);
 }
 
 /* pgk_gemv_nvf4_bf16 for callers that cannot allocate (CUDA graph capture, tight serving loops): no cudaMalloc / cudaFree,
