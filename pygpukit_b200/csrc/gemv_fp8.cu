@@ -327,6 +327,13 @@ static int launch_fp8(const void* A, const void* B0, const void* S0, const void*
     return launch_fp8_kern(gemv_fp8_sb_kernel<M, NMAT, XCHG>, 16, M, A, B0, S0, B1, S1, C, K, N, epi, st, cache, attr);
 }
 
+// with peers open every M = 1 GEMV runs the XCHG instantiation (exchange off: world = 0), so that a tensor-parallel step
+// keeps ONE hot GEMV kernel in the instruction caches (measured: gemv_nvf4.cu::tp_active)
+static bool tp_active_fp8() {
+    GemvXchg x;
+    return p2p_gemv_xchg(&x) && x.world > 1;
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 static bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
@@ -389,7 +396,8 @@ static int gemv_fp8_dispatch(const void* A, const void* B0, const void* S0, cons
             if (mt == 1) rc = launch_fp8<1, 2>(am, B0, S0, B1, S1, cm, K, N, epi, st);
             else         rc = launch_fp8<2, 2>(am, B0, S0, B1, S1, cm, K, N, epi, st);
         } else {
-            if (mt == 1)      rc = launch_fp8<1, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
+            if (mt == 1 && tp_active_fp8()) rc = launch_fp8<1, 1, true>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
+            else if (mt == 1) rc = launch_fp8<1, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
             else if (mt == 2) rc = launch_fp8<2, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
             else if (mt == 3) rc = launch_fp8<3, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);
             else              rc = launch_fp8<4, 1>(am, B0, S0, nullptr, nullptr, cm, K, N, epi, st);

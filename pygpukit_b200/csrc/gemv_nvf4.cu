@@ -363,6 +363,15 @@ static int launch_nvf4(Nvf4Params p, cudaStream_t st) {
     return 0;
 }
 
+// Under tensor parallelism the row-parallel layers run the XCHG instantiation; measured at 2 GPUs (Llama-3-70B NVF4): when
+// the column-parallel GEMVs of the same step run the plain instantiation, the step alternates between two 41 KB kernels
+// and loses 2.2 us per launch to instruction fetch (132.7 vs 139.9 tok/s) -- so with peers open every M = 1 GEMV runs the
+// XCHG code (its exchange switched off by world = 0) and the step keeps one hot kernel.
+static bool tp_active() {
+    GemvXchg x;
+    return p2p_gemv_xchg(&x) && x.world > 1;
+}
+
 static bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // gemm_tc_nvf4.cu: tcgen05 skinny GEMM (exact BF16 dequantisation, weights read once for up to 64 rows)
@@ -414,7 +423,8 @@ static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C,
             else if (mt == 2) rc = launch_nvf4<2, 16, true>(p, st);
             else              rc = launch_nvf4<4, 8, true>(p, st);
         } else {
-            if (mt == 1)      rc = launch_nvf4<1, 16, false>(p, st);
+            if (mt == 1 && tp_active())  rc = launch_nvf4<1, 16, false, true>(p, st);     // see tp_active()
+            else if (mt == 1) rc = launch_nvf4<1, 16, false>(p, st);
             else if (mt == 2) rc = launch_nvf4<2, 16, false>(p, st);
             else              rc = launch_nvf4<4, 8, false>(p, st);
         }
