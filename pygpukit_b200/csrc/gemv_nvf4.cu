@@ -73,6 +73,7 @@ struct Nvf4Params {
     int K, N;            // N = number of weight columns (2*I for the fused gate/up layout)
     int KS;              // CTAs per column group
     int bpc;             // scale blocks per CTA
+    bool rt_swiglu;      // run-time SwiGLU epilogue in a non-SWIGLU instantiation
     float alpha;
     float* ws;           // [G*KS][M][32*COLS] f32 partials
     unsigned* counters;  // [G], zero between launches
@@ -111,7 +112,8 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
     }
     griddep_wait();
     griddep_launch();
-    const bool xchg = XCHG && M == 1 && !SWIGLU && p.epi.xchg.world > 1;
+    const bool swiglu = SWIGLU || p.rt_swiglu;      // rt_swiglu: the plain instantiation serving the SwiGLU layout (one hot kernel per step)
+    const bool xchg = XCHG && M == 1 && !swiglu && p.epi.xchg.world > 1;
     const unsigned xseq = xchg ? *p.epi.xchg.epoch + 1u : 0u;
     unsigned xticket = 0;
     if (xchg && threadIdx.x == 0) xticket = xchg_arrive(p.epi.xchg);
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(512) gemv_nvf4_kernel(Nvf4Params p) {
         }
         return v * inv_s[m];
     };
-    if (!SWIGLU) {
+    if (!swiglu) {
         for (int t = threadIdx.x; t < M * CW; t += blockDim.x) {
             int m = t / CW, col = t % CW, n = g * CW + col;
             if (n >= N) continue;
@@ -419,7 +421,14 @@ static int nvf4_dispatch(const void* A, const void* Bd, const void* Bs, void* C,
                  (const uint16_t*)gamma, eps};
         int rc;
         if (swiglu) {
-            if (mt == 1)      rc = launch_nvf4<1, 16, true>(p, st);
+            static const bool one_kernel = !(getenv("PGK_NVF4_ONE_KERNEL") && atoi(getenv("PGK_NVF4_ONE_KERNEL")) == 0);
+            if (mt == 1 && one_kernel) {
+                // the gate/up launch runs the SAME instantiation as qkv / o / down (SwiGLU epilogue chosen at run time):
+                // a decode step that alternates between two 41 KB GEMV kernels pays for the instruction fetch
+                p.rt_swiglu = true;
+                rc = tp_active() ? launch_nvf4<1, 16, false, true>(p, st) : launch_nvf4<1, 16, false>(p, st);
+            }
+            else if (mt == 1) rc = launch_nvf4<1, 16, true>(p, st);
             else if (mt == 2) rc = launch_nvf4<2, 16, true>(p, st);
             else              rc = launch_nvf4<4, 8, true>(p, st);
         } else {
