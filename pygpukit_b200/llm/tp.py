@@ -70,7 +70,6 @@ def combine_greedy(pairs: np.ndarray, vocab_offsets: list[int]) -> int:
     return int(vocab_offsets[best] + int(idx[best]))
 
 
-_TIMING_SKIP_EXCHANGE = __import__("os").environ.get("PGK_TP_SKIP_EXCHANGE", "0") == "1"
 _FUSED_AR = __import__("os").environ.get("PGK_TP_FUSED_AR", "1") != "0"
 
 class TensorParallel:
@@ -153,7 +152,7 @@ class TensorParallel:
         (`linear.forward_allreduce`): one token, FP8 / NVF4 weights without bias, peer buffers with the LL regions open.
         PGK_TP_FUSED_AR=0 keeps the two launches (A/B timing, parity tests)."""
         from .layers.linear import LinearFP8, LinearNVF4
-        if not (_FUSED_AR and self.world > 1 and self._p2p and self._ll and M == 1 and not _TIMING_SKIP_EXCHANGE):
+        if not (_FUSED_AR and self.world > 1 and self._p2p and self._ll and M == 1):
             return False
         if not isinstance(linear, (LinearFP8, LinearNVF4)) or linear.bias is not None:
             return False
@@ -168,8 +167,6 @@ class TensorParallel:
             return
         from .._lib import api
         from ..core.stream import current_stream_handle
-        if _TIMING_SKIP_EXCHANGE:       # timing experiment only (wrong tokens): what the step costs without any exchange
-            return
         if self._p2p and part.size % 8 == 0 and part.size <= 8192 and self._ll:
             # one decode row: LL words (payload + exchange number in one 8-byte store), one NVLink hop, no fence
             api.p2p_ll_allreduce_add_bf16(part.device_ptr, hidden.device_ptr, hidden.device_ptr, part.size,
