@@ -114,3 +114,41 @@ def test_shard_range_rejects_uneven():
         shard_range(100, 8, 0)
     with pytest.raises(ValueError):
         shard_range(1024, 4, 0, multiple=512)
+
+
+def test_shard_plan_rejects_vocabulary_remainder():
+    """Equal lm_head shards only: the logits all-gather and the 16-byte (best logit, global index) exchange both assume
+    V / world rows per rank, so a vocabulary that does not divide is refused at plan time."""
+    cfg, _ = named_config("small-qwen3", max_seq=64)
+    cfg.vocab_size = 2049
+    with pytest.raises(ValueError, match="vocab_size"):
+        shard_plan(cfg, 2, 0)
+
+
+def test_fuses_allreduce_needs_peer_buffers_and_one_row():
+    """TensorParallel.fuses_allreduce (GEMV + all-reduce in one launch) is a host decision: never without the
+    peer-memory LL regions, never for more than one row, never for BF16 weights or a layer with a bias."""
+    from pygpukit_b200.llm.layers.linear import LinearFP8, LinearNVF4
+    from pygpukit_b200.llm.tp import TensorParallel
+
+    class _FP8(LinearFP8):                      # host-only stand-ins: the decision reads shapes and the bias, nothing else
+        def __init__(self, n, k, bias=None):
+            self.in_features, self.out_features, self.bias = k, n, bias
+
+    class _NVF4(LinearNVF4):
+        def __init__(self, n, k, bias=None):
+            self.in_features, self.out_features, self.bias = k, n, bias
+
+    tp = TensorParallel(0, 2)
+    tp._p2p, tp._ll = False, True
+    assert not tp.fuses_allreduce(_FP8(4096, 2048), 1)          # NCCL fallback: two launches
+    tp._p2p = True
+    assert tp.fuses_allreduce(_FP8(4096, 2048), 1) and tp.fuses_allreduce(_NVF4(8192, 4096), 1)
+    assert not tp.fuses_allreduce(_FP8(4096, 2048), 2)          # batch rows go through the slab all-reduce
+    assert not tp.fuses_allreduce(_FP8(16384, 2048), 1)         # one LL region holds 8192 words per rank
+    assert not tp.fuses_allreduce(_FP8(4096, 2048, bias=object()), 1)
+    assert not tp.fuses_allreduce(_NVF4(4104, 4096), 1)         # NVF4 columns in 16s
+    assert not tp.fuses_allreduce(object(), 1)                  # BF16 / unknown layers
+    tp._ll = False
+    assert not tp.fuses_allreduce(_FP8(4096, 2048), 1)
+    assert not TensorParallel(0, 1).fuses_allreduce(_FP8(4096, 2048), 1)
