@@ -305,6 +305,17 @@ int pgk_moe_grouped_gemv_nvf4_ex(const void* A, int a_stride, const void* B_data
                                  const int32_t* row_expert_ids, int M, int K, int N, int expert_offset,
                                  int num_local_experts, void* stream);
 
+/* ------------------------------------------------------------------ token sampling on the device
+ * sample_token (llm/sampling.py:11-63: temperature -> softmax -> top-k -> top-p -> argmax / draw in index order) for one
+ * row of bf16 logits; replaces the D2H of the logits + NumPy that generate() does per token (models/causal.py:62-71) and
+ * the reference's sample_token_gpu (ops/sampling.py:11-41 -> native/ops/sampling/sampling.cu:336-362), whose top-k kernel
+ * is timing-dependent and whose top-p kernel does not truncate the distribution (see sampling.cu).  The uniform number is
+ * the caller's: random_val in [0, 1), or random_buf (device, one float) when not NULL -- update it and replay a graph.
+ * temperature == 0: the first maximum.  Ties at a top-k / top-p cut keep the highest indices (a stable argsort's choice).
+ * vocab_size <= 1048576, logits 16-byte aligned; token_out is an int32 device buffer. */
+int pgk_sample_token_bf16(const void* logits, int vocab_size, float temperature, int top_k, float top_p,
+                          float random_val, const float* random_buf, int32_t* token_out, void* stream);
+
 /* Decode (num_tokens == 1) forms of MoELayer.__call__ (llm/layers/moe.py:153-318).  With one token the k
  * rows can stay in slot order, so permutation / expand / gather drop out; each entry reproduces the generic
  * kernels' arithmetic exactly (bf16 only).

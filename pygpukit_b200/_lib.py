@@ -98,6 +98,7 @@ _SIGS = {
     "pgk_gemv_nvf4_allreduce_bf16": [vp, vp, vp, vp, vp, i32, i32, f32, vp],
     "pgk_gemv_nvf4_bf16_noalloc": [vp, vp, vp, vp, i32, i32, i32, f32, vp],
     "pgk_moe_combine_t1": [vp, vp, vp, vp, i32, i32, vp],
+    "pgk_sample_token_bf16": [vp, i32, f32, i32, f32, f32, vp, vp, vp],
     "pgk_fill_normal_bf16": [vp, sz, C.c_uint32, f32, vp],
     "pgk_quantize_bf16_to_fp8_block": [vp, vp, vp, i32, i32, vp],
     "pgk_decode_advance": [vp, vp, i32, vp], "pgk_decode_advance_n": [vp, vp, i32, i32, vp],

@@ -35,6 +35,7 @@ SOURCES = {
     "elementwise.cu": [],
     "attention.cu": [],
     "moe.cu": [],
+    "sampling.cu": [],
     "comm.cu": [],
     "p2p.cu": [],
     "step.cu": [],

@@ -377,7 +377,7 @@ class CausalTransformerModel:
                  gpu_sampling: bool = False, use_graph: bool = True) -> list[int]:
         """Autoregressive generation (causal.py:179-255).  temperature == 0 takes the device-resident
         greedy path (one graph replay per token, tokens read back once at the end unless an EOS id
-        must be checked); otherwise logits come back to the host for `sample_token`."""
+        must be checked); otherwise `sample_token` on the host, or on the device with gpu_sampling=True."""
         tokens = list(input_ids)
         if self._buffers is None or self._max_seq < len(tokens) + max_new_tokens:
             self.init_decode(max(self.config.max_position_embeddings, len(tokens) + max_new_tokens),
@@ -414,10 +414,18 @@ class CausalTransformerModel:
                 out = history.to_numpy()[:n]
             tokens.extend(int(v) for v in out)
             return tokens
-        # host sampling path
+        # sampling path: on the device when asked (gpu_sampling: the logits never leave the GPU, 4 bytes come back per
+        # token; ops.sampling.sample_token_gpu, same semantics as sample_token with the generator of set_sampling_seed),
+        # else the reference's host path (full logits D2H + NumPy, models/causal.py:62-71)
+        on_device = gpu_sampling and self.tp == 1
         for step in range(max_new_tokens):
-            logits = _to_float32_logits(self._full_logits_host(last))
-            nxt = sample_token(logits, temperature, top_k, top_p)
+            if on_device:
+                from ...ops.sampling import sample_token_gpu
+                row = None if b.logits is None else (b.logits if b.logits.shape[0] == 1 else b.logits.slice_rows(1))
+                nxt = sample_token_gpu(self.get_logits(last, out=row), temperature, top_k, top_p)
+            else:
+                logits = _to_float32_logits(self._full_logits_host(last))
+                nxt = sample_token(logits, temperature, top_k, top_p)
             tokens.append(nxt)
             if (eos_token_id is not None and nxt == eos_token_id) or step == max_new_tokens - 1:
                 break

@@ -1,9 +1,12 @@
-"""Greedy sampling on the device (mirror of pygpukit/ops/sampling.py:75-88)."""
+"""Sampling on the device (mirror of pygpukit/ops/sampling.py:11-141): greedy argmax, and temperature / top-k / top-p
+sampling with the semantics of pygpukit.llm.sampling.sample_token (llm/sampling.py:11-63)."""
 from __future__ import annotations
+
+import numpy as np
 
 from .._lib import api
 from ..core.array import GPUArray
-from ..core.dtypes import float_code, int32
+from ..core.dtypes import bfloat16, float_code, int32
 from ._common import _st, _validate_float_dtype
 
 
@@ -22,4 +25,40 @@ def sample_greedy_to_buf(logits: GPUArray, out_buf: GPUArray) -> None:
     api.argmax(logits.device_ptr, out_buf.device_ptr, logits.size, float_code(logits.dtype), _st())
 
 
-__all__ = ["sample_greedy", "sample_greedy_to_buf"]
+_rng = np.random.default_rng()
+
+
+def set_sampling_seed(seed: int) -> None:
+    """Seed of the host generator that supplies the uniform numbers (native.set_sampling_seed upstream)."""
+    global _rng
+    _rng = np.random.default_rng(seed)
+
+
+def _check_sampling(logits: GPUArray, temperature: float, top_p: float, fn: str) -> None:
+    if logits.dtype != bfloat16:
+        raise ValueError(f"{fn}: logits must be bfloat16 on the B200 path, got {logits.dtype}")
+    if logits.ndim not in (1, 2) or (logits.ndim == 2 and logits.shape[0] != 1):
+        raise ValueError(f"{fn} expects [vocab_size] or [1, vocab_size] logits")
+    if temperature < 0:
+        raise ValueError(f"{fn}: temperature must be >= 0")
+
+
+def sample_token_to_buf(logits: GPUArray, out_buf: GPUArray, temperature: float = 1.0, top_k: int = 0, top_p: float = 1.0,
+                        random_val: float | None = None, random_buf: GPUArray | None = None) -> None:
+    """Sampled token written to an int32 device buffer (graph-friendly: pass `random_buf`, a float32 [1] device array,
+    update it before each replay).  `random_val` in [0, 1) makes the call a pure function of its inputs."""
+    _check_sampling(logits, temperature, top_p, "sample_token_to_buf")
+    u = float(_rng.random()) if (random_val is None and random_buf is None) else float(random_val or 0.0)
+    api.sample_token_bf16(logits.device_ptr, logits.size, float(temperature), int(top_k), float(top_p), u,
+                          None if random_buf is None else random_buf.device_ptr, out_buf.device_ptr, _st())
+
+
+def sample_token_gpu(logits: GPUArray, temperature: float = 1.0, top_k: int = 0, top_p: float = 1.0,
+                     random_val: float | None = None) -> int:
+    """ops/sampling.py:11-41 signature; only the 4-byte token id comes back to the host."""
+    out = GPUArray((1,), int32)
+    sample_token_to_buf(logits, out, temperature, top_k, top_p, random_val)
+    return int(out.to_numpy()[0])
+
+
+__all__ = ["sample_greedy", "sample_greedy_to_buf", "sample_token_gpu", "sample_token_to_buf", "set_sampling_seed"]
