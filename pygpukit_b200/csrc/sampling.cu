@@ -9,8 +9,10 @@
 // "top-p" kernel scales the threshold by top_p instead of truncating the distribution.  The uniform number comes from
 // the caller (host scalar, or a device buffer for graph replay), as in those kernels' random_val argument.
 //
-// One CTA of 1024 threads; the logits (bf16, <= 300 KB) stay in L2 and are re-read by every pass with coalesced 16-byte
-// loads.  Warp w owns the contiguous index range [w * seg, (w + 1) * seg); within it lane l handles elements
+// A cluster of 8 CTAs x 1024 threads (one CTA alone is instruction-bound: 11 us per pass over 152 k logits, 485 us for
+// top-k + top-p); the logits (bf16, <= 300 KB) stay in L2 and are re-read by every pass with coalesced 16-byte loads;
+// partial results meet over distributed shared memory.  Global warp w (of 256) owns the contiguous index range
+// [w * seg, (w + 1) * seg); within it lane l handles elements
 // i * 256 + l * 8 .. + 7 of iteration i, so (warp, iteration, lane, element) is index order -- ties and the final
 // cumulative walk need that order.  Thresholds are found on the 16-bit order-preserving key of the bf16 logit (the
 // probability is a monotone function of it) by a 16-step binary search: counts for top-k, weight sums for top-p.
@@ -20,6 +22,9 @@
 #include "../../include/pgk_b200.h"
 
 #include <climits>
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
 
 namespace pgk {
 
@@ -101,12 +106,59 @@ __device__ __forceinline__ uint32_t smp_block_max_u(uint32_t v, float* red) {
     return t;
 }
 
-// f(key, index) over this thread's elements, in index order.  Four iterations' loads are issued together: a pass is a
-// chain of L2 round trips otherwise (measured: 12 us per pass over 152 k logits with one load in flight per warp).
+// ---- a cluster of kSmpCtas CTAs shares every pass: global warp g = rank * 32 + warp owns [g * seg, (g + 1) * seg).
+// A cluster reduction = block reduction, one 32-bit cell per CTA in shared memory, barrier.cluster, every CTA reads
+// the kSmpCtas cells over DSMEM in rank order (fixed order: deterministic, and identical in every CTA, so the
+// control flow that depends on it stays uniform across the cluster).  The cell alternates between two slots: a CTA
+// can only write slot s again after a later cluster barrier, which all CTAs pass after their reads of slot s.
+constexpr int kSmpCtas = 8;
+constexpr int kSmpGWarps = kSmpCtas * kSmpWarps;
+
+struct SmpCl {
+    uint32_t* xch;      // [2] shared
+    int par;
+};
+template <class Op>
+__device__ __forceinline__ uint32_t smp_cl_reduce(uint32_t v, SmpCl& cx, Op op) {
+    cg::cluster_group cl = cg::this_cluster();
+    if (threadIdx.x == 0) cx.xch[cx.par] = v;
+    cl.sync();
+    uint32_t r = *cl.map_shared_rank(&cx.xch[cx.par], 0);
+#pragma unroll
+    for (int k = 1; k < kSmpCtas; ++k) r = op(r, *cl.map_shared_rank(&cx.xch[cx.par], k));
+    cx.par ^= 1;
+    return r;
+}
+__device__ __forceinline__ float smp_sum(float v, float* red, SmpCl& cx) {
+    v = smp_block_sum(v, red);
+    return __uint_as_float(smp_cl_reduce(__float_as_uint(v), cx, [](uint32_t a, uint32_t b) {
+        return __float_as_uint(__uint_as_float(a) + __uint_as_float(b)); }));
+}
+__device__ __forceinline__ int smp_sum_i(int v, float* red, SmpCl& cx) {
+    v = smp_block_sum_i(v, red);
+    return (int)smp_cl_reduce((uint32_t)v, cx, [](uint32_t a, uint32_t b) { return a + b; });
+}
+__device__ __forceinline__ uint32_t smp_max_u(uint32_t v, float* red, SmpCl& cx) {
+    v = smp_block_max_u(v, red);
+    return smp_cl_reduce(v, cx, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
+}
+// value already uniform in the CTA (read from shared memory after a barrier)
+__device__ __forceinline__ int smp_cl_max_i(int v, SmpCl& cx) {
+    return (int)smp_cl_reduce((uint32_t)v, cx, [](uint32_t a, uint32_t b) { return (int)a > (int)b ? a : b; });
+}
+__device__ __forceinline__ int smp_cl_min_i(int v, SmpCl& cx) {
+    return (int)smp_cl_reduce((uint32_t)v, cx, [](uint32_t a, uint32_t b) { return (int)a < (int)b ? a : b; });
+}
+
+__device__ __forceinline__ int smp_gwarp() {
+    return (int)cg::this_cluster().block_rank() * kSmpWarps + (int)(threadIdx.x >> 5);
+}
+
+// f(key, index) over this thread's elements, in index order.  Four iterations' loads are issued together.
 template <class F>
 __device__ __forceinline__ void smp_foreach(const SmpParams& p, F f) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int base0 = warp * p.seg + lane * 8;
+    const int lane = threadIdx.x & 31;
+    const int base0 = smp_gwarp() * p.seg + lane * 8;
     for (int i0 = 0; i0 < p.iters; i0 += 4) {
         uint4 v[4];
 #pragma unroll
@@ -134,8 +186,9 @@ __device__ __forceinline__ void smp_foreach(const SmpParams& p, F f) {
 // Index of the `need`-th element, counted from the highest index down, among the candidates with key == c
 // (LEVEL 1: every valid element, LEVEL 2: the elements of the first filter).  1 <= need <= number of such elements.
 template <int LEVEL>
-__device__ int smp_tie_cut(const SmpParams& p, const SmpSet& set, uint32_t c, int need, int* wcnt, int* s_cut) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__device__ int smp_tie_cut(const SmpParams& p, const SmpSet& set, uint32_t c, int need, int* wcnt, int* s_cut, SmpCl& cx) {
+    cg::cluster_group cl = cg::this_cluster();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gw = smp_gwarp();
     auto cand = [&](uint32_t key, int idx) {
         return key == c && (LEVEL == 1 ? idx < p.V : smp_in1(set, key, idx, p.V));
     };
@@ -143,16 +196,17 @@ __device__ int smp_tie_cut(const SmpParams& p, const SmpSet& set, uint32_t c, in
     smp_foreach(p, [&](uint32_t key, int idx) { n += cand(key, idx) ? 1 : 0; });
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
-    __syncthreads();
     if (lane == 0) wcnt[warp] = n;
-    if (threadIdx.x == 0) *s_cut = 0;
-    __syncthreads();
-    int above = 0;
-    for (int w = warp + 1; w < kSmpWarps; ++w) above += wcnt[w];
-    if (above < need && need <= above + n) {                   // warp-uniform: exactly one warp holds the crossing
+    if (threadIdx.x == 0) *s_cut = -1;
+    cl.sync();
+    int above = 0;                                              // candidates in the global warps after this one
+    for (int g = gw + 1 + lane; g < kSmpGWarps; g += 32) above += *cl.map_shared_rank(&wcnt[g & 31], g >> 5);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) above += __shfl_xor_sync(0xffffffffu, above, o);
+    if (above < need && need <= above + n) {                   // warp-uniform: exactly one warp of the cluster
         int rem = need - above;
         for (int i = p.iters - 1; i >= 0; --i) {               // all 32 lanes stay in the loop: it shuffles
-            const int base = warp * p.seg + i * 256 + lane * 8;
+            const int base = gw * p.seg + i * 256 + lane * 8;
             uint32_t b[8];
             smp_load8(p, base, b);
             int c_l = 0;
@@ -179,24 +233,27 @@ __device__ int smp_tie_cut(const SmpParams& p, const SmpSet& set, uint32_t c, in
         }
     }
     __syncthreads();
-    return *s_cut;
+    return smp_cl_max_i(*s_cut, cx);                            // (its barrier also keeps wcnt alive until every CTA has read it)
 }
 
-__global__ void __launch_bounds__(kSmpThreads, 1) sample_token_kernel(SmpParams p) {
+__global__ void __cluster_dims__(kSmpCtas, 1, 1) __launch_bounds__(kSmpThreads, 1) sample_token_kernel(SmpParams p) {
     __shared__ float red[32];
     __shared__ int wcnt[kSmpWarps];
     __shared__ float wtot[kSmpWarps];
+    __shared__ uint32_t xch[2];
     __shared__ int s_cut, s_res;
+    cg::cluster_group cl = cg::this_cluster();
     griddep_wait();
     griddep_launch();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gw = smp_gwarp();
     const float u = p.u_buf ? *p.u_buf : p.u;
+    SmpCl cx = {xch, 0};
     if (threadIdx.x == 0) s_res = INT_MAX;
 
     // ---- the largest logit (softmax shift; its weight is exactly 1)
     uint32_t km = 0;
     smp_foreach(p, [&](uint32_t key, int idx) { if (idx < p.V) km = max(km, key); });
-    km = smp_block_max_u(km, red);
+    km = smp_max_u(km, red, cx);
     const float lmax = smp_key_value(km);
     const float sc = p.inv_t * 1.4426950408889634f;
     auto weight = [&](uint32_t key) { return exp2f((smp_key_value(key) - lmax) * sc); };
@@ -209,37 +266,37 @@ __global__ void __launch_bounds__(kSmpThreads, 1) sample_token_kernel(SmpParams 
             const uint32_t t = c | (1u << bit);
             int n = 0;
             smp_foreach(p, [&](uint32_t key, int idx) { n += (idx < p.V && key >= t) ? 1 : 0; });
-            if (smp_block_sum_i(n, red) >= p.top_k) c = t;
+            if (smp_sum_i(n, red, cx) >= p.top_k) c = t;
         }
         int ngt = 0;
         smp_foreach(p, [&](uint32_t key, int idx) { ngt += (idx < p.V && key > c) ? 1 : 0; });
-        ngt = smp_block_sum_i(ngt, red);
-        const int cut = smp_tie_cut<1>(p, set, c, p.top_k - ngt, wcnt, &s_cut);
+        ngt = smp_sum_i(ngt, red, cx);
+        const int cut = smp_tie_cut<1>(p, set, c, p.top_k - ngt, wcnt, &s_cut, cx);
         set.tk1 = c; set.cut1 = cut;
     }
     // ---- top-p: the largest key whose tail sum reaches top_p of the kept mass
     if (p.top_p < 1.f) {
         float z1 = 0.f;
         smp_foreach(p, [&](uint32_t key, int idx) { if (smp_in1(set, key, idx, p.V)) z1 += weight(key); });
-        z1 = smp_block_sum(z1, red);
+        z1 = smp_sum(z1, red, cx);
         const float target = fmaxf(p.top_p * z1, 1e-30f);
         uint32_t c = 0;
         for (int bit = 15; bit >= 0; --bit) {
             const uint32_t t = c | (1u << bit);
             float f = 0.f;
             smp_foreach(p, [&](uint32_t key, int idx) { if (key >= t && smp_in1(set, key, idx, p.V)) f += weight(key); });
-            if (smp_block_sum(f, red) >= target) c = t;
+            if (smp_sum(f, red, cx) >= target) c = t;
         }
         float sgt = 0.f;
         int ties = 0;
         smp_foreach(p, [&](uint32_t key, int idx) {
             if (smp_in1(set, key, idx, p.V)) { if (key > c) sgt += weight(key); else if (key == c) ++ties; }
         });
-        sgt = smp_block_sum(sgt, red);
-        ties = smp_block_sum_i(ties, red);
+        sgt = smp_sum(sgt, red, cx);
+        ties = smp_sum_i(ties, red, cx);
         int need = (int)ceilf((target - sgt) / weight(c));
         need = min(max(need, 1), max(ties, 1));
-        const int cut = smp_tie_cut<2>(p, set, c, need, wcnt, &s_cut);
+        const int cut = smp_tie_cut<2>(p, set, c, need, wcnt, &s_cut, cx);
         set.tk2 = c; set.cut2 = cut;
     }
     // ---- the token
@@ -248,22 +305,29 @@ __global__ void __launch_bounds__(kSmpThreads, 1) sample_token_kernel(SmpParams 
         smp_foreach(p, [&](uint32_t key, int idx) { if (key == km && smp_in2(set, key, idx, p.V)) best = min(best, idx); });
         if (best != INT_MAX) atomicMin(&s_res, best);
         __syncthreads();
-        if (threadIdx.x == 0) p.out[0] = s_res == INT_MAX ? 0 : s_res;
+        const int res = smp_cl_min_i(s_res, cx);
+        if (cl.block_rank() == 0 && threadIdx.x == 0) p.out[0] = res == INT_MAX ? 0 : res;
+        cl.sync();                                              // no CTA leaves while its cells may still be read
         return;
     }
-    // cumulative walk in index order: per-warp totals, a fixed-order prefix over the warps, then every warp walks its
-    // own range and reports the first index whose running sum exceeds u * total (the smallest reported index wins)
+    // cumulative walk in index order: per-warp totals, a fixed-order prefix over the 256 global warps, then every warp
+    // walks its own range and reports the first index whose running sum exceeds u * total (the smallest one wins)
     float z = 0.f;
     smp_foreach(p, [&](uint32_t key, int idx) { if (smp_in2(set, key, idx, p.V)) z += weight(key); });
     z = warp_sum(z);
-    __syncthreads();
     if (lane == 0) wtot[warp] = z;
-    __syncthreads();
-    float run0 = 0.f, total = 0.f;
-    for (int w = 0; w < kSmpWarps; ++w) { if (w == warp) run0 = total; total += wtot[w]; }
+    cl.sync();
+    float before = 0.f, total = 0.f;
+    for (int g = lane; g < kSmpGWarps; g += 32) {
+        const float t = *cl.map_shared_rank(&wtot[g & 31], g >> 5);
+        total += t;
+        if (g < gw) before += t;
+    }
+    total = warp_sum(total);
+    float run0 = warp_sum(before);
     const float tau = u * total;
     for (int i = 0; i < p.iters; ++i) {                         // all 32 lanes stay in the loop: it shuffles
-        const int base = warp * p.seg + i * 256 + lane * 8;
+        const int base = gw * p.seg + i * 256 + lane * 8;
         uint32_t b[8];
         smp_load8(p, base, b);
         float w8[8], s_l = 0.f;
@@ -292,17 +356,18 @@ __global__ void __launch_bounds__(kSmpThreads, 1) sample_token_kernel(SmpParams 
         if (__any_sync(0xffffffffu, found)) break;
     }
     __syncthreads();
-    if (s_res == INT_MAX) {                                     // u * total rounded up to the total: the last kept index
+    int res = smp_cl_min_i(s_res, cx);
+    if (res == INT_MAX) {                                       // u * total rounded up to the total: the last kept index
         int last = -1;
         smp_foreach(p, [&](uint32_t key, int idx) { if (smp_in2(set, key, idx, p.V) && weight(key) > 0.f) last = max(last, idx); });
         if (threadIdx.x == 0) s_cut = -1;                       // (s_cut is free here: reused as the max cell)
         __syncthreads();
         if (last >= 0) atomicMax(&s_cut, last);
         __syncthreads();
-        if (threadIdx.x == 0) p.out[0] = s_cut < 0 ? 0 : s_cut;
-        return;
+        res = max(smp_cl_max_i(s_cut, cx), 0);
     }
-    if (threadIdx.x == 0) p.out[0] = s_res;
+    if (cl.block_rank() == 0 && threadIdx.x == 0) p.out[0] = res;
+    cl.sync();                                                  // no CTA leaves while its cells may still be read
 }
 
 }  // namespace pgk
@@ -322,12 +387,12 @@ int pgk_sample_token_bf16(const void* logits, int vocab_size, float temperature,
     PGK_REQUIRE(random_buf || (random_val >= 0.f && random_val < 1.f), "sample_token failed: random_val must be in [0, 1)");
     SmpParams p = {};
     p.logits = (const uint16_t*)logits; p.V = vocab_size;
-    p.iters = (vocab_size + kSmpWarps * 256 - 1) / (kSmpWarps * 256);
+    p.iters = (vocab_size + kSmpGWarps * 256 - 1) / (kSmpGWarps * 256);
     p.seg = p.iters * 256;
     p.greedy = temperature == 0.f;
     p.inv_t = (temperature != 1.f && temperature > 0.f) ? 1.f / temperature : 1.f;
     p.top_k = top_k; p.top_p = top_p; p.u = random_val; p.u_buf = random_buf; p.out = token_out;
-    PGK_CUDA(launch(sample_token_kernel, dim3(1), dim3(kSmpThreads), 0, (cudaStream_t)stream, p));
+    PGK_CUDA(launch(sample_token_kernel, dim3(kSmpCtas), dim3(kSmpThreads), 0, (cudaStream_t)stream, p));
     return 0;
 }
 
