@@ -432,6 +432,83 @@ class CausalTransformerModel:
             last = self._decode_step_fixed_cache(nxt, len(tokens) - 1, len(tokens))
         return tokens
 
+    # ------------------------------------------------------------------ self-speculative decode
+    def set_lookahead_confirmed_pos(self, pos: int) -> None:
+        """Tokens 0 .. pos-1 are committed in every layer's cache (causal.py:1204-1211)."""
+        for blk in self.blocks:
+            blk.attn.set_confirmed_pos(pos)
+
+    def reset_lookahead_all(self) -> None:
+        for blk in self.blocks:
+            blk.attn.reset_lookahead()
+
+    def commit_lookahead_all(self, n_accepted: int) -> None:
+        for blk in self.blocks:
+            blk.attn.commit_lookahead(n_accepted)
+
+    def get_lookahead_confirmed_pos(self) -> int:
+        return self.blocks[0].attn.get_confirmed_pos()
+
+    def _draft_forward_early_layers(self, token_id: int, position: int, context_len: int, num_draft_layers: int) -> GPUArray:
+        """The first `num_draft_layers` blocks as the draft model (causal.py:1036-1083): hidden [1, H] BEFORE the final
+        norm.  It writes the early layers' K/V at `position`; the verification pass overwrites those rows."""
+        b = self.buffers
+        hidden = self._embed([token_id], 1, position, b)
+        for blk in self.blocks[:max(0, min(num_draft_layers, len(self.blocks)))]:
+            blk.decode(hidden, position, context_len, b)
+        return hidden
+
+    def _draft_get_logits(self, hidden: GPUArray) -> GPUArray:
+        """final norm + lm_head on the draft's hidden state (causal.py:1085-1094)."""
+        return self.get_logits(self._final(hidden, self.buffers))
+
+    def decode_step_self_speculative_lookahead(self, token_id: int, max_draft_tokens: int = 4,
+                                               draft_layers: int = 8) -> tuple[list[int], dict]:
+        """One self-speculative step on the fixed cache (causal.py:1096-1198): the early layers draft
+        `max_draft_tokens` greedy tokens, the full model verifies them in ONE batched pass, tokens are accepted up to
+        the first disagreement (the full model's token replaces the rejected draft).  Call
+        `set_lookahead_confirmed_pos(prefill_len)` after the prefill.  Greedy argmaxes run on the device (4 bytes per
+        token come back, not the logits).  The reference re-runs the accepted tokens one by one after a partial accept;
+        that is not needed here: the verification pass has already written, for every layer, the K/V rows of exactly
+        the inputs that were accepted (input i sits at position confirmed + i), and rows past the committed position
+        are never read."""
+        if self.tp != 1:
+            raise NotImplementedError("self-speculative decode runs on one GPU (the draft needs the full lm_head)")
+        b = self.buffers
+        n_draft = int(max_draft_tokens)
+        if not 1 <= n_draft <= b.max_batch_size:
+            raise ValueError(f"max_draft_tokens must be in [1, max_batch_size = {b.max_batch_size}]")
+        confirmed = self.get_lookahead_confirmed_pos()
+        if confirmed + n_draft > self._max_seq:
+            raise ValueError(f"speculating {n_draft} tokens from position {confirmed} exceeds the fixed cache ({self._max_seq})")
+        V = self._head.shape[0]
+        tok = GPUArray((max(n_draft, 1),), int32)
+        # 1. draft with the early layers
+        self.reset_lookahead_all()
+        draft, cur = [], int(token_id)
+        for i in range(n_draft):
+            hidden = self._draft_forward_early_layers(cur, confirmed + i, confirmed + i + 1, draft_layers)
+            logits = self._draft_get_logits(hidden)
+            api.argmax_rows(logits.device_ptr, tok.device_ptr, None, 1, V, 2, _st())
+            cur = int(tok.to_numpy()[0])
+            draft.append(cur)
+        # 2. verify with the full model in one batched pass
+        self.reset_lookahead_all()
+        verify_input = [int(token_id)] + draft[:-1]
+        hidden = self._decode_step_fixed_cache_batch(verify_input, confirmed, confirmed + len(verify_input))
+        logits = self.get_logits(hidden)
+        api.argmax_rows(logits.device_ptr, tok.device_ptr, None, len(verify_input), V, 2, _st())
+        target = [int(t) for t in tok.to_numpy()[:len(verify_input)]]
+        # 3. accept up to the first disagreement
+        accepted = []
+        for d, t in zip(draft, target):
+            accepted.append(t)
+            if t != d:
+                break
+        self.commit_lookahead_all(len(accepted))
+        stats = {"draft_count": len(draft), "accepted_count": sum(1 for a, d in zip(accepted, draft) if a == d)}
+        return accepted, stats
+
     # ------------------------------------------------------------------ accounting
     def weight_bytes_per_token(self) -> int:
         """Algorithmic weight bytes one decode token streams on this rank."""
