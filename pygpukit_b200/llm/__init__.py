@@ -5,7 +5,7 @@ from .buffers import DecodeBuffers, PrefillBuffers
 from .config import (GPT2_SPEC, LLAMA_SPEC, MIXTRAL_SPEC, MODEL_SPECS, QWEN2_SPEC, QWEN3_MOE_SPEC, QWEN3_SPEC,
                      GPT2Config, LlamaConfig, ModelSpec, Qwen3Config, TransformerConfig, detect_model_spec,
                      named_config)
-from .decode import DecodeBatch, DecodeM1, DecodeM1Graph, DecodeSpeculative, DecodeStrategy
+from .decode import DecodeBatch, DecodeJacobi, DecodeM1, DecodeM1Graph, DecodeSpeculative, DecodeStrategy
 from .layers import (MLP, Attention, Linear, LinearBF16, LinearFP8, LinearNVF4, MoELayer, Norm, TransformerBlock,
                      apply_rotary_pos_emb_numpy, precompute_freqs_cis)
 from .models import CausalTransformerModel, GPT2Model, LlamaModel, QwenModel

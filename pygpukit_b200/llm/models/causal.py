@@ -509,6 +509,73 @@ class CausalTransformerModel:
         stats = {"draft_count": len(draft), "accepted_count": sum(1 for a, d in zip(accepted, draft) if a == d)}
         return accepted, stats
 
+    # ------------------------------------------------------------------ Jacobi decode
+    def _argmax_tokens(self, hidden: GPUArray, scratch: GPUArray) -> list[int]:
+        """greedy token of every row of final-normed hidden states: lm_head + row argmax on the device"""
+        M = hidden.shape[0]
+        logits = self.get_logits(hidden)
+        api.argmax_rows(logits.device_ptr, scratch.device_ptr, None, M, self._head.shape[0], 2, _st())
+        return [int(t) for t in scratch.to_numpy()[:M]]
+
+    def _init_jacobi_guess_lookahead(self, last_token: int, n_tokens: int, strategy: str) -> list[int]:
+        """Initial guess of the next n_tokens (causal.py:1305-1355): "repeat" the last token, the "ngram" cache of
+        earlier steps, or a sequential "greedy" decode on the lookahead rows (exact, but as slow as plain decoding)."""
+        if strategy == "repeat":
+            return [int(last_token)] * n_tokens
+        if strategy == "ngram":
+            cached = getattr(self, "_ngram_cache", {}).get(int(last_token))
+            return list(cached[:n_tokens]) if cached is not None and len(cached) >= n_tokens else [int(last_token)] * n_tokens
+        if strategy == "greedy":
+            confirmed = self.get_lookahead_confirmed_pos()
+            scratch = GPUArray((1,), int32)
+            guess, cur = [], int(last_token)
+            for i in range(n_tokens):
+                cur = self._argmax_tokens(self._decode_step_fixed_cache(cur, confirmed + i, confirmed + i + 1), scratch)[0]
+                guess.append(cur)
+            self.reset_lookahead_all()
+            return guess
+        raise ValueError(f"Unknown init strategy: {strategy}")
+
+    def decode_step_jacobi_lookahead(self, token_id: int, n_tokens: int = 8, max_iter: int = 3,
+                                     init_strategy: str = "repeat") -> tuple[list[int], dict]:
+        """One Jacobi step on the fixed cache (causal.py:1357-1476): guess n_tokens future tokens, run the batched
+        forward pass on [token, guess[:-1]], replace the guess by the row argmaxes, repeat up to max_iter times or until
+        nothing changes.  Output token i is the model's greedy token whenever the inputs before it were right, so the
+        accepted tokens are the prefix on which the last two iterations agree PLUS the first token after it (computed
+        from inputs that are all confirmed; the reference stops one token earlier).  No re-run after a partial accept:
+        row confirmed + i of every layer's cache already holds the K/V of input i, which is an accepted token."""
+        if self.tp != 1:
+            raise NotImplementedError("Jacobi decode runs on one GPU (row argmaxes over the full vocabulary)")
+        b = self.buffers
+        n = int(n_tokens)
+        if not 1 <= n <= b.max_batch_size:
+            raise ValueError(f"n_tokens must be in [1, max_batch_size = {b.max_batch_size}]")
+        confirmed = self.get_lookahead_confirmed_pos()
+        if confirmed + n > self._max_seq:
+            raise ValueError(f"decoding {n} tokens from position {confirmed} exceeds the fixed cache ({self._max_seq})")
+        guess = self._init_jacobi_guess_lookahead(token_id, n, init_strategy)
+        scratch = GPUArray((n,), int32)
+        prev, converged, iterations = None, False, 0
+        for _ in range(max(1, int(max_iter))):
+            iterations += 1
+            self.reset_lookahead_all()
+            hidden = self._decode_step_fixed_cache_batch([int(token_id)] + guess[:-1], confirmed, confirmed + n)
+            new = self._argmax_tokens(hidden, scratch)
+            prev, guess = guess, new
+            if new == prev:
+                converged = True
+                break
+        accepted = []
+        for i in range(n):                         # guess[i] is right if prev[0 .. i-1] were: keep it, stop after a change
+            accepted.append(guess[i])
+            if guess[i] != prev[i]:
+                break
+        self.commit_lookahead_all(len(accepted))
+        if not hasattr(self, "_ngram_cache"):
+            self._ngram_cache = {}
+        self._ngram_cache[int(token_id)] = list(accepted)
+        return accepted, {"iterations": iterations, "converged": converged, "accepted_count": len(accepted)}
+
     # ------------------------------------------------------------------ accounting
     def weight_bytes_per_token(self) -> int:
         """Algorithmic weight bytes one decode token streams on this rank."""

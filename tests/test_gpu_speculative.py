@@ -64,3 +64,50 @@ def test_full_depth_draft_is_always_accepted():
     assert steps <= 13
     with pytest.raises(ValueError):
         model.decode_step_self_speculative_lookahead(got[-1], 64, 1)      # more drafts than max_batch_size
+
+
+def _jacobi(model, prompt, n_new, n_tokens, max_iter, init, via_strategy=False):
+    hidden = model.prefill(prompt)
+    last = hidden.row(hidden.shape[0] - 1).view((1, hidden.shape[1]))
+    tok = int(np.argmax(bf16_bits_to_f32(model.get_logits(last).to_numpy()[0])))
+    out, steps, iters, full = [tok], 0, 0, 0
+    model.set_lookahead_confirmed_pos(len(prompt))
+    strat = llm.DecodeJacobi(n_tokens, max_iter, init)
+    strat.bind(model)
+    while len(out) < n_new:
+        pos = len(prompt) + len(out) - 1
+        if via_strategy:
+            accepted, new_pos, stats = strat.step_jacobi(tok, pos, pos + 1)
+            assert new_pos == pos + len(accepted)
+        else:
+            assert model.get_lookahead_confirmed_pos() == pos
+            accepted, stats = model.decode_step_jacobi_lookahead(tok, n_tokens, max_iter, init)
+        assert 1 <= len(accepted) <= n_tokens and stats["accepted_count"] == len(accepted)
+        assert 1 <= stats["iterations"] <= max_iter and (not stats["converged"] or len(accepted) == n_tokens)
+        out.extend(accepted)
+        steps += 1
+        iters += stats["iterations"]
+        full += int(len(accepted) == n_tokens)
+        tok = accepted[-1]
+    return out[:n_new], steps, iters, full
+
+
+@pytest.mark.parametrize("n_tokens,max_iter,init,via_strategy", [(4, 3, "repeat", False), (8, 3, "repeat", True),
+                                                                 (4, 2, "ngram", False), (4, 1, "greedy", False)])
+def test_jacobi_tokens_are_the_models_greedy_tokens(n_tokens, max_iter, init, via_strategy):
+    """Jacobi decode (causal.py:1357-1476, decode/jacobi.py) emits the greedy continuation whatever the guesses were;
+    n_tokens = 8 runs the projections on the tcgen05 GEMM, so, as for every batched pass, only BF16-resolution ties may
+    differ from the oracle's single-token steps."""
+    name, fmt = "small-qwen3", "fp8"
+    model = _build(name, fmt)
+    rng = np.random.default_rng(3)
+    prompt = [int(t) for t in rng.integers(0, model.config.vocab_size, 12)]
+    exp, margins, tops = _oracle_tokens((name, fmt), model, prompt, 128)
+    got, steps, iters, full = _jacobi(model, prompt, N_NEW, n_tokens, max_iter, init, via_strategy)
+    ok = _check_tokens(list(prompt) + got, exp[:len(prompt) + N_NEW], margins, len(prompt), tops)
+    assert ok >= N_NEW // 4, f"only {ok} tokens before a tie"
+    assert steps <= N_NEW and iters <= steps * max_iter
+    if init == "greedy":                           # the guess is the answer: (almost) every step accepts all n tokens
+        assert full >= 0.8 * steps, (full, steps)
+    with pytest.raises(ValueError):
+        model.decode_step_jacobi_lookahead(got[-1], 4, 3, "nonsense")
