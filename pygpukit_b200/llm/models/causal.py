@@ -432,6 +432,34 @@ class CausalTransformerModel:
             last = self._decode_step_fixed_cache(nxt, len(tokens) - 1, len(tokens))
         return tokens
 
+    def generate_stream(self, input_ids: list[int], max_new_tokens: int = 20, temperature: float = 1.0, top_k: int = 50,
+                        top_p: float = 0.9, eos_token_id: int | None = None, gpu_sampling: bool = False):
+        """generate() as a generator (causal.py:257-322): yields each new token as soon as it exists.  temperature == 0
+        and gpu_sampling keep the logits on the device (4 bytes per token come back); otherwise `sample_token` runs on
+        the host, as upstream."""
+        from ...ops.sampling import sample_token_gpu
+        tokens = list(input_ids)
+        if max_new_tokens <= 0:
+            return
+        if self._buffers is None or self._max_seq < len(tokens) + max_new_tokens:
+            self.init_decode(max(self.config.max_position_embeddings, len(tokens) + max_new_tokens),
+                             max_batch_size=min(64, max(1, len(tokens))))
+        b = self.buffers
+        on_device = (gpu_sampling or temperature == 0) and self.tp == 1
+        hidden = self.prefill(tokens)
+        last = hidden.row(hidden.shape[0] - 1).view((1, hidden.shape[1]))
+        for step in range(max_new_tokens):
+            if on_device:
+                row = None if b.logits is None else (b.logits if b.logits.shape[0] == 1 else b.logits.slice_rows(1))
+                nxt = sample_token_gpu(self.get_logits(last, out=row), temperature, top_k, top_p)
+            else:
+                nxt = sample_token(_to_float32_logits(self._full_logits_host(last)), temperature, top_k, top_p)
+            tokens.append(nxt)
+            yield nxt
+            if (eos_token_id is not None and nxt == eos_token_id) or step == max_new_tokens - 1:
+                return
+            last = self._decode_step_fixed_cache(nxt, len(tokens) - 1, len(tokens))
+
     # ------------------------------------------------------------------ self-speculative decode (SURVEY 8f-4)
     def set_lookahead_confirmed_pos(self, pos: int) -> None:
         """Tokens 0 .. pos-1 are committed in every layer's cache (causal.py:1204-1211)."""

@@ -118,3 +118,24 @@ def test_generate_with_gpu_sampling():
         ops.set_sampling_seed(1234)
         runs.append(m.generate(prompt, 12, temperature=1.0, top_k=50, top_p=0.95, gpu_sampling=True))
     assert runs[0] == runs[1] and all(0 <= t < m.config.vocab_size for t in runs[0])
+
+
+def test_generate_stream_yields_the_tokens_of_generate():
+    """generate_stream (causal.py:257-322): greedy streaming == generate(); with gpu_sampling and one seed, the same run."""
+    from pygpukit_b200 import llm
+
+    def fresh():
+        m = llm.build_random_model("tiny-qwen3", "fp8", max_seq=96, seed=7, std=0.05)
+        m.init_decode(96, max_batch_size=16)
+        return m
+
+    prompt = [3, 17, 99, 250, 7]
+    greedy = fresh().generate(prompt, 10, temperature=0.0)
+    assert list(fresh().generate_stream(prompt, 10, temperature=0.0)) == greedy[len(prompt):]
+    ops.set_sampling_seed(99)
+    a = list(fresh().generate_stream(prompt, 10, temperature=0.9, top_k=40, top_p=0.9, gpu_sampling=True))
+    ops.set_sampling_seed(99)
+    bb = fresh().generate(prompt, 10, temperature=0.9, top_k=40, top_p=0.9, gpu_sampling=True)[len(prompt):]
+    assert a == bb and len(a) == 10
+    gen = fresh().generate_stream(prompt, 10, temperature=0.0, eos_token_id=greedy[len(prompt) + 2])
+    assert list(gen) == greedy[len(prompt):len(prompt) + 3]                # stops after yielding the EOS token
