@@ -432,6 +432,20 @@ class CausalTransformerModel:
             last = self._decode_step_fixed_cache(nxt, len(tokens) - 1, len(tokens))
         return tokens
 
+    def snapshot_kv_cache(self) -> list[tuple[np.ndarray, np.ndarray]]:
+        """Every layer's K / V cache on the host (causal.py:1003-1015): BF16 bit patterns, [sequences x n_kv, max_seq,
+        head_dim].  The speculative / Jacobi paths here do not need it (lookahead pointers); kept for callers that do."""
+        return [(blk.attn._k_cache.to_numpy().copy(), blk.attn._v_cache.to_numpy().copy()) for blk in self.blocks]
+
+    def restore_kv_cache(self, snapshot: list[tuple[np.ndarray, np.ndarray]]) -> None:
+        """Copy a snapshot back INTO the existing cache arrays (causal.py:1017-1034): device pointers are unchanged, so
+        a captured decode graph stays valid."""
+        if len(snapshot) != len(self.blocks):
+            raise ValueError(f"snapshot holds {len(snapshot)} layers, the model has {len(self.blocks)}")
+        for blk, (k_np, v_np) in zip(self.blocks, snapshot):
+            blk.attn._k_cache.copy_from_numpy(np.ascontiguousarray(k_np, np.uint16))
+            blk.attn._v_cache.copy_from_numpy(np.ascontiguousarray(v_np, np.uint16))
+
     def generate_stream(self, input_ids: list[int], max_new_tokens: int = 20, temperature: float = 1.0, top_k: int = 50,
                         top_p: float = 0.9, eos_token_id: int | None = None, gpu_sampling: bool = False):
         """generate() as a generator (causal.py:257-322): yields each new token as soon as it exists.  temperature == 0

@@ -111,3 +111,24 @@ def test_jacobi_tokens_are_the_models_greedy_tokens(n_tokens, max_iter, init, vi
         assert full >= 0.8 * steps, (full, steps)
     with pytest.raises(ValueError):
         model.decode_step_jacobi_lookahead(got[-1], 4, 3, "nonsense")
+
+
+def test_kv_cache_snapshot_restore_round_trip():
+    """snapshot_kv_cache / restore_kv_cache (causal.py:1003-1034): after steps that overwrite cache rows, restoring the
+    snapshot brings back the same bits, in the same device arrays (pointers unchanged), and the same next token."""
+    model = _build("tiny-qwen3", "fp8")
+    prompt = [5, 99, 1023, 77, 300, 12]
+    hidden = model.prefill(prompt)
+    ptrs = [(b.attn._k_cache.device_ptr, b.attn._v_cache.device_ptr) for b in model.blocks]
+    snap = model.snapshot_kv_cache()
+    pos = len(prompt)
+    h1 = model._decode_step_fixed_cache(7, pos, pos + 1).to_numpy().copy()
+    model._decode_step_fixed_cache(9, pos, pos + 1)                     # another token overwrites row `pos`
+    assert any(not np.array_equal(b.attn._k_cache.to_numpy(), s[0]) for b, s in zip(model.blocks, snap))
+    model.restore_kv_cache(snap)
+    for b, (k, v), (pk, pv) in zip(model.blocks, snap, ptrs):
+        assert np.array_equal(b.attn._k_cache.to_numpy(), k) and np.array_equal(b.attn._v_cache.to_numpy(), v)
+        assert (b.attn._k_cache.device_ptr, b.attn._v_cache.device_ptr) == (pk, pv)
+    assert np.array_equal(model._decode_step_fixed_cache(7, pos, pos + 1).to_numpy(), h1)
+    with pytest.raises(ValueError):
+        model.restore_kv_cache(snap[:-1])
