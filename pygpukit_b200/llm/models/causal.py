@@ -29,6 +29,7 @@ from ..config import ModelSpec, TransformerConfig
 from ..layers.block import TransformerBlock
 from ..layers.linear import can_fuse_norm
 from ..layers.norm import Norm
+from ..decode.accept import accept_jacobi, accept_speculative
 from ..sampling import sample_token
 
 
@@ -542,11 +543,7 @@ class CausalTransformerModel:
         api.argmax_rows(logits.device_ptr, tok.device_ptr, None, len(verify_input), V, 2, _st())
         target = [int(t) for t in tok.to_numpy()[:len(verify_input)]]
         # 3. accept up to the first disagreement
-        accepted = []
-        for d, t in zip(draft, target):
-            accepted.append(t)
-            if t != d:
-                break
+        accepted = accept_speculative(draft, target)
         self.commit_lookahead_all(len(accepted))
         stats = {"draft_count": len(draft), "accepted_count": sum(1 for a, d in zip(accepted, draft) if a == d)}
         return accepted, stats
@@ -607,11 +604,7 @@ class CausalTransformerModel:
             if new == prev:
                 converged = True
                 break
-        accepted = []
-        for i in range(n):                         # guess[i] is right if prev[0 .. i-1] were: keep it, stop after a change
-            accepted.append(guess[i])
-            if guess[i] != prev[i]:
-                break
+        accepted = accept_jacobi(prev, guess)      # guess[i] is right if prev[0 .. i-1] were: keep it, stop after a change
         self.commit_lookahead_all(len(accepted))
         if not hasattr(self, "_ngram_cache"):
             self._ngram_cache = {}
