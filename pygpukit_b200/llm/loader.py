@@ -212,6 +212,12 @@ def load_gpt2_from_safetensors(model_path: str, dtype: str = "bfloat16") -> Caus
     return load_model_from_safetensors(model_path, dtype, GPT2_SPEC)
 
 
+def load_mixtral_from_safetensors(model_path: str, dtype: str = "bfloat16") -> CausalTransformerModel:
+    """Mixtral MoE checkpoint (loader.py:111-130): the generic loader with the Mixtral tensor names."""
+    from .config import MIXTRAL_SPEC
+    return load_model_from_safetensors(model_path, dtype, MIXTRAL_SPEC)
+
+
 def load_llama_from_safetensors(model_path: str, dtype: str = "bfloat16") -> CausalTransformerModel:
     return load_model_from_safetensors(model_path, dtype, MODEL_SPECS["llama"])
 
@@ -280,6 +286,6 @@ def save_model_to_safetensors(model: CausalTransformerModel, directory: str) -> 
     return path
 
 
-__all__ = ["load_model_from_safetensors", "load_gpt2_from_safetensors", "load_llama_from_safetensors",
+__all__ = ["load_model_from_safetensors", "load_gpt2_from_safetensors", "load_llama_from_safetensors", "load_mixtral_from_safetensors",
            "load_qwen3_from_safetensors", "save_model_to_safetensors", "config_from_hf"]
 _ = (bfloat16, uint8)

@@ -52,3 +52,14 @@ def test_rejects_unknown_dtype(tmp_path):
         f.write(len(hdr).to_bytes(8, "little") + hdr + b"\0" * 8)
     with pytest.raises(ValueError):
         load_safetensors(path)
+
+
+def test_llm_exports_legacy_names():
+    """Names of pygpukit/llm/__init__.py that are aliases upstream (models/causal.py:1496-1501) resolve to the same classes."""
+    from pygpukit_b200 import llm
+    assert llm.RMSNorm is llm.Norm and llm.LayerNorm is llm.Norm
+    assert llm.LlamaAttention is llm.Attention and llm.CausalSelfAttention is llm.Attention
+    assert llm.LlamaMLP is llm.MLP and llm.LlamaBlock is llm.TransformerBlock
+    assert llm.ShardedSafeTensorsFile is llm.SafeTensorsFile
+    for name in ("load_mixtral_from_safetensors", "TensorInfo", "DecodeSpeculative", "DecodeJacobi", "sample_token"):
+        assert hasattr(llm, name)
