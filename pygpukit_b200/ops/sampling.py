@@ -61,4 +61,36 @@ def sample_token_gpu(logits: GPUArray, temperature: float = 1.0, top_k: int = 0,
     return int(out.to_numpy()[0])
 
 
-__all__ = ["sample_greedy", "sample_greedy_to_buf", "sample_token_gpu", "sample_token_to_buf", "set_sampling_seed"]
+def sample_multinomial(logits: GPUArray, temperature: float) -> int:
+    """ops/sampling.py:91-105: draw from softmax(logits / temperature)."""
+    if temperature <= 0:
+        raise ValueError("sample_multinomial: temperature must be > 0")
+    return sample_token_gpu(logits, temperature, 0, 1.0)
+
+
+def sample_topk(logits: GPUArray, top_k: int, temperature: float) -> int:
+    """ops/sampling.py:108-123: draw among the top_k largest logits (ties at the cut: highest indices)."""
+    if temperature <= 0 or top_k <= 0:
+        raise ValueError("sample_topk: temperature and top_k must be > 0")
+    return sample_token_gpu(logits, temperature, top_k, 1.0)
+
+
+def sample_topp(logits: GPUArray, top_p: float, temperature: float) -> int:
+    """ops/sampling.py:126-141 with llm.sampling.sample_token's nucleus rule: the smallest set of most probable tokens
+    whose mass reaches top_p (the reference's kernel scales its threshold by top_p instead of truncating)."""
+    if temperature <= 0 or not 0 < top_p <= 1:
+        raise ValueError("sample_topp: temperature must be > 0 and top_p in (0, 1]")
+    return sample_token_gpu(logits, temperature, 0, top_p)
+
+
+def sample_topk_to_buf_ptr(logits: GPUArray, result_buf: GPUArray, random_val_buf: GPUArray, top_k: int,
+                           temperature: float) -> None:
+    """ops/sampling.py:44-73: top-k sampling for graph replay -- the uniform number is read from `random_val_buf`
+    (float32 [1] on the device), the token goes to `result_buf` (int32 [1]); nothing returns to the host."""
+    if temperature <= 0 or top_k <= 0:
+        raise ValueError("sample_topk_to_buf_ptr: temperature and top_k must be > 0")
+    sample_token_to_buf(logits, result_buf, temperature, top_k, 1.0, random_buf=random_val_buf)
+
+
+__all__ = ["sample_greedy", "sample_greedy_to_buf", "sample_token_gpu", "sample_token_to_buf", "set_sampling_seed",
+           "sample_multinomial", "sample_topk", "sample_topp", "sample_topk_to_buf_ptr"]

@@ -139,3 +139,25 @@ def test_generate_stream_yields_the_tokens_of_generate():
     assert a == bb and len(a) == 10
     gen = fresh().generate_stream(prompt, 10, temperature=0.0, eos_token_id=greedy[len(prompt) + 2])
     assert list(gen) == greedy[len(prompt):len(prompt) + 3]                # stops after yielding the EOS token
+
+
+def test_reference_named_sampling_ops():
+    """sample_multinomial / sample_topk / sample_topp / sample_topk_to_buf_ptr (ops/sampling.py:44-141) are
+    sample_token_gpu with the matching filters; seeded, they give what it gives."""
+    V = 5000
+    lg = f32(bf16((np.random.default_rng(8).standard_normal(V) * 2).astype(np.float32)))
+    g = gk.from_numpy(bf16(lg))
+    for fn, args, ref in ((ops.sample_multinomial, (0.8,), (0.8, 0, 1.0)), (ops.sample_topk, (30, 0.8), (0.8, 30, 1.0)),
+                          (ops.sample_topp, (0.9, 0.8), (0.8, 0, 0.9))):
+        ops.set_sampling_seed(5)
+        a = [fn(g, *args) for _ in range(6)]
+        ops.set_sampling_seed(5)
+        assert a == [ops.sample_token_gpu(g, *ref) for _ in range(6)]
+    out = gk.zeros((1,), gk.int32)
+    ub = gk.from_numpy(np.array([0.625], np.float32))
+    ops.sample_topk_to_buf_ptr(g, out, ub, 30, 0.8)
+    assert int(out.to_numpy()[0]) == ops.sample_token_gpu(g, 0.8, 30, 1.0, random_val=0.625)
+    kth = np.sort(lg)[-30]
+    assert lg[int(out.to_numpy()[0])] >= kth
+    with pytest.raises(ValueError):
+        ops.sample_topk(g, 0, 1.0)
